@@ -1,0 +1,280 @@
+/*
+ * ksa_replay.h — C ABI of libksareplay, the B200 (sm_100a) batched replay engine for the
+ * kube-sqs-autoscaler scaling policy.
+ *
+ * The reference (Go, /root/reference) has no FFI; its interface for this path is in-process:
+ *   Run(p *scale.PodAutoScaler, sqs *kubesqs.SqsClient)        main.go:35
+ *   (*SqsClient).NumMessages() (int, error)                    sqs/sqs.go:45
+ *   (*PodAutoScaler).ScaleUp(ctx) error / ScaleDown(ctx) error scale/scale.go:54,81
+ * parameterised by the flag globals main.go:16-33,83-91 and the PodAutoScaler struct
+ * scale/scale.go:21-29. The entry points below are what a cgo binding for a batched replay of
+ * that path binds (INTEGRATION.md shows the Go side): the SQS responses become an int64
+ * depth array [T][A][N], the Deployment's Spec.Replicas becomes an int32 register per trace.
+ *
+ * Conventions
+ *  - Plain C types only. All `*_dev` pointers are CUDA device pointers on the CURRENT device of
+ *    the calling thread (cudaSetDevice / ksa_set_device); `stream` is a cudaStream_t passed as
+ *    void* (NULL = legacy default stream). All launches are asynchronous on that stream.
+ *  - Every function returns 0 (KSA_OK) or a negative KSA_E* code; ksa_last_error() returns the
+ *    thread-local message of the last failure. Nothing aborts, nothing falls back to the CPU.
+ *  - The caller owns every buffer. The replay entry points allocate nothing.
+ *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
+ *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
+ *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.
+ *  - Row layout: element (t, a, n) of depth is depth[(t*A + a)*ld + n]; replicas and events rows
+ *    use the same pitch: replicas[t*ld + n], events[t*ld + n]. ld >= N, in ELEMENTS.
+ *    Fast (vectorised) path: ld % 16 == 0 and all base pointers 32-byte aligned (cudaMalloc gives
+ *    256); anything else silently takes the scalar kernel (same results, lower bandwidth).
+ */
+#ifndef KSA_REPLAY_H
+#define KSA_REPLAY_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KSA_ABI_VERSION 1
+
+/* ---- status codes --------------------------------------------------------------------- */
+#define KSA_OK 0
+#define KSA_EINVAL (-1)  /* bad argument (poll<=0, T/N/ld/A out of range, NULL pointer, ...)   */
+#define KSA_ECUDA (-2)   /* a CUDA runtime call failed; message carries cudaGetErrorString     */
+#define KSA_ENOMEM (-3)  /* an allocating helper (ksa_dev_alloc, pipeline create) failed        */
+#define KSA_ELIMIT (-4)  /* a documented size limit was exceeded                                */
+
+/* ---- event bits: one per log line of the reference ------------------------------------- */
+#define KSA_EV_UP_APPLIED 0x01   /* "Scale up successful"               scale/scale.go:77  */
+#define KSA_EV_DOWN_APPLIED 0x02 /* "Scale down successful"             scale/scale.go:105 */
+#define KSA_EV_UP_NOOP 0x04      /* "More than max pods running"        scale/scale.go:63  */
+#define KSA_EV_DOWN_NOOP 0x08    /* "Less than min pods running"        scale/scale.go:90  */
+#define KSA_EV_UP_COOL 0x10      /* "Waiting for cool down, skipping scale up"   main.go:53 */
+#define KSA_EV_DOWN_COOL 0x20    /* "Waiting for cool down, skipping scale down" main.go:67 */
+
+/* ---- attribute axis: order of sqs.DefaultAttributeNames, sqs/sqs.go:28-32 ---------------- */
+#define KSA_ATTR_MESSAGES 0x1u             /* ApproximateNumberOfMessages           */
+#define KSA_ATTR_MESSAGES_DELAYED 0x2u     /* ApproximateNumberOfMessagesDelayed    */
+#define KSA_ATTR_MESSAGES_NOT_VISIBLE 0x4u /* ApproximateNumberOfMessagesNotVisible */
+#define KSA_MAX_ATTRS 3
+
+/*
+ * The policy record: the flag globals of main.go:16-25 (defaults main.go:83-91) plus the fields
+ * of scale.PodAutoScaler (scale/scale.go:21-29). Pod counts are carried as Go `int` (int64) and
+ * truncated with int32(...) inside the library exactly where scale.go does (:62,66-68,89,94-96).
+ * Durations are Go time.Duration (int64 nanoseconds) and are converted to ticks inside the
+ * library: cool_ticks = max(0, ceil(cool/poll)).
+ */
+typedef struct ksa_policy {
+  int64_t scale_up_messages;       /* --scale-up-messages    main.go:86  (n >= this  => up)   */
+  int64_t scale_down_messages;     /* --scale-down-messages  main.go:87  (n <= this  => down) */
+  int64_t max_pods;                /* --max-pods             main.go:90                       */
+  int64_t min_pods;                /* --min-pods             main.go:91                       */
+  int64_t scale_up_pods;           /* --scale-up-pods        main.go:88                       */
+  int64_t scale_down_pods;         /* --scale-down-pods      main.go:89                       */
+  int64_t poll_period_ns;          /* --poll-period          main.go:83  must be > 0          */
+  int64_t scale_up_cool_down_ns;   /* --scale-up-cool-down   main.go:85                       */
+  int64_t scale_down_cool_down_ns; /* --scale-down-cool-down main.go:84                       */
+  uint32_t attr_mask;              /* --attribute-names      main.go:93,103-110 (KSA_ATTR_*)  */
+  uint32_t reserved;               /* must be 0                                               */
+} ksa_policy;
+
+/*
+ * Per-trace carry state (structure of arrays, device memory, N elements each). It is what the
+ * reference keeps between ticks: Spec.Replicas in the cluster (scale/scale.go:60,87) and the two
+ * stamps lastScaleUpTime / lastScaleDownTime (main.go:37-38,62,76), the stamps expressed as the
+ * absolute tick index at which they were taken (0 = process start). Replay calls read it,
+ * advance it by T ticks and write it back, so a trace can be replayed in any number of chunks.
+ */
+typedef struct ksa_state {
+  int32_t* replicas_dev;       /* [N] current replica count                          */
+  int64_t* last_up_tick_dev;   /* [N] tick of the last lastScaleUpTime stamp, >= 0   */
+  int64_t* last_down_tick_dev; /* [N] tick of the last lastScaleDownTime stamp, >= 0 */
+} ksa_state;
+
+/*
+ * Per-trace summary (64 bytes). Counters accumulate across chunked calls when the caller does not
+ * clear the buffer in between (ksa_summary_clear starts a fresh accumulation).
+ *  hash: order-sensitive 64-bit fingerprint of the (replicas, event) trajectory:
+ *        h <- (h + ((uint64)(uint32)replicas << 8 | event)) * 0x9E3779B97F4A7C15  per tick, h0 = 0.
+ */
+typedef struct ksa_summary {
+  int32_t final_replicas;
+  int32_t min_replicas; /* over ticks replayed so far (INT32_MAX when none) */
+  int32_t max_replicas; /* (INT32_MIN when none)                            */
+  uint32_t up_applied;
+  uint32_t down_applied;
+  uint32_t up_noop;
+  uint32_t down_noop;
+  uint32_t up_cool;
+  uint32_t down_cool;
+  uint32_t reserved;
+  int64_t ticks;        /* ticks replayed so far                            */
+  int64_t sum_replicas; /* wrapping sum of the post-tick replica counts     */
+  uint64_t hash;
+} ksa_summary;
+
+/* ---- synthetic trace generator (integer-only, counter-based; include/ksa_tracegen.h) ----- */
+#define KSA_GEN_BANDS 0       /* i.i.d. three-band mixture around the thresholds          */
+#define KSA_GEN_WALK 1        /* bounded integer random walk (sequential per trace)       */
+#define KSA_GEN_ADVERSARIAL 2 /* threshold +-1, extremes, negatives, overflowing sums     */
+
+typedef struct ksa_gen_params {
+  uint64_t seed;
+  int32_t family;        /* KSA_GEN_*                                                        */
+  int32_t reserved;      /* must be 0                                                        */
+  int64_t low_max;       /* BANDS: low band [0, low_max]            (40 % of entries)       */
+  int64_t high_min;      /* BANDS: middle band (low_max, high_min)  (30 %)                  */
+  int64_t high_max;      /* BANDS: high band [high_min, high_max]   (30 %); WALK: upper wall */
+  int64_t walk_step;     /* WALK: step uniform in [-walk_step, +walk_step], reflect at walls */
+  uint32_t overflow_log2; /* A==3 only: 1 entry in 2^overflow_log2 becomes a triple whose     */
+                          /* int64 sum wraps; 0 = never                                       */
+  uint32_t reserved2;
+} ksa_gen_params;
+
+/* ---- library / device ------------------------------------------------------------------- */
+
+/* ABI version of the loaded library (== KSA_ABI_VERSION of the header it was built from). */
+int ksa_abi_version(void);
+
+/* Thread-local message describing the last non-zero return on this thread ("" if none). */
+const char* ksa_last_error(void);
+
+/* cudaSetDevice for callers that do not link the CUDA runtime themselves (Go, ctypes). */
+int ksa_set_device(int device);
+
+/* Number of visible CUDA devices, or a negative KSA_E* code. */
+int ksa_device_count(void);
+
+/* Convenience allocators for hosts without a CUDA binding. Not used by the replay calls. */
+int ksa_dev_alloc(void** ptr_dev, size_t bytes);
+int ksa_dev_free(void* ptr_dev);
+int ksa_host_alloc(void** ptr_host, size_t bytes); /* pinned (page-locked) host memory */
+int ksa_host_free(void* ptr_host);
+int ksa_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int ksa_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream);
+int ksa_stream_sync(void* stream);
+
+/* ---- policy helpers (host only) ---------------------------------------------------------- */
+
+/* Fill *p with the reference's flag defaults, main.go:83-93 (poll 5 s, down-cool 30 s, up-cool
+ * 10 s, up 100, down 10, steps 1/1, max 5, min 1, all three attributes). */
+int ksa_policy_default(ksa_policy* p);
+
+/* Cool-downs in ticks, as the kernels use them: max(0, ceil(cool/poll)). Replaces the wall-clock
+ * test lastScaleXTime.Add(cool).After(time.Now()) of main.go:52,66. */
+int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_ticks);
+
+/* ---- the hot path ------------------------------------------------------------------------ */
+
+/*
+ * Replay T ticks of N independent traces, full trajectory out.
+ * Replaces, per (trace, tick): NumMessages' attribute sum (sqs/sqs.go:56-64), Run's threshold and
+ * cool-down tests and stamps (main.go:51-55,62,65-69,76), ScaleUp (scale/scale.go:60-69) and
+ * ScaleDown (scale/scale.go:87-97).
+ *   depth_dev    [T][A][ld] int64, A = number of attribute planes stored (1..3); the planes are
+ *                the attributes selected by policy->attr_mask, lowest bit first. The kernel sums
+ *                all A planes; popcount(attr_mask) must equal A.
+ *   state        in/out carry state (see ksa_state)
+ *   replicas_dev [T][ld] int32  replica count after each tick     (may be NULL: not written)
+ *   events_dev   [T][ld] uint8  KSA_EV_* bits of each tick        (may be NULL: not written)
+ * Limits: 1 <= T <= 2^30, 1 <= N <= 2^31-1, N <= ld.
+ */
+int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
+                    int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                    int32_t* replicas_dev, uint8_t* events_dev, void* stream);
+
+/*
+ * Same replay, no per-tick output: accumulates a ksa_summary per trace (read-modify-write of
+ * summary_dev[N], so T-chunks accumulate). Same code path references as ksa_replay_full; the
+ * counters are the reference's log lines counted (main.go:53,67; scale/scale.go:63,77,90,105).
+ */
+int ksa_replay_summary(const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
+                       int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                       ksa_summary* summary_dev, void* stream);
+
+/* Reset N summaries to the empty accumulation (ticks 0, hash 0, min/max sentinels). */
+int ksa_summary_clear(ksa_summary* summary_dev, int64_t N, void* stream);
+
+/*
+ * Policy sweep: replay the same N traces under P policies (the parameter grid of main.go:83-91),
+ * summary per (policy, trace). Every policy starts every trace from replicas0_dev[n] with both
+ * stamps at tick 0 (a fresh process, main.go:37-38). All policies must share A / attr_mask.
+ *   policies      [P] host array
+ *   policies_dev  [P] device scratch for the kernel-side policy table, sizeof(ksa_policy_k)=48 B
+ *                 each (caller-allocated: P * 48 bytes)
+ *   summary_dev   [P][N] ksa_summary, overwritten
+ */
+int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* policies_dev,
+                     const int64_t* depth_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
+                     const int32_t* replicas0_dev, ksa_summary* summary_dev, void* stream);
+
+/*
+ * Fingerprint an existing full trajectory: hash_dev[n] = the ksa_summary.hash the summary replay
+ * would produce for trace n over the same T ticks (h0 = hash_dev[n] on entry when chain != 0, else
+ * 0). Used to compare 100+ GB trajectories without moving them to the host.
+ */
+int ksa_traj_hash(const int32_t* replicas_dev, const uint8_t* events_dev, int64_t T, int64_t N,
+                  int64_t ld, int32_t chain, uint64_t* hash_dev, void* stream);
+
+/* ---- inputs ------------------------------------------------------------------------------ */
+
+/*
+ * Write synthetic depths for ticks tick0+1..tick0+T of traces trace0..trace0+N-1 into
+ * depth_dev [T][A][ld]. Values depend only on (seed, family, attribute, global trace id, absolute
+ * tick), so any sharding / chunking produces the same bits. WALK needs walk_dev[N] (in/out, the
+ * walk position after tick0; ksa_gen_walk_init fills the tick-0 position).
+ */
+int ksa_gen_traces(const ksa_gen_params* g, int64_t tick0, int64_t T, int32_t A, int64_t trace0,
+                   int64_t N, int64_t ld, int64_t* depth_dev, int64_t* walk_dev, void* stream);
+int ksa_gen_walk_init(const ksa_gen_params* g, int64_t trace0, int64_t N, int64_t* walk_dev,
+                      void* stream);
+
+/* Fresh carry state: replicas[n] = lo + hash(seed, trace0+n) mod (hi-lo+1), both stamps 0. */
+int ksa_state_init(uint64_t seed, int64_t trace0, int64_t N, int32_t lo, int32_t hi,
+                   const ksa_state* state, void* stream);
+
+/* ---- host-buffer pipeline (the call a Go / Python host makes with its own slices) --------- */
+
+typedef struct ksa_pipeline ksa_pipeline; /* opaque; owns device staging + 3 streams */
+
+/*
+ * Create a streaming pipeline on `device` for up to N traces x A attributes, moving chunk_ticks
+ * ticks per stage (double-buffered: 2 * chunk_ticks * N * (8A+5) bytes of device memory).
+ */
+int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, int32_t A, int64_t chunk_ticks);
+int ksa_pipeline_destroy(ksa_pipeline* p);
+
+/*
+ * Replay with HOST buffers: depth_host [T][A][N] int64 in, replicas_host [T][N] int32 and
+ * events_host [T][N] uint8 out (either may be NULL), state_*_host [N] in/out (tight rows,
+ * ld == N). H2D copy, kernel and D2H copy of consecutive chunks overlap on three streams.
+ * Buffers should be pinned (ksa_host_alloc) for full PCIe rate; pageable memory works but is
+ * slower. Synchronous: returns when the results are in the host buffers.
+ * If summary_host != NULL it receives [N] ksa_summary for the T ticks (fresh accumulation).
+ */
+int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
+                        int64_t T, int64_t N, int64_t tick0, int32_t* state_replicas_host,
+                        int64_t* state_last_up_host, int64_t* state_last_down_host,
+                        int32_t* replicas_host, uint8_t* events_host, ksa_summary* summary_host);
+
+/* ---- tuning / introspection -------------------------------------------------------------- */
+
+/* Select a kernel variant for ksa_replay_full / ksa_replay_summary on the calling thread
+ * (0 = library default, -2 = the scalar kernel, > 0 = an entry of the variant table). Used by the
+ * tuning sweep in tools/; results never depend on the variant. Returns KSA_EINVAL if unknown. */
+int ksa_set_variant(int32_t full_variant, int32_t summary_variant);
+
+/* Name of a variant ("V4_D4_H1_B128x7": traces per thread, prefetch depth, load hint, block x
+ * min-blocks-per-SM), or NULL if there is no such id. mode 0 = full, 1 = summary; id 0 = scalar. */
+const char* ksa_variant_name(int32_t mode, int32_t id);
+
+/* Number of kernel launches issued by this library on the calling thread since the last call
+ * (returns the count and resets it). bench.py reports it as gpu_launches. */
+int64_t ksa_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KSA_REPLAY_H */

@@ -1,0 +1,401 @@
+// ksa_replay.cu — the hot path: ksa_replay_full and ksa_replay_summary.
+//
+// One thread owns V adjacent traces and walks down the T ticks of the tick-major [T][A][ld] int64
+// depth array. Per tick it issues one 128/256-bit coalesced load per attribute plane (LDG.E.128 /
+// LDG.E.256 on sm_100a), D ticks ahead of use (a register ring, so D*V*A*8 bytes per thread are
+// in flight and the loop-carried state chain never waits on DRAM), runs the branch-free policy
+// step (ksa_policy.cuh) on registers, and writes the per-tick replica counts (int32) and event
+// bytes back as one vector store each. Nothing is re-read, so all accesses carry streaming hints
+// (L1::no_allocate, evict-first). No shared memory: there is no reuse to stage.
+//
+// Replaces, for N traces at once: sqs/sqs.go:56-64 (sum), main.go:51-77 (thresholds, cool-downs,
+// stamps), scale/scale.go:60-69,87-97 (clamped steps). HBM-bound: 8A bytes in + 5 bytes out per
+// (trace, tick) in full mode, 8A in summary mode.
+#include "ksa_internal.h"
+
+namespace {
+
+struct ReplayArgs {
+  ksa_policy_k pk;
+  const long long* depth;
+  long long ld;      // row pitch, elements
+  long long tick0;
+  long long n_begin; // first trace of this launch
+  long long n_count; // traces of this launch (a multiple of V)
+  int T;
+  int* st_r;
+  long long* st_ju;
+  long long* st_jd;
+  int* replicas;           // full mode, may be NULL
+  unsigned char* events;   // full mode, may be NULL
+  ksa_summary* summary;    // summary mode
+};
+
+// MODE_FULL writes both outputs; MODE_FULL_OPT tests the two output pointers at run time (either may
+// be NULL); MODE_SUMMARY writes nothing per tick.
+enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
+// STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (same function, predication spelled out in PTX)
+// Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
+enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
+
+// ---- vector loads / stores (inline PTX: 256-bit global accesses have no C++ spelling) ----------
+template <int HINT>
+__device__ __forceinline__ void ld64x4(const long long* p, long long& a, long long& b, long long& c,
+                                       long long& d) {
+  if (HINT == HINT_NA_EF)
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+  else if (HINT == HINT_NA)
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+  else
+    asm volatile("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+}
+template <int HINT>
+__device__ __forceinline__ void ld64x2(const long long* p, long long& a, long long& b) {
+  if (HINT != HINT_NC)
+    asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+  else
+    asm volatile("ld.global.nc.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+}
+template <int HINT>
+__device__ __forceinline__ void ld64x1(const long long* p, long long& a) {
+  if (HINT != HINT_NC)
+    asm volatile("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(a) : "l"(p));
+  else
+    asm volatile("ld.global.nc.b64 %0, [%1];" : "=l"(a) : "l"(p));
+}
+
+template <int V, int HINT>
+__device__ __forceinline__ void load_depth(const long long* p, long long (&v)[V]) {
+  if constexpr (V == 1) {
+    ld64x1<HINT>(p, v[0]);
+  } else if constexpr (V == 2) {
+    ld64x2<HINT>(p, v[0], v[1]);
+  } else {
+#pragma unroll
+    for (int q = 0; q < V / 4; ++q) ld64x4<HINT>(p + 4 * q, v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void store_replicas(int* p, const int (&r)[V]) {
+  if constexpr (V == 1) {
+    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(r[0]) : "memory");
+  } else if constexpr (V == 2) {
+    asm volatile("st.global.cs.v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(r[0]), "r"(r[1]) : "memory");
+  } else if constexpr (V == 4) {
+    asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(r[0]), "r"(r[1]),
+                 "r"(r[2]), "r"(r[3]) : "memory");
+  } else {
+    static_assert(V == 8, "V must be 1, 2, 4 or 8");
+    asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]),
+                 "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void store_events(unsigned char* p, const unsigned (&e)[V]) {
+  if constexpr (V == 1) {
+    asm volatile("st.global.cs.b8 [%0], %1;" ::"l"(p), "r"(e[0]) : "memory");
+  } else if constexpr (V == 2) {
+    const unsigned short w = (unsigned short)(e[0] | (e[1] << 8));
+    asm volatile("st.global.cs.b16 [%0], %1;" ::"l"(p), "h"(w) : "memory");
+  } else if constexpr (V == 4) {
+    const unsigned w = e[0] | (e[1] << 8) | (e[2] << 16) | (e[3] << 24);
+    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
+  } else {
+    const unsigned w0 = e[0] | (e[1] << 8) | (e[2] << 16) | (e[3] << 24);
+    const unsigned w1 = e[4] | (e[5] << 8) | (e[6] << 16) | (e[7] << 24);
+    asm volatile("st.global.cs.v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(w0), "r"(w1) : "memory");
+  }
+}
+
+// Per-trace accumulators of summary mode (registers).
+struct SummaryRegs {
+  int rmin, rmax;
+  unsigned c_ua, c_da, c_un, c_dn, c_uc, c_dc;
+  long long sum;
+  unsigned long long hash;
+};
+
+template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
+  const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (g * V >= a.n_count) return;
+  const long long n0 = a.n_begin + g * V;
+  const ksa_step_consts c(a.pk);
+  const int T = a.T;
+
+  ksa_trace_regs s[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    s[v].r = a.st_r[n0 + v];
+    s[v].lu = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
+    s[v].ld = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
+  }
+  SummaryRegs sm[MODE == MODE_SUMMARY ? V : 1];
+  if constexpr (MODE == MODE_SUMMARY) {
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      const ksa_summary* q = a.summary + n0 + v;
+      sm[v].rmin = q->min_replicas;
+      sm[v].rmax = q->max_replicas;
+      sm[v].c_ua = sm[v].c_da = sm[v].c_un = sm[v].c_dn = sm[v].c_uc = sm[v].c_dc = 0u;
+      sm[v].sum = q->sum_replicas;
+      sm[v].hash = q->hash;
+    }
+  }
+
+  const long long row = (long long)A * a.ld;  // elements between consecutive ticks
+  const long long* dp = a.depth + n0;
+  int* rp = (MODE != MODE_SUMMARY) ? a.replicas + n0 : nullptr;
+  unsigned char* ep = (MODE != MODE_SUMMARY) ? a.events + n0 : nullptr;
+  const bool want_r = MODE == MODE_FULL || (MODE == MODE_FULL_OPT && a.replicas != nullptr);
+  const bool want_e = MODE == MODE_FULL || (MODE == MODE_FULL_OPT && a.events != nullptr);
+
+  // Register ring: buf[j] holds tick (t + j) for the current group of D ticks.
+  long long buf[D][A][V];
+#pragma unroll
+  for (int j = 0; j < D; ++j)
+    if (j < T) {
+#pragma unroll
+      for (int p = 0; p < A; ++p) load_depth<V, HINT>(dp + (long long)j * row + p * a.ld, buf[j][p]);
+    }
+
+  auto tick = [&](const int tt, const int j, const bool prefetch) {
+    long long n[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      unsigned long long acc = (unsigned long long)buf[j][0][v];  // sqs.go:56-64, wrapping
+#pragma unroll
+      for (int p = 1; p < A; ++p) acc += (unsigned long long)buf[j][p][v];
+      n[v] = (long long)acc;
+    }
+    if (prefetch) {
+#pragma unroll
+      for (int p = 0; p < A; ++p)
+        load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
+    }
+    const int i = tt + 1;  // local tick, 1-based
+    const int iu = i - c.cu, id = i - c.cd;
+    int rr[V];
+    unsigned ev[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      ev[v] = STEP == 1 ? ksa_step_ptx(c, n[v], i, iu, id, s[v]) : ksa_step(c, n[v], i, iu, id, s[v]);
+      rr[v] = s[v].r;
+    }
+    if constexpr (MODE != MODE_SUMMARY) {
+      if (want_r) store_replicas<V>(rp + (long long)tt * a.ld, rr);
+      if (want_e) store_events<V>(ep + (long long)tt * a.ld, ev);
+    } else {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        sm[v].rmin = min(sm[v].rmin, rr[v]);
+        sm[v].rmax = max(sm[v].rmax, rr[v]);
+        sm[v].c_ua += (ev[v] >> 0) & 1u;
+        sm[v].c_da += (ev[v] >> 1) & 1u;
+        sm[v].c_un += (ev[v] >> 2) & 1u;
+        sm[v].c_dn += (ev[v] >> 3) & 1u;
+        sm[v].c_uc += (ev[v] >> 4) & 1u;
+        sm[v].c_dc += (ev[v] >> 5) & 1u;
+        sm[v].sum = (long long)((unsigned long long)sm[v].sum + (unsigned long long)(long long)rr[v]);
+        sm[v].hash = ksa_hash_step(sm[v].hash, rr[v], ev[v]);
+      }
+    }
+  };
+
+  int t = 0;
+  // Steady state: every tick of the group exists and so does the tick D ahead of it.
+#pragma unroll 1
+  for (; t + 2 * D <= T; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) tick(t + j, j, true);
+  }
+  // Drain: at most 2D-1 ticks left; guard both the tick and its prefetch.
+#pragma unroll 1
+  for (; t < T; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+      if (t + j < T) tick(t + j, j, t + j + D < T);
+  }
+
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    a.st_r[n0 + v] = s[v].r;
+    a.st_ju[n0 + v] = ksa_global_stamp(s[v].lu, a.tick0, a.st_ju[n0 + v]);
+    a.st_jd[n0 + v] = ksa_global_stamp(s[v].ld, a.tick0, a.st_jd[n0 + v]);
+  }
+  if constexpr (MODE == MODE_SUMMARY) {
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      ksa_summary* q = a.summary + n0 + v;
+      q->final_replicas = s[v].r;
+      q->min_replicas = sm[v].rmin;
+      q->max_replicas = sm[v].rmax;
+      q->up_applied += sm[v].c_ua;
+      q->down_applied += sm[v].c_da;
+      q->up_noop += sm[v].c_un;
+      q->down_noop += sm[v].c_dn;
+      q->up_cool += sm[v].c_uc;
+      q->down_cool += sm[v].c_dc;
+      q->ticks += (long long)T;
+      q->sum_replicas = sm[v].sum;
+      q->hash = sm[v].hash;
+    }
+  }
+}
+
+typedef void (*replay_kernel_fn)(const ReplayArgs);
+
+// A variant = one tuning point. The register ring costs 2*D*V*A registers, so the multi-attribute
+// kernels use a shallower ring / fewer traces per thread than the A = 1 kernel of the same id.
+struct Variant {
+  int id;
+  int V[3], block[3];  // per A-1
+  const char* name;
+  replay_kernel_fn fn[3];  // indexed by A-1
+};
+
+#define KSA_K(A, V, D, HINT, MODE, STEP, BLOCK, MINB) ksa_replay_kernel<A, V, D, HINT, MODE, STEP, BLOCK, MINB>
+// A=1 tuning point (V, D, HINT, STEP, BLOCK, MINB); A=2 and A=3 points (V, D, BLOCK, MINB) share HINT/STEP.
+#define KSA_VARIANT(ID, MODE, V, D, HINT, STEP, BLOCK, MINB, V2, D2, B2, M2, V3, D3, B3, M3)   \
+  {ID, {V, V2, V3}, {BLOCK, B2, B3}, "V" #V "_D" #D "_H" #HINT "_S" #STEP "_B" #BLOCK "x" #MINB, \
+   {KSA_K(1, V, D, HINT, MODE, STEP, BLOCK, MINB), KSA_K(2, V2, D2, HINT == HINT_NA_EF && V2 < 4 ? HINT_NA : HINT, MODE, STEP, B2, M2),                  \
+    KSA_K(3, V3, D3, HINT == HINT_NA_EF && V3 < 4 ? HINT_NA : HINT, MODE, STEP, B3, M3)}}
+
+// Variant 0 is the scalar kernel (any alignment, any N); it also handles the ragged tail of the
+// vector variants. The default is chosen from tools/sweep_variants.py measurements.
+const Variant kFullVariants[] = {
+    KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(1, MODE_FULL, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
+    KSA_VARIANT(2, MODE_FULL, 4, 4, HINT_NA_EF, 0, 128, 7, 4, 2, 128, 6, 4, 2, 128, 5),
+    KSA_VARIANT(3, MODE_FULL, 4, 2, HINT_NA, 0, 128, 7, 2, 4, 128, 7, 2, 2, 128, 7),
+    KSA_VARIANT(4, MODE_FULL, 4, 8, HINT_NA, 0, 128, 4, 4, 4, 128, 4, 4, 2, 128, 4),
+    KSA_VARIANT(5, MODE_FULL, 2, 4, HINT_NA, 0, 128, 7, 2, 4, 256, 3, 2, 4, 256, 3),
+    KSA_VARIANT(6, MODE_FULL, 2, 8, HINT_NA, 0, 128, 6, 2, 2, 128, 7, 1, 8, 128, 7),
+    KSA_VARIANT(7, MODE_FULL, 2, 6, HINT_NA, 0, 256, 3, 2, 3, 256, 3, 2, 3, 128, 7),
+    KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NC, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
+    KSA_VARIANT(9, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 3, 128, 4),
+    KSA_VARIANT(10, MODE_FULL, 4, 4, HINT_NA, 0, 256, 3, 4, 2, 256, 3, 2, 4, 256, 3),
+    KSA_VARIANT(11, MODE_FULL, 4, 6, HINT_NA, 0, 128, 5, 4, 3, 128, 4, 2, 6, 128, 5),
+    KSA_VARIANT(12, MODE_FULL, 4, 4, HINT_NA, 1, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
+    KSA_VARIANT(13, MODE_FULL, 2, 4, HINT_NA, 1, 128, 7, 2, 4, 256, 3, 2, 4, 256, 3),
+    KSA_VARIANT(14, MODE_FULL, 4, 3, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(15, MODE_FULL, 4, 4, HINT_NA_EF, 1, 128, 7, 4, 2, 128, 6, 4, 2, 128, 5),
+    KSA_VARIANT(16, MODE_FULL_OPT, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
+};
+const Variant kSummaryVariants[] = {
+    KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(1, MODE_SUMMARY, 2, 8, HINT_NA, 0, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
+    KSA_VARIANT(2, MODE_SUMMARY, 4, 4, HINT_NA, 0, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
+    KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 0, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(4, MODE_SUMMARY, 4, 4, HINT_NA_EF, 0, 128, 4, 4, 2, 128, 3, 4, 2, 128, 3),
+    KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
+    KSA_VARIANT(6, MODE_SUMMARY, 1, 8, HINT_NA, 0, 256, 4, 1, 4, 256, 4, 1, 4, 256, 4),
+};
+constexpr int kDefaultFull = 1;
+constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
+constexpr int kDefaultSummary = 1;
+
+template <size_t K>
+const Variant* find_variant(const Variant (&table)[K], int id) {
+  for (size_t i = 0; i < K; ++i)
+    if (table[i].id == id) return &table[i];
+  return nullptr;
+}
+
+int launch(const Variant& var, int A, ReplayArgs args, cudaStream_t stream) {
+  if (args.n_count <= 0) return KSA_OK;
+  const long long threads = (args.n_count + var.V[A - 1] - 1) / var.V[A - 1];
+  const long long blocks = (threads + var.block[A - 1] - 1) / var.block[A - 1];
+  if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "grid too large (%lld blocks)", blocks);
+  var.fn[A - 1]<<<dim3((unsigned)blocks), dim3((unsigned)var.block[A - 1]), 0, stream>>>(args);
+  KSA_LAUNCH_CHECK(var.name);
+  return KSA_OK;
+}
+
+int replay_common(int mode, const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
+                  int64_t N, int64_t ld, int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
+                  uint8_t* events_dev, ksa_summary* summary_dev, void* stream) {
+  if (!policy || !depth_dev || !state) return ksa_fail(KSA_EINVAL, "NULL policy, depth or state");
+  if (!state->replicas_dev || !state->last_up_tick_dev || !state->last_down_tick_dev)
+    return ksa_fail(KSA_EINVAL, "NULL pointer inside ksa_state");
+  if (mode == MODE_SUMMARY && !summary_dev) return ksa_fail(KSA_EINVAL, "NULL summary_dev");
+  if (T < 1 || T > KSA_MAX_CHUNK_TICKS)
+    return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]; chunk longer traces", (long long)T);
+  if (N < 1 || N > 0x7fffffffll) return ksa_fail(KSA_EINVAL, "N=%lld outside [1, 2^31-1]", (long long)N);
+  if (ld < N) return ksa_fail(KSA_EINVAL, "ld=%lld < N=%lld", (long long)ld, (long long)N);
+  if (tick0 < 0) return ksa_fail(KSA_EINVAL, "tick0=%lld < 0", (long long)tick0);
+  ReplayArgs args;
+  int rc = ksa_policy_to_k(policy, A, &args.pk);
+  if (rc != KSA_OK) return rc;
+  args.depth = (const long long*)depth_dev;
+  args.ld = ld;
+  args.tick0 = tick0;
+  args.T = (int)T;
+  args.st_r = state->replicas_dev;
+  args.st_ju = (long long*)state->last_up_tick_dev;
+  args.st_jd = (long long*)state->last_down_tick_dev;
+  args.replicas = replicas_dev;
+  args.events = events_dev;
+  args.summary = summary_dev;
+
+  const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
+  const Variant* var = mode == MODE_FULL
+                           ? find_variant(kFullVariants, want < 0 ? kDefaultFull : want)
+                           : find_variant(kSummaryVariants, want < 0 ? kDefaultSummary : want);
+  // Variants compiled for "both outputs" cannot run with one of them missing.
+  if (mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
+  const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];
+  if (!var) return ksa_fail(KSA_EINVAL, "unknown kernel variant %d", want);
+  // Vector path needs every row start 32-byte aligned in all three arrays.
+  const bool aligned = (ld % 16 == 0) && ksa_aligned(depth_dev, 32) &&
+                       (!replicas_dev || ksa_aligned(replicas_dev, 32)) &&
+                       (!events_dev || ksa_aligned(events_dev, 16));
+  if (!aligned) var = scalar;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = var->V[A - 1];
+  const long long n_vec = (N / V) * V;
+  args.n_begin = 0;
+  args.n_count = n_vec;
+  rc = launch(*var, A, args, st);
+  if (rc != KSA_OK) return rc;
+  if (n_vec < N) {  // ragged tail: fewer than V traces, scalar kernel
+    args.n_begin = n_vec;
+    args.n_count = N - n_vec;
+    rc = launch(*scalar, A, args, st);
+  }
+  return rc;
+}
+
+}  // namespace
+
+extern "C" int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T,
+                               int32_t A, int64_t N, int64_t ld, int64_t tick0,
+                               const ksa_state* state, int32_t* replicas_dev, uint8_t* events_dev,
+                               void* stream) {
+  return replay_common(MODE_FULL, policy, depth_dev, T, A, N, ld, tick0, state, replicas_dev,
+                       events_dev, nullptr, stream);
+}
+
+extern "C" int ksa_replay_summary(const ksa_policy* policy, const int64_t* depth_dev, int64_t T,
+                                  int32_t A, int64_t N, int64_t ld, int64_t tick0,
+                                  const ksa_state* state, ksa_summary* summary_dev, void* stream) {
+  return replay_common(MODE_SUMMARY, policy, depth_dev, T, A, N, ld, tick0, state, nullptr, nullptr,
+                       summary_dev, stream);
+}
+
+// Used by ksa_set_variant to validate ids.
+bool ksa_replay_variant_exists(int mode, int id) {
+  return mode == MODE_FULL ? find_variant(kFullVariants, id) != nullptr
+                           : find_variant(kSummaryVariants, id) != nullptr;
+}
+// Variant names for tools/ (not part of the C ABI header; looked up with dlsym by the sweep tool).
+extern "C" const char* ksa_variant_name(int32_t mode, int32_t id) {
+  const Variant* v = mode == MODE_FULL ? find_variant(kFullVariants, id) : find_variant(kSummaryVariants, id);
+  return v ? v->name : nullptr;
+}
