@@ -103,15 +103,21 @@ def fresh_state(seed: int, trace0: int, N: int, lo: int, hi: int):
 def replay(policy: KsaPolicy, depth: np.ndarray, T: int, A: int, N: int, ld: int, tick0: int,
            state_replicas: np.ndarray, state_last_up: np.ndarray, state_last_down: np.ndarray,
            want_full: bool = True, want_summary: bool = False, summary: np.ndarray | None = None,
-           threads: int = 0) -> OracleResult:
-    """Batch tick-model replay. State arrays are copied, not modified in place."""
+           threads: int = 0, out: tuple[np.ndarray, np.ndarray] | None = None) -> OracleResult:
+    """Batch tick-model replay. State arrays are copied, not modified in place. `out` = preallocated
+    (replicas [T][ld] int32, events [T][ld] uint8) to keep page faults out of a timed call."""
     depth = np.ascontiguousarray(depth, dtype=np.int64)
     assert depth.size >= T * A * ld
     r = np.array(state_replicas, dtype=np.int32, copy=True)
     ju = np.array(state_last_up, dtype=np.int64, copy=True)
     jd = np.array(state_last_down, dtype=np.int64, copy=True)
-    replicas = np.zeros((T, ld), dtype=np.int32) if want_full else None
-    events = np.zeros((T, ld), dtype=np.uint8) if want_full else None
+    if out is not None:
+        replicas, events = out
+        assert replicas.dtype == np.int32 and events.dtype == np.uint8
+        assert replicas.size >= T * ld and events.size >= T * ld
+    else:
+        replicas = np.zeros((T, ld), dtype=np.int32) if want_full else None
+        events = np.zeros((T, ld), dtype=np.uint8) if want_full else None
     if want_summary and summary is None:
         summary = np.empty(N, dtype=SUMMARY_DTYPE)
         load().ksa_oracle_summary_clear(_p(summary), N)

@@ -1,0 +1,513 @@
+"""GPU parity: the CUDA path, called through the C ABI (ctypes -> libksareplay.so), against the CPU
+oracle on the same inputs. Integer work: the bar is bit-exact, everywhere.
+
+Run with `pytest -m gpu` on the B200 box. Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import kube_sqs_autoscaler_b200 as ksa
+from kube_sqs_autoscaler_b200 import _abi
+from tests import oracle_lib
+from tests.helpers import S, load_golden, policy_from_run_kat, policy_from_vector
+
+pytestmark = pytest.mark.gpu
+
+KATS = load_golden("reference_kats.json")
+DERIVED = load_golden("derived_vectors.json")
+FULL_VARIANTS = [-2] + list(range(1, 17))   # -2 = scalar kernel
+SUMMARY_VARIANTS = [-2] + list(range(1, 7))
+
+
+def torch_mod():
+    import torch
+
+    return torch
+
+
+def gpu_full(engine, pol, depth_np, T, A, N, ld, tick0, st, want_summary=True):
+    """Run full + summary replay on the GPU for host depth [T][A][ld]; returns numpy results."""
+    torch = torch_mod()
+    depth = torch.from_numpy(np.ascontiguousarray(depth_np)).to(engine.dev)
+    state = engine.state_from_host(*st)
+    replicas, events = engine.replay_full(pol, depth, T, A, N, ld, tick0, state)
+    out = {
+        "replicas": replicas.cpu().numpy(), "events": events.cpu().numpy(),
+        "st_r": state.replicas.cpu().numpy(), "st_ju": state.last_up.cpu().numpy(),
+        "st_jd": state.last_down.cpu().numpy(),
+    }
+    if want_summary:
+        state2 = engine.state_from_host(*st)
+        summ = engine.replay_summary(pol, depth, T, A, N, ld, tick0, state2)
+        out["summary"] = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+        out["st2_r"] = state2.replicas.cpu().numpy()
+        out["st2_ju"] = state2.last_up.cpu().numpy()
+        out["st2_jd"] = state2.last_down.cpu().numpy()
+        out["hash"] = engine.traj_hash(replicas, events, T, N, ld).cpu().numpy().view(np.uint64)
+    return out
+
+
+def assert_matches_oracle(out, ref, N, label=""):
+    assert np.array_equal(out["replicas"][:, :N], ref.replicas[:, :N]), f"replicas differ {label}"
+    assert np.array_equal(out["events"][:, :N], ref.events[:, :N]), f"events differ {label}"
+    assert np.array_equal(out["st_r"], ref.state_replicas), f"state replicas differ {label}"
+    assert np.array_equal(out["st_ju"], ref.state_last_up), f"last_up differs {label}"
+    assert np.array_equal(out["st_jd"], ref.state_last_down), f"last_down differs {label}"
+    if "summary" in out:
+        assert out["summary"].tobytes() == ref.summary.tobytes(), f"summary differs {label}"
+        assert np.array_equal(out["st2_r"], ref.state_replicas)
+        assert np.array_equal(out["st2_ju"], ref.state_last_up)
+        assert np.array_equal(out["st2_jd"], ref.state_last_down)
+        assert np.array_equal(out["hash"], ref.summary["hash"]), f"traj_hash differs {label}"
+
+
+# ---- config 1: the reference's own tests, through the kernels ------------------------------------
+
+@pytest.mark.parametrize("k", KATS["run"], ids=lambda k: k["name"])
+def test_reference_run_kats_on_gpu(engine, k):
+    pol = policy_from_run_kat(k)
+    for T in k["ticks"]:
+        for N, ld in ((1, 1), (1, 16), (37, 48)):  # N=1 as in the reference, and padded / replicated
+            depth = np.zeros((T, 3, ld), dtype=np.int64)
+            depth[:, :, :N] = np.asarray(k["attributes"], dtype=np.int64)[None, :, None]
+            st = (np.full(N, k["init"], np.int32), np.zeros(N, np.int64), np.zeros(N, np.int64))
+            out = gpu_full(engine, pol, depth, T, 3, N, ld, 0, st)
+            assert (out["st_r"] == k["expect_final"]).all(), (k["name"], T, N)
+            assert (out["replicas"][-1, :N] == k["expect_final"]).all()
+            assert (out["summary"]["final_replicas"] == k["expect_final"]).all()
+
+
+@pytest.mark.parametrize("k", KATS["scale"], ids=lambda k: k["name"])
+def test_reference_scale_kats_on_gpu(engine, k):
+    """ScaleUp/ScaleDown called directly (scale/scale_test.go) == no cool-down, depth forced."""
+    pol = ksa.Policy(max_pods=k["max"], min_pods=k["min"], scale_up_pods=k["up_pods"],
+                     scale_down_pods=k["down_pods"], scale_up_cool_down=0, scale_down_cool_down=0,
+                     scale_up_messages=100, scale_down_messages=10, attr_mask=1)
+    rows = np.asarray([[1000 if c == "up" else 0] for c in k["calls"]], dtype=np.int64)
+    T = len(k["calls"])
+    st = (np.array([k["init"]], np.int32), np.zeros(1, np.int64), np.zeros(1, np.int64))
+    out = gpu_full(engine, pol, rows.reshape(T, 1, 1), T, 1, 1, 1, 0, st)
+    assert out["replicas"][:, 0].tolist() == k["expect"]
+
+
+def test_reference_sum_kat_on_gpu(engine):
+    """sqs/sqs_test.go:19-25: 10+10+10 = 30. Observable through the thresholds: 30 >= 30 scales up,
+    30 < 31 does not."""
+    k = KATS["sum"][0]
+    rows = np.asarray([k["attributes"]], dtype=np.int64).reshape(1, 3, 1)
+    st = (np.array([3], np.int32), np.zeros(1, np.int64), np.zeros(1, np.int64))
+    for thr, expect in ((k["expect"], 4), (k["expect"] + 1, 3)):
+        pol = ksa.Policy(scale_up_messages=thr, scale_down_messages=-1, scale_up_cool_down=0)
+        out = gpu_full(engine, pol, rows, 1, 3, 1, 1, 0, st)
+        assert out["replicas"][0, 0] == expect
+
+
+@pytest.mark.parametrize("v", DERIVED["vectors"], ids=lambda v: v["id"])
+def test_derived_quirk_vectors_on_gpu(engine, v):
+    pol = policy_from_vector(v)
+    rows = np.asarray(v["depth"], dtype=np.int64)
+    T, A = rows.shape
+    for N, ld in ((1, 1), (21, 32)):
+        depth = np.zeros((T, A, ld), dtype=np.int64)
+        depth[:, :, :N] = rows[:, :, None]
+        st = (np.full(N, v["r0"], np.int32), np.zeros(N, np.int64), np.zeros(N, np.int64))
+        out = gpu_full(engine, pol, depth, T, A, N, ld, 0, st)
+        for n in range(N):
+            assert out["replicas"][:, n].tolist() == v["replicas"], v["id"]
+            assert out["events"][:, n].tolist() == v["events"], v["id"]
+
+
+# ---- random policies x adversarial traces, every kernel variant ----------------------------------
+
+def random_policy(rng, A):
+    poll = int(rng.choice([1, 3, S, 5 * S, 7 * S]))
+    def cool():
+        c = rng.integers(0, 4)
+        if c == 0:
+            return int(rng.integers(-2, 7)) * poll
+        if c == 1:
+            return int(rng.integers(0, 40 * S))
+        if c == 2:
+            return 0
+        return int(min(2**63 - 1, int(rng.choice([2**62, 2**31, 5])) * poll))
+    def pods():
+        if rng.integers(0, 5) == 0:
+            return int(rng.choice([2**31 - 1, -(2**31), 2**32 + 2, 2**40 + 7, 0, -1]))
+        return int(rng.integers(-3, 13))
+    def thr():
+        c = rng.integers(0, 6)
+        if c < 4:
+            return int(rng.integers(-5, 600))
+        return int(rng.choice([2**63 - 1, -(2**63), 2**31, 2**32 + 3, -(2**31) - 1, 0]))
+    mask = [m for m in (1, 2, 4, 3, 5, 6, 7) if bin(m).count("1") == A]
+    return ksa.Policy(poll_period=poll, scale_up_cool_down=cool(), scale_down_cool_down=cool(),
+                      scale_up_messages=thr(), scale_down_messages=thr(), scale_up_pods=pods(),
+                      scale_down_pods=pods(), max_pods=pods(), min_pods=pods(),
+                      attr_mask=int(rng.choice(mask)))
+
+
+def adversarial_depth(rng, T, A, ld, pol):
+    base = rng.integers(-5, 600, size=(T, A, ld), dtype=np.int64)
+    special = np.array([2**63 - 1, -(2**63), 2**31, 2**32 + 3, -(2**31) - 1, 0,
+                        pol.scale_up_messages, pol.scale_down_messages,
+                        min(pol.scale_up_messages, 2**63 - 2) + 1, max(pol.scale_down_messages, -(2**63) + 1) - 1],
+                       dtype=np.int64)
+    pick = rng.integers(0, 5, size=base.shape) == 0
+    base[pick] = special[rng.integers(0, special.size, size=int(pick.sum()))]
+    return base
+
+
+def random_state(rng, N, tick0):
+    r = rng.integers(-3, 13, size=N).astype(np.int32)
+    edge = rng.integers(0, 8, size=N) == 0
+    r[edge] = rng.choice(np.array([2**31 - 1, -(2**31), 2147483000, -2147483000], dtype=np.int64),
+                         size=int(edge.sum())).astype(np.int32)
+    ju = rng.integers(0, tick0 + 1, size=N).astype(np.int64)
+    jd = rng.integers(0, tick0 + 1, size=N).astype(np.int64)
+    return r, ju, jd
+
+
+@pytest.mark.parametrize("A", [1, 2, 3])
+def test_random_policies_all_variants(engine, A):
+    rng = np.random.default_rng(1234 + A)
+    cases = []
+    for case in range(6):
+        pol = random_policy(rng, A)
+        T = int(rng.integers(1, 70))
+        N = int(rng.choice([1, 5, 64, 129, 1000, 2051]))
+        ld = (N + 15) // 16 * 16 if case % 3 else N
+        tick0 = int(rng.choice([0, 0, 17, 10**6, 2**40]))
+        depth = adversarial_depth(rng, T, A, ld, pol)
+        st = random_state(rng, N, tick0)
+        ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st, want_summary=True)
+        cases.append((pol, T, N, ld, tick0, depth, st, ref))
+    try:
+        for fv in FULL_VARIANTS:
+            sv = SUMMARY_VARIANTS[min(len(SUMMARY_VARIANTS) - 1, FULL_VARIANTS.index(fv))]
+            engine.set_variant(fv, sv)
+            for pol, T, N, ld, tick0, depth, st, ref in cases:
+                out = gpu_full(engine, pol, depth, T, A, N, ld, tick0, st)
+                assert_matches_oracle(out, ref, N, f"A={A} full_variant={fv} summary_variant={sv} N={N} T={T} ld={ld}")
+    finally:
+        engine.set_variant(0, 0)
+
+
+def test_default_policy_bands_large_block(engine):
+    """Config-2-shaped block (default policy, single attribute, band generator) at a size the
+    oracle finishes in seconds; every trace compared in full."""
+    pol = ksa.Policy(attr_mask=1)
+    gen = ksa.GenParams(seed=0x5EED0001)
+    T, N = 512, 1 << 15
+    depth = engine.gen_traces(gen, 0, T, 1, 0, N, N)
+    state = engine.new_state(N, seed=gen.seed, lo=1, hi=5)
+    replicas, events = engine.replay_full(pol, depth, T, 1, N, N, 0, state)
+    d_host = depth.cpu().numpy()
+    assert np.array_equal(d_host, oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, N))
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, N, 0,
+                            *oracle_lib.fresh_state(gen.seed, 0, N, 1, 5), want_summary=True)
+    assert np.array_equal(replicas.cpu().numpy(), ref.replicas)
+    assert np.array_equal(events.cpu().numpy(), ref.events)
+    assert np.array_equal(state.replicas.cpu().numpy(), ref.state_replicas)
+    # the workload is not degenerate: every outcome occurs
+    tot = {k: int(ref.summary[k].sum()) for k in ("up_applied", "down_applied", "up_noop", "down_noop", "up_cool", "down_cool")}
+    assert all(v > 0 for v in tot.values()), tot
+
+
+# ---- generator ------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("family", [ksa.GEN_BANDS, ksa.GEN_WALK, ksa.GEN_ADVERSARIAL])
+@pytest.mark.parametrize("A", [1, 2, 3])
+def test_generator_matches_host_and_is_shard_chunk_invariant(engine, family, A):
+    torch = torch_mod()
+    gen = ksa.GenParams(seed=42 + family, family=family, low_max=25, high_min=250, high_max=1000,
+                        walk_step=15, overflow_log2=6 if A == 3 else 0)
+    T, N, ld = 97, 777, 784
+    walk = engine.gen_walk_init(gen, 0, N) if family == ksa.GEN_WALK else None
+    hwalk = oracle_lib.gen_walk_init(gen.to_c(), 0, N) if family == ksa.GEN_WALK else None
+    if walk is not None:
+        assert np.array_equal(walk.cpu().numpy(), hwalk)
+    dev = engine.gen_traces(gen, 0, T, A, 0, N, ld, walk=walk).cpu().numpy()
+    host = oracle_lib.gen_traces(gen.to_c(), 0, T, A, 0, N, ld, walk=hwalk)
+    assert np.array_equal(dev[:, :, :N], host[:, :, :N])
+    if walk is not None:
+        assert np.array_equal(walk.cpu().numpy(), hwalk)
+    if A == 3 and family == ksa.GEN_BANDS:
+        assert (dev[:, 0, :N] == 2**63 - 1).any(), "overflow triples expected at rate 2^-6"
+    # shard + chunk: traces [300, 500), ticks 41..97 generated on their own == the same block
+    n0, n1, t0 = 300, 500, 40
+    w2 = None
+    if family == ksa.GEN_WALK:
+        w2 = engine.gen_walk_init(gen, n0, n1 - n0)
+        engine.gen_traces(gen, 0, t0, A, n0, n1 - n0, n1 - n0, walk=w2)  # advance the walk to tick t0
+    part = engine.gen_traces(gen, t0, T - t0, A, n0, n1 - n0, n1 - n0, walk=w2).cpu().numpy()
+    assert np.array_equal(part, dev[t0:, :, n0:n1])
+    torch.cuda.synchronize()
+
+
+def test_state_init_matches_host(engine):
+    st = engine.new_state(1000, seed=0x5EED0001, lo=1, hi=5, trace0=12345)
+    r, ju, jd = oracle_lib.fresh_state(0x5EED0001, 12345, 1000, 1, 5)
+    assert np.array_equal(st.replicas.cpu().numpy(), r)
+    assert (st.last_up.cpu().numpy() == 0).all() and (st.last_down.cpu().numpy() == 0).all()
+    assert r.min() == 1 and r.max() == 5
+
+
+# ---- layout edge cases ----------------------------------------------------------------------------
+
+def test_unaligned_pointers_take_the_scalar_path(engine):
+    """Base pointers that are only 8-byte aligned and an odd pitch: same results."""
+    torch = torch_mod()
+    rng = np.random.default_rng(5)
+    pol = ksa.Policy(attr_mask=1)
+    T, N, ld = 33, 301, 303
+    depth_np = rng.integers(0, 400, size=(T, 1, ld), dtype=np.int64)
+    st = oracle_lib.fresh_state(3, 0, N, 1, 5)
+    ref = oracle_lib.replay(pol.to_c(), depth_np, T, 1, N, ld, 0, *st)
+    big = torch.zeros(T * ld + 1, dtype=torch.int64, device=engine.dev)
+    depth = big[1:]  # 8-byte aligned only
+    depth.copy_(torch.from_numpy(depth_np.reshape(-1)).to(engine.dev))
+    rbig = torch.zeros(T * ld + 1, dtype=torch.int32, device=engine.dev)
+    ebig = torch.zeros(T * ld + 3, dtype=torch.uint8, device=engine.dev)
+    state = engine.state_from_host(*st)
+    pc, sc = pol.to_c(), state.to_c()
+    _abi.check(engine.lib.ksa_replay_full(C.byref(pc), depth.data_ptr(), T, 1, N, ld, 0, C.byref(sc),
+                                          rbig[1:].data_ptr(), ebig[3:].data_ptr(), None))
+    torch.cuda.synchronize()
+    assert np.array_equal(rbig[1:].cpu().numpy().reshape(T, ld)[:, :N], ref.replicas[:, :N])
+    assert np.array_equal(ebig[3:].cpu().numpy().reshape(T, ld)[:, :N], ref.events[:, :N])
+
+
+def test_padding_columns_are_never_written(engine):
+    torch = torch_mod()
+    pol = ksa.Policy(attr_mask=1)
+    T, N, ld = 20, 100, 112
+    depth = torch.full((T, 1, ld), 500, dtype=torch.int64, device=engine.dev)
+    replicas = torch.full((T, ld), -77, dtype=torch.int32, device=engine.dev)
+    events = torch.full((T, ld), 0xEE, dtype=torch.uint8, device=engine.dev)
+    state = engine.new_state(N, seed=1, lo=1, hi=5)
+    engine.replay_full(pol, depth, T, 1, N, ld, 0, state, replicas=replicas, events=events)
+    assert (replicas[:, N:] == -77).all() and (events[:, N:] == 0xEE).all()
+    assert (replicas[:, :N] != -77).all()
+
+
+def test_optional_outputs(engine):
+    torch = torch_mod()
+    rng = np.random.default_rng(11)
+    pol = ksa.Policy(attr_mask=1)
+    T, N = 40, 515
+    ld = 528
+    depth_np = rng.integers(0, 400, size=(T, 1, ld), dtype=np.int64)
+    st = oracle_lib.fresh_state(3, 0, N, 1, 5)
+    ref = oracle_lib.replay(pol.to_c(), depth_np, T, 1, N, ld, 0, *st)
+    depth = torch.from_numpy(depth_np).to(engine.dev)
+    s1 = engine.state_from_host(*st)
+    r_only, e_none = engine.replay_full(pol, depth, T, 1, N, ld, 0, s1, want_events=False)
+    assert e_none is None and np.array_equal(r_only.cpu().numpy()[:, :N], ref.replicas[:, :N])
+    s2 = engine.state_from_host(*st)
+    r_none, e_only = engine.replay_full(pol, depth, T, 1, N, ld, 0, s2, want_replicas=False)
+    assert r_none is None and np.array_equal(e_only.cpu().numpy()[:, :N], ref.events[:, :N])
+    s3 = engine.state_from_host(*st)
+    engine.replay_full(pol, depth, T, 1, N, ld, 0, s3, want_replicas=False, want_events=False)
+    for s in (s1, s2, s3):
+        assert np.array_equal(s.replicas.cpu().numpy(), ref.state_replicas)
+
+
+# ---- chunking / carry state -----------------------------------------------------------------------
+
+def test_t_chunks_with_carry_state_equal_one_shot(engine):
+    """Config 3's execution shape: A=3, non-default policy, T-chunks carrying (r, ju, jd)."""
+    pol = ksa.Policy(scale_up_messages=250, scale_down_messages=25, scale_up_pods=3, scale_down_pods=2,
+                     max_pods=50, min_pods=2, scale_up_cool_down=12 * S, scale_down_cool_down=45 * S)
+    gen = ksa.GenParams(seed=0x5EED0003, low_max=25, high_min=250, high_max=1000, overflow_log2=8)
+    T, A, N, ld = 1000, 3, 4099, 4112
+    depth = engine.gen_traces(gen, 0, T, A, 0, N, ld)
+    d_host = depth.cpu().numpy()
+    st = oracle_lib.fresh_state(gen.seed, 0, N, 2, 50)
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, A, N, ld, 0, *st, want_summary=True)
+    state = engine.new_state(N, seed=gen.seed, lo=2, hi=50)
+    state_s = state.clone()
+    summ = engine.new_summary(N)
+    reps, evs = [], []
+    for t0 in range(0, T, 250):
+        r, e = engine.replay_full(pol, depth[t0:t0 + 250], 250, A, N, ld, t0, state)
+        engine.replay_summary(pol, depth[t0:t0 + 250], 250, A, N, ld, t0, state_s, summary=summ)
+        reps.append(r.cpu().numpy())
+        evs.append(e.cpu().numpy())
+    assert np.array_equal(np.concatenate(reps)[:, :N], ref.replicas[:, :N])
+    assert np.array_equal(np.concatenate(evs)[:, :N], ref.events[:, :N])
+    assert summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.summary.tobytes()
+    assert np.array_equal(state.last_up.cpu().numpy(), ref.state_last_up)
+    assert np.array_equal(state_s.last_down.cpu().numpy(), ref.state_last_down)
+
+
+def test_policy_change_between_chunks(engine):
+    """Stamps are absolute ticks, so the policy may change at a chunk boundary (e.g. replaying a
+    cool-down retune): chunk 2 under the new cool-down still honours stamps taken in chunk 1."""
+    rng = np.random.default_rng(21)
+    N, ld, T1, T2 = 300, 304, 25, 40
+    p1 = ksa.Policy(attr_mask=1, scale_up_cool_down=10 * S, scale_down_cool_down=30 * S)
+    p2 = ksa.Policy(attr_mask=1, scale_up_cool_down=60 * S, scale_down_cool_down=5 * S, max_pods=9)
+    d = rng.integers(0, 400, size=(T1 + T2, 1, ld), dtype=np.int64)
+    st = oracle_lib.fresh_state(5, 0, N, 1, 5)
+    a = oracle_lib.replay(p1.to_c(), d[:T1], T1, 1, N, ld, 0, *st)
+    b = oracle_lib.replay(p2.to_c(), d[T1:], T2, 1, N, ld, T1, a.state_replicas, a.state_last_up, a.state_last_down)
+    torch = torch_mod()
+    depth = torch.from_numpy(d).to(engine.dev)
+    state = engine.state_from_host(*st)
+    engine.replay_full(p1, depth[:T1], T1, 1, N, ld, 0, state)
+    r2, e2 = engine.replay_full(p2, depth[T1:], T2, 1, N, ld, T1, state)
+    assert np.array_equal(r2.cpu().numpy()[:, :N], b.replicas[:, :N])
+    assert np.array_equal(e2.cpu().numpy()[:, :N], b.events[:, :N])
+    assert np.array_equal(state.last_up.cpu().numpy(), b.state_last_up)
+
+
+def test_cool_down_longer_than_any_chunk(engine):
+    """cool = 2^62 ticks of 1 ns: the first scale-up never happens, stamps stay 0; and a trace
+    that did scale at tick0 - 1 stays blocked. Exercises the KSA_COOL_CAP clamp."""
+    torch = torch_mod()
+    pol = ksa.Policy(attr_mask=1, poll_period=1, scale_up_cool_down=2**62, scale_down_cool_down=2**62)
+    T, N = 50, 64
+    depth = torch.full((T, 1, N), 500, dtype=torch.int64, device=engine.dev)
+    depth[::2] = 0
+    tick0 = 2**45
+    st = (np.full(N, 3, np.int32), np.full(N, tick0 - 1, np.int64), np.zeros(N, np.int64))
+    ref = oracle_lib.replay(pol.to_c(), depth.cpu().numpy(), T, 1, N, N, tick0, *st, want_summary=True)
+    out = gpu_full(engine, pol, depth.cpu().numpy(), T, 1, N, N, tick0, st)
+    assert_matches_oracle(out, ref, N)
+    assert (out["replicas"] == 3).all() and (out["st_ju"] == tick0 - 1).all()
+
+
+# ---- sweep ----------------------------------------------------------------------------------------
+
+def test_policy_sweep_matches_oracle_per_policy(engine):
+    """Config 4's shape at small scale: a grid including overlapping thresholds and min>max."""
+    torch = torch_mod()
+    gen = ksa.GenParams(seed=77, family=ksa.GEN_WALK, high_max=500, walk_step=15)
+    T, N = 300, 130
+    walk = engine.gen_walk_init(gen, 0, N)
+    depth = engine.gen_traces(gen, 0, T, 1, 0, N, N, walk=walk)
+    d_host = depth.cpu().numpy()
+    pols = []
+    for up in (100, 250, 30):
+        for down in (10, 120):
+            for cu, cd in ((10 * S, 30 * S), (0, 0), (12 * S, 45 * S)):
+                for mn, mx, su, sd in ((1, 5, 1, 1), (2, 50, 3, 2), (7, 2, 1, 1)):
+                    pols.append(ksa.Policy(attr_mask=1, scale_up_messages=up, scale_down_messages=down,
+                                           scale_up_cool_down=cu, scale_down_cool_down=cd, min_pods=mn,
+                                           max_pods=mx, scale_up_pods=su, scale_down_pods=sd))
+    pols = pols[:53]  # not a multiple of the policy tile
+    r0 = oracle_lib.fresh_state(gen.seed, 0, N, 1, 5)
+    got = engine.replay_sweep(pols, depth, T, 1, N, N, torch.from_numpy(r0[0]).to(engine.dev))
+    got = got.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
+    for i, pol in enumerate(pols):
+        ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, N, 0, *r0, want_full=False, want_summary=True)
+        assert got[i].tobytes() == ref.summary.tobytes(), f"policy {i}: {pol}"
+
+
+# ---- host-buffer pipeline (the e2e path) ----------------------------------------------------------
+
+@pytest.mark.parametrize("A,N,T,chunk", [(1, 1000, 130, 32), (3, 517, 77, 77), (1, 4096, 64, 7)])
+def test_host_pipeline_matches_oracle(engine, A, N, T, chunk):
+    rng = np.random.default_rng(A * 100 + N)
+    pol = ksa.Policy(attr_mask=(1 << A) - 1, scale_up_messages=250, scale_down_messages=25,
+                     scale_up_cool_down=12 * S, scale_down_cool_down=45 * S, max_pods=9)
+    depth = ksa.pinned_empty((T, A, N), np.int64)
+    depth[...] = rng.integers(0, 200, size=(T, A, N), dtype=np.int64)
+    st = oracle_lib.fresh_state(8, 0, N, 1, 5)
+    ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, N, 0, *st, want_summary=True)
+    pipe = ksa.HostPipeline(0, N + 5, A, chunk)
+    try:
+        r, ju, jd = (np.array(x, copy=True) for x in st)
+        replicas = ksa.pinned_empty((T, N), np.int32)
+        events = ksa.pinned_empty((T, N), np.uint8)
+        summary = np.empty(N, dtype=ksa.SUMMARY_DTYPE)
+        pipe.replay(pol, depth, 0, r, ju, jd, replicas, events, summary)
+        assert np.array_equal(replicas, ref.replicas) and np.array_equal(events, ref.events)
+        assert summary.tobytes() == ref.summary.tobytes()
+        assert np.array_equal(r, ref.state_replicas) and np.array_equal(ju, ref.state_last_up)
+        assert np.array_equal(jd, ref.state_last_down)
+        # summary-only call (no per-tick outputs) also advances the state
+        r2, ju2, jd2 = (np.array(x, copy=True) for x in st)
+        pipe.replay(pol, depth, 0, r2, ju2, jd2, None, None, summary)
+        assert summary.tobytes() == ref.summary.tobytes() and np.array_equal(r2, ref.state_replicas)
+    finally:
+        pipe.close()
+
+
+# ---- error behaviour: status codes, never an abort ------------------------------------------------
+
+def test_errors_are_reported_not_raised_as_crashes(engine):
+    torch = torch_mod()
+    depth = torch.zeros((4, 1, 16), dtype=torch.int64, device=engine.dev)
+    state = engine.new_state(16)
+    with pytest.raises(ksa.KsaError, match="poll_period_ns"):
+        engine.replay_full(ksa.Policy(attr_mask=1, poll_period=0), depth, 4, 1, 16, 16, 0, state)
+    with pytest.raises(ksa.KsaError, match="attr_mask"):
+        engine.replay_full(ksa.Policy(attr_mask=7), depth, 4, 1, 16, 16, 0, state)
+    with pytest.raises(ksa.KsaError, match="ld="):
+        engine.replay_full(ksa.Policy(attr_mask=1), depth, 4, 1, 16, 8, 0, state)
+    with pytest.raises(ksa.KsaError, match="2\\^30"):
+        engine.replay_full(ksa.Policy(attr_mask=1), depth, 2**30 + 1, 1, 16, 16, 0, state)
+    with pytest.raises(ksa.KsaError, match="variant"):
+        engine.set_variant(999, 0)
+    # and the engine still works afterwards
+    engine.replay_full(ksa.Policy(attr_mask=1), depth, 4, 1, 16, 16, 0, state)
+    torch.cuda.synchronize()
+
+
+# ---- full BASELINE size, checked through size-independent properties ------------------------------
+
+def test_config2_full_size_properties(engine):
+    """1M traces x 10k ticks, default policy, single attribute (BASELINE.json configs[1]); 136 GB.
+    Checks: (a) a 2048-trace column block equals the oracle bit-for-bit over all 10k ticks,
+    (b) the fingerprint of the full-mode trajectory equals the summary-mode fingerprint for every
+    one of the 2^20 traces, (c) replaying again from the same state reproduces the same bytes
+    (idempotence), (d) chunked == one-shot on the carry state."""
+    torch = torch_mod()
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    N, T = 1 << 20, 10_000
+    need = N * T * 13 + (2 << 30)
+    if free < need:
+        pytest.skip(f"needs {need >> 30} GiB of free device memory, have {free >> 30}")
+    pol = ksa.Policy(attr_mask=1)
+    gen = ksa.GenParams(seed=0x5EED0001)
+    depth = engine.gen_traces(gen, 0, T, 1, 0, N, N)
+    state = engine.new_state(N, seed=gen.seed, lo=1, hi=5)
+    s0 = state.clone()
+    replicas, events = engine.replay_full(pol, depth, T, 1, N, N, 0, state)
+    # (b)
+    st_s = s0.clone()
+    summ = engine.replay_summary(pol, depth, T, 1, N, N, 0, st_s)
+    h_full = engine.traj_hash(replicas, events, T, N, N)
+    sv = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+    assert np.array_equal(h_full.cpu().numpy().view(np.uint64), sv["hash"])
+    assert np.array_equal(sv["final_replicas"], state.replicas.cpu().numpy())
+    assert (sv["ticks"] == T).all()
+    assert torch.equal(st_s.last_up, state.last_up) and torch.equal(st_s.last_down, state.last_down)
+    # (a)
+    c0, c1 = 517 * 1024, 517 * 1024 + 2048
+    d_blk = depth[:, :, c0:c1].contiguous().cpu().numpy()
+    ref = oracle_lib.replay(pol.to_c(), d_blk, T, 1, c1 - c0, c1 - c0, 0,
+                            *oracle_lib.fresh_state(gen.seed, c0, c1 - c0, 1, 5), want_summary=True)
+    assert np.array_equal(replicas[:, c0:c1].cpu().numpy(), ref.replicas)
+    assert np.array_equal(events[:, c0:c1].cpu().numpy(), ref.events)
+    assert sv[c0:c1].tobytes() == ref.summary.tobytes()
+    # (c) idempotence: same inputs, same state -> same fingerprint
+    h_first = h_full.clone()
+    state2 = s0.clone()
+    engine.replay_full(pol, depth, T, 1, N, N, 0, state2, replicas=replicas, events=events)
+    assert torch.equal(engine.traj_hash(replicas, events, T, N, N), h_first)
+    # (d) chunked replay of the same block reaches the same carry state
+    state3 = s0.clone()
+    for t0 in range(0, T, 2500):
+        engine.replay_full(pol, depth[t0:t0 + 2500], 2500, 1, N, N, t0, state3,
+                           replicas=replicas[t0:t0 + 2500], events=events[t0:t0 + 2500])
+    assert torch.equal(state3.replicas, state.replicas) and torch.equal(state3.last_up, state.last_up)
+    assert torch.equal(engine.traj_hash(replicas, events, T, N, N), h_first)
+    del depth, replicas, events
+    torch.cuda.empty_cache()

@@ -1,0 +1,109 @@
+"""CPU: the host-side mirror of the reference's operator interface (flags, durations, sharding)."""
+from __future__ import annotations
+
+import argparse
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import kube_sqs_autoscaler_b200 as ksa
+from kube_sqs_autoscaler_b200.policy import Policy, attr_mask_from_names, parse_duration
+
+S = 10**9
+
+
+@pytest.mark.parametrize("text,ns", [
+    ("5s", 5 * S), ("30s", 30 * S), ("10s", 10 * S), ("5m", 300 * S), ("1h", 3600 * S),
+    ("1.5s", 1_500_000_000), ("300ms", 300_000_000), ("2h45m", (2 * 3600 + 45 * 60) * S),
+    ("-1.5h", -5400 * S), ("0", 0), ("1us", 1000), ("1µs", 1000), ("7ns", 7), (".5s", S // 2),
+    ("+3s", 3 * S),
+])
+def test_parse_duration_go_syntax(text, ns):
+    assert parse_duration(text) == ns
+
+
+@pytest.mark.parametrize("text", ["", "5", "s", "1.s.", "5 s", "1d", "--1s", "9223372036854775808ns"])
+def test_parse_duration_rejects(text):
+    with pytest.raises(ValueError):
+        parse_duration(text)
+
+
+def test_reference_command_line_parses_unchanged():
+    """The README's deployment command (README.md:39-54) must parse; network flags are ignored."""
+    ap = argparse.ArgumentParser()
+    Policy.add_flags(ap)
+    ns = ap.parse_args([
+        "--sqs-queue-url=https://sqs.your_aws_region.amazonaws.com/your_aws_account_number/your_queue_name",
+        "--kubernetes-deployment=your-kubernetes-deployment-name", "--kubernetes-namespace=$(K8S_NAMESPACE)",
+        "--aws-region=us-west-2", "--poll-period=10s", "--scale-down-cool-down=30s",
+        "--scale-up-cool-down=5m", "--scale-up-messages=20", "--scale-down-messages=10",
+        "--max-pods=30", "--min-pods=1",
+    ])
+    p = Policy.from_args(ns)
+    assert (p.poll_period, p.scale_up_cool_down, p.scale_down_cool_down) == (10 * S, 300 * S, 30 * S)
+    assert (p.scale_up_messages, p.scale_down_messages, p.max_pods, p.min_pods) == (20, 10, 30, 1)
+    assert p.attr_mask == 0b111 and p.num_attrs == 3
+
+
+def test_defaults_are_the_reference_defaults():
+    ap = argparse.ArgumentParser()
+    Policy.add_flags(ap)
+    assert Policy.from_args(ap.parse_args([])) == Policy()  # main.go:83-93
+
+
+def test_attribute_names():
+    assert attr_mask_from_names("ApproximateNumberOfMessages") == 1
+    assert attr_mask_from_names(" ApproximateNumberOfMessagesNotVisible , ApproximateNumberOfMessages") == 5
+    with pytest.raises(ValueError):
+        attr_mask_from_names("ApproximateAgeOfOldestMessage")
+
+
+def test_shard_range_partitions_exactly():
+    for n_total in (0, 1, 7, 64, 2**26, 1000003):
+        for world in (1, 2, 3, 4, 8):
+            cuts = [ksa.shard_range(n_total, world, r) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n_total
+            assert all(cuts[i][1] == cuts[i + 1][0] for i in range(world - 1))
+            sizes = [e - b for b, e in cuts]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        ksa.shard_range(10, 2, 2)
+
+
+def test_engine_refuses_to_run_without_cuda(built):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("this check is for the CPU box")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ksa.ReplayEngine()
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_two_rank_gloo_shards_and_gathers(tmp_path):
+    """world_size=2 over gloo: each rank replays its shard (with the CPU oracle standing in for the
+    GPU on this box), rank 0 gathers the summaries; result equals the unsharded replay."""
+    worker = os.path.join(os.path.dirname(__file__), "gloo_shard_worker.py")
+    out = tmp_path / "gathered.npy"
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"], worker, str(out)],
+                       capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    got = np.load(out)
+    from tests import oracle_lib
+    from tests.gloo_shard_worker import GEN, N_TOTAL, POLICY, T
+    depth = oracle_lib.gen_traces(GEN.to_c(), 0, T, 1, 0, N_TOTAL, N_TOTAL)
+    ref = oracle_lib.replay(POLICY.to_c(), depth, T, 1, N_TOTAL, N_TOTAL, 0,
+                            *oracle_lib.fresh_state(GEN.seed, 0, N_TOTAL, 1, 5),
+                            want_full=False, want_summary=True)
+    assert got.tobytes() == ref.summary.tobytes()
