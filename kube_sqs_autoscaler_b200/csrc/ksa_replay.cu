@@ -287,6 +287,19 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(14, MODE_FULL, 4, 3, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
     KSA_VARIANT(15, MODE_FULL, 4, 4, HINT_NA_EF, 1, 128, 7, 4, 2, 128, 6, 4, 2, 128, 5),
     KSA_VARIANT(16, MODE_FULL_OPT, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
+    KSA_VARIANT(17, MODE_FULL, 4, 2, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 2, 128, 8),
+    KSA_VARIANT(18, MODE_FULL, 4, 3, HINT_NA, 0, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(19, MODE_FULL, 4, 3, HINT_NA, 1, 256, 4, 4, 2, 256, 3, 2, 3, 256, 3),
+    KSA_VARIANT(20, MODE_FULL, 2, 4, HINT_NA, 1, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(21, MODE_FULL, 2, 6, HINT_NA, 1, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
+    KSA_VARIANT(22, MODE_FULL, 4, 3, HINT_NA_EF, 1, 128, 8, 4, 2, 128, 6, 4, 1, 128, 8),
+    KSA_VARIANT(23, MODE_FULL, 8, 2, HINT_NA, 1, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    KSA_VARIANT(24, MODE_FULL, 4, 2, HINT_NA, 1, 128, 9, 4, 1, 128, 8, 2, 2, 128, 9),
+    KSA_VARIANT(25, MODE_FULL, 4, 3, HINT_NA, 1, 64, 16, 4, 2, 64, 12, 2, 3, 64, 14),
+    KSA_VARIANT(26, MODE_FULL, 2, 8, HINT_NA, 1, 128, 7, 2, 4, 128, 7, 1, 6, 128, 8),
+    KSA_VARIANT(27, MODE_FULL, 1, 8, HINT_NA, 1, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+    KSA_VARIANT(28, MODE_FULL, 1, 12, HINT_NA, 1, 256, 4, 1, 6, 256, 4, 1, 4, 256, 4),
+    KSA_VARIANT(29, MODE_FULL, 4, 3, HINT_NA, 1, 128, 7, 4, 2, 128, 6, 2, 3, 128, 7),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -297,9 +310,9 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
     KSA_VARIANT(6, MODE_SUMMARY, 1, 8, HINT_NA, 0, 256, 4, 1, 4, 256, 4, 1, 4, 256, 4),
 };
-constexpr int kDefaultFull = 1;
+constexpr int kDefaultFull = 14;
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
-constexpr int kDefaultSummary = 1;
+constexpr int kDefaultSummary = 0;  // the scalar kernel: summary mode is ALU-bound, more traces per thread only add register pressure
 
 template <size_t K>
 const Variant* find_variant(const Variant (&table)[K], int id) {
