@@ -345,7 +345,7 @@ def main():
                        "policy": "reference defaults (main.go:83-91)", "generator": "bands seed 0x5EED0001",
                        "parallelism": f"trace-sharded x{world}, no collective",
                        "l2": "inputs (84 GB) >> L2, no flush needed",
-                       "kernel_variant": eng.variant_name(0, args.variant or 14)},
+                       "kernel_variant": eng.variant_name(0, args.variant or -1)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8TBs": achieved / 8000.0,
                          "traffic": (traffic or {}).get("dram_bytes_per_launch"),

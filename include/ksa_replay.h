@@ -97,7 +97,8 @@ typedef struct ksa_state {
  * Per-trace summary (64 bytes). Counters accumulate across chunked calls when the caller does not
  * clear the buffer in between (ksa_summary_clear starts a fresh accumulation).
  *  hash: order-sensitive 64-bit fingerprint of the (replicas, event) trajectory:
- *        h <- (h + ((uint64)(uint32)replicas << 8 | event)) * 0x9E3779B97F4A7C15  per tick, h0 = 0.
+ *        h <- h * 0x9E3779B97F4A7C15 + ((uint64)event << 32 | (uint32)replicas)  per tick, h0 = 0
+ *        (a polynomial in the odd multiplier over Z/2^64: any single-tick difference changes it).
  */
 typedef struct ksa_summary {
   int32_t final_replicas;
@@ -267,7 +268,8 @@ int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy, const int64_t
 int ksa_set_variant(int32_t full_variant, int32_t summary_variant);
 
 /* Name of a variant ("V4_D4_H1_B128x7": traces per thread, prefetch depth, load hint, block x
- * min-blocks-per-SM), or NULL if there is no such id. mode 0 = full, 1 = summary; id 0 = scalar. */
+ * min-blocks-per-SM), or NULL if there is no such id. mode 0 = full, 1 = summary; id 0 = the scalar
+ * kernel, id -1 = the library default. */
 const char* ksa_variant_name(int32_t mode, int32_t id);
 
 /* Number of kernel launches issued by this library on the calling thread since the last call

@@ -142,8 +142,50 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
   return ev;
 }
 
-// Trajectory fingerprint step (ksa_summary.hash, include/ksa_replay.h).
+// Third spelling: as ksa_step_ptx, but every conditional move / add is written as a predicated
+// integer multiply-add by `one` (a kernel argument that is always 1 and that ptxas cannot fold).
+// On sm_100a IMAD issues on the FMA pipe while ISETP/SEL/VIADDMNMX issue on the half-rate ALU pipe,
+// which is the pipe this state machine saturates first (profiles/r01_ncu_full_v14_T2000.txt: ALU
+// 56 % active, FMA 12 %). This moves 9 of the 22 ALU operations per decision to the idle pipe.
+__device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long long n, int i, int iu,
+                                                 int id, int one, ksa_trace_regs& s) {
+  unsigned ev;
+  asm("{\n\t"
+      ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dcool, dapp;\n\t"
+      ".reg .s32 t, u;\n\t"
+      "setp.ge.s64 uh, %4, %5;\n\t"                 // main.go:51
+      "setp.le.and.s32 ugo, %2, %12, uh;\n\t"       // main.go:52
+      "setp.gt.and.s32 ucool, %2, %12, uh;\n\t"
+      "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
+      "@ugo mad.lo.s32 %2, %11, %14, 0;\n\t"        // main.go:62   lu = i
+      "selp.u32 %0, 16, 0, ucool;\n\t"
+      "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"         // UP_NOOP unless ...
+      "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"       // ... UP_APPLIED
+      "add.s32 t, %1, %9;\n\t"                      // scale.go:66
+      "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
+      "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
+      "setp.le.and.s64 dh, %4, %6, !ucool;\n\t"     // main.go:65 (+ :54)
+      "setp.le.and.s32 dgo, %3, %13, dh;\n\t"       // main.go:66
+      "setp.gt.and.s32 dcool, %3, %13, dh;\n\t"
+      "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
+      "@dgo mad.lo.s32 %3, %11, %14, 0;\n\t"        // main.go:76   ld = i
+      "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
+      "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
+      "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
+      "sub.s32 u, %1, %10;\n\t"                     // scale.go:94
+      "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
+      "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
+      "}"
+      : "=r"(ev), "+r"(s.r), "+r"(s.lu), "+r"(s.ld)
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
+        "r"(c.down32), "r"(i), "r"(iu), "r"(id), "r"(one));
+  return ev;
+}
+
+// Trajectory fingerprint step (ksa_summary.hash, include/ksa_replay.h):
+//   h <- h * M + ((uint64)event << 32 | (uint32)replicas)
+// Three IMADs on the FMA pipe; the addend needs no shifting or masking.
 #define KSA_HASH_MUL 0x9E3779B97F4A7C15ull
 __device__ __forceinline__ unsigned long long ksa_hash_step(unsigned long long h, int r, unsigned ev) {
-  return (h + (((unsigned long long)(unsigned)r << 8) | (unsigned long long)ev)) * KSA_HASH_MUL;
+  return h * KSA_HASH_MUL + (((unsigned long long)ev << 32) | (unsigned long long)(unsigned)r);
 }

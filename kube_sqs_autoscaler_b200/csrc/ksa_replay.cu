@@ -23,6 +23,7 @@ struct ReplayArgs {
   long long n_begin; // first trace of this launch
   long long n_count; // traces of this launch (a multiple of V)
   int T;
+  int one;  // always 1: a multiplier ptxas cannot fold (ksa_step_fma)
   int* st_r;
   long long* st_ju;
   long long* st_jd;
@@ -34,7 +35,8 @@ struct ReplayArgs {
 // MODE_FULL writes both outputs; MODE_FULL_OPT tests the two output pointers at run time (either may
 // be NULL); MODE_SUMMARY writes nothing per tick.
 enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
-// STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (same function, predication spelled out in PTX)
+// STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (predication spelled out in PTX), 2 = ksa_step_fma
+// (conditional moves/adds as predicated IMADs on the FMA pipe). Same function, same results.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
 
@@ -89,14 +91,33 @@ __device__ __forceinline__ void store_replicas(int* p, const int (&r)[V]) {
     asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(r[0]), "r"(r[1]),
                  "r"(r[2]), "r"(r[3]) : "memory");
   } else {
-    static_assert(V == 8, "V must be 1, 2, 4 or 8");
-    asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]),
-                 "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
-                 : "memory");
+    static_assert(V == 8 || V == 16, "V must be 1, 2, 4, 8 or 16");
+#pragma unroll
+    for (int q = 0; q < V / 8; ++q)
+      asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p + 8 * q),
+                   "r"(r[8 * q]), "r"(r[8 * q + 1]), "r"(r[8 * q + 2]), "r"(r[8 * q + 3]),
+                   "r"(r[8 * q + 4]), "r"(r[8 * q + 5]), "r"(r[8 * q + 6]), "r"(r[8 * q + 7])
+                   : "memory");
   }
 }
 
-template <int V>
+// Pack V event bytes into words. FMA = true packs with multiply-adds (e1 * 256 + e0 ...), which
+// ptxas emits as IMAD on the FMA pipe instead of shifts and LOP3 on the ALU pipe.
+template <bool FMA>
+__device__ __forceinline__ unsigned pack4(unsigned e0, unsigned e1, unsigned e2, unsigned e3) {
+  if constexpr (FMA) {
+    unsigned w;
+    asm("mad.lo.u32 %0, %2, 256, %1;\n\t"
+        "mad.lo.u32 %0, %3, 65536, %0;\n\t"
+        "mad.lo.u32 %0, %4, 16777216, %0;"
+        : "=&r"(w) : "r"(e0), "r"(e1), "r"(e2), "r"(e3));
+    return w;
+  } else {
+    return e0 | (e1 << 8) | (e2 << 16) | (e3 << 24);
+  }
+}
+
+template <int V, bool FMA>
 __device__ __forceinline__ void store_events(unsigned char* p, const unsigned (&e)[V]) {
   if constexpr (V == 1) {
     asm volatile("st.global.cs.b8 [%0], %1;" ::"l"(p), "r"(e[0]) : "memory");
@@ -104,22 +125,45 @@ __device__ __forceinline__ void store_events(unsigned char* p, const unsigned (&
     const unsigned short w = (unsigned short)(e[0] | (e[1] << 8));
     asm volatile("st.global.cs.b16 [%0], %1;" ::"l"(p), "h"(w) : "memory");
   } else if constexpr (V == 4) {
-    const unsigned w = e[0] | (e[1] << 8) | (e[2] << 16) | (e[3] << 24);
+    const unsigned w = pack4<FMA>(e[0], e[1], e[2], e[3]);
     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
-  } else {
-    const unsigned w0 = e[0] | (e[1] << 8) | (e[2] << 16) | (e[3] << 24);
-    const unsigned w1 = e[4] | (e[5] << 8) | (e[6] << 16) | (e[7] << 24);
+  } else if constexpr (V == 8) {
+    const unsigned w0 = pack4<FMA>(e[0], e[1], e[2], e[3]);
+    const unsigned w1 = pack4<FMA>(e[4], e[5], e[6], e[7]);
     asm volatile("st.global.cs.v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(w0), "r"(w1) : "memory");
+  } else {
+    static_assert(V == 16, "V must be 1, 2, 4, 8 or 16");
+    const unsigned w0 = pack4<FMA>(e[0], e[1], e[2], e[3]);
+    const unsigned w1 = pack4<FMA>(e[4], e[5], e[6], e[7]);
+    const unsigned w2 = pack4<FMA>(e[8], e[9], e[10], e[11]);
+    const unsigned w3 = pack4<FMA>(e[12], e[13], e[14], e[15]);
+    asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
   }
 }
 
-// Per-trace accumulators of summary mode (registers).
+// Per-trace accumulators of summary mode (registers). The six event counters are kept as 8-bit
+// fields of two registers (pk4: bits 0..3 of the event byte, one field per byte; pk2: bits 4 and 5
+// at bit 8 and bit 16) and are added into the 32-bit counters of the ksa_summary record in global
+// memory before a field can overflow (every <= 255 ticks).
 struct SummaryRegs {
   int rmin, rmax;
-  unsigned c_ua, c_da, c_un, c_dn, c_uc, c_dc;
+  unsigned pk4, pk2;
   long long sum;
   unsigned long long hash;
 };
+constexpr int kFlushTicks = 255;
+
+// d = a * b + c on the FMA pipe (ptxas keeps a true IMAD when b is not a compile-time constant).
+__device__ __forceinline__ unsigned mad_u32(unsigned a, unsigned b, unsigned c) {
+  unsigned d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ long long mad_wide_s32(int a, int b, long long c) {
+  long long d;
+  asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+  return d;
+}
 
 template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
@@ -128,6 +172,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const long long n0 = a.n_begin + g * V;
   const ksa_step_consts c(a.pk);
   const int T = a.T;
+  const int one = a.one;  // always 1; see ksa_step_fma
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -143,11 +188,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       const ksa_summary* q = a.summary + n0 + v;
       sm[v].rmin = q->min_replicas;
       sm[v].rmax = q->max_replicas;
-      sm[v].c_ua = sm[v].c_da = sm[v].c_un = sm[v].c_dn = sm[v].c_uc = sm[v].c_dc = 0u;
+      sm[v].pk4 = sm[v].pk2 = 0u;
       sm[v].sum = q->sum_replicas;
       sm[v].hash = q->hash;
     }
   }
+  auto flush_counters = [&]() {
+    if constexpr (MODE == MODE_SUMMARY) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        ksa_summary* q = a.summary + n0 + v;
+        q->up_applied += sm[v].pk4 & 0xffu;
+        q->down_applied += (sm[v].pk4 >> 8) & 0xffu;
+        q->up_noop += (sm[v].pk4 >> 16) & 0xffu;
+        q->down_noop += sm[v].pk4 >> 24;
+        q->up_cool += (sm[v].pk2 >> 8) & 0xffu;
+        q->down_cool += (sm[v].pk2 >> 16) & 0xffu;
+        sm[v].pk4 = sm[v].pk2 = 0u;
+      }
+    }
+  };
 
   const long long row = (long long)A * a.ld;  // elements between consecutive ticks
   const long long* dp = a.depth + n0;
@@ -185,35 +245,53 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     unsigned ev[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      ev[v] = STEP == 1 ? ksa_step_ptx(c, n[v], i, iu, id, s[v]) : ksa_step(c, n[v], i, iu, id, s[v]);
+      if constexpr (STEP == 2)
+        ev[v] = ksa_step_fma(c, n[v], i, iu, id, one, s[v]);
+      else if constexpr (STEP == 1)
+        ev[v] = ksa_step_ptx(c, n[v], i, iu, id, s[v]);
+      else
+        ev[v] = ksa_step(c, n[v], i, iu, id, s[v]);
       rr[v] = s[v].r;
     }
     if constexpr (MODE != MODE_SUMMARY) {
       if (want_r) store_replicas<V>(rp + (long long)tt * a.ld, rr);
-      if (want_e) store_events<V>(ep + (long long)tt * a.ld, ev);
+      if (want_e) store_events<V, STEP == 2>(ep + (long long)tt * a.ld, ev);
     } else {
 #pragma unroll
       for (int v = 0; v < V; ++v) {
         sm[v].rmin = min(sm[v].rmin, rr[v]);
         sm[v].rmax = max(sm[v].rmax, rr[v]);
-        sm[v].c_ua += (ev[v] >> 0) & 1u;
-        sm[v].c_da += (ev[v] >> 1) & 1u;
-        sm[v].c_un += (ev[v] >> 2) & 1u;
-        sm[v].c_dn += (ev[v] >> 3) & 1u;
-        sm[v].c_uc += (ev[v] >> 4) & 1u;
-        sm[v].c_dc += (ev[v] >> 5) & 1u;
-        sm[v].sum = (long long)((unsigned long long)sm[v].sum + (unsigned long long)(long long)rr[v]);
+        // spread event bits 0..3 into four byte fields / bits 4,5 into two: one IMAD + one LOP3 each
+        const unsigned f4 = (ev[v] * 0x00204081u) & 0x01010101u;
+        const unsigned f2 = (ev[v] * 0x00000810u) & 0x00010100u;
+        if constexpr (STEP == 2) {
+          sm[v].pk4 = mad_u32(f4, (unsigned)one, sm[v].pk4);
+          sm[v].pk2 = mad_u32(f2, (unsigned)one, sm[v].pk2);
+          sm[v].sum = mad_wide_s32(rr[v], one, sm[v].sum);
+        } else {
+          sm[v].pk4 += f4;
+          sm[v].pk2 += f2;
+          sm[v].sum = (long long)((unsigned long long)sm[v].sum + (unsigned long long)(long long)rr[v]);
+        }
         sm[v].hash = ksa_hash_step(sm[v].hash, rr[v], ev[v]);
       }
     }
   };
 
   int t = 0;
+  int pending = 0;  // ticks accumulated in the packed counters
   // Steady state: every tick of the group exists and so does the tick D ahead of it.
 #pragma unroll 1
   for (; t + 2 * D <= T; t += D) {
 #pragma unroll
     for (int j = 0; j < D; ++j) tick(t + j, j, true);
+    if constexpr (MODE == MODE_SUMMARY) {
+      pending += D;
+      if (pending > kFlushTicks - D) {
+        flush_counters();
+        pending = 0;
+      }
+    }
   }
   // Drain: at most 2D-1 ticks left; guard both the tick and its prefetch.
 #pragma unroll 1
@@ -221,6 +299,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
     for (int j = 0; j < D; ++j)
       if (t + j < T) tick(t + j, j, t + j + D < T);
+    if constexpr (MODE == MODE_SUMMARY) {
+      flush_counters();
+    }
   }
 
 #pragma unroll
@@ -230,18 +311,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     a.st_jd[n0 + v] = ksa_global_stamp(s[v].ld, a.tick0, a.st_jd[n0 + v]);
   }
   if constexpr (MODE == MODE_SUMMARY) {
+    flush_counters();
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       ksa_summary* q = a.summary + n0 + v;
       q->final_replicas = s[v].r;
       q->min_replicas = sm[v].rmin;
       q->max_replicas = sm[v].rmax;
-      q->up_applied += sm[v].c_ua;
-      q->down_applied += sm[v].c_da;
-      q->up_noop += sm[v].c_un;
-      q->down_noop += sm[v].c_dn;
-      q->up_cool += sm[v].c_uc;
-      q->down_cool += sm[v].c_dc;
       q->ticks += (long long)T;
       q->sum_replicas = sm[v].sum;
       q->hash = sm[v].hash;
@@ -300,6 +376,18 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(27, MODE_FULL, 1, 8, HINT_NA, 1, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
     KSA_VARIANT(28, MODE_FULL, 1, 12, HINT_NA, 1, 256, 4, 1, 6, 256, 4, 1, 4, 256, 4),
     KSA_VARIANT(29, MODE_FULL, 4, 3, HINT_NA, 1, 128, 7, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(30, MODE_FULL, 8, 2, HINT_NA, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    KSA_VARIANT(31, MODE_FULL, 8, 3, HINT_NA, 2, 128, 3, 4, 4, 128, 4, 4, 3, 128, 4),
+    KSA_VARIANT(32, MODE_FULL, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
+    KSA_VARIANT(33, MODE_FULL, 8, 2, HINT_NA, 2, 64, 8, 4, 3, 64, 10, 4, 2, 64, 10),
+    KSA_VARIANT(34, MODE_FULL, 8, 1, HINT_NA, 2, 128, 5, 8, 1, 128, 5, 4, 1, 128, 6),
+    KSA_VARIANT(35, MODE_FULL, 16, 1, HINT_NA, 2, 128, 2, 8, 2, 128, 3, 8, 1, 128, 4),
+    KSA_VARIANT(36, MODE_FULL, 16, 2, HINT_NA, 2, 64, 4, 8, 2, 64, 6, 8, 1, 64, 8),
+    KSA_VARIANT(37, MODE_FULL, 4, 3, HINT_NA, 2, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(38, MODE_FULL, 8, 2, HINT_NA_EF, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    KSA_VARIANT(39, MODE_FULL, 8, 2, HINT_NA, 2, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
+    KSA_VARIANT(40, MODE_FULL, 8, 2, HINT_NA, 1, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
+    KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -309,10 +397,17 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(4, MODE_SUMMARY, 4, 4, HINT_NA_EF, 0, 128, 4, 4, 2, 128, 3, 4, 2, 128, 3),
     KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
     KSA_VARIANT(6, MODE_SUMMARY, 1, 8, HINT_NA, 0, 256, 4, 1, 4, 256, 4, 1, 4, 256, 4),
+    KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+    KSA_VARIANT(8, MODE_SUMMARY, 2, 8, HINT_NA, 2, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
+    KSA_VARIANT(9, MODE_SUMMARY, 4, 4, HINT_NA, 2, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
+    KSA_VARIANT(10, MODE_SUMMARY, 8, 2, HINT_NA, 2, 128, 3, 4, 3, 128, 3, 4, 2, 128, 3),
+    KSA_VARIANT(11, MODE_SUMMARY, 4, 4, HINT_NA, 1, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
+    KSA_VARIANT(12, MODE_SUMMARY, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(13, MODE_SUMMARY, 4, 3, HINT_NA, 2, 128, 6, 4, 2, 128, 5, 4, 1, 128, 6),
 };
-constexpr int kDefaultFull = 14;
+constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
-constexpr int kDefaultSummary = 0;  // the scalar kernel: summary mode is ALU-bound, more traces per thread only add register pressure
+constexpr int kDefaultSummary = 12;  // summary mode is ALU-bound: few traces per thread, high occupancy
 
 template <size_t K>
 const Variant* find_variant(const Variant (&table)[K], int id) {
@@ -350,6 +445,7 @@ int replay_common(int mode, const ksa_policy* policy, const int64_t* depth_dev, 
   args.ld = ld;
   args.tick0 = tick0;
   args.T = (int)T;
+  args.one = 1;
   args.st_r = state->replicas_dev;
   args.st_ju = (long long*)state->last_up_tick_dev;
   args.st_jd = (long long*)state->last_down_tick_dev;
@@ -409,6 +505,7 @@ bool ksa_replay_variant_exists(int mode, int id) {
 }
 // Variant names for tools/ (not part of the C ABI header; looked up with dlsym by the sweep tool).
 extern "C" const char* ksa_variant_name(int32_t mode, int32_t id) {
+  if (id == -1) id = mode == MODE_FULL ? kDefaultFull : kDefaultSummary;  // the library default
   const Variant* v = mode == MODE_FULL ? find_variant(kFullVariants, id) : find_variant(kSummaryVariants, id);
   return v ? v->name : nullptr;
 }

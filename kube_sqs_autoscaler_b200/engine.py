@@ -58,6 +58,11 @@ class TraceState:
         return self.replicas.numel()
 
 
+def policy_array(policies: list[Policy]):
+    """ctypes array of ksa_policy records for replay_sweep (build once, reuse across calls)."""
+    return (_abi.KsaPolicy * len(policies))(*[p.to_c() for p in policies])
+
+
 def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -150,7 +155,8 @@ class ReplayEngine:
                      replicas0: torch.Tensor, summary: torch.Tensor | None = None) -> torch.Tensor:
         """ksa_replay_sweep: [P][N][64] uint8 summaries, every policy from a fresh process."""
         P = len(policies)
-        arr = (_abi.KsaPolicy * P)(*[p.to_c() for p in policies])
+        # a prebuilt ctypes array (policy_array) skips the per-call conversion of the grid
+        arr = policies if isinstance(policies, C.Array) else policy_array(policies)
         table = torch.empty(P * _abi.POLICY_K_BYTES, dtype=torch.uint8, device=self.dev)
         if summary is None:
             summary = torch.empty((P, N, 64), dtype=torch.uint8, device=self.dev)

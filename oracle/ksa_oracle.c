@@ -133,7 +133,7 @@ static inline void summary_add(ksa_summary* s, int32_t r, uint8_t ev) {
   s->down_cool += (ev & KSA_EV_DOWN_COOL) != 0;
   s->ticks += 1;
   s->sum_replicas = wrap_add64(s->sum_replicas, (int64_t)r);
-  s->hash = (s->hash + (((uint64_t)(uint32_t)r << 8) | ev)) * HASH_MUL;
+  s->hash = s->hash * HASH_MUL + (((uint64_t)ev << 32) | (uint64_t)(uint32_t)r);
 }
 
 void ksa_oracle_summary_clear(ksa_summary* s, int64_t N) {
@@ -261,7 +261,7 @@ void ksa_oracle_traj_hash(const int32_t* replicas, const uint8_t* events, int64_
   for (int64_t n = 0; n < N; ++n) {
     uint64_t h = chain ? hash[n] : 0;
     for (int64_t t = 0; t < T; ++t)
-      h = (h + (((uint64_t)(uint32_t)replicas[t * ld + n] << 8) | events[t * ld + n])) * HASH_MUL;
+      h = h * HASH_MUL + (((uint64_t)events[t * ld + n] << 32) | (uint64_t)(uint32_t)replicas[t * ld + n]);
     hash[n] = h;
   }
 }

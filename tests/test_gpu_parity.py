@@ -19,8 +19,8 @@ pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2] + list(range(1, 30))   # -2 = scalar kernel
-SUMMARY_VARIANTS = [-2] + list(range(1, 7))
+FULL_VARIANTS = [-2] + list(range(1, 42))   # -2 = scalar kernel
+SUMMARY_VARIANTS = [-2] + list(range(1, 14))
 
 
 def torch_mod():

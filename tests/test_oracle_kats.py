@@ -139,7 +139,7 @@ def test_c_oracles_equal_python_restatement(pol, data):
         assert s[name] == sum(1 for e in p_e if e & bit)
     h = 0
     for r, e in zip(p_r, p_e):
-        h = ((h + (((r & 0xFFFFFFFF) << 8) | e)) * 0x9E3779B97F4A7C15) & (2**64 - 1)
+        h = (h * 0x9E3779B97F4A7C15 + ((e << 32) | (r & 0xFFFFFFFF))) & (2**64 - 1)
     assert int(s["hash"]) == h
     assert int(s["sum_replicas"]) == ((sum(p_r) + 2**63) % 2**64) - 2**63
 
