@@ -35,33 +35,33 @@ static_assert(sizeof(ksa_policy_k) == 48, "ksa_policy_k is part of the sweep ABI
 // Cool-downs longer than a chunk behave, inside the chunk, like "blocked until the chunk ends".
 #define KSA_COOL_CAP ((1 << 30) + 1)
 
-// Chunk-local cool-down state of one direction: `l` = local tick of the last stamp, shifted so
-// that the gate is a single compare:   blocked at local tick i   <=>   i - c < l,
-// with c = min(cool_ticks, KSA_COOL_CAP). A stamp at local tick i sets l = i (>= 1); values <= 0
-// encode the stamp inherited from before the chunk:
-//   l0 = min(max(cool - (tick0 - last), 0), c) - c         (in [-c, 0]).
-// Proof of equivalence with `k - last < cool` (k = tick0 + i): SURVEY.md §3.4 gives the tick
-// form; for an inherited stamp, blocked <=> i < cool - (tick0 - last) =: s; clamping s into
-// [0, c] does not change `i < s` for 1 <= i <= T <= 2^30 < c when cool > c, and is the identity
-// otherwise.
+// Chunk-local cool-down state of one direction: `s` = the first local tick at which the gate is
+// open again, so the gate is a single compare:   blocked at local tick i   <=>   i < s.
+// A stamp at local tick i sets s = i + c with c = min(cool_ticks, KSA_COOL_CAP) (so s >= 1 + c);
+// the stamp inherited from before the chunk is encoded as
+//   s0 = min(max(cool - (tick0 - last), 0), c)            (in [0, c]).
+// Equivalence with the reference's `last.Add(cool).After(now)`: SURVEY.md §3.4 gives the tick form
+// `k - last < cool` with k = tick0 + i; for an inherited stamp that is i < cool - (tick0 - last),
+// and clamping the right-hand side into [0, c] does not change the comparison for
+// 1 <= i <= T <= 2^30 < KSA_COOL_CAP. All values stay below 2^31: i + c <= 2^30 + 2^30 + 1.
 __device__ __forceinline__ int ksa_local_stamp(long long cool, int c, long long tick0, long long last) {
   long long s = cool - (tick0 - last);
   s = s < 0 ? 0 : s;
   s = s > (long long)c ? (long long)c : s;
-  return (int)s - c;
+  return (int)s;
 }
-// Stamp to write back: unchanged unless a stamp was taken in this chunk (l >= 1).
-__device__ __forceinline__ long long ksa_global_stamp(int l, long long tick0, long long last) {
-  return l >= 1 ? tick0 + (long long)l : last;
+// Stamp to write back: unchanged unless a stamp was taken in this chunk (s > c).
+__device__ __forceinline__ long long ksa_global_stamp(int s, int c, long long tick0, long long last) {
+  return s > c ? tick0 + (long long)(s - c) : last;
 }
 
 struct ksa_trace_regs {
   int r;   // replicas (Deployment.Spec.Replicas)
-  int lu;  // chunk-local lastScaleUpTime   (see above)
-  int ld;  // chunk-local lastScaleDownTime
+  int su;  // chunk-local "scale-up gate opens at" tick   (lastScaleUpTime + cool, see above)
+  int sd;  // chunk-local "scale-down gate opens at" tick
 };
 
-// Per-launch constants in the form the step function wants them.
+// Per-launch (replay) or per-policy (sweep) constants in the form the step function wants them.
 struct ksa_step_consts {
   long long up_msgs, down_msgs;
   int max32, min32, up32, down32;
@@ -73,16 +73,15 @@ struct ksa_step_consts {
         cd((int)(p.cd > KSA_COOL_CAP ? KSA_COOL_CAP : p.cd)) {}
 };
 
-// One tick of one trace. `n` = attribute sum, `i` = local tick (1-based), `iu` = i - cu,
-// `id` = i - cd (warp-uniform, hoisted by the caller). Returns the KSA_EV_* bits.
+// One tick of one trace. `n` = attribute sum, `i` = local tick (1-based). Returns the KSA_EV_* bits.
 // Written so that each predicate dies right after it is used: a thread has only 7 predicate
-// registers and runs 2-8 traces interleaved.
-__device__ __forceinline__ unsigned ksa_step(const ksa_step_consts& c, long long n, int i, int iu,
-                                             int id, ksa_trace_regs& s) {
+// registers and runs up to 16 traces interleaved.
+__device__ __forceinline__ unsigned ksa_step(const ksa_step_consts& c, long long n, int i,
+                                             ksa_trace_regs& s) {
   // ---- scale-up half: main.go:51-63 ----
   const bool up_hit = n >= c.up_msgs;                 // main.go:51
-  const bool up_go = up_hit && (s.lu <= iu);          // main.go:52 false -> :57
-  const bool up_cool = up_hit && (s.lu > iu);         // main.go:52 true  -> :53-54 (continue)
+  const bool up_go = up_hit && (s.su <= i);           // main.go:52 false -> :57
+  const bool up_cool = up_hit && (s.su > i);          // main.go:52 true  -> :53-54 (continue)
   const bool up_applied = up_go && (s.r < c.max32);   // scale.go:62 false -> :66-78
   //    up_noop = up_go && !up_applied                   scale.go:62 true  -> :63-64, returns nil
   unsigned ev = up_cool ? KSA_EV_UP_COOL : 0u;
@@ -90,34 +89,35 @@ __device__ __forceinline__ unsigned ksa_step(const ksa_step_consts& c, long long
   ev = up_applied ? KSA_EV_UP_APPLIED : ev;
   const int r_up = min((int)((unsigned)s.r + (unsigned)c.up32), c.max32);  // scale.go:66-69
   s.r = up_applied ? r_up : s.r;
-  s.lu = up_go ? i : s.lu;                            // main.go:62 (also after the no-op)
+  s.su = up_go ? i + c.cu : s.su;                     // main.go:62 (also after the no-op)
   // ---- scale-down half: main.go:65-77; skipped when the up half `continue`d ----
   const bool down_hit = (n <= c.down_msgs) && !up_cool;   // main.go:65 (+ :54)
-  const bool down_go = down_hit && (s.ld <= id);      // main.go:66 false -> :71
-  const bool down_cool = down_hit && (s.ld > id);     // main.go:66 true  -> :67-68
+  const bool down_go = down_hit && (s.sd <= i);       // main.go:66 false -> :71
+  const bool down_cool = down_hit && (s.sd > i);      // main.go:66 true  -> :67-68
   const bool down_applied = down_go && (s.r > c.min32);   // scale.go:89 (sees the post-up replicas)
   unsigned evd = down_cool ? KSA_EV_DOWN_COOL : 0u;
   evd = down_go ? KSA_EV_DOWN_NOOP : evd;             // scale.go:90-91
   evd = down_applied ? KSA_EV_DOWN_APPLIED : evd;
   const int r_down = max((int)((unsigned)s.r - (unsigned)c.down32), c.min32);  // scale.go:94-97
   s.r = down_applied ? r_down : s.r;
-  s.ld = down_go ? i : s.ld;                          // main.go:76
+  s.sd = down_go ? i + c.cd : s.sd;                   // main.go:76
   return ev | evd;
 }
 
 // The same function with the predication written out in PTX (identical results; the kernels pick
-// whichever the variant table says, tools/sweep_variants.py measures both).
-__device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long long n, int i, int iu,
-                                                 int id, ksa_trace_regs& s) {
+// whichever the variant table says, tools/sweep_variants.py measures all spellings).
+__device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long long n, int i,
+                                                 ksa_trace_regs& s) {
   unsigned ev;
+  const int icu = i + c.cu, icd = i + c.cd;  // warp-uniform in the replay kernels
   asm("{\n\t"
       ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dcool, dapp;\n\t"
       ".reg .s32 t, u;\n\t"
       "setp.ge.s64 uh, %4, %5;\n\t"              // main.go:51
-      "setp.le.and.s32 ugo, %2, %12, uh;\n\t"    // main.go:52
-      "setp.gt.and.s32 ucool, %2, %12, uh;\n\t"
+      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"    // main.go:52
+      "setp.gt.and.s32 ucool, %2, %11, uh;\n\t"
       "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"   // scale.go:62
-      "@ugo mov.s32 %2, %11;\n\t"                // main.go:62
+      "@ugo mov.s32 %2, %12;\n\t"                // main.go:62
       "selp.u32 %0, 16, 0, ucool;\n\t"
       "@ugo mov.u32 %0, 4;\n\t"
       "@uapp mov.u32 %0, 1;\n\t"
@@ -125,10 +125,10 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
       "min.s32 t, t, %7;\n\t"                    // scale.go:67-69
       "selp.s32 %1, t, %1, uapp;\n\t"
       "setp.le.and.s64 dh, %4, %6, !ucool;\n\t"  // main.go:65 (+ :54)
-      "setp.le.and.s32 dgo, %3, %13, dh;\n\t"    // main.go:66
-      "setp.gt.and.s32 dcool, %3, %13, dh;\n\t"
+      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"    // main.go:66
+      "setp.gt.and.s32 dcool, %3, %11, dh;\n\t"
       "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"   // scale.go:89
-      "@dgo mov.s32 %3, %11;\n\t"                // main.go:76
+      "@dgo mov.s32 %3, %13;\n\t"                // main.go:76
       "@dcool add.u32 %0, %0, 32;\n\t"
       "@dgo add.u32 %0, %0, 8;\n\t"
       "@dapp add.u32 %0, %0, -6;\n\t"
@@ -136,9 +136,9 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
       "max.s32 u, u, %8;\n\t"                    // scale.go:95-97
       "selp.s32 %1, u, %1, dapp;\n\t"
       "}"
-      : "=r"(ev), "+r"(s.r), "+r"(s.lu), "+r"(s.ld)
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
       : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
-        "r"(c.down32), "r"(i), "r"(iu), "r"(id));
+        "r"(c.down32), "r"(i), "r"(icu), "r"(icd));
   return ev;
 }
 
@@ -146,18 +146,19 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
 // integer multiply-add by `one` (a kernel argument that is always 1 and that ptxas cannot fold).
 // On sm_100a IMAD issues on the FMA pipe while ISETP/SEL/VIADDMNMX issue on the half-rate ALU pipe,
 // which is the pipe this state machine saturates first (profiles/r01_ncu_full_v14_T2000.txt: ALU
-// 56 % active, FMA 12 %). This moves 9 of the 22 ALU operations per decision to the idle pipe.
-__device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long long n, int i, int iu,
-                                                 int id, int one, ksa_trace_regs& s) {
+// 56 % active, FMA 12 %). This moves 9 of the 22 ALU operations per decision to the idle pipe, and
+// the stamp `s = i * one + cool` needs no precomputed i + cool (the sweep has one cool per policy).
+__device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long long n, int i, int one,
+                                                 ksa_trace_regs& s) {
   unsigned ev;
   asm("{\n\t"
       ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dcool, dapp;\n\t"
       ".reg .s32 t, u;\n\t"
       "setp.ge.s64 uh, %4, %5;\n\t"                 // main.go:51
-      "setp.le.and.s32 ugo, %2, %12, uh;\n\t"       // main.go:52
-      "setp.gt.and.s32 ucool, %2, %12, uh;\n\t"
+      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"       // main.go:52
+      "setp.gt.and.s32 ucool, %2, %11, uh;\n\t"
       "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
-      "@ugo mad.lo.s32 %2, %11, %14, 0;\n\t"        // main.go:62   lu = i
+      "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"      // main.go:62   su = i + cu
       "selp.u32 %0, 16, 0, ucool;\n\t"
       "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"         // UP_NOOP unless ...
       "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"       // ... UP_APPLIED
@@ -165,10 +166,10 @@ __device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long 
       "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
       "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
       "setp.le.and.s64 dh, %4, %6, !ucool;\n\t"     // main.go:65 (+ :54)
-      "setp.le.and.s32 dgo, %3, %13, dh;\n\t"       // main.go:66
-      "setp.gt.and.s32 dcool, %3, %13, dh;\n\t"
+      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"       // main.go:66
+      "setp.gt.and.s32 dcool, %3, %11, dh;\n\t"
       "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
-      "@dgo mad.lo.s32 %3, %11, %14, 0;\n\t"        // main.go:76   ld = i
+      "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"      // main.go:76   sd = i + cd
       "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
       "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
       "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
@@ -176,11 +177,36 @@ __device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long 
       "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
       "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
       "}"
-      : "=r"(ev), "+r"(s.r), "+r"(s.lu), "+r"(s.ld)
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
       : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
-        "r"(c.down32), "r"(i), "r"(iu), "r"(id), "r"(one));
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one));
   return ev;
 }
+
+// d = a * b + c as a true IMAD (FMA pipe): ptxas cannot fold it when b is not a compile-time
+// constant, which is what the `one` kernel argument is for.
+__device__ __forceinline__ unsigned ksa_mad_u32(unsigned a, unsigned b, unsigned c) {
+  unsigned d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c) {
+  long long d;
+  asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+  return d;
+}
+
+// Per-trace accumulators of the summary kernels (registers). The six event counters are kept as
+// 8-bit fields of two registers (pk4: bits 0..3 of the event byte, one field per byte; pk2: bits 4
+// and 5 at bit 8 and bit 16) and must be added into 32-bit counters before a field can overflow,
+// i.e. at least every KSA_FLUSH_TICKS ticks (ksa_summary_flush).
+struct ksa_summary_acc {
+  int rmin, rmax;
+  unsigned pk4, pk2;
+  long long sum;
+  unsigned long long hash;
+};
+#define KSA_FLUSH_TICKS 255
 
 // Trajectory fingerprint step (ksa_summary.hash, include/ksa_replay.h):
 //   h <- h * M + ((uint64)event << 32 | (uint32)replicas)
@@ -188,4 +214,36 @@ __device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long 
 #define KSA_HASH_MUL 0x9E3779B97F4A7C15ull
 __device__ __forceinline__ unsigned long long ksa_hash_step(unsigned long long h, int r, unsigned ev) {
   return h * KSA_HASH_MUL + (((unsigned long long)ev << 32) | (unsigned long long)(unsigned)r);
+}
+
+// One tick of summary accumulation. FMA = true spells the adds as IMADs by `one` (FMA pipe).
+template <bool FMA>
+__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned ev, int one) {
+  m.rmin = min(m.rmin, r);
+  m.rmax = max(m.rmax, r);
+  // spread event bits 0..3 into four byte fields, bits 4..5 into two: one IMAD + one LOP3 each.
+  // ev < 64, so the shifted copies (shifts 0/7/14/21 and 4/11) never overlap: no carries.
+  const unsigned f4 = (ev * 0x00204081u) & 0x01010101u;
+  const unsigned f2 = (ev * 0x00000810u) & 0x00010100u;
+  if constexpr (FMA) {
+    m.pk4 = ksa_mad_u32(f4, (unsigned)one, m.pk4);
+    m.pk2 = ksa_mad_u32(f2, (unsigned)one, m.pk2);
+    m.sum = ksa_mad_wide_s32(r, one, m.sum);
+  } else {
+    m.pk4 += f4;
+    m.pk2 += f2;
+    m.sum = (long long)((unsigned long long)m.sum + (unsigned long long)(long long)r);
+  }
+  m.hash = ksa_hash_step(m.hash, r, ev);
+}
+
+// Add the packed fields into the 32-bit counters of a ksa_summary record and clear them.
+__device__ __forceinline__ void ksa_summary_flush(ksa_summary_acc& m, ksa_summary* q) {
+  q->up_applied += m.pk4 & 0xffu;
+  q->down_applied += (m.pk4 >> 8) & 0xffu;
+  q->up_noop += (m.pk4 >> 16) & 0xffu;
+  q->down_noop += m.pk4 >> 24;
+  q->up_cool += (m.pk2 >> 8) & 0xffu;
+  q->down_cool += (m.pk2 >> 16) & 0xffu;
+  m.pk4 = m.pk2 = 0u;
 }

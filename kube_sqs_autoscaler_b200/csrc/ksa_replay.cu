@@ -141,29 +141,8 @@ __device__ __forceinline__ void store_events(unsigned char* p, const unsigned (&
   }
 }
 
-// Per-trace accumulators of summary mode (registers). The six event counters are kept as 8-bit
-// fields of two registers (pk4: bits 0..3 of the event byte, one field per byte; pk2: bits 4 and 5
-// at bit 8 and bit 16) and are added into the 32-bit counters of the ksa_summary record in global
-// memory before a field can overflow (every <= 255 ticks).
-struct SummaryRegs {
-  int rmin, rmax;
-  unsigned pk4, pk2;
-  long long sum;
-  unsigned long long hash;
-};
-constexpr int kFlushTicks = 255;
-
-// d = a * b + c on the FMA pipe (ptxas keeps a true IMAD when b is not a compile-time constant).
-__device__ __forceinline__ unsigned mad_u32(unsigned a, unsigned b, unsigned c) {
-  unsigned d;
-  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-  return d;
-}
-__device__ __forceinline__ long long mad_wide_s32(int a, int b, long long c) {
-  long long d;
-  asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
-  return d;
-}
+typedef ksa_summary_acc SummaryRegs;
+constexpr int kFlushTicks = KSA_FLUSH_TICKS;
 
 template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
@@ -178,8 +157,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     s[v].r = a.st_r[n0 + v];
-    s[v].lu = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
-    s[v].ld = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
+    s[v].su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
+    s[v].sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
   }
   SummaryRegs sm[MODE == MODE_SUMMARY ? V : 1];
   if constexpr (MODE == MODE_SUMMARY) {
@@ -196,16 +175,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   auto flush_counters = [&]() {
     if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
-      for (int v = 0; v < V; ++v) {
-        ksa_summary* q = a.summary + n0 + v;
-        q->up_applied += sm[v].pk4 & 0xffu;
-        q->down_applied += (sm[v].pk4 >> 8) & 0xffu;
-        q->up_noop += (sm[v].pk4 >> 16) & 0xffu;
-        q->down_noop += sm[v].pk4 >> 24;
-        q->up_cool += (sm[v].pk2 >> 8) & 0xffu;
-        q->down_cool += (sm[v].pk2 >> 16) & 0xffu;
-        sm[v].pk4 = sm[v].pk2 = 0u;
-      }
+      for (int v = 0; v < V; ++v) ksa_summary_flush(sm[v], a.summary + n0 + v);
     }
   };
 
@@ -240,17 +210,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
         load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
     }
     const int i = tt + 1;  // local tick, 1-based
-    const int iu = i - c.cu, id = i - c.cd;
     int rr[V];
     unsigned ev[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       if constexpr (STEP == 2)
-        ev[v] = ksa_step_fma(c, n[v], i, iu, id, one, s[v]);
+        ev[v] = ksa_step_fma(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
-        ev[v] = ksa_step_ptx(c, n[v], i, iu, id, s[v]);
+        ev[v] = ksa_step_ptx(c, n[v], i, s[v]);
       else
-        ev[v] = ksa_step(c, n[v], i, iu, id, s[v]);
+        ev[v] = ksa_step(c, n[v], i, s[v]);
       rr[v] = s[v].r;
     }
     if constexpr (MODE != MODE_SUMMARY) {
@@ -258,23 +227,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       if (want_e) store_events<V, STEP == 2>(ep + (long long)tt * a.ld, ev);
     } else {
 #pragma unroll
-      for (int v = 0; v < V; ++v) {
-        sm[v].rmin = min(sm[v].rmin, rr[v]);
-        sm[v].rmax = max(sm[v].rmax, rr[v]);
-        // spread event bits 0..3 into four byte fields / bits 4,5 into two: one IMAD + one LOP3 each
-        const unsigned f4 = (ev[v] * 0x00204081u) & 0x01010101u;
-        const unsigned f2 = (ev[v] * 0x00000810u) & 0x00010100u;
-        if constexpr (STEP == 2) {
-          sm[v].pk4 = mad_u32(f4, (unsigned)one, sm[v].pk4);
-          sm[v].pk2 = mad_u32(f2, (unsigned)one, sm[v].pk2);
-          sm[v].sum = mad_wide_s32(rr[v], one, sm[v].sum);
-        } else {
-          sm[v].pk4 += f4;
-          sm[v].pk2 += f2;
-          sm[v].sum = (long long)((unsigned long long)sm[v].sum + (unsigned long long)(long long)rr[v]);
-        }
-        sm[v].hash = ksa_hash_step(sm[v].hash, rr[v], ev[v]);
-      }
+      for (int v = 0; v < V; ++v) ksa_summary_tick<STEP == 2>(sm[v], rr[v], ev[v], one);
     }
   };
 
@@ -307,8 +260,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     a.st_r[n0 + v] = s[v].r;
-    a.st_ju[n0 + v] = ksa_global_stamp(s[v].lu, a.tick0, a.st_ju[n0 + v]);
-    a.st_jd[n0 + v] = ksa_global_stamp(s[v].ld, a.tick0, a.st_jd[n0 + v]);
+    a.st_ju[n0 + v] = ksa_global_stamp(s[v].su, c.cu, a.tick0, a.st_ju[n0 + v]);
+    a.st_jd[n0 + v] = ksa_global_stamp(s[v].sd, c.cd, a.tick0, a.st_jd[n0 + v]);
   }
   if constexpr (MODE == MODE_SUMMARY) {
     flush_counters();

@@ -4,9 +4,12 @@
 // Thread = one trace x a register tile of R policies: each depth value is loaded once and fed to
 // R independent state machines (ksa_policy.cuh), so the depth block is re-read P/R times in total
 // and stays resident in the 126 MB L2. Unlike the single-policy replay this kernel is bound by
-// integer issue, not HBM: bytes per decision are ~0.01.
+// integer issue, not HBM: compulsory bytes per decision are ~0.01. The state
+// machine therefore uses ksa_step_fma (conditional moves as IMADs on the FMA pipe) and the packed
+// event counters of ksa_summary_tick, which halve the work of the half-rate ALU pipe.
 #include "ksa_internal.h"
 
+#include <cstdlib>
 #include <vector>
 
 namespace {
@@ -17,41 +20,47 @@ struct SweepArgs {
   long long ld;
   long long N;
   int P, T, A;
+  int one;  // always 1 (see ksa_step_fma)
   const int* replicas0;
   ksa_summary* summary;  // [P][N]
 };
 
-template <int R, int D, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
+template <int R, int D, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
   const int p0 = blockIdx.y * R;
-  const int T = a.T, A = a.A;
+  const int T = a.T, A = a.A, one = a.one;
 
-  // The R policy records of this block: block-uniform loads (served from L1/constant path).
+  // The R policy records of this block (block-uniform addresses; served from L1 / L2).
   ksa_policy_k pk[R];
 #pragma unroll
   for (int q = 0; q < R; ++q) pk[q] = a.policies[min(p0 + q, a.P - 1)];
 
   ksa_trace_regs s[R];
-  int rmin[R], rmax[R];
-  unsigned cnt[R][6];
-  long long sum[R];
-  unsigned long long hash[R];
+  ksa_summary_acc m[R];
   const int r0 = a.replicas0[n];
 #pragma unroll
   for (int q = 0; q < R; ++q) {
     const ksa_step_consts c(pk[q]);
     s[q].r = r0;
-    s[q].lu = ksa_local_stamp(pk[q].cu, c.cu, 0, 0);  // fresh process: both stamps at tick 0,
-    s[q].ld = ksa_local_stamp(pk[q].cd, c.cd, 0, 0);  // main.go:37-38
-    rmin[q] = INT_MAX;
-    rmax[q] = INT_MIN;
-#pragma unroll
-    for (int b = 0; b < 6; ++b) cnt[q][b] = 0u;
-    sum[q] = 0;
-    hash[q] = 0ull;
+    s[q].su = ksa_local_stamp(pk[q].cu, c.cu, 0, 0);  // fresh process: both stamps at tick 0,
+    s[q].sd = ksa_local_stamp(pk[q].cd, c.cd, 0, 0);  // main.go:37-38
+    m[q].rmin = INT_MAX;
+    m[q].rmax = INT_MIN;
+    m[q].pk4 = m[q].pk2 = 0u;
+    m[q].sum = 0;
+    m[q].hash = 0ull;
+    if (p0 + q < a.P) {  // counters live in the output record; start them at zero
+      ksa_summary* z = a.summary + (long long)(p0 + q) * a.N + n;
+      z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
+    }
   }
+  auto flush = [&]() {
+#pragma unroll
+    for (int q = 0; q < R; ++q)
+      if (p0 + q < a.P) ksa_summary_flush(m[q], a.summary + (long long)(p0 + q) * a.N + n);
+  };
 
   const long long row = (long long)A * a.ld;
   const long long* dp = a.depth + n;
@@ -64,6 +73,7 @@ __global__ void __launch_bounds__(BLOCK) ksa_sweep_kernel(const __grid_constant_
 #pragma unroll
   for (int j = 0; j < D; ++j) buf[j] = j < T ? load_sum(j) : 0;
 
+  int pending = 0;
 #pragma unroll 1
   for (int t = 0; t < T; t += D) {
 #pragma unroll
@@ -76,40 +86,51 @@ __global__ void __launch_bounds__(BLOCK) ksa_sweep_kernel(const __grid_constant_
 #pragma unroll
         for (int q = 0; q < R; ++q) {
           const ksa_step_consts c(pk[q]);
-          const unsigned ev = ksa_step(c, msgs, i, i - c.cu, i - c.cd, s[q]);
-          const int r = s[q].r;
-          rmin[q] = min(rmin[q], r);
-          rmax[q] = max(rmax[q], r);
-#pragma unroll
-          for (int b = 0; b < 6; ++b) cnt[q][b] += (ev >> b) & 1u;
-          sum[q] = (long long)((unsigned long long)sum[q] + (unsigned long long)(long long)r);
-          hash[q] = ksa_hash_step(hash[q], r, ev);
+          const unsigned ev = ksa_step_fma(c, msgs, i, one, s[q]);
+          ksa_summary_tick<true>(m[q], s[q].r, ev, one);
         }
       }
     }
+    pending += D;
+    if (pending > KSA_FLUSH_TICKS - D) {
+      flush();
+      pending = 0;
+    }
   }
+  flush();
 
 #pragma unroll
   for (int q = 0; q < R; ++q) {
     if (p0 + q < a.P) {
-      ksa_summary z;
-      z.final_replicas = s[q].r;
-      z.min_replicas = rmin[q];
-      z.max_replicas = rmax[q];
-      z.up_applied = cnt[q][0];
-      z.down_applied = cnt[q][1];
-      z.up_noop = cnt[q][2];
-      z.down_noop = cnt[q][3];
-      z.up_cool = cnt[q][4];
-      z.down_cool = cnt[q][5];
-      z.reserved = 0u;
-      z.ticks = T;
-      z.sum_replicas = sum[q];
-      z.hash = hash[q];
-      a.summary[(long long)(p0 + q) * a.N + n] = z;
+      ksa_summary* z = a.summary + (long long)(p0 + q) * a.N + n;
+      z->final_replicas = s[q].r;
+      z->min_replicas = m[q].rmin;
+      z->max_replicas = m[q].rmax;
+      z->reserved = 0u;
+      z->ticks = T;
+      z->sum_replicas = m[q].sum;
+      z->hash = m[q].hash;
     }
   }
 }
+
+typedef void (*sweep_fn)(const SweepArgs);
+struct SweepVariant {
+  int R, block;
+  sweep_fn fn;
+};
+// Tuning points; KSA_SWEEP_VARIANT=<index> (environment) overrides the default for measurements.
+const SweepVariant kSweepVariants[] = {
+    {4, 128, ksa_sweep_kernel<4, 4, 128, 3>},
+    {2, 128, ksa_sweep_kernel<2, 4, 128, 6>},
+    {4, 128, ksa_sweep_kernel<4, 2, 128, 4>},
+    {2, 256, ksa_sweep_kernel<2, 4, 256, 3>},
+    {1, 128, ksa_sweep_kernel<1, 8, 128, 8>},
+    {8, 128, ksa_sweep_kernel<8, 2, 128, 2>},
+    {4, 64, ksa_sweep_kernel<4, 4, 64, 6>},
+    {3, 128, ksa_sweep_kernel<3, 4, 128, 4>},
+};
+constexpr int kDefaultSweep = 2;  // R=4, D=2: profiles/r01_config4_sweep_tune.txt
 
 }  // namespace
 
@@ -141,12 +162,18 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   a.P = P;
   a.T = (int)T;
   a.A = A;
+  a.one = 1;
   a.replicas0 = replicas0_dev;
   a.summary = summary_dev;
-  constexpr int R = 4, D = 4, BLOCK = 128;
-  dim3 grid((unsigned)((N + BLOCK - 1) / BLOCK), (unsigned)((P + R - 1) / R));
+  int vi = kDefaultSweep;
+  if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
+    const int want = std::atoi(e);
+    if (want >= 0 && want < (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]))) vi = want;
+  }
+  const SweepVariant& v = kSweepVariants[vi];
+  dim3 grid((unsigned)((N + v.block - 1) / v.block), (unsigned)((P + v.R - 1) / v.R));
   if (grid.y > 65535) return ksa_fail(KSA_ELIMIT, "P too large for one launch");
-  ksa_sweep_kernel<R, D, BLOCK><<<grid, BLOCK, 0, st>>>(a);
+  v.fn<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel");
   return KSA_OK;
 }

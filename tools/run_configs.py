@@ -113,15 +113,25 @@ def run_config4(args):
     depth = eng.gen_traces(gen, 0, T, 1, 0, N, N, walk=walk)
     r0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5).replicas
     summ = torch.empty((P, N, 64), dtype=torch.uint8, device=eng.dev)
-    ms = []
-    for rep in range(args.reps + 2):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        eng.replay_sweep(parr, depth, T, 1, N, N, r0, summary=summ)
-        b.record()
-        torch.cuda.synchronize()
-        if rep >= 2:
-            ms.append(a.elapsed_time(b))
+    def time_sweep(reps):
+        out = []
+        for rep in range(reps + 2):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            eng.replay_sweep(parr, depth, T, 1, N, N, r0, summary=summ)
+            b.record()
+            torch.cuda.synchronize()
+            if rep >= 2:
+                out.append(a.elapsed_time(b))
+        return out
+
+    if args.sweep_tune:  # every tuning point of ksa_sweep.cu (KSA_SWEEP_VARIANT), then the default
+        for vi in range(8):
+            os.environ["KSA_SWEEP_VARIANT"] = str(vi)
+            t = min(time_sweep(1))
+            print(f"# sweep variant {vi}: {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
+        os.environ.pop("KSA_SWEEP_VARIANT", None)
+    ms = time_sweep(args.reps)
     # parity sample: 3 policies x all traces against the single-policy summary kernel
     ok = True
     for i in (0, P // 2 + 3, P - 1):
@@ -221,6 +231,7 @@ def main():
     ap.add_argument("--sweep-ticks", type=int, default=4096)
     ap.add_argument("--total-traces", type=int, default=1 << 26)
     ap.add_argument("--chunks-per-rank", type=int, default=0)
+    ap.add_argument("--sweep-tune", action="store_true")
     args = ap.parse_args()
     {3: run_config3, 4: run_config4, 5: run_config5}[args.config](args)
 
