@@ -212,6 +212,37 @@ int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* policies_dev,
                      const int32_t* replicas0_dev, ksa_summary* summary_dev, void* stream);
 
 /*
+ * The same sweep for callers that cannot allocate. (No counterpart in the reference: it has no
+ * sweep, and no device memory to manage.)
+ *
+ * Who needs it: a host that embeds this library next to a framework which has already claimed the
+ * GPU's memory for its own pool, so that a further cudaMalloc may simply fail; a Go host calling
+ * through cgo with no CUDA binding of its own, for which "allocate 48*P bytes on the device and
+ * keep them alive until the stream has drained" is one more lifetime to get wrong; and a caller
+ * that re-runs sweeps from a latency-sensitive loop, where cudaMalloc and cudaFree are
+ * unwelcome because they can stall the whole device while they run.
+ *
+ * What differs from ksa_replay_sweep: there is no policies_dev argument. The kernel-side policy
+ * table lives in a fixed array inside the library's device image, KSA_SWEEP_STATIC_MAX_POLICIES
+ * records of 48 bytes (192 KB), present on every GPU that loads the library until the process
+ * exits. The call makes no cudaMalloc / cudaFree and no host heap allocation. Inputs, outputs and
+ * results are exactly those of ksa_replay_sweep.
+ *
+ *  - P > KSA_SWEEP_STATIC_MAX_POLICIES returns KSA_ELIMIT; split the grid into several calls.
+ *  - The first call on each device looks up the array's device address (once, with that device
+ *    current). Make that first call before starting any stream capture on the device.
+ *  - All calls on one device share the one array. It keeps the previous call's records; every call
+ *    rewrites records [0, P) before its kernel reads them and nothing beyond P-1 is read, so stale
+ *    contents are harmless. But two calls whose work overlaps on the same GPU (different streams,
+ *    or different host threads) race on the table: run them on one stream, or wait for the first
+ *    to finish. Calls on different GPUs do not interfere.
+ */
+#define KSA_SWEEP_STATIC_MAX_POLICIES 4096
+int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P, const int64_t* depth_dev,
+                            int64_t T, int32_t A, int64_t N, int64_t ld,
+                            const int32_t* replicas0_dev, ksa_summary* summary_dev, void* stream);
+
+/*
  * Fingerprint an existing full trajectory: hash_dev[n] = the ksa_summary.hash the summary replay
  * would produce for trace n over the same T ticks (h0 = hash_dev[n] on entry when chain != 0, else
  * 0). Used to compare 100+ GB trajectories without moving them to the host.

@@ -79,6 +79,7 @@ SUMMARY_DTYPE = np.dtype(
 )
 assert SUMMARY_DTYPE.itemsize == 64 == C.sizeof(KsaSummary)
 POLICY_K_BYTES = 48  # sizeof(ksa_policy_k): the kernel-side policy record (csrc/ksa_policy.cuh)
+SWEEP_STATIC_MAX_POLICIES = 4096  # KSA_SWEEP_STATIC_MAX_POLICIES
 
 
 class KsaGenParams(C.Structure):
@@ -127,6 +128,8 @@ SIGNATURES = {
     "ksa_summary_clear": (C.c_int, [_vp, _i64, _vp]),
     "ksa_replay_sweep": (C.c_int, [_P(KsaPolicy), _i32, _vp, _vp, _i64, _i32, _i64, _i64, _vp,
                                    _vp, _vp]),
+    "ksa_replay_sweep_static": (C.c_int, [_P(KsaPolicy), _i32, _vp, _i64, _i32, _i64, _i64, _vp,
+                                          _vp, _vp]),
     "ksa_traj_hash": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp]),
     "ksa_gen_traces": (C.c_int, [_P(KsaGenParams), _i64, _i64, _i32, _i64, _i64, _i64, _vp, _vp,
                                  _vp]),

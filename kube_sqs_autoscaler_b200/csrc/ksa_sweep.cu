@@ -10,6 +10,7 @@
 #include "ksa_internal.h"
 
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 namespace {
@@ -175,5 +176,86 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   if (grid.y > 65535) return ksa_fail(KSA_ELIMIT, "P too large for one launch");
   v.fn<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel");
+  return KSA_OK;
+}
+
+// ---- ksa_replay_sweep_static: the sweep for callers that must not allocate -----------------------
+//
+// Same kernel, same results as ksa_replay_sweep; the only difference is where the kernel-side
+// policy table (the sweep's scratch memory) lives. Here it is a fixed array inside the library's
+// device image, KSA_SWEEP_STATIC_MAX_POLICIES records long, so the call needs no buffer from the
+// caller and performs no device or host allocation of its own. It is meant for hosts that have no
+// safe way to get 48*P bytes of device memory at call time: the GPU's memory already belongs to
+// another framework's pool, the host is Go over cgo and owns no CUDA allocator, or the sweep runs
+// in a loop that must not be stalled by cudaMalloc / cudaFree (include/ksa_replay.h has the
+// contract: size limit, first-call set-up, shared table).
+
+namespace {
+
+// 4096 x 48 B = 192 KB of device memory on every GPU that loads the library, held until exit.
+static __device__ __align__(256) unsigned char g_static_policy_table[KSA_SWEEP_STATIC_MAX_POLICIES * sizeof(ksa_policy_k)];
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mutex;                          // guards the two arrays below
+void* g_static_table_addr[kMaxStaticDevices] = {};  // device address of the table, per device
+ksa_policy_k g_static_host_table[KSA_SWEEP_STATIC_MAX_POLICIES];  // conversion buffer (host, .bss)
+
+}  // namespace
+
+extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
+                                       const int64_t* depth_dev, int64_t T, int32_t A, int64_t N,
+                                       int64_t ld, const int32_t* replicas0_dev,
+                                       ksa_summary* summary_dev, void* stream) {
+  if (!policies || !depth_dev || !replicas0_dev || !summary_dev)
+    return ksa_fail(KSA_EINVAL, "NULL pointer");
+  if (P < 1) return ksa_fail(KSA_EINVAL, "P=%d < 1", P);
+  if (P > KSA_SWEEP_STATIC_MAX_POLICIES)
+    return ksa_fail(KSA_ELIMIT,
+                    "P=%d exceeds the built-in policy table of ksa_replay_sweep_static (%d policies); "
+                    "split the grid or use ksa_replay_sweep with a caller-provided table",
+                    P, KSA_SWEEP_STATIC_MAX_POLICIES);
+  if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]", (long long)T);
+  if (N < 1 || N > 0x7fffffffll || ld < N) return ksa_fail(KSA_EINVAL, "bad N=%lld / ld=%lld", (long long)N, (long long)ld);
+
+  int device = -1;
+  KSA_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= kMaxStaticDevices)
+    return ksa_fail(KSA_ELIMIT, "device ordinal %d outside [0, %d)", device, kMaxStaticDevices);
+
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  // Set-up, once per device, with that device current: in host code the array's name is only a
+  // handle for the runtime, the address the kernel must be given comes from the runtime.
+  void* table = g_static_table_addr[device];
+  if (!table) {
+    KSA_CUDA(cudaGetSymbolAddress(&table, g_static_policy_table));
+    g_static_table_addr[device] = table;
+  }
+  for (int q = 0; q < P; ++q) {
+    int rc = ksa_policy_to_k(&policies[q], A, &g_static_host_table[q]);
+    if (rc != KSA_OK) return rc;
+    if (policies[q].attr_mask != policies[0].attr_mask)
+      return ksa_fail(KSA_EINVAL, "policy %d: attr_mask differs from policy 0", q);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  // Pageable source: the call returns once the bytes are staged, so the shared host buffer is free
+  // again when the mutex is released. Records [0, P) are rewritten by every call and the kernel
+  // never reads past P-1, so nothing left over from an earlier call needs clearing.
+  KSA_CUDA(cudaMemcpyAsync(table, g_static_host_table, sizeof(ksa_policy_k) * (size_t)P,
+                           cudaMemcpyHostToDevice, st));
+  SweepArgs a;
+  a.policies = (const ksa_policy_k*)table;
+  a.depth = (const long long*)depth_dev;
+  a.ld = ld;
+  a.N = N;
+  a.P = P;
+  a.T = (int)T;
+  a.A = A;
+  a.one = 1;
+  a.replicas0 = replicas0_dev;
+  a.summary = summary_dev;
+  const SweepVariant& v = kSweepVariants[kDefaultSweep];
+  dim3 grid((unsigned)((N + v.block - 1) / v.block), (unsigned)((P + v.R - 1) / v.R));
+  v.fn<<<grid, v.block, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("ksa_sweep_kernel (static table)");
   return KSA_OK;
 }

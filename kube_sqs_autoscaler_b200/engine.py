@@ -166,6 +166,21 @@ class ReplayEngine:
         # `table` must outlive the kernel: torch's caching allocator keeps the block on this stream.
         return summary
 
+    def replay_sweep_static(self, policies, depth: torch.Tensor, T: int, A: int, N: int, ld: int,
+                            replicas0: torch.Tensor, summary: torch.Tensor) -> torch.Tensor:
+        """ksa_replay_sweep_static: the sweep for hosts that cannot allocate device memory at call
+        time (another framework owns the GPU's memory, or a loop that cudaMalloc/cudaFree must not
+        stall). The policy table lives inside the library (at most SWEEP_STATIC_MAX_POLICIES
+        policies per call), `summary` ([P][N][64] uint8) is the caller's, and this wrapper creates
+        no tensor either. Calls on one GPU share that table: keep them on one stream."""
+        P = len(policies)
+        arr = policies if isinstance(policies, C.Array) else policy_array(policies)
+        assert replicas0.dtype == torch.int32 and replicas0.is_cuda and summary.is_cuda
+        _abi.check(self.lib.ksa_replay_sweep_static(arr, P, depth.data_ptr(), T, A, N, ld,
+                                                    replicas0.data_ptr(), summary.data_ptr(),
+                                                    _stream_ptr()))
+        return summary
+
     def traj_hash(self, replicas: torch.Tensor, events: torch.Tensor, T: int, N: int, ld: int,
                   hash_out: torch.Tensor | None = None, chain: bool = False) -> torch.Tensor:
         if hash_out is None:
