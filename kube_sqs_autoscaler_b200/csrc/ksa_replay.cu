@@ -36,7 +36,8 @@ struct ReplayArgs {
 // be NULL); MODE_SUMMARY writes nothing per tick.
 enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
 // STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (predication spelled out in PTX), 2 = ksa_step_fma
-// (conditional moves/adds as predicated IMADs on the FMA pipe). Same function, same results.
+// (conditional moves/adds as predicated IMADs on the FMA pipe), 3 = 2 with the policy constants
+// pinned in ordinary registers. Same function, same results.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
 
@@ -149,7 +150,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
-  const ksa_step_consts c(a.pk);
+  ksa_step_consts c(a.pk);
+  if constexpr (STEP == 3) {
+    // Keep the 32-bit policy constants in ordinary registers: left in uniform registers, every
+    // VIADDMNMX / IMAD that takes two of them pays an extra UR->R move inside the loop.
+    asm volatile("" : "+r"(c.max32), "+r"(c.min32), "+r"(c.up32), "+r"(c.down32), "+r"(c.cu), "+r"(c.cd));
+  }
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
 
@@ -214,7 +220,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     unsigned ev[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      if constexpr (STEP == 2)
+      if constexpr (STEP >= 2)
         ev[v] = ksa_step_fma(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
         ev[v] = ksa_step_ptx(c, n[v], i, s[v]);
@@ -224,10 +230,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     }
     if constexpr (MODE != MODE_SUMMARY) {
       if (want_r) store_replicas<V>(rp + (long long)tt * a.ld, rr);
-      if (want_e) store_events<V, STEP == 2>(ep + (long long)tt * a.ld, ev);
+      if (want_e) store_events<V, (STEP >= 2)>(ep + (long long)tt * a.ld, ev);
     } else {
 #pragma unroll
-      for (int v = 0; v < V; ++v) ksa_summary_tick<STEP == 2>(sm[v], rr[v], ev[v], one);
+      for (int v = 0; v < V; ++v) ksa_summary_tick<(STEP >= 2)>(sm[v], rr[v], ev[v], one);
     }
   };
 
@@ -341,6 +347,8 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(39, MODE_FULL, 8, 2, HINT_NA, 2, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
     KSA_VARIANT(40, MODE_FULL, 8, 2, HINT_NA, 1, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
     KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    KSA_VARIANT(42, MODE_FULL, 8, 2, HINT_NA, 3, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
+    KSA_VARIANT(43, MODE_FULL, 8, 2, HINT_NA, 3, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -357,6 +365,13 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(11, MODE_SUMMARY, 4, 4, HINT_NA, 1, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
     KSA_VARIANT(12, MODE_SUMMARY, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(13, MODE_SUMMARY, 4, 3, HINT_NA, 2, 128, 6, 4, 2, 128, 5, 4, 1, 128, 6),
+    KSA_VARIANT(14, MODE_SUMMARY, 2, 4, HINT_NA, 3, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(15, MODE_SUMMARY, 2, 4, HINT_NA, 3, 128, 7, 2, 3, 128, 7, 2, 2, 128, 7),
+    KSA_VARIANT(16, MODE_SUMMARY, 2, 3, HINT_NA, 3, 256, 4, 2, 2, 256, 4, 2, 2, 256, 4),
+    KSA_VARIANT(17, MODE_SUMMARY, 4, 2, HINT_NA, 3, 128, 6, 4, 2, 128, 5, 4, 1, 128, 6),
+    KSA_VARIANT(18, MODE_SUMMARY, 2, 2, HINT_NA, 3, 128, 8, 2, 2, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(19, MODE_SUMMARY, 1, 4, HINT_NA, 3, 128, 12, 1, 4, 128, 10, 1, 3, 128, 10),
+    KSA_VARIANT(20, MODE_SUMMARY, 2, 4, HINT_NA, 2, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL

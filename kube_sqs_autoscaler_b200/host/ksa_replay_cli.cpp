@@ -1,0 +1,249 @@
+// ksa-replay — command-line host over the C ABI (include/ksa_replay.h), C++ because the reference
+// is compiled code and this image has no Go toolchain. It keeps the reference's operator API: the
+// flags of main.go:83-97 with the same names, defaults and Go duration syntax, so a command line
+// written for kube-sqs-autoscaler parses unchanged (the flags that only configure the AWS and
+// Kubernetes clients are accepted and ignored). Instead of polling one queue forever it replays
+// the policy over --traces synthetic queue-depth traces x --ticks polls on one GPU and prints
+// what the autoscaler would have done.
+//
+// Links only libksareplay.so: all CUDA calls happen behind the ABI.
+#include <algorithm>
+#include <cctype>
+#include <chrono>
+#include <cinttypes>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "ksa_replay.h"
+
+namespace {
+
+[[noreturn]] void die(const std::string& msg) {
+  std::fprintf(stderr, "ksa-replay: %s\n", msg.c_str());
+  std::exit(2);
+}
+
+void check(int rc, const char* what) {
+  if (rc != KSA_OK) die(std::string(what) + ": " + ksa_last_error());
+}
+
+// time.ParseDuration (what flag.DurationVar uses, main.go:83-85): [+-] then (number unit)+,
+// units ns us µs ms s m h; "0" alone is allowed.
+bool parse_duration(const std::string& text, int64_t* out) {
+  size_t p = 0;
+  bool neg = false;
+  if (p < text.size() && (text[p] == '+' || text[p] == '-')) neg = text[p++] == '-';
+  if (text.substr(p) == "0") {
+    *out = 0;
+    return true;
+  }
+  if (p >= text.size()) return false;
+  long double total = 0;
+  while (p < text.size()) {
+    size_t q = p;
+    while (q < text.size() && (std::isdigit((unsigned char)text[q]) || text[q] == '.')) ++q;
+    if (q == p) return false;
+    const std::string num = text.substr(p, q - p);
+    if (num == "." || std::count(num.begin(), num.end(), '.') > 1) return false;
+    size_t u = q;
+    while (u < text.size() && !std::isdigit((unsigned char)text[u]) && text[u] != '.') ++u;
+    const std::string unit = text.substr(q, u - q);
+    long double scale;
+    if (unit == "ns") scale = 1;
+    else if (unit == "us" || unit == "\xC2\xB5s" || unit == "\xCE\xBCs") scale = 1e3L;
+    else if (unit == "ms") scale = 1e6L;
+    else if (unit == "s") scale = 1e9L;
+    else if (unit == "m") scale = 60e9L;
+    else if (unit == "h") scale = 3600e9L;
+    else return false;
+    total += std::strtold(num.c_str(), nullptr) * scale;
+    p = u;
+  }
+  if (total > 9223372036854775807.0L) return false;
+  *out = (int64_t)total;
+  if (neg) *out = -*out;
+  return true;
+}
+
+uint32_t attr_mask(const std::string& names) {
+  static const char* kNames[3] = {"ApproximateNumberOfMessages", "ApproximateNumberOfMessagesDelayed",
+                                  "ApproximateNumberOfMessagesNotVisible"};  // sqs/sqs.go:28-32
+  uint32_t mask = 0;
+  size_t p = 0;
+  while (p <= names.size()) {
+    size_t q = names.find(',', p);
+    if (q == std::string::npos) q = names.size();
+    std::string n = names.substr(p, q - p);
+    n.erase(0, n.find_first_not_of(" \t"));  // strings.TrimSpace, main.go:108
+    n.erase(n.find_last_not_of(" \t") + 1);
+    bool found = false;
+    for (int a = 0; a < 3; ++a)
+      if (n == kNames[a]) {
+        mask |= 1u << a;
+        found = true;
+      }
+    if (!found) die("unknown attribute name '" + n + "'");
+    p = q + 1;
+  }
+  return mask;
+}
+
+struct Options {
+  ksa_policy policy;
+  int64_t traces = 1 << 20, ticks = 1000;
+  uint64_t seed = 0x5EED0001;
+  std::string mode = "summary";
+  int device = 0;
+};
+
+Options parse(int argc, char** argv) {
+  Options o;
+  check(ksa_policy_default(&o.policy), "ksa_policy_default");
+  std::map<std::string, std::string> kv;
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i];
+    if (a.rfind("--", 0) == 0) a = a.substr(2);
+    else if (a.rfind("-", 0) == 0) a = a.substr(1);  // Go's flag package accepts -flag too
+    else die("unexpected argument '" + a + "'");
+    std::string v;
+    const size_t eq = a.find('=');
+    if (eq != std::string::npos) {
+      v = a.substr(eq + 1);
+      a = a.substr(0, eq);
+    } else if (a == "help" || a == "h") {
+      v = "";
+    } else {
+      if (i + 1 >= argc) die("flag needs an argument: -" + a);
+      v = argv[++i];
+    }
+    kv[a] = v;
+  }
+  for (const auto& [k, v] : kv) {
+    auto as_int = [&](const char* what) {
+      char* end = nullptr;
+      const long long x = std::strtoll(v.c_str(), &end, 0);
+      if (v.empty() || *end) die(std::string("invalid value \"") + v + "\" for flag -" + what);
+      return (int64_t)x;
+    };
+    auto as_dur = [&](const char* what) {
+      int64_t d;
+      if (!parse_duration(v, &d)) die(std::string("invalid value \"") + v + "\" for flag -" + what + ": time: invalid duration");
+      return d;
+    };
+    if (k == "poll-period") o.policy.poll_period_ns = as_dur("poll-period");
+    else if (k == "scale-down-cool-down") o.policy.scale_down_cool_down_ns = as_dur("scale-down-cool-down");
+    else if (k == "scale-up-cool-down") o.policy.scale_up_cool_down_ns = as_dur("scale-up-cool-down");
+    else if (k == "scale-up-messages") o.policy.scale_up_messages = as_int("scale-up-messages");
+    else if (k == "scale-down-messages") o.policy.scale_down_messages = as_int("scale-down-messages");
+    else if (k == "scale-up-pods") o.policy.scale_up_pods = as_int("scale-up-pods");
+    else if (k == "scale-down-pods") o.policy.scale_down_pods = as_int("scale-down-pods");
+    else if (k == "max-pods") o.policy.max_pods = as_int("max-pods");
+    else if (k == "min-pods") o.policy.min_pods = as_int("min-pods");
+    else if (k == "attribute-names") o.policy.attr_mask = attr_mask(v);
+    else if (k == "aws-region" || k == "sqs-queue-url" || k == "kubernetes-deployment" || k == "kubernetes-namespace") {
+      // network clients of the live daemon (main.go:92,95-97): nothing to do in a replay
+    } else if (k == "traces") o.traces = as_int("traces");
+    else if (k == "ticks") o.ticks = as_int("ticks");
+    else if (k == "seed") o.seed = (uint64_t)as_int("seed");
+    else if (k == "mode") o.mode = v;
+    else if (k == "device") o.device = (int)as_int("device");
+    else if (k == "help" || k == "h") {
+      std::puts("usage: ksa-replay [reference flags: --poll-period --scale-up-cool-down --scale-down-cool-down\n"
+                "  --scale-up-messages --scale-down-messages --scale-up-pods --scale-down-pods --max-pods --min-pods\n"
+                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D]");
+      std::exit(0);
+    } else {
+      die("flag provided but not defined: -" + k);
+    }
+  }
+  if (o.mode != "full" && o.mode != "summary") die("--mode must be full or summary");
+  return o;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options o = parse(argc, argv);
+  const int A = __builtin_popcount(o.policy.attr_mask);
+  const int64_t N = o.traces, T = o.ticks, ld = (N + 15) / 16 * 16;
+  check(ksa_set_device(o.device), "ksa_set_device");
+  int64_t cu = 0, cd = 0;
+  check(ksa_policy_cool_ticks(&o.policy, &cu, &cd), "ksa_policy_cool_ticks");
+
+  void *depth = nullptr, *r = nullptr, *ju = nullptr, *jd = nullptr, *summ = nullptr, *rep = nullptr, *evs = nullptr;
+  const bool full = o.mode == "full";
+  const int64_t chunk = std::min<int64_t>(T, std::max<int64_t>(1, (int64_t)((full ? 48.0e9 : 64.0e9) / ((8.0 * A + (full ? 5 : 0)) * ld))));
+  check(ksa_dev_alloc(&depth, (size_t)chunk * A * ld * 8), "depth");
+  check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
+  check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&jd, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&summ, (size_t)ld * sizeof(ksa_summary)), "summary");
+  if (full) {
+    check(ksa_dev_alloc(&rep, (size_t)chunk * ld * 4), "replicas");
+    check(ksa_dev_alloc(&evs, (size_t)chunk * ld), "events");
+  }
+  ksa_state st = {(int32_t*)r, (int64_t*)ju, (int64_t*)jd};
+  ksa_state st_sum = st;
+  void *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr;
+  if (full) {  // the summary pass needs its own copy of the carry state
+    check(ksa_dev_alloc(&r2, (size_t)ld * 4), "state");
+    check(ksa_dev_alloc(&ju2, (size_t)ld * 8), "state");
+    check(ksa_dev_alloc(&jd2, (size_t)ld * 8), "state");
+    st_sum = {(int32_t*)r2, (int64_t*)ju2, (int64_t*)jd2};
+    check(ksa_state_init(o.seed, 0, N, (int32_t)o.policy.min_pods, (int32_t)o.policy.max_pods >= (int32_t)o.policy.min_pods ? (int32_t)o.policy.max_pods : (int32_t)o.policy.min_pods, &st_sum, nullptr), "ksa_state_init");
+  }
+  const int32_t lo = (int32_t)o.policy.min_pods;
+  const int32_t hi = (int32_t)o.policy.max_pods >= lo ? (int32_t)o.policy.max_pods : lo;
+  check(ksa_state_init(o.seed, 0, N, lo, hi, &st, nullptr), "ksa_state_init");
+  check(ksa_summary_clear((ksa_summary*)summ, N, nullptr), "ksa_summary_clear");
+
+  ksa_gen_params g;
+  std::memset(&g, 0, sizeof(g));
+  g.seed = o.seed;
+  g.family = KSA_GEN_BANDS;
+  g.low_max = o.policy.scale_down_messages < 0 ? 0 : o.policy.scale_down_messages;
+  g.high_min = o.policy.scale_up_messages > g.low_max ? o.policy.scale_up_messages : g.low_max + 1;
+  g.high_max = 4 * g.high_min;
+  double replay_s = 0;
+  for (int64_t t0 = 0; t0 < T; t0 += chunk) {
+    const int64_t tc = std::min(chunk, T - t0);
+    check(ksa_gen_traces(&g, t0, tc, A, 0, N, ld, (int64_t*)depth, nullptr, nullptr), "ksa_gen_traces");
+    check(ksa_stream_sync(nullptr), "sync");
+    const auto a = std::chrono::steady_clock::now();
+    if (full) check(ksa_replay_full(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
+    else check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+    check(ksa_stream_sync(nullptr), "sync");
+    replay_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+    if (full) check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+  }
+  std::vector<ksa_summary> host((size_t)N);
+  check(ksa_memcpy_d2h(host.data(), summ, (size_t)N * sizeof(ksa_summary), nullptr), "d2h");
+  check(ksa_stream_sync(nullptr), "sync");
+  uint64_t tot[6] = {0, 0, 0, 0, 0, 0}, digest = 0;
+  long double replica_ticks = 0;
+  for (const ksa_summary& s : host) {
+    tot[0] += s.up_applied; tot[1] += s.down_applied; tot[2] += s.up_noop;
+    tot[3] += s.down_noop; tot[4] += s.up_cool; tot[5] += s.down_cool;
+    replica_ticks += (long double)s.sum_replicas;
+    digest ^= s.hash;
+  }
+  std::printf("policy: up>=%" PRId64 " down<=%" PRId64 " steps +%" PRId64 "/-%" PRId64 " pods [%" PRId64 ",%" PRId64
+              "] cool-down ticks up %" PRId64 " down %" PRId64 " attributes %d\n",
+              o.policy.scale_up_messages, o.policy.scale_down_messages, o.policy.scale_up_pods, o.policy.scale_down_pods,
+              o.policy.min_pods, o.policy.max_pods, cu, cd, A);
+  std::printf("replayed %" PRId64 " traces x %" PRId64 " ticks (%s mode) in %.3f ms of kernel wall time: %.3e decisions/s\n",
+              N, T, o.mode.c_str(), replay_s * 1e3, (double)N * (double)T / replay_s);
+  std::printf("scale up successful %" PRIu64 " | scale down successful %" PRIu64 " | at max %" PRIu64 " | at min %" PRIu64
+              " | up cool-down skips %" PRIu64 " | down cool-down skips %" PRIu64 "\n",
+              tot[0], tot[1], tot[2], tot[3], tot[4], tot[5]);
+  std::printf("mean replicas %.4Lf | xor of trajectory fingerprints %016" PRIx64 "\n",
+              replica_ticks / ((long double)N * (long double)T), digest);
+  for (void* p : {depth, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
+    if (p) ksa_dev_free(p);
+  return 0;
+}

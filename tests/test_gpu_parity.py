@@ -19,8 +19,8 @@ pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2] + list(range(1, 42))   # -2 = scalar kernel
-SUMMARY_VARIANTS = [-2] + list(range(1, 14))
+FULL_VARIANTS = [-2] + list(range(1, 44))   # -2 = scalar kernel
+SUMMARY_VARIANTS = [-2] + list(range(1, 21))
 
 
 def torch_mod():
@@ -511,3 +511,39 @@ def test_config2_full_size_properties(engine):
     assert torch.equal(engine.traj_hash(replicas, events, T, N, N), h_first)
     del depth, replicas, events
     torch.cuda.empty_cache()
+
+
+# ---- the C++ host CLI ------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("mode", ["summary", "full"])
+def test_cli_totals_match_the_python_host(engine, mode):
+    """kube_sqs_autoscaler_b200/ksa-replay with reference flags: its event totals equal the totals of
+    the same replay driven from Python (same generator, seed, policy), which equals the oracle."""
+    import os
+    import re
+    import subprocess
+
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    N, T = 5000, 300
+    r = subprocess.run([cli, "--poll-period=5s", "--scale-up-cool-down=12s", "--scale-down-cool-down=45s",
+                        "--scale-up-messages=250", "--scale-down-messages=25", "--scale-up-pods=3",
+                        "--scale-down-pods=2", "--max-pods=50", "--min-pods=2", "--aws-region=us-west-2",
+                        "--sqs-queue-url=https://example", "--kubernetes-deployment=deploy",
+                        "--traces", str(N), "--ticks", str(T), "--mode", mode, "--seed", "77"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    m = re.search(r"scale up successful (\d+) \| scale down successful (\d+) \| at max (\d+) \| at min (\d+) \| "
+                  r"up cool-down skips (\d+) \| down cool-down skips (\d+)", r.stdout)
+    assert m, r.stdout
+    got = [int(x) for x in m.groups()]
+    digest = int(re.search(r"fingerprints ([0-9a-f]{16})", r.stdout).group(1), 16)
+    pol = ksa.Policy(scale_up_messages=250, scale_down_messages=25, scale_up_pods=3, scale_down_pods=2,
+                     max_pods=50, min_pods=2, scale_up_cool_down=12 * S, scale_down_cool_down=45 * S)
+    gen = ksa.GenParams(seed=77, low_max=25, high_min=250, high_max=1000)
+    ld = (N + 15) // 16 * 16
+    d_host = oracle_lib.gen_traces(gen.to_c(), 0, T, 3, 0, N, ld)
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, 3, N, ld, 0, *oracle_lib.fresh_state(77, 0, N, 2, 50),
+                            want_full=False, want_summary=True)
+    want = [int(ref.summary[k].sum()) for k in ("up_applied", "down_applied", "up_noop", "down_noop", "up_cool", "down_cool")]
+    assert got == want
+    assert digest == int(np.bitwise_xor.reduce(ref.summary["hash"]))

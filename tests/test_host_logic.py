@@ -107,3 +107,25 @@ def test_two_rank_gloo_shards_and_gathers(tmp_path):
                             *oracle_lib.fresh_state(GEN.seed, 0, N_TOTAL, 1, 5),
                             want_full=False, want_summary=True)
     assert got.tobytes() == ref.summary.tobytes()
+
+
+def test_cli_keeps_the_reference_flag_surface(built):
+    """ksa-replay (C++ host): reference flags parse, Go-style errors for bad values, and without
+    a GPU it fails loudly instead of computing anything on the CPU."""
+    import torch
+
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    assert os.path.exists(cli)
+    r = subprocess.run([cli, "--poll-period=5x"], capture_output=True, text=True)
+    assert r.returncode == 2 and 'invalid value "5x" for flag -poll-period' in r.stderr
+    r = subprocess.run([cli, "--scale-up-messages", "many"], capture_output=True, text=True)
+    assert r.returncode == 2 and "scale-up-messages" in r.stderr
+    r = subprocess.run([cli, "--no-such-flag=1"], capture_output=True, text=True)
+    assert r.returncode == 2 and "flag provided but not defined: -no-such-flag" in r.stderr
+    r = subprocess.run([cli, "--attribute-names=ApproximateAgeOfOldestMessage"], capture_output=True, text=True)
+    assert r.returncode == 2 and "unknown attribute name" in r.stderr
+    if not torch.cuda.is_available():
+        r = subprocess.run([cli, "-poll-period", "10s", "--kubernetes-deployment=x", "--sqs-queue-url=y",
+                            "--aws-region=us-west-2", "--traces", "64", "--ticks", "8"],
+                           capture_output=True, text=True)
+        assert r.returncode == 2 and "ksa_set_device" in r.stderr  # flags parsed, then no GPU
