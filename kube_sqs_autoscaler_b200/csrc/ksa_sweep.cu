@@ -26,12 +26,12 @@ struct SweepArgs {
   ksa_summary* summary;  // [P][N]
 };
 
-template <int R, int D, int BLOCK, int MINB>
+template <int A, int R, int D, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
   const int p0 = blockIdx.y * R;
-  const int T = a.T, A = a.A, one = a.one;
+  const int T = a.T, one = a.one;
 
   // The R policy records of this block (block-uniform addresses; served from L1 / L2).
   ksa_policy_k pk[R];
@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
   const long long* dp = a.depth + n;
   auto load_sum = [&](int t) {
     unsigned long long acc = (unsigned long long)__ldg(dp + (long long)t * row);
+#pragma unroll
     for (int p = 1; p < A; ++p) acc += (unsigned long long)__ldg(dp + (long long)t * row + p * a.ld);
     return (long long)acc;  // sqs.go:56-64, wrapping
   };
@@ -115,23 +116,148 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
   }
 }
 
+// Second layout: lane = policy. A block replays V adjacent traces under BLOCK consecutive policies;
+// the depth value of a (trace, tick) is block-uniform (one broadcast load), the policy constants
+// and the whole state of a (policy, trace) pair are per-lane registers. One or two state machines
+// per thread, so ptxas never has more than a few predicates live (the register-tile kernel above
+// runs four machines per thread and, in SASS, spends 13 LOP3 + 3 P2R per decision spilling
+// predicates into a general register; profiles/r01_ncu_sweep.txt: 48.5 instructions per decision).
+// Latency is hidden by the ~40 resident warps per SM instead of by ILP inside a thread.
+template <int A, int V, int D, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __grid_constant__ SweepArgs a) {
+  const int pblocks = (a.P + BLOCK - 1) / BLOCK;
+  const int pb = (int)(blockIdx.x % (unsigned)pblocks);        // policy block: fastest, so that
+  const long long n0 = (long long)(blockIdx.x / (unsigned)pblocks) * V;  // co-running blocks share traces
+  const int p = pb * BLOCK + threadIdx.x;
+  const bool live = p < a.P;
+  const int T = a.T, one = a.one;
+  const ksa_policy_k pk = a.policies[live ? p : a.P - 1];
+  const ksa_step_consts c(pk);
+
+  ksa_trace_regs s[V];
+  ksa_summary_acc m[V];
+  bool have[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    have[v] = live && (n0 + v < a.N);
+    s[v].r = a.replicas0[min(n0 + v, a.N - 1)];
+    s[v].su = ksa_local_stamp(pk.cu, c.cu, 0, 0);  // fresh process: both stamps at tick 0,
+    s[v].sd = ksa_local_stamp(pk.cd, c.cd, 0, 0);  // main.go:37-38
+    m[v].rmin = INT_MAX;
+    m[v].rmax = INT_MIN;
+    m[v].pk4 = m[v].pk2 = 0u;
+    m[v].sum = 0;
+    m[v].hash = 0ull;
+    if (have[v]) {  // counters live in the output record; start them at zero
+      ksa_summary* z = a.summary + (long long)p * a.N + n0 + v;
+      z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
+    }
+  }
+  auto flush = [&]() {
+#pragma unroll
+    for (int v = 0; v < V; ++v)
+      if (have[v]) ksa_summary_flush(m[v], a.summary + (long long)p * a.N + n0 + v);
+  };
+
+  const long long row = (long long)A * a.ld;
+  const long long* dp = a.depth + n0;  // block-uniform
+  auto load_sum = [&](int t, int v) {
+    const long long* q = dp + (long long)t * row + (n0 + v < a.N ? v : 0);
+    unsigned long long acc = (unsigned long long)__ldg(q);
+#pragma unroll
+    for (int k = 1; k < A; ++k) acc += (unsigned long long)__ldg(q + k * a.ld);
+    return (long long)acc;  // sqs.go:56-64, wrapping
+  };
+  long long buf[D][V];
+#pragma unroll
+  for (int j = 0; j < D; ++j)
+#pragma unroll
+    for (int v = 0; v < V; ++v) buf[j][v] = j < T ? load_sum(j, v) : 0;
+
+  int pending = 0;
+#pragma unroll 1
+  for (int t = 0; t < T; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const int tt = t + j;
+      if (tt < T) {
+        long long msgs[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) msgs[v] = buf[j][v];
+        if (tt + D < T) {
+#pragma unroll
+          for (int v = 0; v < V; ++v) buf[j][v] = load_sum(tt + D, v);
+        }
+        const int i = tt + 1;
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          const unsigned ev = ksa_step_fma(c, msgs[v], i, one, s[v]);
+          ksa_summary_tick<true>(m[v], s[v].r, ev, one);
+        }
+      }
+    }
+    pending += D;
+    if (pending > KSA_FLUSH_TICKS - D) {
+      flush();
+      pending = 0;
+    }
+  }
+  flush();
+
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    if (have[v]) {
+      ksa_summary* z = a.summary + (long long)p * a.N + n0 + v;
+      z->final_replicas = s[v].r;
+      z->min_replicas = m[v].rmin;
+      z->max_replicas = m[v].rmax;
+      z->reserved = 0u;
+      z->ticks = T;
+      z->sum_replicas = m[v].sum;
+      z->hash = m[v].hash;
+    }
+  }
+}
+
 typedef void (*sweep_fn)(const SweepArgs);
 struct SweepVariant {
-  int R, block;
-  sweep_fn fn;
+  int R;      // register-tile kernel: policies per thread; lane kernel: 0
+  int V;      // lane kernel: traces per thread
+  int block;
+  sweep_fn fn[3];  // indexed by A-1
 };
+#define KSA_SWEEP(R, D, BLOCK, MINB)                                                   \
+  {R, 0, BLOCK, {ksa_sweep_kernel<1, R, D, BLOCK, MINB>, ksa_sweep_kernel<2, R, D, BLOCK, MINB>, \
+                 ksa_sweep_kernel<3, R, D, BLOCK, MINB>}}
+#define KSA_SWEEP_LANE(V, D, BLOCK, MINB)                                                        \
+  {0, V, BLOCK, {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>, \
+                 ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}}
 // Tuning points; KSA_SWEEP_VARIANT=<index> (environment) overrides the default for measurements.
 const SweepVariant kSweepVariants[] = {
-    {4, 128, ksa_sweep_kernel<4, 4, 128, 3>},
-    {2, 128, ksa_sweep_kernel<2, 4, 128, 6>},
-    {4, 128, ksa_sweep_kernel<4, 2, 128, 4>},
-    {2, 256, ksa_sweep_kernel<2, 4, 256, 3>},
-    {1, 128, ksa_sweep_kernel<1, 8, 128, 8>},
-    {8, 128, ksa_sweep_kernel<8, 2, 128, 2>},
-    {4, 64, ksa_sweep_kernel<4, 4, 64, 6>},
-    {3, 128, ksa_sweep_kernel<3, 4, 128, 4>},
+    KSA_SWEEP(4, 4, 128, 3), KSA_SWEEP(2, 4, 128, 6), KSA_SWEEP(4, 2, 128, 4), KSA_SWEEP(2, 4, 256, 3),
+    KSA_SWEEP(1, 8, 128, 8), KSA_SWEEP(8, 2, 128, 2), KSA_SWEEP(4, 4, 64, 6),  KSA_SWEEP(3, 4, 128, 4),
+    KSA_SWEEP_LANE(1, 4, 128, 10), KSA_SWEEP_LANE(2, 4, 128, 8), KSA_SWEEP_LANE(1, 8, 128, 8),
+    KSA_SWEEP_LANE(2, 2, 128, 8),  KSA_SWEEP_LANE(1, 4, 256, 4), KSA_SWEEP_LANE(2, 4, 256, 4),
+    KSA_SWEEP_LANE(1, 2, 128, 12), KSA_SWEEP_LANE(1, 4, 64, 16),
 };
-constexpr int kDefaultSweep = 2;  // R=4, D=2: profiles/r01_config4_sweep_tune.txt
+constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]));
+constexpr int kDefaultSweep = 0;  // R=4, D=4, 128x3: profiles/r01_config4_sweep_tune.txt (115.6 ms on
+                                  // configs[3]; the lane kernels reach 123 ms at V=2, 158 ms at V=1:
+                                  // their per-tick loop overhead is not shared between machines)
+
+// Grid of a sweep launch, or false if it does not fit one launch.
+bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
+  if (v.R > 0) {
+    const long long gy = (P + v.R - 1) / v.R;
+    if (gy > 65535) return false;
+    *grid = dim3((unsigned)((N + v.block - 1) / v.block), (unsigned)gy);
+  } else {
+    const long long blocks = (long long)((P + v.block - 1) / v.block) * ((N + v.V - 1) / v.V);
+    if (blocks > 0x7fffffffll) return false;
+    *grid = dim3((unsigned)blocks);
+  }
+  return true;
+}
 
 }  // namespace
 
@@ -169,12 +295,13 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   int vi = kDefaultSweep;
   if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
     const int want = std::atoi(e);
-    if (want >= 0 && want < (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]))) vi = want;
+    if (want >= 0 && want < kNumSweepVariants) vi = want;
   }
   const SweepVariant& v = kSweepVariants[vi];
-  dim3 grid((unsigned)((N + v.block - 1) / v.block), (unsigned)((P + v.R - 1) / v.R));
-  if (grid.y > 65535) return ksa_fail(KSA_ELIMIT, "P too large for one launch");
-  v.fn<<<grid, v.block, 0, st>>>(a);
+  dim3 grid;
+  if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+  if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
+  v.fn[A - 1]<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel");
   return KSA_OK;
 }
@@ -254,8 +381,9 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
   a.replicas0 = replicas0_dev;
   a.summary = summary_dev;
   const SweepVariant& v = kSweepVariants[kDefaultSweep];
-  dim3 grid((unsigned)((N + v.block - 1) / v.block), (unsigned)((P + v.R - 1) / v.R));
-  v.fn<<<grid, v.block, 0, st>>>(a);
+  dim3 grid;
+  if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+  v.fn[A - 1]<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel (static table)");
   return KSA_OK;
 }
