@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--traces", type=int, default=N_TRACES, help="traces per GPU (default 2^20)")
     ap.add_argument("--ticks", type=int, default=N_TICKS)
     ap.add_argument("--e2e-ticks", type=int, default=1000, help="ticks per e2e step (host buffers)")
-    ap.add_argument("--e2e-chunk", type=int, default=50, help="ticks per pipeline stage")
+    ap.add_argument("--e2e-chunk", type=int, default=25, help="ticks per pipeline stage")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU-baseline duration")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

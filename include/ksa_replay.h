@@ -52,6 +52,16 @@ extern "C" {
 #define KSA_EV_DOWN_NOOP 0x08    /* "Less than min pods running"        scale/scale.go:90  */
 #define KSA_EV_UP_COOL 0x10      /* "Waiting for cool down, skipping scale up"   main.go:53 */
 #define KSA_EV_DOWN_COOL 0x20    /* "Waiting for cool down, skipping scale down" main.go:67 */
+/* Only the *_faults entry points produce these three (the plain ones replay a world without errors): */
+#define KSA_EV_UP_FAILED 0x40    /* "Failed scaling up"    main.go:58 (tick ends, no stamp)           */
+#define KSA_EV_DOWN_FAILED 0x80  /* "Failed scaling down"  main.go:72 (no stamp)                      */
+#define KSA_EV_POLL_FAILED 0xC0  /* "Failed to get SQS messages" main.go:45: the event byte is exactly */
+                                 /* this value (both failure bits: neither call could be attempted)   */
+
+/* ---- failure mask (input of the *_faults entry points): what went wrong in a (tick, trace) ----- */
+#define KSA_FAIL_POLL 0x01 /* sqs.NumMessages returned an error  main.go:43-47, sqs/sqs.go:51-54,59-61 */
+#define KSA_FAIL_UP 0x02   /* p.ScaleUp returned an error         main.go:57-60, scale/scale.go:55-58,72-75 */
+#define KSA_FAIL_DOWN 0x04 /* p.ScaleDown returned an error       main.go:71-74, scale/scale.go:82-85,100-103 */
 
 /* ---- attribute axis: order of sqs.DefaultAttributeNames, sqs/sqs.go:28-32 ---------------- */
 #define KSA_ATTR_MESSAGES 0x1u             /* ApproximateNumberOfMessages           */
@@ -110,8 +120,9 @@ typedef struct ksa_summary {
   uint32_t down_noop;
   uint32_t up_cool;
   uint32_t down_cool;
-  uint32_t reserved;
-  int64_t ticks;        /* ticks replayed so far                            */
+  uint32_t poll_failed; /* the three failure counters stay 0 outside the *_faults entry points */
+  uint32_t up_failed;
+  uint32_t down_failed;
   int64_t sum_replicas; /* wrapping sum of the post-tick replica counts     */
   uint64_t hash;
 } ksa_summary;
@@ -195,8 +206,40 @@ int ksa_replay_summary(const ksa_policy* policy, const int64_t* depth_dev, int64
                        int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
                        ksa_summary* summary_dev, void* stream);
 
-/* Reset N summaries to the empty accumulation (ticks 0, hash 0, min/max sentinels). */
+/* Reset N summaries to the empty accumulation (counters 0, hash 0, min/max sentinels). */
 int ksa_summary_clear(ksa_summary* summary_dev, int64_t N, void* stream);
+
+/*
+ * The same two replays in a world where calls fail: fail_dev [T][ld] uint8 carries KSA_FAIL_* bits
+ * per (tick, trace) and reproduces the three error paths of Run, each of which `continue`s without
+ * touching the stamps or the replicas:
+ *   KSA_FAIL_POLL  NumMessages failed (main.go:43-47): the tick ends, event == KSA_EV_POLL_FAILED.
+ *   KSA_FAIL_UP    ScaleUp failed (main.go:57-60): only matters if the tick reaches the call
+ *                  (threshold met, cool-down over); no stamp, the tick ends (the down branch is
+ *                  skipped), event bit KSA_EV_UP_FAILED.
+ *   KSA_FAIL_DOWN  ScaleDown failed (main.go:71-74): likewise; an up-scale earlier in the same tick
+ *                  stands; event bit KSA_EV_DOWN_FAILED.
+ * A failing Scale call fails whether or not the replica count is at its limit (the reference's
+ * Get comes first, scale/scale.go:55,82). Algorithmic traffic: +1 byte per decision.
+ */
+int ksa_replay_full_faults(const ksa_policy* policy, const int64_t* depth_dev,
+                           const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
+                           int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
+                           uint8_t* events_dev, void* stream);
+int ksa_replay_summary_faults(const ksa_policy* policy, const int64_t* depth_dev,
+                              const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
+                              int64_t tick0, const ksa_state* state, ksa_summary* summary_dev,
+                              void* stream);
+
+/*
+ * Synthetic failure mask for ticks tick0+1..tick0+T of traces trace0..trace0+N-1: each KSA_FAIL_*
+ * bit is set independently with probability 2^-poll_log2 / 2^-up_log2 / 2^-down_log2 (0 = never),
+ * from the same counter-based hash as ksa_gen_traces (values depend only on seed, global trace id
+ * and absolute tick).
+ */
+int ksa_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, uint32_t down_log2,
+                   int64_t tick0, int64_t T, int64_t trace0, int64_t N, int64_t ld,
+                   uint8_t* fail_dev, void* stream);
 
 /*
  * Policy sweep: replay the same N traces under P policies (the parameter grid of main.go:83-91),

@@ -121,6 +121,21 @@ KSA_HD int64_t ksa_gen_iid_value(const ksa_gen_params* g, uint64_t h) {
                                           : ksa_gen_bands_value(g, h);
 }
 
+/* Failure mask byte of one (trace, tick): bit k set with probability 2^-log2[k] (0 = never). The key
+ * uses slot 0xF0, so the mask is independent of the depth of the same entry. */
+KSA_HD uint8_t ksa_gen_fault_byte(uint64_t fault_key, uint64_t tick, uint32_t poll_log2,
+                                  uint32_t up_log2, uint32_t down_log2) {
+  const uint64_t h0 = ksa_entry_word(fault_key, tick);
+  const uint64_t h1 = ksa_mix64(h0);
+  const uint64_t h2 = ksa_mix64(h1);
+  uint8_t f = 0;
+  if (poll_log2 != 0 && (h0 >> (64 - poll_log2)) == 0) f |= KSA_FAIL_POLL;
+  if (up_log2 != 0 && (h1 >> (64 - up_log2)) == 0) f |= KSA_FAIL_UP;
+  if (down_log2 != 0 && (h2 >> (64 - down_log2)) == 0) f |= KSA_FAIL_DOWN;
+  return f;
+}
+KSA_HD uint64_t ksa_fault_key(uint64_t seed, uint64_t trace) { return ksa_trace_key(seed, 0xF0u, trace); }
+
 /* Initial replica count of a fresh trace: lo + hash(seed, trace) mod (hi - lo + 1). */
 KSA_HD int32_t ksa_gen_replicas0(uint64_t seed, uint64_t trace, int32_t lo, int32_t hi) {
   uint64_t h = ksa_trace_key(seed, 0xA5u, trace);

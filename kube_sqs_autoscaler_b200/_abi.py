@@ -18,6 +18,8 @@ KSA_ABI_VERSION = 1
 KSA_OK, KSA_EINVAL, KSA_ECUDA, KSA_ENOMEM, KSA_ELIMIT = 0, -1, -2, -3, -4
 
 EV_UP_APPLIED, EV_DOWN_APPLIED, EV_UP_NOOP, EV_DOWN_NOOP, EV_UP_COOL, EV_DOWN_COOL = 1, 2, 4, 8, 16, 32
+EV_UP_FAILED, EV_DOWN_FAILED, EV_POLL_FAILED = 0x40, 0x80, 0xC0  # only from the *_faults entry points
+FAIL_POLL, FAIL_UP, FAIL_DOWN = 1, 2, 4
 EVENT_NAMES = {
     EV_UP_APPLIED: "up_applied", EV_DOWN_APPLIED: "down_applied", EV_UP_NOOP: "up_noop",
     EV_DOWN_NOOP: "down_noop", EV_UP_COOL: "up_cool", EV_DOWN_COOL: "down_cool",
@@ -62,8 +64,9 @@ class KsaSummary(C.Structure):
         ("down_noop", C.c_uint32),
         ("up_cool", C.c_uint32),
         ("down_cool", C.c_uint32),
-        ("reserved", C.c_uint32),
-        ("ticks", C.c_int64),
+        ("poll_failed", C.c_uint32),
+        ("up_failed", C.c_uint32),
+        ("down_failed", C.c_uint32),
         ("sum_replicas", C.c_int64),
         ("hash", C.c_uint64),
     ]
@@ -73,8 +76,8 @@ SUMMARY_DTYPE = np.dtype(
     [
         ("final_replicas", "<i4"), ("min_replicas", "<i4"), ("max_replicas", "<i4"),
         ("up_applied", "<u4"), ("down_applied", "<u4"), ("up_noop", "<u4"), ("down_noop", "<u4"),
-        ("up_cool", "<u4"), ("down_cool", "<u4"), ("reserved", "<u4"),
-        ("ticks", "<i8"), ("sum_replicas", "<i8"), ("hash", "<u8"),
+        ("up_cool", "<u4"), ("down_cool", "<u4"), ("poll_failed", "<u4"), ("up_failed", "<u4"),
+        ("down_failed", "<u4"), ("sum_replicas", "<i8"), ("hash", "<u8"),
     ]
 )
 assert SUMMARY_DTYPE.itemsize == 64 == C.sizeof(KsaSummary)
@@ -126,6 +129,12 @@ SIGNATURES = {
     "ksa_replay_summary": (C.c_int, [_P(KsaPolicy), _vp, _i64, _i32, _i64, _i64, _i64,
                                      _P(KsaState), _vp, _vp]),
     "ksa_summary_clear": (C.c_int, [_vp, _i64, _vp]),
+    "ksa_replay_full_faults": (C.c_int, [_P(KsaPolicy), _vp, _vp, _i64, _i32, _i64, _i64, _i64,
+                                         _P(KsaState), _vp, _vp, _vp]),
+    "ksa_replay_summary_faults": (C.c_int, [_P(KsaPolicy), _vp, _vp, _i64, _i32, _i64, _i64, _i64,
+                                            _P(KsaState), _vp, _vp]),
+    "ksa_gen_faults": (C.c_int, [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, _i64, _i64, _i64, _i64,
+                                 _i64, _vp, _vp]),
     "ksa_replay_sweep": (C.c_int, [_P(KsaPolicy), _i32, _vp, _vp, _i64, _i32, _i64, _i64, _vp,
                                    _vp, _vp]),
     "ksa_replay_sweep_static": (C.c_int, [_P(KsaPolicy), _i32, _vp, _i64, _i32, _i64, _i64, _vp,

@@ -90,11 +90,27 @@ __global__ void __launch_bounds__(kBlock) summary_clear_kernel(ksa_summary* s, l
   z.min_replicas = INT_MAX;
   z.max_replicas = INT_MIN;
   z.up_applied = z.down_applied = z.up_noop = z.down_noop = z.up_cool = z.down_cool = 0u;
-  z.reserved = 0u;
-  z.ticks = 0;
+  z.poll_failed = z.up_failed = z.down_failed = 0u;
   z.sum_replicas = 0;
   z.hash = 0ull;
   s[n] = z;
+}
+
+// Synthetic failure mask (include/ksa_tracegen.h): one thread per trace and tick-strip, byte stores
+// coalesced across traces.
+__global__ void __launch_bounds__(kBlock) gen_faults_kernel(unsigned long long seed, unsigned poll_log2,
+                                                            unsigned up_log2, unsigned down_log2,
+                                                            long long tick0, int T, long long trace0,
+                                                            long long N, long long ld, unsigned char* fail,
+                                                            int ticks_per_block) {
+  const long long n = (long long)blockIdx.x * kBlock + threadIdx.x;
+  if (n >= N) return;
+  const unsigned long long key = ksa_fault_key(seed, (unsigned long long)(trace0 + n));
+  const int t_begin = blockIdx.y * ticks_per_block;
+  const int t_end = min(T, t_begin + ticks_per_block);
+  for (int t = t_begin; t < t_end; ++t)
+    fail[(long long)t * ld + n] =
+        ksa_gen_fault_byte(key, (unsigned long long)(tick0 + 1 + t), poll_log2, up_log2, down_log2);
 }
 
 // Fingerprint of an existing trajectory: one thread per trace, coalesced 4-byte / 1-byte reads,
@@ -168,6 +184,24 @@ extern "C" int ksa_gen_traces(const ksa_gen_params* g, int64_t tick0, int64_t T,
         *g, tick0, (int)T, A, trace0, N, ld, (long long*)depth_dev, per);
     KSA_LAUNCH_CHECK("gen_iid_kernel");
   }
+  return KSA_OK;
+}
+
+extern "C" int ksa_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, uint32_t down_log2,
+                              int64_t tick0, int64_t T, int64_t trace0, int64_t N, int64_t ld,
+                              uint8_t* fail_dev, void* stream) {
+  if (!fail_dev) return ksa_fail(KSA_EINVAL, "NULL fail_dev");
+  if (poll_log2 > 63 || up_log2 > 63 || down_log2 > 63) return ksa_fail(KSA_EINVAL, "log2 rates must be <= 63");
+  if (T < 0 || T > KSA_MAX_CHUNK_TICKS || N < 0 || N > 0x7fffffffll || ld < N)
+    return ksa_fail(KSA_EINVAL, "bad T/N/ld");
+  if (N == 0 || T == 0) return KSA_OK;
+  int strips = (int)((T + 63) / 64);
+  if (strips > 65535) strips = 65535;
+  const int per = (int)((T + strips - 1) / strips);
+  strips = (int)((T + per - 1) / per);
+  gen_faults_kernel<<<dim3(blocks_for(N), (unsigned)strips), kBlock, 0, (cudaStream_t)stream>>>(
+      seed, poll_log2, up_log2, down_log2, tick0, (int)T, trace0, N, ld, fail_dev, per);
+  KSA_LAUNCH_CHECK("gen_faults_kernel");
   return KSA_OK;
 }
 

@@ -183,6 +183,46 @@ __device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long 
   return ev;
 }
 
+// The step in a world where calls fail (the *_faults entry points). `f` carries the KSA_FAIL_* bits
+// of this (trace, tick). The three error paths of Run all `continue` before any state changes:
+//   NumMessages failed  main.go:43-47   nothing else happens in the tick
+//   ScaleUp failed      main.go:57-60   no stamp, tick ends (down branch skipped)
+//   ScaleDown failed    main.go:71-74   no stamp; an up-scale earlier in the tick stands
+// A fail bit whose call is not reached (threshold not met, still cooling down) has no effect.
+__device__ __forceinline__ unsigned ksa_step_faults(const ksa_step_consts& c, long long n, unsigned f,
+                                                    int i, ksa_trace_regs& s) {
+  const bool poll_ok = (f & KSA_FAIL_POLL) == 0;          // main.go:44
+  // ---- scale-up half ----
+  const bool up_hit = poll_ok && n >= c.up_msgs;          // main.go:51
+  const bool up_reach = up_hit && (s.su <= i);            // main.go:52 false: ScaleUp is called
+  const bool up_cool = up_hit && (s.su > i);              // main.go:52 true -> :53-54
+  const bool up_failed = up_reach && (f & KSA_FAIL_UP);   // main.go:57-60 (continue)
+  const bool up_go = up_reach && !(f & KSA_FAIL_UP);      // ScaleUp returned nil
+  const bool up_applied = up_go && (s.r < c.max32);       // scale.go:62
+  unsigned ev = up_cool ? KSA_EV_UP_COOL : 0u;
+  ev = up_go ? KSA_EV_UP_NOOP : ev;
+  ev = up_applied ? KSA_EV_UP_APPLIED : ev;
+  ev = up_failed ? KSA_EV_UP_FAILED : ev;
+  const int r_up = min((int)((unsigned)s.r + (unsigned)c.up32), c.max32);  // scale.go:66-69
+  s.r = up_applied ? r_up : s.r;
+  s.su = up_go ? i + c.cu : s.su;                         // main.go:62
+  // ---- scale-down half: skipped when the up half `continue`d (cool-down or error) ----
+  const bool down_hit = poll_ok && (n <= c.down_msgs) && !up_cool && !up_failed;  // main.go:65
+  const bool down_reach = down_hit && (s.sd <= i);        // main.go:66 false: ScaleDown is called
+  const bool down_cool = down_hit && (s.sd > i);          // main.go:66 true -> :67-68
+  const bool down_failed = down_reach && (f & KSA_FAIL_DOWN);  // main.go:71-74
+  const bool down_go = down_reach && !(f & KSA_FAIL_DOWN);
+  const bool down_applied = down_go && (s.r > c.min32);   // scale.go:89
+  unsigned evd = down_cool ? KSA_EV_DOWN_COOL : 0u;
+  evd = down_go ? KSA_EV_DOWN_NOOP : evd;
+  evd = down_applied ? KSA_EV_DOWN_APPLIED : evd;
+  evd = down_failed ? KSA_EV_DOWN_FAILED : evd;
+  const int r_down = max((int)((unsigned)s.r - (unsigned)c.down32), c.min32);  // scale.go:94-97
+  s.r = down_applied ? r_down : s.r;
+  s.sd = down_go ? i + c.cd : s.sd;                       // main.go:76
+  return poll_ok ? (ev | evd) : (unsigned)KSA_EV_POLL_FAILED;  // main.go:45
+}
+
 // d = a * b + c as a true IMAD (FMA pipe): ptxas cannot fold it when b is not a compile-time
 // constant, which is what the `one` kernel argument is for.
 __device__ __forceinline__ unsigned ksa_mad_u32(unsigned a, unsigned b, unsigned c) {
@@ -203,6 +243,7 @@ __device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c)
 struct ksa_summary_acc {
   int rmin, rmax;
   unsigned pk4, pk2;
+  unsigned pkf;  // *_faults kernels only: UP_FAILED bit at field 0, DOWN_FAILED at 8, failed polls at 16
   long long sum;
   unsigned long long hash;
 };
@@ -217,14 +258,17 @@ __device__ __forceinline__ unsigned long long ksa_hash_step(unsigned long long h
 }
 
 // One tick of summary accumulation. FMA = true spells the adds as IMADs by `one` (FMA pipe).
+// `ev6` = the low six event bits (the *_faults kernels mask the two failure bits off; everywhere
+// else ev6 == ev).
 template <bool FMA>
-__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned ev, int one) {
+__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned ev, unsigned ev6,
+                                                 int one) {
   m.rmin = min(m.rmin, r);
   m.rmax = max(m.rmax, r);
   // spread event bits 0..3 into four byte fields, bits 4..5 into two: one IMAD + one LOP3 each.
-  // ev < 64, so the shifted copies (shifts 0/7/14/21 and 4/11) never overlap: no carries.
-  const unsigned f4 = (ev * 0x00204081u) & 0x01010101u;
-  const unsigned f2 = (ev * 0x00000810u) & 0x00010100u;
+  // ev6 < 64, so the shifted copies (shifts 0/7/14/21 and 4/11) never overlap: no carries.
+  const unsigned f4 = (ev6 * 0x00204081u) & 0x01010101u;
+  const unsigned f2 = (ev6 * 0x00000810u) & 0x00010100u;
   if constexpr (FMA) {
     m.pk4 = ksa_mad_u32(f4, (unsigned)one, m.pk4);
     m.pk2 = ksa_mad_u32(f2, (unsigned)one, m.pk2);
@@ -235,6 +279,19 @@ __device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsi
     m.sum = (long long)((unsigned long long)m.sum + (unsigned long long)(long long)r);
   }
   m.hash = ksa_hash_step(m.hash, r, ev);
+}
+
+// Failure counters of the *_faults kernels. `f` is the KSA_FAIL_* input byte: a poll fails exactly
+// when its bit is set, and a failed poll shows as both failure bits in the event byte.
+__device__ __forceinline__ void ksa_summary_tick_faults(ksa_summary_acc& m, unsigned ev, unsigned f) {
+  m.pkf += (((ev >> 6) * 0x81u) & 0x101u) + ((f & KSA_FAIL_POLL) << 16);
+}
+__device__ __forceinline__ void ksa_summary_flush_faults(ksa_summary_acc& m, ksa_summary* q) {
+  const unsigned polls = (m.pkf >> 16) & 0xffu;
+  q->poll_failed += polls;
+  q->up_failed += (m.pkf & 0xffu) - polls;
+  q->down_failed += ((m.pkf >> 8) & 0xffu) - polls;
+  m.pkf = 0u;
 }
 
 // Add the packed fields into the 32-bit counters of a ksa_summary record and clear them.

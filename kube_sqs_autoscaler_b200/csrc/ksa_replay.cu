@@ -18,6 +18,7 @@ namespace {
 struct ReplayArgs {
   ksa_policy_k pk;
   const long long* depth;
+  const unsigned char* fail;  // *_faults entry points: [T][ld] KSA_FAIL_* bits, else NULL
   long long ld;      // row pitch, elements
   long long tick0;
   long long n_begin; // first trace of this launch
@@ -37,7 +38,8 @@ struct ReplayArgs {
 enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
 // STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (predication spelled out in PTX), 2 = ksa_step_fma
 // (conditional moves/adds as predicated IMADs on the FMA pipe), 3 = 2 with the policy constants
-// pinned in ordinary registers. Same function, same results.
+// pinned in ordinary registers. Same function, same results. 4 = ksa_step_faults: the step of the
+// *_faults entry points, which also reads one failure-mask byte per decision.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
 
@@ -142,6 +144,26 @@ __device__ __forceinline__ void store_events(unsigned char* p, const unsigned (&
   }
 }
 
+// V failure-mask bytes of one tick, as packed words (same streaming hints as the depth loads).
+template <int V>
+__device__ __forceinline__ void load_fail(const unsigned char* p, unsigned (&w)[(V + 3) / 4]) {
+  if constexpr (V == 1) {
+    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(w[0]) : "l"(p));
+  } else if constexpr (V == 2) {
+    unsigned short h;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(h) : "l"(p));
+    w[0] = h;
+  } else if constexpr (V == 4) {
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w[0]) : "l"(p));
+  } else if constexpr (V == 8) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p));
+  } else {
+    static_assert(V == 16, "V must be 1, 2, 4, 8 or 16");
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p));
+  }
+}
+
 typedef ksa_summary_acc SummaryRegs;
 constexpr int kFlushTicks = KSA_FLUSH_TICKS;
 
@@ -158,6 +180,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   }
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
+  constexpr bool FAULTS = (STEP == 4);
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -173,7 +196,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       const ksa_summary* q = a.summary + n0 + v;
       sm[v].rmin = q->min_replicas;
       sm[v].rmax = q->max_replicas;
-      sm[v].pk4 = sm[v].pk2 = 0u;
+      sm[v].pk4 = sm[v].pk2 = sm[v].pkf = 0u;
       sm[v].sum = q->sum_replicas;
       sm[v].hash = q->hash;
     }
@@ -181,7 +204,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   auto flush_counters = [&]() {
     if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
-      for (int v = 0; v < V; ++v) ksa_summary_flush(sm[v], a.summary + n0 + v);
+      for (int v = 0; v < V; ++v) {
+        ksa_summary_flush(sm[v], a.summary + n0 + v);
+        if constexpr (FAULTS) ksa_summary_flush_faults(sm[v], a.summary + n0 + v);
+      }
     }
   };
 
@@ -200,6 +226,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
       for (int p = 0; p < A; ++p) load_depth<V, HINT>(dp + (long long)j * row + p * a.ld, buf[j][p]);
     }
+  // The failure mask rides the same ring (one byte per trace and tick).
+  const unsigned char* fp = FAULTS ? a.fail + n0 : nullptr;
+  unsigned fbuf[FAULTS ? D : 1][(V + 3) / 4];
+  if constexpr (FAULTS) {
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+      if (j < T) load_fail<V>(fp + (long long)j * a.ld, fbuf[j]);
+  }
 
   auto tick = [&](const int tt, const int j, const bool prefetch) {
     long long n[V];
@@ -210,17 +244,28 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       for (int p = 1; p < A; ++p) acc += (unsigned long long)buf[j][p][v];
       n[v] = (long long)acc;
     }
+    unsigned fw[(V + 3) / 4];
+    if constexpr (FAULTS) {
+#pragma unroll
+      for (int w = 0; w < (V + 3) / 4; ++w) fw[w] = fbuf[j][w];
+    }
     if (prefetch) {
 #pragma unroll
       for (int p = 0; p < A; ++p)
         load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
+      if constexpr (FAULTS) load_fail<V>(fp + (long long)(tt + D) * a.ld, fbuf[j]);
     }
     const int i = tt + 1;  // local tick, 1-based
     int rr[V];
     unsigned ev[V];
+    unsigned fv[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      if constexpr (STEP >= 2)
+      fv[v] = 0u;
+      if constexpr (FAULTS) {
+        fv[v] = (fw[v / 4] >> (8 * (v % 4))) & 0xffu;
+        ev[v] = ksa_step_faults(c, n[v], fv[v], i, s[v]);
+      } else if constexpr (STEP >= 2)
         ev[v] = ksa_step_fma(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
         ev[v] = ksa_step_ptx(c, n[v], i, s[v]);
@@ -230,10 +275,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     }
     if constexpr (MODE != MODE_SUMMARY) {
       if (want_r) store_replicas<V>(rp + (long long)tt * a.ld, rr);
-      if (want_e) store_events<V, (STEP >= 2)>(ep + (long long)tt * a.ld, ev);
+      if (want_e) store_events<V, (STEP == 2 || STEP == 3)>(ep + (long long)tt * a.ld, ev);
     } else {
 #pragma unroll
-      for (int v = 0; v < V; ++v) ksa_summary_tick<(STEP >= 2)>(sm[v], rr[v], ev[v], one);
+      for (int v = 0; v < V; ++v) {
+        ksa_summary_tick<(STEP == 2 || STEP == 3)>(sm[v], rr[v], ev[v], FAULTS ? (ev[v] & 0x3fu) : ev[v], one);
+        if constexpr (FAULTS) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
+      }
     }
   };
 
@@ -277,7 +325,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       q->final_replicas = s[v].r;
       q->min_replicas = sm[v].rmin;
       q->max_replicas = sm[v].rmax;
-      q->ticks += (long long)T;
       q->sum_replicas = sm[v].sum;
       q->hash = sm[v].hash;
     }
@@ -373,6 +420,15 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(19, MODE_SUMMARY, 1, 4, HINT_NA, 3, 128, 12, 1, 4, 128, 10, 1, 3, 128, 10),
     KSA_VARIANT(20, MODE_SUMMARY, 2, 4, HINT_NA, 2, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
 };
+// The *_faults entry points: one vector kernel + the scalar kernel per mode (STEP 4).
+const Variant kFullFaultsVariants[] = {
+    KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(1, MODE_FULL_OPT, 8, 2, HINT_NA, 4, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
+};
+const Variant kSummaryFaultsVariants[] = {
+    KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(1, MODE_SUMMARY, 2, 4, HINT_NA, 4, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+};
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
 constexpr int kDefaultSummary = 12;  // summary mode is ALU-bound: few traces per thread, high occupancy
@@ -394,10 +450,12 @@ int launch(const Variant& var, int A, ReplayArgs args, cudaStream_t stream) {
   return KSA_OK;
 }
 
-int replay_common(int mode, const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
-                  int64_t N, int64_t ld, int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
-                  uint8_t* events_dev, ksa_summary* summary_dev, void* stream) {
+int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t* depth_dev,
+                  const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0,
+                  const ksa_state* state, int32_t* replicas_dev, uint8_t* events_dev,
+                  ksa_summary* summary_dev, void* stream) {
   if (!policy || !depth_dev || !state) return ksa_fail(KSA_EINVAL, "NULL policy, depth or state");
+  if (faults && !fail_dev) return ksa_fail(KSA_EINVAL, "NULL fail_dev");
   if (!state->replicas_dev || !state->last_up_tick_dev || !state->last_down_tick_dev)
     return ksa_fail(KSA_EINVAL, "NULL pointer inside ksa_state");
   if (mode == MODE_SUMMARY && !summary_dev) return ksa_fail(KSA_EINVAL, "NULL summary_dev");
@@ -410,6 +468,7 @@ int replay_common(int mode, const ksa_policy* policy, const int64_t* depth_dev, 
   int rc = ksa_policy_to_k(policy, A, &args.pk);
   if (rc != KSA_OK) return rc;
   args.depth = (const long long*)depth_dev;
+  args.fail = faults ? fail_dev : nullptr;
   args.ld = ld;
   args.tick0 = tick0;
   args.T = (int)T;
@@ -426,11 +485,16 @@ int replay_common(int mode, const ksa_policy* policy, const int64_t* depth_dev, 
                            ? find_variant(kFullVariants, want < 0 ? kDefaultFull : want)
                            : find_variant(kSummaryVariants, want < 0 ? kDefaultSummary : want);
   // Variants compiled for "both outputs" cannot run with one of them missing.
-  if (mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
+  if (!faults && mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
   const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];
+  if (faults) {
+    var = mode == MODE_FULL ? &kFullFaultsVariants[1] : &kSummaryFaultsVariants[1];
+    if (want == 0) var = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
+    scalar = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
+  }
   if (!var) return ksa_fail(KSA_EINVAL, "unknown kernel variant %d", want);
   // Vector path needs every row start 32-byte aligned in all three arrays.
-  const bool aligned = (ld % 16 == 0) && ksa_aligned(depth_dev, 32) &&
+  const bool aligned = (ld % 16 == 0) && ksa_aligned(depth_dev, 32) && (!faults || ksa_aligned(fail_dev, 16)) &&
                        (!replicas_dev || ksa_aligned(replicas_dev, 32)) &&
                        (!events_dev || ksa_aligned(events_dev, 16));
   if (!aligned) var = scalar;
@@ -455,15 +519,31 @@ extern "C" int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_de
                                int32_t A, int64_t N, int64_t ld, int64_t tick0,
                                const ksa_state* state, int32_t* replicas_dev, uint8_t* events_dev,
                                void* stream) {
-  return replay_common(MODE_FULL, policy, depth_dev, T, A, N, ld, tick0, state, replicas_dev,
-                       events_dev, nullptr, stream);
+  return replay_common(MODE_FULL, false, policy, depth_dev, nullptr, T, A, N, ld, tick0, state,
+                       replicas_dev, events_dev, nullptr, stream);
 }
 
 extern "C" int ksa_replay_summary(const ksa_policy* policy, const int64_t* depth_dev, int64_t T,
                                   int32_t A, int64_t N, int64_t ld, int64_t tick0,
                                   const ksa_state* state, ksa_summary* summary_dev, void* stream) {
-  return replay_common(MODE_SUMMARY, policy, depth_dev, T, A, N, ld, tick0, state, nullptr, nullptr,
-                       summary_dev, stream);
+  return replay_common(MODE_SUMMARY, false, policy, depth_dev, nullptr, T, A, N, ld, tick0, state,
+                       nullptr, nullptr, summary_dev, stream);
+}
+
+extern "C" int ksa_replay_full_faults(const ksa_policy* policy, const int64_t* depth_dev,
+                                      const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N,
+                                      int64_t ld, int64_t tick0, const ksa_state* state,
+                                      int32_t* replicas_dev, uint8_t* events_dev, void* stream) {
+  return replay_common(MODE_FULL, true, policy, depth_dev, fail_dev, T, A, N, ld, tick0, state,
+                       replicas_dev, events_dev, nullptr, stream);
+}
+
+extern "C" int ksa_replay_summary_faults(const ksa_policy* policy, const int64_t* depth_dev,
+                                         const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N,
+                                         int64_t ld, int64_t tick0, const ksa_state* state,
+                                         ksa_summary* summary_dev, void* stream) {
+  return replay_common(MODE_SUMMARY, true, policy, depth_dev, fail_dev, T, A, N, ld, tick0, state,
+                       nullptr, nullptr, summary_dev, stream);
 }
 
 // Used by ksa_set_variant to validate ids.

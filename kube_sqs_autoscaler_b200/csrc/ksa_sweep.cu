@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
         for (int q = 0; q < R; ++q) {
           const ksa_step_consts c(pk[q]);
           const unsigned ev = ksa_step_fma(c, msgs, i, one, s[q]);
-          ksa_summary_tick<true>(m[q], s[q].r, ev, one);
+          ksa_summary_tick<true>(m[q], s[q].r, ev, ev, one);
         }
       }
     }
@@ -108,8 +108,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
       z->final_replicas = s[q].r;
       z->min_replicas = m[q].rmin;
       z->max_replicas = m[q].rmax;
-      z->reserved = 0u;
-      z->ticks = T;
+      z->poll_failed = z->up_failed = z->down_failed = 0u;
       z->sum_replicas = m[q].sum;
       z->hash = m[q].hash;
     }
@@ -192,7 +191,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
 #pragma unroll
         for (int v = 0; v < V; ++v) {
           const unsigned ev = ksa_step_fma(c, msgs[v], i, one, s[v]);
-          ksa_summary_tick<true>(m[v], s[v].r, ev, one);
+          ksa_summary_tick<true>(m[v], s[v].r, ev, ev, one);
         }
       }
     }
@@ -211,8 +210,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
       z->final_replicas = s[v].r;
       z->min_replicas = m[v].rmin;
       z->max_replicas = m[v].rmax;
-      z->reserved = 0u;
-      z->ticks = T;
+      z->poll_failed = z->up_failed = z->down_failed = 0u;
       z->sum_replicas = m[v].sum;
       z->hash = m[v].hash;
     }

@@ -99,6 +99,16 @@ class ReplayEngine:
         _abi.check(self.lib.ksa_gen_walk_init(C.byref(g), trace0, N, walk.data_ptr(), _stream_ptr()))
         return walk
 
+    def gen_faults(self, seed: int, poll_log2: int, up_log2: int, down_log2: int, tick0: int, T: int,
+                   trace0: int, N: int, ld: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+        """Synthetic failure mask [T][ld] uint8: each FAIL_* bit with probability 2^-log2 (0 = never)."""
+        ld = ld or N
+        if out is None:
+            out = torch.zeros((T, ld), dtype=torch.uint8, device=self.dev)
+        _abi.check(self.lib.ksa_gen_faults(seed, poll_log2, up_log2, down_log2, tick0, T, trace0, N, ld,
+                                           out.data_ptr(), _stream_ptr()))
+        return out
+
     def new_state(self, N: int, seed: int = 0, lo: int = 1, hi: int = 1, trace0: int = 0) -> TraceState:
         """Fresh process (main.go:37-38): replicas = lo + hash(seed, trace) mod (hi-lo+1), stamps 0."""
         st = TraceState(torch.empty(N, dtype=torch.int32, device=self.dev),
@@ -121,18 +131,25 @@ class ReplayEngine:
     def replay_full(self, policy: Policy, depth: torch.Tensor, T: int, A: int, N: int, ld: int,
                     tick0: int, state: TraceState, replicas: torch.Tensor | None = None,
                     events: torch.Tensor | None = None, want_replicas: bool = True,
-                    want_events: bool = True):
-        """ksa_replay_full. Returns (replicas [T][ld] int32, events [T][ld] uint8); advances state."""
+                    want_events: bool = True, fail: torch.Tensor | None = None):
+        """ksa_replay_full. Returns (replicas [T][ld] int32, events [T][ld] uint8); advances state.
+        With `fail` ([T][ld] uint8 of FAIL_* bits) it is ksa_replay_full_faults: the error paths of
+        Run (main.go:44-47,57-60,71-74) are replayed too."""
         assert depth.dtype == torch.int64 and depth.is_cuda and depth.is_contiguous()
         if replicas is None and want_replicas:
             replicas = torch.empty((T, ld), dtype=torch.int32, device=self.dev)
         if events is None and want_events:
             events = torch.empty((T, ld), dtype=torch.uint8, device=self.dev)
         pc, sc = policy.to_c(), state.to_c()
-        _abi.check(self.lib.ksa_replay_full(
-            C.byref(pc), depth.data_ptr(), T, A, N, ld, tick0, C.byref(sc),
-            replicas.data_ptr() if replicas is not None else None,
-            events.data_ptr() if events is not None else None, _stream_ptr()))
+        rp = replicas.data_ptr() if replicas is not None else None
+        ep = events.data_ptr() if events is not None else None
+        if fail is None:
+            _abi.check(self.lib.ksa_replay_full(C.byref(pc), depth.data_ptr(), T, A, N, ld, tick0,
+                                                C.byref(sc), rp, ep, _stream_ptr()))
+        else:
+            assert fail.dtype == torch.uint8 and fail.is_cuda and fail.is_contiguous()
+            _abi.check(self.lib.ksa_replay_full_faults(C.byref(pc), depth.data_ptr(), fail.data_ptr(), T,
+                                                       A, N, ld, tick0, C.byref(sc), rp, ep, _stream_ptr()))
         return replicas, events
 
     def new_summary(self, N: int) -> torch.Tensor:
@@ -141,14 +158,22 @@ class ReplayEngine:
         return s
 
     def replay_summary(self, policy: Policy, depth: torch.Tensor, T: int, A: int, N: int, ld: int,
-                       tick0: int, state: TraceState, summary: torch.Tensor | None = None) -> torch.Tensor:
-        """ksa_replay_summary. `summary` ([N][64] uint8 = ksa_summary records) accumulates."""
+                       tick0: int, state: TraceState, summary: torch.Tensor | None = None,
+                       fail: torch.Tensor | None = None) -> torch.Tensor:
+        """ksa_replay_summary (ksa_replay_summary_faults when `fail` is given). `summary` ([N][64]
+        uint8 = ksa_summary records) accumulates."""
         assert depth.dtype == torch.int64 and depth.is_cuda and depth.is_contiguous()
         if summary is None:
             summary = self.new_summary(N)
         pc, sc = policy.to_c(), state.to_c()
-        _abi.check(self.lib.ksa_replay_summary(C.byref(pc), depth.data_ptr(), T, A, N, ld, tick0,
-                                               C.byref(sc), summary.data_ptr(), _stream_ptr()))
+        if fail is None:
+            _abi.check(self.lib.ksa_replay_summary(C.byref(pc), depth.data_ptr(), T, A, N, ld, tick0,
+                                                   C.byref(sc), summary.data_ptr(), _stream_ptr()))
+        else:
+            assert fail.dtype == torch.uint8 and fail.is_cuda and fail.is_contiguous()
+            _abi.check(self.lib.ksa_replay_summary_faults(C.byref(pc), depth.data_ptr(), fail.data_ptr(),
+                                                          T, A, N, ld, tick0, C.byref(sc),
+                                                          summary.data_ptr(), _stream_ptr()))
         return summary
 
     def replay_sweep(self, policies: list[Policy], depth: torch.Tensor, T: int, A: int, N: int, ld: int,

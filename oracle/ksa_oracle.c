@@ -56,9 +56,10 @@ uint8_t ksa_oracle_scale_down(const ksa_policy* p, int32_t* replicas) {
 }
 
 /* main.go:35-80, virtual wall clock, one trace. */
-void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, int64_t T, int32_t A,
-                              int64_t tick0, int32_t* replicas_state, int64_t* last_up_tick,
-                              int64_t* last_down_tick, int32_t* replicas_out, uint8_t* events_out) {
+void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, const uint8_t* fail,
+                              int64_t T, int32_t A, int64_t tick0, int32_t* replicas_state,
+                              int64_t* last_up_tick, int64_t* last_down_tick, int32_t* replicas_out,
+                              uint8_t* events_out) {
   typedef __int128 ns_t;
   const ns_t poll = p->poll_period_ns;
   ns_t last_up = (ns_t)*last_up_tick * poll;     /* main.go:37 (tick 0 = process start) */
@@ -67,13 +68,21 @@ void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, int64_t
   for (int64_t i = 0; i < T; ++i) {
     const int64_t k = tick0 + 1 + i;
     const ns_t now = (ns_t)k * poll;             /* main.go:41 time.Sleep(pollInterval) */
-    const int64_t n = ksa_oracle_num_messages(depth + i * A, A); /* main.go:43          */
+    const uint8_t f = fail ? fail[i] : 0;
     uint8_t ev = 0;
     int skip = 0;
-    if (n >= p->scale_up_messages) {             /* main.go:51                           */
+    if (f & KSA_FAIL_POLL) {                     /* main.go:44 err != nil                */
+      ev = KSA_EV_POLL_FAILED;                   /* :45 log                              */
+      skip = 2;                                  /* :46 continue                         */
+    }
+    const int64_t n = ksa_oracle_num_messages(depth + i * A, A); /* main.go:43          */
+    if (!skip && n >= p->scale_up_messages) {    /* main.go:51                           */
       if (last_up + (ns_t)p->scale_up_cool_down_ns > now) { /* :52 Add(cool).After(now)  */
         ev |= KSA_EV_UP_COOL;                    /* :53                                  */
         skip = 1;                                /* :54 continue                         */
+      } else if (f & KSA_FAIL_UP) {              /* :57 err != nil                       */
+        ev |= KSA_EV_UP_FAILED;                  /* :58 log                              */
+        skip = 1;                                /* :59 continue (no stamp)              */
       } else {
         ev |= ksa_oracle_scale_up(p, &r);        /* :57                                  */
         last_up = now;                           /* :62 (also after the nil no-op)       */
@@ -83,6 +92,8 @@ void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, int64_t
     if (!skip && n <= p->scale_down_messages) {  /* main.go:65                           */
       if (last_down + (ns_t)p->scale_down_cool_down_ns > now) { /* :66                   */
         ev |= KSA_EV_DOWN_COOL;                  /* :67-68                               */
+      } else if (f & KSA_FAIL_DOWN) {            /* :71 err != nil                       */
+        ev |= KSA_EV_DOWN_FAILED;                /* :72-73 log, continue (no stamp)      */
       } else {
         ev |= ksa_oracle_scale_down(p, &r);      /* :71                                  */
         last_down = now;                         /* :76                                  */
@@ -105,16 +116,19 @@ int ksa_oracle_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
 }
 
 /* One tick of main.go:40-78 in the integer-tick model. */
-static inline uint8_t tick_model(const ksa_policy* p, int64_t cu, int64_t cd, int64_t n, int64_t k,
-                                 int32_t* r, int64_t* ju, int64_t* jd) {
+static inline uint8_t tick_model(const ksa_policy* p, int64_t cu, int64_t cd, int64_t n, uint8_t f,
+                                 int64_t k, int32_t* r, int64_t* ju, int64_t* jd) {
   uint8_t ev = 0;
+  if (f & KSA_FAIL_POLL) return KSA_EV_POLL_FAILED; /* main.go:44-47 */
   if (n >= p->scale_up_messages) {               /* main.go:51    */
     if (k - *ju < cu) return KSA_EV_UP_COOL;     /* main.go:52-55 */
+    if (f & KSA_FAIL_UP) return KSA_EV_UP_FAILED; /* main.go:57-60 */
     ev |= ksa_oracle_scale_up(p, r);             /* main.go:57    */
     *ju = k;                                     /* main.go:62    */
   }
   if (n <= p->scale_down_messages) {             /* main.go:65    */
     if (k - *jd < cd) return ev | KSA_EV_DOWN_COOL; /* main.go:66-69 */
+    if (f & KSA_FAIL_DOWN) return ev | KSA_EV_DOWN_FAILED; /* main.go:71-74 */
     ev |= ksa_oracle_scale_down(p, r);           /* main.go:71    */
     *jd = k;                                     /* main.go:76    */
   }
@@ -131,7 +145,12 @@ static inline void summary_add(ksa_summary* s, int32_t r, uint8_t ev) {
   s->down_noop += (ev & KSA_EV_DOWN_NOOP) != 0;
   s->up_cool += (ev & KSA_EV_UP_COOL) != 0;
   s->down_cool += (ev & KSA_EV_DOWN_COOL) != 0;
-  s->ticks += 1;
+  if (ev == KSA_EV_POLL_FAILED) {
+    s->poll_failed += 1;
+  } else {
+    s->up_failed += (ev & KSA_EV_UP_FAILED) != 0;
+    s->down_failed += (ev & KSA_EV_DOWN_FAILED) != 0;
+  }
   s->sum_replicas = wrap_add64(s->sum_replicas, (int64_t)r);
   s->hash = s->hash * HASH_MUL + (((uint64_t)ev << 32) | (uint64_t)(uint32_t)r);
 }
@@ -147,6 +166,7 @@ void ksa_oracle_summary_clear(ksa_summary* s, int64_t N) {
 typedef struct {
   const ksa_policy* p;
   const int64_t* depth;
+  const uint8_t* fail; /* [T][ld] KSA_FAIL_* bits, or NULL */
   int64_t T, N, ld, tick0, cu, cd;
   int32_t A;
   int32_t* st_r;
@@ -171,8 +191,9 @@ static void* replay_worker(void* arg) {
         int64_t attrs[KSA_MAX_ATTRS];
         for (int32_t a = 0; a < j->A; ++a) attrs[a] = row[a * j->ld + n];
         const int64_t msgs = ksa_oracle_num_messages(attrs, j->A);
+        const uint8_t f = j->fail ? j->fail[t * j->ld + n] : 0;
         const uint8_t ev =
-            tick_model(j->p, j->cu, j->cd, msgs, k, &j->st_r[n], &j->st_ju[n], &j->st_jd[n]);
+            tick_model(j->p, j->cu, j->cd, msgs, f, k, &j->st_r[n], &j->st_ju[n], &j->st_jd[n]);
         if (j->replicas) j->replicas[t * j->ld + n] = j->st_r[n];
         if (j->events) j->events[t * j->ld + n] = ev;
         if (j->summary) summary_add(&j->summary[n], j->st_r[n], ev);
@@ -230,8 +251,8 @@ static int run_split(worker_fn fn, const void* proto, size_t job_size, size_t of
   return threads;
 }
 
-int ksa_oracle_replay(const ksa_policy* p, const int64_t* depth, int64_t T, int32_t A, int64_t N,
-                      int64_t ld, int64_t tick0, int32_t* state_replicas, int64_t* state_last_up,
+int ksa_oracle_replay(const ksa_policy* p, const int64_t* depth, const uint8_t* fail, int64_t T,
+                      int32_t A, int64_t N, int64_t ld, int64_t tick0, int32_t* state_replicas, int64_t* state_last_up,
                       int64_t* state_last_down, int32_t* replicas_out, uint8_t* events_out,
                       ksa_summary* summary, int threads) {
   replay_job proto;
@@ -240,6 +261,7 @@ int ksa_oracle_replay(const ksa_policy* p, const int64_t* depth, int64_t T, int3
   if (ksa_oracle_cool_ticks(p, &proto.cu, &proto.cd) != 0) return -1;
   proto.p = p;
   proto.depth = depth;
+  proto.fail = fail;
   proto.T = T;
   proto.N = N;
   proto.ld = ld;
@@ -354,5 +376,15 @@ void ksa_oracle_state_init(uint64_t seed, int64_t trace0, int64_t N, int32_t lo,
     replicas[n] = ksa_gen_replicas0(seed, (uint64_t)(trace0 + n), lo, hi);
     last_up[n] = 0;
     last_down[n] = 0;
+  }
+}
+
+void ksa_oracle_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, uint32_t down_log2,
+                           int64_t tick0, int64_t T, int64_t trace0, int64_t N, int64_t ld,
+                           uint8_t* fail) {
+  for (int64_t n = 0; n < N; ++n) {
+    const uint64_t key = ksa_fault_key(seed, (uint64_t)(trace0 + n));
+    for (int64_t t = 0; t < T; ++t)
+      fail[t * ld + n] = ksa_gen_fault_byte(key, (uint64_t)(tick0 + 1 + t), poll_log2, up_log2, down_log2);
   }
 }

@@ -36,22 +36,25 @@ uint8_t ksa_oracle_scale_down(const ksa_policy* p, int32_t* replicas);
  * stamps are the instant of the tick that took them, the cool-down test is the reference's
  * `last.Add(cool).After(now)`. depth is [T][A] for this one trace (tight).
  * state: replicas, last_up_ns / last_down_ns as multiples of poll given in TICKS.
+ * fail: [T] KSA_FAIL_* bits for this trace (the three error paths main.go:44-47,57-60,71-74), or NULL.
  */
-void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, int64_t T, int32_t A,
-                              int64_t tick0, int32_t* replicas_state, int64_t* last_up_tick,
-                              int64_t* last_down_tick, int32_t* replicas_out, uint8_t* events_out);
+void ksa_oracle_run_wallclock(const ksa_policy* p, const int64_t* depth, const uint8_t* fail,
+                              int64_t T, int32_t A, int64_t tick0, int32_t* replicas_state,
+                              int64_t* last_up_tick, int64_t* last_down_tick, int32_t* replicas_out,
+                              uint8_t* events_out);
 
 /* max(0, ceil(cool/poll)) for both directions. Returns 0, or -1 if poll <= 0. */
 int ksa_oracle_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_ticks);
 
 /*
  * Batch replay in the integer-tick model, same array layout as ksa_replay_full (ksa_replay.h):
- * depth [T][A][ld], replicas/events [T][ld] (either may be NULL), state arrays [N] in/out,
+ * depth [T][A][ld], fail [T][ld] (NULL: no failures), replicas/events [T][ld] (either may be NULL),
+ * state arrays [N] in/out,
  * summary [N] accumulated when non-NULL. `threads` host threads split the trace axis
  * (<= 0: one per online CPU). Returns the number of threads used, or -1 on bad arguments.
  */
-int ksa_oracle_replay(const ksa_policy* p, const int64_t* depth, int64_t T, int32_t A, int64_t N,
-                      int64_t ld, int64_t tick0, int32_t* state_replicas, int64_t* state_last_up,
+int ksa_oracle_replay(const ksa_policy* p, const int64_t* depth, const uint8_t* fail, int64_t T,
+                      int32_t A, int64_t N, int64_t ld, int64_t tick0, int32_t* state_replicas, int64_t* state_last_up,
                       int64_t* state_last_down, int32_t* replicas_out, uint8_t* events_out,
                       ksa_summary* summary, int threads);
 
@@ -70,6 +73,11 @@ int ksa_oracle_gen_traces(const ksa_gen_params* g, int64_t tick0, int64_t T, int
 void ksa_oracle_gen_walk_init(const ksa_gen_params* g, int64_t trace0, int64_t N, int64_t* walk);
 void ksa_oracle_state_init(uint64_t seed, int64_t trace0, int64_t N, int32_t lo, int32_t hi,
                            int32_t* replicas, int64_t* last_up, int64_t* last_down);
+
+/* Host side of ksa_gen_faults. */
+void ksa_oracle_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, uint32_t down_log2,
+                           int64_t tick0, int64_t T, int64_t trace0, int64_t N, int64_t ld,
+                           uint8_t* fail);
 
 int ksa_oracle_online_cpus(void);
 

@@ -15,6 +15,13 @@ from __future__ import annotations
 from dataclasses import dataclass, field
 
 EV_UP_APPLIED, EV_DOWN_APPLIED, EV_UP_NOOP, EV_DOWN_NOOP, EV_UP_COOL, EV_DOWN_COOL = 1, 2, 4, 8, 16, 32
+EV_UP_FAILED, EV_DOWN_FAILED, EV_POLL_FAILED = 0x40, 0x80, 0xC0
+FAIL_POLL, FAIL_UP, FAIL_DOWN = 1, 2, 4
+
+
+class InjectedError(Exception):
+    """Stands for the `err != nil` returns of the AWS / Kubernetes clients (sqs/sqs.go:52-54,
+    scale/scale.go:56-58,73-75,83-85,101-103)."""
 
 DEFAULT_ATTRIBUTE_NAMES = (  # sqs/sqs.go:28-32
     "ApproximateNumberOfMessages",
@@ -40,8 +47,12 @@ class MockSQS:
 
     def __init__(self, attributes: dict[str, str]):
         self.attributes = dict(attributes)
+        self.fail_next = False  # test hook: make the next GetQueueAttributes return an error
 
     def get_queue_attributes(self) -> dict[str, str]:
+        if self.fail_next:
+            self.fail_next = False
+            raise InjectedError("Failed to get messages in SQS")  # sqs/sqs.go:52-54
         return self.attributes
 
     def set_queue_attributes(self, attributes: dict[str, str]) -> None:
@@ -80,8 +91,13 @@ class PodAutoScaler:
     scale_down_pods: int
     deployment: FakeDeployment = field(default_factory=lambda: FakeDeployment(0))
     log: list[str] = field(default_factory=list)
+    fail_next_up: bool = False    # test hooks: the next Get/Update of that call returns an error
+    fail_next_down: bool = False
 
     def scale_up(self) -> None:  # scale/scale.go:54-79; returning None == returning nil
+        if self.fail_next_up:
+            self.fail_next_up = False
+            raise InjectedError("Failed to get deployment from kube server, no scale up occurred")  # :55-58
         current = self.deployment.replicas  # :60
         if current >= _i32(self.max):  # :62
             self.log.append("max")  # :63
@@ -93,6 +109,9 @@ class PodAutoScaler:
         self.log.append("up")  # :77
 
     def scale_down(self) -> None:  # scale/scale.go:81-107
+        if self.fail_next_down:
+            self.fail_next_down = False
+            raise InjectedError("Failed to get deployment from kube server, no scale down occurred")  # :82-85
         current = self.deployment.replicas  # :87
         if current <= _i32(self.min):  # :89
             self.log.append("min")  # :90
@@ -119,7 +138,7 @@ _LOG_TO_EVENT = {"up": EV_UP_APPLIED, "down": EV_DOWN_APPLIED, "max": EV_UP_NOOP
 
 
 def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
-        start_tick: int = 0, last_up_tick: int = 0, last_down_tick: int = 0):
+        start_tick: int = 0, last_up_tick: int = 0, last_down_tick: int = 0, fail_feed=None):
     """main.go:35-80 for `ticks` iterations of the `for` loop, virtual clock.
 
     `depth_feed(k)` is called before tick k's poll and may call `sqs.client.set_queue_attributes`
@@ -135,6 +154,10 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
         depth_feed(k)
         ev = 0
         p.log.clear()
+        f = fail_feed(k) if fail_feed else 0
+        sqs.client.fail_next = bool(f & FAIL_POLL)
+        p.fail_next_up = bool(f & FAIL_UP)      # consumed only if ScaleUp is actually called this tick
+        p.fail_next_down = bool(f & FAIL_DOWN)
 
         def emit(ev):
             for line in p.log:  # the log lines of scale.go:63,77,90,105 printed this tick
@@ -142,13 +165,22 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
             replicas.append(p.deployment.replicas)
             events.append(ev)
 
-        num_messages = sqs.num_messages()  # main.go:43
+        try:
+            num_messages = sqs.num_messages()  # main.go:43
+        except InjectedError:  # main.go:44-47
+            replicas.append(p.deployment.replicas)
+            events.append(EV_POLL_FAILED)
+            continue
         if num_messages >= flags.scale_up_messages:  # main.go:51
             if last_scale_up_time + flags.scale_up_cool_period > now:  # :52 Add(..).After(now)
                 ev |= EV_UP_COOL  # :53
                 emit(ev)
                 continue  # :54
-            p.scale_up()  # :57 (never errors here)
+            try:
+                p.scale_up()  # :57
+            except InjectedError:  # :57-60: log, continue; no stamp
+                emit(ev | EV_UP_FAILED)
+                continue
             last_scale_up_time = now  # :62
             last_up_tick = k
         if num_messages <= flags.scale_down_messages:  # main.go:65
@@ -156,7 +188,11 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
                 ev |= EV_DOWN_COOL  # :67
                 emit(ev)
                 continue  # :68
-            p.scale_down()  # :71
+            try:
+                p.scale_down()  # :71
+            except InjectedError:  # :71-74
+                emit(ev | EV_DOWN_FAILED)
+                continue
             last_scale_down_time = now  # :76
             last_down_tick = k
         emit(ev)
@@ -164,7 +200,7 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
 
 
 def replay_trace(policy: dict, depth_rows, replicas0: int, start_tick: int = 0,
-                 last_up_tick: int = 0, last_down_tick: int = 0):
+                 last_up_tick: int = 0, last_down_tick: int = 0, fail_rows=None):
     """Convenience wrapper: `policy` uses the C-ABI field names (include/ksa_replay.h),
     `depth_rows` is a list of per-tick tuples of the selected attributes' values."""
     names = DEFAULT_ATTRIBUTE_NAMES[: len(depth_rows[0])] if depth_rows else DEFAULT_ATTRIBUTE_NAMES
@@ -180,4 +216,5 @@ def replay_trace(policy: dict, depth_rows, replicas0: int, start_tick: int = 0,
         row = depth_rows[k - start_tick - 1]
         mock.set_queue_attributes({n: str(v) for n, v in zip(names, row)})
 
-    return run(flags, p, sqs, feed, len(depth_rows), start_tick, last_up_tick, last_down_tick)
+    fail_feed = (lambda k: fail_rows[k - start_tick - 1]) if fail_rows is not None else None
+    return run(flags, p, sqs, feed, len(depth_rows), start_tick, last_up_tick, last_down_tick, fail_feed)

@@ -41,13 +41,16 @@ def load() -> C.CDLL:
     lib.ksa_oracle_scale_down.restype = C.c_uint8
     lib.ksa_oracle_scale_down.argtypes = [C.POINTER(KsaPolicy), C.POINTER(_i32)]
     lib.ksa_oracle_run_wallclock.restype = None
-    lib.ksa_oracle_run_wallclock.argtypes = [C.POINTER(KsaPolicy), _vp, _i64, _i32, _i64,
+    lib.ksa_oracle_run_wallclock.argtypes = [C.POINTER(KsaPolicy), _vp, _vp, _i64, _i32, _i64,
                                              C.POINTER(_i32), C.POINTER(_i64), C.POINTER(_i64), _vp, _vp]
     lib.ksa_oracle_cool_ticks.restype = C.c_int
     lib.ksa_oracle_cool_ticks.argtypes = [C.POINTER(KsaPolicy), C.POINTER(_i64), C.POINTER(_i64)]
     lib.ksa_oracle_replay.restype = C.c_int
-    lib.ksa_oracle_replay.argtypes = [C.POINTER(KsaPolicy), _vp, _i64, _i32, _i64, _i64, _i64, _vp,
+    lib.ksa_oracle_replay.argtypes = [C.POINTER(KsaPolicy), _vp, _vp, _i64, _i32, _i64, _i64, _i64, _vp,
                                       _vp, _vp, _vp, _vp, _vp, C.c_int]
+    lib.ksa_oracle_gen_faults.restype = None
+    lib.ksa_oracle_gen_faults.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, _i64, _i64,
+                                          _i64, _i64, _i64, _vp]
     lib.ksa_oracle_summary_clear.restype = None
     lib.ksa_oracle_summary_clear.argtypes = [_vp, _i64]
     lib.ksa_oracle_traj_hash.restype = None
@@ -103,7 +106,8 @@ def fresh_state(seed: int, trace0: int, N: int, lo: int, hi: int):
 def replay(policy: KsaPolicy, depth: np.ndarray, T: int, A: int, N: int, ld: int, tick0: int,
            state_replicas: np.ndarray, state_last_up: np.ndarray, state_last_down: np.ndarray,
            want_full: bool = True, want_summary: bool = False, summary: np.ndarray | None = None,
-           threads: int = 0, out: tuple[np.ndarray, np.ndarray] | None = None) -> OracleResult:
+           threads: int = 0, out: tuple[np.ndarray, np.ndarray] | None = None,
+           fail: np.ndarray | None = None) -> OracleResult:
     """Batch tick-model replay. State arrays are copied, not modified in place. `out` = preallocated
     (replicas [T][ld] int32, events [T][ld] uint8) to keep page faults out of a timed call."""
     depth = np.ascontiguousarray(depth, dtype=np.int64)
@@ -123,7 +127,10 @@ def replay(policy: KsaPolicy, depth: np.ndarray, T: int, A: int, N: int, ld: int
         load().ksa_oracle_summary_clear(_p(summary), N)
     elif summary is not None:
         summary = np.array(summary, copy=True)
-    used = load().ksa_oracle_replay(C.byref(policy), _p(depth), T, A, N, ld, tick0, _p(r), _p(ju),
+    if fail is not None:
+        fail = np.ascontiguousarray(fail, dtype=np.uint8)
+        assert fail.size >= T * ld
+    used = load().ksa_oracle_replay(C.byref(policy), _p(depth), _p(fail), T, A, N, ld, tick0, _p(r), _p(ju),
                                     _p(jd), _p(replicas), _p(events), _p(summary), threads)
     if used < 0:
         raise ValueError("ksa_oracle_replay rejected its arguments")
@@ -131,7 +138,7 @@ def replay(policy: KsaPolicy, depth: np.ndarray, T: int, A: int, N: int, ld: int
 
 
 def run_wallclock(policy: KsaPolicy, depth_rows: np.ndarray, replicas0: int, tick0: int = 0,
-                  last_up: int = 0, last_down: int = 0):
+                  last_up: int = 0, last_down: int = 0, fail=None):
     """Literal main.go:35-80 restatement, one trace. depth_rows: [T][A]."""
     d = np.ascontiguousarray(depth_rows, dtype=np.int64)
     T, A = d.shape
@@ -139,7 +146,8 @@ def run_wallclock(policy: KsaPolicy, depth_rows: np.ndarray, replicas0: int, tic
     ju, jd = _i64(last_up), _i64(last_down)
     reps = np.zeros(T, dtype=np.int32)
     evs = np.zeros(T, dtype=np.uint8)
-    load().ksa_oracle_run_wallclock(C.byref(policy), _p(d), T, A, tick0, C.byref(r), C.byref(ju),
+    fa = np.ascontiguousarray(fail, dtype=np.uint8) if fail is not None else None
+    load().ksa_oracle_run_wallclock(C.byref(policy), _p(d), _p(fa), T, A, tick0, C.byref(r), C.byref(ju),
                                     C.byref(jd), _p(reps), _p(evs))
     return reps, evs, r.value, ju.value, jd.value
 
@@ -151,6 +159,13 @@ def gen_traces(gen: KsaGenParams, tick0: int, T: int, A: int, trace0: int, N: in
     if rc < 0:
         raise ValueError("ksa_oracle_gen_traces rejected its arguments")
     return depth
+
+
+def gen_faults(seed: int, poll_log2: int, up_log2: int, down_log2: int, tick0: int, T: int,
+               trace0: int, N: int, ld: int) -> np.ndarray:
+    fail = np.zeros((T, ld), dtype=np.uint8)
+    load().ksa_oracle_gen_faults(seed, poll_log2, up_log2, down_log2, tick0, T, trace0, N, ld, _p(fail))
+    return fail
 
 
 def gen_walk_init(gen: KsaGenParams, trace0: int, N: int) -> np.ndarray:

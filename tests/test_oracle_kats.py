@@ -71,13 +71,16 @@ def test_derived_vectors_all_oracles(v):
     rows = np.asarray(v["depth"], dtype=np.int64)
     T, A = rows.shape
     assert pol.num_attrs == A
-    reps, evs, _, _, _ = oracle_lib.run_wallclock(pol.to_c(), rows, v["r0"])
+    fail = np.asarray(v["fail"], dtype=np.uint8) if "fail" in v else None
+    reps, evs, _, _, _ = oracle_lib.run_wallclock(pol.to_c(), rows, v["r0"], fail=fail)
     assert reps.tolist() == v["replicas"], "wall-clock C oracle"
     assert evs.tolist() == v["events"], "wall-clock C oracle"
-    res = oracle_lib.replay(pol.to_c(), rows.reshape(T, A, 1), T, A, 1, 1, 0, [v["r0"]], [0], [0])
+    res = oracle_lib.replay(pol.to_c(), rows.reshape(T, A, 1), T, A, 1, 1, 0, [v["r0"]], [0], [0],
+                            fail=None if fail is None else fail.reshape(T, 1))
     assert res.replicas[:, 0].tolist() == v["replicas"], "tick-model C oracle"
     assert res.events[:, 0].tolist() == v["events"], "tick-model C oracle"
-    pr, pe, _, _ = policy_py.replay_trace(pol.as_abi_dict(), [tuple(r) for r in rows.tolist()], v["r0"])
+    pr, pe, _, _ = policy_py.replay_trace(pol.as_abi_dict(), [tuple(r) for r in rows.tolist()], v["r0"],
+                                          fail_rows=v.get("fail"))
     assert pr == v["replicas"] and pe == v["events"], "python restatement"
 
 
@@ -122,21 +125,29 @@ def test_c_oracles_equal_python_restatement(pol, data):
     ju = data.draw(st.integers(0, tick0)) if tick0 else 0
     jd = data.draw(st.integers(0, tick0)) if tick0 else 0
     arr = np.asarray(rows, dtype=np.int64).reshape(T, A)
-    w_r, w_e, w_final, w_ju, w_jd = oracle_lib.run_wallclock(pol.to_c(), arr, r0, tick0, ju, jd)
+    fail_rows = None
+    if data.draw(st.booleans()):  # half of the cases also inject call failures (Q10)
+        fail_rows = [data.draw(st.sampled_from([0, 0, 0, 1, 2, 4, 6, 3, 7])) for _ in range(T)]
+    fail = None if fail_rows is None else np.asarray(fail_rows, dtype=np.uint8)
+    w_r, w_e, w_final, w_ju, w_jd = oracle_lib.run_wallclock(pol.to_c(), arr, r0, tick0, ju, jd, fail=fail)
     res = oracle_lib.replay(pol.to_c(), arr.reshape(T, A, 1), T, A, 1, 1, tick0, [r0], [ju], [jd],
-                            want_summary=True)
-    p_r, p_e, p_ju, p_jd = policy_py.replay_trace(pol.as_abi_dict(), rows, r0, tick0, ju, jd)
+                            want_summary=True, fail=None if fail is None else fail.reshape(T, 1))
+    p_r, p_e, p_ju, p_jd = policy_py.replay_trace(pol.as_abi_dict(), rows, r0, tick0, ju, jd,
+                                                  fail_rows=fail_rows)
     assert w_r.tolist() == p_r and w_e.tolist() == p_e
     assert res.replicas[:, 0].tolist() == p_r and res.events[:, 0].tolist() == p_e
     assert (w_ju, w_jd) == (p_ju, p_jd) == (int(res.state_last_up[0]), int(res.state_last_down[0]))
     assert w_final == p_r[-1]
     # summary consistency
     s = res.summary[0]
-    assert s["ticks"] == T and s["final_replicas"] == p_r[-1]
+    assert s["final_replicas"] == p_r[-1]
     assert s["min_replicas"] == min(p_r) and s["max_replicas"] == max(p_r)
     for bit, name in ((1, "up_applied"), (2, "down_applied"), (4, "up_noop"), (8, "down_noop"),
                       (16, "up_cool"), (32, "down_cool")):
         assert s[name] == sum(1 for e in p_e if e & bit)
+    assert s["poll_failed"] == sum(1 for e in p_e if e == 0xC0)
+    assert s["up_failed"] == sum(1 for e in p_e if e != 0xC0 and e & 0x40)
+    assert s["down_failed"] == sum(1 for e in p_e if e != 0xC0 and e & 0x80)
     h = 0
     for r, e in zip(p_r, p_e):
         h = (h * 0x9E3779B97F4A7C15 + ((e << 32) | (r & 0xFFFFFFFF))) & (2**64 - 1)

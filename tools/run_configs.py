@@ -218,9 +218,50 @@ def run_config5(args):
         dist.destroy_process_group()
 
 
+def run_config6(args):
+    """configs[1] with call failures (row f3): 2^20 traces x --ticks ticks, default policy, single
+    attribute, failure mask with 1/32 failed polls and 1/16 failing ScaleUp / ScaleDown calls."""
+    eng = ksa.ReplayEngine(0)
+    N, T = args.traces, min(args.ticks, 4000)
+    pol = ksa.Policy(attr_mask=1)
+    gen = ksa.GenParams(seed=0x5EED0001)
+    depth = eng.gen_traces(gen, 0, T, 1, 0, N, N)
+    fail = eng.gen_faults(gen.seed, 5, 4, 4, 0, T, 0, N, N)
+    replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
+    events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
+    state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
+    out = {}
+    for mode in ("full", "summary"):
+        ms = []
+        for rep in range(args.reps + 2):
+            st = state0.clone()
+            summ = eng.new_summary(N)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            if mode == "full":
+                eng.replay_full(pol, depth, T, 1, N, N, 0, st, replicas=replicas, events=events, fail=fail)
+            else:
+                eng.replay_summary(pol, depth, T, 1, N, N, 0, st, summary=summ, fail=fail)
+            b.record()
+            torch.cuda.synchronize()
+            if rep >= 2:
+                ms.append(a.elapsed_time(b))
+        bpd = 14 if mode == "full" else 9
+        best = min(ms) / 1e3
+        out[mode] = {"ms": min(ms), "decisions_per_s": N * T / best, "GBps_algorithmic": bpd * N * T / best / 1e9,
+                     "frac_of_measured_peak": bpd * N * T / best / 1e9 / peak(), "bytes_per_decision": bpd}
+        if mode == "summary":
+            sv = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+            h = eng.traj_hash(replicas, events, T, N, N).cpu().numpy().view(np.uint64)
+            out["parity"] = "traj_hash(full) == summary hash: " + ("ok" if np.array_equal(h, sv["hash"]) else "MISMATCH")
+            out["failed_polls"] = int(sv["poll_failed"].sum())
+            out["failed_scale_calls"] = int(sv["up_failed"].sum() + sv["down_failed"].sum())
+    print(json.dumps({"config": "2+faults", "workload": f"{N} traces x {T} ticks, default policy, failure mask", **out}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5])
+    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5, 6])
     ap.add_argument("--traces", type=int, default=1 << 20)
     ap.add_argument("--ticks", type=int, default=10_000)
     ap.add_argument("--chunk", type=int, default=2500)
@@ -233,7 +274,7 @@ def main():
     ap.add_argument("--chunks-per-rank", type=int, default=0)
     ap.add_argument("--sweep-tune", action="store_true")
     args = ap.parse_args()
-    {3: run_config3, 4: run_config4, 5: run_config5}[args.config](args)
+    {3: run_config3, 4: run_config4, 5: run_config5, 6: run_config6}[args.config](args)
 
 
 if __name__ == "__main__":
