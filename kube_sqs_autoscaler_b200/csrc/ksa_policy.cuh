@@ -223,6 +223,57 @@ __device__ __forceinline__ unsigned ksa_step_faults(const ksa_step_consts& c, lo
   return poll_ok ? (ev | evd) : (unsigned)KSA_EV_POLL_FAILED;  // main.go:45
 }
 
+// ksa_step_faults with the conditional moves / adds as predicated IMADs (see ksa_step_fma).
+// `ucont` = the up half `continue`d (cool-down or failed call) = up_hit && !up_go.
+__device__ __forceinline__ unsigned ksa_step_faults_fma(const ksa_step_consts& c, long long n, unsigned f,
+                                                        int i, int one, ksa_trace_regs& s) {
+  unsigned ev;
+  asm("{\n\t"
+      ".reg .pred pok, uh, ureach, ucool, ufail, ugo, uapp, ucont, dh, dreach, dcool, dfail, dgo, dapp;\n\t"
+      ".reg .s32 t, u;\n\t"
+      ".reg .b32 fb;\n\t"
+      "and.b32 fb, %15, 1;\n\t"
+      "setp.eq.u32 pok, fb, 0;\n\t"                 // main.go:44 err == nil
+      "setp.ge.and.s64 uh, %4, %5, pok;\n\t"        // main.go:51
+      "setp.le.and.s32 ureach, %2, %11, uh;\n\t"    // main.go:52 false: ScaleUp is called
+      "setp.gt.and.s32 ucool, %2, %11, uh;\n\t"     // main.go:52 true
+      "and.b32 fb, %15, 2;\n\t"
+      "setp.ne.and.u32 ufail, fb, 0, ureach;\n\t"   // main.go:57-60
+      "setp.eq.and.u32 ugo, fb, 0, ureach;\n\t"     // ScaleUp returned nil
+      "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
+      "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"      // main.go:62   su = i + cu
+      "selp.u32 %0, 16, 0, ucool;\n\t"
+      "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"
+      "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"
+      "@ufail mad.lo.s32 %0, %14, 64, %0;\n\t"      // KSA_EV_UP_FAILED
+      "add.s32 t, %1, %9;\n\t"                      // scale.go:66
+      "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
+      "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
+      "and.pred ucont, uh, !ugo;\n\t"               // main.go:54 / :59 continue
+      "setp.le.and.s64 dh, %4, %6, pok;\n\t"        // main.go:65
+      "and.pred dh, dh, !ucont;\n\t"
+      "setp.le.and.s32 dreach, %3, %11, dh;\n\t"    // main.go:66 false: ScaleDown is called
+      "setp.gt.and.s32 dcool, %3, %11, dh;\n\t"
+      "and.b32 fb, %15, 4;\n\t"
+      "setp.ne.and.u32 dfail, fb, 0, dreach;\n\t"   // main.go:71-74
+      "setp.eq.and.u32 dgo, fb, 0, dreach;\n\t"
+      "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
+      "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"      // main.go:76   sd = i + cd
+      "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
+      "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
+      "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
+      "@dfail mad.lo.s32 %0, %14, 128, %0;\n\t"     // KSA_EV_DOWN_FAILED
+      "sub.s32 u, %1, %10;\n\t"                     // scale.go:94
+      "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
+      "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
+      "@!pok mov.u32 %0, 192;\n\t"                  // KSA_EV_POLL_FAILED, main.go:45
+      "}"
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "r"(f));
+  return ev;
+}
+
 // d = a * b + c as a true IMAD (FMA pipe): ptxas cannot fold it when b is not a compile-time
 // constant, which is what the `one` kernel argument is for.
 __device__ __forceinline__ unsigned ksa_mad_u32(unsigned a, unsigned b, unsigned c) {

@@ -13,6 +13,8 @@
 // (trace, tick) in full mode, 8A in summary mode.
 #include "ksa_internal.h"
 
+#include <cstdlib>
+
 namespace {
 
 struct ReplayArgs {
@@ -180,7 +182,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   }
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
-  constexpr bool FAULTS = (STEP == 4);
+  constexpr bool FAULTS = (STEP == 4 || STEP == 5);
+  constexpr bool FMA = (STEP == 2 || STEP == 3 || STEP == 5);
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -264,7 +267,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       fv[v] = 0u;
       if constexpr (FAULTS) {
         fv[v] = (fw[v / 4] >> (8 * (v % 4))) & 0xffu;
-        ev[v] = ksa_step_faults(c, n[v], fv[v], i, s[v]);
+        ev[v] = STEP == 5 ? ksa_step_faults_fma(c, n[v], fv[v], i, one, s[v])
+                          : ksa_step_faults(c, n[v], fv[v], i, s[v]);
       } else if constexpr (STEP >= 2)
         ev[v] = ksa_step_fma(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
@@ -275,11 +279,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     }
     if constexpr (MODE != MODE_SUMMARY) {
       if (want_r) store_replicas<V>(rp + (long long)tt * a.ld, rr);
-      if (want_e) store_events<V, (STEP == 2 || STEP == 3)>(ep + (long long)tt * a.ld, ev);
+      if (want_e) store_events<V, FMA>(ep + (long long)tt * a.ld, ev);
     } else {
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        ksa_summary_tick<(STEP == 2 || STEP == 3)>(sm[v], rr[v], ev[v], FAULTS ? (ev[v] & 0x3fu) : ev[v], one);
+        ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], FAULTS ? (ev[v] & 0x3fu) : ev[v], one);
         if constexpr (FAULTS) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
       }
     }
@@ -424,10 +428,15 @@ const Variant kSummaryVariants[] = {
 const Variant kFullFaultsVariants[] = {
     KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
     KSA_VARIANT(1, MODE_FULL_OPT, 8, 2, HINT_NA, 4, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
+    KSA_VARIANT(2, MODE_FULL, 8, 2, HINT_NA, 5, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
+    KSA_VARIANT(3, MODE_FULL, 8, 2, HINT_NA, 5, 256, 2, 4, 3, 256, 2, 4, 2, 256, 2),
+    KSA_VARIANT(4, MODE_FULL, 4, 3, HINT_NA, 5, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
 };
 const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
     KSA_VARIANT(1, MODE_SUMMARY, 2, 4, HINT_NA, 4, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(2, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 7, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
@@ -488,7 +497,13 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   if (!faults && mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
   const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];
   if (faults) {
-    var = mode == MODE_FULL ? &kFullFaultsVariants[1] : &kSummaryFaultsVariants[1];
+    // Faults variants: default = the FMA-steered kernel when both outputs are wanted; the tuning
+    // knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
+    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? 4 : 1) : 3;  // profiles/r01_config2_faults.txt
+    if (const char* e = std::getenv("KSA_FAULTS_VARIANT")) fid = std::atoi(e);
+    var = mode == MODE_FULL ? find_variant(kFullFaultsVariants, fid) : find_variant(kSummaryFaultsVariants, fid);
+    if (!var) var = mode == MODE_FULL ? &kFullFaultsVariants[2] : &kSummaryFaultsVariants[2];  // unknown id
+    if (var && mode == MODE_FULL && (!replicas_dev || !events_dev) && fid >= 2) var = &kFullFaultsVariants[1];
     if (want == 0) var = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
     scalar = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
   }

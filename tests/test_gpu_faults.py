@@ -5,6 +5,8 @@ and the independent Python restatement in tests/test_oracle_kats.py.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import pytest
 
@@ -80,7 +82,13 @@ def test_random_policies_with_failures(engine, A):
                 engine.set_variant(-2 if scalar else 0, -2 if scalar else 0)
                 out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
                 check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} scalar={scalar}")
+            for fid in ("1", "2", "3", "4"):  # every entry of the faults variant tables
+                os.environ["KSA_FAULTS_VARIANT"] = fid
+                out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
+                check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} faults_variant={fid}")
+            os.environ.pop("KSA_FAULTS_VARIANT", None)
     finally:
+        os.environ.pop("KSA_FAULTS_VARIANT", None)
         engine.set_variant(0, 0)
 
 

@@ -231,6 +231,25 @@ def run_config6(args):
     events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
     state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
     out = {}
+    if args.sweep_tune:
+        for fid in range(1, 5):
+            os.environ["KSA_FAULTS_VARIANT"] = str(fid)
+            for mode in ("full", "summary"):
+                ts = []
+                for rep in range(3):
+                    st = state0.clone()
+                    summ = eng.new_summary(N)
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    if mode == "full":
+                        eng.replay_full(pol, depth, T, 1, N, N, 0, st, replicas=replicas, events=events, fail=fail)
+                    else:
+                        eng.replay_summary(pol, depth, T, 1, N, N, 0, st, summary=summ, fail=fail)
+                    b.record()
+                    torch.cuda.synchronize()
+                    ts.append(a.elapsed_time(b))
+                print(f"# faults variant {fid} {mode}: {min(ts):.3f} ms {N * T / (min(ts) * 1e-3):.3e} decisions/s", flush=True)
+        os.environ.pop("KSA_FAULTS_VARIANT", None)
     for mode in ("full", "summary"):
         ms = []
         for rep in range(args.reps + 2):
