@@ -310,6 +310,36 @@ int ksa_gen_walk_init(const ksa_gen_params* g, int64_t trace0, int64_t N, int64_
 int ksa_state_init(uint64_t seed, int64_t trace0, int64_t N, int32_t lo, int32_t hi,
                    const ksa_state* state, void* stream);
 
+/* ---- ingest: recorded depths in the formats they arrive in ------------------------------- */
+
+/*
+ * Recorded queue-depth series usually arrive trace-major: one queue's history at a time
+ * ([N][T], e.g. one metrics export per queue). The replay wants tick-major [T][A][ld]. This is a
+ * tiled transpose through shared memory that also widens the element type.
+ *   src_dev   [N][src_ld] elements of src_bytes (8 = int64, 4 = int32, sign-extended), src_ld >= T
+ *   depth_dev [T][A][ld] int64; plane `a` (0 <= a < A) receives depth[(t*A + a)*ld + n] = src[n][t]
+ * Replaces nothing in the reference (its only source is one live GetQueueAttributes per poll,
+ * sqs/sqs.go:51); it is the step immediately before the path when replaying recorded data.
+ * Traffic: src_bytes read + 8 written per element.
+ */
+int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int64_t src_ld, int64_t T,
+                         int64_t N, int32_t A, int32_t a, int64_t ld, int64_t* depth_dev,
+                         void* stream);
+
+/*
+ * Decode SQS attribute values as the reference does: strconv.Atoi on a decimal string
+ * (sqs/sqs.go:58). text_dev holds `count` fixed-width records of `width` bytes (1..32), each the
+ * string followed by NUL padding (a record without NUL uses all `width` bytes).
+ * Atoi semantics (Go 1.15 strconv): optional '+' or '-', then one or more ASCII digits, nothing
+ * else; the value must fit a Go int (int64). Anything else is an error, for which the reference
+ * returns from NumMessages with err != nil and Run skips the tick (sqs/sqs.go:59-61, main.go:44-47):
+ *   values_dev[i] = the number, or 0 on error
+ *   fail_dev[i]   = 0, or KSA_FAIL_POLL on error   (feeds the *_faults replays; may be NULL)
+ * Traffic: width read + 9 written per record.
+ */
+int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t count, int64_t* values_dev,
+                       uint8_t* fail_dev, void* stream);
+
 /* ---- host-buffer pipeline (the call a Go / Python host makes with its own slices) --------- */
 
 typedef struct ksa_pipeline ksa_pipeline; /* opaque; owns device staging + 3 streams */

@@ -1,0 +1,148 @@
+// ksa_ingest.cu — the step immediately before the path when the depths are recorded rather than
+// synthetic: (1) trace-major [N][T] series -> the tick-major [T][A][ld] int64 array the replay
+// kernels stream, (2) SQS attribute strings -> int64 with strconv.Atoi semantics, the decode the
+// reference performs per attribute (sqs/sqs.go:58). Both are HBM-bound byte movers.
+#include "ksa_internal.h"
+
+namespace {
+
+constexpr int kTile = 64;   // 64 ticks x 64 traces per block
+constexpr int kPitch = 65;  // odd pitch (in 8-byte words): column reads hit distinct banks
+
+// Tiled transpose + widen. Block = 256 threads = 8 warps. Load phase: warp w reads trace rows
+// w, w+8, ... of the tile, 32 consecutive ticks per instruction (256 B for int64 sources). Store
+// phase: warp w writes tick rows w, w+8, ..., 32 consecutive traces per instruction (256 B).
+// Every global access is a run of full 32-byte sectors; each element is read once, written once.
+template <typename SRC>
+__global__ void __launch_bounds__(256) transpose_kernel(const SRC* __restrict__ src, long long src_ld,
+                                                        long long T, long long N, int A, int a,
+                                                        long long ld, long long* __restrict__ dst) {
+  __shared__ long long tile[kTile][kPitch];
+  const long long t0 = (long long)blockIdx.x * kTile;
+  const long long n0 = (long long)blockIdx.y * kTile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < kTile / 8; ++k) {
+    const int nl = warp + 8 * k;
+    const long long n = n0 + nl;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int tl = lane + 32 * h;
+      const long long t = t0 + tl;
+      long long v = 0;
+      if (n < N && t < T) v = (long long)__ldg(src + n * src_ld + t);
+      tile[nl][tl] = v;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kTile / 8; ++k) {
+    const int tl = warp + 8 * k;
+    const long long t = t0 + tl;
+    if (t >= T) continue;
+    long long* row = dst + (t * A + a) * ld;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int nl = lane + 32 * h;
+      const long long n = n0 + nl;
+      if (n < N) __stcs(row + n, tile[nl][tl]);
+    }
+  }
+}
+
+// strconv.Atoi on one fixed-width record. Go 1.15 semantics for base 10, 64-bit int:
+//   ""            -> ErrSyntax          "+" / "-"    -> ErrSyntax
+//   [+-]?[0-9]+   -> value, ErrRange if it does not fit int64 (|-2^63| allowed for '-')
+//   anything else (spaces, '_', letters, a second sign) -> ErrSyntax
+// The record ends at the first NUL or at `width` bytes.
+__device__ __forceinline__ bool atoi_record(const unsigned char* s, int width, long long* out) {
+  int p = 0;
+  bool neg = false;
+  if (p < width && (s[p] == '+' || s[p] == '-')) neg = s[p++] == '-';
+  unsigned long long acc = 0;
+  int digits = 0;
+  bool overflow = false;
+  for (; p < width; ++p) {
+    const unsigned c = s[p];
+    if (c == 0) break;
+    const unsigned d = c - '0';
+    if (d > 9u) return false;  // ErrSyntax
+    // acc * 10 + d must stay <= 2^63 (checked against the signed limit below)
+    if (acc > (0x8000000000000000ull - d) / 10ull) overflow = true;
+    acc = acc * 10ull + d;
+    ++digits;
+  }
+  if (digits == 0) return false;  // "" or a bare sign
+  // a NUL must be followed by NULs only; trailing garbage after the terminator is not part of the string
+  if (overflow) return false;     // ErrRange
+  if (!neg && acc > 0x7fffffffffffffffull) return false;
+  *out = neg ? (long long)(0ull - acc) : (long long)acc;
+  return true;
+}
+
+template <int WIDTH_VEC>  // WIDTH_VEC = width / 16 when the records can be fetched as uint4, else 0
+__global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ text, int width,
+                                                      long long count, long long* __restrict__ values,
+                                                      unsigned char* __restrict__ fail) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= count) return;
+  unsigned char rec[32];
+  if constexpr (WIDTH_VEC > 0) {
+    const uint4* p = reinterpret_cast<const uint4*>(text + i * width);
+#pragma unroll
+    for (int q = 0; q < WIDTH_VEC; ++q) {
+      const uint4 w = __ldg(p + q);
+      reinterpret_cast<uint4*>(rec)[q] = w;
+    }
+  } else {
+    for (int q = 0; q < width; ++q) rec[q] = (unsigned char)__ldg(text + i * width + q);
+  }
+  long long v = 0;
+  const bool ok = atoi_record(rec, width, &v);
+  values[i] = ok ? v : 0;
+  if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;  // sqs.go:59-61 -> main.go:44-47
+}
+
+}  // namespace
+
+extern "C" int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int64_t src_ld, int64_t T,
+                                    int64_t N, int32_t A, int32_t a, int64_t ld, int64_t* depth_dev,
+                                    void* stream) {
+  if (!src_dev || !depth_dev) return ksa_fail(KSA_EINVAL, "NULL pointer");
+  if (src_bytes != 8 && src_bytes != 4) return ksa_fail(KSA_EINVAL, "src_bytes=%d: 8 (int64) or 4 (int32)", src_bytes);
+  if (A < 1 || A > KSA_MAX_ATTRS || a < 0 || a >= A) return ksa_fail(KSA_EINVAL, "bad plane a=%d of A=%d", a, A);
+  if (T < 0 || N < 0 || src_ld < T || ld < N) return ksa_fail(KSA_EINVAL, "bad T/N/src_ld/ld");
+  if (T == 0 || N == 0) return KSA_OK;
+  const long long gx = (T + kTile - 1) / kTile, gy = (N + kTile - 1) / kTile;
+  if (gx > 0x7fffffffll || gy > 65535) return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max 65535*64 traces)", (long long)N);
+  dim3 grid((unsigned)gx, (unsigned)gy);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (src_bytes == 8)
+    transpose_kernel<long long><<<grid, 256, 0, st>>>((const long long*)src_dev, src_ld, T, N, A, a, ld,
+                                                       (long long*)depth_dev);
+  else
+    transpose_kernel<int><<<grid, 256, 0, st>>>((const int*)src_dev, src_ld, T, N, A, a, ld,
+                                                 (long long*)depth_dev);
+  KSA_LAUNCH_CHECK("transpose_kernel");
+  return KSA_OK;
+}
+
+extern "C" int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t count, int64_t* values_dev,
+                                  uint8_t* fail_dev, void* stream) {
+  if (!text_dev || !values_dev) return ksa_fail(KSA_EINVAL, "NULL pointer");
+  if (width < 1 || width > 32) return ksa_fail(KSA_EINVAL, "width=%d outside [1,32]", width);
+  if (count < 0) return ksa_fail(KSA_EINVAL, "count < 0");
+  if (count == 0) return KSA_OK;
+  const long long blocks = (count + 255) / 256;
+  if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "count too large for one launch");
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (width % 16 == 0) && ksa_aligned(text_dev, 16);
+  if (vec && width == 16)
+    decimal_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
+  else if (vec && width == 32)
+    decimal_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
+  else
+    decimal_kernel<0><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
+  KSA_LAUNCH_CHECK("decimal_kernel");
+  return KSA_OK;
+}

@@ -109,6 +109,30 @@ class ReplayEngine:
                                            out.data_ptr(), _stream_ptr()))
         return out
 
+    # ---- ingest -------------------------------------------------------------------------------
+    def ingest_transpose(self, src: torch.Tensor, T: int, N: int, A: int = 1, a: int = 0,
+                         ld: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+        """ksa_ingest_transpose: trace-major src [N][src_ld] (int64 or int32) -> plane `a` of the
+        tick-major depth array [T][A][ld] int64."""
+        assert src.is_cuda and src.dim() == 2 and src.is_contiguous() and src.dtype in (torch.int64, torch.int32)
+        ld = ld or N
+        if out is None:
+            out = torch.zeros((T, A, ld), dtype=torch.int64, device=self.dev)
+        _abi.check(self.lib.ksa_ingest_transpose(src.data_ptr(), src.element_size(), src.shape[1], T, N, A, a,
+                                                 ld, out.data_ptr(), _stream_ptr()))
+        return out
+
+    def ingest_decimal(self, text: torch.Tensor, want_fail: bool = True):
+        """ksa_ingest_decimal: text [count][width] uint8 (NUL-padded decimal strings) -> (values int64
+        [count], fail uint8 [count] with FAIL_POLL where strconv.Atoi would return an error)."""
+        assert text.is_cuda and text.dtype == torch.uint8 and text.dim() == 2 and text.is_contiguous()
+        count, width = text.shape
+        values = torch.empty(count, dtype=torch.int64, device=self.dev)
+        fail = torch.empty(count, dtype=torch.uint8, device=self.dev) if want_fail else None
+        _abi.check(self.lib.ksa_ingest_decimal(text.data_ptr(), width, count, values.data_ptr(),
+                                               fail.data_ptr() if fail is not None else None, _stream_ptr()))
+        return values, fail
+
     def new_state(self, N: int, seed: int = 0, lo: int = 1, hi: int = 1, trace0: int = 0) -> TraceState:
         """Fresh process (main.go:37-38): replicas = lo + hash(seed, trace) mod (hi-lo+1), stamps 0."""
         st = TraceState(torch.empty(N, dtype=torch.int32, device=self.dev),

@@ -388,3 +388,42 @@ void ksa_oracle_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, 
       fail[t * ld + n] = ksa_gen_fault_byte(key, (uint64_t)(tick0 + 1 + t), poll_log2, up_log2, down_log2);
   }
 }
+
+/* ---- strconv.Atoi, as sqs/sqs.go:58 applies it to every attribute value --------------------
+ * Restated from the published Go 1.15 strconv algorithm (the stdlib is not part of the reference
+ * tree): Atoi(s) = ParseInt(s, 10, 0): optional sign, then ParseUint: every byte must be '0'..'9'
+ * (no underscores in base 10), at least one digit, overflow of uint64 or of the signed range is
+ * ErrRange, anything else ErrSyntax. Both error kinds make NumMessages return an error
+ * (sqs/sqs.go:59-61). Records are fixed-width, NUL padded. Returns the number of failed records. */
+int64_t ksa_oracle_atoi(const char* text, int32_t width, int64_t count, int64_t* values, uint8_t* fail) {
+  int64_t bad = 0;
+  for (int64_t i = 0; i < count; ++i) {
+    const unsigned char* s = (const unsigned char*)text + i * width;
+    int len = 0;
+    while (len < width && s[len] != 0) ++len;
+    int ok = 1;
+    int neg = 0;
+    int p = 0;
+    if (len == 0) ok = 0;                                  /* ParseInt: s == "" -> syntaxError */
+    if (ok && (s[0] == '+' || s[0] == '-')) { neg = s[0] == '-'; p = 1; }
+    if (ok && p == len) ok = 0;                            /* ParseUint("") after the sign */
+    uint64_t n = 0;
+    const uint64_t cutoff = UINT64_MAX / 10 + 1;           /* ParseUint: n >= cutoff -> n*10 overflows */
+    for (; ok && p < len; ++p) {
+      const unsigned c = s[p];
+      if (c < '0' || c > '9') { ok = 0; break; }           /* syntaxError */
+      if (n >= cutoff) { ok = 0; break; }                  /* rangeError */
+      n *= 10;
+      const uint64_t n1 = n + (c - '0');
+      if (n1 < n) { ok = 0; break; }                       /* rangeError: n+d overflows */
+      n = n1;
+    }
+    const uint64_t limit = (uint64_t)1 << 63;              /* ParseInt: cutoff := 1 << (bitSize-1) */
+    if (ok && !neg && n >= limit) ok = 0;
+    if (ok && neg && n > limit) ok = 0;
+    values[i] = ok ? (neg ? (int64_t)(0 - n) : (int64_t)n) : 0;
+    if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;
+    bad += !ok;
+  }
+  return bad;
+}

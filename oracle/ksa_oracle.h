@@ -79,6 +79,10 @@ void ksa_oracle_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, 
                            int64_t tick0, int64_t T, int64_t trace0, int64_t N, int64_t ld,
                            uint8_t* fail);
 
+/* strconv.Atoi over fixed-width NUL-padded records, as ksa_ingest_decimal (sqs/sqs.go:58-61).
+ * Returns the number of records that failed to parse. */
+int64_t ksa_oracle_atoi(const char* text, int32_t width, int64_t count, int64_t* values, uint8_t* fail);
+
 int ksa_oracle_online_cpus(void);
 
 #ifdef __cplusplus

@@ -218,3 +218,21 @@ def replay_trace(policy: dict, depth_rows, replicas0: int, start_tick: int = 0,
 
     fail_feed = (lambda k: fail_rows[k - start_tick - 1]) if fail_rows is not None else None
     return run(flags, p, sqs, feed, len(depth_rows), start_tick, last_up_tick, last_down_tick, fail_feed)
+
+
+_ATOI_RE = None
+
+
+def atoi(text: bytes):
+    """Go strconv.Atoi on a byte string (sqs/sqs.go:58): returns the int, or None where Go returns an
+    error (ErrSyntax / ErrRange). Independent of oracle/ksa_oracle.c: a regular expression and a
+    range check on Python's unbounded ints."""
+    import re
+
+    global _ATOI_RE
+    if _ATOI_RE is None:
+        _ATOI_RE = re.compile(rb"[+-]?[0-9]+")
+    if not _ATOI_RE.fullmatch(text):
+        return None
+    v = int(text.decode("ascii"))
+    return v if -(1 << 63) <= v <= (1 << 63) - 1 else None

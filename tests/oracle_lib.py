@@ -62,6 +62,8 @@ def load() -> C.CDLL:
     lib.ksa_oracle_gen_walk_init.argtypes = [C.POINTER(KsaGenParams), _i64, _i64, _vp]
     lib.ksa_oracle_state_init.restype = None
     lib.ksa_oracle_state_init.argtypes = [C.c_uint64, _i64, _i64, _i32, _i32, _vp, _vp, _vp]
+    lib.ksa_oracle_atoi.restype = _i64
+    lib.ksa_oracle_atoi.argtypes = [_vp, _i32, _i64, _vp, _vp]
     lib.ksa_oracle_online_cpus.restype = C.c_int
     lib.ksa_oracle_online_cpus.argtypes = []
     _lib = lib
@@ -196,3 +198,13 @@ def scale_calls(policy: KsaPolicy, init: int, calls: list[str]) -> list[int]:
 def num_messages(values) -> int:
     a = np.asarray(values, dtype=np.int64)
     return load().ksa_oracle_num_messages(_p(a), a.size)
+
+
+def atoi_records(text: np.ndarray):
+    """text: uint8 [count][width] fixed-width NUL-padded records -> (values int64, fail uint8)."""
+    text = np.ascontiguousarray(text, dtype=np.uint8)
+    count, width = text.shape
+    values = np.zeros(count, dtype=np.int64)
+    fail = np.zeros(count, dtype=np.uint8)
+    load().ksa_oracle_atoi(_p(text), width, count, _p(values), _p(fail))
+    return values, fail

@@ -1,0 +1,146 @@
+"""Ingest: trace-major -> tick-major transposition and the strconv.Atoi decode
+of SQS attribute strings (sqs/sqs.go:58). CPU tests pin the C oracle to the golden Atoi vectors and
+to the independent Python restatement; GPU tests compare the CUDA kernels with the oracle / numpy,
+bit for bit, through the C ABI."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+import kube_sqs_autoscaler_b200 as ksa
+from oracle import policy_py
+from tests import oracle_lib
+from tests.helpers import load_golden
+
+ATOI = load_golden("atoi_vectors.json")
+
+
+def records(texts: list[bytes], width: int) -> np.ndarray:
+    out = np.zeros((len(texts), width), dtype=np.uint8)
+    for i, t in enumerate(texts):
+        t = t[:width]
+        out[i, : len(t)] = np.frombuffer(t, dtype=np.uint8)
+    return out
+
+
+@pytest.mark.parametrize("group", ["reference", "derived"])
+def test_atoi_golden_vectors(group):
+    cases = ATOI[group]
+    texts = [c["text"].encode("utf-8") for c in cases]
+    values, fail = oracle_lib.atoi_records(records(texts, 32))
+    for c, t, v, f in zip(cases, texts, values, fail):
+        assert policy_py.atoi(t) == c["value"], c
+        if c["value"] is None:
+            assert f == 1 and v == 0, c
+        else:
+            assert f == 0 and int(v) == c["value"], c
+
+
+ALPHABET = "0123456789+- _aex."
+
+
+@settings(max_examples=400, deadline=None)
+@given(st.lists(st.one_of(st.text(alphabet=ALPHABET, max_size=22),
+                          st.integers(-(2**64), 2**64).map(str)), min_size=1, max_size=20),
+       st.sampled_from([8, 16, 20, 32]))
+def test_atoi_c_oracle_equals_python_restatement(texts, width):
+    raw = [t.encode("ascii")[:width] for t in texts]
+    values, fail = oracle_lib.atoi_records(records(raw, width))
+    for t, v, f in zip(raw, values, fail):
+        want = policy_py.atoi(t)
+        assert (want is None) == (f == 1), t
+        assert int(v) == (want or 0), t
+
+
+def test_reference_sum_through_the_decoder():
+    """sqs/sqs_test.go:19-25 end to end: "10","10","10" -> Atoi -> sum 30."""
+    v, f = oracle_lib.atoi_records(records([b"10", b"10", b"10"], 16))
+    assert f.sum() == 0 and oracle_lib.num_messages(v) == 30
+
+
+# ---- GPU ------------------------------------------------------------------------------------------
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("width", [16, 32, 20, 7])
+def test_decimal_kernel_matches_oracle(engine, width):
+    import torch
+
+    rng = np.random.default_rng(width)
+    texts = [c["text"].encode("utf-8") for c in ATOI["reference"] + ATOI["derived"]]
+    for _ in range(20000):
+        kind = rng.integers(0, 6)
+        if kind < 3:
+            texts.append(str(int(rng.integers(0, 10 ** int(rng.integers(1, 7))))).encode())
+        elif kind == 3:
+            texts.append(str(int(rng.integers(-(2**63), 2**63 - 1, endpoint=True))).encode())
+        elif kind == 4:
+            texts.append(bytes(rng.choice(np.frombuffer(ALPHABET.encode(), dtype=np.uint8), size=int(rng.integers(0, 12)))))
+        else:
+            texts.append(str(int(rng.integers(2**63 - 5, 2**63 + 5, dtype=np.uint64))).encode())
+    rec = records(texts, width)
+    want_v, want_f = oracle_lib.atoi_records(rec)
+    got_v, got_f = engine.ingest_decimal(torch.from_numpy(rec).to(engine.dev))
+    assert np.array_equal(got_v.cpu().numpy(), want_v)
+    assert np.array_equal(got_f.cpu().numpy(), want_f)
+    assert 0 < want_f.sum() < len(texts)
+    # unaligned base pointer -> byte-load path, same results
+    big = torch.zeros(rec.size + 1, dtype=torch.uint8, device=engine.dev)
+    big[1:] = torch.from_numpy(rec.reshape(-1)).to(engine.dev)
+    got_v2, got_f2 = engine.ingest_decimal(big[1:].view(len(texts), width))
+    assert np.array_equal(got_v2.cpu().numpy(), want_v) and np.array_equal(got_f2.cpu().numpy(), want_f)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int64, np.int32])
+@pytest.mark.parametrize("T,N,A,a", [(64, 64, 1, 0), (1, 1, 1, 0), (130, 67, 3, 1), (1000, 257, 2, 1), (63, 4100, 1, 0)])
+def test_transpose_kernel_matches_numpy(engine, dtype, T, N, A, a):
+    import torch
+
+    rng = np.random.default_rng(T * 7 + N)
+    src_ld = T + (3 if T % 2 else 0)
+    lo, hi = (-(2**63), 2**63 - 1) if dtype == np.int64 else (-(2**31), 2**31 - 1)
+    src = rng.integers(lo, hi, size=(N, src_ld), dtype=dtype, endpoint=True)
+    ld = (N + 15) // 16 * 16
+    out = torch.full((T, A, ld), -12345, dtype=torch.int64, device=engine.dev)
+    engine.ingest_transpose(torch.from_numpy(src).to(engine.dev), T, N, A, a, ld, out=out)
+    got = out.cpu().numpy()
+    assert np.array_equal(got[:, a, :N], src[:, :T].T.astype(np.int64))
+    mask = np.ones((T, A, ld), dtype=bool)
+    mask[:, a, :N] = False
+    assert (got[mask] == -12345).all(), "wrote outside its plane / its N columns"
+
+
+@pytest.mark.gpu
+def test_recorded_strings_to_trajectory(engine):
+    """The whole ingest chain on a small recording: per-queue histories of attribute STRINGS (what
+    SQS returns, sqs/sqs.go:58) -> Atoi decode -> transpose to tick-major -> replay with the parse
+    failures as failed polls; equals the oracle fed the same strings one tick at a time."""
+    import torch
+
+    rng = np.random.default_rng(99)
+    T, N = 200, 150
+    vals = rng.integers(0, 400, size=(N, T))
+    texts = [str(int(v)).encode() for v in vals.reshape(-1)]
+    bad = rng.choice(N * T, size=300, replace=False)
+    for i in bad:
+        texts[i] = [b"", b"n/a", b"12 ", b"1_0", b"9223372036854775808"][int(rng.integers(0, 5))]
+    rec = records(texts, 32)
+    values, fail = engine.ingest_decimal(torch.from_numpy(rec).to(engine.dev))
+    ld = 160
+    depth = engine.ingest_transpose(values.view(N, T), T, N, 1, 0, ld)
+    # the failure mask is trace-major too: transpose it with the same kernel (as int32), then narrow
+    fail_t = engine.ingest_transpose(fail.view(N, T).to(torch.int32), T, N, 1, 0, ld)[:, 0, :].to(torch.uint8).contiguous()
+    pol = ksa.Policy(attr_mask=1)
+    state = engine.new_state(N, seed=3, lo=1, hi=5)
+    replicas, events = engine.replay_full(pol, depth, T, 1, N, ld, 0, state, fail=fail_t)
+    # oracle: decode on the host, per tick
+    hv, hf = oracle_lib.atoi_records(rec)
+    d_host = np.zeros((T, 1, ld), dtype=np.int64)
+    d_host[:, 0, :N] = hv.reshape(N, T).T
+    f_host = np.zeros((T, ld), dtype=np.uint8)
+    f_host[:, :N] = hf.reshape(N, T).T
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, ld, 0, *oracle_lib.fresh_state(3, 0, N, 1, 5), fail=f_host)
+    assert np.array_equal(replicas.cpu().numpy()[:, :N], ref.replicas[:, :N])
+    assert np.array_equal(events.cpu().numpy()[:, :N], ref.events[:, :N])
+    assert (ref.events[:, :N] == 0xC0).sum() == 300

@@ -278,9 +278,59 @@ def run_config6(args):
     print(json.dumps({"config": "2+faults", "workload": f"{N} traces x {T} ticks, default policy, failure mask", **out}), flush=True)
 
 
+def run_config7(args):
+    """Ingest (row f2): trace-major -> tick-major transposition and the strconv.Atoi decode."""
+    eng = ksa.ReplayEngine(0)
+    N, T = args.traces, min(args.ticks, 2000)
+    out = {}
+
+    def best_ms(fn, reps=4):
+        ts = []
+        for rep in range(reps + 2):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            if rep >= 2:
+                ts.append(a.elapsed_time(b))
+        return min(ts)
+
+    dst = torch.empty((T, 1, N), dtype=torch.int64, device=eng.dev)
+    for name, dt, nbytes in (("transpose_int64", torch.int64, 8), ("transpose_int32", torch.int32, 4)):
+        src = torch.randint(0, 400, (N, T), dtype=dt, device=eng.dev)
+        ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst))
+        ok = bool(torch.equal(dst[:, 0, :], src.t().to(torch.int64)))
+        gbs = (nbytes + 8) * N * T / (ms * 1e-3) / 1e9
+        out[name] = {"ms": ms, "elements_per_s": N * T / (ms * 1e-3), "GBps_algorithmic": gbs,
+                     "frac_of_measured_peak": gbs / peak(), "bytes_per_element": nbytes + 8, "parity": "ok" if ok else "MISMATCH"}
+        del src
+    count, width = 1 << 26, 16
+    vals = torch.randint(0, 100000, (count,), dtype=torch.int64, device=eng.dev)
+    # build the records on the device: decimal digits of vals, NUL padded
+    digits = torch.zeros((count, width), dtype=torch.uint8, device=eng.dev)
+    v = vals.clone()
+    ndig = torch.ones_like(vals)
+    for k in range(1, 6):
+        ndig += (vals >= 10**k).to(torch.int64)
+    for pos in range(5, -1, -1):
+        d = (v % 10).to(torch.uint8) + 48
+        idx = ndig - 1 - (5 - pos)
+        sel = idx >= 0
+        digits[torch.nonzero(sel).squeeze(1), idx[sel]] = d[sel]
+        v = v // 10
+    ms = best_ms(lambda: eng.ingest_decimal(digits))
+    got, fl = eng.ingest_decimal(digits)
+    ok = bool(torch.equal(got, vals)) and int(fl.sum()) == 0
+    gbs = (width + 9) * count / (ms * 1e-3) / 1e9
+    out["decimal_w16"] = {"ms": ms, "records_per_s": count / (ms * 1e-3), "GBps_algorithmic": gbs,
+                          "frac_of_measured_peak": gbs / peak(), "bytes_per_record": width + 9, "parity": "ok" if ok else "MISMATCH"}
+    print(json.dumps({"config": "ingest", "workload": f"transpose {N} traces x {T} ticks; Atoi on {count} records of {width} B", **out}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5, 6])
+    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5, 6, 7])
     ap.add_argument("--traces", type=int, default=1 << 20)
     ap.add_argument("--ticks", type=int, default=10_000)
     ap.add_argument("--chunk", type=int, default=2500)
@@ -293,7 +343,7 @@ def main():
     ap.add_argument("--chunks-per-rank", type=int, default=0)
     ap.add_argument("--sweep-tune", action="store_true")
     args = ap.parse_args()
-    {3: run_config3, 4: run_config4, 5: run_config5, 6: run_config6}[args.config](args)
+    {3: run_config3, 4: run_config4, 5: run_config5, 6: run_config6, 7: run_config7}[args.config](args)
 
 
 if __name__ == "__main__":
