@@ -55,26 +55,33 @@ __global__ void __launch_bounds__(256) transpose_kernel(const SRC* __restrict__ 
 //   [+-]?[0-9]+   -> value, ErrRange if it does not fit int64 (|-2^63| allowed for '-')
 //   anything else (spaces, '_', letters, a second sign) -> ErrSyntax
 // The record ends at the first NUL or at `width` bytes.
+// W > 0: compile-time width, fully unrolled so that the record stays in registers (no local-memory
+// array, no divergent early exit: `live` masks the positions after the terminator). W == 0: run-time
+// width, plain loop.
+template <int W>
 __device__ __forceinline__ bool atoi_record(const unsigned char* s, int width, long long* out) {
-  int p = 0;
-  bool neg = false;
-  if (p < width && (s[p] == '+' || s[p] == '-')) neg = s[p++] == '-';
+  const int n = W > 0 ? W : width;
+  const unsigned c0 = s[0];
+  const bool has_sign = (c0 == '+' || c0 == '-');
+  const bool neg = c0 == '-';
   unsigned long long acc = 0;
   int digits = 0;
-  bool overflow = false;
-  for (; p < width; ++p) {
+  bool bad = false, live = true;
+#pragma unroll
+  for (int p = 0; p < (W > 0 ? W : 32); ++p) {
+    if (W == 0 && p >= n) break;
     const unsigned c = s[p];
-    if (c == 0) break;
     const unsigned d = c - '0';
-    if (d > 9u) return false;  // ErrSyntax
-    // acc * 10 + d must stay <= 2^63 (checked against the signed limit below)
-    if (acc > (0x8000000000000000ull - d) / 10ull) overflow = true;
-    acc = acc * 10ull + d;
-    ++digits;
+    const bool skip = (p == 0) && has_sign;
+    live = live && (c != 0);                     // the record ends at the first NUL
+    const bool use = live && !skip;
+    bad = bad || (use && d > 9u);                // ErrSyntax
+    // acc * 10 + d must stay <= 2^63 (the signed limit is checked below): ErrRange otherwise
+    bad = bad || (use && d <= 9u && acc > (0x8000000000000000ull - d) / 10ull);
+    acc = (use && d <= 9u) ? acc * 10ull + d : acc;
+    digits += (use && d <= 9u) ? 1 : 0;
   }
-  if (digits == 0) return false;  // "" or a bare sign
-  // a NUL must be followed by NULs only; trailing garbage after the terminator is not part of the string
-  if (overflow) return false;     // ErrRange
+  if (bad || digits == 0) return false;          // "" or a bare sign is ErrSyntax too
   if (!neg && acc > 0x7fffffffffffffffull) return false;
   *out = neg ? (long long)(0ull - acc) : (long long)acc;
   return true;
@@ -98,7 +105,7 @@ __global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ t
     for (int q = 0; q < width; ++q) rec[q] = (unsigned char)__ldg(text + i * width + q);
   }
   long long v = 0;
-  const bool ok = atoi_record(rec, width, &v);
+  const bool ok = atoi_record<WIDTH_VEC * 16>(rec, width, &v);
   values[i] = ok ? v : 0;
   if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;  // sqs.go:59-61 -> main.go:44-47
 }

@@ -400,6 +400,11 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
     KSA_VARIANT(42, MODE_FULL, 8, 2, HINT_NA, 3, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
     KSA_VARIANT(43, MODE_FULL, 8, 2, HINT_NA, 3, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    // block sizes chosen for wave balance at N = 2^20 (2^17 threads over 148 SMs x 2 blocks):
+    KSA_VARIANT(44, MODE_FULL, 8, 2, HINT_NA, 2, 224, 2, 8, 1, 224, 2, 8, 1, 224, 2),
+    KSA_VARIANT(45, MODE_FULL, 8, 2, HINT_NA, 2, 448, 1, 8, 1, 448, 1, 8, 1, 448, 1),
+    KSA_VARIANT(46, MODE_FULL, 8, 2, HINT_NA, 2, 96, 5, 8, 1, 96, 5, 8, 1, 96, 5),
+    KSA_VARIANT(47, MODE_FULL, 8, 2, HINT_NA, 2, 160, 3, 8, 1, 160, 3, 8, 1, 160, 3),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),

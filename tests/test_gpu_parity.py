@@ -19,7 +19,7 @@ pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2] + list(range(1, 44))   # -2 = scalar kernel
+FULL_VARIANTS = [-2] + list(range(1, 48))   # -2 = scalar kernel
 SUMMARY_VARIANTS = [-2] + list(range(1, 21))
 
 
