@@ -26,7 +26,7 @@ struct SweepArgs {
   ksa_summary* summary;  // [P][N]
 };
 
-template <int A, int R, int D, int BLOCK, int MINB>
+template <int A, int R, int D, int BLOCK, int MINB, int CHAIN>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
@@ -85,10 +85,21 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
         const long long msgs = buf[j];
         if (tt + D < T) buf[j] = load_sum(tt + D);
         const int i = tt + 1;
+        // CHAIN > 0: the R machines run in groups of CHAIN. The first compare of a group is made
+        // to wait for the last event of the previous group through an add that changes nothing
+        // (an event byte is < 256, so ev >> 8 == 0, which ptxas cannot know). Without it ptxas
+        // interleaves all R machines, runs out of its 7 predicate registers and spills them into
+        // a general register (13 LOP3 + 3 P2R per decision at R = 4).
+        long long m_in = msgs;
+        unsigned ev_last = 0u;
 #pragma unroll
         for (int q = 0; q < R; ++q) {
           const ksa_step_consts c(pk[q]);
-          const unsigned ev = ksa_step_fma(c, msgs, i, one, s[q]);
+          if (CHAIN > 0 && q > 0 && q % CHAIN == 0)
+            asm volatile("{\n\t.reg .u32 z;\n\t.reg .u64 zz;\n\tshr.u32 z, %1, 8;\n\t"
+                         "cvt.u64.u32 zz, z;\n\tadd.s64 %0, %0, zz;\n\t}" : "+l"(m_in) : "r"(ev_last));
+          const unsigned ev = ksa_step_fma(c, m_in, i, one, s[q]);
+          ev_last = ev;
           ksa_summary_tick<true>(m[q], s[q].r, ev, ev, one);
         }
       }
@@ -224,9 +235,10 @@ struct SweepVariant {
   int block;
   sweep_fn fn[3];  // indexed by A-1
 };
-#define KSA_SWEEP(R, D, BLOCK, MINB)                                                   \
-  {R, 0, BLOCK, {ksa_sweep_kernel<1, R, D, BLOCK, MINB>, ksa_sweep_kernel<2, R, D, BLOCK, MINB>, \
-                 ksa_sweep_kernel<3, R, D, BLOCK, MINB>}}
+#define KSA_SWEEP_CH(R, D, BLOCK, MINB, CH)                                                        \
+  {R, 0, BLOCK, {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH>, \
+                 ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH>}}
+#define KSA_SWEEP(R, D, BLOCK, MINB) KSA_SWEEP_CH(R, D, BLOCK, MINB, 0)
 #define KSA_SWEEP_LANE(V, D, BLOCK, MINB)                                                        \
   {0, V, BLOCK, {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>, \
                  ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}}
@@ -237,11 +249,14 @@ const SweepVariant kSweepVariants[] = {
     KSA_SWEEP_LANE(1, 4, 128, 10), KSA_SWEEP_LANE(2, 4, 128, 8), KSA_SWEEP_LANE(1, 8, 128, 8),
     KSA_SWEEP_LANE(2, 2, 128, 8),  KSA_SWEEP_LANE(1, 4, 256, 4), KSA_SWEEP_LANE(2, 4, 256, 4),
     KSA_SWEEP_LANE(1, 2, 128, 12), KSA_SWEEP_LANE(1, 4, 64, 16),
+    // 16..: register tile with chained groups
+    KSA_SWEEP_CH(4, 4, 128, 3, 2), KSA_SWEEP_CH(4, 2, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 3, 1),
+    KSA_SWEEP_CH(8, 2, 128, 2, 2), KSA_SWEEP_CH(8, 2, 128, 2, 4), KSA_SWEEP_CH(6, 2, 128, 3, 2), KSA_SWEEP_CH(4, 4, 64, 6, 2),
 };
 constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]));
-constexpr int kDefaultSweep = 0;  // R=4, D=4, 128x3: profiles/r01_config4_sweep_tune.txt (115.6 ms on
-                                  // configs[3]; the lane kernels reach 123 ms at V=2, 158 ms at V=1:
-                                  // their per-tick loop overhead is not shared between machines)
+constexpr int kDefaultSweep = 16;  // R=4 in chained groups of 2, D=4, 128x3: 107.0 ms on configs[3]
+                                   // (unchained 115.6 ms; lane kernels 123 ms at V=2, 158 ms at V=1);
+                                   // profiles/r01_config4_sweep_tune.txt
 
 // Grid of a sweep launch, or false if it does not fit one launch.
 bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
