@@ -39,9 +39,9 @@ struct ReplayArgs {
 // be NULL); MODE_SUMMARY writes nothing per tick.
 enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
 // STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (predication spelled out in PTX), 2 = ksa_step_fma
-// (conditional moves/adds as predicated IMADs on the FMA pipe), 3 = 2 with the policy constants
-// pinned in ordinary registers. Same function, same results. 4 = ksa_step_faults: the step of the
-// *_faults entry points, which also reads one failure-mask byte per decision.
+// (conditional moves/adds as predicated IMADs on the FMA pipe). Same function, same results.
+// 4 = ksa_step_faults (C++), 5 = ksa_step_faults_fma: the steps of the *_faults entry points, which
+// also read one failure-mask byte per decision.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
 
@@ -174,16 +174,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
-  ksa_step_consts c(a.pk);
-  if constexpr (STEP == 3) {
-    // Keep the 32-bit policy constants in ordinary registers: left in uniform registers, every
-    // VIADDMNMX / IMAD that takes two of them pays an extra UR->R move inside the loop.
-    asm volatile("" : "+r"(c.max32), "+r"(c.min32), "+r"(c.up32), "+r"(c.down32), "+r"(c.cu), "+r"(c.cd));
-  }
+  const ksa_step_consts c(a.pk);
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
   constexpr bool FAULTS = (STEP == 4 || STEP == 5);
-  constexpr bool FMA = (STEP == 2 || STEP == 3 || STEP == 5);
+  constexpr bool FMA = (STEP == 2 || STEP == 5);
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -354,80 +349,35 @@ struct Variant {
     KSA_K(3, V3, D3, HINT == HINT_NA_EF && V3 < 4 ? HINT_NA : HINT, MODE, STEP, B3, M3)}}
 
 // Variant 0 is the scalar kernel (any alignment, any N); it also handles the ragged tail of the
-// vector variants. The default is chosen from tools/sweep_variants.py measurements.
+// vector variants. The default is chosen from tools/sweep_variants.py measurements;
+// ids are stable, the gaps are tuning points that were measured, lost and removed
+// (profiles/r01_sweep_variants_a1_T2000.txt still lists them).
 const Variant kFullVariants[] = {
     KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
     KSA_VARIANT(1, MODE_FULL, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
-    KSA_VARIANT(2, MODE_FULL, 4, 4, HINT_NA_EF, 0, 128, 7, 4, 2, 128, 6, 4, 2, 128, 5),
-    KSA_VARIANT(3, MODE_FULL, 4, 2, HINT_NA, 0, 128, 7, 2, 4, 128, 7, 2, 2, 128, 7),
-    KSA_VARIANT(4, MODE_FULL, 4, 8, HINT_NA, 0, 128, 4, 4, 4, 128, 4, 4, 2, 128, 4),
-    KSA_VARIANT(5, MODE_FULL, 2, 4, HINT_NA, 0, 128, 7, 2, 4, 256, 3, 2, 4, 256, 3),
-    KSA_VARIANT(6, MODE_FULL, 2, 8, HINT_NA, 0, 128, 6, 2, 2, 128, 7, 1, 8, 128, 7),
-    KSA_VARIANT(7, MODE_FULL, 2, 6, HINT_NA, 0, 256, 3, 2, 3, 256, 3, 2, 3, 128, 7),
-    KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NC, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
-    KSA_VARIANT(9, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 3, 128, 4),
-    KSA_VARIANT(10, MODE_FULL, 4, 4, HINT_NA, 0, 256, 3, 4, 2, 256, 3, 2, 4, 256, 3),
-    KSA_VARIANT(11, MODE_FULL, 4, 6, HINT_NA, 0, 128, 5, 4, 3, 128, 4, 2, 6, 128, 5),
-    KSA_VARIANT(12, MODE_FULL, 4, 4, HINT_NA, 1, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
-    KSA_VARIANT(13, MODE_FULL, 2, 4, HINT_NA, 1, 128, 7, 2, 4, 256, 3, 2, 4, 256, 3),
     KSA_VARIANT(14, MODE_FULL, 4, 3, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
-    KSA_VARIANT(15, MODE_FULL, 4, 4, HINT_NA_EF, 1, 128, 7, 4, 2, 128, 6, 4, 2, 128, 5),
-    KSA_VARIANT(16, MODE_FULL_OPT, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
-    KSA_VARIANT(17, MODE_FULL, 4, 2, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 2, 128, 8),
-    KSA_VARIANT(18, MODE_FULL, 4, 3, HINT_NA, 0, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(16, MODE_FULL_OPT, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
     KSA_VARIANT(19, MODE_FULL, 4, 3, HINT_NA, 1, 256, 4, 4, 2, 256, 3, 2, 3, 256, 3),
     KSA_VARIANT(20, MODE_FULL, 2, 4, HINT_NA, 1, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(21, MODE_FULL, 2, 6, HINT_NA, 1, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
-    KSA_VARIANT(22, MODE_FULL, 4, 3, HINT_NA_EF, 1, 128, 8, 4, 2, 128, 6, 4, 1, 128, 8),
     KSA_VARIANT(23, MODE_FULL, 8, 2, HINT_NA, 1, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
-    KSA_VARIANT(24, MODE_FULL, 4, 2, HINT_NA, 1, 128, 9, 4, 1, 128, 8, 2, 2, 128, 9),
-    KSA_VARIANT(25, MODE_FULL, 4, 3, HINT_NA, 1, 64, 16, 4, 2, 64, 12, 2, 3, 64, 14),
-    KSA_VARIANT(26, MODE_FULL, 2, 8, HINT_NA, 1, 128, 7, 2, 4, 128, 7, 1, 6, 128, 8),
     KSA_VARIANT(27, MODE_FULL, 1, 8, HINT_NA, 1, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
-    KSA_VARIANT(28, MODE_FULL, 1, 12, HINT_NA, 1, 256, 4, 1, 6, 256, 4, 1, 4, 256, 4),
-    KSA_VARIANT(29, MODE_FULL, 4, 3, HINT_NA, 1, 128, 7, 4, 2, 128, 6, 2, 3, 128, 7),
     KSA_VARIANT(30, MODE_FULL, 8, 2, HINT_NA, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
     KSA_VARIANT(31, MODE_FULL, 8, 3, HINT_NA, 2, 128, 3, 4, 4, 128, 4, 4, 3, 128, 4),
     KSA_VARIANT(32, MODE_FULL, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
-    KSA_VARIANT(33, MODE_FULL, 8, 2, HINT_NA, 2, 64, 8, 4, 3, 64, 10, 4, 2, 64, 10),
     KSA_VARIANT(34, MODE_FULL, 8, 1, HINT_NA, 2, 128, 5, 8, 1, 128, 5, 4, 1, 128, 6),
-    KSA_VARIANT(35, MODE_FULL, 16, 1, HINT_NA, 2, 128, 2, 8, 2, 128, 3, 8, 1, 128, 4),
     KSA_VARIANT(36, MODE_FULL, 16, 2, HINT_NA, 2, 64, 4, 8, 2, 64, 6, 8, 1, 64, 8),
-    KSA_VARIANT(37, MODE_FULL, 4, 3, HINT_NA, 2, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
     KSA_VARIANT(38, MODE_FULL, 8, 2, HINT_NA_EF, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
-    KSA_VARIANT(39, MODE_FULL, 8, 2, HINT_NA, 2, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
-    KSA_VARIANT(40, MODE_FULL, 8, 2, HINT_NA, 1, 128, 5, 4, 3, 128, 6, 4, 2, 128, 6),
     KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
-    KSA_VARIANT(42, MODE_FULL, 8, 2, HINT_NA, 3, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
-    KSA_VARIANT(43, MODE_FULL, 8, 2, HINT_NA, 3, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
-    // block sizes chosen for wave balance at N = 2^20 (2^17 threads over 148 SMs x 2 blocks):
-    KSA_VARIANT(44, MODE_FULL, 8, 2, HINT_NA, 2, 224, 2, 8, 1, 224, 2, 8, 1, 224, 2),
-    KSA_VARIANT(45, MODE_FULL, 8, 2, HINT_NA, 2, 448, 1, 8, 1, 448, 1, 8, 1, 448, 1),
-    KSA_VARIANT(46, MODE_FULL, 8, 2, HINT_NA, 2, 96, 5, 8, 1, 96, 5, 8, 1, 96, 5),
-    KSA_VARIANT(47, MODE_FULL, 8, 2, HINT_NA, 2, 160, 3, 8, 1, 160, 3, 8, 1, 160, 3),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
-    KSA_VARIANT(1, MODE_SUMMARY, 2, 8, HINT_NA, 0, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
-    KSA_VARIANT(2, MODE_SUMMARY, 4, 4, HINT_NA, 0, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
-    KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 0, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
-    KSA_VARIANT(4, MODE_SUMMARY, 4, 4, HINT_NA_EF, 0, 128, 4, 4, 2, 128, 3, 4, 2, 128, 3),
     KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
-    KSA_VARIANT(6, MODE_SUMMARY, 1, 8, HINT_NA, 0, 256, 4, 1, 4, 256, 4, 1, 4, 256, 4),
     KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
     KSA_VARIANT(8, MODE_SUMMARY, 2, 8, HINT_NA, 2, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
     KSA_VARIANT(9, MODE_SUMMARY, 4, 4, HINT_NA, 2, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
     KSA_VARIANT(10, MODE_SUMMARY, 8, 2, HINT_NA, 2, 128, 3, 4, 3, 128, 3, 4, 2, 128, 3),
-    KSA_VARIANT(11, MODE_SUMMARY, 4, 4, HINT_NA, 1, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
     KSA_VARIANT(12, MODE_SUMMARY, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
-    KSA_VARIANT(13, MODE_SUMMARY, 4, 3, HINT_NA, 2, 128, 6, 4, 2, 128, 5, 4, 1, 128, 6),
-    KSA_VARIANT(14, MODE_SUMMARY, 2, 4, HINT_NA, 3, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
-    KSA_VARIANT(15, MODE_SUMMARY, 2, 4, HINT_NA, 3, 128, 7, 2, 3, 128, 7, 2, 2, 128, 7),
-    KSA_VARIANT(16, MODE_SUMMARY, 2, 3, HINT_NA, 3, 256, 4, 2, 2, 256, 4, 2, 2, 256, 4),
-    KSA_VARIANT(17, MODE_SUMMARY, 4, 2, HINT_NA, 3, 128, 6, 4, 2, 128, 5, 4, 1, 128, 6),
-    KSA_VARIANT(18, MODE_SUMMARY, 2, 2, HINT_NA, 3, 128, 8, 2, 2, 128, 8, 2, 2, 128, 8),
-    KSA_VARIANT(19, MODE_SUMMARY, 1, 4, HINT_NA, 3, 128, 12, 1, 4, 128, 10, 1, 3, 128, 10),
-    KSA_VARIANT(20, MODE_SUMMARY, 2, 4, HINT_NA, 2, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
 };
 // The *_faults entry points: one vector kernel + the scalar kernel per mode (STEP 4).
 const Variant kFullFaultsVariants[] = {

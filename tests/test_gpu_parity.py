@@ -19,8 +19,8 @@ pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2] + list(range(1, 48))   # -2 = scalar kernel
-SUMMARY_VARIANTS = [-2] + list(range(1, 21))
+FULL_VARIANTS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41]   # -2 = scalar kernel
+SUMMARY_VARIANTS = [-2, 5, 7, 8, 9, 10, 12]
 
 
 def torch_mod():

@@ -69,11 +69,7 @@ def main():
             return []
         if spec != "all":
             return [int(x) for x in spec.split(",")]
-        out, i = [-2], 1
-        while eng.variant_name(mode, i):
-            out.append(i)
-            i += 1
-        return out
+        return [-2] + [i for i in range(1, 64) if eng.variant_name(mode, i)]
 
     print(f"# N={N} T={T} A={A} peak={peak} GB/s (measured copy)")
     bpd_full, bpd_sum = 8 * A + 5, 8 * A
