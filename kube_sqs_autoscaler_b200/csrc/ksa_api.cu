@@ -151,6 +151,20 @@ extern "C" int64_t ksa_launch_count(void) {
 
 // ---- host-buffer pipeline -----------------------------------------------------------------------
 
+namespace {
+// The pipeline calls work on the pipeline's device and hand the caller's current device back.
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != device) cudaSetDevice(device);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+}  // namespace
+
 struct ksa_pipeline {
   int device;
   int64_t N, ld, chunk;
@@ -213,7 +227,8 @@ extern "C" int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, in
   p->ld = (N + 15) / 16 * 16;  // padded pitch so the vector kernels apply to any N
   p->chunk = chunk_ticks;
   p->A = A;
-  KSA_PIPE_CUDA(cudaSetDevice(device));
+  DeviceGuard guard(device);
+  KSA_PIPE_CUDA(cudaGetLastError());
   KSA_PIPE_CUDA(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
   KSA_PIPE_CUDA(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
   KSA_PIPE_CUDA(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
@@ -236,7 +251,7 @@ extern "C" int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, in
 
 extern "C" int ksa_pipeline_destroy(ksa_pipeline* p) {
   if (!p) return KSA_OK;
-  cudaSetDevice(p->device);
+  DeviceGuard guard(p->device);
   cudaDeviceSynchronize();
   pipeline_free(p);
   return KSA_OK;
@@ -269,7 +284,7 @@ extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,
   ksa_policy_k probe;
   int rc = ksa_policy_to_k(policy, p->A, &probe);  // validate before touching the device
   if (rc != KSA_OK) return rc;
-  KSA_CUDA(cudaSetDevice(p->device));
+  DeviceGuard guard(p->device);
   const int64_t ld = p->ld;
   const int32_t A = p->A;
   const bool want_full = replicas_host || events_host;

@@ -3,7 +3,8 @@
 // flags of main.go:83-97 with the same names, defaults and Go duration syntax, so a command line
 // written for kube-sqs-autoscaler parses unchanged (the flags that only configure the AWS and
 // Kubernetes clients are accepted and ignored). Instead of polling one queue forever it replays
-// the policy over --traces synthetic queue-depth traces x --ticks polls on one GPU and prints
+// the policy over --traces synthetic queue-depth traces x --ticks polls, sharded over --gpus GPUs
+// (one host thread per GPU, no collective, host-side gather of the per-trace summaries), and prints
 // what the autoscaler would have done.
 //
 // Links only libksareplay.so: all CUDA calls happen behind the ABI.
@@ -17,6 +18,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ksa_replay.h"
@@ -98,7 +100,8 @@ struct Options {
   int64_t traces = 1 << 20, ticks = 1000;
   uint64_t seed = 0x5EED0001;
   std::string mode = "summary";
-  int device = 0;
+  int device = 0;  // first device
+  int gpus = 1;    // devices device .. device+gpus-1, one host thread each
 };
 
 Options parse(int argc, char** argv) {
@@ -152,10 +155,11 @@ Options parse(int argc, char** argv) {
     else if (k == "seed") o.seed = (uint64_t)as_int("seed");
     else if (k == "mode") o.mode = v;
     else if (k == "device") o.device = (int)as_int("device");
+    else if (k == "gpus") o.gpus = (int)as_int("gpus");
     else if (k == "help" || k == "h") {
       std::puts("usage: ksa-replay [reference flags: --poll-period --scale-up-cool-down --scale-down-cool-down\n"
                 "  --scale-up-messages --scale-down-messages --scale-up-pods --scale-down-pods --max-pods --min-pods\n"
-                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D]");
+                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D] [--gpus G]");
       std::exit(0);
     } else {
       die("flag provided but not defined: -" + k);
@@ -165,43 +169,35 @@ Options parse(int argc, char** argv) {
   return o;
 }
 
-}  // namespace
-
-int main(int argc, char** argv) {
-  Options o = parse(argc, argv);
+// One GPU's share of the job: traces [begin, end) in N-chunks of at most 2^20 traces (so that a
+// chunk's depth array fits next to its outputs whatever --traces is), each chunk in T-chunks with
+// the carry state. Summaries land in `host` at their global trace ids; returns seconds spent in
+// replay kernels on this device.
+double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::vector<ksa_summary>* host) {
+  check(ksa_set_device(device), "ksa_set_device");
   const int A = __builtin_popcount(o.policy.attr_mask);
-  const int64_t N = o.traces, T = o.ticks, ld = (N + 15) / 16 * 16;
-  check(ksa_set_device(o.device), "ksa_set_device");
-  int64_t cu = 0, cd = 0;
-  check(ksa_policy_cool_ticks(&o.policy, &cu, &cd), "ksa_policy_cool_ticks");
-
-  void *depth = nullptr, *r = nullptr, *ju = nullptr, *jd = nullptr, *summ = nullptr, *rep = nullptr, *evs = nullptr;
+  const int64_t T = o.ticks, NC = std::min<int64_t>(end - begin, 1 << 20), ld = (NC + 15) / 16 * 16;
   const bool full = o.mode == "full";
   const int64_t chunk = std::min<int64_t>(T, std::max<int64_t>(1, (int64_t)((full ? 48.0e9 : 64.0e9) / ((8.0 * A + (full ? 5 : 0)) * ld))));
+  void *depth = nullptr, *r = nullptr, *ju = nullptr, *jd = nullptr, *summ = nullptr, *rep = nullptr, *evs = nullptr;
+  void *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr;
   check(ksa_dev_alloc(&depth, (size_t)chunk * A * ld * 8), "depth");
   check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
   check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
   check(ksa_dev_alloc(&jd, (size_t)ld * 8), "state");
   check(ksa_dev_alloc(&summ, (size_t)ld * sizeof(ksa_summary)), "summary");
-  if (full) {
-    check(ksa_dev_alloc(&rep, (size_t)chunk * ld * 4), "replicas");
-    check(ksa_dev_alloc(&evs, (size_t)chunk * ld), "events");
-  }
   ksa_state st = {(int32_t*)r, (int64_t*)ju, (int64_t*)jd};
   ksa_state st_sum = st;
-  void *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr;
-  if (full) {  // the summary pass needs its own copy of the carry state
+  if (full) {  // per-tick outputs, and a second copy of the carry state for the summary pass
+    check(ksa_dev_alloc(&rep, (size_t)chunk * ld * 4), "replicas");
+    check(ksa_dev_alloc(&evs, (size_t)chunk * ld), "events");
     check(ksa_dev_alloc(&r2, (size_t)ld * 4), "state");
     check(ksa_dev_alloc(&ju2, (size_t)ld * 8), "state");
     check(ksa_dev_alloc(&jd2, (size_t)ld * 8), "state");
     st_sum = {(int32_t*)r2, (int64_t*)ju2, (int64_t*)jd2};
-    check(ksa_state_init(o.seed, 0, N, (int32_t)o.policy.min_pods, (int32_t)o.policy.max_pods >= (int32_t)o.policy.min_pods ? (int32_t)o.policy.max_pods : (int32_t)o.policy.min_pods, &st_sum, nullptr), "ksa_state_init");
   }
   const int32_t lo = (int32_t)o.policy.min_pods;
   const int32_t hi = (int32_t)o.policy.max_pods >= lo ? (int32_t)o.policy.max_pods : lo;
-  check(ksa_state_init(o.seed, 0, N, lo, hi, &st, nullptr), "ksa_state_init");
-  check(ksa_summary_clear((ksa_summary*)summ, N, nullptr), "ksa_summary_clear");
-
   ksa_gen_params g;
   std::memset(&g, 0, sizeof(g));
   g.seed = o.seed;
@@ -210,20 +206,58 @@ int main(int argc, char** argv) {
   g.high_min = o.policy.scale_up_messages > g.low_max ? o.policy.scale_up_messages : g.low_max + 1;
   g.high_max = 4 * g.high_min;
   double replay_s = 0;
-  for (int64_t t0 = 0; t0 < T; t0 += chunk) {
-    const int64_t tc = std::min(chunk, T - t0);
-    check(ksa_gen_traces(&g, t0, tc, A, 0, N, ld, (int64_t*)depth, nullptr, nullptr), "ksa_gen_traces");
+  for (int64_t c0 = begin; c0 < end; c0 += NC) {
+    const int64_t n = std::min(NC, end - c0);
+    check(ksa_state_init(o.seed, c0, n, lo, hi, &st, nullptr), "ksa_state_init");
+    if (full) check(ksa_state_init(o.seed, c0, n, lo, hi, &st_sum, nullptr), "ksa_state_init");
+    check(ksa_summary_clear((ksa_summary*)summ, n, nullptr), "ksa_summary_clear");
+    for (int64_t t0 = 0; t0 < T; t0 += chunk) {
+      const int64_t tc = std::min(chunk, T - t0);
+      check(ksa_gen_traces(&g, t0, tc, A, c0, n, ld, (int64_t*)depth, nullptr, nullptr), "ksa_gen_traces");
+      check(ksa_stream_sync(nullptr), "sync");
+      const auto a = std::chrono::steady_clock::now();
+      if (full) check(ksa_replay_full(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
+      else check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+      check(ksa_stream_sync(nullptr), "sync");
+      replay_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+      if (full) check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+    }
+    // host gather: this chunk's summaries at their global trace ids
+    check(ksa_memcpy_d2h(host->data() + c0, summ, (size_t)n * sizeof(ksa_summary), nullptr), "d2h");
     check(ksa_stream_sync(nullptr), "sync");
-    const auto a = std::chrono::steady_clock::now();
-    if (full) check(ksa_replay_full(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
-    else check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
-    check(ksa_stream_sync(nullptr), "sync");
-    replay_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
-    if (full) check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, N, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
   }
+  for (void* p : {depth, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
+    if (p) ksa_dev_free(p);
+  return replay_s;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options o = parse(argc, argv);
+  const int A = __builtin_popcount(o.policy.attr_mask);
+  const int64_t N = o.traces, T = o.ticks;
+  int64_t cu = 0, cd = 0;
+  check(ksa_policy_cool_ticks(&o.policy, &cu, &cd), "ksa_policy_cool_ticks");
+  const int have = ksa_device_count();
+  if (have < 0) die(std::string("ksa_device_count: ") + ksa_last_error());
+  if (o.gpus < 1 || o.device + o.gpus > have)
+    die("--gpus " + std::to_string(o.gpus) + " from --device " + std::to_string(o.device) + ": only " + std::to_string(have) + " CUDA devices");
+
+  // Traces are independent: contiguous shards, one host thread per GPU, no collective; the only
+  // cross-GPU step is the host-side gather of the per-trace summaries.
   std::vector<ksa_summary> host((size_t)N);
-  check(ksa_memcpy_d2h(host.data(), summ, (size_t)N * sizeof(ksa_summary), nullptr), "d2h");
-  check(ksa_stream_sync(nullptr), "sync");
+  std::vector<double> secs((size_t)o.gpus, 0.0);
+  std::vector<std::thread> workers;
+  for (int g = 0; g < o.gpus; ++g) {
+    const int64_t base = N / o.gpus, extra = N % o.gpus;
+    const int64_t begin = g * base + std::min<int64_t>(g, extra);
+    const int64_t end = begin + base + (g < extra ? 1 : 0);
+    workers.emplace_back([&, g, begin, end] { if (end > begin) secs[(size_t)g] = run_shard(o, o.device + g, begin, end, &host); });
+  }
+  for (auto& w : workers) w.join();
+  const double replay_s = *std::max_element(secs.begin(), secs.end());
+
   uint64_t tot[6] = {0, 0, 0, 0, 0, 0}, digest = 0;
   long double replica_ticks = 0;
   for (const ksa_summary& s : host) {
@@ -236,14 +270,12 @@ int main(int argc, char** argv) {
               "] cool-down ticks up %" PRId64 " down %" PRId64 " attributes %d\n",
               o.policy.scale_up_messages, o.policy.scale_down_messages, o.policy.scale_up_pods, o.policy.scale_down_pods,
               o.policy.min_pods, o.policy.max_pods, cu, cd, A);
-  std::printf("replayed %" PRId64 " traces x %" PRId64 " ticks (%s mode) in %.3f ms of kernel wall time: %.3e decisions/s\n",
-              N, T, o.mode.c_str(), replay_s * 1e3, (double)N * (double)T / replay_s);
+  std::printf("replayed %" PRId64 " traces x %" PRId64 " ticks (%s mode) on %d GPU(s) in %.3f ms of kernel wall time (slowest GPU): %.3e decisions/s\n",
+              N, T, o.mode.c_str(), o.gpus, replay_s * 1e3, (double)N * (double)T / replay_s);
   std::printf("scale up successful %" PRIu64 " | scale down successful %" PRIu64 " | at max %" PRIu64 " | at min %" PRIu64
               " | up cool-down skips %" PRIu64 " | down cool-down skips %" PRIu64 "\n",
               tot[0], tot[1], tot[2], tot[3], tot[4], tot[5]);
   std::printf("mean replicas %.4Lf | xor of trajectory fingerprints %016" PRIx64 "\n",
               replica_ticks / ((long double)N * (long double)T), digest);
-  for (void* p : {depth, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
-    if (p) ksa_dev_free(p);
   return 0;
 }

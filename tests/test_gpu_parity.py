@@ -547,3 +547,26 @@ def test_cli_totals_match_the_python_host(engine, mode):
     want = [int(ref.summary[k].sum()) for k in ("up_applied", "down_applied", "up_noop", "down_noop", "up_cool", "down_cool")]
     assert got == want
     assert digest == int(np.bitwise_xor.reduce(ref.summary["hash"]))
+    assert "on 1 GPU(s)" in r.stdout
+
+
+def test_cli_shards_over_gpus_without_changing_results(engine):
+    """--gpus G: one host thread per GPU, contiguous trace shards, host gather. The totals and the
+    fingerprint digest do not depend on G (global trace ids in the generator)."""
+    import os
+    import re
+    import subprocess
+
+    import torch
+
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    args = ["--traces", "70001", "--ticks", "200", "--seed", "9", "--attribute-names=ApproximateNumberOfMessages"]
+    outs = []
+    for g in sorted({1, min(2, torch.cuda.device_count()), torch.cuda.device_count()}):
+        r = subprocess.run([cli, *args, "--gpus", str(g)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        outs.append((re.search(r"scale up successful.*", r.stdout).group(0),
+                     re.search(r"fingerprints ([0-9a-f]{16})", r.stdout).group(1)))
+    assert all(o == outs[0] for o in outs), outs
+    r = subprocess.run([cli, *args, "--gpus", str(torch.cuda.device_count() + 1)], capture_output=True, text=True)
+    assert r.returncode == 2 and "CUDA devices" in r.stderr

@@ -128,4 +128,4 @@ def test_cli_keeps_the_reference_flag_surface(built):
         r = subprocess.run([cli, "-poll-period", "10s", "--kubernetes-deployment=x", "--sqs-queue-url=y",
                             "--aws-region=us-west-2", "--traces", "64", "--ticks", "8"],
                            capture_output=True, text=True)
-        assert r.returncode == 2 and "ksa_set_device" in r.stderr  # flags parsed, then no GPU
+        assert r.returncode == 2 and "ksa_device_count" in r.stderr  # flags parsed, then no GPU
