@@ -87,6 +87,30 @@ __device__ __forceinline__ bool atoi_record(const unsigned char* s, int width, l
   return true;
 }
 
+// Fast path for records of at most 8 characters (sign included), i.e. every realistic queue depth:
+// the 8 bytes are handled as one 64-bit word (SWAR). `x` holds the string little-endian (first
+// character in the low byte), NUL padded. Returns false when the slow path must decide (a '+'/'-'
+// sign, a non-digit, or an empty record); true with the value otherwise.
+__device__ __forceinline__ bool atoi_swar8(unsigned long long x, long long* out) {
+  // length = index of the first NUL byte (8 if none)
+  const unsigned long long nul = (x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull;
+  const int len = nul ? (__ffsll((long long)nul) - 1) >> 3 : 8;
+  if (len == 0) return false;
+  // right-align: the string occupies the top `len` bytes, the low bytes become '0'
+  const int sh = 8 * (8 - len);
+  const unsigned long long xs = len == 8 ? x : ((x << sh) | (0x3030303030303030ull >> (8 * len)));
+  // '0'..'9' -> 0..9; every other byte value maps to >= 10 under the XOR
+  const unsigned long long d = xs ^ 0x3030303030303030ull;
+  if (((d + 0x7676767676767676ull) | d) & 0x8080808080808080ull) return false;  // a non-digit (or sign)
+  // 8 digits -> number: pairs, then 4-digit groups, then the two halves (most significant digit is
+  // in the low byte)
+  unsigned long long t = (d * 10ull + (d >> 8)) & 0x00FF00FF00FF00FFull;
+  t = (t * 100ull + (t >> 16)) & 0x0000FFFF0000FFFFull;
+  t = (t * 10000ull + (t >> 32)) & 0x00000000FFFFFFFFull;
+  *out = (long long)t;
+  return true;
+}
+
 template <int WIDTH_VEC>  // WIDTH_VEC = width / 16 when the records can be fetched as uint4, else 0
 __global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ text, int width,
                                                       long long count, long long* __restrict__ values,
@@ -94,18 +118,30 @@ __global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ t
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= count) return;
   unsigned char rec[32];
+  long long v = 0;
+  bool ok;
   if constexpr (WIDTH_VEC > 0) {
     const uint4* p = reinterpret_cast<const uint4*>(text + i * width);
+    uint4 w[WIDTH_VEC];
 #pragma unroll
-    for (int q = 0; q < WIDTH_VEC; ++q) {
-      const uint4 w = __ldg(p + q);
-      reinterpret_cast<uint4*>(rec)[q] = w;
+    for (int q = 0; q < WIDTH_VEC; ++q) w[q] = __ldg(p + q);
+    unsigned rest = w[0].z | w[0].w;
+#pragma unroll
+    for (int q = 1; q < WIDTH_VEC; ++q) rest |= w[q].x | w[q].y | w[q].z | w[q].w;
+    const unsigned long long x0 = (unsigned long long)w[0].x | ((unsigned long long)w[0].y << 32);
+    // bytes 8.. all NUL and the first 8 are plain digits: done; anything else takes the exact
+    // character-by-character path below (rare: signs, long numbers, malformed strings)
+    if (rest == 0u && atoi_swar8(x0, &v)) {
+      ok = true;
+    } else {
+#pragma unroll
+      for (int q = 0; q < WIDTH_VEC; ++q) reinterpret_cast<uint4*>(rec)[q] = w[q];
+      ok = atoi_record<WIDTH_VEC * 16>(rec, width, &v);
     }
   } else {
     for (int q = 0; q < width; ++q) rec[q] = (unsigned char)__ldg(text + i * width + q);
+    ok = atoi_record<0>(rec, width, &v);
   }
-  long long v = 0;
-  const bool ok = atoi_record<WIDTH_VEC * 16>(rec, width, &v);
   values[i] = ok ? v : 0;
   if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;  // sqs.go:59-61 -> main.go:44-47
 }
