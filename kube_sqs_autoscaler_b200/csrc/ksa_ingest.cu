@@ -4,51 +4,88 @@
 // reference performs per attribute (sqs/sqs.go:58). Both are HBM-bound byte movers.
 #include "ksa_internal.h"
 
+#include <cstdlib>
+
 namespace {
 
-constexpr int kTile = 64;   // 64 ticks x 64 traces per block
-constexpr int kPitch = 65;  // odd pitch (in 8-byte words): column reads hit distinct banks
-
-// Tiled transpose + widen. Block = 256 threads = 8 warps. Load phase: warp w reads trace rows
-// w, w+8, ... of the tile, 32 consecutive ticks per instruction (256 B for int64 sources). Store
-// phase: warp w writes tick rows w, w+8, ..., 32 consecutive traces per instruction (256 B).
-// Every global access is a run of full 32-byte sectors; each element is read once, written once.
-template <typename SRC>
-__global__ void __launch_bounds__(256) transpose_kernel(const SRC* __restrict__ src, long long src_ld,
-                                                        long long T, long long N, int A, int a,
-                                                        long long ld, long long* __restrict__ dst) {
-  __shared__ long long tile[kTile][kPitch];
-  const long long t0 = (long long)blockIdx.x * kTile;
-  const long long n0 = (long long)blockIdx.y * kTile;
+// Tiled transpose + widen. A block moves a tile of TT ticks x TN traces through shared memory.
+// Load phase: each warp reads trace rows of the tile, 32 consecutive ticks per instruction (256 B for
+// int64 sources), TT * 8 contiguous bytes per row. Store phase: each warp writes tick rows, 32
+// consecutive traces per instruction, TN * 8 contiguous bytes per row. Every global access is a run
+// of full 32-byte sectors; each element is read once and written once. The pitch TT + 1 (in 8-byte
+// words, odd) makes the column reads of the store phase hit distinct banks.
+// The tile shape trades DRAM row locality between the two sides: the kernel is latency/DRAM-page
+// bound, not instruction bound (profiles/r01_ncu_transpose.txt), so longer contiguous runs help.
+template <typename SRC, int TT, int TN, int THREADS>
+__global__ void __launch_bounds__(THREADS) transpose_kernel(const SRC* __restrict__ src, long long src_ld,
+                                                            long long T, long long N, int A, int a,
+                                                            long long ld, long long* __restrict__ dst) {
+  extern __shared__ long long tile[];  // [TN][TT + 1]
+  constexpr int PITCH = TT + 1;
+  constexpr int WARPS = THREADS / 32;
+  const long long t0 = (long long)blockIdx.x * TT;
+  const long long n0 = (long long)blockIdx.y * TN;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int k = 0; k < kTile / 8; ++k) {
-    const int nl = warp + 8 * k;
+  for (int k = 0; k < TN / WARPS; ++k) {
+    const int nl = warp + WARPS * k;
     const long long n = n0 + nl;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
+    for (int h = 0; h < TT / 32; ++h) {
       const int tl = lane + 32 * h;
       const long long t = t0 + tl;
       long long v = 0;
       if (n < N && t < T) v = (long long)__ldg(src + n * src_ld + t);
-      tile[nl][tl] = v;
+      tile[nl * PITCH + tl] = v;
     }
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < kTile / 8; ++k) {
-    const int tl = warp + 8 * k;
+  for (int k = 0; k < TT / WARPS; ++k) {
+    const int tl = warp + WARPS * k;
     const long long t = t0 + tl;
     if (t >= T) continue;
     long long* row = dst + (t * A + a) * ld;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
+    for (int h = 0; h < TN / 32; ++h) {
       const int nl = lane + 32 * h;
       const long long n = n0 + nl;
-      if (n < N) __stcs(row + n, tile[nl][tl]);
+      if (n < N) __stcs(row + n, tile[nl * PITCH + tl]);
     }
   }
 }
+
+template <typename SRC, int TT, int TN, int THREADS>
+int launch_transpose(const void* src, long long src_ld, long long T, long long N, int A, int a, long long ld,
+                     long long* dst, cudaStream_t st) {
+  const long long gx = (T + TT - 1) / TT, gy = (N + TN - 1) / TN;
+  if (gx > 0x7fffffffll || gy > 65535)
+    return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max %d traces)", N, 65535 * TN);
+  constexpr size_t smem = sizeof(long long) * (size_t)TN * (TT + 1);
+  auto kernel = transpose_kernel<SRC, TT, TN, THREADS>;
+  if (smem > 48 * 1024) KSA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kernel<<<dim3((unsigned)gx, (unsigned)gy), THREADS, smem, st>>>((const SRC*)src, src_ld, T, N, A, a, ld, dst);
+  KSA_LAUNCH_CHECK("transpose_kernel");
+  return KSA_OK;
+}
+
+template <typename SRC>
+int dispatch_transpose(int shape, const void* src, long long src_ld, long long T, long long N, int A, int a,
+                       long long ld, long long* dst, cudaStream_t st) {
+  switch (shape) {
+    case 1: return launch_transpose<SRC, 128, 64, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 2: return launch_transpose<SRC, 256, 32, 256>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 3: return launch_transpose<SRC, 128, 128, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 4: return launch_transpose<SRC, 64, 128, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 5: return launch_transpose<SRC, 128, 32, 256>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 6: return launch_transpose<SRC, 512, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 7: return launch_transpose<SRC, 256, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 8: return launch_transpose<SRC, 512, 32, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 9: return launch_transpose<SRC, 256, 64, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    default: return launch_transpose<SRC, 64, 64, 256>(src, src_ld, T, N, A, a, ld, dst, st);
+  }
+}
+constexpr int kDefaultTransposeShape = 7;  // 256 ticks x 32 traces, 512 threads: profiles/r01_ingest_tune.txt
 
 // strconv.Atoi on one fixed-width record. Go 1.15 semantics for base 10, 64-bit int:
 //   ""            -> ErrSyntax          "+" / "-"    -> ErrSyntax
@@ -156,18 +193,12 @@ extern "C" int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int6
   if (A < 1 || A > KSA_MAX_ATTRS || a < 0 || a >= A) return ksa_fail(KSA_EINVAL, "bad plane a=%d of A=%d", a, A);
   if (T < 0 || N < 0 || src_ld < T || ld < N) return ksa_fail(KSA_EINVAL, "bad T/N/src_ld/ld");
   if (T == 0 || N == 0) return KSA_OK;
-  const long long gx = (T + kTile - 1) / kTile, gy = (N + kTile - 1) / kTile;
-  if (gx > 0x7fffffffll || gy > 65535) return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max 65535*64 traces)", (long long)N);
-  dim3 grid((unsigned)gx, (unsigned)gy);
+  int shape = kDefaultTransposeShape;
+  if (const char* e = std::getenv("KSA_TRANSPOSE_SHAPE")) shape = std::atoi(e);  // tuning knob (tools/)
   cudaStream_t st = (cudaStream_t)stream;
-  if (src_bytes == 8)
-    transpose_kernel<long long><<<grid, 256, 0, st>>>((const long long*)src_dev, src_ld, T, N, A, a, ld,
-                                                       (long long*)depth_dev);
-  else
-    transpose_kernel<int><<<grid, 256, 0, st>>>((const int*)src_dev, src_ld, T, N, A, a, ld,
-                                                 (long long*)depth_dev);
-  KSA_LAUNCH_CHECK("transpose_kernel");
-  return KSA_OK;
+  return src_bytes == 8
+             ? dispatch_transpose<long long>(shape, src_dev, src_ld, T, N, A, a, ld, (long long*)depth_dev, st)
+             : dispatch_transpose<int>(shape, src_dev, src_ld, T, N, A, a, ld, (long long*)depth_dev, st);
 }
 
 extern "C" int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t count, int64_t* values_dev,

@@ -297,6 +297,15 @@ def run_config7(args):
         return min(ts)
 
     dst = torch.empty((T, 1, N), dtype=torch.int64, device=eng.dev)
+    if args.sweep_tune:
+        src = torch.randint(0, 400, (N, T), dtype=torch.int64, device=eng.dev)
+        for shape in range(10):
+            os.environ["KSA_TRANSPOSE_SHAPE"] = str(shape)
+            ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst), reps=2)
+            print(f"# transpose shape {shape}: {ms:.3f} ms {16 * N * T / (ms * 1e-3) / 1e9:.1f} GB/s "
+                  f"ok={bool(torch.equal(dst[:, 0, :], src.t()))}", flush=True)
+        os.environ.pop("KSA_TRANSPOSE_SHAPE", None)
+        del src
     for name, dt, nbytes in (("transpose_int64", torch.int64, 8), ("transpose_int32", torch.int32, 4)):
         src = torch.randint(0, 400, (N, T), dtype=dt, device=eng.dev)
         ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst))
