@@ -286,6 +286,33 @@ int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P, const int64_t
                             const int32_t* replicas0_dev, ksa_summary* summary_dev, void* stream);
 
 /*
+ * Sweep reduction: score the P x N summaries of a sweep and pick policies. EXTENSION: the reference
+ * has no cost model (it only has the tunables, main.go:83-91); the cost below is a plain linear
+ * form over what the summaries count, in wrapping int64:
+ *   cost(p, n) = w_pod_ticks * sum_replicas            (capacity paid for: pods x ticks)
+ *              + w_saturated * up_noop                 (ticks over the up threshold while at max)
+ *              + w_churn     * (up_applied + down_applied)
+ *              + w_blocked   * (up_cool + down_cool)   (ticks a wanted scale was held by a cool-down)
+ * Outputs (any may be NULL):
+ *   policy_cost_dev [P] int64   sum over the N traces of cost(p, n); ACCUMULATED into, so that
+ *                               trace shards (chunks, GPUs) add up: zero it before the first call
+ *   best_policy_dev [N] int32   argmin over p of cost(p, n), lowest p on ties
+ *   best_cost_dev   [N] int64   that minimum
+ * One pass over the summaries (64 B per (policy, trace), HBM-bound). With traces sharded over GPUs
+ * the per-policy totals are the one quantity that needs a cross-GPU step: an all-reduce (sum) of
+ * the [P] vector, done by the host (kube_sqs_autoscaler_b200.shard.allreduce_policy_costs).
+ */
+typedef struct ksa_cost {
+  int64_t w_pod_ticks;
+  int64_t w_saturated;
+  int64_t w_churn;
+  int64_t w_blocked;
+} ksa_cost;
+int ksa_sweep_reduce(const ksa_summary* summary_dev, int32_t P, int64_t N, const ksa_cost* cost,
+                     int64_t* policy_cost_dev, int32_t* best_policy_dev, int64_t* best_cost_dev,
+                     void* stream);
+
+/*
  * Fingerprint an existing full trajectory: hash_dev[n] = the ksa_summary.hash the summary replay
  * would produce for trace n over the same T ticks (h0 = hash_dev[n] on entry when chain != 0, else
  * 0). Used to compare 100+ GB trajectories without moving them to the host.

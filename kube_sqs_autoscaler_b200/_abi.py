@@ -85,6 +85,13 @@ POLICY_K_BYTES = 48  # sizeof(ksa_policy_k): the kernel-side policy record (csrc
 SWEEP_STATIC_MAX_POLICIES = 4096  # KSA_SWEEP_STATIC_MAX_POLICIES
 
 
+class KsaCost(C.Structure):
+    """struct ksa_cost: weights of ksa_sweep_reduce (an extension; the reference has no cost model)."""
+
+    _fields_ = [("w_pod_ticks", C.c_int64), ("w_saturated", C.c_int64), ("w_churn", C.c_int64),
+                ("w_blocked", C.c_int64)]
+
+
 class KsaGenParams(C.Structure):
     _fields_ = [
         ("seed", C.c_uint64),
@@ -139,6 +146,7 @@ SIGNATURES = {
                                    _vp, _vp]),
     "ksa_replay_sweep_static": (C.c_int, [_P(KsaPolicy), _i32, _vp, _i64, _i32, _i64, _i64, _vp,
                                           _vp, _vp]),
+    "ksa_sweep_reduce": (C.c_int, [_vp, _i32, _i64, _P(KsaCost), _vp, _vp, _vp, _vp]),
     "ksa_traj_hash": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp]),
     "ksa_gen_traces": (C.c_int, [_P(KsaGenParams), _i64, _i64, _i32, _i64, _i64, _i64, _vp, _vp,
                                  _vp]),

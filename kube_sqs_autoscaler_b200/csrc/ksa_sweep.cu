@@ -400,3 +400,100 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
   KSA_LAUNCH_CHECK("ksa_sweep_kernel (static table)");
   return KSA_OK;
 }
+
+// ---- ksa_sweep_reduce: score a sweep and pick policies (extension; the reference has no cost) -----
+//
+// One pass over the [P][N] summaries. A block owns 32 adjacent traces (lane = trace) and its 16
+// warps split the policies (warp w takes p = w, w+16, ...), so that even a 4096-trace grid fills
+// the GPU: N/32 blocks of 512 threads, each warp keeping kReduceUnroll 2-KB rows (32 records of
+// 64 B) in flight. Per policy the warp's 32 costs are summed with shuffles and added to
+// policy_cost[p] with one 64-bit atomic; wrapping int64 addition is associative, so the totals are
+// exact whatever the order of the atomics. Per trace every warp keeps the argmin over its own
+// policies (ascending p, strict <), and warp 0 merges the 16 candidates through shared memory,
+// cost first, then the lower p.
+
+namespace {
+
+constexpr int kReduceWarps = 16;
+constexpr int kReduceUnroll = 4;
+
+__global__ void __launch_bounds__(kReduceWarps * 32) sweep_reduce_kernel(
+    const ksa_summary* __restrict__ summary, int P, long long N, const __grid_constant__ ksa_cost w,
+    long long* __restrict__ policy_cost, int* __restrict__ best_policy, long long* __restrict__ best_cost) {
+  __shared__ long long s_best[kReduceWarps][32];
+  __shared__ int s_arg[kReduceWarps][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long n = (long long)blockIdx.x * 32 + lane;
+  const bool live = n < N;
+  long long best = 0;
+  int arg = -1;
+  for (int p0 = warp; p0 < P; p0 += kReduceWarps * kReduceUnroll) {
+    // the record as four 16-byte loads (it is 64-byte aligned); all rows of the round first
+    uint4 a[kReduceUnroll], b[kReduceUnroll], d[kReduceUnroll], e[kReduceUnroll];
+#pragma unroll
+    for (int q = 0; q < kReduceUnroll; ++q) {
+      const int p = p0 + q * kReduceWarps;
+      a[q] = b[q] = d[q] = e[q] = make_uint4(0, 0, 0, 0);
+      if (live && p < P) {
+        const uint4* rec = reinterpret_cast<const uint4*>(summary + (long long)p * N + n);
+        a[q] = __ldg(rec), b[q] = __ldg(rec + 1), d[q] = __ldg(rec + 2), e[q] = __ldg(rec + 3);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kReduceUnroll; ++q) {
+      const int p = p0 + q * kReduceWarps;
+      // fields by byte offset: 12 up_applied, 16 down_applied, 20 up_noop, 28 up_cool,
+      // 32 down_cool, 48 sum_replicas
+      const unsigned up_applied = a[q].w, down_applied = b[q].x, up_noop = b[q].y, up_cool = b[q].w,
+                     down_cool = d[q].x;
+      const unsigned long long sum_replicas = (unsigned long long)e[q].x | ((unsigned long long)e[q].y << 32);
+      const unsigned long long c =
+          (unsigned long long)w.w_pod_ticks * sum_replicas +
+          (unsigned long long)w.w_saturated * (unsigned long long)up_noop +
+          (unsigned long long)w.w_churn * ((unsigned long long)up_applied + (unsigned long long)down_applied) +
+          (unsigned long long)w.w_blocked * ((unsigned long long)up_cool + (unsigned long long)down_cool);
+      if (live && p < P && (arg < 0 || (long long)c < best)) {
+        best = (long long)c;
+        arg = p;
+      }
+      if (policy_cost && p < P) {  // p is warp-uniform; dead lanes carry c == 0
+        unsigned long long s = c;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+        if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(policy_cost) + p, s);
+      }
+    }
+  }
+  if (!best_policy && !best_cost) return;
+  s_best[warp][lane] = best;
+  s_arg[warp][lane] = arg;
+  __syncthreads();
+  if (warp == 0 && live) {
+#pragma unroll
+    for (int k = 1; k < kReduceWarps; ++k) {
+      const long long ob = s_best[k][lane];
+      const int oa = s_arg[k][lane];
+      if (oa >= 0 && (arg < 0 || ob < best || (ob == best && oa < arg))) {
+        best = ob;
+        arg = oa;
+      }
+    }
+    if (best_policy) best_policy[n] = arg;
+    if (best_cost) best_cost[n] = best;
+  }
+}
+
+}  // namespace
+
+extern "C" int ksa_sweep_reduce(const ksa_summary* summary_dev, int32_t P, int64_t N, const ksa_cost* cost,
+                                int64_t* policy_cost_dev, int32_t* best_policy_dev, int64_t* best_cost_dev,
+                                void* stream) {
+  if (!summary_dev || !cost) return ksa_fail(KSA_EINVAL, "NULL summary_dev or cost");
+  if (P < 1 || N < 1) return ksa_fail(KSA_EINVAL, "P=%d, N=%lld: both must be >= 1", P, (long long)N);
+  const long long blocks = (N + 31) / 32;
+  if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "N too large for one launch");
+  sweep_reduce_kernel<<<(unsigned)blocks, kReduceWarps * 32, 0, (cudaStream_t)stream>>>(
+      summary_dev, P, N, *cost, (long long*)policy_cost_dev, best_policy_dev, (long long*)best_cost_dev);
+  KSA_LAUNCH_CHECK("sweep_reduce_kernel");
+  return KSA_OK;
+}

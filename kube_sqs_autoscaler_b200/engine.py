@@ -230,6 +230,19 @@ class ReplayEngine:
                                                     _stream_ptr()))
         return summary
 
+    def sweep_reduce(self, summary: torch.Tensor, P: int, N: int, w_pod_ticks: int = 1, w_saturated: int = 0,
+                     w_churn: int = 0, w_blocked: int = 0, policy_cost: torch.Tensor | None = None):
+        """ksa_sweep_reduce (extension beyond the reference): per-policy total cost [P] (accumulated
+        into `policy_cost` when given, so shards add up), per-trace best policy [N] and its cost [N]."""
+        if policy_cost is None:
+            policy_cost = torch.zeros(P, dtype=torch.int64, device=self.dev)
+        best_policy = torch.empty(N, dtype=torch.int32, device=self.dev)
+        best_cost = torch.empty(N, dtype=torch.int64, device=self.dev)
+        w = _abi.KsaCost(w_pod_ticks, w_saturated, w_churn, w_blocked)
+        _abi.check(self.lib.ksa_sweep_reduce(summary.data_ptr(), P, N, C.byref(w), policy_cost.data_ptr(),
+                                             best_policy.data_ptr(), best_cost.data_ptr(), _stream_ptr()))
+        return policy_cost, best_policy, best_cost
+
     def traj_hash(self, replicas: torch.Tensor, events: torch.Tensor, T: int, N: int, ld: int,
                   hash_out: torch.Tensor | None = None, chain: bool = False) -> torch.Tensor:
         if hash_out is None:

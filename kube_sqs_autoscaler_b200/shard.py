@@ -45,3 +45,14 @@ def gather_summaries(local: np.ndarray, n_total: int, group=None):
         b, e = shard_range(n_total, world, r)
         out[b:e] = bufs[r].cpu().numpy()[: (e - b) * SUMMARY_DTYPE.itemsize].view(SUMMARY_DTYPE)
     return out
+
+
+def allreduce_policy_costs(policy_cost, group=None):
+    """Sum the per-policy cost vectors of ksa_sweep_reduce over the ranks (in place; every rank gets
+    the totals). This is the one cross-GPU step of the engine that is a collective: each rank scored
+    its own shard of traces, the [P] int64 totals are all-reduced over NCCL (or gloo on CPU).
+    Wrapping int64 sums are order-independent, so the result is exact."""
+    import torch.distributed as dist
+
+    dist.all_reduce(policy_cost, op=dist.ReduceOp.SUM, group=group)
+    return policy_cost

@@ -236,3 +236,22 @@ def atoi(text: bytes):
         return None
     v = int(text.decode("ascii"))
     return v if -(1 << 63) <= v <= (1 << 63) - 1 else None
+
+
+def sweep_reduce(summary, w_pod_ticks=1, w_saturated=0, w_churn=0, w_blocked=0):
+    """numpy restatement of ksa_sweep_reduce (an extension: the reference has no cost model).
+    summary: structured array [P][N] (SUMMARY_DTYPE). Returns (policy_cost [P] int64, best_policy [N]
+    int32, best_cost [N] int64), all in wrapping int64 arithmetic, ties to the lowest policy."""
+    import numpy as np
+
+    with np.errstate(over="ignore"):
+        u = lambda a: a.astype(np.uint64)  # noqa: E731
+        cost = (np.uint64(w_pod_ticks % 2**64) * summary["sum_replicas"].astype(np.int64).view(np.uint64)
+                + np.uint64(w_saturated % 2**64) * u(summary["up_noop"])
+                + np.uint64(w_churn % 2**64) * (u(summary["up_applied"]) + u(summary["down_applied"]))
+                + np.uint64(w_blocked % 2**64) * (u(summary["up_cool"]) + u(summary["down_cool"])))
+        policy_cost = cost.sum(axis=1, dtype=np.uint64).view(np.int64)
+    signed = cost.view(np.int64)
+    best_policy = signed.argmin(axis=0).astype(np.int32)  # numpy argmin returns the first minimum
+    best_cost = signed.min(axis=0)
+    return policy_cost, best_policy, best_cost

@@ -570,3 +570,43 @@ def test_cli_shards_over_gpus_without_changing_results(engine):
     assert all(o == outs[0] for o in outs), outs
     r = subprocess.run([cli, *args, "--gpus", str(torch.cuda.device_count() + 1)], capture_output=True, text=True)
     assert r.returncode == 2 and "CUDA devices" in r.stderr
+
+
+@pytest.mark.parametrize("P,N", [(1, 1), (7, 37), (9, 515), (33, 4099)])
+def test_sweep_reduce_matches_restatement(engine, P, N):
+    """ksa_sweep_reduce (extension): totals per policy, argmin per trace and its cost, bit-exact
+    against oracle/policy_py.sweep_reduce on real sweep summaries and on wrapping random records;
+    the policy totals accumulate over calls (shards add up)."""
+    import torch
+    from oracle import policy_py
+
+    rng = np.random.default_rng(P * 1000 + N)
+    T, S = 48, 10**9
+    pols = [ksa.Policy(attr_mask=1, scale_up_messages=40 + 9 * i, scale_down_messages=3 + 2 * (i % 7),
+                       scale_up_cool_down=(i % 3) * 10 * S, scale_down_cool_down=(i % 4) * 10 * S,
+                       max_pods=2 + i % 9) for i in range(P)]
+    depth = torch.from_numpy(rng.integers(0, 200, size=(T, 1, N), dtype=np.int64)).to(engine.dev)
+    r0 = torch.ones(N, dtype=torch.int32, device=engine.dev)
+    summ = engine.replay_sweep(pols, depth, T, 1, N, N, r0)
+    host = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(P, N)
+    w = dict(w_pod_ticks=3, w_saturated=40, w_churn=11, w_blocked=-1)
+    pc, bp, bc = engine.sweep_reduce(summ, P, N, **w)
+    rpc, rbp, rbc = policy_py.sweep_reduce(host, **w)
+    assert np.array_equal(pc.cpu().numpy(), rpc)
+    assert np.array_equal(bp.cpu().numpy(), rbp) and np.array_equal(bc.cpu().numpy(), rbc)
+    pc2, _, _ = engine.sweep_reduce(summ, P, N, policy_cost=pc, **w)  # accumulates
+    with np.errstate(over="ignore"):
+        assert np.array_equal(pc2.cpu().numpy(), rpc + rpc)
+    # wrapping arithmetic and ties on synthetic records
+    fake = np.zeros((P, N), dtype=ksa.SUMMARY_DTYPE)
+    for f in ("up_applied", "down_applied", "up_noop", "up_cool", "down_cool"):
+        fake[f] = rng.integers(0, 2**32, size=(P, N), dtype=np.uint64).astype(np.uint32)
+    fake["sum_replicas"] = rng.integers(-2**62, 2**62, size=(P, N), dtype=np.int64)
+    if P > 2:
+        fake[P - 1] = fake[1]
+    w = dict(w_pod_ticks=2**33 + 1, w_saturated=-5, w_churn=2**40, w_blocked=3)
+    dev = torch.from_numpy(fake.view(np.uint8).reshape(P, N, 64)).to(engine.dev)
+    pc, bp, bc = engine.sweep_reduce(dev, P, N, **w)
+    rpc, rbp, rbc = policy_py.sweep_reduce(fake, **w)
+    assert np.array_equal(pc.cpu().numpy(), rpc)
+    assert np.array_equal(bp.cpu().numpy(), rbp) and np.array_equal(bc.cpu().numpy(), rbc)

@@ -109,6 +109,53 @@ def test_two_rank_gloo_shards_and_gathers(tmp_path):
     assert got.tobytes() == ref.summary.tobytes()
 
 
+def test_two_rank_gloo_allreduces_policy_costs(tmp_path):
+    """world_size=2 over gloo: per-policy cost totals of the two shards, all-reduced, equal the
+    totals of the unsharded grid (the only collective of the engine: shard.allreduce_policy_costs)."""
+    worker = os.path.join(os.path.dirname(__file__), "gloo_reduce_worker.py")
+    out = tmp_path / "costs.npy"
+    port = str(_free_port())
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", port, worker, str(out)],
+                       capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    from tests.gloo_reduce_worker import N_TOTAL, shard_costs
+    want, _, _ = shard_costs(0, N_TOTAL)
+    assert np.array_equal(np.load(out), want)
+
+
+def test_sweep_reduce_restatement_matches_a_plain_loop():
+    """oracle/policy_py.sweep_reduce (numpy) against the definition written as Python loops:
+    wrapping int64 cost, totals per policy, argmin per trace with ties to the lowest policy."""
+    from kube_sqs_autoscaler_b200 import SUMMARY_DTYPE
+    from oracle import policy_py
+
+    rng = np.random.default_rng(11)
+    P, N = 5, 9
+    summ = np.zeros((P, N), dtype=SUMMARY_DTYPE)
+    for f in ("up_applied", "down_applied", "up_noop", "up_cool", "down_cool"):
+        summ[f] = rng.integers(0, 2**32, size=(P, N), dtype=np.uint64).astype(np.uint32)
+    summ["sum_replicas"] = rng.integers(-2**62, 2**62, size=(P, N), dtype=np.int64)
+    summ[3] = summ[1]  # exact ties between policies 1 and 3
+    w = dict(w_pod_ticks=2**33 + 1, w_saturated=-5, w_churn=2**40, w_blocked=3)
+
+    def wrap(x):
+        x &= 2**64 - 1
+        return x - 2**64 if x >= 2**63 else x
+
+    cost = [[wrap(w["w_pod_ticks"] * int(summ["sum_replicas"][p, n]) + w["w_saturated"] * int(summ["up_noop"][p, n])
+                  + w["w_churn"] * (int(summ["up_applied"][p, n]) + int(summ["down_applied"][p, n]))
+                  + w["w_blocked"] * (int(summ["up_cool"][p, n]) + int(summ["down_cool"][p, n])))
+             for n in range(N)] for p in range(P)]
+    pc, bp, bc = policy_py.sweep_reduce(summ, **w)
+    assert [int(x) for x in pc] == [wrap(sum(cost[p])) for p in range(P)]
+    for n in range(N):
+        col = [cost[p][n] for p in range(P)]
+        assert int(bc[n]) == min(col) and int(bp[n]) == col.index(min(col))
+    assert 3 not in bp.tolist()
+
+
 def test_cli_keeps_the_reference_flag_surface(built):
     """ksa-replay (C++ host): reference flags parse, Go-style errors for bad values, and without
     a GPU it fails loudly instead of computing anything on the CPU."""

@@ -145,6 +145,31 @@ def run_config4(args):
                       "compulsory_bytes": 8 * N * T + 64 * P * N + 48 * P,
                       "note": "integer-issue bound, not HBM bound (includes the 192 KB policy-table upload)",
                       "parity": "3 policies == single-policy summary kernel: " + ("ok" if ok else "MISMATCH")}), flush=True)
+    # follow-up: score the grid. One HBM pass over the P x N summaries.
+    pc = torch.zeros(P, dtype=torch.int64, device=eng.dev)
+    rms = []
+    for rep in range(args.reps + 2):
+        pc.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        pc, bp, bc = eng.sweep_reduce(summ, P, N, w_pod_ticks=1, w_saturated=25, w_churn=5, w_blocked=1, policy_cost=pc)
+        b.record()
+        torch.cuda.synchronize()
+        if rep >= 2:
+            rms.append(a.elapsed_time(b))
+    # cross-check of the totals with torch integer ops on the same records (the bit-exact parity
+    # test against the restatement is tests/test_gpu_parity.py::test_sweep_reduce_matches_restatement)
+    sub = slice(0, min(P, 64))
+    w32 = summ[sub].view(torch.int32).view(-1, N, 16).to(torch.int64) & 0xFFFFFFFF
+    sumr = summ[sub].view(torch.int64).view(-1, N, 8)[:, :, 6]
+    rpc = (sumr + 25 * w32[:, :, 5] + 5 * (w32[:, :, 3] + w32[:, :, 4]) + (w32[:, :, 7] + w32[:, :, 8])).sum(dim=1).cpu().numpy()
+    rbytes = 64 * P * N + 12 * N + 8 * P
+    print(json.dumps({"config": 4, "workload": f"ksa_sweep_reduce over {P} x {N} summaries", "ms": min(rms), "ms_all": rms,
+                      "algorithmic_bytes": rbytes, "GBps": rbytes / (min(rms) * 1e-3) / 1e9,
+                      "frac_of_measured_peak": rbytes / (min(rms) * 1e-3) / 1e9 / peak(),
+                      "best_policy_overall": int(pc.argmin()),
+                      "parity": "first policies' totals == torch integer ops: " + ("ok" if np.array_equal(pc[sub].cpu().numpy(), rpc) else "MISMATCH")}),
+          flush=True)
 
 
 def run_config5(args):
