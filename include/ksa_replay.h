@@ -373,7 +373,7 @@ typedef struct ksa_pipeline ksa_pipeline; /* opaque; owns device staging + 3 str
 
 /*
  * Create a streaming pipeline on `device` for up to N traces x A attributes, moving chunk_ticks
- * ticks per stage (double-buffered: 2 * chunk_ticks * N * (8A+5) bytes of device memory).
+ * ticks per stage (double-buffered: 2 * chunk_ticks * N * (8A+6) bytes of device memory).
  */
 int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, int32_t A, int64_t chunk_ticks);
 int ksa_pipeline_destroy(ksa_pipeline* p);
@@ -390,6 +390,18 @@ int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy, const int64_t
                         int64_t T, int64_t N, int64_t tick0, int32_t* state_replicas_host,
                         int64_t* state_last_up_host, int64_t* state_last_down_host,
                         int32_t* replicas_host, uint8_t* events_host, ksa_summary* summary_host);
+
+/*
+ * The same with a failure mask: fail_host [T][N] uint8 of KSA_FAIL_* bits (tight rows), staged
+ * with the depths (one more byte per decision host -> device) and replayed by
+ * ksa_replay_full_faults / ksa_replay_summary_faults, i.e. Run's three error paths
+ * (main.go:44-47, 57-60, 71-74). fail_host must not be NULL.
+ */
+int ksa_pipeline_replay_faults(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
+                               const uint8_t* fail_host, int64_t T, int64_t N, int64_t tick0,
+                               int32_t* state_replicas_host, int64_t* state_last_up_host,
+                               int64_t* state_last_down_host, int32_t* replicas_host,
+                               uint8_t* events_host, ksa_summary* summary_host);
 
 /* ---- tuning / introspection -------------------------------------------------------------- */
 

@@ -158,6 +158,8 @@ SIGNATURES = {
     "ksa_pipeline_destroy": (C.c_int, [_vp]),
     "ksa_pipeline_replay": (C.c_int, [_vp, _P(KsaPolicy), _vp, _i64, _i64, _i64, _vp, _vp, _vp,
                                       _vp, _vp, _vp]),
+    "ksa_pipeline_replay_faults": (C.c_int, [_vp, _P(KsaPolicy), _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp,
+                                             _vp, _vp, _vp]),
     "ksa_set_variant": (C.c_int, [_i32, _i32]),
     "ksa_variant_name": (C.c_char_p, [_i32, _i32]),
     "ksa_launch_count": (_i64, []),

@@ -174,6 +174,7 @@ struct ksa_pipeline {
   long long* depth[2];
   int* replicas[2];
   unsigned char* events[2];
+  unsigned char* fail[2];  // failure-mask staging (ksa_pipeline_replay_faults)
   int* st_r[2];            // [0] full-mode state, [1] summary-mode state (same start values)
   long long* st_ju[2];
   long long* st_jd[2];
@@ -186,6 +187,7 @@ static void pipeline_free(ksa_pipeline* p) {
     cudaFree(p->depth[i]);
     cudaFree(p->replicas[i]);
     cudaFree(p->events[i]);
+    cudaFree(p->fail[i]);
     cudaFree(p->st_r[i]);
     cudaFree(p->st_ju[i]);
     cudaFree(p->st_jd[i]);
@@ -240,6 +242,7 @@ extern "C" int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, in
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->depth[i], cells * (size_t)A * sizeof(long long)));
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->replicas[i], cells * sizeof(int)));
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->events[i], cells));
+    KSA_PIPE_CUDA(cudaMalloc((void**)&p->fail[i], cells));
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->st_r[i], (size_t)p->ld * sizeof(int)));
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->st_ju[i], (size_t)p->ld * sizeof(long long)));
     KSA_PIPE_CUDA(cudaMalloc((void**)&p->st_jd[i], (size_t)p->ld * sizeof(long long)));
@@ -271,11 +274,13 @@ static cudaError_t copy_rows_d2h(void* dst, const void* src, size_t elem, int64_
                            (size_t)rows, cudaMemcpyDeviceToHost, st);
 }
 
-extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,
-                                   const int64_t* depth_host, int64_t T, int64_t N, int64_t tick0,
-                                   int32_t* state_replicas_host, int64_t* state_last_up_host,
-                                   int64_t* state_last_down_host, int32_t* replicas_host,
-                                   uint8_t* events_host, ksa_summary* summary_host) {
+// fail_host == NULL: the plain replay; otherwise the *_faults kernels with the mask staged
+// alongside the depths (one more byte per decision on the H2D stream).
+static int pipeline_run(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
+                        const uint8_t* fail_host, int64_t T, int64_t N, int64_t tick0,
+                        int32_t* state_replicas_host, int64_t* state_last_up_host,
+                        int64_t* state_last_down_host, int32_t* replicas_host, uint8_t* events_host,
+                        ksa_summary* summary_host) {
   if (!p || !policy || !depth_host || !state_replicas_host || !state_last_up_host || !state_last_down_host)
     return ksa_fail(KSA_EINVAL, "NULL pipeline, policy, depth or state");
   if (N < 1 || N > p->N) return ksa_fail(KSA_ELIMIT, "N=%lld exceeds the pipeline's %lld traces", (long long)N, (long long)p->N);
@@ -317,19 +322,26 @@ extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,
     if (c >= 2) KSA_CUDA(cudaStreamWaitEvent(p->s_in, p->k_done[s], 0));
     KSA_CUDA(copy_rows_h2d(p->depth[s], depth_host + (size_t)t_begin * (size_t)A * (size_t)N,
                            sizeof(long long), N, ld, tc * A, p->s_in));
+    if (fail_host)
+      KSA_CUDA(copy_rows_h2d(p->fail[s], fail_host + (size_t)t_begin * (size_t)N, 1, N, ld, tc, p->s_in));
     KSA_CUDA(cudaEventRecord(p->in_done[s], p->s_in));
     KSA_CUDA(cudaStreamWaitEvent(p->s_k, p->in_done[s], 0));
     // stage s's output buffers are free once chunk c-2's D2H copies are done
     if (c >= 2 && want_full) KSA_CUDA(cudaStreamWaitEvent(p->s_k, p->out_done[s], 0));
     if (want_full) {
-      rc = ksa_replay_full(policy, (const int64_t*)p->depth[s], tc, A, N, ld, tick0 + t_begin, &sf,
-                           replicas_host ? p->replicas[s] : nullptr,
-                           events_host ? p->events[s] : nullptr, p->s_k);
+      int32_t* r_dev = replicas_host ? p->replicas[s] : nullptr;
+      uint8_t* e_dev = events_host ? p->events[s] : nullptr;
+      rc = fail_host ? ksa_replay_full_faults(policy, (const int64_t*)p->depth[s], p->fail[s], tc, A, N, ld,
+                                              tick0 + t_begin, &sf, r_dev, e_dev, p->s_k)
+                     : ksa_replay_full(policy, (const int64_t*)p->depth[s], tc, A, N, ld, tick0 + t_begin, &sf,
+                                       r_dev, e_dev, p->s_k);
       if (rc != KSA_OK) return rc;
     }
     if (want_summary) {
-      rc = ksa_replay_summary(policy, (const int64_t*)p->depth[s], tc, A, N, ld, tick0 + t_begin,
-                              &ss, p->summary, p->s_k);
+      rc = fail_host ? ksa_replay_summary_faults(policy, (const int64_t*)p->depth[s], p->fail[s], tc, A, N, ld,
+                                                 tick0 + t_begin, &ss, p->summary, p->s_k)
+                     : ksa_replay_summary(policy, (const int64_t*)p->depth[s], tc, A, N, ld, tick0 + t_begin,
+                                          &ss, p->summary, p->s_k);
       if (rc != KSA_OK) return rc;
     }
     KSA_CUDA(cudaEventRecord(p->k_done[s], p->s_k));
@@ -353,4 +365,24 @@ extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,
   KSA_CUDA(cudaStreamSynchronize(p->s_k));
   KSA_CUDA(cudaStreamSynchronize(p->s_out));
   return KSA_OK;
+}
+
+extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,
+                                   const int64_t* depth_host, int64_t T, int64_t N, int64_t tick0,
+                                   int32_t* state_replicas_host, int64_t* state_last_up_host,
+                                   int64_t* state_last_down_host, int32_t* replicas_host,
+                                   uint8_t* events_host, ksa_summary* summary_host) {
+  return pipeline_run(p, policy, depth_host, nullptr, T, N, tick0, state_replicas_host, state_last_up_host,
+                      state_last_down_host, replicas_host, events_host, summary_host);
+}
+
+extern "C" int ksa_pipeline_replay_faults(ksa_pipeline* p, const ksa_policy* policy,
+                                          const int64_t* depth_host, const uint8_t* fail_host, int64_t T,
+                                          int64_t N, int64_t tick0, int32_t* state_replicas_host,
+                                          int64_t* state_last_up_host, int64_t* state_last_down_host,
+                                          int32_t* replicas_host, uint8_t* events_host,
+                                          ksa_summary* summary_host) {
+  if (!fail_host) return ksa_fail(KSA_EINVAL, "NULL fail_host (use ksa_pipeline_replay)");
+  return pipeline_run(p, policy, depth_host, fail_host, T, N, tick0, state_replicas_host, state_last_up_host,
+                      state_last_down_host, replicas_host, events_host, summary_host);
 }

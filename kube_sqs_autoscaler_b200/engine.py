@@ -286,7 +286,8 @@ class HostPipeline:
     def replay(self, policy: Policy, depth: np.ndarray, tick0: int, state_replicas: np.ndarray,
                state_last_up: np.ndarray, state_last_down: np.ndarray,
                replicas: np.ndarray | None = None, events: np.ndarray | None = None,
-               summary: np.ndarray | None = None) -> None:
+               summary: np.ndarray | None = None, fail: np.ndarray | None = None) -> None:
+        """fail: optional [T][N] uint8 of KSA_FAIL_* bits -> ksa_pipeline_replay_faults."""
         T, A, N = depth.shape
         assert A == self.A and depth.dtype == np.int64 and depth.flags.c_contiguous
         for arr, dt in ((state_replicas, np.int32), (state_last_up, np.int64), (state_last_down, np.int64)):
@@ -299,6 +300,13 @@ class HostPipeline:
             assert summary.dtype == _abi.SUMMARY_DTYPE and summary.size == N
         pc = policy.to_c()
         ptr = lambda a: a.ctypes.data if a is not None else None  # noqa: E731
+        if fail is not None:
+            assert fail.dtype == np.uint8 and fail.shape == (T, N) and fail.flags.c_contiguous
+            _abi.check(self.lib.ksa_pipeline_replay_faults(self.handle, C.byref(pc), ptr(depth), ptr(fail), T, N,
+                                                           tick0, ptr(state_replicas), ptr(state_last_up),
+                                                           ptr(state_last_down), ptr(replicas), ptr(events),
+                                                           ptr(summary)))
+            return
         _abi.check(self.lib.ksa_pipeline_replay(self.handle, C.byref(pc), ptr(depth), T, N, tick0,
                                                 ptr(state_replicas), ptr(state_last_up),
                                                 ptr(state_last_down), ptr(replicas), ptr(events),

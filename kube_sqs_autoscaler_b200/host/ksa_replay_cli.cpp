@@ -102,6 +102,9 @@ struct Options {
   std::string mode = "summary";
   int device = 0;  // first device
   int gpus = 1;    // devices device .. device+gpus-1, one host thread each
+  // injected API failures (main.go:44-47,57-60,71-74): each call fails with probability 2^-k, 0 = never
+  uint32_t poll_fail_log2 = 0, up_fail_log2 = 0, down_fail_log2 = 0;
+  bool faults() const { return poll_fail_log2 || up_fail_log2 || down_fail_log2; }
 };
 
 Options parse(int argc, char** argv) {
@@ -156,16 +159,21 @@ Options parse(int argc, char** argv) {
     else if (k == "mode") o.mode = v;
     else if (k == "device") o.device = (int)as_int("device");
     else if (k == "gpus") o.gpus = (int)as_int("gpus");
+    else if (k == "poll-fail-log2") o.poll_fail_log2 = (uint32_t)as_int("poll-fail-log2");
+    else if (k == "up-fail-log2") o.up_fail_log2 = (uint32_t)as_int("up-fail-log2");
+    else if (k == "down-fail-log2") o.down_fail_log2 = (uint32_t)as_int("down-fail-log2");
     else if (k == "help" || k == "h") {
       std::puts("usage: ksa-replay [reference flags: --poll-period --scale-up-cool-down --scale-down-cool-down\n"
                 "  --scale-up-messages --scale-down-messages --scale-up-pods --scale-down-pods --max-pods --min-pods\n"
-                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D] [--gpus G]");
+                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D] [--gpus G]\n"
+                "  [--poll-fail-log2 K] [--up-fail-log2 K] [--down-fail-log2 K]  (each API call fails with probability 2^-K)");
       std::exit(0);
     } else {
       die("flag provided but not defined: -" + k);
     }
   }
   if (o.mode != "full" && o.mode != "summary") die("--mode must be full or summary");
+  if (o.poll_fail_log2 > 63 || o.up_fail_log2 > 63 || o.down_fail_log2 > 63) die("--*-fail-log2 must be in [0, 63]");
   return o;
 }
 
@@ -178,10 +186,13 @@ double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::
   const int A = __builtin_popcount(o.policy.attr_mask);
   const int64_t T = o.ticks, NC = std::min<int64_t>(end - begin, 1 << 20), ld = (NC + 15) / 16 * 16;
   const bool full = o.mode == "full";
-  const int64_t chunk = std::min<int64_t>(T, std::max<int64_t>(1, (int64_t)((full ? 48.0e9 : 64.0e9) / ((8.0 * A + (full ? 5 : 0)) * ld))));
+  const bool faults = o.faults();
+  const int64_t chunk = std::min<int64_t>(T, std::max<int64_t>(1, (int64_t)((full ? 48.0e9 : 64.0e9) / ((8.0 * A + (full ? 5 : 0) + (faults ? 1 : 0)) * ld))));
+  void* fail = nullptr;
   void *depth = nullptr, *r = nullptr, *ju = nullptr, *jd = nullptr, *summ = nullptr, *rep = nullptr, *evs = nullptr;
   void *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr;
   check(ksa_dev_alloc(&depth, (size_t)chunk * A * ld * 8), "depth");
+  if (faults) check(ksa_dev_alloc(&fail, (size_t)chunk * ld), "fail");
   check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
   check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
   check(ksa_dev_alloc(&jd, (size_t)ld * 8), "state");
@@ -214,19 +225,26 @@ double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::
     for (int64_t t0 = 0; t0 < T; t0 += chunk) {
       const int64_t tc = std::min(chunk, T - t0);
       check(ksa_gen_traces(&g, t0, tc, A, c0, n, ld, (int64_t*)depth, nullptr, nullptr), "ksa_gen_traces");
+      if (faults)
+        check(ksa_gen_faults(o.seed, o.poll_fail_log2, o.up_fail_log2, o.down_fail_log2, t0, tc, c0, n, ld, (uint8_t*)fail, nullptr), "ksa_gen_faults");
       check(ksa_stream_sync(nullptr), "sync");
+      const int64_t* d = (const int64_t*)depth;
+      const uint8_t* f = (const uint8_t*)fail;
       const auto a = std::chrono::steady_clock::now();
-      if (full) check(ksa_replay_full(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
-      else check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+      if (full && faults) check(ksa_replay_full_faults(&o.policy, d, f, tc, A, n, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full_faults");
+      else if (full) check(ksa_replay_full(&o.policy, d, tc, A, n, ld, t0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
+      else if (faults) check(ksa_replay_summary_faults(&o.policy, d, f, tc, A, n, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary_faults");
+      else check(ksa_replay_summary(&o.policy, d, tc, A, n, ld, t0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
       check(ksa_stream_sync(nullptr), "sync");
       replay_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
-      if (full) check(ksa_replay_summary(&o.policy, (const int64_t*)depth, tc, A, n, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+      if (full && faults) check(ksa_replay_summary_faults(&o.policy, d, f, tc, A, n, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary_faults");
+      else if (full) check(ksa_replay_summary(&o.policy, d, tc, A, n, ld, t0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
     }
     // host gather: this chunk's summaries at their global trace ids
     check(ksa_memcpy_d2h(host->data() + c0, summ, (size_t)n * sizeof(ksa_summary), nullptr), "d2h");
     check(ksa_stream_sync(nullptr), "sync");
   }
-  for (void* p : {depth, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
+  for (void* p : {depth, fail, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
     if (p) ksa_dev_free(p);
   return replay_s;
 }
@@ -258,11 +276,12 @@ int main(int argc, char** argv) {
   for (auto& w : workers) w.join();
   const double replay_s = *std::max_element(secs.begin(), secs.end());
 
-  uint64_t tot[6] = {0, 0, 0, 0, 0, 0}, digest = 0;
+  uint64_t tot[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, digest = 0;
   long double replica_ticks = 0;
   for (const ksa_summary& s : host) {
     tot[0] += s.up_applied; tot[1] += s.down_applied; tot[2] += s.up_noop;
     tot[3] += s.down_noop; tot[4] += s.up_cool; tot[5] += s.down_cool;
+    tot[6] += s.poll_failed; tot[7] += s.up_failed; tot[8] += s.down_failed;
     replica_ticks += (long double)s.sum_replicas;
     digest ^= s.hash;
   }
@@ -275,6 +294,9 @@ int main(int argc, char** argv) {
   std::printf("scale up successful %" PRIu64 " | scale down successful %" PRIu64 " | at max %" PRIu64 " | at min %" PRIu64
               " | up cool-down skips %" PRIu64 " | down cool-down skips %" PRIu64 "\n",
               tot[0], tot[1], tot[2], tot[3], tot[4], tot[5]);
+  if (o.faults())
+    std::printf("failed to get SQS messages %" PRIu64 " | failed scaling up %" PRIu64 " | failed scaling down %" PRIu64 "\n",
+                tot[6], tot[7], tot[8]);
   std::printf("mean replicas %.4Lf | xor of trajectory fingerprints %016" PRIx64 "\n",
               replica_ticks / ((long double)N * (long double)T), digest);
   return 0;

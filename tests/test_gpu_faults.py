@@ -142,3 +142,78 @@ def test_generated_mask_chunks_and_counters(engine):
     # every tick has exactly one poll; a failed poll is the only event of its tick
     ev = ref.events[:, :N]
     assert ((ev == 0xC0) == ((f_host[:, :N] & 1) == 1)).all()
+
+
+@pytest.mark.parametrize("A,N,T,chunk", [(1, 1000, 130, 32), (3, 517, 77, 77), (2, 2049, 64, 7)])
+def test_host_pipeline_with_failure_mask_matches_oracle(engine, A, N, T, chunk):
+    """ksa_pipeline_replay_faults: host depths + host failure mask, chunked and overlapped, equal to
+    the oracle's replay with the same mask (outputs, summary, carry state); two calls in a row
+    (state carried through the host arrays) equal one call over all ticks."""
+    rng = np.random.default_rng(A * 100 + N)
+    pol = ksa.Policy(attr_mask=(1 << A) - 1, scale_up_messages=250, scale_down_messages=25,
+                     scale_up_cool_down=12 * S, scale_down_cool_down=45 * S, max_pods=9)
+    depth = ksa.pinned_empty((T, A, N), np.int64)
+    depth[...] = rng.integers(0, 200, size=(T, A, N), dtype=np.int64)
+    fail = ksa.pinned_empty((T, N), np.uint8)
+    fail[...] = rng.choice(np.array([0, 0, 0, 0, 1, 2, 4, 6, 7], dtype=np.uint8), size=(T, N))
+    st = oracle_lib.fresh_state(8, 0, N, 1, 5)
+    ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, N, 0, *st, want_summary=True, fail=fail)
+    pipe = ksa.HostPipeline(0, N + 5, A, chunk)
+    try:
+        r, ju, jd = (np.array(x, copy=True) for x in st)
+        replicas = ksa.pinned_empty((T, N), np.int32)
+        events = ksa.pinned_empty((T, N), np.uint8)
+        summary = np.empty(N, dtype=ksa.SUMMARY_DTYPE)
+        pipe.replay(pol, depth, 0, r, ju, jd, replicas, events, summary, fail=fail)
+        assert np.array_equal(replicas, ref.replicas) and np.array_equal(events, ref.events)
+        assert summary.tobytes() == ref.summary.tobytes()
+        assert np.array_equal(r, ref.state_replicas) and np.array_equal(ju, ref.state_last_up)
+        assert np.array_equal(jd, ref.state_last_down)
+        # split in time: [0, T1) then [T1, T), state carried by the caller
+        T1 = T // 3
+        r2, ju2, jd2 = (np.array(x, copy=True) for x in st)
+        rr, ee = ksa.pinned_empty((T, N), np.int32), ksa.pinned_empty((T, N), np.uint8)
+        pipe.replay(pol, depth[:T1], 0, r2, ju2, jd2, rr[:T1], ee[:T1], None, fail=fail[:T1])
+        pipe.replay(pol, depth[T1:], T1, r2, ju2, jd2, rr[T1:], ee[T1:], None, fail=fail[T1:])
+        assert np.array_equal(rr, ref.replicas) and np.array_equal(ee, ref.events)
+        assert np.array_equal(r2, ref.state_replicas)
+        # summary-only
+        r3, ju3, jd3 = (np.array(x, copy=True) for x in st)
+        pipe.replay(pol, depth, 0, r3, ju3, jd3, None, None, summary, fail=fail)
+        assert summary.tobytes() == ref.summary.tobytes() and np.array_equal(r3, ref.state_replicas)
+    finally:
+        pipe.close()
+
+
+@pytest.mark.parametrize("mode", ["summary", "full"])
+def test_cli_with_injected_failures_matches_oracle(engine, mode):
+    """ksa-replay --poll-fail-log2/--up-fail-log2/--down-fail-log2: totals (including the three
+    failure counters) and the fingerprint digest equal the oracle's replay of the same generated
+    depths and failure mask."""
+    import re
+    import subprocess
+
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    N, T = 3000, 200
+    r = subprocess.run([cli, "--poll-period=5s", "--scale-up-cool-down=12s", "--scale-down-cool-down=20s",
+                        "--max-pods=9", "--traces", str(N), "--ticks", str(T), "--mode", mode, "--seed", "91",
+                        "--poll-fail-log2", "4", "--up-fail-log2", "2", "--down-fail-log2", "3"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    m = re.search(r"scale up successful (\d+) \| scale down successful (\d+) \| at max (\d+) \| at min (\d+) \| "
+                  r"up cool-down skips (\d+) \| down cool-down skips (\d+)", r.stdout)
+    f = re.search(r"failed to get SQS messages (\d+) \| failed scaling up (\d+) \| failed scaling down (\d+)", r.stdout)
+    assert m and f, r.stdout
+    got = [int(x) for x in m.groups() + f.groups()]
+    digest = int(re.search(r"fingerprints ([0-9a-f]{16})", r.stdout).group(1), 16)
+    pol = ksa.Policy(attr_mask=1, max_pods=9, scale_up_cool_down=12 * S, scale_down_cool_down=20 * S)
+    gen = ksa.GenParams(seed=91, low_max=10, high_min=100, high_max=400)
+    ld = (N + 15) // 16 * 16
+    d_host = oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, ld)
+    fail = oracle_lib.gen_faults(91, 4, 2, 3, 0, T, 0, N, ld)
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, ld, 0, *oracle_lib.fresh_state(91, 0, N, 1, 9),
+                            want_full=False, want_summary=True, fail=fail)
+    want = [int(ref.summary[k].sum()) for k in ("up_applied", "down_applied", "up_noop", "down_noop", "up_cool",
+                                                "down_cool", "poll_failed", "up_failed", "down_failed")]
+    assert got == want and min(want[6:]) > 0
+    assert digest == int(np.bitwise_xor.reduce(ref.summary["hash"]))
