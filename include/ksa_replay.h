@@ -106,10 +106,18 @@ typedef struct ksa_state {
 /*
  * Per-trace summary (64 bytes). Counters accumulate across chunked calls when the caller does not
  * clear the buffer in between (ksa_summary_clear starts a fresh accumulation).
- *  hash: order-sensitive 64-bit fingerprint of the (replicas, event) trajectory:
- *        h <- h * 0x9E3779B97F4A7C15 + ((uint64)event << 32 | (uint32)replicas)  per tick, h0 = 0
- *        (a polynomial in the odd multiplier over Z/2^64: any single-tick difference changes it).
+ *  hash: order-sensitive fingerprint of the (replicas, event) trajectory, two 32-bit lanes
+ *        updated once per tick from h0 = 0 (hash = hi << 32 | lo):
+ *          lo <- lo * 0x9E3779B1 + (uint32)replicas
+ *          hi <- hi * 0x85EBCA6B + wide(event)
+ *        wide(event) = the event byte with bit k (k = 0..5) moved to bit 5k and the two failure
+ *        bits (6, 7) moved to bits 30, 31 (KSA_EV_WIDE below). Each lane is a polynomial in an
+ *        odd multiplier over Z/2^32: any single-tick difference changes it. One integer
+ *        multiply-add per lane and tick on the GPU.
  */
+#define KSA_EV_WIDE(ev)                                                                        \
+  (((((uint32_t)(ev)) & 7u) * 0x111u & 0x421u) | (((((uint32_t)(ev)) >> 3 & 7u) * 0x111u & 0x421u) << 15) | \
+   ((((uint32_t)(ev)) >> 6) << 30))
 typedef struct ksa_summary {
   int32_t final_replicas;
   int32_t min_replicas; /* over ticks replayed so far (INT32_MAX when none) */

@@ -73,6 +73,27 @@ struct ksa_step_consts {
         cd((int)(p.cd > KSA_COOL_CAP ? KSA_COOL_CAP : p.cd)) {}
 };
 
+// The "wide" event code: event bit k (KSA_EV_*) moved to bit 5k for the six policy events, the two
+// failure bits to 30 and 31. The summary kernels build it directly (the same six predicated
+// operations that would build the event byte), add it as it is into a packed counter word (six
+// 5-bit fields, folded every <= 31 ticks) and feed it to the fingerprint; they never need the
+// byte. include/ksa_replay.h documents it as part of the definition of ksa_summary.hash.
+#define KSA_W_UP_APPLIED (1u << 0)
+#define KSA_W_DOWN_APPLIED (1u << 5)
+#define KSA_W_UP_NOOP (1u << 10)
+#define KSA_W_DOWN_NOOP (1u << 15)
+#define KSA_W_UP_COOL (1u << 20)
+#define KSA_W_DOWN_COOL (1u << 25)
+#define KSA_W_UP_FAILED (1u << 30)
+#define KSA_W_DOWN_FAILED (1u << 31)
+__host__ __device__ __forceinline__ unsigned ksa_wide_event(unsigned ev) {
+  // three bits at a time: b0 b1 b2 -> bits 0, 5, 10 (times 0x111 lands bit k at k + 4j; the mask
+  // keeps j == k; the nine partial products are at distinct positions, so nothing carries)
+  const unsigned lo = ((ev & 7u) * 0x111u) & 0x421u;
+  const unsigned hi = (((ev >> 3) & 7u) * 0x111u) & 0x421u;
+  return lo | (hi << 15) | ((ev >> 6) << 30);
+}
+
 // One tick of one trace. `n` = attribute sum, `i` = local tick (1-based). Returns the KSA_EV_* bits.
 // Written so that each predicate dies right after it is used: a thread has only 7 predicate
 // registers and runs up to 16 traces interleaved.
@@ -148,39 +169,107 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
 // which is the pipe this state machine saturates first (profiles/r01_ncu_full_v14_T2000.txt: ALU
 // 56 % active, FMA 12 %). This moves 9 of the 22 ALU operations per decision to the idle pipe, and
 // the stamp `s = i * one + cool` needs no precomputed i + cool (the sweep has one cool per policy).
+// WIDE = true returns the wide event code (ksa_wide_event of the byte) instead of the byte.
+// ORDERED = true is for policies with scale_up_messages > scale_down_messages (the caller checks):
+// then the two thresholds cannot both be met in one tick, so the `continue` of main.go:54 never
+// has a down branch to skip and the up cool-down predicate is not needed at all (one ISETP less;
+// ISETP issues on the half-rate ALU pipe, which is what bounds the summary and sweep kernels).
+// The cool-down events are entered from the threshold predicate and corrected when the gate is
+// open, so neither direction needs a separate "blocked" compare for its event.
+template <bool WIDE = false, bool ORDERED = false>
 __device__ __forceinline__ unsigned ksa_step_fma(const ksa_step_consts& c, long long n, int i, int one,
                                                  ksa_trace_regs& s) {
+  constexpr int kUpCool = WIDE ? (int)KSA_W_UP_COOL : KSA_EV_UP_COOL;
+  constexpr int kUpNoop = WIDE ? (int)KSA_W_UP_NOOP : KSA_EV_UP_NOOP;
+  constexpr int kUpApp = WIDE ? (int)KSA_W_UP_APPLIED : KSA_EV_UP_APPLIED;
+  constexpr int kDownCool = WIDE ? (int)KSA_W_DOWN_COOL : KSA_EV_DOWN_COOL;
+  constexpr int kDownNoop = WIDE ? (int)KSA_W_DOWN_NOOP : KSA_EV_DOWN_NOOP;
+  constexpr int kDownApp = WIDE ? (int)KSA_W_DOWN_APPLIED : KSA_EV_DOWN_APPLIED;
+  unsigned ev;
+#define KSA_STEP_FMA_BODY(DOWN_HIT)                                                              \
+  asm("{\n\t"                                                                                    \
+      ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dapp;\n\t"                                      \
+      ".reg .s32 t, u;\n\t"                                                                      \
+      "setp.ge.s64 uh, %4, %5;\n\t"                /* main.go:51 */                              \
+      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"      /* main.go:52 false */                        \
+      "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"     /* scale.go:62 */                             \
+      "selp.u32 %0, %15, 0, uh;\n\t"               /* UP_COOL unless the gate is open ... */     \
+      "@ugo mad.lo.s32 %0, %14, %16, %0;\n\t"      /* ... then UP_NOOP unless ... */             \
+      "@uapp mad.lo.s32 %0, %14, %17, %0;\n\t"     /* ... UP_APPLIED */                          \
+      "add.s32 t, %1, %9;\n\t"                     /* scale.go:66 */                             \
+      "min.s32 t, t, %7;\n\t"                      /* scale.go:67-69 */                          \
+      "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"                                                      \
+      DOWN_HIT                                     /* main.go:65 (+ :54), reads the old su */    \
+      "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"     /* main.go:62   su = i + cu */                \
+      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"      /* main.go:66 false */                        \
+      "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"     /* scale.go:89 */                             \
+      "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"     /* main.go:76   sd = i + cd */                \
+      "@dh mad.lo.s32 %0, %14, %18, %0;\n\t"       /* DOWN_COOL unless ... */                    \
+      "@dgo mad.lo.s32 %0, %14, %19, %0;\n\t"      /* ... DOWN_NOOP unless ... */                \
+      "@dapp mad.lo.s32 %0, %14, %20, %0;\n\t"     /* ... DOWN_APPLIED */                        \
+      "sub.s32 u, %1, %10;\n\t"                    /* scale.go:94 */                             \
+      "max.s32 u, u, %8;\n\t"                      /* scale.go:95-97 */                          \
+      "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"                                                      \
+      "}"                                                                                        \
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)                                              \
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),       \
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "n"(kUpCool),                     \
+        "n"(kUpNoop - kUpCool), "n"(kUpApp - kUpNoop), "n"(kDownCool), "n"(kDownNoop - kDownCool), \
+        "n"(kDownApp - kDownNoop))
+  if constexpr (ORDERED)
+    KSA_STEP_FMA_BODY("setp.le.s64 dh, %4, %6;\n\t");
+  else
+    KSA_STEP_FMA_BODY("setp.gt.and.s32 ucool, %2, %11, uh;\n\t"
+                      "setp.le.and.s64 dh, %4, %6, !ucool;\n\t");
+#undef KSA_STEP_FMA_BODY
+  return ev;
+}
+
+// The sweep's step when every policy of the launch is ORDERED and has thresholds that fit 32 bits
+// (INT_MIN < up <= INT_MAX, INT_MIN <= down < INT_MAX; the host checks). `n32` is the attribute
+// sum saturated to int32, computed once per (trace, tick) and shared by all policies of the
+// thread; under those bounds  n >= up <=> sat(n) >= up  and  n <= down <=> sat(n) <= down
+// (a sum beyond int32 saturates to a value that is still on the same side of both thresholds).
+// Two ISETP less than ksa_step_fma<true, true>. Returns the wide event code.
+__device__ __forceinline__ unsigned ksa_step_fma_narrow(int up_thr, int down_thr, const ksa_step_consts& c,
+                                                        int n32, int i, int one, ksa_trace_regs& s) {
   unsigned ev;
   asm("{\n\t"
-      ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dcool, dapp;\n\t"
+      ".reg .pred uh, ugo, uapp, dh, dgo, dapp;\n\t"
       ".reg .s32 t, u;\n\t"
-      "setp.ge.s64 uh, %4, %5;\n\t"                 // main.go:51
-      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"       // main.go:52
-      "setp.gt.and.s32 ucool, %2, %11, uh;\n\t"
+      "setp.ge.s32 uh, %4, %5;\n\t"                 // main.go:51
+      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"       // main.go:52 false
       "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
       "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"      // main.go:62   su = i + cu
-      "selp.u32 %0, 16, 0, ucool;\n\t"
-      "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"         // UP_NOOP unless ...
-      "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"       // ... UP_APPLIED
+      "selp.u32 %0, %15, 0, uh;\n\t"
+      "@ugo mad.lo.s32 %0, %14, %16, %0;\n\t"
+      "@uapp mad.lo.s32 %0, %14, %17, %0;\n\t"
       "add.s32 t, %1, %9;\n\t"                      // scale.go:66
       "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
       "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
-      "setp.le.and.s64 dh, %4, %6, !ucool;\n\t"     // main.go:65 (+ :54)
-      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"       // main.go:66
-      "setp.gt.and.s32 dcool, %3, %11, dh;\n\t"
+      "setp.le.s32 dh, %4, %6;\n\t"                 // main.go:65
+      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"       // main.go:66 false
       "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
       "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"      // main.go:76   sd = i + cd
-      "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
-      "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
-      "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
+      "@dh mad.lo.s32 %0, %14, %18, %0;\n\t"
+      "@dgo mad.lo.s32 %0, %14, %19, %0;\n\t"
+      "@dapp mad.lo.s32 %0, %14, %20, %0;\n\t"
       "sub.s32 u, %1, %10;\n\t"                     // scale.go:94
       "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
       "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
       "}"
       : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
-      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
-        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one));
+      : "r"(n32), "r"(up_thr), "r"(down_thr), "r"(c.max32), "r"(c.min32), "r"(c.up32),
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "n"((int)KSA_W_UP_COOL),
+        "n"((int)KSA_W_UP_NOOP - (int)KSA_W_UP_COOL), "n"((int)KSA_W_UP_APPLIED - (int)KSA_W_UP_NOOP),
+        "n"((int)KSA_W_DOWN_COOL), "n"((int)KSA_W_DOWN_NOOP - (int)KSA_W_DOWN_COOL),
+        "n"((int)KSA_W_DOWN_APPLIED - (int)KSA_W_DOWN_NOOP));
   return ev;
+}
+__device__ __forceinline__ int ksa_saturate_s32(long long n) {
+  int r;
+  asm("cvt.sat.s32.s64 %0, %1;" : "=r"(r) : "l"(n));
+  return r;
 }
 
 // The step in a world where calls fail (the *_faults entry points). `f` carries the KSA_FAIL_* bits
@@ -225,8 +314,18 @@ __device__ __forceinline__ unsigned ksa_step_faults(const ksa_step_consts& c, lo
 
 // ksa_step_faults with the conditional moves / adds as predicated IMADs (see ksa_step_fma).
 // `ucont` = the up half `continue`d (cool-down or failed call) = up_hit && !up_go.
+template <bool WIDE = false>
 __device__ __forceinline__ unsigned ksa_step_faults_fma(const ksa_step_consts& c, long long n, unsigned f,
                                                         int i, int one, ksa_trace_regs& s) {
+  constexpr int kUpCool = WIDE ? (int)KSA_W_UP_COOL : KSA_EV_UP_COOL;
+  constexpr int kUpNoop = WIDE ? (int)KSA_W_UP_NOOP : KSA_EV_UP_NOOP;
+  constexpr int kUpApp = WIDE ? (int)KSA_W_UP_APPLIED : KSA_EV_UP_APPLIED;
+  constexpr int kUpFail = WIDE ? (int)KSA_W_UP_FAILED : KSA_EV_UP_FAILED;
+  constexpr int kDownCool = WIDE ? (int)KSA_W_DOWN_COOL : KSA_EV_DOWN_COOL;
+  constexpr int kDownNoop = WIDE ? (int)KSA_W_DOWN_NOOP : KSA_EV_DOWN_NOOP;
+  constexpr int kDownApp = WIDE ? (int)KSA_W_DOWN_APPLIED : KSA_EV_DOWN_APPLIED;
+  constexpr int kDownFail = WIDE ? (int)KSA_W_DOWN_FAILED : KSA_EV_DOWN_FAILED;
+  constexpr int kPollFail = WIDE ? (int)(KSA_W_UP_FAILED | KSA_W_DOWN_FAILED) : KSA_EV_POLL_FAILED;
   unsigned ev;
   asm("{\n\t"
       ".reg .pred pok, uh, ureach, ucool, ufail, ugo, uapp, ucont, dh, dreach, dcool, dfail, dgo, dapp;\n\t"
@@ -242,10 +341,10 @@ __device__ __forceinline__ unsigned ksa_step_faults_fma(const ksa_step_consts& c
       "setp.eq.and.u32 ugo, fb, 0, ureach;\n\t"     // ScaleUp returned nil
       "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
       "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"      // main.go:62   su = i + cu
-      "selp.u32 %0, 16, 0, ucool;\n\t"
-      "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"
-      "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"
-      "@ufail mad.lo.s32 %0, %14, 64, %0;\n\t"      // KSA_EV_UP_FAILED
+      "selp.u32 %0, %16, 0, ucool;\n\t"
+      "@ugo mad.lo.s32 %0, %14, %17, %0;\n\t"
+      "@uapp mad.lo.s32 %0, %14, %18, %0;\n\t"
+      "@ufail mad.lo.s32 %0, %14, %19, %0;\n\t"     // UP_FAILED
       "add.s32 t, %1, %9;\n\t"                      // scale.go:66
       "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
       "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
@@ -259,18 +358,20 @@ __device__ __forceinline__ unsigned ksa_step_faults_fma(const ksa_step_consts& c
       "setp.eq.and.u32 dgo, fb, 0, dreach;\n\t"
       "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
       "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"      // main.go:76   sd = i + cd
-      "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
-      "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
-      "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
-      "@dfail mad.lo.s32 %0, %14, 128, %0;\n\t"     // KSA_EV_DOWN_FAILED
+      "@dcool mad.lo.s32 %0, %14, %20, %0;\n\t"
+      "@dgo mad.lo.s32 %0, %14, %21, %0;\n\t"
+      "@dapp mad.lo.s32 %0, %14, %22, %0;\n\t"
+      "@dfail mad.lo.s32 %0, %14, %23, %0;\n\t"     // DOWN_FAILED
       "sub.s32 u, %1, %10;\n\t"                     // scale.go:94
       "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
       "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
-      "@!pok mov.u32 %0, 192;\n\t"                  // KSA_EV_POLL_FAILED, main.go:45
+      "@!pok mov.u32 %0, %24;\n\t"                  // POLL_FAILED, main.go:45
       "}"
       : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
       : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
-        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "r"(f));
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "r"(f), "n"(kUpCool), "n"(kUpNoop),
+        "n"(kUpApp - kUpNoop), "n"(kUpFail), "n"(kDownCool), "n"(kDownNoop), "n"(kDownApp - kDownNoop),
+        "n"(kDownFail), "n"(kPollFail));
   return ev;
 }
 
@@ -293,65 +394,74 @@ __device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c)
 // i.e. at least every KSA_FLUSH_TICKS ticks (ksa_summary_flush).
 struct ksa_summary_acc {
   int rmin, rmax;
-  unsigned pk4, pk2;
-  unsigned pkf;  // *_faults kernels only: UP_FAILED bit at field 0, DOWN_FAILED at 8, failed polls at 16
+  unsigned pk;        // six 5-bit event counters, field k at bit 5k (bits 30-31: don't care)
+  unsigned lva, lvb;  // second level, 10-bit fields: lva = events 0, 2, 4 at bits 0, 10, 20; lvb = 1, 3, 5
+  unsigned pkf;       // *_faults kernels only, 10-bit fields: up_failed at 0, down_failed at 10, failed polls at 20
   long long sum;
-  unsigned long long hash;
+  unsigned ha, hb;    // the two lanes of the fingerprint
 };
-#define KSA_FLUSH_TICKS 255
+// pk is folded into lva/lvb after at most KSA_FOLD_TICKS ticks, those are flushed to the 32-bit
+// counters of the record after at most KSA_FLUSH_FOLDS folds (30 * 31 = 930, plus the at most 93 ticks
+// that the end of a kernel adds before its last flush: <= 1023).
+#define KSA_FOLD_TICKS 31
+#define KSA_FLUSH_FOLDS 30
 
-// Trajectory fingerprint step (ksa_summary.hash, include/ksa_replay.h):
-//   h <- h * M + ((uint64)event << 32 | (uint32)replicas)
-// Three IMADs on the FMA pipe; the addend needs no shifting or masking.
-#define KSA_HASH_MUL 0x9E3779B97F4A7C15ull
-__device__ __forceinline__ unsigned long long ksa_hash_step(unsigned long long h, int r, unsigned ev) {
-  return h * KSA_HASH_MUL + (((unsigned long long)ev << 32) | (unsigned long long)(unsigned)r);
+// Trajectory fingerprint (ksa_summary.hash, include/ksa_replay.h): two 32-bit lanes,
+//   lo <- lo * KSA_HASH_MUL_LO + (uint32)replicas      hi <- hi * KSA_HASH_MUL_HI + wide_event
+// one IMAD each; hash = hi << 32 | lo.
+#define KSA_HASH_MUL_LO 0x9E3779B1u
+#define KSA_HASH_MUL_HI 0x85EBCA6Bu
+__host__ __device__ __forceinline__ unsigned long long ksa_hash_step(unsigned long long h, int r, unsigned ev) {
+  const unsigned lo = (unsigned)h * KSA_HASH_MUL_LO + (unsigned)r;
+  const unsigned hi = (unsigned)(h >> 32) * KSA_HASH_MUL_HI + ksa_wide_event(ev);
+  return ((unsigned long long)hi << 32) | lo;
 }
 
-// One tick of summary accumulation. FMA = true spells the adds as IMADs by `one` (FMA pipe).
-// `ev6` = the low six event bits (the *_faults kernels mask the two failure bits off; everywhere
-// else ev6 == ev).
+// One tick of summary accumulation; `w` = the wide event code of the tick. FMA = true spells the
+// adds as IMADs by `one` (FMA pipe).
 template <bool FMA>
-__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned ev, unsigned ev6,
-                                                 int one) {
+__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned w, int one) {
   m.rmin = min(m.rmin, r);
   m.rmax = max(m.rmax, r);
-  // spread event bits 0..3 into four byte fields, bits 4..5 into two: one IMAD + one LOP3 each.
-  // ev6 < 64, so the shifted copies (shifts 0/7/14/21 and 4/11) never overlap: no carries.
-  const unsigned f4 = (ev6 * 0x00204081u) & 0x01010101u;
-  const unsigned f2 = (ev6 * 0x00000810u) & 0x00010100u;
   if constexpr (FMA) {
-    m.pk4 = ksa_mad_u32(f4, (unsigned)one, m.pk4);
-    m.pk2 = ksa_mad_u32(f2, (unsigned)one, m.pk2);
+    m.pk = ksa_mad_u32(w, (unsigned)one, m.pk);
     m.sum = ksa_mad_wide_s32(r, one, m.sum);
   } else {
-    m.pk4 += f4;
-    m.pk2 += f2;
+    m.pk += w;
     m.sum = (long long)((unsigned long long)m.sum + (unsigned long long)(long long)r);
   }
-  m.hash = ksa_hash_step(m.hash, r, ev);
+  m.ha = m.ha * KSA_HASH_MUL_LO + (unsigned)r;
+  m.hb = m.hb * KSA_HASH_MUL_HI + w;
 }
 
 // Failure counters of the *_faults kernels. `f` is the KSA_FAIL_* input byte: a poll fails exactly
-// when its bit is set, and a failed poll shows as both failure bits in the event byte.
-__device__ __forceinline__ void ksa_summary_tick_faults(ksa_summary_acc& m, unsigned ev, unsigned f) {
-  m.pkf += (((ev >> 6) * 0x81u) & 0x101u) + ((f & KSA_FAIL_POLL) << 16);
-}
-__device__ __forceinline__ void ksa_summary_flush_faults(ksa_summary_acc& m, ksa_summary* q) {
-  const unsigned polls = (m.pkf >> 16) & 0xffu;
-  q->poll_failed += polls;
-  q->up_failed += (m.pkf & 0xffu) - polls;
-  q->down_failed += ((m.pkf >> 8) & 0xffu) - polls;
-  m.pkf = 0u;
+// when its bit is set, and a failed poll shows as both failure bits in the event code.
+__device__ __forceinline__ void ksa_summary_tick_faults(ksa_summary_acc& m, unsigned w, unsigned f) {
+  m.pkf += (((w >> 30) * 0x201u) & 0x401u) + ((f & KSA_FAIL_POLL) << 20);
 }
 
-// Add the packed fields into the 32-bit counters of a ksa_summary record and clear them.
+// First level: move the 5-bit fields into the 10-bit ones.
+__device__ __forceinline__ void ksa_summary_fold(ksa_summary_acc& m) {
+  m.lva += m.pk & 0x01F07C1Fu;
+  m.lvb += (m.pk >> 5) & 0x01F07C1Fu;
+  m.pk = 0u;
+}
+
+// Second level: fold, then add the 10-bit fields into the 32-bit counters of a ksa_summary record.
 __device__ __forceinline__ void ksa_summary_flush(ksa_summary_acc& m, ksa_summary* q) {
-  q->up_applied += m.pk4 & 0xffu;
-  q->down_applied += (m.pk4 >> 8) & 0xffu;
-  q->up_noop += (m.pk4 >> 16) & 0xffu;
-  q->down_noop += m.pk4 >> 24;
-  q->up_cool += (m.pk2 >> 8) & 0xffu;
-  q->down_cool += (m.pk2 >> 16) & 0xffu;
-  m.pk4 = m.pk2 = 0u;
+  ksa_summary_fold(m);
+  q->up_applied += m.lva & 0x3ffu;
+  q->up_noop += (m.lva >> 10) & 0x3ffu;
+  q->up_cool += (m.lva >> 20) & 0x3ffu;
+  q->down_applied += m.lvb & 0x3ffu;
+  q->down_noop += (m.lvb >> 10) & 0x3ffu;
+  q->down_cool += (m.lvb >> 20) & 0x3ffu;
+  m.lva = m.lvb = 0u;
+}
+__device__ __forceinline__ void ksa_summary_flush_faults(ksa_summary_acc& m, ksa_summary* q) {
+  const unsigned polls = (m.pkf >> 20) & 0x3ffu;
+  q->poll_failed += polls;
+  q->up_failed += (m.pkf & 0x3ffu) - polls;
+  q->down_failed += ((m.pkf >> 10) & 0x3ffu) - polls;
+  m.pkf = 0u;
 }

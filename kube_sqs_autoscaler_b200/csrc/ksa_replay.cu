@@ -167,7 +167,6 @@ __device__ __forceinline__ void load_fail(const unsigned char* p, unsigned (&w)[
 }
 
 typedef ksa_summary_acc SummaryRegs;
-constexpr int kFlushTicks = KSA_FLUSH_TICKS;
 
 template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
@@ -178,7 +177,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
   constexpr bool FAULTS = (STEP == 4 || STEP == 5);
-  constexpr bool FMA = (STEP == 2 || STEP == 5);
+  constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6);
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -194,11 +193,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       const ksa_summary* q = a.summary + n0 + v;
       sm[v].rmin = q->min_replicas;
       sm[v].rmax = q->max_replicas;
-      sm[v].pk4 = sm[v].pk2 = sm[v].pkf = 0u;
+      sm[v].pk = sm[v].lva = sm[v].lvb = sm[v].pkf = 0u;
       sm[v].sum = q->sum_replicas;
-      sm[v].hash = q->hash;
+      sm[v].ha = (unsigned)q->hash;
+      sm[v].hb = (unsigned)(q->hash >> 32);
     }
   }
+  auto fold_counters = [&]() {
+    if constexpr (MODE == MODE_SUMMARY) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) ksa_summary_fold(sm[v]);
+    }
+  };
   auto flush_counters = [&]() {
     if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
@@ -233,6 +239,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       if (j < T) load_fail<V>(fp + (long long)j * a.ld, fbuf[j]);
   }
 
+  // Summary mode only: the wide event code of the previous tick of each trace. Bit 4 of a wide
+  // code is always 0 (a field counts one event per tick), which ptxas cannot know; xor-ing that bit
+  // into the next tick's depth changes nothing but makes the next tick's threshold compares wait
+  // for this tick. Without it ptxas hoists the compares of all D unrolled ticks to the top of the
+  // loop body, runs out of its 7 predicate registers and keeps them as bits of a general register
+  // (62 LOP3 + 9 P2R per 8 decisions in SASS).
+  unsigned taint[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) taint[v] = 0u;
+
   auto tick = [&](const int tt, const int j, const bool prefetch) {
     long long n[V];
 #pragma unroll
@@ -240,6 +256,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       unsigned long long acc = (unsigned long long)buf[j][0][v];  // sqs.go:56-64, wrapping
 #pragma unroll
       for (int p = 1; p < A; ++p) acc += (unsigned long long)buf[j][p][v];
+      if constexpr (MODE == MODE_SUMMARY && FMA) {
+        unsigned lo = (unsigned)acc;
+        asm("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(lo) : "r"(taint[v]));  // lo ^ (taint & 16)
+        acc = (acc & 0xffffffff00000000ull) | lo;
+      }
       n[v] = (long long)acc;
     }
     unsigned fw[(V + 3) / 4];
@@ -255,21 +276,28 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     }
     const int i = tt + 1;  // local tick, 1-based
     int rr[V];
-    unsigned ev[V];
+    unsigned ev[V];  // the event byte; in summary mode the wide event code (ksa_wide_event)
     unsigned fv[V];
+    constexpr bool WIDE = MODE == MODE_SUMMARY;
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       fv[v] = 0u;
       if constexpr (FAULTS) {
         fv[v] = (fw[v / 4] >> (8 * (v % 4))) & 0xffu;
-        ev[v] = STEP == 5 ? ksa_step_faults_fma(c, n[v], fv[v], i, one, s[v])
-                          : ksa_step_faults(c, n[v], fv[v], i, s[v]);
-      } else if constexpr (STEP >= 2)
-        ev[v] = ksa_step_fma(c, n[v], i, one, s[v]);
+        if constexpr (STEP == 5)
+          ev[v] = ksa_step_faults_fma<WIDE>(c, n[v], fv[v], i, one, s[v]);
+        else
+          ev[v] = ksa_step_faults(c, n[v], fv[v], i, s[v]);
+      } else if constexpr (STEP == 6)
+        ev[v] = ksa_step_fma<WIDE, true>(c, n[v], i, one, s[v]);
+      else if constexpr (STEP >= 2)
+        ev[v] = ksa_step_fma<WIDE>(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
         ev[v] = ksa_step_ptx(c, n[v], i, s[v]);
       else
         ev[v] = ksa_step(c, n[v], i, s[v]);
+      if constexpr (WIDE && !FMA) ev[v] = ksa_wide_event(ev[v]);
+      taint[v] = ev[v];
       rr[v] = s[v].r;
     }
     if constexpr (MODE != MODE_SUMMARY) {
@@ -278,14 +306,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     } else {
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], FAULTS ? (ev[v] & 0x3fu) : ev[v], one);
+        ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], one);
         if constexpr (FAULTS) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
       }
     }
   };
 
   int t = 0;
-  int pending = 0;  // ticks accumulated in the packed counters
+  int pending = 0;  // ticks accumulated in the 5-bit counters
+  int folds = 0;    // folds accumulated in the 10-bit counters
   // Steady state: every tick of the group exists and so does the tick D ahead of it.
 #pragma unroll 1
   for (; t + 2 * D <= T; t += D) {
@@ -293,21 +322,25 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     for (int j = 0; j < D; ++j) tick(t + j, j, true);
     if constexpr (MODE == MODE_SUMMARY) {
       pending += D;
-      if (pending > kFlushTicks - D) {
-        flush_counters();
+      if (pending > KSA_FOLD_TICKS - D) {
         pending = 0;
+        if (++folds == KSA_FLUSH_FOLDS) {
+          flush_counters();
+          folds = 0;
+        } else {
+          fold_counters();
+        }
       }
     }
   }
+  fold_counters();  // the drain adds up to 2D-1 ticks
   // Drain: at most 2D-1 ticks left; guard both the tick and its prefetch.
 #pragma unroll 1
   for (; t < T; t += D) {
 #pragma unroll
     for (int j = 0; j < D; ++j)
       if (t + j < T) tick(t + j, j, t + j + D < T);
-    if constexpr (MODE == MODE_SUMMARY) {
-      flush_counters();
-    }
+    fold_counters();
   }
 
 #pragma unroll
@@ -325,7 +358,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       q->min_replicas = sm[v].rmin;
       q->max_replicas = sm[v].rmax;
       q->sum_replicas = sm[v].sum;
-      q->hash = sm[v].hash;
+      q->hash = ((unsigned long long)sm[v].hb << 32) | sm[v].ha;
     }
   }
 }
@@ -336,6 +369,7 @@ typedef void (*replay_kernel_fn)(const ReplayArgs);
 // kernels use a shallower ring / fewer traces per thread than the A = 1 kernel of the same id.
 struct Variant {
   int id;
+  int step;            // STEP template argument (6 = only valid for ordered policies)
   int V[3], block[3];  // per A-1
   const char* name;
   replay_kernel_fn fn[3];  // indexed by A-1
@@ -344,7 +378,7 @@ struct Variant {
 #define KSA_K(A, V, D, HINT, MODE, STEP, BLOCK, MINB) ksa_replay_kernel<A, V, D, HINT, MODE, STEP, BLOCK, MINB>
 // A=1 tuning point (V, D, HINT, STEP, BLOCK, MINB); A=2 and A=3 points (V, D, BLOCK, MINB) share HINT/STEP.
 #define KSA_VARIANT(ID, MODE, V, D, HINT, STEP, BLOCK, MINB, V2, D2, B2, M2, V3, D3, B3, M3)   \
-  {ID, {V, V2, V3}, {BLOCK, B2, B3}, "V" #V "_D" #D "_H" #HINT "_S" #STEP "_B" #BLOCK "x" #MINB, \
+  {ID, STEP, {V, V2, V3}, {BLOCK, B2, B3}, "V" #V "_D" #D "_H" #HINT "_S" #STEP "_B" #BLOCK "x" #MINB, \
    {KSA_K(1, V, D, HINT, MODE, STEP, BLOCK, MINB), KSA_K(2, V2, D2, HINT == HINT_NA_EF && V2 < 4 ? HINT_NA : HINT, MODE, STEP, B2, M2),                  \
     KSA_K(3, V3, D3, HINT == HINT_NA_EF && V3 < 4 ? HINT_NA : HINT, MODE, STEP, B3, M3)}}
 
@@ -378,6 +412,18 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(9, MODE_SUMMARY, 4, 4, HINT_NA, 2, 128, 4, 4, 2, 128, 4, 4, 2, 128, 3),
     KSA_VARIANT(10, MODE_SUMMARY, 8, 2, HINT_NA, 2, 128, 3, 4, 3, 128, 3, 4, 2, 128, 3),
     KSA_VARIANT(12, MODE_SUMMARY, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(13, MODE_SUMMARY, 1, 4, HINT_NA, 2, 128, 12, 1, 2, 128, 12, 1, 2, 128, 10),
+    KSA_VARIANT(14, MODE_SUMMARY, 1, 6, HINT_NA, 2, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
+    KSA_VARIANT(15, MODE_SUMMARY, 1, 8, HINT_NA, 2, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
+    KSA_VARIANT(16, MODE_SUMMARY, 1, 12, HINT_NA, 2, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
+    KSA_VARIANT(17, MODE_SUMMARY, 1, 16, HINT_NA, 2, 128, 6, 1, 8, 128, 6, 1, 5, 128, 6),
+    KSA_VARIANT(18, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
+    KSA_VARIANT(19, MODE_SUMMARY, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
+    KSA_VARIANT(20, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    // STEP 6: for policies with scale_up_messages > scale_down_messages only (ksa_step_fma ORDERED);
+    // replay_common substitutes the general default when the policy is not ordered.
+    KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    KSA_VARIANT(22, MODE_SUMMARY, 2, 4, HINT_NA, 6, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
 };
 // The *_faults entry points: one vector kernel + the scalar kernel per mode (STEP 4).
 const Variant kFullFaultsVariants[] = {
@@ -395,7 +441,8 @@ const Variant kSummaryFaultsVariants[] = {
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
-constexpr int kDefaultSummary = 12;  // summary mode is ALU-bound: few traces per thread, high occupancy
+constexpr int kDefaultSummary = 20;  // one trace per thread: no interleaved state machines, no predicate spills
+constexpr int kDefaultSummaryOrdered = 21;  // the same with the ordered-thresholds step
 
 template <size_t K>
 const Variant* find_variant(const Variant (&table)[K], int id) {
@@ -445,9 +492,12 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   args.summary = summary_dev;
 
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
+  const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
+  const int default_summary = ordered ? kDefaultSummaryOrdered : kDefaultSummary;
   const Variant* var = mode == MODE_FULL
                            ? find_variant(kFullVariants, want < 0 ? kDefaultFull : want)
-                           : find_variant(kSummaryVariants, want < 0 ? kDefaultSummary : want);
+                           : find_variant(kSummaryVariants, want < 0 ? default_summary : want);
+  if (var && var->step == 6 && !ordered) var = find_variant(kSummaryVariants, kDefaultSummary);
   // Variants compiled for "both outputs" cannot run with one of them missing.
   if (!faults && mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
   const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];

@@ -26,7 +26,10 @@ struct SweepArgs {
   ksa_summary* summary;  // [P][N]
 };
 
-template <int A, int R, int D, int BLOCK, int MINB, int CHAIN>
+// FAST = every policy of the launch has scale_up_messages > scale_down_messages and thresholds
+// that fit 32 bits (sweep_policies_fast below): the step is ksa_step_fma_narrow on the attribute
+// sum saturated once per tick, 6 compares per decision instead of 9.
+template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, bool FAST>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
@@ -49,14 +52,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
     s[q].sd = ksa_local_stamp(pk[q].cd, c.cd, 0, 0);  // main.go:37-38
     m[q].rmin = INT_MAX;
     m[q].rmax = INT_MIN;
-    m[q].pk4 = m[q].pk2 = 0u;
+    m[q].pk = m[q].lva = m[q].lvb = 0u;
     m[q].sum = 0;
-    m[q].hash = 0ull;
+    m[q].ha = m[q].hb = 0u;
     if (p0 + q < a.P) {  // counters live in the output record; start them at zero
       ksa_summary* z = a.summary + (long long)(p0 + q) * a.N + n;
       z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
     }
   }
+  auto fold = [&]() {
+#pragma unroll
+    for (int q = 0; q < R; ++q) ksa_summary_fold(m[q]);
+  };
   auto flush = [&]() {
 #pragma unroll
     for (int q = 0; q < R; ++q)
@@ -75,7 +82,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
 #pragma unroll
   for (int j = 0; j < D; ++j) buf[j] = j < T ? load_sum(j) : 0;
 
-  int pending = 0;
+  int pending = 0, folds = 0;
 #pragma unroll 1
   for (int t = 0; t < T; t += D) {
 #pragma unroll
@@ -86,28 +93,42 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
         if (tt + D < T) buf[j] = load_sum(tt + D);
         const int i = tt + 1;
         // CHAIN > 0: the R machines run in groups of CHAIN. The first compare of a group is made
-        // to wait for the last event of the previous group through an add that changes nothing
-        // (an event byte is < 256, so ev >> 8 == 0, which ptxas cannot know). Without it ptxas
+        // to wait for the last event of the previous group through a xor that changes nothing
+        // (bit 4 of a wide event code is always 0, which ptxas cannot know). Without it ptxas
         // interleaves all R machines, runs out of its 7 predicate registers and spills them into
         // a general register (13 LOP3 + 3 P2R per decision at R = 4).
-        long long m_in = msgs;
+        unsigned m_lo = (unsigned)(unsigned long long)msgs;
+        const unsigned m_hi = (unsigned)((unsigned long long)msgs >> 32);
+        int m32 = FAST ? ksa_saturate_s32(msgs) : 0;
         unsigned ev_last = 0u;
 #pragma unroll
         for (int q = 0; q < R; ++q) {
           const ksa_step_consts c(pk[q]);
-          if (CHAIN > 0 && q > 0 && q % CHAIN == 0)
-            asm volatile("{\n\t.reg .u32 z;\n\t.reg .u64 zz;\n\tshr.u32 z, %1, 8;\n\t"
-                         "cvt.u64.u32 zz, z;\n\tadd.s64 %0, %0, zz;\n\t}" : "+l"(m_in) : "r"(ev_last));
-          const unsigned ev = ksa_step_fma(c, m_in, i, one, s[q]);
+          if (CHAIN > 0 && q > 0 && q % CHAIN == 0) {
+            if constexpr (FAST)
+              asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m32) : "r"(ev_last));  // m32 ^ (ev & 16)
+            else
+              asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m_lo) : "r"(ev_last));
+          }
+          unsigned ev;  // wide event code
+          if constexpr (FAST)
+            ev = ksa_step_fma_narrow((int)pk[q].up_msgs, (int)pk[q].down_msgs, c, m32, i, one, s[q]);
+          else
+            ev = ksa_step_fma<true>(c, (long long)(((unsigned long long)m_hi << 32) | m_lo), i, one, s[q]);
           ev_last = ev;
-          ksa_summary_tick<true>(m[q], s[q].r, ev, ev, one);
+          ksa_summary_tick<true>(m[q], s[q].r, ev, one);
         }
       }
     }
     pending += D;
-    if (pending > KSA_FLUSH_TICKS - D) {
-      flush();
+    if (pending > KSA_FOLD_TICKS - D) {
       pending = 0;
+      if (++folds == KSA_FLUSH_FOLDS) {
+        flush();
+        folds = 0;
+      } else {
+        fold();
+      }
     }
   }
   flush();
@@ -121,7 +142,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
       z->max_replicas = m[q].rmax;
       z->poll_failed = z->up_failed = z->down_failed = 0u;
       z->sum_replicas = m[q].sum;
-      z->hash = m[q].hash;
+      z->hash = ((unsigned long long)m[q].hb << 32) | m[q].ha;
     }
   }
 }
@@ -155,14 +176,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
     s[v].sd = ksa_local_stamp(pk.cd, c.cd, 0, 0);  // main.go:37-38
     m[v].rmin = INT_MAX;
     m[v].rmax = INT_MIN;
-    m[v].pk4 = m[v].pk2 = 0u;
+    m[v].pk = m[v].lva = m[v].lvb = 0u;
     m[v].sum = 0;
-    m[v].hash = 0ull;
+    m[v].ha = m[v].hb = 0u;
     if (have[v]) {  // counters live in the output record; start them at zero
       ksa_summary* z = a.summary + (long long)p * a.N + n0 + v;
       z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
     }
   }
+  auto fold = [&]() {
+#pragma unroll
+    for (int v = 0; v < V; ++v) ksa_summary_fold(m[v]);
+  };
   auto flush = [&]() {
 #pragma unroll
     for (int v = 0; v < V; ++v)
@@ -184,7 +209,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
 #pragma unroll
     for (int v = 0; v < V; ++v) buf[j][v] = j < T ? load_sum(j, v) : 0;
 
-  int pending = 0;
+  int pending = 0, folds = 0;
 #pragma unroll 1
   for (int t = 0; t < T; t += D) {
 #pragma unroll
@@ -201,15 +226,20 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
         const int i = tt + 1;
 #pragma unroll
         for (int v = 0; v < V; ++v) {
-          const unsigned ev = ksa_step_fma(c, msgs[v], i, one, s[v]);
-          ksa_summary_tick<true>(m[v], s[v].r, ev, ev, one);
+          const unsigned ev = ksa_step_fma<true>(c, msgs[v], i, one, s[v]);  // wide event code
+          ksa_summary_tick<true>(m[v], s[v].r, ev, one);
         }
       }
     }
     pending += D;
-    if (pending > KSA_FLUSH_TICKS - D) {
-      flush();
+    if (pending > KSA_FOLD_TICKS - D) {
       pending = 0;
+      if (++folds == KSA_FLUSH_FOLDS) {
+        flush();
+        folds = 0;
+      } else {
+        fold();
+      }
     }
   }
   flush();
@@ -223,7 +253,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
       z->max_replicas = m[v].rmax;
       z->poll_failed = z->up_failed = z->down_failed = 0u;
       z->sum_replicas = m[v].sum;
-      z->hash = m[v].hash;
+      z->hash = ((unsigned long long)m[v].hb << 32) | m[v].ha;
     }
   }
 }
@@ -233,15 +263,22 @@ struct SweepVariant {
   int R;      // register-tile kernel: policies per thread; lane kernel: 0
   int V;      // lane kernel: traces per thread
   int block;
-  sweep_fn fn[3];  // indexed by A-1
+  sweep_fn fn[3];       // indexed by A-1
+  sweep_fn fast_fn[3];  // FAST instantiation (register-tile kernels), else the same as fn
 };
 #define KSA_SWEEP_CH(R, D, BLOCK, MINB, CH)                                                        \
-  {R, 0, BLOCK, {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH>, \
-                 ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH>}}
+  {R, 0, BLOCK,                                                                                    \
+   {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, false>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, false>, \
+    ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, false>},                                            \
+   {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, true>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, true>, \
+    ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, true>}}
 #define KSA_SWEEP(R, D, BLOCK, MINB) KSA_SWEEP_CH(R, D, BLOCK, MINB, 0)
 #define KSA_SWEEP_LANE(V, D, BLOCK, MINB)                                                        \
-  {0, V, BLOCK, {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>, \
-                 ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}}
+  {0, V, BLOCK,                                                                                  \
+   {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>,    \
+    ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>},                                                \
+   {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>,    \
+    ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}}
 // Tuning points; KSA_SWEEP_VARIANT=<index> (environment) overrides the default for measurements.
 const SweepVariant kSweepVariants[] = {
     KSA_SWEEP(4, 4, 128, 3), KSA_SWEEP(2, 4, 128, 6), KSA_SWEEP(4, 2, 128, 4), KSA_SWEEP(2, 4, 256, 3),
@@ -257,6 +294,21 @@ constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVa
 constexpr int kDefaultSweep = 16;  // R=4 in chained groups of 2, D=4, 128x3: 107.0 ms on configs[3]
                                    // (unchained 115.6 ms; lane kernels 123 ms at V=2, 158 ms at V=1);
                                    // profiles/r01_config4_sweep_tune.txt
+
+// Whether the FAST kernels are exact for this grid (see ksa_step_fma_narrow): thresholds ordered
+// and inside the range where comparing the saturated sum is the same as comparing the sum.
+// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels, for measurements and tests.
+bool sweep_policies_fast(const ksa_policy* policies, int P) {
+  if (const char* e = std::getenv("KSA_SWEEP_GENERAL"))
+    if (std::atoi(e) != 0) return false;
+  for (int q = 0; q < P; ++q) {
+    const long long up = policies[q].scale_up_messages, down = policies[q].scale_down_messages;
+    if (!(up > down && up > (long long)INT_MIN && up <= (long long)INT_MAX && down >= (long long)INT_MIN &&
+          down < (long long)INT_MAX))
+      return false;
+  }
+  return true;
+}
 
 // Grid of a sweep launch, or false if it does not fit one launch.
 bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
@@ -314,7 +366,7 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   dim3 grid;
   if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
   if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
-  v.fn[A - 1]<<<grid, v.block, 0, st>>>(a);
+  (sweep_policies_fast(policies, P) ? v.fast_fn : v.fn)[A - 1]<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel");
   return KSA_OK;
 }
@@ -396,7 +448,7 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
   const SweepVariant& v = kSweepVariants[kDefaultSweep];
   dim3 grid;
   if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
-  v.fn[A - 1]<<<grid, v.block, 0, st>>>(a);
+  (sweep_policies_fast(policies, P) ? v.fast_fn : v.fn)[A - 1]<<<grid, v.block, 0, st>>>(a);
   KSA_LAUNCH_CHECK("ksa_sweep_kernel (static table)");
   return KSA_OK;
 }

@@ -15,7 +15,19 @@
 #include <string.h>
 #include <unistd.h>
 
-#define HASH_MUL 0x9E3779B97F4A7C15ull
+/* ksa_summary.hash (include/ksa_replay.h): two 32-bit lanes, event bits spread to 5-bit fields. */
+#define HASH_MUL_LO 0x9E3779B1u
+#define HASH_MUL_HI 0x85EBCA6Bu
+static uint32_t wide_event(uint32_t ev) {
+  uint32_t w = 0;
+  for (int k = 0; k < 6; ++k) w |= ((ev >> k) & 1u) << (5 * k);
+  return w | (((ev >> 6) & 1u) << 30) | (((ev >> 7) & 1u) << 31);
+}
+static uint64_t hash_step(uint64_t h, int32_t r, uint32_t ev) {
+  const uint32_t lo = (uint32_t)h * HASH_MUL_LO + (uint32_t)r;
+  const uint32_t hi = (uint32_t)(h >> 32) * HASH_MUL_HI + wide_event(ev);
+  return ((uint64_t)hi << 32) | lo;
+}
 
 /* Go's int32(x) on a Go int: keep the low 32 bits (scale/scale.go:62,66-68,89,94-96). */
 static inline int32_t go_int32(int64_t x) { return (int32_t)(uint32_t)(uint64_t)x; }
@@ -152,7 +164,7 @@ static inline void summary_add(ksa_summary* s, int32_t r, uint8_t ev) {
     s->down_failed += (ev & KSA_EV_DOWN_FAILED) != 0;
   }
   s->sum_replicas = wrap_add64(s->sum_replicas, (int64_t)r);
-  s->hash = s->hash * HASH_MUL + (((uint64_t)ev << 32) | (uint64_t)(uint32_t)r);
+  s->hash = hash_step(s->hash, r, ev);
 }
 
 void ksa_oracle_summary_clear(ksa_summary* s, int64_t N) {
@@ -283,7 +295,7 @@ void ksa_oracle_traj_hash(const int32_t* replicas, const uint8_t* events, int64_
   for (int64_t n = 0; n < N; ++n) {
     uint64_t h = chain ? hash[n] : 0;
     for (int64_t t = 0; t < T; ++t)
-      h = h * HASH_MUL + (((uint64_t)events[t * ld + n] << 32) | (uint64_t)(uint32_t)replicas[t * ld + n]);
+      h = hash_step(h, replicas[t * ld + n], events[t * ld + n]);
     hash[n] = h;
   }
 }

@@ -20,7 +20,7 @@ pytestmark = pytest.mark.gpu
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
 FULL_VARIANTS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41]   # -2 = scalar kernel
-SUMMARY_VARIANTS = [-2, 5, 7, 8, 9, 10, 12]
+SUMMARY_VARIANTS = [-2, 5, 7, 8, 9, 10, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22]  # 21, 22: ordered-thresholds step
 
 
 def torch_mod():
@@ -186,8 +186,8 @@ def test_random_policies_all_variants(engine, A):
         ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st, want_summary=True)
         cases.append((pol, T, N, ld, tick0, depth, st, ref))
     try:
-        for fv in FULL_VARIANTS:
-            sv = SUMMARY_VARIANTS[min(len(SUMMARY_VARIANTS) - 1, FULL_VARIANTS.index(fv))]
+        for k in range(max(len(FULL_VARIANTS), len(SUMMARY_VARIANTS))):
+            fv, sv = FULL_VARIANTS[k % len(FULL_VARIANTS)], SUMMARY_VARIANTS[k % len(SUMMARY_VARIANTS)]
             engine.set_variant(fv, sv)
             for pol, T, N, ld, tick0, depth, st, ref in cases:
                 out = gpu_full(engine, pol, depth, T, A, N, ld, tick0, st)
@@ -406,6 +406,51 @@ def test_policy_sweep_matches_oracle_per_policy(engine):
     for i, pol in enumerate(pols):
         ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, N, 0, *r0, want_full=False, want_summary=True)
         assert got[i].tobytes() == ref.summary.tobytes(), f"policy {i}: {pol}"
+
+
+def test_sweep_fast_path_edges_match_oracle(engine, monkeypatch):
+    """The sweep's narrow kernels (all policies ordered, thresholds inside int32) compare the
+    attribute sum saturated to int32. Grid with thresholds at the edges of the allowed range and
+    depths far outside int32, against the oracle, for every register-tile tuning point, and the
+    same grid through the general kernels (KSA_SWEEP_GENERAL=1)."""
+    torch = torch_mod()
+    rng = np.random.default_rng(99)
+    T, N, A = 97, 77, 2
+    special = np.array([2**31 - 1, 2**31, 2**31 + 1, -(2**31), -(2**31) - 1, -(2**31) + 1, 2**40, -(2**40),
+                        2**62, -(2**62), 0, 1, -1, 100, 10], dtype=np.int64)
+    d_host = rng.integers(-50, 400, size=(T, A, N), dtype=np.int64)
+    pick = rng.integers(0, 3, size=(T, A, N)) == 0
+    d_host[pick] = special[rng.integers(0, special.size, size=int(pick.sum()))]
+    pols = []
+    for up, down in ((100, 10), (2**31 - 1, 2**31 - 2), (2**31 - 1, -(2**31)), (-(2**31) + 1, -(2**31)),
+                     (1, 0), (0, -1), (300, 299), (2**31 - 1, 0)):
+        for cu, cd in ((0, 0), (10 * S, 15 * S)):
+            pols.append(ksa.Policy(attr_mask=3, scale_up_messages=up, scale_down_messages=down,
+                                   scale_up_cool_down=cu, scale_down_cool_down=cd, max_pods=7))
+    depth = torch.from_numpy(d_host).to(engine.dev)
+    r0 = oracle_lib.fresh_state(5, 0, N, 1, 7)
+    want = [oracle_lib.replay(p.to_c(), d_host, T, A, N, N, 0, *r0, want_full=False, want_summary=True).summary
+            for p in pols]
+    r0_dev = torch.from_numpy(r0[0]).to(engine.dev)
+    for general in ("0", "1"):
+        monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
+        for sv in (0, 1, 2, 5, 6, 7, 9, 16, 17, 18, 19, 20, 21, 22, 23):
+            monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
+            got = engine.replay_sweep(pols, depth, T, A, N, N, r0_dev).cpu().numpy().view(ksa.SUMMARY_DTYPE)
+            got = got.reshape(len(pols), N)
+            for i in range(len(pols)):
+                assert got[i].tobytes() == want[i].tobytes(), f"general={general} variant={sv} policy {i}: {pols[i]}"
+    # one unordered or out-of-range policy sends the whole grid through the general kernels
+    monkeypatch.delenv("KSA_SWEEP_GENERAL")
+    monkeypatch.delenv("KSA_SWEEP_VARIANT")
+    extra = [ksa.Policy(attr_mask=3, scale_up_messages=2**31, scale_down_messages=5, max_pods=7),
+             ksa.Policy(attr_mask=3, scale_up_messages=50, scale_down_messages=50, max_pods=7),
+             ksa.Policy(attr_mask=3, scale_up_messages=50, scale_down_messages=-(2**31) - 1, max_pods=7)]
+    for e in extra:
+        grid = pols[:5] + [e]
+        got = engine.replay_sweep(grid, depth, T, A, N, N, r0_dev).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(6, N)
+        ref = oracle_lib.replay(e.to_c(), d_host, T, A, N, N, 0, *r0, want_full=False, want_summary=True).summary
+        assert got[5].tobytes() == ref.tobytes() and got[0].tobytes() == want[0].tobytes(), str(e)
 
 
 # ---- host-buffer pipeline (the e2e path) ----------------------------------------------------------

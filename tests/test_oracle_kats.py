@@ -148,10 +148,12 @@ def test_c_oracles_equal_python_restatement(pol, data):
     assert s["poll_failed"] == sum(1 for e in p_e if e == 0xC0)
     assert s["up_failed"] == sum(1 for e in p_e if e != 0xC0 and e & 0x40)
     assert s["down_failed"] == sum(1 for e in p_e if e != 0xC0 and e & 0x80)
-    h = 0
+    lo = hi = 0  # the two lanes of ksa_summary.hash (include/ksa_replay.h)
     for r, e in zip(p_r, p_e):
-        h = (h * 0x9E3779B97F4A7C15 + ((e << 32) | (r & 0xFFFFFFFF))) & (2**64 - 1)
-    assert int(s["hash"]) == h
+        wide = sum(((e >> k) & 1) << pos for k, pos in enumerate((0, 5, 10, 15, 20, 25, 30, 31)))
+        lo = (lo * 0x9E3779B1 + (r & 0xFFFFFFFF)) & 0xFFFFFFFF
+        hi = (hi * 0x85EBCA6B + wide) & 0xFFFFFFFF
+    assert int(s["hash"]) == (hi << 32 | lo)
     assert int(s["sum_replicas"]) == ((sum(p_r) + 2**63) % 2**64) - 2**63
 
 
@@ -189,3 +191,12 @@ def test_oracle_threads_do_not_change_results():
     assert np.array_equal(a.replicas, b.replicas) and np.array_equal(a.events, b.events)
     assert a.summary.tobytes() == b.summary.tobytes()
     assert np.array_equal(oracle_lib.traj_hash(a.replicas, a.events, T, N, N), a.summary["hash"])
+
+
+def test_wide_event_formula_matches_its_definition():
+    """KSA_EV_WIDE (include/ksa_replay.h; also ksa_wide_event in csrc/ksa_policy.cuh): the
+    multiply-and-mask spelling equals 'bit k to bit 5k, failure bits to 30 and 31' for every byte."""
+    for ev in range(256):
+        want = sum(((ev >> k) & 1) << pos for k, pos in enumerate((0, 5, 10, 15, 20, 25, 30, 31)))
+        got = (((ev & 7) * 0x111) & 0x421) | ((((ev >> 3 & 7) * 0x111) & 0x421) << 15) | ((ev >> 6) << 30)
+        assert got == want, ev
