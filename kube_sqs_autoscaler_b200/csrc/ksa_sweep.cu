@@ -22,13 +22,22 @@ struct SweepArgs {
   long long N;
   int P, T, A;
   int one;  // always 1 (see ksa_step_fma)
+  int split;  // register-tile kernels: 1 = run only the policy tiles whose kind (narrow or not) is this kernel's
   const int* replicas0;
   ksa_summary* summary;  // [P][N]
 };
 
-// FAST = every policy of the launch has scale_up_messages > scale_down_messages and thresholds
-// that fit 32 bits (sweep_policies_fast below): the step is ksa_step_fma_narrow on the attribute
-// sum saturated once per tick, 6 compares per decision instead of 9.
+// Whether ksa_step_fma_narrow is exact for a policy: thresholds ordered and inside the range where
+// comparing the saturated sum is the same as comparing the sum. Host and device use the same test.
+__host__ __device__ inline bool ksa_policy_is_narrow(long long up, long long down) {
+  return up > down && up > (long long)INT_MIN && up <= (long long)INT_MAX && down >= (long long)INT_MIN &&
+         down < (long long)INT_MAX;
+}
+
+// FAST = every policy of the tile is narrow: the step is ksa_step_fma_narrow on the attribute sum
+// saturated once per tick, 6 compares per decision instead of 9. A grid that mixes narrow and other
+// tiles is launched twice with a.split = 1, once per kind; each block then returns at once unless
+// its tile is of the kernel's kind.
 template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, bool FAST>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
@@ -40,6 +49,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
   ksa_policy_k pk[R];
 #pragma unroll
   for (int q = 0; q < R; ++q) pk[q] = a.policies[min(p0 + q, a.P - 1)];
+  if (a.split) {
+    bool narrow = true;
+#pragma unroll
+    for (int q = 0; q < R; ++q) narrow = narrow && ksa_policy_is_narrow(pk[q].up_msgs, pk[q].down_msgs);
+    if (narrow != FAST) return;
+  }
 
   ksa_trace_regs s[R];
   ksa_summary_acc m[R];
@@ -90,7 +105,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
       const int tt = t + j;
       if (tt < T) {
         const long long msgs = buf[j];
-        if (tt + D < T) buf[j] = load_sum(tt + D);
+        // FAST keeps the saturated sum in the ring slot's register for the whole tick; refilling the
+        // slot here would go through a temporary that ptxas copies back at the end of the tick,
+        // i.e. it would wait for the load it has just issued. FAST refills after the machines.
+        if (!FAST && tt + D < T) buf[j] = load_sum(tt + D);
         const int i = tt + 1;
         // CHAIN > 0: the R machines run in groups of CHAIN. The first compare of a group is made
         // to wait for the last event of the previous group through a xor that changes nothing
@@ -118,6 +136,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
           ev_last = ev;
           ksa_summary_tick<true>(m[q], s[q].r, ev, one);
         }
+        if (FAST && tt + D < T) buf[j] = load_sum(tt + D);
       }
     }
     pending += D;
@@ -289,26 +308,15 @@ const SweepVariant kSweepVariants[] = {
     // 16..: register tile with chained groups
     KSA_SWEEP_CH(4, 4, 128, 3, 2), KSA_SWEEP_CH(4, 2, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 3, 1),
     KSA_SWEEP_CH(8, 2, 128, 2, 2), KSA_SWEEP_CH(8, 2, 128, 2, 4), KSA_SWEEP_CH(6, 2, 128, 3, 2), KSA_SWEEP_CH(4, 4, 64, 6, 2),
+    // 24..: more unchained R=4 points (the narrow step needs fewer predicates)
+    KSA_SWEEP(4, 1, 128, 4), KSA_SWEEP(4, 2, 64, 8), KSA_SWEEP(4, 3, 128, 4), KSA_SWEEP(4, 2, 256, 2), KSA_SWEEP(4, 2, 128, 5),
+    KSA_SWEEP(4, 2, 128, 3),
 };
 constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]));
+constexpr int kDefaultSweepNarrow = 2;  // tiles of narrow policies: R=4, D=2, 128x4, unchained
 constexpr int kDefaultSweep = 16;  // R=4 in chained groups of 2, D=4, 128x3: 107.0 ms on configs[3]
                                    // (unchained 115.6 ms; lane kernels 123 ms at V=2, 158 ms at V=1);
                                    // profiles/r01_config4_sweep_tune.txt
-
-// Whether the FAST kernels are exact for this grid (see ksa_step_fma_narrow): thresholds ordered
-// and inside the range where comparing the saturated sum is the same as comparing the sum.
-// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels, for measurements and tests.
-bool sweep_policies_fast(const ksa_policy* policies, int P) {
-  if (const char* e = std::getenv("KSA_SWEEP_GENERAL"))
-    if (std::atoi(e) != 0) return false;
-  for (int q = 0; q < P; ++q) {
-    const long long up = policies[q].scale_up_messages, down = policies[q].scale_down_messages;
-    if (!(up > down && up > (long long)INT_MIN && up <= (long long)INT_MAX && down >= (long long)INT_MIN &&
-          down < (long long)INT_MAX))
-      return false;
-  }
-  return true;
-}
 
 // Grid of a sweep launch, or false if it does not fit one launch.
 bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
@@ -322,6 +330,51 @@ bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
     *grid = dim3((unsigned)blocks);
   }
   return true;
+}
+
+// How the policy tiles (R consecutive policies, the last one padded with copies of policy P-1 as
+// in the kernel) of a grid split into narrow and other: 0 = none narrow, 1 = all narrow, 2 = mixed.
+// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels, for measurements and tests.
+int sweep_tile_kinds(const ksa_policy* policies, int P, int R) {
+  if (const char* e = std::getenv("KSA_SWEEP_GENERAL"))
+    if (std::atoi(e) != 0) return 0;
+  bool any_narrow = false, any_other = false;
+  for (int p0 = 0; p0 < P; p0 += R) {
+    bool narrow = true;
+    for (int q = 0; q < R; ++q) {
+      const ksa_policy& pol = policies[std::min(p0 + q, P - 1)];
+      narrow = narrow && ksa_policy_is_narrow(pol.scale_up_messages, pol.scale_down_messages);
+    }
+    (narrow ? any_narrow : any_other) = true;
+  }
+  return any_narrow ? (any_other ? 2 : 1) : 0;
+}
+
+// Launch the sweep: the narrow and the general kernel each on the tiles of its kind.
+int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st, const char* what) {
+  int gi = kDefaultSweep, fi = kDefaultSweepNarrow;
+  if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
+    const int want = std::atoi(e);
+    if (want >= 0 && want < kNumSweepVariants) gi = fi = want;
+  }
+  const SweepVariant& vg = kSweepVariants[gi];
+  const SweepVariant& vf = kSweepVariants[fi];
+  // Tiles of the two kernels must coincide for the split; the lane kernels have no narrow form.
+  const int kinds = (vg.R > 0 && vg.R == vf.R) ? sweep_tile_kinds(policies, a.P, vg.R) : 0;
+  dim3 grid;
+  if (kinds != 1) {
+    if (!sweep_grid(vg, a.P, a.N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+    a.split = kinds == 2;
+    vg.fn[A - 1]<<<grid, vg.block, 0, st>>>(a);
+    KSA_LAUNCH_CHECK(what);
+  }
+  if (kinds != 0) {
+    if (!sweep_grid(vf, a.P, a.N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+    a.split = kinds == 2;
+    vf.fast_fn[A - 1]<<<grid, vf.block, 0, st>>>(a);
+    KSA_LAUNCH_CHECK(what);
+  }
+  return KSA_OK;
 }
 
 }  // namespace
@@ -355,20 +408,11 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   a.T = (int)T;
   a.A = A;
   a.one = 1;
+  a.split = 0;
   a.replicas0 = replicas0_dev;
   a.summary = summary_dev;
-  int vi = kDefaultSweep;
-  if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
-    const int want = std::atoi(e);
-    if (want >= 0 && want < kNumSweepVariants) vi = want;
-  }
-  const SweepVariant& v = kSweepVariants[vi];
-  dim3 grid;
-  if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
   if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
-  (sweep_policies_fast(policies, P) ? v.fast_fn : v.fn)[A - 1]<<<grid, v.block, 0, st>>>(a);
-  KSA_LAUNCH_CHECK("ksa_sweep_kernel");
-  return KSA_OK;
+  return sweep_launch(policies, a, A, st, "ksa_sweep_kernel");
 }
 
 // ---- ksa_replay_sweep_static: the sweep for callers that must not allocate -----------------------
@@ -443,14 +487,10 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
   a.T = (int)T;
   a.A = A;
   a.one = 1;
+  a.split = 0;
   a.replicas0 = replicas0_dev;
   a.summary = summary_dev;
-  const SweepVariant& v = kSweepVariants[kDefaultSweep];
-  dim3 grid;
-  if (!sweep_grid(v, P, N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
-  (sweep_policies_fast(policies, P) ? v.fast_fn : v.fn)[A - 1]<<<grid, v.block, 0, st>>>(a);
-  KSA_LAUNCH_CHECK("ksa_sweep_kernel (static table)");
-  return KSA_OK;
+  return sweep_launch(policies, a, A, st, "ksa_sweep_kernel (static table)");
 }
 
 // ---- ksa_sweep_reduce: score a sweep and pick policies (extension; the reference has no cost) -----

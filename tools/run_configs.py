@@ -82,11 +82,13 @@ def run_config3(args):
                       "parity": "chained traj_hash(full) == summary hash: " + ("ok" if ok else "MISMATCH")}), flush=True)
 
 
-def sweep_grid():
+def sweep_grid(ordered=False):
     """4096 policies = 8 up-thresholds x 8 down-thresholds (overlapping pairs included) x 8 (up, down)
     cool-down pairs x 8 (min, max, up step, down step) tuples."""
     ups = [50, 100, 150, 200, 250, 300, 400, 20]
     downs = [5, 10, 25, 50, 75, 100, 160, 0]
+    if ordered:  # every up-threshold above every down-threshold: the narrow sweep kernels apply
+        downs = [5, 10, 12, 15, 17, 19, 3, 0]
     cools = [(0, 0), (5, 5), (10, 30), (12, 45), (30, 10), (60, 60), (300, 30), (7, 23)]
     pods = [(1, 5, 1, 1), (1, 10, 2, 1), (2, 50, 3, 2), (1, 100, 10, 5), (0, 3, 1, 1), (5, 20, 5, 5),
             (7, 2, 1, 1), (1, 1000, 100, 50)]
@@ -104,7 +106,7 @@ def sweep_grid():
 def run_config4(args):
     eng = ksa.ReplayEngine(0)
     P, N, T = args.policies, args.sweep_traces, args.sweep_ticks
-    pols = sweep_grid()[:P]
+    pols = sweep_grid(args.ordered_grid)[:P]
     from kube_sqs_autoscaler_b200.engine import policy_array
 
     parr = policy_array(pols)
@@ -126,7 +128,7 @@ def run_config4(args):
         return out
 
     if args.sweep_tune:  # every tuning point of ksa_sweep.cu (KSA_SWEEP_VARIANT), then the default
-        for vi in range(24):
+        for vi in range(30):
             os.environ["KSA_SWEEP_VARIANT"] = str(vi)
             t = min(time_sweep(1))
             print(f"# sweep variant {vi}: {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
@@ -371,6 +373,7 @@ def main():
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--policies", type=int, default=4096)
+    ap.add_argument("--ordered-grid", action="store_true", help="config 4 with no overlapping threshold pairs")
     ap.add_argument("--sweep-traces", type=int, default=4096)
     ap.add_argument("--sweep-ticks", type=int, default=4096)
     ap.add_argument("--total-traces", type=int, default=1 << 26)
