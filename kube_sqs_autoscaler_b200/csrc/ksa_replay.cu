@@ -438,6 +438,9 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(1, MODE_SUMMARY, 2, 4, HINT_NA, 4, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(2, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 7, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(4, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
+    KSA_VARIANT(5, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(6, MODE_SUMMARY, 1, 6, HINT_NA, 5, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL

@@ -40,7 +40,13 @@ __host__ __device__ inline bool ksa_policy_is_narrow(long long up, long long dow
 // its tile is of the kernel's kind.
 template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, bool FAST>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
-  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  // Block mapping: grid = (trace blocks of a group, policy tiles, groups). Blocks are dispatched x
+  // fastest, then y, then z, so a group of gridDim.x trace blocks goes through all policy tiles
+  // before the next group starts, and the blocks resident at any time share one L2-sized slice of
+  // the depth array. (A flat (trace block, policy tile) grid streams the whole depth array once
+  // per policy tile, which only stays in L2 for small arrays.) All block-uniform, so the policy
+  // records stay in uniform registers.
+  const long long n = ((long long)blockIdx.z * gridDim.x + blockIdx.x) * BLOCK + threadIdx.x;
   if (n >= a.N) return;
   const int p0 = blockIdx.y * R;
   const int T = a.T, one = a.one;
@@ -318,12 +324,21 @@ constexpr int kDefaultSweep = 16;  // R=4 in chained groups of 2, D=4, 128x3: 10
                                    // (unchained 115.6 ms; lane kernels 123 ms at V=2, 158 ms at V=1);
                                    // profiles/r01_config4_sweep_tune.txt
 
-// Grid of a sweep launch, or false if it does not fit one launch.
-bool sweep_grid(const SweepVariant& v, int P, long long N, dim3* grid) {
+// Grid of a sweep launch, or false if it does not fit one launch. Register-tile kernels:
+// (gw trace blocks, policy tiles, groups of gw trace blocks), see the block mapping in the kernel;
+// gw is chosen so that a group's slice of the depth array is about 48 MB.
+bool sweep_grid(const SweepVariant& v, int P, long long N, int A, int T, dim3* grid) {
   if (v.R > 0) {
     const long long gy = (P + v.R - 1) / v.R;
     if (gy > 65535) return false;
-    *grid = dim3((unsigned)((N + v.block - 1) / v.block), (unsigned)gy);
+    const long long gx = (N + v.block - 1) / v.block;
+    long long gw = 48000000ll / ((long long)v.block * 8 * A * T);
+    if (const char* e = std::getenv("KSA_SWEEP_GW"))  // tuning knob: trace blocks per group
+      if (std::atoi(e) > 0) gw = std::atoi(e);
+    gw = std::max<long long>(1, std::min(gw, gx));
+    const long long gz = (gx + gw - 1) / gw;
+    if (gz > 65535) return false;
+    *grid = dim3((unsigned)gw, (unsigned)gy, (unsigned)gz);
   } else {
     const long long blocks = (long long)((P + v.block - 1) / v.block) * ((N + v.V - 1) / v.V);
     if (blocks > 0x7fffffffll) return false;
@@ -363,13 +378,13 @@ int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st
   const int kinds = (vg.R > 0 && vg.R == vf.R) ? sweep_tile_kinds(policies, a.P, vg.R) : 0;
   dim3 grid;
   if (kinds != 1) {
-    if (!sweep_grid(vg, a.P, a.N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+    if (!sweep_grid(vg, a.P, a.N, A, a.T, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
     a.split = kinds == 2;
     vg.fn[A - 1]<<<grid, vg.block, 0, st>>>(a);
     KSA_LAUNCH_CHECK(what);
   }
   if (kinds != 0) {
-    if (!sweep_grid(vf, a.P, a.N, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+    if (!sweep_grid(vf, a.P, a.N, A, a.T, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
     a.split = kinds == 2;
     vf.fast_fn[A - 1]<<<grid, vf.block, 0, st>>>(a);
     KSA_LAUNCH_CHECK(what);

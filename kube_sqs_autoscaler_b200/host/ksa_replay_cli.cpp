@@ -5,7 +5,10 @@
 // Kubernetes clients are accepted and ignored). Instead of polling one queue forever it replays
 // the policy over --traces synthetic queue-depth traces x --ticks polls, sharded over --gpus GPUs
 // (one host thread per GPU, no collective, host-side gather of the per-trace summaries), and prints
-// what the autoscaler would have done.
+// what the autoscaler would have done. With --mode sweep every tunable flag of main.go:83-91 may be
+// a comma-separated list; the cross product is replayed as a policy grid (ksa_replay_sweep), scored
+// (ksa_sweep_reduce, an extension: the reference has no cost model) and the cheapest policies are
+// printed as ready-to-paste flag sets.
 //
 // Links only libksareplay.so: all CUDA calls happen behind the ABI.
 #include <algorithm>
@@ -105,6 +108,10 @@ struct Options {
   // injected API failures (main.go:44-47,57-60,71-74): each call fails with probability 2^-k, 0 = never
   uint32_t poll_fail_log2 = 0, up_fail_log2 = 0, down_fail_log2 = 0;
   bool faults() const { return poll_fail_log2 || up_fail_log2 || down_fail_log2; }
+  // --mode sweep: the value lists of the nine tunables (a single value outside sweep mode) and the cost
+  std::vector<int64_t> up_cool, down_cool, up_msgs, down_msgs, up_pods, down_pods, max_pods, min_pods;
+  ksa_cost cost = {1, 0, 0, 0};
+  int top = 5;
 };
 
 Options parse(int argc, char** argv) {
@@ -129,6 +136,7 @@ Options parse(int argc, char** argv) {
     }
     kv[a] = v;
   }
+  const bool sweep = kv.count("mode") && kv["mode"] == "sweep";
   for (const auto& [k, v] : kv) {
     auto as_int = [&](const char* what) {
       char* end = nullptr;
@@ -141,15 +149,41 @@ Options parse(int argc, char** argv) {
       if (!parse_duration(v, &d)) die(std::string("invalid value \"") + v + "\" for flag -" + what + ": time: invalid duration");
       return d;
     };
+    // A tunable: one value, or in sweep mode a comma-separated list of values.
+    auto as_list = [&](const char* what, bool duration, std::vector<int64_t>* out) {
+      out->clear();
+      size_t p = 0;
+      while (p <= v.size()) {
+        size_t q = sweep ? v.find(',', p) : std::string::npos;
+        if (q == std::string::npos) q = v.size();
+        const std::string item = v.substr(p, q - p);
+        int64_t x;
+        if (duration) {
+          if (!parse_duration(item, &x)) die(std::string("invalid value \"") + item + "\" for flag -" + what + ": time: invalid duration");
+        } else {
+          char* end = nullptr;
+          x = (int64_t)std::strtoll(item.c_str(), &end, 0);
+          if (item.empty() || *end) die(std::string("invalid value \"") + item + "\" for flag -" + what);
+        }
+        out->push_back(x);
+        p = q + 1;
+      }
+      return out->front();
+    };
     if (k == "poll-period") o.policy.poll_period_ns = as_dur("poll-period");
-    else if (k == "scale-down-cool-down") o.policy.scale_down_cool_down_ns = as_dur("scale-down-cool-down");
-    else if (k == "scale-up-cool-down") o.policy.scale_up_cool_down_ns = as_dur("scale-up-cool-down");
-    else if (k == "scale-up-messages") o.policy.scale_up_messages = as_int("scale-up-messages");
-    else if (k == "scale-down-messages") o.policy.scale_down_messages = as_int("scale-down-messages");
-    else if (k == "scale-up-pods") o.policy.scale_up_pods = as_int("scale-up-pods");
-    else if (k == "scale-down-pods") o.policy.scale_down_pods = as_int("scale-down-pods");
-    else if (k == "max-pods") o.policy.max_pods = as_int("max-pods");
-    else if (k == "min-pods") o.policy.min_pods = as_int("min-pods");
+    else if (k == "scale-down-cool-down") o.policy.scale_down_cool_down_ns = as_list("scale-down-cool-down", true, &o.down_cool);
+    else if (k == "scale-up-cool-down") o.policy.scale_up_cool_down_ns = as_list("scale-up-cool-down", true, &o.up_cool);
+    else if (k == "scale-up-messages") o.policy.scale_up_messages = as_list("scale-up-messages", false, &o.up_msgs);
+    else if (k == "scale-down-messages") o.policy.scale_down_messages = as_list("scale-down-messages", false, &o.down_msgs);
+    else if (k == "scale-up-pods") o.policy.scale_up_pods = as_list("scale-up-pods", false, &o.up_pods);
+    else if (k == "scale-down-pods") o.policy.scale_down_pods = as_list("scale-down-pods", false, &o.down_pods);
+    else if (k == "max-pods") o.policy.max_pods = as_list("max-pods", false, &o.max_pods);
+    else if (k == "min-pods") o.policy.min_pods = as_list("min-pods", false, &o.min_pods);
+    else if (k == "cost-pod-ticks") o.cost.w_pod_ticks = as_int("cost-pod-ticks");
+    else if (k == "cost-saturated") o.cost.w_saturated = as_int("cost-saturated");
+    else if (k == "cost-churn") o.cost.w_churn = as_int("cost-churn");
+    else if (k == "cost-blocked") o.cost.w_blocked = as_int("cost-blocked");
+    else if (k == "top") o.top = (int)as_int("top");
     else if (k == "attribute-names") o.policy.attr_mask = attr_mask(v);
     else if (k == "aws-region" || k == "sqs-queue-url" || k == "kubernetes-deployment" || k == "kubernetes-namespace") {
       // network clients of the live daemon (main.go:92,95-97): nothing to do in a replay
@@ -165,14 +199,18 @@ Options parse(int argc, char** argv) {
     else if (k == "help" || k == "h") {
       std::puts("usage: ksa-replay [reference flags: --poll-period --scale-up-cool-down --scale-down-cool-down\n"
                 "  --scale-up-messages --scale-down-messages --scale-up-pods --scale-down-pods --max-pods --min-pods\n"
-                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary] [--device D] [--gpus G]\n"
+                "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary|sweep] [--device D] [--gpus G]\n"
+                "  --mode sweep: every tunable may be a comma-separated list; [--cost-pod-ticks W] [--cost-saturated W]\n"
+                "  [--cost-churn W] [--cost-blocked W] [--top K]\n"
                 "  [--poll-fail-log2 K] [--up-fail-log2 K] [--down-fail-log2 K]  (each API call fails with probability 2^-K)");
       std::exit(0);
     } else {
       die("flag provided but not defined: -" + k);
     }
   }
-  if (o.mode != "full" && o.mode != "summary") die("--mode must be full or summary");
+  if (o.mode != "full" && o.mode != "summary" && o.mode != "sweep") die("--mode must be full, summary or sweep");
+  if (o.mode == "sweep" && o.faults()) die("--mode sweep does not take --*-fail-log2");
+  if (o.top < 1) die("--top must be >= 1");
   if (o.poll_fail_log2 > 63 || o.up_fail_log2 > 63 || o.down_fail_log2 > 63) die("--*-fail-log2 must be in [0, 63]");
   return o;
 }
@@ -249,10 +287,163 @@ double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::
   return replay_s;
 }
 
+// ---- --mode sweep -------------------------------------------------------------------------------
+
+// The policy grid: cross product of the value lists, the last tunable varying fastest.
+std::vector<ksa_policy> build_grid(const Options& o) {
+  auto one = [](const std::vector<int64_t>& v, int64_t dflt) { return v.empty() ? std::vector<int64_t>{dflt} : v; };
+  const auto ucs = one(o.up_cool, o.policy.scale_up_cool_down_ns), dcs = one(o.down_cool, o.policy.scale_down_cool_down_ns);
+  const auto ums = one(o.up_msgs, o.policy.scale_up_messages), dms = one(o.down_msgs, o.policy.scale_down_messages);
+  const auto ups = one(o.up_pods, o.policy.scale_up_pods), dps = one(o.down_pods, o.policy.scale_down_pods);
+  const auto mxs = one(o.max_pods, o.policy.max_pods), mns = one(o.min_pods, o.policy.min_pods);
+  std::vector<ksa_policy> grid;
+  for (int64_t um : ums) for (int64_t dm : dms) for (int64_t uc : ucs) for (int64_t dc : dcs)
+  for (int64_t up : ups) for (int64_t dp : dps) for (int64_t mx : mxs) for (int64_t mn : mns) {
+    ksa_policy p = o.policy;
+    p.scale_up_messages = um; p.scale_down_messages = dm;
+    p.scale_up_cool_down_ns = uc; p.scale_down_cool_down_ns = dc;
+    p.scale_up_pods = up; p.scale_down_pods = dp; p.max_pods = mx; p.min_pods = mn;
+    grid.push_back(p);
+    if (grid.size() > (1u << 20)) die("policy grid larger than 2^20");
+  }
+  return grid;
+}
+
+// One GPU's share of a sweep: traces [begin, end) in N-chunks sized so that the P x n summaries fit
+// in 8 GB; per chunk: generate, sweep, score. policy_cost accumulates over the chunks on the device
+// (ksa_sweep_reduce adds); best_policy lands in `best` at the global trace ids.
+double run_sweep_shard(const Options& o, const std::vector<ksa_policy>& grid, int device, int64_t begin, int64_t end,
+                       std::vector<int64_t>* cost_out, std::vector<int32_t>* best) {
+  check(ksa_set_device(device), "ksa_set_device");
+  const int A = __builtin_popcount(o.policy.attr_mask);
+  const int32_t P = (int32_t)grid.size();
+  const int64_t T = o.ticks;
+  int64_t NC = std::min<int64_t>(end - begin, std::max<int64_t>(16, (int64_t)(8.0e9 / (64.0 * P)) / 16 * 16));
+  NC = std::min<int64_t>(NC, std::max<int64_t>(16, (int64_t)(32.0e9 / (8.0 * A * T)) / 16 * 16));
+  const int64_t ld = (NC + 15) / 16 * 16;
+  void *depth = nullptr, *r = nullptr, *ju = nullptr, *jd = nullptr, *summ = nullptr, *table = nullptr;
+  void *pcost = nullptr, *bpol = nullptr, *bcost = nullptr;
+  check(ksa_dev_alloc(&depth, (size_t)T * A * ld * 8), "depth");
+  check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
+  check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&jd, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&summ, (size_t)P * NC * sizeof(ksa_summary)), "summary");
+  check(ksa_dev_alloc(&table, (size_t)P * 48), "policy table");
+  check(ksa_dev_alloc(&pcost, (size_t)P * 8), "policy cost");
+  check(ksa_dev_alloc(&bpol, (size_t)NC * 4), "best policy");
+  check(ksa_dev_alloc(&bcost, (size_t)NC * 8), "best cost");
+  std::vector<int64_t> zeros((size_t)P, 0);
+  check(ksa_memcpy_h2d(pcost, zeros.data(), (size_t)P * 8, nullptr), "h2d");
+  ksa_state st = {(int32_t*)r, (int64_t*)ju, (int64_t*)jd};
+  const int32_t lo = (int32_t)o.policy.min_pods;
+  const int32_t hi = (int32_t)o.policy.max_pods >= lo ? (int32_t)o.policy.max_pods : lo;
+  ksa_gen_params g;
+  std::memset(&g, 0, sizeof(g));
+  g.seed = o.seed;
+  g.family = KSA_GEN_WALK;  // queue depths that drift: the shape a tuner cares about
+  g.low_max = 0;            // (the band limits are unused by the walk but validated)
+  g.high_min = 1;
+  g.high_max = 4 * std::max<int64_t>(1, o.policy.scale_up_messages);
+  g.walk_step = std::max<int64_t>(1, g.high_max / 32);
+  void* walk = nullptr;
+  check(ksa_dev_alloc(&walk, (size_t)ld * 8), "walk state");
+  double secs = 0;
+  {  // untimed short pass: the first launch of a kernel pays for loading it onto the device, and
+     // an idle GPU needs some tens of milliseconds of work before its clocks are up
+    const int64_t n = std::min<int64_t>(NC, end - begin);
+    const int64_t tw = std::min<int64_t>(T, 512);
+    check(ksa_state_init(o.seed, begin, n, lo, hi, &st, nullptr), "ksa_state_init");
+    check(ksa_gen_walk_init(&g, begin, n, (int64_t*)walk, nullptr), "ksa_gen_walk_init");
+    check(ksa_gen_traces(&g, 0, tw, A, begin, n, ld, (int64_t*)depth, (int64_t*)walk, nullptr), "ksa_gen_traces");
+    check(ksa_replay_sweep(grid.data(), P, table, (const int64_t*)depth, tw, A, n, ld, (const int32_t*)r,
+                           (ksa_summary*)summ, nullptr), "ksa_replay_sweep");
+    check(ksa_sweep_reduce((const ksa_summary*)summ, P, n, &o.cost, (int64_t*)pcost, (int32_t*)bpol, (int64_t*)bcost, nullptr),
+          "ksa_sweep_reduce");
+    check(ksa_memcpy_h2d(pcost, zeros.data(), (size_t)P * 8, nullptr), "h2d");
+    check(ksa_stream_sync(nullptr), "sync");
+  }
+  for (int64_t c0 = begin; c0 < end; c0 += NC) {
+    const int64_t n = std::min(NC, end - c0);
+    check(ksa_state_init(o.seed, c0, n, lo, hi, &st, nullptr), "ksa_state_init");
+    check(ksa_gen_walk_init(&g, c0, n, (int64_t*)walk, nullptr), "ksa_gen_walk_init");
+    check(ksa_gen_traces(&g, 0, T, A, c0, n, ld, (int64_t*)depth, (int64_t*)walk, nullptr), "ksa_gen_traces");
+    check(ksa_stream_sync(nullptr), "sync");
+    const auto a = std::chrono::steady_clock::now();
+    check(ksa_replay_sweep(grid.data(), P, table, (const int64_t*)depth, T, A, n, ld, (const int32_t*)r,
+                           (ksa_summary*)summ, nullptr), "ksa_replay_sweep");
+    check(ksa_sweep_reduce((const ksa_summary*)summ, P, n, &o.cost, (int64_t*)pcost, (int32_t*)bpol, (int64_t*)bcost, nullptr),
+          "ksa_sweep_reduce");
+    check(ksa_stream_sync(nullptr), "sync");
+    secs += std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+    check(ksa_memcpy_d2h(best->data() + c0, bpol, (size_t)n * 4, nullptr), "d2h");
+    check(ksa_stream_sync(nullptr), "sync");
+  }
+  check(ksa_memcpy_d2h(cost_out->data(), pcost, (size_t)P * 8, nullptr), "d2h");
+  check(ksa_stream_sync(nullptr), "sync");
+  for (void* p : {depth, r, ju, jd, summ, table, pcost, bpol, bcost, walk}) ksa_dev_free(p);
+  return secs;
+}
+
+std::string fmt_duration(int64_t ns) {
+  char buf[64];
+  if (ns % 1000000000 == 0) std::snprintf(buf, sizeof buf, "%" PRId64 "s", ns / 1000000000);
+  else if (ns % 1000000 == 0) std::snprintf(buf, sizeof buf, "%" PRId64 "ms", ns / 1000000);
+  else std::snprintf(buf, sizeof buf, "%" PRId64 "ns", ns);
+  return buf;
+}
+
+int run_sweep(const Options& o) {
+  const std::vector<ksa_policy> grid = build_grid(o);
+  const int32_t P = (int32_t)grid.size();
+  const int64_t N = o.traces, T = o.ticks;
+  const int have = ksa_device_count();
+  if (have < 0) die(std::string("ksa_device_count: ") + ksa_last_error());
+  if (o.gpus < 1 || o.device + o.gpus > have)
+    die("--gpus " + std::to_string(o.gpus) + " from --device " + std::to_string(o.device) + ": only " + std::to_string(have) + " CUDA devices");
+  // Shards of traces, one host thread per GPU; the per-policy totals of the shards are added on the host.
+  std::vector<std::vector<int64_t>> costs((size_t)o.gpus, std::vector<int64_t>((size_t)P, 0));
+  std::vector<int32_t> best((size_t)N, -1);
+  std::vector<double> secs((size_t)o.gpus, 0.0);
+  std::vector<std::thread> workers;
+  for (int g = 0; g < o.gpus; ++g) {
+    const int64_t base = N / o.gpus, extra = N % o.gpus;
+    const int64_t begin = g * base + std::min<int64_t>(g, extra);
+    const int64_t end = begin + base + (g < extra ? 1 : 0);
+    workers.emplace_back([&, g, begin, end] {
+      if (end > begin) secs[(size_t)g] = run_sweep_shard(o, grid, o.device + g, begin, end, &costs[(size_t)g], &best);
+    });
+  }
+  for (auto& w : workers) w.join();
+  std::vector<int64_t> total((size_t)P, 0);
+  for (const auto& c : costs)
+    for (int32_t p = 0; p < P; ++p) total[(size_t)p] = (int64_t)((uint64_t)total[(size_t)p] + (uint64_t)c[(size_t)p]);
+  std::vector<int64_t> wins((size_t)P, 0);
+  for (int32_t b : best) if (b >= 0) ++wins[(size_t)b];
+  std::vector<int32_t> order((size_t)P);
+  for (int32_t p = 0; p < P; ++p) order[(size_t)p] = p;
+  std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return total[(size_t)a] < total[(size_t)b]; });
+  const double s = *std::max_element(secs.begin(), secs.end());
+  std::printf("swept %d policies x %" PRId64 " traces x %" PRId64 " ticks on %d GPU(s) in %.3f ms (slowest GPU, sweep + scoring): %.3e decisions/s\n",
+              P, N, T, o.gpus, s * 1e3, (double)P * (double)N * (double)T / s);
+  std::printf("cost = %" PRId64 "*pod_ticks + %" PRId64 "*ticks_saturated_at_max + %" PRId64 "*scale_events + %" PRId64 "*cool_down_skips\n",
+              o.cost.w_pod_ticks, o.cost.w_saturated, o.cost.w_churn, o.cost.w_blocked);
+  for (int k = 0; k < std::min<int>(o.top, P); ++k) {
+    const ksa_policy& p = grid[(size_t)order[(size_t)k]];
+    std::printf("#%d policy %d cost %" PRId64 " best-for %" PRId64 " traces: --scale-up-messages=%" PRId64 " --scale-down-messages=%" PRId64
+                " --scale-up-cool-down=%s --scale-down-cool-down=%s --scale-up-pods=%" PRId64 " --scale-down-pods=%" PRId64
+                " --max-pods=%" PRId64 " --min-pods=%" PRId64 "\n",
+                k + 1, order[(size_t)k], total[(size_t)order[(size_t)k]], wins[(size_t)order[(size_t)k]], p.scale_up_messages,
+                p.scale_down_messages, fmt_duration(p.scale_up_cool_down_ns).c_str(), fmt_duration(p.scale_down_cool_down_ns).c_str(),
+                p.scale_up_pods, p.scale_down_pods, p.max_pods, p.min_pods);
+  }
+  return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
   Options o = parse(argc, argv);
+  if (o.mode == "sweep") return run_sweep(o);
   const int A = __builtin_popcount(o.policy.attr_mask);
   const int64_t N = o.traces, T = o.ticks;
   int64_t cu = 0, cd = 0;

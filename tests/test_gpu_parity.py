@@ -655,3 +655,49 @@ def test_sweep_reduce_matches_restatement(engine, P, N):
     rpc, rbp, rbc = policy_py.sweep_reduce(fake, **w)
     assert np.array_equal(pc.cpu().numpy(), rpc)
     assert np.array_equal(bp.cpu().numpy(), rbp) and np.array_equal(bc.cpu().numpy(), rbc)
+
+
+def test_cli_sweep_mode_matches_engine_and_restatement(engine):
+    """ksa-replay --mode sweep: comma lists on the reference's flags -> policy grid -> ksa_replay_sweep
+    + ksa_sweep_reduce. The printed ranking (policy index, total cost, traces won) equals the one
+    computed from the oracle's per-policy replays and oracle/policy_py.sweep_reduce on the same
+    generated traces; chunked over traces and sharded over GPUs it stays the same."""
+    import os
+    import re
+    import subprocess
+    from oracle import policy_py
+
+    torch = torch_mod()
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    N, T = 700, 120
+    args = [cli, "--mode", "sweep", "--poll-period=5s", "--scale-up-messages=60,100,200", "--scale-down-messages=5,20",
+            "--scale-up-cool-down=0s,20s", "--scale-down-cool-down=30s", "--max-pods=4,9", "--traces", str(N),
+            "--ticks", str(T), "--seed", "31", "--cost-pod-ticks", "2", "--cost-saturated", "30", "--cost-churn", "3",
+            "--cost-blocked", "1", "--top", "24"]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    rows = re.findall(r"#(\d+) policy (\d+) cost (-?\d+) best-for (\d+) traces: (.*)", r.stdout)
+    assert len(rows) == 24, r.stdout
+    # the same grid in the CLI's order (last tunable fastest), the same traces
+    pols = [ksa.Policy(attr_mask=1, poll_period=5 * S, scale_up_messages=um, scale_down_messages=dm,
+                       scale_up_cool_down=uc * S, scale_down_cool_down=30 * S, max_pods=mx)
+            for um in (60, 100, 200) for dm in (5, 20) for uc in (0, 20) for mx in (4, 9)]
+    gen = ksa.GenParams(seed=31, family=ksa.GEN_WALK, low_max=0, high_min=1, high_max=4 * 60,
+                        walk_step=max(1, 4 * 60 // 32))
+    ld = (N + 15) // 16 * 16
+    walk = oracle_lib.gen_walk_init(gen.to_c(), 0, N)
+    d_host = oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, ld, walk=walk)
+    st = oracle_lib.fresh_state(31, 0, N, 1, 4)
+    summ = np.stack([oracle_lib.replay(p.to_c(), d_host, T, 1, N, ld, 0, *st, want_full=False, want_summary=True).summary
+                     for p in pols])
+    cost, best, _ = policy_py.sweep_reduce(summ, w_pod_ticks=2, w_saturated=30, w_churn=3, w_blocked=1)
+    order = sorted(range(len(pols)), key=lambda p: (int(cost[p]), p))
+    wins = np.bincount(best, minlength=len(pols))
+    for k, (rank, pid, c, w, flags) in enumerate(rows):
+        assert int(rank) == k + 1 and int(pid) == order[k] and int(c) == int(cost[order[k]]) and int(w) == wins[order[k]], (k, rows[k])
+    p0 = pols[order[0]]
+    assert f"--scale-up-messages={p0.scale_up_messages} " in rows[0][4] and f"--max-pods={p0.max_pods} " in rows[0][4]
+    if torch.cuda.device_count() >= 2:
+        r2 = subprocess.run(args + ["--gpus", "2"], capture_output=True, text=True, timeout=120)
+        assert r2.returncode == 0, r2.stderr
+        assert re.findall(r"#(\d+) policy (\d+) cost (-?\d+) best-for (\d+)", r2.stdout) == [x[:4] for x in rows]
