@@ -169,6 +169,45 @@ __device__ __forceinline__ unsigned ksa_step_ptx(const ksa_step_consts& c, long 
 // which is the pipe this state machine saturates first (profiles/r01_ncu_full_v14_T2000.txt: ALU
 // 56 % active, FMA 12 %). This moves 9 of the 22 ALU operations per decision to the idle pipe, and
 // the stamp `s = i * one + cool` needs no precomputed i + cool (the sweep has one cool per policy).
+// The spelling the full-trajectory kernels use (event byte out). It differs from ksa_step_fma
+// below only in how the cool-down events are entered (from their own "blocked" predicates): with
+// 8 traces per thread this order of operations measured 1.01 of the copy bandwidth against 0.99
+// for the one below (tools/sweep_variants.py, ids 30 / 32), so the HBM-bound kernels keep it.
+__device__ __forceinline__ unsigned ksa_step_fma_byte(const ksa_step_consts& c, long long n, int i, int one,
+                                                      ksa_trace_regs& s) {
+  unsigned ev;
+  asm("{\n\t"
+      ".reg .pred uh, ugo, ucool, uapp, dh, dgo, dcool, dapp;\n\t"
+      ".reg .s32 t, u;\n\t"
+      "setp.ge.s64 uh, %4, %5;\n\t"                 // main.go:51
+      "setp.le.and.s32 ugo, %2, %11, uh;\n\t"       // main.go:52
+      "setp.gt.and.s32 ucool, %2, %11, uh;\n\t"
+      "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"      // scale.go:62
+      "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"      // main.go:62   su = i + cu
+      "selp.u32 %0, 16, 0, ucool;\n\t"
+      "@ugo mad.lo.s32 %0, %14, 4, %0;\n\t"         // UP_NOOP unless ...
+      "@uapp mad.lo.s32 %0, %14, -3, %0;\n\t"       // ... UP_APPLIED
+      "add.s32 t, %1, %9;\n\t"                      // scale.go:66
+      "min.s32 t, t, %7;\n\t"                       // scale.go:67-69
+      "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"
+      "setp.le.and.s64 dh, %4, %6, !ucool;\n\t"     // main.go:65 (+ :54)
+      "setp.le.and.s32 dgo, %3, %11, dh;\n\t"       // main.go:66
+      "setp.gt.and.s32 dcool, %3, %11, dh;\n\t"
+      "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"      // scale.go:89
+      "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"      // main.go:76   sd = i + cd
+      "@dcool mad.lo.s32 %0, %14, 32, %0;\n\t"
+      "@dgo mad.lo.s32 %0, %14, 8, %0;\n\t"
+      "@dapp mad.lo.s32 %0, %14, -6, %0;\n\t"
+      "sub.s32 u, %1, %10;\n\t"                     // scale.go:94
+      "max.s32 u, u, %8;\n\t"                       // scale.go:95-97
+      "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"
+      "}"
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one));
+  return ev;
+}
+
 // WIDE = true returns the wide event code (ksa_wide_event of the byte) instead of the byte.
 // ORDERED = true is for policies with scale_up_messages > scale_down_messages (the caller checks):
 // then the two thresholds cannot both be met in one tick, so the `continue` of main.go:54 never

@@ -290,8 +290,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
           ev[v] = ksa_step_faults(c, n[v], fv[v], i, s[v]);
       } else if constexpr (STEP == 6)
         ev[v] = ksa_step_fma<WIDE, true>(c, n[v], i, one, s[v]);
+      else if constexpr (STEP >= 2 && !WIDE)
+        ev[v] = ksa_step_fma_byte(c, n[v], i, one, s[v]);
       else if constexpr (STEP >= 2)
-        ev[v] = ksa_step_fma<WIDE>(c, n[v], i, one, s[v]);
+        ev[v] = ksa_step_fma<true>(c, n[v], i, one, s[v]);
       else if constexpr (STEP == 1)
         ev[v] = ksa_step_ptx(c, n[v], i, s[v]);
       else
