@@ -365,6 +365,164 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   }
 }
 
+// ---- summary replay with the depth rows staged in shared memory by the bulk-copy engine ---------
+//
+// The register-ring kernel above spends ~3 instructions per decision on load addresses and can
+// only keep D * 8 bytes per thread in flight. Here one thread per block issues whole rows
+// (BLOCK traces x 8 B = 1 KB, contiguous in the tick-major layout) as cp.async.bulk copies into a
+// ring of S stages of K ticks each; completion is signalled on one mbarrier per stage
+// (complete_tx), consumption on a second one (one arrive per warp), so no __syncthreads in the
+// loop. Every thread then reads its own 8 bytes per tick from shared memory at a compile-time
+// offset (conflict-free LDS.64) and runs the same step and summary accumulation as above.
+// Block = BLOCK adjacent traces, one per thread; needs n_count to be a multiple of BLOCK (the
+// ragged tail goes to the scalar kernel) and the usual alignment (ld % 16 == 0).
+__device__ __forceinline__ unsigned ksa_smem_u32(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void ksa_mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ksa_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void ksa_mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(ksa_smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void ksa_mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ksa_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void ksa_mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "KSA_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra KSA_DONE;\n\t"
+      "bra KSA_WAIT;\n\t"
+      "KSA_DONE:\n\t"
+      "}" ::"r"(ksa_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void ksa_bulk_g2s(void* dst_smem, const void* src, unsigned bytes,
+                                             unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   ksa_smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(ksa_smem_u32(bar))
+               : "memory");
+}
+
+// Launched with BLOCK + 32 threads: warps 0..BLOCK/32-1 replay, the last warp only feeds the ring.
+template <int A, int K, int S, int BLOCK, int MINB, bool ORDERED>
+__global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(const __grid_constant__ ReplayArgs a) {
+  static_assert(K <= KSA_FOLD_TICKS, "a stage must fit one fold period");
+  __shared__ __align__(128) long long ring[S][K][A][BLOCK];
+  __shared__ __align__(8) unsigned long long full_bar[S], empty_bar[S];
+  const int tid = threadIdx.x;
+  const long long nb = a.n_begin + (long long)blockIdx.x * BLOCK;  // first trace of the block
+  const long long n = nb + tid;
+  const ksa_step_consts c(a.pk);
+  const int T = a.T;
+  const int one = a.one;
+
+  const int chunks = (T + K - 1) / K;
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+      ksa_mbar_init(&full_bar[i], 1);
+      ksa_mbar_init(&empty_bar[i], BLOCK / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const long long row = (long long)A * a.ld;
+  const long long* const src0 = a.depth + nb;
+  auto issue = [&](int ch) {  // producer lane: rows of chunk ch into stage ch % S
+    const int st = ch % S, t0 = ch * K;
+    const int kk = min(K, T - t0);
+    ksa_mbar_expect_tx(&full_bar[st], (unsigned)(kk * A * BLOCK * 8));
+    for (int k = 0; k < kk; ++k)
+#pragma unroll
+      for (int p = 0; p < A; ++p)
+        ksa_bulk_g2s(&ring[st][k][p][0], src0 + (long long)(t0 + k) * row + p * a.ld, BLOCK * 8, &full_bar[st]);
+  };
+  if (tid >= BLOCK) {  // producer warp: one lane keeps the ring full, then the warp is done
+    if (tid == BLOCK) {
+      for (int ch = 0; ch < chunks; ++ch) {
+        if (ch >= S) ksa_mbar_wait(&empty_bar[ch % S], (unsigned)((ch / S - 1) & 1));
+        issue(ch);
+      }
+    }
+    return;
+  }
+
+  ksa_trace_regs s;
+  s.r = a.st_r[n];
+  s.su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n]);
+  s.sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n]);
+  ksa_summary* const q = a.summary + n;
+  ksa_summary_acc m;
+  m.rmin = q->min_replicas;
+  m.rmax = q->max_replicas;
+  m.pk = m.lva = m.lvb = m.pkf = 0u;
+  m.sum = q->sum_replicas;
+  m.ha = (unsigned)q->hash;
+  m.hb = (unsigned)(q->hash >> 32);
+
+  unsigned taint = 0u;  // see ksa_replay_kernel
+  auto tick = [&](const int st, const int k, const int i) {
+    unsigned long long acc = (unsigned long long)ring[st][k][0][tid];  // sqs.go:56-64, wrapping
+#pragma unroll
+    for (int p = 1; p < A; ++p) acc += (unsigned long long)ring[st][k][p][tid];
+    unsigned lo = (unsigned)acc;
+    asm("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(lo) : "r"(taint));  // lo ^ (taint & 16) == lo
+    acc = (acc & 0xffffffff00000000ull) | lo;
+    const unsigned w = ksa_step_fma<true, ORDERED>(c, (long long)acc, i, one, s);
+    taint = w;
+    ksa_summary_tick<true>(m, s.r, w, one);
+  };
+  int pending = 0, folds = 0;
+  const int full_chunks = T / K;
+  int st = 0;
+  unsigned parity = 0u;
+#pragma unroll 1
+  for (int ch = 0; ch < full_chunks; ++ch) {  // steady state: every tick of the stage exists
+    ksa_mbar_wait(&full_bar[st], parity);
+#pragma unroll
+    for (int k = 0; k < K; ++k) tick(st, k, ch * K + k + 1);
+    __syncwarp();
+    if ((tid & 31) == 0) ksa_mbar_arrive(&empty_bar[st]);
+    if (++st == S) {
+      st = 0;
+      parity ^= 1u;
+    }
+    pending += K;
+    if (pending > KSA_FOLD_TICKS - K) {
+      pending = 0;
+      if (++folds == KSA_FLUSH_FOLDS) {
+        ksa_summary_flush(m, q);
+        folds = 0;
+      } else {
+        ksa_summary_fold(m);
+      }
+    }
+  }
+  if (full_chunks < chunks) {  // last, partial stage
+    ksa_summary_fold(m);
+    ksa_mbar_wait(&full_bar[st], parity);
+    for (int k = 0; k < T - full_chunks * K; ++k) tick(st, k, full_chunks * K + k + 1);
+  }
+
+  a.st_r[n] = s.r;
+  a.st_ju[n] = ksa_global_stamp(s.su, c.cu, a.tick0, a.st_ju[n]);
+  a.st_jd[n] = ksa_global_stamp(s.sd, c.cd, a.tick0, a.st_jd[n]);
+  ksa_summary_flush(m, q);
+  q->final_replicas = s.r;
+  q->min_replicas = m.rmin;
+  q->max_replicas = m.rmax;
+  q->sum_replicas = m.sum;
+  q->hash = ((unsigned long long)m.hb << 32) | m.ha;
+}
+
 typedef void (*replay_kernel_fn)(const ReplayArgs);
 
 // A variant = one tuning point. The register ring costs 2*D*V*A registers, so the multi-attribute
@@ -372,6 +530,7 @@ typedef void (*replay_kernel_fn)(const ReplayArgs);
 struct Variant {
   int id;
   int step;            // STEP template argument (6 = only valid for ordered policies)
+  int tile;            // > 0: the kernel needs n_count to be a multiple of `tile` traces (bulk kernels)
   int V[3], block[3];  // per A-1
   const char* name;
   replay_kernel_fn fn[3];  // indexed by A-1
@@ -380,9 +539,15 @@ struct Variant {
 #define KSA_K(A, V, D, HINT, MODE, STEP, BLOCK, MINB) ksa_replay_kernel<A, V, D, HINT, MODE, STEP, BLOCK, MINB>
 // A=1 tuning point (V, D, HINT, STEP, BLOCK, MINB); A=2 and A=3 points (V, D, BLOCK, MINB) share HINT/STEP.
 #define KSA_VARIANT(ID, MODE, V, D, HINT, STEP, BLOCK, MINB, V2, D2, B2, M2, V3, D3, B3, M3)   \
-  {ID, STEP, {V, V2, V3}, {BLOCK, B2, B3}, "V" #V "_D" #D "_H" #HINT "_S" #STEP "_B" #BLOCK "x" #MINB, \
+  {ID, STEP, 0, {V, V2, V3}, {BLOCK, B2, B3}, "V" #V "_D" #D "_H" #HINT "_S" #STEP "_B" #BLOCK "x" #MINB, \
    {KSA_K(1, V, D, HINT, MODE, STEP, BLOCK, MINB), KSA_K(2, V2, D2, HINT == HINT_NA_EF && V2 < 4 ? HINT_NA : HINT, MODE, STEP, B2, M2),                  \
     KSA_K(3, V3, D3, HINT == HINT_NA_EF && V3 < 4 ? HINT_NA : HINT, MODE, STEP, B3, M3)}}
+
+// Bulk-copy summary kernels: (K ticks per stage, S stages) per A; STEP 2 = any policy, 6 = ordered.
+#define KSA_BK(A, K, S, BLOCK, MINB, STEP) ksa_summary_bulk_kernel<A, K, S, BLOCK, MINB, STEP == 6>
+#define KSA_BULK_VARIANT(ID, STEP, BLOCK, K1, S1, M1, K2, S2, M2, K3, S3, M3)                     \
+  {ID, STEP, BLOCK, {1, 1, 1}, {BLOCK + 32, BLOCK + 32, BLOCK + 32}, "BULK_K" #K1 "_S" #S1 "_S" #STEP "_B" #BLOCK "x" #M1, \
+   {KSA_BK(1, K1, S1, BLOCK, M1, STEP), KSA_BK(2, K2, S2, BLOCK, M2, STEP), KSA_BK(3, K3, S3, BLOCK, M3, STEP)}}
 
 // Variant 0 is the scalar kernel (any alignment, any N); it also handles the ragged tail of the
 // vector variants. The default is chosen from tools/sweep_variants.py measurements;
@@ -426,6 +591,12 @@ const Variant kSummaryVariants[] = {
     // replay_common substitutes the general default when the policy is not ordered.
     KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
     KSA_VARIANT(22, MODE_SUMMARY, 2, 4, HINT_NA, 6, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    // 30..: rows staged in shared memory by cp.async.bulk (ksa_summary_bulk_kernel). Measured
+    // 0.87 (33) / 0.86 (38) of the copy bandwidth against 0.92 for the register ring (21), so they
+    // are tuning points, not the default; K = 4 stages reach 0.77 (profiles/r01_summary_bulk.txt).
+    KSA_BULK_VARIANT(30, 2, 128, 8, 3, 8, 4, 3, 8, 2, 4, 8),
+    KSA_BULK_VARIANT(33, 6, 128, 8, 3, 8, 4, 3, 8, 2, 4, 8),
+    KSA_BULK_VARIANT(38, 6, 128, 8, 4, 6, 4, 4, 6, 2, 4, 6),
 };
 // The *_faults entry points: one vector kernel + the scalar kernel per mode (STEP 4).
 const Variant kFullFaultsVariants[] = {
@@ -459,7 +630,7 @@ const Variant* find_variant(const Variant (&table)[K], int id) {
 int launch(const Variant& var, int A, ReplayArgs args, cudaStream_t stream) {
   if (args.n_count <= 0) return KSA_OK;
   const long long threads = (args.n_count + var.V[A - 1] - 1) / var.V[A - 1];
-  const long long blocks = (threads + var.block[A - 1] - 1) / var.block[A - 1];
+  const long long blocks = var.tile > 0 ? args.n_count / var.tile : (threads + var.block[A - 1] - 1) / var.block[A - 1];
   if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "grid too large (%lld blocks)", blocks);
   var.fn[A - 1]<<<dim3((unsigned)blocks), dim3((unsigned)var.block[A - 1]), 0, stream>>>(args);
   KSA_LAUNCH_CHECK(var.name);
@@ -524,7 +695,7 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
                        (!events_dev || ksa_aligned(events_dev, 16));
   if (!aligned) var = scalar;
   cudaStream_t st = (cudaStream_t)stream;
-  const int V = var->V[A - 1];
+  const int V = var->tile > 0 ? var->tile : var->V[A - 1];  // granularity of the vector launch
   const long long n_vec = (N / V) * V;
   args.n_begin = 0;
   args.n_count = n_vec;
