@@ -702,3 +702,65 @@ def test_cli_sweep_mode_matches_engine_and_restatement(engine):
         r2 = subprocess.run(args + ["--gpus", "2"], capture_output=True, text=True, timeout=120)
         assert r2.returncode == 0, r2.stderr
         assert re.findall(r"#(\d+) policy (\d+) cost (-?\d+) best-for (\d+)", r2.stdout) == [x[:4] for x in rows]
+
+
+def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
+    """The summary kernels count events in packed 5-bit fields, folded every <= 31 ticks into 10-bit
+    fields, flushed every <= 30 folds. Traces on which the same event fires on EVERY tick (the worst
+    case for each field) over T = 2100 ticks (more than two flushes), for every summary variant,
+    both sweep kernels and the failure-mask kernel, against the oracle."""
+    torch = torch_mod()
+    T, N, A = 2100, 96, 1
+    d_host = np.zeros((T, A, N), dtype=np.int64)
+    d_host[:, 0, 0:16] = 500          # above the up threshold on every tick
+    d_host[:, 0, 16:32] = 0           # below the down threshold on every tick
+    d_host[:, 0, 32:48] = 50          # both thresholds at once for the overlapping policy
+    rng = np.random.default_rng(3)
+    d_host[:, 0, 48:] = rng.integers(0, 600, size=(T, N - 48))
+    pols = [ksa.Policy(attr_mask=1, scale_up_messages=100, scale_down_messages=10, scale_up_cool_down=0,
+                       scale_down_cool_down=0, max_pods=3),                       # noop on every tick
+            ksa.Policy(attr_mask=1, scale_up_messages=100, scale_down_messages=10, scale_up_cool_down=10**6 * S,
+                       scale_down_cool_down=10**6 * S, max_pods=3),               # cool-down skip on every tick
+            ksa.Policy(attr_mask=1, scale_up_messages=40, scale_down_messages=60, scale_up_cool_down=0,
+                       scale_down_cool_down=0, max_pods=2**31 - 1, min_pods=-(2**31)),  # up and down applied on every tick
+            ksa.Policy(attr_mask=1, scale_up_messages=100, scale_down_messages=10, scale_up_cool_down=7 * S,
+                       scale_down_cool_down=11 * S, max_pods=9)]
+    depth = torch.from_numpy(d_host).to(engine.dev)
+    st = oracle_lib.fresh_state(9, 0, N, 1, 3)
+    want = [oracle_lib.replay(p.to_c(), d_host, T, A, N, N, 0, *st, want_full=False, want_summary=True).summary
+            for p in pols]
+    assert int(want[0]["up_noop"].max()) >= T - 3 and int(want[1]["down_cool"].max()) == T
+    assert int(want[2]["up_applied"].max()) == T and int(want[2]["down_applied"].max()) == T
+    try:
+        for sv in SUMMARY_VARIANTS:
+            engine.set_variant(0, sv)
+            for i, pol in enumerate(pols):
+                got = engine.replay_summary(pol, depth, T, A, N, N, 0, engine.state_from_host(*st))
+                got = got.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+                assert got.tobytes() == want[i].tobytes(), f"summary variant {sv} policy {i}"
+    finally:
+        engine.set_variant(0, 0)
+    r0 = torch.from_numpy(st[0]).to(engine.dev)
+    for general in ("0", "1"):
+        monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
+        for sv in (0, 2, 5, 9, 16, 22, 27):
+            monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
+            got = engine.replay_sweep(pols, depth, T, A, N, N, r0).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
+            for i in range(len(pols)):
+                assert got[i].tobytes() == want[i].tobytes(), f"sweep general={general} variant={sv} policy {i}"
+    monkeypatch.delenv("KSA_SWEEP_GENERAL")
+    monkeypatch.delenv("KSA_SWEEP_VARIANT")
+    # failure mask: a failed poll / failed calls on every tick for some traces
+    fail = np.zeros((T, N), dtype=np.uint8)
+    fail[:, 0:8] = 1
+    fail[:, 8:16] = 2
+    fail[:, 16:24] = 4
+    fail[:, 48:] = rng.choice(np.array([0, 0, 1, 2, 4, 7], dtype=np.uint8), size=(T, N - 48))
+    f_dev = torch.from_numpy(fail).to(engine.dev)
+    for fv in ("0", "1", "2", "3", "4", "5", "6"):
+        monkeypatch.setenv("KSA_FAULTS_VARIANT", fv)
+        for i, pol in enumerate(pols):
+            ref = oracle_lib.replay(pol.to_c(), d_host, T, A, N, N, 0, *st, want_full=False, want_summary=True, fail=fail).summary
+            got = engine.replay_summary(pol, depth, T, A, N, N, 0, engine.state_from_host(*st), fail=f_dev)
+            assert got.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.tobytes(), f"faults variant {fv} policy {i}"
+    assert int(ref["poll_failed"].max()) == T
