@@ -20,7 +20,10 @@ template <typename SRC, int TT, int TN, int THREADS>
 __global__ void __launch_bounds__(THREADS) transpose_kernel(const SRC* __restrict__ src, long long src_ld,
                                                             long long T, long long N, int A, int a,
                                                             long long ld, long long* __restrict__ dst) {
-  extern __shared__ long long tile[];  // [TN][TT + 1]
+  // [TN][TT + 1] in the source's element type: an int32 source keeps the tile at half the size,
+  // which is what lets it use tiles twice as long in T (same 2 KB contiguous reads per trace row).
+  extern __shared__ __align__(16) unsigned char tile_bytes[];
+  SRC* const tile = reinterpret_cast<SRC*>(tile_bytes);
   constexpr int PITCH = TT + 1;
   constexpr int WARPS = THREADS / 32;
   const long long t0 = (long long)blockIdx.x * TT;
@@ -34,8 +37,8 @@ __global__ void __launch_bounds__(THREADS) transpose_kernel(const SRC* __restric
     for (int h = 0; h < TT / 32; ++h) {
       const int tl = lane + 32 * h;
       const long long t = t0 + tl;
-      long long v = 0;
-      if (n < N && t < T) v = (long long)__ldg(src + n * src_ld + t);
+      SRC v = 0;
+      if (n < N && t < T) v = __ldg(src + n * src_ld + t);
       tile[nl * PITCH + tl] = v;
     }
   }
@@ -50,7 +53,7 @@ __global__ void __launch_bounds__(THREADS) transpose_kernel(const SRC* __restric
     for (int h = 0; h < TN / 32; ++h) {
       const int nl = lane + 32 * h;
       const long long n = n0 + nl;
-      if (n < N) __stcs(row + n, tile[nl * PITCH + tl]);
+      if (n < N) __stcs(row + n, (long long)tile[nl * PITCH + tl]);  // sign-extends an int32 source
     }
   }
 }
@@ -61,7 +64,8 @@ int launch_transpose(const void* src, long long src_ld, long long T, long long N
   const long long gx = (T + TT - 1) / TT, gy = (N + TN - 1) / TN;
   if (gx > 0x7fffffffll || gy > 65535)
     return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max %d traces)", N, 65535 * TN);
-  constexpr size_t smem = sizeof(long long) * (size_t)TN * (TT + 1);
+  constexpr size_t smem = sizeof(SRC) * (size_t)TN * (TT + 1);
+  if (smem > 227 * 1024) return ksa_fail(KSA_EINVAL, "transpose shape %dx%d needs %zu bytes of shared memory", TT, TN, smem);
   auto kernel = transpose_kernel<SRC, TT, TN, THREADS>;
   if (smem > 48 * 1024) KSA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kernel<<<dim3((unsigned)gx, (unsigned)gy), THREADS, smem, st>>>((const SRC*)src, src_ld, T, N, A, a, ld, dst);
@@ -82,10 +86,15 @@ int dispatch_transpose(int shape, const void* src, long long src_ld, long long T
     case 7: return launch_transpose<SRC, 256, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
     case 8: return launch_transpose<SRC, 512, 32, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
     case 9: return launch_transpose<SRC, 256, 64, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 10: return launch_transpose<SRC, 32, 256, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 11: return launch_transpose<SRC, 64, 256, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
     default: return launch_transpose<SRC, 64, 64, 256>(src, src_ld, T, N, A, a, ld, dst, st);
   }
 }
-constexpr int kDefaultTransposeShape = 7;  // 256 ticks x 32 traces, 512 threads: profiles/r01_ingest_tune.txt
+// profiles/r01_ingest_tune.txt: int64 source 256 ticks x 32 traces, 512 threads (1.00 of the copy
+// bandwidth); int32 source 64 ticks x 128 traces, 512 threads (0.98; its tile is half the bytes).
+constexpr int kDefaultTransposeShape = 7;
+constexpr int kDefaultTransposeShapeInt32 = 4;
 
 // strconv.Atoi on one fixed-width record. Go 1.15 semantics for base 10, 64-bit int:
 //   ""            -> ErrSyntax          "+" / "-"    -> ErrSyntax
@@ -148,39 +157,63 @@ __device__ __forceinline__ bool atoi_swar8(unsigned long long x, long long* out)
   return true;
 }
 
-template <int WIDTH_VEC>  // WIDTH_VEC = width / 16 when the records can be fetched as uint4, else 0
+// WIDTH_VEC = width / 16 when the records can be fetched as uint4, else 0. A block decodes
+// 256 * U records: thread t takes records t, t + 256, ... of the block's range, so every load and
+// store instruction of a warp is contiguous, and the U loads of a thread are all issued before the
+// first one is used. At U = 1 a full SM has only 32 KB of loads in flight: 0.80 of the copy
+// bandwidth on 2^28 records; U = 2: 0.94, U = 4: 0.99, U = 8: 1.05 (profiles/r01_ingest_tune.txt).
+template <int WIDTH_VEC, int U>
 __global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ text, int width,
                                                       long long count, long long* __restrict__ values,
                                                       unsigned char* __restrict__ fail) {
-  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (i >= count) return;
-  unsigned char rec[32];
-  long long v = 0;
-  bool ok;
+  const long long base = (long long)blockIdx.x * (256 * U) + threadIdx.x;
   if constexpr (WIDTH_VEC > 0) {
-    const uint4* p = reinterpret_cast<const uint4*>(text + i * width);
-    uint4 w[WIDTH_VEC];
+    uint4 w[U][WIDTH_VEC];
 #pragma unroll
-    for (int q = 0; q < WIDTH_VEC; ++q) w[q] = __ldg(p + q);
-    unsigned rest = w[0].z | w[0].w;
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + u * 256;
+      if (i < count) {
+        const uint4* p = reinterpret_cast<const uint4*>(text + i * width);
 #pragma unroll
-    for (int q = 1; q < WIDTH_VEC; ++q) rest |= w[q].x | w[q].y | w[q].z | w[q].w;
-    const unsigned long long x0 = (unsigned long long)w[0].x | ((unsigned long long)w[0].y << 32);
-    // bytes 8.. all NUL and the first 8 are plain digits: done; anything else takes the exact
-    // character-by-character path below (rare: signs, long numbers, malformed strings)
-    if (rest == 0u && atoi_swar8(x0, &v)) {
-      ok = true;
-    } else {
+        for (int q = 0; q < WIDTH_VEC; ++q) w[u][q] = __ldg(p + q);
+      }
+    }
 #pragma unroll
-      for (int q = 0; q < WIDTH_VEC; ++q) reinterpret_cast<uint4*>(rec)[q] = w[q];
-      ok = atoi_record<WIDTH_VEC * 16>(rec, width, &v);
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + u * 256;
+      if (i >= count) continue;
+      unsigned rest = w[u][0].z | w[u][0].w;
+#pragma unroll
+      for (int q = 1; q < WIDTH_VEC; ++q) rest |= w[u][q].x | w[u][q].y | w[u][q].z | w[u][q].w;
+      const unsigned long long x0 = (unsigned long long)w[u][0].x | ((unsigned long long)w[u][0].y << 32);
+      long long v = 0;
+      bool ok;
+      // bytes 8.. all NUL and the first 8 are plain digits: done; anything else takes the exact
+      // character-by-character path (rare: signs, long numbers, malformed strings)
+      if (rest == 0u && atoi_swar8(x0, &v)) {
+        ok = true;
+      } else {
+        unsigned char rec[32];
+#pragma unroll
+        for (int q = 0; q < WIDTH_VEC; ++q) reinterpret_cast<uint4*>(rec)[q] = w[u][q];
+        ok = atoi_record<WIDTH_VEC * 16>(rec, width, &v);
+      }
+      values[i] = ok ? v : 0;
+      if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;  // sqs.go:59-61 -> main.go:44-47
     }
   } else {
-    for (int q = 0; q < width; ++q) rec[q] = (unsigned char)__ldg(text + i * width + q);
-    ok = atoi_record<0>(rec, width, &v);
+#pragma unroll 1
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + u * 256;
+      if (i >= count) continue;
+      unsigned char rec[32];
+      for (int q = 0; q < width; ++q) rec[q] = (unsigned char)__ldg(text + i * width + q);
+      long long v = 0;
+      const bool ok = atoi_record<0>(rec, width, &v);
+      values[i] = ok ? v : 0;
+      if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;
+    }
   }
-  values[i] = ok ? v : 0;
-  if (fail) fail[i] = ok ? 0 : KSA_FAIL_POLL;  // sqs.go:59-61 -> main.go:44-47
 }
 
 }  // namespace
@@ -193,7 +226,7 @@ extern "C" int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int6
   if (A < 1 || A > KSA_MAX_ATTRS || a < 0 || a >= A) return ksa_fail(KSA_EINVAL, "bad plane a=%d of A=%d", a, A);
   if (T < 0 || N < 0 || src_ld < T || ld < N) return ksa_fail(KSA_EINVAL, "bad T/N/src_ld/ld");
   if (T == 0 || N == 0) return KSA_OK;
-  int shape = kDefaultTransposeShape;
+  int shape = src_bytes == 8 ? kDefaultTransposeShape : kDefaultTransposeShapeInt32;
   if (const char* e = std::getenv("KSA_TRANSPOSE_SHAPE")) shape = std::atoi(e);  // tuning knob (tools/)
   cudaStream_t st = (cudaStream_t)stream;
   return src_bytes == 8
@@ -207,16 +240,23 @@ extern "C" int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t c
   if (width < 1 || width > 32) return ksa_fail(KSA_EINVAL, "width=%d outside [1,32]", width);
   if (count < 0) return ksa_fail(KSA_EINVAL, "count < 0");
   if (count == 0) return KSA_OK;
-  const long long blocks = (count + 255) / 256;
+  int U = 8;
+  if (const char* e = std::getenv("KSA_DECIMAL_UNROLL")) U = std::atoi(e);  // tuning knob (tools/): 1, 2, 4 or 8
+  if (U != 1 && U != 2 && U != 4) U = 8;
+  const long long blocks = (count + 256 * U - 1) / (256 * U);
   if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "count too large for one launch");
   cudaStream_t st = (cudaStream_t)stream;
   const bool vec = (width % 16 == 0) && ksa_aligned(text_dev, 16);
-  if (vec && width == 16)
-    decimal_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
-  else if (vec && width == 32)
-    decimal_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
-  else
-    decimal_kernel<0><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, (long long*)values_dev, fail_dev);
+  long long* out = (long long*)values_dev;
+#define KSA_DEC(WV, UU) decimal_kernel<WV, UU><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, out, fail_dev)
+  if (vec && width == 16) {
+    if (U == 1) KSA_DEC(1, 1); else if (U == 2) KSA_DEC(1, 2); else if (U == 4) KSA_DEC(1, 4); else KSA_DEC(1, 8);
+  } else if (vec && width == 32) {
+    if (U == 1) KSA_DEC(2, 1); else if (U == 2) KSA_DEC(2, 2); else if (U == 4) KSA_DEC(2, 4); else KSA_DEC(2, 8);
+  } else {
+    if (U == 1) KSA_DEC(0, 1); else if (U == 2) KSA_DEC(0, 2); else if (U == 4) KSA_DEC(0, 4); else KSA_DEC(0, 8);
+  }
+#undef KSA_DEC
   KSA_LAUNCH_CHECK("decimal_kernel");
   return KSA_OK;
 }

@@ -325,14 +325,19 @@ def run_config7(args):
 
     dst = torch.empty((T, 1, N), dtype=torch.int64, device=eng.dev)
     if args.sweep_tune:
-        src = torch.randint(0, 400, (N, T), dtype=torch.int64, device=eng.dev)
-        for shape in range(10):
-            os.environ["KSA_TRANSPOSE_SHAPE"] = str(shape)
-            ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst), reps=2)
-            print(f"# transpose shape {shape}: {ms:.3f} ms {16 * N * T / (ms * 1e-3) / 1e9:.1f} GB/s "
-                  f"ok={bool(torch.equal(dst[:, 0, :], src.t()))}", flush=True)
-        os.environ.pop("KSA_TRANSPOSE_SHAPE", None)
-        del src
+        for dt, nbytes in ((torch.int64, 8), (torch.int32, 4)):
+            src = torch.randint(0, 400, (N, T), dtype=dt, device=eng.dev)
+            for shape in range(12):
+                os.environ["KSA_TRANSPOSE_SHAPE"] = str(shape)
+                try:
+                    ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst), reps=2)
+                except ksa.KsaError as e:
+                    print(f"# transpose {str(dt)[6:]} shape {shape}: {e}", flush=True)
+                    continue
+                print(f"# transpose {str(dt)[6:]} shape {shape}: {ms:.3f} ms {(nbytes + 8) * N * T / (ms * 1e-3) / 1e9:.1f} GB/s "
+                      f"ok={bool(torch.equal(dst[:, 0, :], src.t().to(torch.int64)))}", flush=True)
+            os.environ.pop("KSA_TRANSPOSE_SHAPE", None)
+            del src
     for name, dt, nbytes in (("transpose_int64", torch.int64, 8), ("transpose_int32", torch.int32, 4)):
         src = torch.randint(0, 400, (N, T), dtype=dt, device=eng.dev)
         ms = best_ms(lambda: eng.ingest_transpose(src, T, N, 1, 0, N, out=dst))
@@ -341,7 +346,7 @@ def run_config7(args):
         out[name] = {"ms": ms, "elements_per_s": N * T / (ms * 1e-3), "GBps_algorithmic": gbs,
                      "frac_of_measured_peak": gbs / peak(), "bytes_per_element": nbytes + 8, "parity": "ok" if ok else "MISMATCH"}
         del src
-    count, width = 1 << 26, 16
+    count, width = args.records, 16
     vals = torch.randint(0, 100000, (count,), dtype=torch.int64, device=eng.dev)
     # build the records on the device: decimal digits of vals, NUL padded
     digits = torch.zeros((count, width), dtype=torch.uint8, device=eng.dev)
@@ -372,6 +377,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=2500)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--records", type=int, default=1 << 26, help="config 7: Atoi records")
     ap.add_argument("--policies", type=int, default=4096)
     ap.add_argument("--ordered-grid", action="store_true", help="config 4 with no overlapping threshold pairs")
     ap.add_argument("--sweep-traces", type=int, default=4096)

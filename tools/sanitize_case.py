@@ -93,7 +93,7 @@ def main():
     # ingest
     for dt in (np.int64, np.int32):
         src = rng.integers(-1000, 1000, size=(70, 301), dtype=dt)
-        for shape in range(10):
+        for shape in range(12):
             os.environ["KSA_TRANSPOSE_SHAPE"] = str(shape)
             got = eng.ingest_transpose(torch.from_numpy(src).to(eng.dev), 300, 70, 2, 1, 80).cpu().numpy()
             assert np.array_equal(got[:, 1, :70], src[:, :300].T.astype(np.int64))
