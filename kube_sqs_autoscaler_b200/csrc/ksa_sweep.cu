@@ -510,20 +510,18 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
 
 // ---- ksa_sweep_reduce: score a sweep and pick policies (extension; the reference has no cost) -----
 //
-// One pass over the [P][N] summaries. A block owns 32 adjacent traces (lane = trace) and its 16
-// warps split the policies (warp w takes p = w, w+16, ...), so that even a 4096-trace grid fills
-// the GPU: N/32 blocks of 512 threads, each warp keeping kReduceUnroll 2-KB rows (32 records of
-// 64 B) in flight. Per policy the warp's 32 costs are summed with shuffles and added to
+// One pass over the [P][N] summaries. A block owns 32 adjacent traces (lane = trace) and its
+// warps split the policies (warp w takes p = w, w + kReduceWarps, ...), so that even a 4096-trace
+// grid fills the GPU: N/32 blocks of 32 warps, each warp keeping kReduceUnroll 2-KB rows (32
+// records of 64 B) in flight. Per policy the warp's 32 costs are summed with shuffles and added to
 // policy_cost[p] with one 64-bit atomic; wrapping int64 addition is associative, so the totals are
 // exact whatever the order of the atomics. Per trace every warp keeps the argmin over its own
-// policies (ascending p, strict <), and warp 0 merges the 16 candidates through shared memory,
+// policies (ascending p, strict <), and warp 0 merges the candidates of all warps through shared memory,
 // cost first, then the lower p.
 
 namespace {
 
-constexpr int kReduceWarps = 16;
-constexpr int kReduceUnroll = 4;
-
+template <int kReduceWarps, int kReduceUnroll>
 __global__ void __launch_bounds__(kReduceWarps * 32) sweep_reduce_kernel(
     const ksa_summary* __restrict__ summary, int P, long long N, const __grid_constant__ ksa_cost w,
     long long* __restrict__ policy_cost, int* __restrict__ best_policy, long long* __restrict__ best_cost) {
@@ -599,8 +597,22 @@ extern "C" int ksa_sweep_reduce(const ksa_summary* summary_dev, int32_t P, int64
   if (P < 1 || N < 1) return ksa_fail(KSA_EINVAL, "P=%d, N=%lld: both must be >= 1", P, (long long)N);
   const long long blocks = (N + 31) / 32;
   if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "N too large for one launch");
-  sweep_reduce_kernel<<<(unsigned)blocks, kReduceWarps * 32, 0, (cudaStream_t)stream>>>(
-      summary_dev, P, N, *cost, (long long*)policy_cost_dev, best_policy_dev, (long long*)best_cost_dev);
+  int shape = 0;
+  if (const char* e = std::getenv("KSA_REDUCE_SHAPE")) shape = std::atoi(e);  // tuning knob (tools/)
+#define KSA_RED(W, U)                                                                                  \
+  sweep_reduce_kernel<W, U><<<(unsigned)blocks, W * 32, 0, (cudaStream_t)stream>>>(                       \
+      summary_dev, P, N, *cost, (long long*)policy_cost_dev, best_policy_dev, (long long*)best_cost_dev)
+  switch (shape) {
+    case 1: KSA_RED(16, 8); break;
+    case 2: KSA_RED(32, 4); break;
+    case 3: KSA_RED(32, 8); break;
+    case 4: KSA_RED(8, 8); break;
+    case 5: KSA_RED(16, 4); break;
+    case 6: KSA_RED(32, 1); break;
+    case 7: KSA_RED(32, 3); break;
+    default: KSA_RED(32, 2); break;  // 0.184 ms on 4096 x 4096 records; (16, 4): 0.244 ms (profiles/r01_config4_reduce.txt)
+  }
+#undef KSA_RED
   KSA_LAUNCH_CHECK("sweep_reduce_kernel");
   return KSA_OK;
 }
