@@ -414,6 +414,80 @@ __device__ __forceinline__ unsigned ksa_step_faults_fma(const ksa_step_consts& c
   return ev;
 }
 
+// Second spelling of the step with failures, used by the summary kernels (fewer operations on the
+// half-rate ALU pipe, which binds there): the cool-down events are entered from the threshold
+// predicates and corrected when the gate is open (as in ksa_step_fma), and a failed call is
+// entered arithmetically from its KSA_FAIL_* bit under the "call reached" predicate,
+//   W += (f & KSA_FAIL_UP) * (UP_FAILED - UP_COOL) / 2,
+// so neither the "blocked" nor the "failed" predicates exist. ORDERED (scale_up_messages >
+// scale_down_messages, checked by the caller): both thresholds cannot be met in one tick, so the
+// up half never has a down half to skip.
+template <bool WIDE, bool ORDERED>
+__device__ __forceinline__ unsigned ksa_step_faults_fma2(const ksa_step_consts& c, long long n, unsigned f,
+                                                         int i, int one, ksa_trace_regs& s) {
+  constexpr int kUpCool = WIDE ? (int)KSA_W_UP_COOL : KSA_EV_UP_COOL;
+  constexpr int kUpNoop = WIDE ? (int)KSA_W_UP_NOOP : KSA_EV_UP_NOOP;
+  constexpr int kUpApp = WIDE ? (int)KSA_W_UP_APPLIED : KSA_EV_UP_APPLIED;
+  constexpr long long kUpFail = WIDE ? (long long)KSA_W_UP_FAILED : KSA_EV_UP_FAILED;
+  constexpr int kDownCool = WIDE ? (int)KSA_W_DOWN_COOL : KSA_EV_DOWN_COOL;
+  constexpr int kDownNoop = WIDE ? (int)KSA_W_DOWN_NOOP : KSA_EV_DOWN_NOOP;
+  constexpr int kDownApp = WIDE ? (int)KSA_W_DOWN_APPLIED : KSA_EV_DOWN_APPLIED;
+  constexpr long long kDownFail = WIDE ? (long long)KSA_W_DOWN_FAILED : KSA_EV_DOWN_FAILED;
+  constexpr int kPollFail = WIDE ? (int)(KSA_W_UP_FAILED | KSA_W_DOWN_FAILED) : KSA_EV_POLL_FAILED;
+  constexpr int kUpFailStep = (int)((kUpFail - kUpCool) / KSA_FAIL_UP);        // times (f & KSA_FAIL_UP)
+  constexpr int kDownFailStep = (int)((kDownFail - kDownCool) / KSA_FAIL_DOWN);  // times (f & KSA_FAIL_DOWN)
+  static_assert((kUpFail - kUpCool) % KSA_FAIL_UP == 0 && (kDownFail - kDownCool) % KSA_FAIL_DOWN == 0, "");
+  unsigned ev;
+#define KSA_STEP_FAULTS2_BODY(DOWN_HIT)                                                          \
+  asm("{\n\t"                                                                                    \
+      ".reg .pred pok, uh, ureach, ugo, uapp, ucont, dh, dreach, dgo, dapp;\n\t"                 \
+      ".reg .s32 t, u;\n\t"                                                                      \
+      ".reg .b32 fb, fu, fd;\n\t"                                                                \
+      "and.b32 fb, %15, 1;\n\t"                                                                  \
+      "setp.eq.u32 pok, fb, 0;\n\t"                /* main.go:44 err == nil */                   \
+      "setp.ge.and.s64 uh, %4, %5, pok;\n\t"       /* main.go:51 */                              \
+      "setp.le.and.s32 ureach, %2, %11, uh;\n\t"   /* main.go:52 false: ScaleUp is called */     \
+      "and.b32 fu, %15, 2;\n\t"                                                                  \
+      "setp.eq.and.u32 ugo, fu, 0, ureach;\n\t"    /* ScaleUp returned nil */                    \
+      "setp.lt.and.s32 uapp, %1, %7, ugo;\n\t"     /* scale.go:62 */                             \
+      "selp.u32 %0, %16, 0, uh;\n\t"               /* UP_COOL unless the call is reached ... */  \
+      "@ugo mad.lo.s32 %0, %14, %17, %0;\n\t"      /* ... and returns nil: UP_NOOP unless ... */ \
+      "@uapp mad.lo.s32 %0, %14, %18, %0;\n\t"     /* ... UP_APPLIED */                          \
+      "@ureach mad.lo.s32 %0, fu, %19, %0;\n\t"    /* ... or fails: UP_FAILED, main.go:57-60 */  \
+      "add.s32 t, %1, %9;\n\t"                     /* scale.go:66 */                             \
+      "min.s32 t, t, %7;\n\t"                      /* scale.go:67-69 */                          \
+      "@uapp mad.lo.s32 %1, t, %14, 0;\n\t"                                                      \
+      DOWN_HIT                                     /* main.go:65, after :54 / :59 continue */    \
+      "@ugo mad.lo.s32 %2, %11, %14, %12;\n\t"     /* main.go:62   su = i + cu */                \
+      "setp.le.and.s32 dreach, %3, %11, dh;\n\t"   /* main.go:66 false: ScaleDown is called */   \
+      "and.b32 fd, %15, 4;\n\t"                                                                  \
+      "setp.eq.and.u32 dgo, fd, 0, dreach;\n\t"                                                  \
+      "setp.gt.and.s32 dapp, %1, %8, dgo;\n\t"     /* scale.go:89 */                             \
+      "@dgo mad.lo.s32 %3, %11, %14, %13;\n\t"     /* main.go:76   sd = i + cd */                \
+      "@dh mad.lo.s32 %0, %14, %20, %0;\n\t"       /* DOWN_COOL unless ... */                    \
+      "@dgo mad.lo.s32 %0, %14, %21, %0;\n\t"      /* ... DOWN_NOOP unless ... */                \
+      "@dapp mad.lo.s32 %0, %14, %22, %0;\n\t"     /* ... DOWN_APPLIED */                        \
+      "@dreach mad.lo.s32 %0, fd, %23, %0;\n\t"    /* ... or DOWN_FAILED, main.go:71-74 */       \
+      "sub.s32 u, %1, %10;\n\t"                    /* scale.go:94 */                             \
+      "max.s32 u, u, %8;\n\t"                      /* scale.go:95-97 */                          \
+      "@dapp mad.lo.s32 %1, u, %14, 0;\n\t"                                                      \
+      "@!pok mov.u32 %0, %24;\n\t"                 /* POLL_FAILED, main.go:45 */                 \
+      "}"                                                                                        \
+      : "=r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)                                              \
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),       \
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "r"(f), "n"(kUpCool),             \
+        "n"(kUpNoop - kUpCool), "n"(kUpApp - kUpNoop), "n"(kUpFailStep), "n"(kDownCool),         \
+        "n"(kDownNoop - kDownCool), "n"(kDownApp - kDownNoop), "n"(kDownFailStep), "n"(kPollFail))
+  if constexpr (ORDERED)
+    KSA_STEP_FAULTS2_BODY("setp.le.and.s64 dh, %4, %6, pok;\n\t");
+  else
+    KSA_STEP_FAULTS2_BODY("and.pred ucont, uh, !ugo;\n\t"
+                          "setp.le.and.s64 dh, %4, %6, pok;\n\t"
+                          "and.pred dh, dh, !ucont;\n\t");
+#undef KSA_STEP_FAULTS2_BODY
+  return ev;
+}
+
 // d = a * b + c as a true IMAD (FMA pipe): ptxas cannot fold it when b is not a compile-time
 // constant, which is what the `one` kernel argument is for.
 __device__ __forceinline__ unsigned ksa_mad_u32(unsigned a, unsigned b, unsigned c) {

@@ -176,8 +176,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const ksa_step_consts c(a.pk);
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
-  constexpr bool FAULTS = (STEP == 4 || STEP == 5);
-  constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6);
+  constexpr bool FAULTS = (STEP == 4 || STEP == 5 || STEP == 7 || STEP == 8);
+  constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6 || STEP == 7 || STEP == 8);
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -249,6 +249,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
   for (int v = 0; v < V; ++v) taint[v] = 0u;
 
+  const long long* pf_d = dp + (long long)D * row;                  // next row to prefetch (summary mode)
+  const unsigned char* pf_f = FAULTS ? fp + (long long)D * a.ld : nullptr;
   auto tick = [&](const int tt, const int j, const bool prefetch) {
     long long n[V];
 #pragma unroll
@@ -269,10 +271,22 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       for (int w = 0; w < (V + 3) / 4; ++w) fw[w] = fbuf[j][w];
     }
     if (prefetch) {
+      if constexpr (MODE == MODE_SUMMARY) {
+        // Prefetches happen in tick order, so a running pointer per array replaces the 64-bit
+        // multiply per load (with one trace per thread that was ~5 instructions per decision).
 #pragma unroll
-      for (int p = 0; p < A; ++p)
-        load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
-      if constexpr (FAULTS) load_fail<V>(fp + (long long)(tt + D) * a.ld, fbuf[j]);
+        for (int p = 0; p < A; ++p) load_depth<V, HINT>(pf_d + p * a.ld, buf[j][p]);
+        pf_d += row;
+        if constexpr (FAULTS) {
+          load_fail<V>(pf_f, fbuf[j]);
+          pf_f += a.ld;
+        }
+      } else {
+#pragma unroll
+        for (int p = 0; p < A; ++p)
+          load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
+        if constexpr (FAULTS) load_fail<V>(fp + (long long)(tt + D) * a.ld, fbuf[j]);
+      }
     }
     const int i = tt + 1;  // local tick, 1-based
     int rr[V];
@@ -284,8 +298,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       fv[v] = 0u;
       if constexpr (FAULTS) {
         fv[v] = (fw[v / 4] >> (8 * (v % 4))) & 0xffu;
-        if constexpr (STEP == 5)
-          ev[v] = ksa_step_faults_fma<WIDE>(c, n[v], fv[v], i, one, s[v]);
+        if constexpr (STEP == 7)  // ordered thresholds (summary mode only)
+          ev[v] = ksa_step_faults_fma2<WIDE, true>(c, n[v], fv[v], i, one, s[v]);
+        else if constexpr ((STEP == 5 && WIDE) || STEP == 8)
+          ev[v] = ksa_step_faults_fma2<WIDE, false>(c, n[v], fv[v], i, one, s[v]);
+        else if constexpr (STEP == 5)
+          ev[v] = ksa_step_faults_fma<false>(c, n[v], fv[v], i, one, s[v]);
         else
           ev[v] = ksa_step_faults(c, n[v], fv[v], i, s[v]);
       } else if constexpr (STEP == 6)
@@ -605,6 +623,10 @@ const Variant kFullFaultsVariants[] = {
     KSA_VARIANT(2, MODE_FULL, 8, 2, HINT_NA, 5, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
     KSA_VARIANT(3, MODE_FULL, 8, 2, HINT_NA, 5, 256, 2, 4, 3, 256, 2, 4, 2, 256, 2),
     KSA_VARIANT(4, MODE_FULL, 4, 3, HINT_NA, 5, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
+    // STEP 8: the second spelling of the failure-aware step (ksa_step_faults_fma2), event byte out
+    KSA_VARIANT(5, MODE_FULL, 4, 3, HINT_NA, 8, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
+    KSA_VARIANT(6, MODE_FULL, 8, 2, HINT_NA, 8, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
+    KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NA, 8, 128, 5, 4, 2, 128, 5, 2, 3, 128, 6),
 };
 const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -614,6 +636,10 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(4, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
     KSA_VARIANT(5, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(6, MODE_SUMMARY, 1, 6, HINT_NA, 5, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
+    // STEP 7: ordered thresholds only (replay_common substitutes the STEP 5 twin otherwise)
+    KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 7, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
+    KSA_VARIANT(8, MODE_SUMMARY, 2, 4, HINT_NA, 7, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(9, MODE_SUMMARY, 1, 8, HINT_NA, 7, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
@@ -680,10 +706,11 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   if (faults) {
     // Faults variants: default = the FMA-steered kernel when both outputs are wanted; the tuning
     // knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
-    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? 4 : 1) : 3;  // profiles/r01_config2_faults.txt
+    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? 8 : 1) : (ordered ? 7 : 4);  // profiles/r01_config2_faults.txt
     if (const char* e = std::getenv("KSA_FAULTS_VARIANT")) fid = std::atoi(e);
     var = mode == MODE_FULL ? find_variant(kFullFaultsVariants, fid) : find_variant(kSummaryFaultsVariants, fid);
     if (!var) var = mode == MODE_FULL ? &kFullFaultsVariants[2] : &kSummaryFaultsVariants[2];  // unknown id
+    if (var->step == 7 && !ordered) var = find_variant(kSummaryFaultsVariants, 4);  // same shape, any policy
     if (var && mode == MODE_FULL && (!replicas_dev || !events_dev) && fid >= 2) var = &kFullFaultsVariants[1];
     if (want == 0) var = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
     scalar = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];

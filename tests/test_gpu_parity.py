@@ -757,7 +757,7 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
     fail[:, 16:24] = 4
     fail[:, 48:] = rng.choice(np.array([0, 0, 1, 2, 4, 7], dtype=np.uint8), size=(T, N - 48))
     f_dev = torch.from_numpy(fail).to(engine.dev)
-    for fv in ("0", "1", "2", "3", "4", "5", "6"):
+    for fv in ("0", "1", "2", "3", "4", "5", "6", "7", "8", "9"):
         monkeypatch.setenv("KSA_FAULTS_VARIANT", fv)
         for i, pol in enumerate(pols):
             ref = oracle_lib.replay(pol.to_c(), d_host, T, A, N, N, 0, *st, want_full=False, want_summary=True, fail=fail).summary

@@ -259,7 +259,7 @@ def run_config6(args):
     state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
     out = {}
     if args.sweep_tune:
-        for fid in range(1, 7):
+        for fid in range(1, 10):
             os.environ["KSA_FAULTS_VARIANT"] = str(fid)
             for mode in ("full", "summary"):
                 ts = []
