@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--ticks", type=int, default=2000)
     ap.add_argument("--attrs", type=int, default=1)
     ap.add_argument("--reps", type=int, default=4)
+    ap.add_argument("--family", choices=["bands", "walk"], default="bands",
+                    help="depth generator: SURVEY.md 8(d) family A (bands) or B (random walk, step 15, walls 0 and 500)")
     ap.add_argument("--full", type=str, default="all")
     ap.add_argument("--summary", type=str, default="all")
     args = ap.parse_args()
@@ -43,7 +45,11 @@ def main():
                          scale_up_pods=3, scale_down_pods=2, max_pods=50, min_pods=2,
                          scale_up_cool_down=12 * 10**9, scale_down_cool_down=45 * 10**9)
         gen = ksa.GenParams(seed=0x5EED0001, low_max=25, high_min=250, high_max=1000, overflow_log2=20)
-    depth = eng.gen_traces(gen, 0, T, A, 0, N, N)
+    walk = None
+    if args.family == "walk":
+        gen = ksa.GenParams(seed=gen.seed, family=ksa.GEN_WALK, low_max=0, high_min=1, high_max=500, walk_step=15)
+        walk = eng.gen_walk_init(gen, 0, N)
+    depth = eng.gen_traces(gen, 0, T, A, 0, N, N, walk=walk)
     replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
     events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
     state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
@@ -71,7 +77,7 @@ def main():
             return [int(x) for x in spec.split(",")]
         return [-2] + [i for i in range(1, 64) if eng.variant_name(mode, i)]
 
-    print(f"# N={N} T={T} A={A} peak={peak} GB/s (measured copy)")
+    print(f"# N={N} T={T} A={A} family={args.family} peak={peak} GB/s (measured copy)")
     bpd_full, bpd_sum = 8 * A + 5, 8 * A
     for vid in ids(args.full, 0):
         eng.set_variant(vid, 0)
