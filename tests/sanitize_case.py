@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """A small pass through every kernel of the library, meant to run under compute-sanitizer:
 
-    compute-sanitizer --tool memcheck python tools/sanitize_case.py
+    compute-sanitizer --tool memcheck python tests/sanitize_case.py
 
 Shapes are chosen to hit the edges: ragged N (scalar tail launch), T not a multiple of the ring
 depth, T smaller than the ring, padded pitch, every A, every kernel variant, both sweep layouts,
