@@ -72,3 +72,68 @@ def test_ingest_and_generators_never_write_outside(engine):
         if A > 1:
             assert (buf[4:4 + T, : A - 1] == -5).all()
         assert torch.equal(buf[4:4 + T, A - 1, :N], src[:, :T].t())
+
+
+def test_summary_variants_sweep_and_reduce_never_write_outside(engine, monkeypatch):
+    """Canaries around the summary records for every summary variant (register ring, ordered step,
+    cp.async.bulk staging), around the [P][N] output of both sweep kernels, and around the three
+    outputs of ksa_sweep_reduce; shapes with ragged tails and a last policy tile that is not full."""
+    import torch
+
+    from tests.test_gpu_parity import SUMMARY_VARIANTS
+
+    rng = np.random.default_rng(5)
+    guard = 16
+    pol = ksa.Policy(attr_mask=1, scale_up_messages=120, scale_down_messages=30, scale_up_cool_down=10 * S,
+                     scale_down_cool_down=15 * S, max_pods=9)
+    try:
+        for T, N, ld in ((1, 1, 16), (9, 130, 144), (40, 257, 272), (33, 128, 128)):
+            depth_np = rng.integers(0, 200, size=(T, 1, ld), dtype=np.int64)
+            depth = torch.from_numpy(depth_np).to(engine.dev)
+            st = oracle_lib.fresh_state(5, 0, N, 1, 9)
+            ref = oracle_lib.replay(pol.to_c(), depth_np, T, 1, N, ld, 0, *st, want_full=False, want_summary=True)
+            for sv in SUMMARY_VARIANTS:
+                engine.set_variant(0, sv)
+                sbuf = torch.full((N + 2 * guard, 64), 0xEE, dtype=torch.uint8, device=engine.dev)
+                summ = sbuf[guard:guard + N]
+                engine.lib.ksa_summary_clear(summ.data_ptr(), N, torch.cuda.current_stream().cuda_stream)
+                engine.replay_summary(pol, depth, T, 1, N, ld, 0, engine.state_from_host(*st), summary=summ)
+                label = f"T={T} N={N} ld={ld} summary variant {sv}"
+                assert (sbuf[:guard] == 0xEE).all() and (sbuf[guard + N:] == 0xEE).all(), label
+                assert summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.summary.tobytes(), label
+            engine.set_variant(0, 0)
+            # sweep: 7 policies (tile of 4 + ragged 3), mixed narrow / general tiles
+            pols = [ksa.Policy(attr_mask=1, scale_up_messages=60 + 20 * i, scale_down_messages=(70 if i == 5 else 10 + i),
+                               scale_up_cool_down=(i % 3) * 5 * S, max_pods=4 + i) for i in range(7)]
+            P = len(pols)
+            r0 = torch.from_numpy(st[0]).to(engine.dev)
+            want = [oracle_lib.replay(p.to_c(), depth_np, T, 1, N, ld, 0, *st, want_full=False, want_summary=True).summary
+                    for p in pols]
+            for general in ("0", "1"):
+                monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
+                for sv in (2, 9, 16, 27):
+                    monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
+                    big = torch.full((P * N + 2 * guard, 64), 0xEE, dtype=torch.uint8, device=engine.dev)
+                    out = big[guard:guard + P * N].view(P, N, 64)
+                    engine.replay_sweep(pols, depth, T, 1, N, ld, r0, summary=out)
+                    label = f"T={T} N={N} sweep variant {sv} general={general}"
+                    assert (big[:guard] == 0xEE).all() and (big[guard + P * N:] == 0xEE).all(), label
+                    got = out.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(P, N)
+                    assert all(got[i].tobytes() == want[i].tobytes() for i in range(P)), label
+            monkeypatch.delenv("KSA_SWEEP_GENERAL")
+            monkeypatch.delenv("KSA_SWEEP_VARIANT")
+            # reduce
+            pc = torch.full((P + 2 * guard,), -77, dtype=torch.int64, device=engine.dev)
+            bp = torch.full((N + 2 * guard,), -77, dtype=torch.int32, device=engine.dev)
+            bc = torch.full((N + 2 * guard,), -77, dtype=torch.int64, device=engine.dev)
+            pc[guard:guard + P] = 0
+            w = ksa._abi.KsaCost(1, 2, 3, 4)
+            import ctypes as C
+            ksa._abi.check(engine.lib.ksa_sweep_reduce(out.data_ptr(), P, N, C.byref(w), pc[guard:].data_ptr(),
+                                                       bp[guard:].data_ptr(), bc[guard:].data_ptr(),
+                                                       torch.cuda.current_stream().cuda_stream))
+            for buf, n in ((pc, P), (bp, N), (bc, N)):
+                assert (buf[:guard] == -77).all() and (buf[guard + n:] == -77).all(), f"reduce T={T} N={N}"
+            assert (bp[guard:guard + N] >= 0).all() and (bp[guard:guard + N] < P).all()
+    finally:
+        engine.set_variant(0, 0)
