@@ -317,12 +317,18 @@ const SweepVariant kSweepVariants[] = {
     // 24..: more unchained R=4 points (the narrow step needs fewer predicates)
     KSA_SWEEP(4, 1, 128, 4), KSA_SWEEP(4, 2, 64, 8), KSA_SWEEP(4, 3, 128, 4), KSA_SWEEP(4, 2, 256, 2), KSA_SWEEP(4, 2, 128, 5),
     KSA_SWEEP(4, 2, 128, 3),
+    // 30..: 256-thread blocks (2 KB depth rows per block and tick; better with three attributes)
+    KSA_SWEEP_CH(4, 2, 256, 2, 2), KSA_SWEEP_CH(4, 4, 256, 2, 2), KSA_SWEEP(4, 3, 256, 2), KSA_SWEEP(4, 1, 256, 2),
+    KSA_SWEEP(4, 1, 512, 1), KSA_SWEEP(4, 2, 512, 1), KSA_SWEEP_CH(4, 1, 256, 2, 2), KSA_SWEEP(4, 1, 128, 5),
 };
 constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]));
-constexpr int kDefaultSweepNarrow = 2;  // tiles of narrow policies: R=4, D=2, 128x4, unchained
-constexpr int kDefaultSweep = 16;  // R=4 in chained groups of 2, D=4, 128x3: 107.0 ms on configs[3]
-                                   // (unchained 115.6 ms; lane kernels 123 ms at V=2, 158 ms at V=1);
-                                   // profiles/r01_config4_sweep_tune.txt
+// Defaults per number of attributes (index A-1), from profiles/r01_config4_sweep_tune.txt. All have
+// R = 4, which the split launch of a mixed grid needs (tiles of the two kernels must coincide).
+//   narrow tiles:  A=1: R4 D2 128x4 unchained (71.5 ms on configs[3]); A=2,3: R4 D1 256x2 (83 ms at A=3,
+//                  112 ms with the A=1 choice: three 2-KB rows per tick want the wider block)
+//   other tiles:   A=1: R4 D1 128x5 unchained (75.3 ms); A=2,3: R4 D1 256x2 (87 ms at A=3)
+constexpr int kDefaultSweepNarrow[3] = {2, 33, 33};
+constexpr int kDefaultSweep[3] = {37, 33, 33};
 
 // Grid of a sweep launch, or false if it does not fit one launch. Register-tile kernels:
 // (gw trace blocks, policy tiles, groups of gw trace blocks), see the block mapping in the kernel;
@@ -367,7 +373,7 @@ int sweep_tile_kinds(const ksa_policy* policies, int P, int R) {
 
 // Launch the sweep: the narrow and the general kernel each on the tiles of its kind.
 int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st, const char* what) {
-  int gi = kDefaultSweep, fi = kDefaultSweepNarrow;
+  int gi = kDefaultSweep[A - 1], fi = kDefaultSweepNarrow[A - 1];
   if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
     const int want = std::atoi(e);
     if (want >= 0 && want < kNumSweepVariants) gi = fi = want;

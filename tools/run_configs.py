@@ -128,7 +128,7 @@ def run_config4(args):
         return out
 
     if args.sweep_tune:  # every tuning point of ksa_sweep.cu (KSA_SWEEP_VARIANT), then the default
-        for vi in range(30):
+        for vi in range(38):
             os.environ["KSA_SWEEP_VARIANT"] = str(vi)
             t = min(time_sweep(1))
             print(f"# sweep variant {vi}: {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
