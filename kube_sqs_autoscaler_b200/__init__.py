@@ -10,11 +10,12 @@ from ._abi import (EV_DOWN_APPLIED, EV_DOWN_COOL, EV_DOWN_NOOP, EV_UP_APPLIED, E
                    EV_UP_NOOP, EVENT_NAMES, GEN_ADVERSARIAL, GEN_BANDS, GEN_WALK, SUMMARY_DTYPE,
                    KsaError)
 from .policy import DEFAULT_ATTRIBUTE_NAMES, Policy, attr_mask_from_names, parse_duration
+from .logs import render_log
 from .shard import shard_range
 
 __all__ = [
     "Policy", "parse_duration", "attr_mask_from_names", "DEFAULT_ATTRIBUTE_NAMES", "KsaError",
-    "SUMMARY_DTYPE", "EVENT_NAMES", "GEN_BANDS", "GEN_WALK", "GEN_ADVERSARIAL", "shard_range",
+    "SUMMARY_DTYPE", "EVENT_NAMES", "GEN_BANDS", "GEN_WALK", "GEN_ADVERSARIAL", "shard_range", "render_log",
     "EV_UP_APPLIED", "EV_DOWN_APPLIED", "EV_UP_NOOP", "EV_DOWN_NOOP", "EV_UP_COOL", "EV_DOWN_COOL",
     "ReplayEngine", "HostPipeline", "GenParams", "TraceState", "pinned_empty",
 ]

@@ -91,6 +91,7 @@ class PodAutoScaler:
     scale_down_pods: int
     deployment: FakeDeployment = field(default_factory=lambda: FakeDeployment(0))
     log: list[str] = field(default_factory=list)
+    text: list[str] = field(default_factory=list)  # the messages of the log lines, as logrus gets them
     fail_next_up: bool = False    # test hooks: the next Get/Update of that call returns an error
     fail_next_down: bool = False
 
@@ -101,12 +102,14 @@ class PodAutoScaler:
         current = self.deployment.replicas  # :60
         if current >= _i32(self.max):  # :62
             self.log.append("max")  # :63
+            self.text.append(f"More than max pods running. No scale up. Replicas: {current}")
             return
         nxt = _i32(current + _i32(self.scale_up_pods))  # :66
         if nxt > _i32(self.max):  # :67
             nxt = _i32(self.max)  # :68
         self.deployment.replicas = nxt  # :70-72
         self.log.append("up")  # :77
+        self.text.append(f"Scale up successful. Replicas: {nxt}")
 
     def scale_down(self) -> None:  # scale/scale.go:81-107
         if self.fail_next_down:
@@ -115,12 +118,14 @@ class PodAutoScaler:
         current = self.deployment.replicas  # :87
         if current <= _i32(self.min):  # :89
             self.log.append("min")  # :90
+            self.text.append(f"Less than min pods running. No scale down. Replicas: {current}")
             return
         nxt = _i32(current - _i32(self.scale_down_pods))  # :94
         if nxt < _i32(self.min):  # :95
             nxt = _i32(self.min)  # :96
         self.deployment.replicas = nxt  # :98-100
         self.log.append("down")  # :105
+        self.text.append(f"Scale down successful. Replicas: {nxt}")
 
 
 @dataclass
@@ -138,12 +143,15 @@ _LOG_TO_EVENT = {"up": EV_UP_APPLIED, "down": EV_DOWN_APPLIED, "max": EV_UP_NOOP
 
 
 def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
-        start_tick: int = 0, last_up_tick: int = 0, last_down_tick: int = 0, fail_feed=None):
+        start_tick: int = 0, last_up_tick: int = 0, last_down_tick: int = 0, fail_feed=None,
+        text_log: list | None = None):
     """main.go:35-80 for `ticks` iterations of the `for` loop, virtual clock.
 
     `depth_feed(k)` is called before tick k's poll and may call `sqs.client.set_queue_attributes`
     (what the reference's tests do once, main_test.go:49). Returns (replicas, events,
     last_up_tick, last_down_tick): per-tick lists plus the final stamps as tick indices.
+    `text_log`, if given, receives one list per tick with the messages the reference logs in that
+    tick (main.go:45,49,53,58,67,72; scale/scale.go:63,77,90,105), errors without their `%v` detail.
     """
     poll = flags.poll_interval
     last_scale_up_time = last_up_tick * poll  # main.go:37 — time.Now() at start == tick 0
@@ -154,6 +162,9 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
         depth_feed(k)
         ev = 0
         p.log.clear()
+        p.text = lines = []
+        if text_log is not None:
+            text_log.append(lines)
         f = fail_feed(k) if fail_feed else 0
         sqs.client.fail_next = bool(f & FAIL_POLL)
         p.fail_next_up = bool(f & FAIL_UP)      # consumed only if ScaleUp is actually called this tick
@@ -168,17 +179,21 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
         try:
             num_messages = sqs.num_messages()  # main.go:43
         except InjectedError:  # main.go:44-47
+            lines.append("Failed to get SQS messages")  # :45
             replicas.append(p.deployment.replicas)
             events.append(EV_POLL_FAILED)
             continue
+        lines.append(f"Found {num_messages} messages in the queue")  # main.go:49
         if num_messages >= flags.scale_up_messages:  # main.go:51
             if last_scale_up_time + flags.scale_up_cool_period > now:  # :52 Add(..).After(now)
                 ev |= EV_UP_COOL  # :53
+                lines.append("Waiting for cool down, skipping scale up ")  # (sic: trailing space)
                 emit(ev)
                 continue  # :54
             try:
                 p.scale_up()  # :57
             except InjectedError:  # :57-60: log, continue; no stamp
+                lines.append("Failed scaling up")  # :58
                 emit(ev | EV_UP_FAILED)
                 continue
             last_scale_up_time = now  # :62
@@ -186,11 +201,13 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
         if num_messages <= flags.scale_down_messages:  # main.go:65
             if last_scale_down_time + flags.scale_down_cool_period > now:  # :66
                 ev |= EV_DOWN_COOL  # :67
+                lines.append("Waiting for cool down, skipping scale down")
                 emit(ev)
                 continue  # :68
             try:
                 p.scale_down()  # :71
             except InjectedError:  # :71-74
+                lines.append("Failed scaling down")  # :72
                 emit(ev | EV_DOWN_FAILED)
                 continue
             last_scale_down_time = now  # :76
@@ -200,7 +217,7 @@ def run(flags: Flags, p: PodAutoScaler, sqs: SqsClient, depth_feed, ticks: int,
 
 
 def replay_trace(policy: dict, depth_rows, replicas0: int, start_tick: int = 0,
-                 last_up_tick: int = 0, last_down_tick: int = 0, fail_rows=None):
+                 last_up_tick: int = 0, last_down_tick: int = 0, fail_rows=None, text_log=None):
     """Convenience wrapper: `policy` uses the C-ABI field names (include/ksa_replay.h),
     `depth_rows` is a list of per-tick tuples of the selected attributes' values."""
     names = DEFAULT_ATTRIBUTE_NAMES[: len(depth_rows[0])] if depth_rows else DEFAULT_ATTRIBUTE_NAMES
@@ -217,7 +234,8 @@ def replay_trace(policy: dict, depth_rows, replicas0: int, start_tick: int = 0,
         mock.set_queue_attributes({n: str(v) for n, v in zip(names, row)})
 
     fail_feed = (lambda k: fail_rows[k - start_tick - 1]) if fail_rows is not None else None
-    return run(flags, p, sqs, feed, len(depth_rows), start_tick, last_up_tick, last_down_tick, fail_feed)
+    return run(flags, p, sqs, feed, len(depth_rows), start_tick, last_up_tick, last_down_tick, fail_feed,
+               text_log)
 
 
 _ATOI_RE = None

@@ -764,3 +764,28 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
             got = engine.replay_summary(pol, depth, T, A, N, N, 0, engine.state_from_host(*st), fail=f_dev)
             assert got.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.tobytes(), f"faults variant {fv} policy {i}"
     assert int(ref["poll_failed"].max()) == T
+
+
+def test_rendered_log_of_a_gpu_trajectory_matches_the_restated_reference(engine):
+    """a7 end to end: the event bytes and replica counts written by ksa_replay_full_faults, turned
+    back into log messages (render_log), are the lines the restated reference objects print."""
+    from oracle import policy_py
+
+    torch = torch_mod()
+    rng = np.random.default_rng(21)
+    T, N = 60, 48
+    pol = ksa.Policy(attr_mask=3, scale_up_messages=90, scale_down_messages=95, scale_up_cool_down=10 * S,
+                     scale_down_cool_down=15 * S, scale_up_pods=2, max_pods=6)  # overlapping thresholds
+    d_host = rng.integers(0, 100, size=(T, 2, N), dtype=np.int64)
+    fail = rng.choice(np.array([0, 0, 0, 0, 1, 2, 4], dtype=np.uint8), size=(T, N))
+    st = oracle_lib.fresh_state(4, 0, N, 1, 6)
+    replicas, events = engine.replay_full(pol, torch.from_numpy(d_host).to(engine.dev), T, 2, N, N, 0,
+                                          engine.state_from_host(*st), fail=torch.from_numpy(fail).to(engine.dev))
+    replicas, events = replicas.cpu().numpy(), events.cpu().numpy()
+    for n in range(N):
+        text = []
+        rows = [tuple(int(x) for x in d_host[t, :, n]) for t in range(T)]
+        policy_py.replay_trace(pol.as_abi_dict(), rows, int(st[0][n]), fail_rows=[int(f) for f in fail[:, n]],
+                               text_log=text)
+        got = ksa.render_log(pol, int(st[0][n]), d_host[:, :, n].sum(axis=1), replicas[:, n], events[:, n])
+        assert got == text, f"trace {n}"

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 from hypothesis import given, settings, strategies as st
 
-from kube_sqs_autoscaler_b200 import Policy
+from kube_sqs_autoscaler_b200 import Policy, render_log
 from oracle import policy_py
 from tests import oracle_lib
 from tests.helpers import S, load_golden, policy_from_run_kat, policy_from_vector
@@ -132,9 +132,14 @@ def test_c_oracles_equal_python_restatement(pol, data):
     w_r, w_e, w_final, w_ju, w_jd = oracle_lib.run_wallclock(pol.to_c(), arr, r0, tick0, ju, jd, fail=fail)
     res = oracle_lib.replay(pol.to_c(), arr.reshape(T, A, 1), T, A, 1, 1, tick0, [r0], [ju], [jd],
                             want_summary=True, fail=None if fail is None else fail.reshape(T, 1))
+    text = []
     p_r, p_e, p_ju, p_jd = policy_py.replay_trace(pol.as_abi_dict(), rows, r0, tick0, ju, jd,
-                                                  fail_rows=fail_rows)
+                                                  fail_rows=fail_rows, text_log=text)
     assert w_r.tolist() == p_r and w_e.tolist() == p_e
+    # the log lines the reference would print, reconstructed from the replay's outputs alone
+    # (kube_sqs_autoscaler_b200.render_log), equal the ones the restated objects emitted
+    sums = [((sum(r) + 2**63) % 2**64) - 2**63 for r in rows]
+    assert render_log(pol, r0, sums, res.replicas[:, 0], res.events[:, 0]) == text
     assert res.replicas[:, 0].tolist() == p_r and res.events[:, 0].tolist() == p_e
     assert (w_ju, w_jd) == (p_ju, p_jd) == (int(res.state_last_up[0]), int(res.state_last_down[0]))
     assert w_final == p_r[-1]
