@@ -507,6 +507,7 @@ __device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c)
 // i.e. at least every KSA_FLUSH_TICKS ticks (ksa_summary_flush).
 struct ksa_summary_acc {
   int rmin, rmax;
+  int rstash;         // first replica count of a pair of ticks (KSA_TICK_FIRST), see ksa_summary_tick
   unsigned pk;        // six 5-bit event counters, field k at bit 5k (bits 30-31: don't care)
   unsigned lva, lvb;  // second level, 10-bit fields: lva = events 0, 2, 4 at bits 0, 10, 20; lvb = 1, 3, 5
   unsigned pkf;       // *_faults kernels only, 10-bit fields: up_failed at 0, down_failed at 10, failed polls at 20
@@ -531,11 +532,24 @@ __host__ __device__ __forceinline__ unsigned long long ksa_hash_step(unsigned lo
 }
 
 // One tick of summary accumulation; `w` = the wide event code of the tick. FMA = true spells the
-// adds as IMADs by `one` (FMA pipe).
+// adds as IMADs by `one` (FMA pipe). `phase` (a compile-time constant after unrolling) lets two
+// consecutive ticks share their min / max update: sm_100a has three-input VIMNMX3, so
+// min(min(rmin, r_first), r_second) is one instruction instead of two. KSA_TICK_FIRST only stashes
+// its replica count; the caller guarantees that a KSA_TICK_SECOND follows before anything reads
+// rmin / rmax (or calls ksa_summary_minmax_finish when the last tick of a trace is a FIRST).
+enum { KSA_TICK_SINGLE = 0, KSA_TICK_FIRST = 1, KSA_TICK_SECOND = 2 };
 template <bool FMA>
-__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned w, int one) {
-  m.rmin = min(m.rmin, r);
-  m.rmax = max(m.rmax, r);
+__device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsigned w, int one,
+                                                 int phase = KSA_TICK_SINGLE) {
+  if (phase == KSA_TICK_FIRST) {
+    m.rstash = r;
+  } else if (phase == KSA_TICK_SECOND) {
+    m.rmin = min(min(m.rmin, m.rstash), r);
+    m.rmax = max(max(m.rmax, m.rstash), r);
+  } else {
+    m.rmin = min(m.rmin, r);
+    m.rmax = max(m.rmax, r);
+  }
   if constexpr (FMA) {
     m.pk = ksa_mad_u32(w, (unsigned)one, m.pk);
     m.sum = ksa_mad_wide_s32(r, one, m.sum);
@@ -545,6 +559,10 @@ __device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsi
   }
   m.ha = m.ha * KSA_HASH_MUL_LO + (unsigned)r;
   m.hb = m.hb * KSA_HASH_MUL_HI + w;
+}
+__device__ __forceinline__ void ksa_summary_minmax_finish(ksa_summary_acc& m) {
+  m.rmin = min(m.rmin, m.rstash);
+  m.rmax = max(m.rmax, m.rstash);
 }
 
 // Failure counters of the *_faults kernels. `f` is the KSA_FAIL_* input byte: a poll fails exactly

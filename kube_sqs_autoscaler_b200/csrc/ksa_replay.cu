@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       sm[v].rmin = q->min_replicas;
       sm[v].rmax = q->max_replicas;
       sm[v].pk = sm[v].lva = sm[v].lvb = sm[v].pkf = 0u;
+      sm[v].rstash = 0;
       sm[v].sum = q->sum_replicas;
       sm[v].ha = (unsigned)q->hash;
       sm[v].hb = (unsigned)(q->hash >> 32);
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 
   const long long* pf_d = dp + (long long)D * row;                  // next row to prefetch (summary mode)
   const unsigned char* pf_f = FAULTS ? fp + (long long)D * a.ld : nullptr;
-  auto tick = [&](const int tt, const int j, const bool prefetch) {
+  auto tick = [&](const int tt, const int j, const bool prefetch, const int phase) {
     long long n[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
@@ -326,7 +327,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     } else {
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], one);
+        ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], one, phase);
         if constexpr (FAULTS) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
       }
     }
@@ -339,7 +340,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll 1
   for (; t + 2 * D <= T; t += D) {
 #pragma unroll
-    for (int j = 0; j < D; ++j) tick(t + j, j, true);
+    for (int j = 0; j < D; ++j)  // with an even ring depth two ticks share their min / max update
+      tick(t + j, j, true, D % 2 ? KSA_TICK_SINGLE : (j % 2 ? KSA_TICK_SECOND : KSA_TICK_FIRST));
     if constexpr (MODE == MODE_SUMMARY) {
       pending += D;
       if (pending > KSA_FOLD_TICKS - D) {
@@ -359,7 +361,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   for (; t < T; t += D) {
 #pragma unroll
     for (int j = 0; j < D; ++j)
-      if (t + j < T) tick(t + j, j, t + j + D < T);
+      if (t + j < T) tick(t + j, j, t + j + D < T, KSA_TICK_SINGLE);
     fold_counters();
   }
 
@@ -482,12 +484,13 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
   m.rmin = q->min_replicas;
   m.rmax = q->max_replicas;
   m.pk = m.lva = m.lvb = m.pkf = 0u;
+  m.rstash = 0;
   m.sum = q->sum_replicas;
   m.ha = (unsigned)q->hash;
   m.hb = (unsigned)(q->hash >> 32);
 
   unsigned taint = 0u;  // see ksa_replay_kernel
-  auto tick = [&](const int st, const int k, const int i) {
+  auto tick = [&](const int st, const int k, const int i, const int phase) {
     unsigned long long acc = (unsigned long long)ring[st][k][0][tid];  // sqs.go:56-64, wrapping
 #pragma unroll
     for (int p = 1; p < A; ++p) acc += (unsigned long long)ring[st][k][p][tid];
@@ -496,7 +499,7 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
     acc = (acc & 0xffffffff00000000ull) | lo;
     const unsigned w = ksa_step_fma<true, ORDERED>(c, (long long)acc, i, one, s);
     taint = w;
-    ksa_summary_tick<true>(m, s.r, w, one);
+    ksa_summary_tick<true>(m, s.r, w, one, phase);
   };
   int pending = 0, folds = 0;
   const int full_chunks = T / K;
@@ -506,7 +509,8 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
   for (int ch = 0; ch < full_chunks; ++ch) {  // steady state: every tick of the stage exists
     ksa_mbar_wait(&full_bar[st], parity);
 #pragma unroll
-    for (int k = 0; k < K; ++k) tick(st, k, ch * K + k + 1);
+    for (int k = 0; k < K; ++k)
+      tick(st, k, ch * K + k + 1, K % 2 ? KSA_TICK_SINGLE : (k % 2 ? KSA_TICK_SECOND : KSA_TICK_FIRST));
     __syncwarp();
     if ((tid & 31) == 0) ksa_mbar_arrive(&empty_bar[st]);
     if (++st == S) {
@@ -527,7 +531,7 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
   if (full_chunks < chunks) {  // last, partial stage
     ksa_summary_fold(m);
     ksa_mbar_wait(&full_bar[st], parity);
-    for (int k = 0; k < T - full_chunks * K; ++k) tick(st, k, full_chunks * K + k + 1);
+    for (int k = 0; k < T - full_chunks * K; ++k) tick(st, k, full_chunks * K + k + 1, KSA_TICK_SINGLE);
   }
 
   a.st_r[n] = s.r;
