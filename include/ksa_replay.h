@@ -375,6 +375,17 @@ int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int64_t src_ld,
 int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t count, int64_t* values_dev,
                        uint8_t* fail_dev, void* stream);
 
+/*
+ * The failure bytes of ksa_ingest_decimal come out in the order of the records (trace-major when
+ * the strings were); the *_faults replays want them tick-major:
+ *   fail_dev[t*ld + n] = src_dev[n*src_ld + t]            (accumulate == 0)
+ *   fail_dev[t*ld + n] |= src_dev[n*src_ld + t]           (accumulate != 0)
+ * With several attributes, call it once per attribute with accumulate != 0 after the first: a
+ * failed Atoi on any attribute fails the whole poll (sqs/sqs.go:57-61).
+ */
+int ksa_ingest_transpose_mask(const uint8_t* src_dev, int64_t src_ld, int64_t T, int64_t N, int64_t ld,
+                              uint8_t* fail_dev, int32_t accumulate, void* stream);
+
 /* ---- host-buffer pipeline (the call a Go / Python host makes with its own slices) --------- */
 
 typedef struct ksa_pipeline ksa_pipeline; /* opaque; owns device staging + 3 streams */

@@ -154,6 +154,7 @@ SIGNATURES = {
     "ksa_state_init": (C.c_int, [C.c_uint64, _i64, _i64, _i32, _i32, _P(KsaState), _vp]),
     "ksa_ingest_transpose": (C.c_int, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i64, _vp, _vp]),
     "ksa_ingest_decimal": (C.c_int, [_vp, _i32, _i64, _vp, _vp, _vp]),
+    "ksa_ingest_transpose_mask": (C.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _i32, _vp]),
     "ksa_pipeline_create": (C.c_int, [_P(_vp), C.c_int, _i64, _i32, _i64]),
     "ksa_pipeline_destroy": (C.c_int, [_vp]),
     "ksa_pipeline_replay": (C.c_int, [_vp, _P(KsaPolicy), _vp, _i64, _i64, _i64, _vp, _vp, _vp,

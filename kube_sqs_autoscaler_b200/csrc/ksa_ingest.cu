@@ -216,6 +216,34 @@ __global__ void __launch_bounds__(256) decimal_kernel(const char* __restrict__ t
   }
 }
 
+// Failure bytes arrive trace-major next to the decoded values; the replay wants them tick-major.
+// 64 x 64 byte tiles through shared memory; `accumulate` ORs into the destination, so the masks of
+// several attributes (any failed Atoi fails the whole poll, sqs/sqs.go:58-61) add up.
+__global__ void __launch_bounds__(256) transpose_mask_kernel(const unsigned char* __restrict__ src, long long src_ld,
+                                                             long long T, long long N, long long ld,
+                                                             unsigned char* __restrict__ dst, int accumulate) {
+  __shared__ unsigned char tile[64][65];
+  const long long t0 = (long long)blockIdx.x * 64, n0 = (long long)blockIdx.y * 64;
+  const int lane = threadIdx.x & 63, row = threadIdx.x >> 6;  // 4 rows of 64 per pass
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int nl = row + 4 * k;
+    const long long n = n0 + nl, t = t0 + lane;
+    tile[nl][lane] = (n < N && t < T) ? src[n * src_ld + t] : (unsigned char)0;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int tl = row + 4 * k;
+    const long long t = t0 + tl, n = n0 + lane;
+    if (t < T && n < N) {
+      unsigned char v = tile[lane][tl];
+      if (accumulate) v |= dst[t * ld + n];
+      dst[t * ld + n] = v;
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int ksa_ingest_transpose(const void* src_dev, int32_t src_bytes, int64_t src_ld, int64_t T,
@@ -258,5 +286,18 @@ extern "C" int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t c
   }
 #undef KSA_DEC
   KSA_LAUNCH_CHECK("decimal_kernel");
+  return KSA_OK;
+}
+
+extern "C" int ksa_ingest_transpose_mask(const uint8_t* src_dev, int64_t src_ld, int64_t T, int64_t N, int64_t ld,
+                                         uint8_t* fail_dev, int32_t accumulate, void* stream) {
+  if (!src_dev || !fail_dev) return ksa_fail(KSA_EINVAL, "NULL pointer");
+  if (T < 0 || N < 0 || src_ld < T || ld < N) return ksa_fail(KSA_EINVAL, "bad T/N/src_ld/ld");
+  if (T == 0 || N == 0) return KSA_OK;
+  const long long gx = (T + 63) / 64, gy = (N + 63) / 64;
+  if (gx > 0x7fffffffll || gy > 65535) return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max %d traces)", (long long)N, 65535 * 64);
+  transpose_mask_kernel<<<dim3((unsigned)gx, (unsigned)gy), 256, 0, (cudaStream_t)stream>>>(
+      src_dev, src_ld, T, N, ld, fail_dev, accumulate);
+  KSA_LAUNCH_CHECK("transpose_mask_kernel");
   return KSA_OK;
 }

@@ -133,6 +133,17 @@ class ReplayEngine:
                                                fail.data_ptr() if fail is not None else None, _stream_ptr()))
         return values, fail
 
+    def ingest_transpose_mask(self, src: torch.Tensor, T: int, N: int, ld: int, out: torch.Tensor | None = None,
+                              accumulate: bool = False) -> torch.Tensor:
+        """ksa_ingest_transpose_mask: trace-major failure bytes [N][>=T] -> tick-major [T][ld]
+        (OR-ed into `out` when accumulate)."""
+        assert src.is_cuda and src.dtype == torch.uint8 and src.dim() == 2 and src.stride(1) == 1
+        if out is None:
+            out = torch.zeros((T, ld), dtype=torch.uint8, device=self.dev)
+        _abi.check(self.lib.ksa_ingest_transpose_mask(src.data_ptr(), src.stride(0), T, N, ld, out.data_ptr(),
+                                                      1 if accumulate else 0, _stream_ptr()))
+        return out
+
     def new_state(self, N: int, seed: int = 0, lo: int = 1, hi: int = 1, trace0: int = 0) -> TraceState:
         """Fresh process (main.go:37-38): replicas = lo + hash(seed, trace) mod (hi-lo+1), stamps 0."""
         st = TraceState(torch.empty(N, dtype=torch.int32, device=self.dev),

@@ -112,6 +112,9 @@ struct Options {
   std::vector<int64_t> up_cool, down_cool, up_msgs, down_msgs, up_pods, down_pods, max_pods, min_pods;
   ksa_cost cost = {1, 0, 0, 0};
   int top = 5;
+  // recorded depths instead of synthetic ones: a raw file of [A][traces][ticks] values, one queue's
+  // history per row (trace-major), as int64 / int32 or as fixed-width NUL-padded decimal strings
+  std::string depth_file, depth_format = "i64";
 };
 
 Options parse(int argc, char** argv) {
@@ -184,6 +187,8 @@ Options parse(int argc, char** argv) {
     else if (k == "cost-churn") o.cost.w_churn = as_int("cost-churn");
     else if (k == "cost-blocked") o.cost.w_blocked = as_int("cost-blocked");
     else if (k == "top") o.top = (int)as_int("top");
+    else if (k == "depth-file") o.depth_file = v;
+    else if (k == "depth-format") o.depth_format = v;
     else if (k == "attribute-names") o.policy.attr_mask = attr_mask(v);
     else if (k == "aws-region" || k == "sqs-queue-url" || k == "kubernetes-deployment" || k == "kubernetes-namespace") {
       // network clients of the live daemon (main.go:92,95-97): nothing to do in a replay
@@ -202,6 +207,7 @@ Options parse(int argc, char** argv) {
                 "  --attribute-names] [--traces N] [--ticks T] [--seed S] [--mode full|summary|sweep] [--device D] [--gpus G]\n"
                 "  --mode sweep: every tunable may be a comma-separated list; [--cost-pod-ticks W] [--cost-saturated W]\n"
                 "  [--cost-churn W] [--cost-blocked W] [--top K]\n"
+                "  [--depth-file F --depth-format i64|i32|text16|text32]  recorded depths, [attribute][trace][tick], instead of synthetic ones\n"
                 "  [--poll-fail-log2 K] [--up-fail-log2 K] [--down-fail-log2 K]  (each API call fails with probability 2^-K)");
       std::exit(0);
     } else {
@@ -211,6 +217,9 @@ Options parse(int argc, char** argv) {
   if (o.mode != "full" && o.mode != "summary" && o.mode != "sweep") die("--mode must be full, summary or sweep");
   if (o.mode == "sweep" && o.faults()) die("--mode sweep does not take --*-fail-log2");
   if (o.top < 1) die("--top must be >= 1");
+  if (o.depth_format != "i64" && o.depth_format != "i32" && o.depth_format != "text16" && o.depth_format != "text32")
+    die("--depth-format must be i64, i32, text16 or text32");
+  if (!o.depth_file.empty() && (o.mode == "sweep" || o.faults())) die("--depth-file goes with --mode full|summary and no --*-fail-log2");
   if (o.poll_fail_log2 > 63 || o.up_fail_log2 > 63 || o.down_fail_log2 > 63) die("--*-fail-log2 must be in [0, 63]");
   return o;
 }
@@ -284,6 +293,96 @@ double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::
   }
   for (void* p : {depth, fail, r, ju, jd, summ, rep, evs, r2, ju2, jd2})
     if (p) ksa_dev_free(p);
+  return replay_s;
+}
+
+// ---- --depth-file: recorded queue depths ----------------------------------------------------------
+
+// One GPU's share of a recorded block. The file holds, per selected attribute, one row per trace
+// (a queue's history, the order metrics exports come in); rows of adjacent traces are adjacent, so
+// an N-chunk of one attribute is one contiguous read. Each chunk goes host -> device, through
+// ksa_ingest_decimal when the values are strings (strconv.Atoi as sqs/sqs.go:58; a string that
+// does not parse fails that poll) and through ksa_ingest_transpose into the tick-major layout,
+// then through the same replay calls as the synthetic path.
+double run_file_shard(const Options& o, int device, int64_t begin, int64_t end, std::vector<ksa_summary>* host) {
+  check(ksa_set_device(device), "ksa_set_device");
+  const int A = __builtin_popcount(o.policy.attr_mask);
+  const int64_t T = o.ticks, N = o.traces;
+  const bool text = o.depth_format[0] == 't';
+  const int64_t elem = o.depth_format == "i64" ? 8 : o.depth_format == "i32" ? 4 : o.depth_format == "text16" ? 16 : 32;
+  const bool full = o.mode == "full";
+  const double per_trace = (double)T * (elem + (text ? 9 : 0) + 8.0 * A + (text ? 1 : 0) + (full ? 5 : 0)) + 256;
+  int64_t NC = std::max<int64_t>(16, (int64_t)(48.0e9 / per_trace) / 16 * 16);
+  NC = std::min<int64_t>(std::min<int64_t>(NC, 1 << 20), (end - begin + 15) / 16 * 16);
+  const int64_t ld = NC;
+  FILE* f = std::fopen(o.depth_file.c_str(), "rb");
+  if (!f) die("cannot open " + o.depth_file);
+  void *src = nullptr, *vals = nullptr, *fsrc = nullptr, *depth = nullptr, *fail = nullptr, *hostbuf = nullptr;
+  void *r = nullptr, *ju = nullptr, *jd = nullptr, *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr, *summ = nullptr;
+  void *rep = nullptr, *evs = nullptr;
+  check(ksa_host_alloc(&hostbuf, (size_t)NC * T * elem), "host buffer");
+  check(ksa_dev_alloc(&src, (size_t)NC * T * elem), "source");
+  if (text) {
+    check(ksa_dev_alloc(&vals, (size_t)NC * T * 8), "values");
+    check(ksa_dev_alloc(&fsrc, (size_t)NC * T), "parse failures");
+    check(ksa_dev_alloc(&fail, (size_t)T * ld), "fail mask");
+  }
+  check(ksa_dev_alloc(&depth, (size_t)T * A * ld * 8), "depth");
+  check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
+  check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&jd, (size_t)ld * 8), "state");
+  check(ksa_dev_alloc(&summ, (size_t)ld * sizeof(ksa_summary)), "summary");
+  ksa_state st = {(int32_t*)r, (int64_t*)ju, (int64_t*)jd};
+  ksa_state st_sum = st;
+  if (full) {
+    check(ksa_dev_alloc(&rep, (size_t)T * ld * 4), "replicas");
+    check(ksa_dev_alloc(&evs, (size_t)T * ld), "events");
+    check(ksa_dev_alloc(&r2, (size_t)ld * 4), "state");
+    check(ksa_dev_alloc(&ju2, (size_t)ld * 8), "state");
+    check(ksa_dev_alloc(&jd2, (size_t)ld * 8), "state");
+    st_sum = {(int32_t*)r2, (int64_t*)ju2, (int64_t*)jd2};
+  }
+  const int32_t lo = (int32_t)o.policy.min_pods;
+  const int32_t hi = (int32_t)o.policy.max_pods >= lo ? (int32_t)o.policy.max_pods : lo;
+  double replay_s = 0;
+  for (int64_t c0 = begin; c0 < end; c0 += NC) {
+    const int64_t n = std::min(NC, end - c0);
+    for (int a = 0; a < A; ++a) {
+      const long long off = ((long long)a * N + c0) * T * elem;
+      if (fseeko(f, (off_t)off, SEEK_SET) != 0 || std::fread(hostbuf, (size_t)elem, (size_t)(n * T), f) != (size_t)(n * T))
+        die(o.depth_file + ": short read (needs " + std::to_string((long long)A * N * T * elem) + " bytes)");
+      check(ksa_memcpy_h2d(src, hostbuf, (size_t)n * T * elem, nullptr), "h2d");
+      check(ksa_stream_sync(nullptr), "sync");
+      if (text) {
+        check(ksa_ingest_decimal((const char*)src, (int32_t)elem, n * T, (int64_t*)vals, (uint8_t*)fsrc, nullptr), "ksa_ingest_decimal");
+        check(ksa_ingest_transpose(vals, 8, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
+        check(ksa_ingest_transpose_mask((const uint8_t*)fsrc, T, T, n, ld, (uint8_t*)fail, a > 0, nullptr), "ksa_ingest_transpose_mask");
+      } else {
+        check(ksa_ingest_transpose(src, (int32_t)elem, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
+      }
+    }
+    check(ksa_state_init(o.seed, c0, n, lo, hi, &st, nullptr), "ksa_state_init");
+    if (full) check(ksa_state_init(o.seed, c0, n, lo, hi, &st_sum, nullptr), "ksa_state_init");
+    check(ksa_summary_clear((ksa_summary*)summ, n, nullptr), "ksa_summary_clear");
+    check(ksa_stream_sync(nullptr), "sync");
+    const int64_t* d = (const int64_t*)depth;
+    const uint8_t* fm = (const uint8_t*)fail;
+    const auto t_a = std::chrono::steady_clock::now();
+    if (full && text) check(ksa_replay_full_faults(&o.policy, d, fm, T, A, n, ld, 0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full_faults");
+    else if (full) check(ksa_replay_full(&o.policy, d, T, A, n, ld, 0, &st, (int32_t*)rep, (uint8_t*)evs, nullptr), "ksa_replay_full");
+    else if (text) check(ksa_replay_summary_faults(&o.policy, d, fm, T, A, n, ld, 0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary_faults");
+    else check(ksa_replay_summary(&o.policy, d, T, A, n, ld, 0, &st, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+    check(ksa_stream_sync(nullptr), "sync");
+    replay_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_a).count();
+    if (full && text) check(ksa_replay_summary_faults(&o.policy, d, fm, T, A, n, ld, 0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary_faults");
+    else if (full) check(ksa_replay_summary(&o.policy, d, T, A, n, ld, 0, &st_sum, (ksa_summary*)summ, nullptr), "ksa_replay_summary");
+    check(ksa_memcpy_d2h(host->data() + c0, summ, (size_t)n * sizeof(ksa_summary), nullptr), "d2h");
+    check(ksa_stream_sync(nullptr), "sync");
+  }
+  std::fclose(f);
+  for (void* p : {src, vals, fsrc, depth, fail, r, ju, jd, r2, ju2, jd2, summ, rep, evs})
+    if (p) ksa_dev_free(p);
+  ksa_host_free(hostbuf);
   return replay_s;
 }
 
@@ -462,7 +561,11 @@ int main(int argc, char** argv) {
     const int64_t base = N / o.gpus, extra = N % o.gpus;
     const int64_t begin = g * base + std::min<int64_t>(g, extra);
     const int64_t end = begin + base + (g < extra ? 1 : 0);
-    workers.emplace_back([&, g, begin, end] { if (end > begin) secs[(size_t)g] = run_shard(o, o.device + g, begin, end, &host); });
+    workers.emplace_back([&, g, begin, end] {
+      if (end > begin)
+        secs[(size_t)g] = o.depth_file.empty() ? run_shard(o, o.device + g, begin, end, &host)
+                                               : run_file_shard(o, o.device + g, begin, end, &host);
+    });
   }
   for (auto& w : workers) w.join();
   const double replay_s = *std::max_element(secs.begin(), secs.end());
@@ -485,7 +588,7 @@ int main(int argc, char** argv) {
   std::printf("scale up successful %" PRIu64 " | scale down successful %" PRIu64 " | at max %" PRIu64 " | at min %" PRIu64
               " | up cool-down skips %" PRIu64 " | down cool-down skips %" PRIu64 "\n",
               tot[0], tot[1], tot[2], tot[3], tot[4], tot[5]);
-  if (o.faults())
+  if (o.faults() || (!o.depth_file.empty() && o.depth_format[0] == 't'))
     std::printf("failed to get SQS messages %" PRIu64 " | failed scaling up %" PRIu64 " | failed scaling down %" PRIu64 "\n",
                 tot[6], tot[7], tot[8]);
   std::printf("mean replicas %.4Lf | xor of trajectory fingerprints %016" PRIx64 "\n",

@@ -129,8 +129,9 @@ def test_recorded_strings_to_trajectory(engine):
     values, fail = engine.ingest_decimal(torch.from_numpy(rec).to(engine.dev))
     ld = 160
     depth = engine.ingest_transpose(values.view(N, T), T, N, 1, 0, ld)
-    # the failure mask is trace-major too: transpose it with the same kernel (as int32), then narrow
-    fail_t = engine.ingest_transpose(fail.view(N, T).to(torch.int32), T, N, 1, 0, ld)[:, 0, :].to(torch.uint8).contiguous()
+    # the failure bytes are trace-major too
+    fail_t = engine.ingest_transpose_mask(fail.view(N, T), T, N, ld)
+    assert torch.equal(fail_t[:, :N], fail.view(N, T).t())
     pol = ksa.Policy(attr_mask=1)
     state = engine.new_state(N, seed=3, lo=1, hi=5)
     replicas, events = engine.replay_full(pol, depth, T, 1, N, ld, 0, state, fail=fail_t)
@@ -144,3 +145,78 @@ def test_recorded_strings_to_trajectory(engine):
     assert np.array_equal(replicas.cpu().numpy()[:, :N], ref.replicas[:, :N])
     assert np.array_equal(events.cpu().numpy()[:, :N], ref.events[:, :N])
     assert (ref.events[:, :N] == 0xC0).sum() == 300
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,N,ld", [(1, 1, 16), (63, 65, 80), (200, 150, 160), (64, 64, 64)])
+def test_mask_transpose_and_accumulate(engine, T, N, ld):
+    """ksa_ingest_transpose_mask: bytes [N][src_ld] -> [T][ld]; with accumulate the masks of several
+    attributes are OR-ed (a failed Atoi on any attribute fails the poll); nothing outside [T][N]
+    is written."""
+    import torch
+
+    rng = np.random.default_rng(T * 1000 + N)
+    a = torch.from_numpy(rng.choice(np.array([0, 0, 0, 1], dtype=np.uint8), size=(N, T + 3))).to(engine.dev)
+    b = torch.from_numpy(rng.choice(np.array([0, 0, 1], dtype=np.uint8), size=(N, T + 3))).to(engine.dev)
+    out = torch.full((T + 2, ld), 0xEE, dtype=torch.uint8, device=engine.dev)
+    engine.ingest_transpose_mask(a[:, :T], T, N, ld, out=out[1:T + 1])
+    assert torch.equal(out[1:T + 1, :N], a[:, :T].t())
+    engine.ingest_transpose_mask(b[:, :T], T, N, ld, out=out[1:T + 1], accumulate=True)
+    assert torch.equal(out[1:T + 1, :N], (a[:, :T] | b[:, :T]).t())
+    assert (out[0] == 0xEE).all() and (out[T + 1] == 0xEE).all() and (out[1:T + 1, N:] == 0xEE).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt", ["i64", "i32", "text16"])
+@pytest.mark.parametrize("mode", ["summary", "full"])
+def test_cli_replays_a_recorded_file(engine, tmp_path, fmt, mode):
+    """ksa-replay --depth-file: a recording of two attributes, trace-major, as int64 / int32 / decimal
+    strings (some of them unparsable: those polls fail as in sqs/sqs.go:58-61). Totals and the
+    fingerprint digest equal the oracle's replay of the same values."""
+    import os
+    import re
+    import subprocess
+
+    from tests import oracle_lib
+
+    rng = np.random.default_rng(len(fmt) * 10 + len(mode))
+    A, N, T = 2, 333, 150
+    vals = rng.integers(0, 200, size=(A, N, T)).astype(np.int64)
+    fail = np.zeros((T, N), dtype=np.uint8)
+    path = tmp_path / f"depth.{fmt}"
+    if fmt == "i64":
+        vals.tofile(path)
+    elif fmt == "i32":
+        vals.astype(np.int32).tofile(path)
+    else:
+        texts = [str(int(v)).encode() for v in vals.reshape(-1)]
+        bad = rng.choice(A * N * T, size=400, replace=False)
+        for i in bad:
+            texts[i] = [b"", b"n/a", b"12 ", b"1_0"][int(rng.integers(0, 4))]
+            a, rest = divmod(int(i), N * T)
+            n, t = divmod(rest, T)
+            vals[a, n, t] = 0          # what the decoder stores for a failed parse
+            fail[t, n] = 1             # KSA_FAIL_POLL
+        records(texts, 16).tofile(path)
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    r = subprocess.run([cli, "--poll-period=5s", "--scale-up-cool-down=10s", "--scale-down-cool-down=20s",
+                        "--scale-up-messages=250", "--scale-down-messages=40", "--max-pods=7",
+                        "--attribute-names=ApproximateNumberOfMessages,ApproximateNumberOfMessagesDelayed",
+                        "--traces", str(N), "--ticks", str(T), "--mode", mode, "--seed", "5",
+                        "--depth-file", str(path), "--depth-format", fmt], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    m = re.search(r"scale up successful (\d+) \| scale down successful (\d+) \| at max (\d+) \| at min (\d+) \| "
+                  r"up cool-down skips (\d+) \| down cool-down skips (\d+)", r.stdout)
+    assert m, r.stdout
+    digest = int(re.search(r"fingerprints ([0-9a-f]{16})", r.stdout).group(1), 16)
+    pol = ksa.Policy(attr_mask=3, scale_up_messages=250, scale_down_messages=40, max_pods=7,
+                     scale_up_cool_down=10 * 10**9, scale_down_cool_down=20 * 10**9)
+    d_host = np.ascontiguousarray(vals.transpose(2, 0, 1))  # [T][A][N]
+    ref = oracle_lib.replay(pol.to_c(), d_host, T, A, N, N, 0, *oracle_lib.fresh_state(5, 0, N, 1, 7),
+                            want_full=False, want_summary=True, fail=fail if fmt == "text16" else None)
+    want = [int(ref.summary[k].sum()) for k in ("up_applied", "down_applied", "up_noop", "down_noop", "up_cool", "down_cool")]
+    assert [int(x) for x in m.groups()] == want
+    assert digest == int(np.bitwise_xor.reduce(ref.summary["hash"]))
+    if fmt == "text16":
+        f = re.search(r"failed to get SQS messages (\d+)", r.stdout)
+        assert f and int(f.group(1)) == int(ref.summary["poll_failed"].sum()) > 0
