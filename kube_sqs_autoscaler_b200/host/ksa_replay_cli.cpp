@@ -219,7 +219,9 @@ Options parse(int argc, char** argv) {
   if (o.top < 1) die("--top must be >= 1");
   if (o.depth_format != "i64" && o.depth_format != "i32" && o.depth_format != "text16" && o.depth_format != "text32")
     die("--depth-format must be i64, i32, text16 or text32");
-  if (!o.depth_file.empty() && (o.mode == "sweep" || o.faults())) die("--depth-file goes with --mode full|summary and no --*-fail-log2");
+  if (!o.depth_file.empty() && o.faults()) die("--depth-file does not take --*-fail-log2");
+  if (!o.depth_file.empty() && o.mode == "sweep" && o.depth_format[0] == 't')
+    die("--mode sweep reads recordings as --depth-format i64 or i32 (the sweep has no failed polls)");
   if (o.poll_fail_log2 > 63 || o.up_fail_log2 > 63 || o.down_fail_log2 > 63) die("--*-fail-log2 must be in [0, 63]");
   return o;
 }
@@ -298,35 +300,76 @@ double run_shard(const Options& o, int device, int64_t begin, int64_t end, std::
 
 // ---- --depth-file: recorded queue depths ----------------------------------------------------------
 
-// One GPU's share of a recorded block. The file holds, per selected attribute, one row per trace
-// (a queue's history, the order metrics exports come in); rows of adjacent traces are adjacent, so
-// an N-chunk of one attribute is one contiguous read. Each chunk goes host -> device, through
-// ksa_ingest_decimal when the values are strings (strconv.Atoi as sqs/sqs.go:58; a string that
-// does not parse fails that poll) and through ksa_ingest_transpose into the tick-major layout,
-// then through the same replay calls as the synthetic path.
+// Reads N-chunks of a recording into the tick-major device layout. The file holds, per selected
+// attribute, one row per trace (a queue's history, the order metrics exports come in); rows of
+// adjacent traces are adjacent, so an N-chunk of one attribute is one contiguous read. A chunk goes
+// host -> device, through ksa_ingest_decimal when the values are strings (strconv.Atoi as
+// sqs/sqs.go:58; a string that does not parse fails that poll), and through ksa_ingest_transpose.
+struct RecordingLoader {
+  const Options& o;
+  int A;
+  int64_t T, N, elem, max_n;
+  bool text;
+  FILE* f = nullptr;
+  void *hostbuf = nullptr, *src = nullptr, *vals = nullptr, *fsrc = nullptr;
+
+  static int64_t elem_bytes(const std::string& fmt) { return fmt == "i64" ? 8 : fmt == "i32" ? 4 : fmt == "text16" ? 16 : 32; }
+
+  RecordingLoader(const Options& opt, int64_t max_traces)
+      : o(opt), A(__builtin_popcount(opt.policy.attr_mask)), T(opt.ticks), N(opt.traces),
+        elem(elem_bytes(opt.depth_format)), max_n(max_traces), text(opt.depth_format[0] == 't') {
+    f = std::fopen(o.depth_file.c_str(), "rb");
+    if (!f) die("cannot open " + o.depth_file);
+    check(ksa_host_alloc(&hostbuf, (size_t)max_n * T * elem), "host buffer");
+    check(ksa_dev_alloc(&src, (size_t)max_n * T * elem), "source");
+    if (text) {
+      check(ksa_dev_alloc(&vals, (size_t)max_n * T * 8), "values");
+      check(ksa_dev_alloc(&fsrc, (size_t)max_n * T), "parse failures");
+    }
+  }
+  ~RecordingLoader() {
+    if (f) std::fclose(f);
+    for (void* p : {src, vals, fsrc})
+      if (p) ksa_dev_free(p);
+    if (hostbuf) ksa_host_free(hostbuf);
+  }
+  // traces [c0, c0 + n) -> depth [T][A][ld]; fail [T][ld] when the format is text (else untouched)
+  void load(int64_t c0, int64_t n, int64_t ld, void* depth, void* fail) {
+    for (int a = 0; a < A; ++a) {
+      const long long off = ((long long)a * N + c0) * T * elem;
+      if (fseeko(f, (off_t)off, SEEK_SET) != 0 || std::fread(hostbuf, (size_t)elem, (size_t)(n * T), f) != (size_t)(n * T))
+        die(o.depth_file + ": short read (needs " + std::to_string((long long)A * N * T * elem) + " bytes)");
+      check(ksa_memcpy_h2d(src, hostbuf, (size_t)n * T * elem, nullptr), "h2d");
+      check(ksa_stream_sync(nullptr), "sync");
+      if (text) {
+        check(ksa_ingest_decimal((const char*)src, (int32_t)elem, n * T, (int64_t*)vals, (uint8_t*)fsrc, nullptr), "ksa_ingest_decimal");
+        check(ksa_ingest_transpose(vals, 8, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
+        check(ksa_ingest_transpose_mask((const uint8_t*)fsrc, T, T, n, ld, (uint8_t*)fail, a > 0, nullptr), "ksa_ingest_transpose_mask");
+      } else {
+        check(ksa_ingest_transpose(src, (int32_t)elem, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
+      }
+    }
+    check(ksa_stream_sync(nullptr), "sync");
+  }
+};
+
+// One GPU's share of a recorded block: load a chunk, then the same replay calls as the synthetic path.
 double run_file_shard(const Options& o, int device, int64_t begin, int64_t end, std::vector<ksa_summary>* host) {
   check(ksa_set_device(device), "ksa_set_device");
   const int A = __builtin_popcount(o.policy.attr_mask);
-  const int64_t T = o.ticks, N = o.traces;
+  const int64_t T = o.ticks;
   const bool text = o.depth_format[0] == 't';
-  const int64_t elem = o.depth_format == "i64" ? 8 : o.depth_format == "i32" ? 4 : o.depth_format == "text16" ? 16 : 32;
+  const int64_t elem = RecordingLoader::elem_bytes(o.depth_format);
   const bool full = o.mode == "full";
   const double per_trace = (double)T * (elem + (text ? 9 : 0) + 8.0 * A + (text ? 1 : 0) + (full ? 5 : 0)) + 256;
   int64_t NC = std::max<int64_t>(16, (int64_t)(48.0e9 / per_trace) / 16 * 16);
   NC = std::min<int64_t>(std::min<int64_t>(NC, 1 << 20), (end - begin + 15) / 16 * 16);
   const int64_t ld = NC;
-  FILE* f = std::fopen(o.depth_file.c_str(), "rb");
-  if (!f) die("cannot open " + o.depth_file);
-  void *src = nullptr, *vals = nullptr, *fsrc = nullptr, *depth = nullptr, *fail = nullptr, *hostbuf = nullptr;
+  RecordingLoader loader(o, NC);
+  void *depth = nullptr, *fail = nullptr;
   void *r = nullptr, *ju = nullptr, *jd = nullptr, *r2 = nullptr, *ju2 = nullptr, *jd2 = nullptr, *summ = nullptr;
   void *rep = nullptr, *evs = nullptr;
-  check(ksa_host_alloc(&hostbuf, (size_t)NC * T * elem), "host buffer");
-  check(ksa_dev_alloc(&src, (size_t)NC * T * elem), "source");
-  if (text) {
-    check(ksa_dev_alloc(&vals, (size_t)NC * T * 8), "values");
-    check(ksa_dev_alloc(&fsrc, (size_t)NC * T), "parse failures");
-    check(ksa_dev_alloc(&fail, (size_t)T * ld), "fail mask");
-  }
+  if (text) check(ksa_dev_alloc(&fail, (size_t)T * ld), "fail mask");
   check(ksa_dev_alloc(&depth, (size_t)T * A * ld * 8), "depth");
   check(ksa_dev_alloc(&r, (size_t)ld * 4), "state");
   check(ksa_dev_alloc(&ju, (size_t)ld * 8), "state");
@@ -347,20 +390,7 @@ double run_file_shard(const Options& o, int device, int64_t begin, int64_t end, 
   double replay_s = 0;
   for (int64_t c0 = begin; c0 < end; c0 += NC) {
     const int64_t n = std::min(NC, end - c0);
-    for (int a = 0; a < A; ++a) {
-      const long long off = ((long long)a * N + c0) * T * elem;
-      if (fseeko(f, (off_t)off, SEEK_SET) != 0 || std::fread(hostbuf, (size_t)elem, (size_t)(n * T), f) != (size_t)(n * T))
-        die(o.depth_file + ": short read (needs " + std::to_string((long long)A * N * T * elem) + " bytes)");
-      check(ksa_memcpy_h2d(src, hostbuf, (size_t)n * T * elem, nullptr), "h2d");
-      check(ksa_stream_sync(nullptr), "sync");
-      if (text) {
-        check(ksa_ingest_decimal((const char*)src, (int32_t)elem, n * T, (int64_t*)vals, (uint8_t*)fsrc, nullptr), "ksa_ingest_decimal");
-        check(ksa_ingest_transpose(vals, 8, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
-        check(ksa_ingest_transpose_mask((const uint8_t*)fsrc, T, T, n, ld, (uint8_t*)fail, a > 0, nullptr), "ksa_ingest_transpose_mask");
-      } else {
-        check(ksa_ingest_transpose(src, (int32_t)elem, T, T, n, A, a, ld, (int64_t*)depth, nullptr), "ksa_ingest_transpose");
-      }
-    }
+    loader.load(c0, n, ld, depth, fail);
     check(ksa_state_init(o.seed, c0, n, lo, hi, &st, nullptr), "ksa_state_init");
     if (full) check(ksa_state_init(o.seed, c0, n, lo, hi, &st_sum, nullptr), "ksa_state_init");
     check(ksa_summary_clear((ksa_summary*)summ, n, nullptr), "ksa_summary_clear");
@@ -379,10 +409,8 @@ double run_file_shard(const Options& o, int device, int64_t begin, int64_t end, 
     check(ksa_memcpy_d2h(host->data() + c0, summ, (size_t)n * sizeof(ksa_summary), nullptr), "d2h");
     check(ksa_stream_sync(nullptr), "sync");
   }
-  std::fclose(f);
-  for (void* p : {src, vals, fsrc, depth, fail, r, ju, jd, r2, ju2, jd2, summ, rep, evs})
+  for (void* p : {depth, fail, r, ju, jd, r2, ju2, jd2, summ, rep, evs})
     if (p) ksa_dev_free(p);
-  ksa_host_free(hostbuf);
   return replay_s;
 }
 
@@ -446,6 +474,8 @@ double run_sweep_shard(const Options& o, const std::vector<ksa_policy>& grid, in
   g.walk_step = std::max<int64_t>(1, g.high_max / 32);
   void* walk = nullptr;
   check(ksa_dev_alloc(&walk, (size_t)ld * 8), "walk state");
+  const bool recorded = !o.depth_file.empty();
+  RecordingLoader* loader = recorded ? new RecordingLoader(o, NC) : nullptr;
   double secs = 0;
   {  // untimed short pass: the first launch of a kernel pays for loading it onto the device, and
      // an idle GPU needs some tens of milliseconds of work before its clocks are up
@@ -464,8 +494,12 @@ double run_sweep_shard(const Options& o, const std::vector<ksa_policy>& grid, in
   for (int64_t c0 = begin; c0 < end; c0 += NC) {
     const int64_t n = std::min(NC, end - c0);
     check(ksa_state_init(o.seed, c0, n, lo, hi, &st, nullptr), "ksa_state_init");
-    check(ksa_gen_walk_init(&g, c0, n, (int64_t*)walk, nullptr), "ksa_gen_walk_init");
-    check(ksa_gen_traces(&g, 0, T, A, c0, n, ld, (int64_t*)depth, (int64_t*)walk, nullptr), "ksa_gen_traces");
+    if (recorded) {
+      loader->load(c0, n, ld, depth, nullptr);
+    } else {
+      check(ksa_gen_walk_init(&g, c0, n, (int64_t*)walk, nullptr), "ksa_gen_walk_init");
+      check(ksa_gen_traces(&g, 0, T, A, c0, n, ld, (int64_t*)depth, (int64_t*)walk, nullptr), "ksa_gen_traces");
+    }
     check(ksa_stream_sync(nullptr), "sync");
     const auto a = std::chrono::steady_clock::now();
     check(ksa_replay_sweep(grid.data(), P, table, (const int64_t*)depth, T, A, n, ld, (const int32_t*)r,
@@ -480,6 +514,7 @@ double run_sweep_shard(const Options& o, const std::vector<ksa_policy>& grid, in
   check(ksa_memcpy_d2h(cost_out->data(), pcost, (size_t)P * 8, nullptr), "d2h");
   check(ksa_stream_sync(nullptr), "sync");
   for (void* p : {depth, r, ju, jd, summ, table, pcost, bpol, bcost, walk}) ksa_dev_free(p);
+  delete loader;
   return secs;
 }
 

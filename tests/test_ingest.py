@@ -220,3 +220,42 @@ def test_cli_replays_a_recorded_file(engine, tmp_path, fmt, mode):
     if fmt == "text16":
         f = re.search(r"failed to get SQS messages (\d+)", r.stdout)
         assert f and int(f.group(1)) == int(ref.summary["poll_failed"].sum()) > 0
+
+
+@pytest.mark.gpu
+def test_cli_sweeps_a_recorded_file(engine, tmp_path):
+    """ksa-replay --mode sweep --depth-file: tuning the flags on a recording. The ranking equals the
+    one from the oracle's per-policy replays of the same values + oracle/policy_py.sweep_reduce."""
+    import os
+    import re
+    import subprocess
+
+    from oracle import policy_py
+    from tests import oracle_lib
+
+    rng = np.random.default_rng(17)
+    N, T = 210, 90
+    vals = np.cumsum(rng.integers(-20, 21, size=(N, T)), axis=1).clip(0, 400).astype(np.int32)
+    path = tmp_path / "depth.i32"
+    vals.tofile(path)
+    cli = os.path.join(os.path.dirname(os.path.dirname(__file__)), "kube_sqs_autoscaler_b200", "ksa-replay")
+    r = subprocess.run([cli, "--mode", "sweep", "--attribute-names=ApproximateNumberOfMessages",
+                        "--scale-up-messages=80,150", "--scale-down-messages=10,30", "--scale-up-cool-down=0s,15s",
+                        "--max-pods=4,8", "--traces", str(N), "--ticks", str(T), "--seed", "2", "--cost-saturated", "9",
+                        "--cost-churn", "4", "--top", "16", "--depth-file", str(path), "--depth-format", "i32"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    rows = re.findall(r"#(\d+) policy (\d+) cost (-?\d+) best-for (\d+) traces", r.stdout)
+    assert len(rows) == 16, r.stdout
+    S = 10**9
+    pols = [ksa.Policy(attr_mask=1, scale_up_messages=um, scale_down_messages=dm, scale_up_cool_down=uc * S, max_pods=mx)
+            for um in (80, 150) for dm in (10, 30) for uc in (0, 15) for mx in (4, 8)]
+    d_host = np.ascontiguousarray(vals.astype(np.int64).T.reshape(T, 1, N))
+    st = oracle_lib.fresh_state(2, 0, N, 1, 4)
+    summ = np.stack([oracle_lib.replay(p.to_c(), d_host, T, 1, N, N, 0, *st, want_full=False, want_summary=True).summary
+                     for p in pols])
+    cost, best, _ = policy_py.sweep_reduce(summ, w_pod_ticks=1, w_saturated=9, w_churn=4, w_blocked=0)
+    order = sorted(range(len(pols)), key=lambda p: (int(cost[p]), p))
+    wins = np.bincount(best, minlength=len(pols))
+    for k, (rank, pid, c, w) in enumerate(rows):
+        assert (int(rank), int(pid), int(c), int(w)) == (k + 1, order[k], int(cost[order[k]]), int(wins[order[k]])), rows[k]
