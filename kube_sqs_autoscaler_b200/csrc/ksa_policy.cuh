@@ -502,9 +502,9 @@ __device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c)
 }
 
 // Per-trace accumulators of the summary kernels (registers). The six event counters are kept as
-// 8-bit fields of two registers (pk4: bits 0..3 of the event byte, one field per byte; pk2: bits 4
-// and 5 at bit 8 and bit 16) and must be added into 32-bit counters before a field can overflow,
-// i.e. at least every KSA_FLUSH_TICKS ticks (ksa_summary_flush).
+// 5-bit fields of one register, in the layout of the wide event code, so that a tick's code is
+// simply added; they are folded into 10-bit fields before a field can overflow (every <= 31 ticks,
+// ksa_summary_fold) and those into the 32-bit counters of the record (ksa_summary_flush).
 struct ksa_summary_acc {
   int rmin, rmax;
   int rstash;         // first replica count of a pair of ticks (KSA_TICK_FIRST), see ksa_summary_tick

@@ -5,8 +5,10 @@
 // R independent state machines (ksa_policy.cuh), so the depth block is re-read P/R times in total
 // and stays resident in the 126 MB L2. Unlike the single-policy replay this kernel is bound by
 // integer issue, not HBM: compulsory bytes per decision are ~0.01. The state
-// machine therefore uses ksa_step_fma (conditional moves as IMADs on the FMA pipe) and the packed
-// event counters of ksa_summary_tick, which halve the work of the half-rate ALU pipe.
+// machine therefore uses ksa_step_fma / ksa_step_fma_narrow (conditional moves as IMADs on the FMA
+// pipe, as few compares as the policy grid allows) and the packed event counters of
+// ksa_summary_tick. Policy tiles are split by kind (narrow or not) into two launches, and the grid
+// walks L2-sized groups of traces through all policy tiles (see the kernel).
 #include "ksa_internal.h"
 
 #include <cstdlib>
