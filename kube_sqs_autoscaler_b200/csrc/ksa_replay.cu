@@ -6,7 +6,9 @@
 // in flight and the loop-carried state chain never waits on DRAM), runs the branch-free policy
 // step (ksa_policy.cuh) on registers, and writes the per-tick replica counts (int32) and event
 // bytes back as one vector store each. Nothing is re-read, so all accesses carry streaming hints
-// (L1::no_allocate, evict-first). No shared memory: there is no reuse to stage.
+// (L1::no_allocate, evict-first). No shared memory: there is no reuse to stage (a cp.async.bulk /
+// mbarrier staging of the rows exists for the summary replay, ksa_summary_bulk_kernel below; it
+// measured slower than the register ring and is kept as a tuning point).
 //
 // Replaces, for N traces at once: sqs/sqs.go:56-64 (sum), main.go:51-77 (thresholds, cool-downs,
 // stamps), scale/scale.go:60-69,87-97 (clamped steps). HBM-bound: 8A bytes in + 5 bytes out per
@@ -40,8 +42,11 @@ struct ReplayArgs {
 enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
 // STEP: 0 = ksa_step (C++), 1 = ksa_step_ptx (predication spelled out in PTX), 2 = ksa_step_fma
 // (conditional moves/adds as predicated IMADs on the FMA pipe). Same function, same results.
-// 4 = ksa_step_faults (C++), 5 = ksa_step_faults_fma: the steps of the *_faults entry points, which
-// also read one failure-mask byte per decision.
+// 4 = ksa_step_faults (C++), 5 = ksa_step_faults_fma / ksa_step_faults_fma2: the steps of the
+// *_faults entry points, which also read one failure-mask byte per decision.
+// 6 = ksa_step_fma for ordered thresholds (summary mode), 7 = the same with failures,
+// 8 = ksa_step_faults_fma2 with the event byte out (full mode). In summary mode the FMA steps
+// return the wide event code (ksa_policy.cuh) and one trace per thread is the default.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
 
