@@ -789,3 +789,41 @@ def test_rendered_log_of_a_gpu_trajectory_matches_the_restated_reference(engine)
                                text_log=text)
         got = ksa.render_log(pol, int(st[0][n]), d_host[:, :, n].sum(axis=1), replicas[:, n], events[:, n])
         assert got == text, f"trace {n}"
+
+
+@pytest.mark.parametrize("A", [1, 3])
+def test_sweep_random_grids_mixed_tiles(engine, A):
+    """Random policy grids (ordered, overlapping and out-of-int32 thresholds mixed, P not a multiple
+    of the tile) on adversarial depths: every (policy, trace) summary equals the oracle's. Exercises
+    the split launch with arbitrary tile patterns."""
+    torch = torch_mod()
+    rng = np.random.default_rng(4242 + A)
+    for case in range(6):
+        P = int(rng.integers(1, 24))
+        T = int(rng.integers(1, 80))
+        N = int(rng.choice([1, 33, 130, 257]))
+        mask = (1 << A) - 1
+        pols = []
+        for _ in range(P):
+            p = random_policy(rng, A)
+            kind = rng.integers(0, 3)
+            if kind == 0:      # an everyday ordered policy
+                p = ksa.Policy(attr_mask=mask, scale_up_messages=int(rng.integers(50, 400)),
+                               scale_down_messages=int(rng.integers(0, 49)), poll_period=p.poll_period,
+                               scale_up_cool_down=p.scale_up_cool_down, scale_down_cool_down=p.scale_down_cool_down,
+                               max_pods=int(rng.integers(2, 12)))
+            else:              # anything, including thresholds beyond int32 and overlaps
+                p = ksa.Policy(attr_mask=mask, poll_period=p.poll_period, scale_up_cool_down=p.scale_up_cool_down,
+                               scale_down_cool_down=p.scale_down_cool_down, scale_up_messages=p.scale_up_messages,
+                               scale_down_messages=p.scale_down_messages, scale_up_pods=p.scale_up_pods,
+                               scale_down_pods=p.scale_down_pods, max_pods=p.max_pods, min_pods=p.min_pods)
+            pols.append(p)
+        depth_np = adversarial_depth(rng, T, A, N, pols[0])
+        r0 = rng.integers(-2, 9, size=N).astype(np.int32)
+        st = (r0, np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+        got = engine.replay_sweep(pols, torch.from_numpy(depth_np).to(engine.dev), T, A, N, N,
+                                  torch.from_numpy(r0).to(engine.dev))
+        got = got.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(P, N)
+        for i, pol in enumerate(pols):
+            ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, N, 0, *st, want_full=False, want_summary=True)
+            assert got[i].tobytes() == ref.summary.tobytes(), f"A={A} case {case} policy {i}/{P}: {pol}"
