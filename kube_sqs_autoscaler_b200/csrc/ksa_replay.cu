@@ -597,6 +597,11 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(36, MODE_FULL, 16, 2, HINT_NA, 2, 64, 4, 8, 2, 64, 6, 8, 1, 64, 8),
     KSA_VARIANT(38, MODE_FULL, 8, 2, HINT_NA_EF, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
     KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
+    // fewer traces per thread: for trace counts that cannot fill the GPU at V = 8 (see pick_full_variant)
+    KSA_VARIANT(42, MODE_FULL, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+    KSA_VARIANT(43, MODE_FULL, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(44, MODE_FULL, 4, 3, HINT_NA, 2, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
+    KSA_VARIANT(45, MODE_FULL, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -651,6 +656,8 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(9, MODE_SUMMARY, 1, 8, HINT_NA, 7, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
+constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per thread
+constexpr int kDefaultFullV2 = 43;   // fewer than 327680 traces: two traces per thread
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
 constexpr int kDefaultSummary = 20;  // one trace per thread: no interleaved state machines, no predicate spills
 constexpr int kDefaultSummaryOrdered = 21;  // the same with the ordered-thresholds step
@@ -705,8 +712,12 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
   const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
   const int default_summary = ordered ? kDefaultSummaryOrdered : kDefaultSummary;
+  // Full mode: 8 traces per thread need ~600k traces to fill 148 SMs; below that the kernel is bound
+  // by the per-thread state chain, not by HBM, and fewer traces per thread win
+  // (profiles/r01_small_n_variants.txt: at N = 65536, V = 8: 0.30 of the copy peak, V = 1: 0.73).
+  const int default_full = N < 196608 ? kDefaultFullV1 : (N < 327680 ? kDefaultFullV2 : kDefaultFull);
   const Variant* var = mode == MODE_FULL
-                           ? find_variant(kFullVariants, want < 0 ? kDefaultFull : want)
+                           ? find_variant(kFullVariants, want < 0 ? default_full : want)
                            : find_variant(kSummaryVariants, want < 0 ? default_summary : want);
   if (var && var->step == 6 && !ordered) var = find_variant(kSummaryVariants, kDefaultSummary);
   // Variants compiled for "both outputs" cannot run with one of them missing.
