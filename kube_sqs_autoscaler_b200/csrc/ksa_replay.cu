@@ -641,6 +641,7 @@ const Variant kFullFaultsVariants[] = {
     KSA_VARIANT(5, MODE_FULL, 4, 3, HINT_NA, 8, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
     KSA_VARIANT(6, MODE_FULL, 8, 2, HINT_NA, 8, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
     KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NA, 8, 128, 5, 4, 2, 128, 5, 2, 3, 128, 6),
+    KSA_VARIANT(9, MODE_FULL, 1, 8, HINT_NA, 8, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),  // small trace counts
 };
 const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -726,7 +727,8 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   if (faults) {
     // Faults variants: default = the FMA-steered kernel when both outputs are wanted; the tuning
     // knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
-    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? 8 : 1) : (ordered ? 7 : 4);  // profiles/r01_config2_faults.txt
+    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? (N < 131072 ? 9 : 8) : 1)
+                                : (ordered ? 7 : 4);  // profiles/r01_config2_faults.txt
     if (const char* e = std::getenv("KSA_FAULTS_VARIANT")) fid = std::atoi(e);
     var = mode == MODE_FULL ? find_variant(kFullFaultsVariants, fid) : find_variant(kSummaryFaultsVariants, fid);
     if (!var) var = mode == MODE_FULL ? &kFullFaultsVariants[2] : &kSummaryFaultsVariants[2];  // unknown id

@@ -82,7 +82,7 @@ def test_random_policies_with_failures(engine, A):
                 engine.set_variant(-2 if scalar else 0, -2 if scalar else 0)
                 out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
                 check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} scalar={scalar}")
-            for fid in ("1", "2", "3", "4", "5", "6", "7", "8", "9"):  # every entry of the faults variant tables
+            for fid in ("1", "2", "3", "4", "5", "6", "7", "8", "9"):  # every entry of the faults variant tables (9: V1, small N)
                 os.environ["KSA_FAULTS_VARIANT"] = fid
                 out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
                 check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} faults_variant={fid}")
