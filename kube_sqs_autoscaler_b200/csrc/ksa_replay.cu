@@ -602,6 +602,7 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(43, MODE_FULL, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(44, MODE_FULL, 4, 3, HINT_NA, 2, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
     KSA_VARIANT(45, MODE_FULL, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
+    KSA_VARIANT(46, MODE_FULL_OPT, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
@@ -660,6 +661,7 @@ constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.tx
 constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per thread
 constexpr int kDefaultFullV2 = 43;   // fewer than 327680 traces: two traces per thread
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
+constexpr int kDefaultFullOptV1 = 46;  // the same below 196608 traces
 constexpr int kDefaultSummary = 20;  // one trace per thread: no interleaved state machines, no predicate spills
 constexpr int kDefaultSummaryOrdered = 21;  // the same with the ordered-thresholds step
 
@@ -722,7 +724,8 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
                            : find_variant(kSummaryVariants, want < 0 ? default_summary : want);
   if (var && var->step == 6 && !ordered) var = find_variant(kSummaryVariants, kDefaultSummary);
   // Variants compiled for "both outputs" cannot run with one of them missing.
-  if (!faults && mode == MODE_FULL && (!replicas_dev || !events_dev)) var = find_variant(kFullVariants, kDefaultFullOpt);
+  if (!faults && mode == MODE_FULL && (!replicas_dev || !events_dev))
+    var = find_variant(kFullVariants, N < 196608 ? kDefaultFullOptV1 : kDefaultFullOpt);
   const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];
   if (faults) {
     // Faults variants: default = the FMA-steered kernel when both outputs are wanted; the tuning

@@ -13,7 +13,7 @@ from tests import oracle_lib
 
 pytestmark = pytest.mark.gpu
 S = 10**9
-FULL_IDS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45]
+FULL_IDS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45, 46]
 
 
 @pytest.mark.parametrize("A", [1, 3])

@@ -19,7 +19,7 @@ pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45]   # -2 = scalar kernel
+FULL_VARIANTS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45, 46]   # -2 = scalar kernel
 SUMMARY_VARIANTS = [-2, 5, 7, 8, 9, 10, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22,  # 21, 22: ordered-thresholds step
                     30, 33, 38]  # cp.async.bulk + mbarrier staging
 
