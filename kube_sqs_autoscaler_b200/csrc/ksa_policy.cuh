@@ -311,6 +311,47 @@ __device__ __forceinline__ int ksa_saturate_s32(long long n) {
   return r;
 }
 
+// The sweep's step for a register tile whose policies all have the SAME two thresholds (and are
+// narrow, see above): the grid of main.go:86-87 x the other tunables varies the thresholds slowest,
+// so the machines of a tile almost always share them. The two threshold tests of main.go:51,65 are
+// then made once per (trace, tick) by the caller and reach the machines through values, not
+// predicates (a thread has 7 predicate registers for four interleaved machines):
+//   iu = n >= up   ? i : INT_MIN        gate test "su <= iu" is false when the threshold is not met
+//   id = n <= down ? i : INT_MIN        (stamps are >= 0 in the sweep: ksa_local_stamp(.., 0, 0))
+//   e0  = UP_COOL if n >= up, DOWN_COOL if n <= down, else 0     (ordered thresholds: never both)
+//   e0n = e0 + (UP_NOOP - UP_COOL)      only selected when the up gate is open
+// Per machine: 4 ISETP + 1 SEL + 2 VIADDMNMX on the ALU pipe, 7 IMAD on the FMA pipe (the narrow
+// step above: 6 ISETP + 1 SEL + 2 VIADDMNMX + 9 IMAD). Returns the wide event code.
+__device__ __forceinline__ unsigned ksa_step_fma_shared(const ksa_step_consts& c, int iu, int id, unsigned e0,
+                                                        unsigned e0n, int i, int one, ksa_trace_regs& s) {
+  unsigned ev;
+  asm("{\n\t"
+      ".reg .pred ugo, uapp, dgo, dapp;\n\t"
+      ".reg .s32 t, u;\n\t"
+      "setp.le.s32 ugo, %2, %4;\n\t"                // main.go:51 + :52 false
+      "setp.lt.and.s32 uapp, %1, %6, ugo;\n\t"      // scale.go:62
+      "selp.u32 %0, %15, %14, ugo;\n\t"             // UP_COOL -> UP_NOOP when the gate is open ...
+      "@uapp mad.lo.s32 %0, %13, %16, %0;\n\t"      // ... UP_APPLIED
+      "add.s32 t, %1, %8;\n\t"                      // scale.go:66
+      "min.s32 t, t, %6;\n\t"                       // scale.go:67-69
+      "@uapp mad.lo.s32 %1, t, %13, 0;\n\t"
+      "@ugo mad.lo.s32 %2, %10, %13, %11;\n\t"      // main.go:62   su = i + cu
+      "setp.le.s32 dgo, %3, %5;\n\t"                // main.go:65 + :66 false
+      "setp.gt.and.s32 dapp, %1, %7, dgo;\n\t"      // scale.go:89
+      "@dgo mad.lo.s32 %3, %10, %13, %12;\n\t"      // main.go:76   sd = i + cd
+      "@dgo mad.lo.s32 %0, %13, %17, %0;\n\t"       // DOWN_COOL -> DOWN_NOOP ...
+      "@dapp mad.lo.s32 %0, %13, %18, %0;\n\t"      // ... DOWN_APPLIED
+      "sub.s32 u, %1, %9;\n\t"                      // scale.go:94
+      "max.s32 u, u, %7;\n\t"                       // scale.go:95-97
+      "@dapp mad.lo.s32 %1, u, %13, 0;\n\t"
+      "}"
+      : "=&r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd)
+      : "r"(iu), "r"(id), "r"(c.max32), "r"(c.min32), "r"(c.up32), "r"(c.down32), "r"(i), "r"(c.cu),
+        "r"(c.cd), "r"(one), "r"(e0), "r"(e0n), "n"((int)KSA_W_UP_APPLIED - (int)KSA_W_UP_NOOP),
+        "n"((int)KSA_W_DOWN_NOOP - (int)KSA_W_DOWN_COOL), "n"((int)KSA_W_DOWN_APPLIED - (int)KSA_W_DOWN_NOOP));
+  return ev;
+}
+
 // The step in a world where calls fail (the *_faults entry points). `f` carries the KSA_FAIL_* bits
 // of this (trace, tick). The three error paths of Run all `continue` before any state changes:
 //   NumMessages failed  main.go:43-47   nothing else happens in the tick
@@ -488,6 +529,99 @@ __device__ __forceinline__ unsigned ksa_step_faults_fma2(const ksa_step_consts& 
   return ev;
 }
 
+// Third spelling, for the summary kernels (wide event code only). Against ksa_step_faults_fma2:
+//  - the three failure counters of the summary are accumulated here, straight from the mask bits
+//    under the "call reached" predicates, into one packed word `pkf` (KSA_PKF_* below): three
+//    IMADs instead of the six ALU operations that recovered them from the event code afterwards;
+//  - a failed poll enters the event code as (f & KSA_FAIL_POLL) * POLL_FAILED up front (both
+//    thresholds are then unmet, so nothing else is added) instead of a final select.
+// pkf fields (10 bits each, flushed with the other second-level counters, ksa_summary_flush_faults3):
+//   up_failed   in units of KSA_FAIL_UP (2)   at bit 0   -> bits 1..10
+//   down_failed in units of KSA_FAIL_DOWN (4) at bit 10  -> bits 12..21
+//   poll_failed in units of 1                 at bit 22  -> bits 22..31
+#define KSA_PKF_UP_SHIFT 1
+#define KSA_PKF_DOWN_SHIFT 12
+#define KSA_PKF_POLL_SHIFT 22
+template <bool ORDERED>
+__device__ __forceinline__ unsigned ksa_step_faults_fma3(const ksa_step_consts& c, long long n, unsigned f,
+                                                         int i, int one, ksa_trace_regs& s, unsigned& pkf) {
+  constexpr int kUpFailStep = (int)(((long long)KSA_W_UP_FAILED - (long long)KSA_W_UP_COOL) / KSA_FAIL_UP);
+  constexpr int kDownFailStep = (int)(((long long)KSA_W_DOWN_FAILED - (long long)KSA_W_DOWN_COOL) / KSA_FAIL_DOWN);
+  unsigned ev;
+#define KSA_STEP_FAULTS3_BODY(DOWN_HIT)                                                          \
+  asm("{\n\t"                                                                                    \
+      ".reg .pred pok, uh, ureach, ugo, uapp, ucont, dh, dreach, dgo, dapp;\n\t"                 \
+      ".reg .s32 t, u;\n\t"                                                                      \
+      ".reg .b32 fb, fu, fd;\n\t"                                                                \
+      "and.b32 fb, %16, 1;\n\t"                                                                  \
+      "setp.eq.u32 pok, fb, 0;\n\t"                /* main.go:44 err == nil */                   \
+      "mad.lo.s32 %0, fb, %24, 0;\n\t"             /* POLL_FAILED, main.go:45 */                 \
+      "mad.lo.u32 %4, fb, %25, %4;\n\t"            /* count it */                                \
+      "setp.ge.and.s64 uh, %5, %6, pok;\n\t"       /* main.go:51 */                              \
+      "setp.le.and.s32 ureach, %2, %12, uh;\n\t"   /* main.go:52 false: ScaleUp is called */     \
+      "and.b32 fu, %16, 2;\n\t"                                                                  \
+      "setp.eq.and.u32 ugo, fu, 0, ureach;\n\t"    /* ScaleUp returned nil */                    \
+      "setp.lt.and.s32 uapp, %1, %8, ugo;\n\t"     /* scale.go:62 */                             \
+      "@uh mad.lo.s32 %0, %15, %17, %0;\n\t"       /* UP_COOL unless the call is reached ... */  \
+      "@ugo mad.lo.s32 %0, %15, %18, %0;\n\t"      /* ... and returns nil: UP_NOOP unless ... */ \
+      "@uapp mad.lo.s32 %0, %15, %19, %0;\n\t"     /* ... UP_APPLIED */                          \
+      "@ureach mad.lo.s32 %0, fu, %20, %0;\n\t"    /* ... or fails: UP_FAILED, main.go:57-60 */  \
+      "@ureach mad.lo.u32 %4, fu, 1, %4;\n\t"      /* count it (units of 2) */                   \
+      "add.s32 t, %1, %10;\n\t"                    /* scale.go:66 */                             \
+      "min.s32 t, t, %8;\n\t"                      /* scale.go:67-69 */                          \
+      "@uapp mad.lo.s32 %1, t, %15, 0;\n\t"                                                      \
+      DOWN_HIT                                     /* main.go:65, after :54 / :59 continue */    \
+      "@ugo mad.lo.s32 %2, %12, %15, %13;\n\t"     /* main.go:62   su = i + cu */                \
+      "setp.le.and.s32 dreach, %3, %12, dh;\n\t"   /* main.go:66 false: ScaleDown is called */   \
+      "and.b32 fd, %16, 4;\n\t"                                                                  \
+      "setp.eq.and.u32 dgo, fd, 0, dreach;\n\t"                                                  \
+      "setp.gt.and.s32 dapp, %1, %9, dgo;\n\t"     /* scale.go:89 */                             \
+      "@dgo mad.lo.s32 %3, %12, %15, %14;\n\t"     /* main.go:76   sd = i + cd */                \
+      "@dh mad.lo.s32 %0, %15, %21, %0;\n\t"       /* DOWN_COOL unless ... */                    \
+      "@dgo mad.lo.s32 %0, %15, %22, %0;\n\t"      /* ... DOWN_NOOP unless ... */                \
+      "@dapp mad.lo.s32 %0, %15, %23, %0;\n\t"     /* ... DOWN_APPLIED */                        \
+      "@dreach mad.lo.s32 %0, fd, %26, %0;\n\t"    /* ... or DOWN_FAILED, main.go:71-74 */       \
+      "@dreach mad.lo.u32 %4, fd, 1024, %4;\n\t"   /* count it (units of 4, at bit 10) */        \
+      "sub.s32 u, %1, %11;\n\t"                    /* scale.go:94 */                             \
+      "max.s32 u, u, %9;\n\t"                      /* scale.go:95-97 */                          \
+      "@dapp mad.lo.s32 %1, u, %15, 0;\n\t"                                                      \
+      "}"                                                                                        \
+      : "=&r"(ev), "+r"(s.r), "+r"(s.su), "+r"(s.sd), "+r"(pkf)                                  \
+      : "l"(n), "l"(c.up_msgs), "l"(c.down_msgs), "r"(c.max32), "r"(c.min32), "r"(c.up32),       \
+        "r"(c.down32), "r"(i), "r"(c.cu), "r"(c.cd), "r"(one), "r"(f), "n"((int)KSA_W_UP_COOL),  \
+        "n"((int)KSA_W_UP_NOOP - (int)KSA_W_UP_COOL), "n"((int)KSA_W_UP_APPLIED - (int)KSA_W_UP_NOOP), \
+        "n"(kUpFailStep), "n"((int)KSA_W_DOWN_COOL), "n"((int)KSA_W_DOWN_NOOP - (int)KSA_W_DOWN_COOL), \
+        "n"((int)KSA_W_DOWN_APPLIED - (int)KSA_W_DOWN_NOOP),                                     \
+        "n"((int)(KSA_W_UP_FAILED | KSA_W_DOWN_FAILED)), "n"(1 << KSA_PKF_POLL_SHIFT), "n"(kDownFailStep))
+  if constexpr (ORDERED)
+    KSA_STEP_FAULTS3_BODY("setp.le.and.s64 dh, %5, %7, pok;\n\t");
+  else
+    KSA_STEP_FAULTS3_BODY("and.pred ucont, uh, !ugo;\n\t"
+                          "setp.le.and.s64 dh, %5, %7, pok;\n\t"
+                          "and.pred dh, dh, !ucont;\n\t");
+#undef KSA_STEP_FAULTS3_BODY
+  return ev;
+}
+
+// The rare path behind ksa_summary_acc::bad: replay one trace again, plainly, and return the exact
+// 64-bit sum of its T post-tick replica counts. `depth` / `fail` point at the trace's own column
+// (element (t, a) at depth[t * row + a * ld], fail[t * fld]; fail may be NULL); `s` is the state the
+// trace started the call with.
+static __device__ __noinline__ long long ksa_exact_sum(const ksa_policy_k pk, const long long* depth, long long row,
+                                                       long long ld, int A, const unsigned char* fail,
+                                                       long long fld, int T, ksa_trace_regs s) {
+  const ksa_step_consts c(pk);
+  unsigned long long acc = 0ull;
+  for (int t = 0; t < T; ++t) {
+    unsigned long long n = 0ull;
+    for (int a = 0; a < A; ++a) n += (unsigned long long)depth[(long long)t * row + a * ld];
+    const unsigned f = fail ? (unsigned)fail[(long long)t * fld] : 0u;
+    ksa_step_faults(c, (long long)n, f, t + 1, s);  // with f == 0 this is ksa_step
+    acc += (unsigned long long)(long long)s.r;
+  }
+  return (long long)acc;
+}
+
 // d = a * b + c as a true IMAD (FMA pipe): ptxas cannot fold it when b is not a compile-time
 // constant, which is what the `one` kernel argument is for.
 __device__ __forceinline__ unsigned ksa_mad_u32(unsigned a, unsigned b, unsigned c) {
@@ -505,15 +639,25 @@ __device__ __forceinline__ long long ksa_mad_wide_s32(int a, int b, long long c)
 // 5-bit fields of one register, in the layout of the wide event code, so that a tick's code is
 // simply added; they are folded into 10-bit fields before a field can overflow (every <= 31 ticks,
 // ksa_summary_fold) and those into the 32-bit counters of the record (ksa_summary_flush).
+// The sum of the replica counts is kept the same way: `sw` takes one 32-bit multiply-add per tick
+// and is folded into the 64-bit `sum` with the counters. A window of <= 31 ticks cannot overflow
+// 32 bits while every replica count is inside +-KSA_SUM_SAFE (31 * 2^26 < 2^31); each fold checks
+// the running minimum / maximum (which cover the window) and sets `bad` otherwise, and a trace
+// with `bad` set gets its sum recomputed exactly at the end of the kernel (ksa_exact_sum; only
+// deployments with more than 67 million replicas ever go there). A 64-bit add per tick costs
+// three instructions (IMAD.WIDE + IADD3 + IMAD.X in SASS) against one.
 struct ksa_summary_acc {
   int rmin, rmax;
   int rstash;         // first replica count of a pair of ticks (KSA_TICK_FIRST), see ksa_summary_tick
   unsigned pk;        // six 5-bit event counters, field k at bit 5k (bits 30-31: don't care)
   unsigned lva, lvb;  // second level, 10-bit fields: lva = events 0, 2, 4 at bits 0, 10, 20; lvb = 1, 3, 5
-  unsigned pkf;       // *_faults kernels only, 10-bit fields: up_failed at 0, down_failed at 10, failed polls at 20
+  unsigned pkf;       // *_faults kernels only, 10-bit fields (KSA_PKF_* or the older layout, per step)
+  int sw;             // sum of the replica counts since the last fold
+  unsigned bad;       // != 0: a window may have overflowed `sw`; the sum is recomputed at the end
   long long sum;
   unsigned ha, hb;    // the two lanes of the fingerprint
 };
+#define KSA_SUM_SAFE (1 << 26)
 // pk is folded into lva/lvb after at most KSA_FOLD_TICKS ticks, those are flushed to the 32-bit
 // counters of the record after at most KSA_FLUSH_FOLDS folds (30 * 31 = 930, plus the at most 93 ticks
 // that the end of a kernel adds before its last flush: <= 1023).
@@ -552,10 +696,10 @@ __device__ __forceinline__ void ksa_summary_tick(ksa_summary_acc& m, int r, unsi
   }
   if constexpr (FMA) {
     m.pk = ksa_mad_u32(w, (unsigned)one, m.pk);
-    m.sum = ksa_mad_wide_s32(r, one, m.sum);
+    m.sw = (int)ksa_mad_u32((unsigned)r, (unsigned)one, (unsigned)m.sw);
   } else {
     m.pk += w;
-    m.sum = (long long)((unsigned long long)m.sum + (unsigned long long)(long long)r);
+    m.sw = (int)((unsigned)m.sw + (unsigned)r);
   }
   m.ha = m.ha * KSA_HASH_MUL_LO + (unsigned)r;
   m.hb = m.hb * KSA_HASH_MUL_HI + w;
@@ -571,11 +715,27 @@ __device__ __forceinline__ void ksa_summary_tick_faults(ksa_summary_acc& m, unsi
   m.pkf += (((w >> 30) * 0x201u) & 0x401u) + ((f & KSA_FAIL_POLL) << 20);
 }
 
-// First level: move the 5-bit fields into the 10-bit ones.
+// First level: move the 5-bit fields into the 10-bit ones and the window sum into the 64-bit one.
+// Callers fold only when no KSA_TICK_FIRST is pending, so rmin / rmax cover every tick of the window.
 __device__ __forceinline__ void ksa_summary_fold(ksa_summary_acc& m) {
   m.lva += m.pk & 0x01F07C1Fu;
   m.lvb += (m.pk >> 5) & 0x01F07C1Fu;
   m.pk = 0u;
+  m.sum = (long long)((unsigned long long)m.sum + (unsigned long long)(long long)m.sw);
+  m.sw = 0;
+  m.bad |= (unsigned)(m.rmin < -KSA_SUM_SAFE) | (unsigned)(m.rmax >= KSA_SUM_SAFE);
+}
+__device__ __forceinline__ void ksa_summary_acc_init(ksa_summary_acc& m, int rmin, int rmax, long long sum,
+                                                     unsigned long long hash) {
+  m.rmin = rmin;
+  m.rmax = rmax;
+  m.rstash = 0;
+  m.pk = m.lva = m.lvb = m.pkf = 0u;
+  m.sw = 0;
+  m.bad = 0u;
+  m.sum = sum;
+  m.ha = (unsigned)hash;
+  m.hb = (unsigned)(hash >> 32);
 }
 
 // Second level: fold, then add the 10-bit fields into the 32-bit counters of a ksa_summary record.
@@ -588,6 +748,14 @@ __device__ __forceinline__ void ksa_summary_flush(ksa_summary_acc& m, ksa_summar
   q->down_noop += (m.lvb >> 10) & 0x3ffu;
   q->down_cool += (m.lvb >> 20) & 0x3ffu;
   m.lva = m.lvb = 0u;
+}
+// The same for the packed word ksa_step_faults_fma3 accumulates (KSA_PKF_*): the three counts are
+// already separate (a failed poll reaches neither call).
+__device__ __forceinline__ void ksa_summary_flush_faults3(ksa_summary_acc& m, ksa_summary* q) {
+  q->up_failed += (m.pkf >> KSA_PKF_UP_SHIFT) & 0x3ffu;
+  q->down_failed += (m.pkf >> KSA_PKF_DOWN_SHIFT) & 0x3ffu;
+  q->poll_failed += (m.pkf >> KSA_PKF_POLL_SHIFT) & 0x3ffu;
+  m.pkf = 0u;
 }
 __device__ __forceinline__ void ksa_summary_flush_faults(ksa_summary_acc& m, ksa_summary* q) {
   const unsigned polls = (m.pkf >> 20) & 0x3ffu;
