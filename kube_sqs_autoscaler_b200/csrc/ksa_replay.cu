@@ -45,7 +45,8 @@ enum { MODE_FULL = 0, MODE_SUMMARY = 1, MODE_FULL_OPT = 2 };
 // 4 = ksa_step_faults (C++), 5 = ksa_step_faults_fma / ksa_step_faults_fma2: the steps of the
 // *_faults entry points, which also read one failure-mask byte per decision.
 // 6 = ksa_step_fma for ordered thresholds (summary mode), 7 = the same with failures,
-// 8 = ksa_step_faults_fma2 with the event byte out (full mode). In summary mode the FMA steps
+// 8 = ksa_step_faults_fma2 with the event byte out (full mode), 9 / 10 = ksa_step_faults_fma3
+// (summary mode; 9 for ordered thresholds). In summary mode the FMA steps
 // return the wide event code (ksa_policy.cuh) and one trace per thread is the default.
 // Load hints: 0 = ld.global.nc, 1 = + L1::no_allocate, 2 = + L2::evict_first (256-bit loads only)
 enum { HINT_NC = 0, HINT_NA = 1, HINT_NA_EF = 2 };
@@ -178,11 +179,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
-  const ksa_step_consts c(a.pk);
+  ksa_step_consts c(a.pk);
   const int T = a.T;
   const int one = a.one;  // always 1; see ksa_step_fma
-  constexpr bool FAULTS = (STEP == 4 || STEP == 5 || STEP == 7 || STEP == 8);
-  constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6 || STEP == 7 || STEP == 8);
+  constexpr bool FAULTS = (STEP == 4 || STEP == 5 || STEP == 7 || STEP == 8 || STEP == 9 || STEP == 10);
+  constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6 || STEP == 7 || STEP == 8 || STEP == 9 || STEP == 10);
+  constexpr bool FAULTS3 = (STEP == 9 || STEP == 10);  // ksa_step_faults_fma3 counts the failures itself
+  // Summary mode numbers the ticks of a group of D from 1 (compile-time constants after unrolling)
+  // and moves the two stamps back by D after every group instead (see the loops below).
+  constexpr bool REBASE = (MODE == MODE_SUMMARY);
+  if constexpr (MODE == MODE_SUMMARY && V == 1) {
+    // The pod steps and cool-downs are launch constants, which ptxas keeps in uniform registers;
+    // the add of VIADDMNMX and the addend of the stamp's IMAD want them in ordinary ones and get a
+    // copy per tick (3-4 of ~36 instructions per decision with one trace per thread). Adding a zero
+    // that depends on the thread index ((one - 1) * threadIdx.x) makes them per-thread values.
+    const int zero = (one - 1) * (int)threadIdx.x;
+    c.up32 += zero;
+    c.down32 += zero;
+    c.cu += zero;
+    c.cd += zero;
+  }
 
   ksa_trace_regs s[V];
 #pragma unroll
@@ -196,13 +212,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       const ksa_summary* q = a.summary + n0 + v;
-      sm[v].rmin = q->min_replicas;
-      sm[v].rmax = q->max_replicas;
-      sm[v].pk = sm[v].lva = sm[v].lvb = sm[v].pkf = 0u;
-      sm[v].rstash = 0;
-      sm[v].sum = q->sum_replicas;
-      sm[v].ha = (unsigned)q->hash;
-      sm[v].hb = (unsigned)(q->hash >> 32);
+      ksa_summary_acc_init(sm[v], q->min_replicas, q->max_replicas, q->sum_replicas, q->hash);
     }
   }
   auto fold_counters = [&]() {
@@ -216,7 +226,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
       for (int v = 0; v < V; ++v) {
         ksa_summary_flush(sm[v], a.summary + n0 + v);
-        if constexpr (FAULTS) ksa_summary_flush_faults(sm[v], a.summary + n0 + v);
+        if constexpr (FAULTS3) ksa_summary_flush_faults3(sm[v], a.summary + n0 + v);
+        else if constexpr (FAULTS) ksa_summary_flush_faults(sm[v], a.summary + n0 + v);
       }
     }
   };
@@ -276,7 +287,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
       for (int w = 0; w < (V + 3) / 4; ++w) fw[w] = fbuf[j][w];
     }
-    if (prefetch) {
+    // Full mode refills the ring slot before the step (the loads are as early as they can be);
+    // summary mode refills it after the step: there the step still reads the slot's registers (the
+    // high word of the depth in the 64-bit compares) after this point, so ptxas would load into
+    // fresh registers and copy the whole ring back at the end of the loop body (17 moves per 8
+    // decisions in the first build of the failure-aware kernel).
+    auto refill = [&]() {
+      if (!prefetch) return;
       if constexpr (MODE == MODE_SUMMARY) {
         // Prefetches happen in tick order, so a running pointer per array replaces the 64-bit
         // multiply per load (with one trace per thread that was ~5 instructions per decision).
@@ -293,8 +310,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
           load_depth<V, HINT>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
         if constexpr (FAULTS) load_fail<V>(fp + (long long)(tt + D) * a.ld, fbuf[j]);
       }
-    }
-    const int i = tt + 1;  // local tick, 1-based
+    };
+    if constexpr (MODE != MODE_SUMMARY) refill();
+    // tt = tick of the call (0-based) for addressing; i = the tick number the step sees (1-based,
+    // relative to the current group of D when REBASE)
+    const int i = REBASE ? j + 1 : tt + 1;
     int rr[V];
     unsigned ev[V];  // the event byte; in summary mode the wide event code (ksa_wide_event)
     unsigned fv[V];
@@ -303,8 +323,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     for (int v = 0; v < V; ++v) {
       fv[v] = 0u;
       if constexpr (FAULTS) {
-        fv[v] = (fw[v / 4] >> (8 * (v % 4))) & 0xffu;
-        if constexpr (STEP == 7)  // ordered thresholds (summary mode only)
+        fv[v] = V == 1 ? fw[0] : (fw[v / 4] >> (8 * (v % 4))) & 0xffu;  // a u8 load is zero-extended
+        if constexpr (FAULTS3)  // summary mode only; STEP 9 = ordered thresholds
+          ev[v] = ksa_step_faults_fma3<STEP == 9>(c, n[v], fv[v], i, one, s[v], sm[v].pkf);
+        else if constexpr (STEP == 7)  // ordered thresholds (summary mode only)
           ev[v] = ksa_step_faults_fma2<WIDE, true>(c, n[v], fv[v], i, one, s[v]);
         else if constexpr ((STEP == 5 && WIDE) || STEP == 8)
           ev[v] = ksa_step_faults_fma2<WIDE, false>(c, n[v], fv[v], i, one, s[v]);
@@ -333,7 +355,20 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
       for (int v = 0; v < V; ++v) {
         ksa_summary_tick<FMA>(sm[v], rr[v], ev[v], one, phase);
-        if constexpr (FAULTS) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
+        if constexpr (FAULTS && !FAULTS3) ksa_summary_tick_faults(sm[v], ev[v], fv[v]);
+      }
+      refill();
+    }
+  };
+  // REBASE: after a group of D ticks, "tick D + k of this group" is "tick k of the next", so both
+  // stamps move back by D (one IMAD each per D ticks instead of a tick counter per tick). Stamps stay
+  // within int32: >= -(T + 2D) >= -2^30 - 32, <= 2D + KSA_COOL_CAP.
+  auto rebase = [&]() {
+    if constexpr (REBASE) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        s[v].su = (int)ksa_mad_u32((unsigned)one, (unsigned)(-D), (unsigned)s[v].su);
+        s[v].sd = (int)ksa_mad_u32((unsigned)one, (unsigned)(-D), (unsigned)s[v].sd);
       }
     }
   };
@@ -347,6 +382,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
     for (int j = 0; j < D; ++j)  // with an even ring depth two ticks share their min / max update
       tick(t + j, j, true, D % 2 ? KSA_TICK_SINGLE : (j % 2 ? KSA_TICK_SECOND : KSA_TICK_FIRST));
+    rebase();
     if constexpr (MODE == MODE_SUMMARY) {
       pending += D;
       if (pending > KSA_FOLD_TICKS - D) {
@@ -367,9 +403,31 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
 #pragma unroll
     for (int j = 0; j < D; ++j)
       if (t + j < T) tick(t + j, j, t + j + D < T, KSA_TICK_SINGLE);
+    rebase();
     fold_counters();
   }
+  if constexpr (REBASE) {  // back to ticks of the call: every group took D off, t in total
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      s[v].su += t;
+      s[v].sd += t;
+    }
+  }
 
+  if constexpr (MODE == MODE_SUMMARY) {
+    flush_counters();
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      if (sm[v].bad) {  // a replica count left +-KSA_SUM_SAFE: redo the sum exactly (ksa_summary_acc)
+        ksa_trace_regs s0;  // the state this call started from is still in global memory
+        s0.r = a.st_r[n0 + v];
+        s0.su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
+        s0.sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
+        sm[v].sum = a.summary[n0 + v].sum_replicas +
+                    ksa_exact_sum(a.pk, dp + v, row, a.ld, A, FAULTS ? fp + v : nullptr, a.ld, T, s0);
+      }
+    }
+  }
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     a.st_r[n0 + v] = s[v].r;
@@ -377,7 +435,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     a.st_jd[n0 + v] = ksa_global_stamp(s[v].sd, c.cd, a.tick0, a.st_jd[n0 + v]);
   }
   if constexpr (MODE == MODE_SUMMARY) {
-    flush_counters();
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       ksa_summary* q = a.summary + n0 + v;
@@ -390,6 +447,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   }
 }
 
+#ifdef KSA_TUNING_VARIANTS
 // ---- summary replay with the depth rows staged in shared memory by the bulk-copy engine ---------
 //
 // The register-ring kernel above spends ~3 instructions per decision on load addresses and can
@@ -486,13 +544,7 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
   s.sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n]);
   ksa_summary* const q = a.summary + n;
   ksa_summary_acc m;
-  m.rmin = q->min_replicas;
-  m.rmax = q->max_replicas;
-  m.pk = m.lva = m.lvb = m.pkf = 0u;
-  m.rstash = 0;
-  m.sum = q->sum_replicas;
-  m.ha = (unsigned)q->hash;
-  m.hb = (unsigned)(q->hash >> 32);
+  ksa_summary_acc_init(m, q->min_replicas, q->max_replicas, q->sum_replicas, q->hash);
 
   unsigned taint = 0u;  // see ksa_replay_kernel
   auto tick = [&](const int st, const int k, const int i, const int phase) {
@@ -539,16 +591,25 @@ __global__ void __launch_bounds__(BLOCK + 32, MINB) ksa_summary_bulk_kernel(cons
     for (int k = 0; k < T - full_chunks * K; ++k) tick(st, k, full_chunks * K + k + 1, KSA_TICK_SINGLE);
   }
 
+  ksa_summary_flush(m, q);
+  if (m.bad) {  // see ksa_replay_kernel
+    ksa_trace_regs s0;
+    s0.r = a.st_r[n];
+    s0.su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n]);
+    s0.sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n]);
+    m.sum = q->sum_replicas + ksa_exact_sum(a.pk, a.depth + n, row, a.ld, A, nullptr, 0, T, s0);
+  }
   a.st_r[n] = s.r;
   a.st_ju[n] = ksa_global_stamp(s.su, c.cu, a.tick0, a.st_ju[n]);
   a.st_jd[n] = ksa_global_stamp(s.sd, c.cd, a.tick0, a.st_jd[n]);
-  ksa_summary_flush(m, q);
   q->final_replicas = s.r;
   q->min_replicas = m.rmin;
   q->max_replicas = m.rmax;
   q->sum_replicas = m.sum;
   q->hash = ((unsigned long long)m.hb << 32) | m.ha;
 }
+
+#endif  // KSA_TUNING_VARIANTS
 
 typedef void (*replay_kernel_fn)(const ReplayArgs);
 
@@ -577,14 +638,23 @@ struct Variant {
    {KSA_BK(1, K1, S1, BLOCK, M1, STEP), KSA_BK(2, K2, S2, BLOCK, M2, STEP), KSA_BK(3, K3, S3, BLOCK, M3, STEP)}}
 
 // Variant 0 is the scalar kernel (any alignment, any N); it also handles the ragged tail of the
-// vector variants. The default is chosen from tools/sweep_variants.py measurements;
-// ids are stable, the gaps are tuning points that were measured, lost and removed
-// (profiles/r01_sweep_variants_a1_T2000.txt still lists them).
+// vector variants. The defaults were chosen from tools/sweep_variants.py measurements.
+// The product build carries only the kernels replay_common can select by itself: the scalar
+// kernels, the defaults per trace count / policy kind, and the optional-output kernels. Every other
+// tuning point that was measured (profiles/r01_sweep_variants_*.txt) is compiled only with
+// -DKSA_TUNING_VARIANTS (python __graft_entry__.py --tuning), which tools/sweep_variants.py and
+// the all-variants parity runs use; ids are stable across the two builds.
 const Variant kFullVariants[] = {
     KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(16, MODE_FULL_OPT, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
+    KSA_VARIANT(32, MODE_FULL, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
+    // fewer traces per thread: for trace counts that cannot fill the GPU at V = 8 (see replay_common)
+    KSA_VARIANT(42, MODE_FULL, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+    KSA_VARIANT(43, MODE_FULL, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(46, MODE_FULL_OPT, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(1, MODE_FULL, 4, 4, HINT_NA, 0, 128, 7, 4, 2, 128, 6, 2, 4, 128, 6),
     KSA_VARIANT(14, MODE_FULL, 4, 3, HINT_NA, 1, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
-    KSA_VARIANT(16, MODE_FULL_OPT, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
     KSA_VARIANT(19, MODE_FULL, 4, 3, HINT_NA, 1, 256, 4, 4, 2, 256, 3, 2, 3, 256, 3),
     KSA_VARIANT(20, MODE_FULL, 2, 4, HINT_NA, 1, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(21, MODE_FULL, 2, 6, HINT_NA, 1, 256, 4, 2, 3, 256, 4, 2, 2, 256, 4),
@@ -592,20 +662,21 @@ const Variant kFullVariants[] = {
     KSA_VARIANT(27, MODE_FULL, 1, 8, HINT_NA, 1, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
     KSA_VARIANT(30, MODE_FULL, 8, 2, HINT_NA, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
     KSA_VARIANT(31, MODE_FULL, 8, 3, HINT_NA, 2, 128, 3, 4, 4, 128, 4, 4, 3, 128, 4),
-    KSA_VARIANT(32, MODE_FULL, 8, 2, HINT_NA, 2, 256, 2, 8, 1, 128, 4, 8, 1, 128, 3),
     KSA_VARIANT(34, MODE_FULL, 8, 1, HINT_NA, 2, 128, 5, 8, 1, 128, 5, 4, 1, 128, 6),
     KSA_VARIANT(36, MODE_FULL, 16, 2, HINT_NA, 2, 64, 4, 8, 2, 64, 6, 8, 1, 64, 8),
     KSA_VARIANT(38, MODE_FULL, 8, 2, HINT_NA_EF, 2, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
     KSA_VARIANT(41, MODE_FULL, 8, 2, HINT_NA, 0, 128, 4, 4, 3, 128, 5, 4, 2, 128, 5),
-    // fewer traces per thread: for trace counts that cannot fill the GPU at V = 8 (see pick_full_variant)
-    KSA_VARIANT(42, MODE_FULL, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
-    KSA_VARIANT(43, MODE_FULL, 2, 4, HINT_NA, 2, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(44, MODE_FULL, 4, 3, HINT_NA, 2, 128, 8, 4, 2, 128, 6, 2, 3, 128, 7),
     KSA_VARIANT(45, MODE_FULL, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
-    KSA_VARIANT(46, MODE_FULL_OPT, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
+#endif
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    KSA_VARIANT(20, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    // STEP 6: for policies with scale_up_messages > scale_down_messages only (ksa_step_fma ORDERED);
+    // replay_common substitutes the general default when the policy is not ordered.
+    KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
     KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
     KSA_VARIANT(8, MODE_SUMMARY, 2, 8, HINT_NA, 2, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
@@ -619,43 +690,57 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(17, MODE_SUMMARY, 1, 16, HINT_NA, 2, 128, 6, 1, 8, 128, 6, 1, 5, 128, 6),
     KSA_VARIANT(18, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
     KSA_VARIANT(19, MODE_SUMMARY, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
-    KSA_VARIANT(20, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
-    // STEP 6: for policies with scale_up_messages > scale_down_messages only (ksa_step_fma ORDERED);
-    // replay_common substitutes the general default when the policy is not ordered.
-    KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
     KSA_VARIANT(22, MODE_SUMMARY, 2, 4, HINT_NA, 6, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
+    KSA_VARIANT(23, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
+    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 6, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
+    KSA_VARIANT(25, MODE_SUMMARY, 1, 8, HINT_NA, 6, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
     // 30..: rows staged in shared memory by cp.async.bulk (ksa_summary_bulk_kernel). Measured
     // 0.87 (33) / 0.86 (38) of the copy bandwidth against 0.92 for the register ring (21), so they
     // are tuning points, not the default; K = 4 stages reach 0.77 (profiles/r01_summary_bulk.txt).
     KSA_BULK_VARIANT(30, 2, 128, 8, 3, 8, 4, 3, 8, 2, 4, 8),
     KSA_BULK_VARIANT(33, 6, 128, 8, 3, 8, 4, 3, 8, 2, 4, 8),
     KSA_BULK_VARIANT(38, 6, 128, 8, 4, 6, 4, 4, 6, 2, 4, 6),
+#endif
 };
-// The *_faults entry points: one vector kernel + the scalar kernel per mode (STEP 4).
+// The *_faults entry points (STEP 4 = the C++ step: the scalar kernels and the optional-output one).
 const Variant kFullFaultsVariants[] = {
     KSA_VARIANT(0, MODE_FULL_OPT, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
     KSA_VARIANT(1, MODE_FULL_OPT, 8, 2, HINT_NA, 4, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
+    // STEP 8: the second spelling of the failure-aware step (ksa_step_faults_fma2), event byte out
+    KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NA, 8, 128, 5, 4, 2, 128, 5, 2, 3, 128, 6),
+    KSA_VARIANT(9, MODE_FULL, 1, 8, HINT_NA, 8, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),  // small trace counts
+#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(2, MODE_FULL, 8, 2, HINT_NA, 5, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
     KSA_VARIANT(3, MODE_FULL, 8, 2, HINT_NA, 5, 256, 2, 4, 3, 256, 2, 4, 2, 256, 2),
     KSA_VARIANT(4, MODE_FULL, 4, 3, HINT_NA, 5, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
-    // STEP 8: the second spelling of the failure-aware step (ksa_step_faults_fma2), event byte out
     KSA_VARIANT(5, MODE_FULL, 4, 3, HINT_NA, 8, 128, 6, 4, 2, 128, 5, 2, 3, 128, 6),
     KSA_VARIANT(6, MODE_FULL, 8, 2, HINT_NA, 8, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
-    KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NA, 8, 128, 5, 4, 2, 128, 5, 2, 3, 128, 6),
-    KSA_VARIANT(9, MODE_FULL, 1, 8, HINT_NA, 8, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),  // small trace counts
+#endif
 };
 const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
+    // STEP 9 / 10: ksa_step_faults_fma3 (counts the failures itself); 9 = ordered thresholds only,
+    // replay_common substitutes 10 otherwise
+    KSA_VARIANT(10, MODE_SUMMARY, 1, 8, HINT_NA, 10, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
+    KSA_VARIANT(11, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
+#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(1, MODE_SUMMARY, 2, 4, HINT_NA, 4, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(2, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 7, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(4, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
     KSA_VARIANT(5, MODE_SUMMARY, 1, 8, HINT_NA, 5, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(6, MODE_SUMMARY, 1, 6, HINT_NA, 5, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
-    // STEP 7: ordered thresholds only (replay_common substitutes the STEP 5 twin otherwise)
+    // STEP 7: ksa_step_faults_fma2, ordered thresholds only (4 is its twin for any policy)
     KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 7, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
     KSA_VARIANT(8, MODE_SUMMARY, 2, 4, HINT_NA, 7, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(9, MODE_SUMMARY, 1, 8, HINT_NA, 7, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(12, MODE_SUMMARY, 1, 6, HINT_NA, 9, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
+    KSA_VARIANT(13, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(14, MODE_SUMMARY, 2, 4, HINT_NA, 9, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
+    KSA_VARIANT(15, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(16, MODE_SUMMARY, 1, 8, HINT_NA, 9, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
+    KSA_VARIANT(17, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
+#endif
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per thread
@@ -664,6 +749,8 @@ constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
 constexpr int kDefaultFullOptV1 = 46;  // the same below 196608 traces
 constexpr int kDefaultSummary = 20;  // one trace per thread: no interleaved state machines, no predicate spills
 constexpr int kDefaultSummaryOrdered = 21;  // the same with the ordered-thresholds step
+constexpr int kDefaultFullFaults = 8, kDefaultFullFaultsV1 = 9, kDefaultFullFaultsOpt = 1;
+constexpr int kDefaultSummaryFaults = 10, kDefaultSummaryFaultsOrdered = 11;
 
 template <size_t K>
 const Variant* find_variant(const Variant (&table)[K], int id) {
@@ -728,15 +815,18 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
     var = find_variant(kFullVariants, N < 196608 ? kDefaultFullOptV1 : kDefaultFullOpt);
   const Variant* scalar = mode == MODE_FULL ? &kFullVariants[0] : &kSummaryVariants[0];
   if (faults) {
-    // Faults variants: default = the FMA-steered kernel when both outputs are wanted; the tuning
-    // knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
-    int fid = mode == MODE_FULL ? ((replicas_dev && events_dev) ? (N < 131072 ? 9 : 8) : 1)
-                                : (ordered ? 7 : 4);  // profiles/r01_config2_faults.txt
+    // The tuning knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
+    const bool both = replicas_dev && events_dev;
+    int fid = mode == MODE_FULL ? (both ? (N < 131072 ? kDefaultFullFaultsV1 : kDefaultFullFaults) : kDefaultFullFaultsOpt)
+                                : (ordered ? kDefaultSummaryFaultsOrdered : kDefaultSummaryFaults);
     if (const char* e = std::getenv("KSA_FAULTS_VARIANT")) fid = std::atoi(e);
     var = mode == MODE_FULL ? find_variant(kFullFaultsVariants, fid) : find_variant(kSummaryFaultsVariants, fid);
-    if (!var) var = mode == MODE_FULL ? &kFullFaultsVariants[2] : &kSummaryFaultsVariants[2];  // unknown id
-    if (var->step == 7 && !ordered) var = find_variant(kSummaryFaultsVariants, 4);  // same shape, any policy
-    if (var && mode == MODE_FULL && (!replicas_dev || !events_dev) && fid >= 2) var = &kFullFaultsVariants[1];
+    if (!var) return ksa_fail(KSA_EINVAL, "unknown faults kernel variant %d (KSA_FAULTS_VARIANT)", fid);
+    // steps for ordered thresholds only: substitute the twin for any policy
+    if (var->step == 9 && !ordered) var = find_variant(kSummaryFaultsVariants, kDefaultSummaryFaults);
+    if (var->step == 7 && !ordered) var = find_variant(kSummaryFaultsVariants, 4);
+    // variants compiled for "both outputs" cannot run with one of them missing
+    if (mode == MODE_FULL && !both && var->id >= 2) var = find_variant(kFullFaultsVariants, kDefaultFullFaultsOpt);
     if (want == 0) var = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
     scalar = mode == MODE_FULL ? &kFullFaultsVariants[0] : &kSummaryFaultsVariants[0];
   }
@@ -800,8 +890,16 @@ bool ksa_replay_variant_exists(int mode, int id) {
                            : find_variant(kSummaryVariants, id) != nullptr;
 }
 // Variant names for tools/ (not part of the C ABI header; looked up with dlsym by the sweep tool).
+const char* ksa_sweep_variant_name(int id);  // ksa_sweep.cu
 extern "C" const char* ksa_variant_name(int32_t mode, int32_t id) {
-  if (id == -1) id = mode == MODE_FULL ? kDefaultFull : kDefaultSummary;  // the library default
-  const Variant* v = mode == MODE_FULL ? find_variant(kFullVariants, id) : find_variant(kSummaryVariants, id);
+  if (mode == 4) return ksa_sweep_variant_name(id);  // KSA_SWEEP_VARIANT ids
+  const Variant* v = nullptr;
+  switch (mode) {
+    case 0: v = find_variant(kFullVariants, id == -1 ? kDefaultFull : id); break;
+    case 1: v = find_variant(kSummaryVariants, id == -1 ? kDefaultSummary : id); break;
+    case 2: v = find_variant(kFullFaultsVariants, id == -1 ? kDefaultFullFaults : id); break;  // KSA_FAULTS_VARIANT ids
+    case 3: v = find_variant(kSummaryFaultsVariants, id == -1 ? kDefaultSummaryFaults : id); break;
+    default: break;
+  }
   return v ? v->name : nullptr;
 }
