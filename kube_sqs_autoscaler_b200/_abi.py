@@ -12,7 +12,9 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libksareplay.so")
+# KSA_LIBRARY: load another build of the same sources (the tuning build with every variant,
+# libksareplay_tuning.so); default = the product library next to this file.
+LIB_PATH = os.environ.get("KSA_LIBRARY") or os.path.join(HERE, "libksareplay.so")
 
 KSA_ABI_VERSION = 1
 KSA_OK, KSA_EINVAL, KSA_ECUDA, KSA_ENOMEM, KSA_ELIMIT = 0, -1, -2, -3, -4

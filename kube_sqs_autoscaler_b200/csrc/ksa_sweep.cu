@@ -12,8 +12,8 @@
 #include "ksa_internal.h"
 
 #include <cstdlib>
+#include <algorithm>
 #include <mutex>
-#include <vector>
 
 namespace {
 
@@ -36,12 +36,31 @@ __host__ __device__ inline bool ksa_policy_is_narrow(long long up, long long dow
          down < (long long)INT_MAX;
 }
 
-// FAST = every policy of the tile is narrow: the step is ksa_step_fma_narrow on the attribute sum
-// saturated once per tick, 6 compares per decision instead of 9. A grid that mixes narrow and other
-// tiles is launched twice with a.split = 1, once per kind; each block then returns at once unless
-// its tile is of the kernel's kind.
-template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, bool FAST>
+// Kind of a policy tile (R consecutive policies, the last tile padded with copies of policy P-1).
+// Host (sweep_tile_kinds) and device (the split test in the kernel) use this one function.
+enum { TILE_GENERAL = 0, TILE_NARROW = 1, TILE_SHARED = 2 };
+template <int R>
+__host__ __device__ inline int ksa_tile_kind(const long long (&up)[R], const long long (&down)[R]) {
+  bool narrow = true, shared = true;
+  for (int q = 0; q < R; ++q) {
+    narrow = narrow && ksa_policy_is_narrow(up[q], down[q]);
+    shared = shared && up[q] == up[0] && down[q] == down[0];
+  }
+  return narrow ? (shared ? TILE_SHARED : TILE_NARROW) : TILE_GENERAL;
+}
+
+// KIND = the kind of tile the kernel is compiled for:
+//  TILE_NARROW  every policy of the tile is narrow: the step is ksa_step_fma_narrow on the attribute
+//               sum saturated once per tick, 6 compares per decision instead of 9.
+//  TILE_SHARED  narrow, and all policies of the tile have the same two thresholds (the usual case:
+//               grids vary the thresholds slowest): the two threshold tests are made once per
+//               (trace, tick) and shared by the R machines (ksa_step_fma_shared, 4 compares per decision).
+// A grid that mixes kinds is launched once per kind present with a.split = 1; each block then
+// returns at once unless its tile is of the kernel's kind.
+template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, int KIND>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
+  constexpr bool FAST = KIND != TILE_GENERAL;
+  constexpr bool SHARED = KIND == TILE_SHARED;
   // Block mapping: grid = (trace blocks of a group, policy tiles, groups). Blocks are dispatched x
   // fastest, then y, then z, so a group of gridDim.x trace blocks goes through all policy tiles
   // before the next group starts, and the blocks resident at any time share one L2-sized slice of
@@ -58,10 +77,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
 #pragma unroll
   for (int q = 0; q < R; ++q) pk[q] = a.policies[min(p0 + q, a.P - 1)];
   if (a.split) {
-    bool narrow = true;
+    long long up[R], down[R];
 #pragma unroll
-    for (int q = 0; q < R; ++q) narrow = narrow && ksa_policy_is_narrow(pk[q].up_msgs, pk[q].down_msgs);
-    if (narrow != FAST) return;
+    for (int q = 0; q < R; ++q) up[q] = pk[q].up_msgs, down[q] = pk[q].down_msgs;
+    if (ksa_tile_kind<R>(up, down) != KIND) return;
   }
 
   ksa_trace_regs s[R];
@@ -73,12 +92,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
     s[q].r = r0;
     s[q].su = ksa_local_stamp(pk[q].cu, c.cu, 0, 0);  // fresh process: both stamps at tick 0,
     s[q].sd = ksa_local_stamp(pk[q].cd, c.cd, 0, 0);  // main.go:37-38
-    m[q].rmin = INT_MAX;
-    m[q].rmax = INT_MIN;
-    m[q].rstash = r0;
-    m[q].pk = m[q].lva = m[q].lvb = 0u;
-    m[q].sum = 0;
-    m[q].ha = m[q].hb = 0u;
+    ksa_summary_acc_init(m[q], INT_MAX, INT_MIN, 0, 0ull);
     if (p0 + q < a.P) {  // counters live in the output record; start them at zero
       ksa_summary* z = a.summary + (long long)(p0 + q) * a.N + n;
       z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
@@ -128,6 +142,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
         const unsigned m_hi = (unsigned)((unsigned long long)msgs >> 32);
         int m32 = FAST ? ksa_saturate_s32(msgs) : 0;
         unsigned ev_last = 0u;
+        // SHARED: main.go:51,65 once for the whole tile (see ksa_step_fma_shared)
+        int iu = 0, id = 0;
+        unsigned e0 = 0u, e0n = 0u;
+        if constexpr (SHARED) {
+          const bool uh = m32 >= (int)pk[0].up_msgs, dh = m32 <= (int)pk[0].down_msgs;
+          iu = uh ? i : INT_MIN;
+          id = dh ? i : INT_MIN;
+          e0 = uh ? KSA_W_UP_COOL : (dh ? KSA_W_DOWN_COOL : 0u);
+          e0n = e0 + (KSA_W_UP_NOOP - KSA_W_UP_COOL);
+        }
 #pragma unroll
         for (int q = 0; q < R; ++q) {
           const ksa_step_consts c(pk[q]);
@@ -138,7 +162,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
               asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m_lo) : "r"(ev_last));
           }
           unsigned ev;  // wide event code
-          if constexpr (FAST)
+          if constexpr (SHARED)
+            ev = ksa_step_fma_shared(c, iu, id, e0, e0n, i, one, s[q]);
+          else if constexpr (FAST)
             ev = ksa_step_fma_narrow((int)pk[q].up_msgs, (int)pk[q].down_msgs, c, m32, i, one, s[q]);
           else
             ev = ksa_step_fma<true>(c, (long long)(((unsigned long long)m_hi << 32) | m_lo), i, one, s[q]);
@@ -166,6 +192,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
   for (int q = 0; q < R; ++q) {
     if (p0 + q < a.P) {
       ksa_summary* z = a.summary + (long long)(p0 + q) * a.N + n;
+      if (m[q].bad) {  // a replica count left +-KSA_SUM_SAFE: redo the sum exactly (ksa_summary_acc)
+        const ksa_step_consts c(pk[q]);
+        ksa_trace_regs s0;
+        s0.r = r0;
+        s0.su = ksa_local_stamp(pk[q].cu, c.cu, 0, 0);
+        s0.sd = ksa_local_stamp(pk[q].cd, c.cd, 0, 0);
+        m[q].sum = ksa_exact_sum(pk[q], dp, row, a.ld, A, nullptr, 0, T, s0);
+      }
       z->final_replicas = s[q].r;
       z->min_replicas = m[q].rmin;
       z->max_replicas = m[q].rmax;
@@ -203,12 +237,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
     s[v].r = a.replicas0[min(n0 + v, a.N - 1)];
     s[v].su = ksa_local_stamp(pk.cu, c.cu, 0, 0);  // fresh process: both stamps at tick 0,
     s[v].sd = ksa_local_stamp(pk.cd, c.cd, 0, 0);  // main.go:37-38
-    m[v].rmin = INT_MAX;
-    m[v].rmax = INT_MIN;
-    m[v].rstash = 0;
-    m[v].pk = m[v].lva = m[v].lvb = 0u;
-    m[v].sum = 0;
-    m[v].ha = m[v].hb = 0u;
+    ksa_summary_acc_init(m[v], INT_MAX, INT_MIN, 0, 0ull);
     if (have[v]) {  // counters live in the output record; start them at zero
       ksa_summary* z = a.summary + (long long)p * a.N + n0 + v;
       z->up_applied = z->down_applied = z->up_noop = z->down_noop = z->up_cool = z->down_cool = 0u;
@@ -278,6 +307,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
   for (int v = 0; v < V; ++v) {
     if (have[v]) {
       ksa_summary* z = a.summary + (long long)p * a.N + n0 + v;
+      if (m[v].bad) {  // see ksa_sweep_kernel
+        ksa_trace_regs s0;
+        s0.r = a.replicas0[n0 + v];
+        s0.su = ksa_local_stamp(pk.cu, c.cu, 0, 0);
+        s0.sd = ksa_local_stamp(pk.cd, c.cd, 0, 0);
+        m[v].sum = ksa_exact_sum(pk, dp + v, row, a.ld, A, nullptr, 0, T, s0);
+      }
       z->final_replicas = s[v].r;
       z->min_replicas = m[v].rmin;
       z->max_replicas = m[v].rmax;
@@ -290,50 +326,68 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_lane_kernel(const __gri
 
 typedef void (*sweep_fn)(const SweepArgs);
 struct SweepVariant {
+  int id;     // stable across builds (KSA_SWEEP_VARIANT=<id>)
   int R;      // register-tile kernel: policies per thread; lane kernel: 0
   int V;      // lane kernel: traces per thread
   int block;
-  sweep_fn fn[3];       // indexed by A-1
-  sweep_fn fast_fn[3];  // FAST instantiation (register-tile kernels), else the same as fn
+  const char* name;
+  sweep_fn fn[3][3];  // [tile kind][A-1]; the lane kernels have one form for every kind
 };
-#define KSA_SWEEP_CH(R, D, BLOCK, MINB, CH)                                                        \
-  {R, 0, BLOCK,                                                                                    \
-   {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, false>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, false>, \
-    ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, false>},                                            \
-   {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, true>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, true>, \
-    ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, true>}}
-#define KSA_SWEEP(R, D, BLOCK, MINB) KSA_SWEEP_CH(R, D, BLOCK, MINB, 0)
-#define KSA_SWEEP_LANE(V, D, BLOCK, MINB)                                                        \
-  {0, V, BLOCK,                                                                                  \
-   {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>,    \
-    ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>},                                                \
-   {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>,    \
-    ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}}
-// Tuning points; KSA_SWEEP_VARIANT=<index> (environment) overrides the default for measurements.
+#define KSA_SWEEP_CH(ID, R, D, BLOCK, MINB, CH)                                                    \
+  {ID, R, 0, BLOCK, "R" #R "_D" #D "_B" #BLOCK "x" #MINB "_C" #CH,                                 \
+   {{ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, TILE_GENERAL>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, TILE_GENERAL>, \
+     ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, TILE_GENERAL>},                                    \
+    {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, TILE_NARROW>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, TILE_NARROW>, \
+     ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, TILE_NARROW>},                                     \
+    {ksa_sweep_kernel<1, R, D, BLOCK, MINB, CH, TILE_SHARED>, ksa_sweep_kernel<2, R, D, BLOCK, MINB, CH, TILE_SHARED>, \
+     ksa_sweep_kernel<3, R, D, BLOCK, MINB, CH, TILE_SHARED>}}}
+#define KSA_SWEEP(ID, R, D, BLOCK, MINB) KSA_SWEEP_CH(ID, R, D, BLOCK, MINB, 0)
+#define KSA_LANE3(V, D, BLOCK, MINB)                                                             \
+  {ksa_sweep_lane_kernel<1, V, D, BLOCK, MINB>, ksa_sweep_lane_kernel<2, V, D, BLOCK, MINB>,     \
+   ksa_sweep_lane_kernel<3, V, D, BLOCK, MINB>}
+#define KSA_SWEEP_LANE(ID, V, D, BLOCK, MINB)                                                    \
+  {ID, 0, V, BLOCK, "LANE_V" #V "_D" #D "_B" #BLOCK "x" #MINB,                                   \
+   {KSA_LANE3(V, D, BLOCK, MINB), KSA_LANE3(V, D, BLOCK, MINB), KSA_LANE3(V, D, BLOCK, MINB)}}
+// Launch shapes. The product build has the defaults only; -DKSA_TUNING_VARIANTS adds the points that
+// were measured (profiles/r01_config4_sweep_tune.txt). KSA_SWEEP_VARIANT=<id> (environment)
+// overrides the default for measurements and tests.
 const SweepVariant kSweepVariants[] = {
-    KSA_SWEEP(4, 4, 128, 3), KSA_SWEEP(2, 4, 128, 6), KSA_SWEEP(4, 2, 128, 4), KSA_SWEEP(2, 4, 256, 3),
-    KSA_SWEEP(1, 8, 128, 8), KSA_SWEEP(8, 2, 128, 2), KSA_SWEEP(4, 4, 64, 6),  KSA_SWEEP(3, 4, 128, 4),
-    KSA_SWEEP_LANE(1, 4, 128, 10), KSA_SWEEP_LANE(2, 4, 128, 8), KSA_SWEEP_LANE(1, 8, 128, 8),
-    KSA_SWEEP_LANE(2, 2, 128, 8),  KSA_SWEEP_LANE(1, 4, 256, 4), KSA_SWEEP_LANE(2, 4, 256, 4),
-    KSA_SWEEP_LANE(1, 2, 128, 12), KSA_SWEEP_LANE(1, 4, 64, 16),
+    KSA_SWEEP(2, 4, 2, 128, 4),   // A=1: narrow and shared tiles
+    KSA_SWEEP(37, 4, 1, 128, 5),  // A=1: general tiles
+    KSA_SWEEP(33, 4, 1, 256, 2),  // A=2,3: every kind (three 2-KB rows per tick want the wider block)
+    KSA_SWEEP_LANE(9, 2, 4, 128, 8),  // the second layout (lane = policy), kept as a cross-check
+#ifdef KSA_TUNING_VARIANTS
+    KSA_SWEEP(0, 4, 4, 128, 3), KSA_SWEEP(1, 2, 4, 128, 6), KSA_SWEEP(3, 2, 4, 256, 3),
+    KSA_SWEEP(4, 1, 8, 128, 8), KSA_SWEEP(5, 8, 2, 128, 2), KSA_SWEEP(6, 4, 4, 64, 6), KSA_SWEEP(7, 3, 4, 128, 4),
+    KSA_SWEEP_LANE(8, 1, 4, 128, 10), KSA_SWEEP_LANE(10, 1, 8, 128, 8),
+    KSA_SWEEP_LANE(11, 2, 2, 128, 8), KSA_SWEEP_LANE(12, 1, 4, 256, 4), KSA_SWEEP_LANE(13, 2, 4, 256, 4),
+    KSA_SWEEP_LANE(14, 1, 2, 128, 12), KSA_SWEEP_LANE(15, 1, 4, 64, 16),
     // 16..: register tile with chained groups
-    KSA_SWEEP_CH(4, 4, 128, 3, 2), KSA_SWEEP_CH(4, 2, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 4, 2), KSA_SWEEP_CH(4, 4, 128, 3, 1),
-    KSA_SWEEP_CH(8, 2, 128, 2, 2), KSA_SWEEP_CH(8, 2, 128, 2, 4), KSA_SWEEP_CH(6, 2, 128, 3, 2), KSA_SWEEP_CH(4, 4, 64, 6, 2),
+    KSA_SWEEP_CH(16, 4, 4, 128, 3, 2), KSA_SWEEP_CH(17, 4, 2, 128, 4, 2), KSA_SWEEP_CH(18, 4, 4, 128, 4, 2),
+    KSA_SWEEP_CH(19, 4, 4, 128, 3, 1), KSA_SWEEP_CH(20, 8, 2, 128, 2, 2), KSA_SWEEP_CH(21, 8, 2, 128, 2, 4),
+    KSA_SWEEP_CH(22, 6, 2, 128, 3, 2), KSA_SWEEP_CH(23, 4, 4, 64, 6, 2),
     // 24..: more unchained R=4 points (the narrow step needs fewer predicates)
-    KSA_SWEEP(4, 1, 128, 4), KSA_SWEEP(4, 2, 64, 8), KSA_SWEEP(4, 3, 128, 4), KSA_SWEEP(4, 2, 256, 2), KSA_SWEEP(4, 2, 128, 5),
-    KSA_SWEEP(4, 2, 128, 3),
+    KSA_SWEEP(24, 4, 1, 128, 4), KSA_SWEEP(25, 4, 2, 64, 8), KSA_SWEEP(26, 4, 3, 128, 4), KSA_SWEEP(27, 4, 2, 256, 2),
+    KSA_SWEEP(28, 4, 2, 128, 5), KSA_SWEEP(29, 4, 2, 128, 3),
     // 30..: 256-thread blocks (2 KB depth rows per block and tick; better with three attributes)
-    KSA_SWEEP_CH(4, 2, 256, 2, 2), KSA_SWEEP_CH(4, 4, 256, 2, 2), KSA_SWEEP(4, 3, 256, 2), KSA_SWEEP(4, 1, 256, 2),
-    KSA_SWEEP(4, 1, 512, 1), KSA_SWEEP(4, 2, 512, 1), KSA_SWEEP_CH(4, 1, 256, 2, 2), KSA_SWEEP(4, 1, 128, 5),
+    KSA_SWEEP_CH(30, 4, 2, 256, 2, 2), KSA_SWEEP_CH(31, 4, 4, 256, 2, 2), KSA_SWEEP(32, 4, 3, 256, 2),
+    KSA_SWEEP(34, 4, 1, 512, 1), KSA_SWEEP(35, 4, 2, 512, 1), KSA_SWEEP_CH(36, 4, 1, 256, 2, 2),
+    // 38..: shapes for the shared-threshold tiles (fewer live predicates: deeper rings / more blocks fit)
+    KSA_SWEEP(38, 4, 2, 128, 6), KSA_SWEEP(39, 4, 4, 128, 4), KSA_SWEEP(40, 8, 2, 128, 2), KSA_SWEEP(41, 8, 1, 128, 3),
+    KSA_SWEEP(42, 6, 2, 128, 3), KSA_SWEEP(43, 4, 2, 64, 10), KSA_SWEEP(44, 8, 2, 64, 5),
+#endif
 };
-constexpr int kNumSweepVariants = (int)(sizeof(kSweepVariants) / sizeof(kSweepVariants[0]));
-// Defaults per number of attributes (index A-1), from profiles/r01_config4_sweep_tune.txt. All have
-// R = 4, which the split launch of a mixed grid needs (tiles of the two kernels must coincide).
+const SweepVariant* find_sweep_variant(int id) {
+  for (const SweepVariant& v : kSweepVariants)
+    if (v.id == id) return &v;
+  return nullptr;
+}
+// Defaults per tile kind and number of attributes (index A-1), from profiles/r01_config4_sweep_tune.txt.
+// All have R = 4, which the split launch of a mixed grid needs (tiles of the kernels must coincide).
 //   narrow tiles:  A=1: R4 D2 128x4 unchained (71.5 ms on configs[3]); A=2,3: R4 D1 256x2 (83 ms at A=3,
-//                  112 ms with the A=1 choice: three 2-KB rows per tick want the wider block)
+//                  112 ms with the A=1 choice)
 //   other tiles:   A=1: R4 D1 128x5 unchained (75.3 ms); A=2,3: R4 D1 256x2 (87 ms at A=3)
-constexpr int kDefaultSweepNarrow[3] = {2, 33, 33};
-constexpr int kDefaultSweep[3] = {37, 33, 33};
+constexpr int kDefaultSweepId[3][3] = {{37, 33, 33}, {2, 33, 33}, {2, 33, 33}};
 
 // Grid of a sweep launch, or false if it does not fit one launch. Register-tile kernels:
 // (gw trace blocks, policy tiles, groups of gw trace blocks), see the block mapping in the kernel;
@@ -358,52 +412,109 @@ bool sweep_grid(const SweepVariant& v, int P, long long N, int A, int T, dim3* g
   return true;
 }
 
-// How the policy tiles (R consecutive policies, the last one padded with copies of policy P-1 as
-// in the kernel) of a grid split into narrow and other: 0 = none narrow, 1 = all narrow, 2 = mixed.
-// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels, for measurements and tests.
-int sweep_tile_kinds(const ksa_policy* policies, int P, int R) {
-  if (const char* e = std::getenv("KSA_SWEEP_GENERAL"))
-    if (std::atoi(e) != 0) return 0;
-  bool any_narrow = false, any_other = false;
+// Which kinds of policy tiles (ksa_tile_kind; R consecutive policies, the last tile padded with
+// copies of policy P-1 as in the kernel) a grid has: bit k set = some tile is of kind k.
+template <int R>
+unsigned sweep_tile_kinds_r(const ksa_policy* policies, int P) {
+  unsigned kinds = 0u;
   for (int p0 = 0; p0 < P; p0 += R) {
-    bool narrow = true;
+    long long up[R], down[R];
     for (int q = 0; q < R; ++q) {
       const ksa_policy& pol = policies[std::min(p0 + q, P - 1)];
-      narrow = narrow && ksa_policy_is_narrow(pol.scale_up_messages, pol.scale_down_messages);
+      up[q] = pol.scale_up_messages, down[q] = pol.scale_down_messages;
     }
-    (narrow ? any_narrow : any_other) = true;
+    kinds |= 1u << ksa_tile_kind<R>(up, down);
   }
-  return any_narrow ? (any_other ? 2 : 1) : 0;
+  return kinds;
+}
+unsigned sweep_tile_kinds(const ksa_policy* policies, int P, int R) {
+  switch (R) {
+    case 1: return sweep_tile_kinds_r<1>(policies, P);
+    case 2: return sweep_tile_kinds_r<2>(policies, P);
+    case 3: return sweep_tile_kinds_r<3>(policies, P);
+    case 4: return sweep_tile_kinds_r<4>(policies, P);
+    case 6: return sweep_tile_kinds_r<6>(policies, P);
+    case 8: return sweep_tile_kinds_r<8>(policies, P);
+    default: return 1u << TILE_GENERAL;
+  }
 }
 
-// Launch the sweep: the narrow and the general kernel each on the tiles of its kind.
+// Launch the sweep: one launch per kind of tile the grid has, each kernel on the tiles of its kind.
+// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels for every tile, =2 the narrow kernel
+// for shared tiles (a shared tile is also narrow), for measurements and tests.
 int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st, const char* what) {
-  int gi = kDefaultSweep[A - 1], fi = kDefaultSweepNarrow[A - 1];
+  const SweepVariant* v[3];
+  for (int k = 0; k < 3; ++k) v[k] = find_sweep_variant(kDefaultSweepId[k][A - 1]);
   if (const char* e = std::getenv("KSA_SWEEP_VARIANT")) {
-    const int want = std::atoi(e);
-    if (want >= 0 && want < kNumSweepVariants) gi = fi = want;
+    const SweepVariant* want = find_sweep_variant(std::atoi(e));
+    if (!want) return ksa_fail(KSA_EINVAL, "unknown sweep variant %s (KSA_SWEEP_VARIANT)", e);
+    v[0] = v[1] = v[2] = want;
   }
-  const SweepVariant& vg = kSweepVariants[gi];
-  const SweepVariant& vf = kSweepVariants[fi];
-  // Tiles of the two kernels must coincide for the split; the lane kernels have no narrow form.
-  const int kinds = (vg.R > 0 && vg.R == vf.R) ? sweep_tile_kinds(policies, a.P, vg.R) : 0;
+  if (const char* e = std::getenv("KSA_SWEEP_SHARED_VARIANT")) {  // tuning knob: shape of the shared-tile kernel only
+    const SweepVariant* want = find_sweep_variant(std::atoi(e));
+    if (!want || want->R != v[1]->R) return ksa_fail(KSA_EINVAL, "bad KSA_SWEEP_SHARED_VARIANT %s", e);
+    v[2] = want;
+  }
+  int force = 0;
+  if (const char* e = std::getenv("KSA_SWEEP_GENERAL")) force = std::atoi(e);
+  // Tiles of the kernels must coincide for the split; the lane kernels have one form.
+  unsigned kinds = 1u << TILE_GENERAL;
+  if (v[0]->R > 0 && v[0]->R == v[1]->R && v[0]->R == v[2]->R && force != 1) kinds = sweep_tile_kinds(policies, a.P, v[0]->R);
+  if (force == 2 && (kinds & (1u << TILE_SHARED))) {
+    if (kinds & (1u << TILE_GENERAL)) return ksa_fail(KSA_EINVAL, "KSA_SWEEP_GENERAL=2 needs an all-narrow grid");
+    kinds = 1u << TILE_NARROW;  // one unsplit launch of the narrow kernel over narrow and shared tiles
+  }
+  a.split = (kinds & (kinds - 1)) != 0;  // a kernel tests the kind of its tile only when another kernel has tiles too
   dim3 grid;
-  if (kinds != 1) {
-    if (!sweep_grid(vg, a.P, a.N, A, a.T, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
-    a.split = kinds == 2;
-    vg.fn[A - 1]<<<grid, vg.block, 0, st>>>(a);
-    KSA_LAUNCH_CHECK(what);
-  }
-  if (kinds != 0) {
-    if (!sweep_grid(vf, a.P, a.N, A, a.T, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
-    a.split = kinds == 2;
-    vf.fast_fn[A - 1]<<<grid, vf.block, 0, st>>>(a);
+  for (int k = 0; k < 3; ++k) {
+    if (!(kinds & (1u << k))) continue;
+    if (!sweep_grid(*v[k], a.P, a.N, A, a.T, &grid)) return ksa_fail(KSA_ELIMIT, "P x N too large for one launch");
+    v[k]->fn[k][A - 1]<<<grid, v[k]->block, 0, st>>>(a);
     KSA_LAUNCH_CHECK(what);
   }
   return KSA_OK;
 }
 
+// The kernel-side policy table is written by small kernels that carry the records in their
+// parameter block (640 records = 30 KB per launch; sm_100a takes 32 KB of parameters), not by a
+// host-to-device copy: a copy from a host buffer would still be reading that buffer when the call
+// has returned if the stream is being captured into a graph (the copy becomes a node that runs at
+// graph launch), while kernel parameters are taken by value at the call.
+constexpr int kPolicySlab = 640;
+struct PolicySlab {
+  ksa_policy_k rec[kPolicySlab];
+};
+__global__ void __launch_bounds__(128) policy_fill_kernel(const __grid_constant__ PolicySlab slab,
+                                                          ksa_policy_k* __restrict__ dst, int count) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  if (i < count) dst[i] = slab.rec[i];
+}
+
+// Validate and convert policies [0, P) and write them to table_dev[0, P) on `st`. No allocation.
+int upload_policies(const ksa_policy* policies, int P, int A, ksa_policy_k* table_dev, cudaStream_t st) {
+  PolicySlab slab;  // 30 KB of stack
+  for (int base = 0; base < P; base += kPolicySlab) {
+    const int count = std::min(kPolicySlab, P - base);
+    for (int q = 0; q < count; ++q) {
+      int rc = ksa_policy_to_k(&policies[base + q], A, &slab.rec[q]);
+      if (rc != KSA_OK) return rc;
+      if (policies[base + q].attr_mask != policies[0].attr_mask)
+        return ksa_fail(KSA_EINVAL, "policy %d: attr_mask differs from policy 0", base + q);
+    }
+    policy_fill_kernel<<<(count + 127) / 128, 128, 0, st>>>(slab, table_dev + base, count);
+    KSA_LAUNCH_CHECK("policy_fill_kernel");
+  }
+  return KSA_OK;
+}
+
 }  // namespace
+
+// For ksa_variant_name(4, id): name of a sweep launch shape, or NULL if this build does not have it.
+const char* ksa_sweep_variant_name(int id) {
+  if (id == -1) id = kDefaultSweepId[TILE_SHARED][0];
+  const SweepVariant* v = find_sweep_variant(id);
+  return v ? v->name : nullptr;
+}
 
 extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* policies_dev,
                                 const int64_t* depth_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
@@ -413,18 +524,10 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   if (P < 1 || P > (1 << 20)) return ksa_fail(KSA_EINVAL, "P=%d outside [1, 2^20]", P);
   if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]", (long long)T);
   if (N < 1 || N > 0x7fffffffll || ld < N) return ksa_fail(KSA_EINVAL, "bad N=%lld / ld=%lld", (long long)N, (long long)ld);
-  // Convert on the host, then upload. The source is pageable memory, for which cudaMemcpyAsync
-  // returns only after the bytes have been staged, so the vector may die at function exit.
-  std::vector<ksa_policy_k> host_table((size_t)P);
-  for (int q = 0; q < P; ++q) {
-    int rc = ksa_policy_to_k(&policies[q], A, &host_table[q]);
-    if (rc != KSA_OK) return rc;
-    if (policies[q].attr_mask != policies[0].attr_mask)
-      return ksa_fail(KSA_EINVAL, "policy %d: attr_mask differs from policy 0", q);
-  }
+  if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
   cudaStream_t st = (cudaStream_t)stream;
-  KSA_CUDA(cudaMemcpyAsync(policies_dev, host_table.data(), sizeof(ksa_policy_k) * (size_t)P,
-                           cudaMemcpyHostToDevice, st));
+  int rc = upload_policies(policies, P, A, (ksa_policy_k*)policies_dev, st);
+  if (rc != KSA_OK) return rc;
   SweepArgs a;
   a.policies = (const ksa_policy_k*)policies_dev;
   a.depth = (const long long*)depth_dev;
@@ -437,7 +540,6 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   a.split = 0;
   a.replicas0 = replicas0_dev;
   a.summary = summary_dev;
-  if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
   return sweep_launch(policies, a, A, st, "ksa_sweep_kernel");
 }
 
@@ -458,9 +560,8 @@ namespace {
 static __device__ __align__(256) unsigned char g_static_policy_table[KSA_SWEEP_STATIC_MAX_POLICIES * sizeof(ksa_policy_k)];
 
 constexpr int kMaxStaticDevices = 64;
-std::mutex g_static_mutex;                          // guards the two arrays below
+std::mutex g_static_mutex;                          // guards the array below
 void* g_static_table_addr[kMaxStaticDevices] = {};  // device address of the table, per device
-ksa_policy_k g_static_host_table[KSA_SWEEP_STATIC_MAX_POLICIES];  // conversion buffer (host, .bss)
 
 }  // namespace
 
@@ -484,26 +585,24 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
   if (device < 0 || device >= kMaxStaticDevices)
     return ksa_fail(KSA_ELIMIT, "device ordinal %d outside [0, %d)", device, kMaxStaticDevices);
 
-  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
   // Set-up, once per device, with that device current: in host code the array's name is only a
   // handle for the runtime, the address the kernel must be given comes from the runtime.
-  void* table = g_static_table_addr[device];
-  if (!table) {
-    KSA_CUDA(cudaGetSymbolAddress(&table, g_static_policy_table));
-    g_static_table_addr[device] = table;
-  }
-  for (int q = 0; q < P; ++q) {
-    int rc = ksa_policy_to_k(&policies[q], A, &g_static_host_table[q]);
-    if (rc != KSA_OK) return rc;
-    if (policies[q].attr_mask != policies[0].attr_mask)
-      return ksa_fail(KSA_EINVAL, "policy %d: attr_mask differs from policy 0", q);
+  void* table = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    table = g_static_table_addr[device];
+    if (!table) {
+      KSA_CUDA(cudaGetSymbolAddress(&table, g_static_policy_table));
+      g_static_table_addr[device] = table;
+    }
   }
   cudaStream_t st = (cudaStream_t)stream;
-  // Pageable source: the call returns once the bytes are staged, so the shared host buffer is free
-  // again when the mutex is released. Records [0, P) are rewritten by every call and the kernel
-  // never reads past P-1, so nothing left over from an earlier call needs clearing.
-  KSA_CUDA(cudaMemcpyAsync(table, g_static_host_table, sizeof(ksa_policy_k) * (size_t)P,
-                           cudaMemcpyHostToDevice, st));
+  // Records [0, P) are rewritten by every call (by kernels on `st`, ahead of the sweep kernel) and
+  // nothing past P-1 is read, so nothing left over from an earlier call needs clearing. The
+  // conversion buffer is on this thread's stack: no host state is shared between calls.
+  int rc = upload_policies(policies, P, A, (ksa_policy_k*)table, st);
+  if (rc != KSA_OK) return rc;
   SweepArgs a;
   a.policies = (const ksa_policy_k*)table;
   a.depth = (const long long*)depth_dev;
