@@ -40,26 +40,28 @@ __host__ __device__ inline bool ksa_policy_is_narrow(long long up, long long dow
 // Host (sweep_tile_kinds) and device (the split test in the kernel) use this one function.
 enum { TILE_GENERAL = 0, TILE_NARROW = 1, TILE_SHARED = 2 };
 template <int R>
-__host__ __device__ inline int ksa_tile_kind(const long long (&up)[R], const long long (&down)[R]) {
-  bool narrow = true, shared = true;
+__host__ __device__ inline int ksa_tile_kind(const long long (&up)[R], const long long (&down)[R], bool allow_shared) {
+  bool narrow = true, shared = allow_shared && up[0] > down[0];
   for (int q = 0; q < R; ++q) {
     narrow = narrow && ksa_policy_is_narrow(up[q], down[q]);
     shared = shared && up[q] == up[0] && down[q] == down[0];
   }
-  return narrow ? (shared ? TILE_SHARED : TILE_NARROW) : TILE_GENERAL;
+  return shared ? TILE_SHARED : (narrow ? TILE_NARROW : TILE_GENERAL);
 }
 
 // KIND = the kind of tile the kernel is compiled for:
 //  TILE_NARROW  every policy of the tile is narrow: the step is ksa_step_fma_narrow on the attribute
 //               sum saturated once per tick, 6 compares per decision instead of 9.
-//  TILE_SHARED  narrow, and all policies of the tile have the same two thresholds (the usual case:
-//               grids vary the thresholds slowest): the two threshold tests are made once per
-//               (trace, tick) and shared by the R machines (ksa_step_fma_shared, 4 compares per decision).
-// A grid that mixes kinds is launched once per kind present with a.split = 1; each block then
-// returns at once unless its tile is of the kernel's kind.
+//  TILE_SHARED  all policies of the tile have the same two thresholds, scale_up_messages >
+//               scale_down_messages (the usual case: grids vary the thresholds slowest): the two
+//               threshold tests are made once per (trace, tick), on the 64-bit sum, and shared by
+//               the R machines (ksa_step_fma_shared, 4 compares per decision).
+// A grid that mixes kinds is launched once per kind present with a.split != 0 (1: the three kinds,
+// 2: shared tiles not recognised, KSA_SWEEP_NOSHARED); each block then returns at once unless its
+// tile is of the kernel's kind.
 template <int A, int R, int D, int BLOCK, int MINB, int CHAIN, int KIND>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_constant__ SweepArgs a) {
-  constexpr bool FAST = KIND != TILE_GENERAL;
+  constexpr bool FAST = KIND == TILE_NARROW;
   constexpr bool SHARED = KIND == TILE_SHARED;
   // Block mapping: grid = (trace blocks of a group, policy tiles, groups). Blocks are dispatched x
   // fastest, then y, then z, so a group of gridDim.x trace blocks goes through all policy tiles
@@ -80,7 +82,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
     long long up[R], down[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) up[q] = pk[q].up_msgs, down[q] = pk[q].down_msgs;
-    if (ksa_tile_kind<R>(up, down) != KIND) return;
+    if (ksa_tile_kind<R>(up, down, a.split == 1) != KIND) return;
   }
 
   ksa_trace_regs s[R];
@@ -120,62 +122,62 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
 #pragma unroll
   for (int j = 0; j < D; ++j) buf[j] = j < T ? load_sum(j) : 0;
 
-  int pending = 0, folds = 0;
-#pragma unroll 1
-  for (int t = 0; t < T; t += D) {
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-      const int tt = t + j;
-      if (tt < T) {
-        const long long msgs = buf[j];
-        // FAST keeps the saturated sum in the ring slot's register for the whole tick; refilling the
-        // slot here would go through a temporary that ptxas copies back at the end of the tick,
-        // i.e. it would wait for the load it has just issued. FAST refills after the machines.
-        if (!FAST && tt + D < T) buf[j] = load_sum(tt + D);
-        const int i = tt + 1;
-        // CHAIN > 0: the R machines run in groups of CHAIN. The first compare of a group is made
-        // to wait for the last event of the previous group through a xor that changes nothing
-        // (bit 4 of a wide event code is always 0, which ptxas cannot know). Without it ptxas
-        // interleaves all R machines, runs out of its 7 predicate registers and spills them into
-        // a general register (13 LOP3 + 3 P2R per decision at R = 4).
-        unsigned m_lo = (unsigned)(unsigned long long)msgs;
-        const unsigned m_hi = (unsigned)((unsigned long long)msgs >> 32);
-        int m32 = FAST ? ksa_saturate_s32(msgs) : 0;
-        unsigned ev_last = 0u;
-        // SHARED: main.go:51,65 once for the whole tile (see ksa_step_fma_shared)
-        int iu = 0, id = 0;
-        unsigned e0 = 0u, e0n = 0u;
-        if constexpr (SHARED) {
-          const bool uh = m32 >= (int)pk[0].up_msgs, dh = m32 <= (int)pk[0].down_msgs;
-          iu = uh ? i : INT_MIN;
-          id = dh ? i : INT_MIN;
-          e0 = uh ? KSA_W_UP_COOL : (dh ? KSA_W_DOWN_COOL : 0u);
-          e0n = e0 + (KSA_W_UP_NOOP - KSA_W_UP_COOL);
-        }
-#pragma unroll
-        for (int q = 0; q < R; ++q) {
-          const ksa_step_consts c(pk[q]);
-          if (CHAIN > 0 && q > 0 && q % CHAIN == 0) {
-            if constexpr (FAST)
-              asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m32) : "r"(ev_last));  // m32 ^ (ev & 16)
-            else
-              asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m_lo) : "r"(ev_last));
-          }
-          unsigned ev;  // wide event code
-          if constexpr (SHARED)
-            ev = ksa_step_fma_shared(c, iu, id, e0, e0n, i, one, s[q]);
-          else if constexpr (FAST)
-            ev = ksa_step_fma_narrow((int)pk[q].up_msgs, (int)pk[q].down_msgs, c, m32, i, one, s[q]);
-          else
-            ev = ksa_step_fma<true>(c, (long long)(((unsigned long long)m_hi << 32) | m_lo), i, one, s[q]);
-          ev_last = ev;
-          // (pairing the min / max updates of two ticks, as the replay kernels do, costs a register
-          // per machine here and measured slower: 74.0 vs 71.4 ms)
-          ksa_summary_tick<true>(m[q], s[q].r, ev, one);
-        }
-        if (FAST && tt + D < T) buf[j] = load_sum(tt + D);
-      }
+  // One tick of the R machines. `tt` = tick (0-based), j = its ring slot, prefetch = tick tt + D exists.
+  auto tick = [&](const int tt, const int j, const bool prefetch, const int phase) {
+    const long long msgs = buf[j];
+    // The narrow and shared kernels keep (part of) the sum in the ring slot's registers for the
+    // whole tick; refilling the slot here would go through a temporary that ptxas copies back at the
+    // end of the tick, i.e. it would wait for the load it has just issued. They refill after the
+    // machines.
+    if (KIND == TILE_GENERAL && prefetch) buf[j] = load_sum(tt + D);
+    const int i = tt + 1;
+    // CHAIN > 0: the R machines run in groups of CHAIN. The first compare of a group is made
+    // to wait for the last event of the previous group through a xor that changes nothing
+    // (bit 4 of a wide event code is always 0, which ptxas cannot know). Without it ptxas
+    // interleaves all R machines, runs out of its 7 predicate registers and spills them into
+    // a general register (13 LOP3 + 3 P2R per decision at R = 4).
+    unsigned m_lo = (unsigned)(unsigned long long)msgs;
+    const unsigned m_hi = (unsigned)((unsigned long long)msgs >> 32);
+    int m32 = FAST ? ksa_saturate_s32(msgs) : 0;
+    unsigned ev_last = 0u;
+    // SHARED: main.go:51,65 once for the whole tile (see ksa_step_fma_shared)
+    int iu = 0, id = 0;
+    unsigned e0 = 0u, e0n = 0u;
+    if constexpr (SHARED) {
+      const bool uh = msgs >= pk[0].up_msgs, dh = msgs <= pk[0].down_msgs;
+      iu = uh ? i : INT_MIN;
+      id = dh ? i : INT_MIN;
+      e0 = uh ? KSA_W_UP_COOL : (dh ? KSA_W_DOWN_COOL : 0u);
+      e0n = e0 + (KSA_W_UP_NOOP - KSA_W_UP_COOL);
     }
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const ksa_step_consts c(pk[q]);
+      if (CHAIN > 0 && q > 0 && q % CHAIN == 0) {
+        if constexpr (SHARED)
+          asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(iu) : "r"(ev_last));  // iu ^ (ev & 16)
+        else if constexpr (FAST)
+          asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m32) : "r"(ev_last));  // m32 ^ (ev & 16)
+        else
+          asm volatile("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(m_lo) : "r"(ev_last));
+      }
+      unsigned ev;  // wide event code
+      if constexpr (SHARED)
+        ev = ksa_step_fma_shared(c, iu, id, e0, e0n, i, one, s[q]);
+      else if constexpr (FAST)
+        ev = ksa_step_fma_narrow((int)pk[q].up_msgs, (int)pk[q].down_msgs, c, m32, i, one, s[q]);
+      else
+        ev = ksa_step_fma<true>(c, (long long)(((unsigned long long)m_hi << 32) | m_lo), i, one, s[q]);
+      ev_last = ev;
+      // (pairing the min / max updates of two ticks, as the replay kernels do, costs a register
+      // per machine: with the narrow step it measured slower, 74.0 vs 71.4 ms; the shared step
+      // holds fewer values per machine and takes it)
+      ksa_summary_tick<true>(m[q], s[q].r, ev, one, phase);
+    }
+    if (KIND != TILE_GENERAL && prefetch) buf[j] = load_sum(tt + D);
+  };
+  int pending = 0, folds = 0;
+  auto count_folds = [&]() {
     pending += D;
     if (pending > KSA_FOLD_TICKS - D) {
       pending = 0;
@@ -186,6 +188,23 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_sweep_kernel(const __grid_con
         fold();
       }
     }
+  };
+  int t = 0;
+  // Steady state: every tick of the group exists and so does the tick D ahead of it (no guards).
+#pragma unroll 1
+  for (; t + 2 * D <= T; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+      tick(t + j, j, true, (SHARED && D % 2 == 0) ? (j % 2 ? KSA_TICK_SECOND : KSA_TICK_FIRST) : KSA_TICK_SINGLE);
+    count_folds();
+  }
+  // Drain: at most 2D-1 ticks left; guard both the tick and its prefetch.
+#pragma unroll 1
+  for (; t < T; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+      if (t + j < T) tick(t + j, j, t + j + D < T, KSA_TICK_SINGLE);
+    count_folds();
   }
   flush();
 #pragma unroll
@@ -415,7 +434,7 @@ bool sweep_grid(const SweepVariant& v, int P, long long N, int A, int T, dim3* g
 // Which kinds of policy tiles (ksa_tile_kind; R consecutive policies, the last tile padded with
 // copies of policy P-1 as in the kernel) a grid has: bit k set = some tile is of kind k.
 template <int R>
-unsigned sweep_tile_kinds_r(const ksa_policy* policies, int P) {
+unsigned sweep_tile_kinds_r(const ksa_policy* policies, int P, bool allow_shared) {
   unsigned kinds = 0u;
   for (int p0 = 0; p0 < P; p0 += R) {
     long long up[R], down[R];
@@ -423,25 +442,26 @@ unsigned sweep_tile_kinds_r(const ksa_policy* policies, int P) {
       const ksa_policy& pol = policies[std::min(p0 + q, P - 1)];
       up[q] = pol.scale_up_messages, down[q] = pol.scale_down_messages;
     }
-    kinds |= 1u << ksa_tile_kind<R>(up, down);
+    kinds |= 1u << ksa_tile_kind<R>(up, down, allow_shared);
   }
   return kinds;
 }
-unsigned sweep_tile_kinds(const ksa_policy* policies, int P, int R) {
+unsigned sweep_tile_kinds(const ksa_policy* policies, int P, int R, bool allow_shared) {
   switch (R) {
-    case 1: return sweep_tile_kinds_r<1>(policies, P);
-    case 2: return sweep_tile_kinds_r<2>(policies, P);
-    case 3: return sweep_tile_kinds_r<3>(policies, P);
-    case 4: return sweep_tile_kinds_r<4>(policies, P);
-    case 6: return sweep_tile_kinds_r<6>(policies, P);
-    case 8: return sweep_tile_kinds_r<8>(policies, P);
+    case 1: return sweep_tile_kinds_r<1>(policies, P, allow_shared);
+    case 2: return sweep_tile_kinds_r<2>(policies, P, allow_shared);
+    case 3: return sweep_tile_kinds_r<3>(policies, P, allow_shared);
+    case 4: return sweep_tile_kinds_r<4>(policies, P, allow_shared);
+    case 6: return sweep_tile_kinds_r<6>(policies, P, allow_shared);
+    case 8: return sweep_tile_kinds_r<8>(policies, P, allow_shared);
     default: return 1u << TILE_GENERAL;
   }
 }
 
 // Launch the sweep: one launch per kind of tile the grid has, each kernel on the tiles of its kind.
-// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels for every tile, =2 the narrow kernel
-// for shared tiles (a shared tile is also narrow), for measurements and tests.
+// KSA_SWEEP_GENERAL=1 (environment) forces the general kernels for every tile, KSA_SWEEP_NOSHARED=1
+// classifies without the shared kind (shared tiles then run as narrow or general ones), for
+// measurements and tests.
 int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st, const char* what) {
   const SweepVariant* v[3];
   for (int k = 0; k < 3; ++k) v[k] = find_sweep_variant(kDefaultSweepId[k][A - 1]);
@@ -459,12 +479,12 @@ int sweep_launch(const ksa_policy* policies, SweepArgs a, int A, cudaStream_t st
   if (const char* e = std::getenv("KSA_SWEEP_GENERAL")) force = std::atoi(e);
   // Tiles of the kernels must coincide for the split; the lane kernels have one form.
   unsigned kinds = 1u << TILE_GENERAL;
-  if (v[0]->R > 0 && v[0]->R == v[1]->R && v[0]->R == v[2]->R && force != 1) kinds = sweep_tile_kinds(policies, a.P, v[0]->R);
-  if (force == 2 && (kinds & (1u << TILE_SHARED))) {
-    if (kinds & (1u << TILE_GENERAL)) return ksa_fail(KSA_EINVAL, "KSA_SWEEP_GENERAL=2 needs an all-narrow grid");
-    kinds = 1u << TILE_NARROW;  // one unsplit launch of the narrow kernel over narrow and shared tiles
-  }
-  a.split = (kinds & (kinds - 1)) != 0;  // a kernel tests the kind of its tile only when another kernel has tiles too
+  bool allow_shared = true;
+  if (const char* e = std::getenv("KSA_SWEEP_NOSHARED")) allow_shared = std::atoi(e) == 0;
+  if (v[0]->R > 0 && v[0]->R == v[1]->R && v[0]->R == v[2]->R && force != 1)
+    kinds = sweep_tile_kinds(policies, a.P, v[0]->R, allow_shared);
+  // a kernel tests the kind of its tile only when another kernel has tiles too
+  a.split = (kinds & (kinds - 1)) != 0 ? (allow_shared ? 1 : 2) : 0;
   dim3 grid;
   for (int k = 0; k < 3; ++k) {
     if (!(kinds & (1u << k))) continue;

@@ -10,6 +10,18 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 S = 1_000_000_000  # one second in Go time.Duration units
 
 
+# Kernel variant ids of the tables in csrc/ (mode for ksa_variant_name: 0 full, 1 summary, 2 full with
+# failures, 3 summary with failures, 4 sweep launch shapes). The product build has the defaults only,
+# the tuning build (python __graft_entry__.py --tuning; KSA_LIBRARY=...tuning.so) all of them.
+ALL_VARIANT_IDS = {0: range(1, 64), 1: range(1, 64), 2: range(1, 32), 3: range(1, 32), 4: range(0, 64)}
+
+
+def variants_present(engine, mode: int, wanted=None) -> list[int]:
+    """The ids among `wanted` (default: every id) that the loaded library was built with."""
+    ids = ALL_VARIANT_IDS[mode] if wanted is None else wanted
+    return [i for i in ids if i == -2 or engine.variant_name(mode, i) is not None]
+
+
 def load_golden(name: str):
     with open(os.path.join(HERE, "golden", name)) as f:
         return json.load(f)

@@ -52,7 +52,7 @@ def main():
                 assert sm.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.summary.tobytes()
                 checked += 1
             eng.set_variant(0, 0)
-            for fv in ("0", "1", "2", "3", "4"):
+            for fv in ["0"] + [str(i) for i in range(1, 32) if eng.variant_name(2, i) or eng.variant_name(3, i)]:
                 os.environ["KSA_FAULTS_VARIANT"] = fv
                 s1, s2 = eng.state_from_host(*st), eng.state_from_host(*st)
                 r, e = eng.replay_full(pol, d, T, A, N, ld, 0, s1, fail=f)
@@ -71,7 +71,7 @@ def main():
             r0 = torch.from_numpy(st[0]).to(eng.dev)
             want = [oracle_lib.replay(p.to_c(), depth, T, A, N, ld, 0, *st, want_full=False, want_summary=True).summary
                     for p in pols]
-            for sv in ("0", "5", "8", "9", "16", "20"):
+            for sv in [str(i) for i in (0, 2, 5, 8, 9, 16, 20, 33, 37) if eng.variant_name(4, i)]:
                 os.environ["KSA_SWEEP_VARIANT"] = sv
                 got = eng.replay_sweep(pols, d, T, A, N, ld, r0).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
                 for i in range(len(pols)):

@@ -10,10 +10,10 @@ import pytest
 
 import kube_sqs_autoscaler_b200 as ksa
 from tests import oracle_lib
+from tests.test_gpu_parity import full_variants
 
 pytestmark = pytest.mark.gpu
 S = 10**9
-FULL_IDS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45, 46]
 
 
 @pytest.mark.parametrize("A", [1, 3])
@@ -31,7 +31,7 @@ def test_replay_never_writes_outside_its_outputs(engine, A):
                 st = oracle_lib.fresh_state(5, 0, N, 1, 9)
                 ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, ld, 0, *st, want_summary=True)
                 depth = torch.from_numpy(depth_np).to(engine.dev)
-                for fid in FULL_IDS:
+                for fid in full_variants(engine):
                     engine.set_variant(fid, 0)
                     rbuf = torch.full((T + 2 * guard, ld), -7777, dtype=torch.int32, device=engine.dev)
                     ebuf = torch.full((T + 2 * guard, ld), 0xEE, dtype=torch.uint8, device=engine.dev)
@@ -80,7 +80,8 @@ def test_summary_variants_sweep_and_reduce_never_write_outside(engine, monkeypat
     outputs of ksa_sweep_reduce; shapes with ragged tails and a last policy tile that is not full."""
     import torch
 
-    from tests.test_gpu_parity import SUMMARY_VARIANTS
+    from tests.helpers import variants_present
+    from tests.test_gpu_parity import summary_variants
 
     rng = np.random.default_rng(5)
     guard = 16
@@ -92,7 +93,7 @@ def test_summary_variants_sweep_and_reduce_never_write_outside(engine, monkeypat
             depth = torch.from_numpy(depth_np).to(engine.dev)
             st = oracle_lib.fresh_state(5, 0, N, 1, 9)
             ref = oracle_lib.replay(pol.to_c(), depth_np, T, 1, N, ld, 0, *st, want_full=False, want_summary=True)
-            for sv in SUMMARY_VARIANTS:
+            for sv in summary_variants(engine):
                 engine.set_variant(0, sv)
                 sbuf = torch.full((N + 2 * guard, 64), 0xEE, dtype=torch.uint8, device=engine.dev)
                 summ = sbuf[guard:guard + N]
@@ -111,7 +112,7 @@ def test_summary_variants_sweep_and_reduce_never_write_outside(engine, monkeypat
                     for p in pols]
             for general in ("0", "1"):
                 monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
-                for sv in (2, 9, 16, 27):
+                for sv in variants_present(engine, 4, (2, 9, 16, 27, 33, 37)):
                     monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
                     big = torch.full((P * N + 2 * guard, 64), 0xEE, dtype=torch.uint8, device=engine.dev)
                     out = big[guard:guard + P * N].view(P, N, 64)

@@ -12,7 +12,7 @@ import pytest
 
 import kube_sqs_autoscaler_b200 as ksa
 from tests import oracle_lib
-from tests.helpers import S, load_golden, policy_from_vector
+from tests.helpers import S, load_golden, policy_from_vector, variants_present
 from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 
 pytestmark = pytest.mark.gpu
@@ -82,7 +82,10 @@ def test_random_policies_with_failures(engine, A):
                 engine.set_variant(-2 if scalar else 0, -2 if scalar else 0)
                 out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
                 check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} scalar={scalar}")
-            for fid in ("1", "2", "3", "4", "5", "6", "7", "8", "9"):  # every entry of the faults variant tables (9: V1, small N)
+            # every entry of the two faults variant tables the loaded build has (an id that only the
+            # other mode's table has selects this mode's default)
+            for fid in sorted(set(variants_present(engine, 2)) | set(variants_present(engine, 3))):
+                fid = str(fid)
                 os.environ["KSA_FAULTS_VARIANT"] = fid
                 out = run_gpu(engine, pol, depth, fail, T, A, N, ld, tick0, st)
                 check(out, ref, N, f"A={A} case={case} N={N} T={T} ld={ld} faults_variant={fid}")

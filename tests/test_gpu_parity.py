@@ -6,6 +6,7 @@ Run with `pytest -m gpu` on the B200 box. Nothing here reads /root/reference.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -13,15 +14,21 @@ import pytest
 import kube_sqs_autoscaler_b200 as ksa
 from kube_sqs_autoscaler_b200 import _abi
 from tests import oracle_lib
-from tests.helpers import S, load_golden, policy_from_run_kat, policy_from_vector
+from tests.helpers import S, load_golden, policy_from_run_kat, policy_from_vector, variants_present
 
 pytestmark = pytest.mark.gpu
 
 KATS = load_golden("reference_kats.json")
 DERIVED = load_golden("derived_vectors.json")
-FULL_VARIANTS = [-2, 1, 14, 16, 19, 20, 21, 23, 27, 30, 31, 32, 34, 36, 38, 41, 42, 43, 44, 45, 46]   # -2 = scalar kernel
-SUMMARY_VARIANTS = [-2, 5, 7, 8, 9, 10, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22,  # 21, 22: ordered-thresholds step
-                    30, 33, 38]  # cp.async.bulk + mbarrier staging
+
+
+def full_variants(engine):
+    """-2 = the scalar kernel, then every full-mode variant the loaded build has."""
+    return [-2] + variants_present(engine, 0)
+
+
+def summary_variants(engine):
+    return [-2] + variants_present(engine, 1)  # 21.. ordered-thresholds step; 30.. bulk-copy staging (tuning build)
 
 
 def torch_mod():
@@ -187,8 +194,9 @@ def test_random_policies_all_variants(engine, A):
         ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st, want_summary=True)
         cases.append((pol, T, N, ld, tick0, depth, st, ref))
     try:
-        for k in range(max(len(FULL_VARIANTS), len(SUMMARY_VARIANTS))):
-            fv, sv = FULL_VARIANTS[k % len(FULL_VARIANTS)], SUMMARY_VARIANTS[k % len(SUMMARY_VARIANTS)]
+        fvs, svs = full_variants(engine), summary_variants(engine)
+        for k in range(max(len(fvs), len(svs))):
+            fv, sv = fvs[k % len(fvs)], svs[k % len(svs)]
             engine.set_variant(fv, sv)
             for pol, T, N, ld, tick0, depth, st, ref in cases:
                 out = gpu_full(engine, pol, depth, T, A, N, ld, tick0, st)
@@ -435,7 +443,7 @@ def test_sweep_fast_path_edges_match_oracle(engine, monkeypatch):
     r0_dev = torch.from_numpy(r0[0]).to(engine.dev)
     for general in ("0", "1"):
         monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
-        for sv in (0, 1, 2, 5, 6, 7, 9, 16, 17, 18, 19, 20, 21, 22, 23):
+        for sv in variants_present(engine, 4, (0, 1, 2, 5, 6, 7, 9, 16, 17, 18, 19, 20, 21, 22, 23, 33, 37, 40)):
             monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
             got = engine.replay_sweep(pols, depth, T, A, N, N, r0_dev).cpu().numpy().view(ksa.SUMMARY_DTYPE)
             got = got.reshape(len(pols), N)
@@ -732,7 +740,7 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
     assert int(want[0]["up_noop"].max()) >= T - 3 and int(want[1]["down_cool"].max()) == T
     assert int(want[2]["up_applied"].max()) == T and int(want[2]["down_applied"].max()) == T
     try:
-        for sv in SUMMARY_VARIANTS:
+        for sv in summary_variants(engine):
             engine.set_variant(0, sv)
             for i, pol in enumerate(pols):
                 got = engine.replay_summary(pol, depth, T, A, N, N, 0, engine.state_from_host(*st))
@@ -743,7 +751,7 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
     r0 = torch.from_numpy(st[0]).to(engine.dev)
     for general in ("0", "1"):
         monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
-        for sv in (0, 2, 5, 9, 16, 22, 27):
+        for sv in variants_present(engine, 4, (0, 2, 5, 9, 16, 22, 27, 33, 37)):
             monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
             got = engine.replay_sweep(pols, depth, T, A, N, N, r0).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
             for i in range(len(pols)):
@@ -757,7 +765,7 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
     fail[:, 16:24] = 4
     fail[:, 48:] = rng.choice(np.array([0, 0, 1, 2, 4, 7], dtype=np.uint8), size=(T, N - 48))
     f_dev = torch.from_numpy(fail).to(engine.dev)
-    for fv in ("0", "1", "2", "3", "4", "5", "6", "7", "8", "9"):
+    for fv in ["0"] + [str(i) for i in variants_present(engine, 3)]:
         monkeypatch.setenv("KSA_FAULTS_VARIANT", fv)
         for i, pol in enumerate(pols):
             ref = oracle_lib.replay(pol.to_c(), d_host, T, A, N, N, 0, *st, want_full=False, want_summary=True, fail=fail).summary
@@ -827,3 +835,118 @@ def test_sweep_random_grids_mixed_tiles(engine, A):
         for i, pol in enumerate(pols):
             ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, N, 0, *st, want_full=False, want_summary=True)
             assert got[i].tobytes() == ref.summary.tobytes(), f"A={A} case {case} policy {i}/{P}: {pol}"
+
+
+@pytest.mark.parametrize("A", [1, 3])
+def test_sweep_shared_threshold_tiles(engine, A, monkeypatch):
+    """Grids laid out as real parameter grids are (thresholds vary slowest): runs of policies with the
+    same two thresholds, so that whole register tiles share them and take the shared-threshold kernel
+    (one pair of threshold tests per (trace, tick) for the tile). Mixed with tiles that straddle a
+    threshold change (narrow kernel), tiles with overlapping thresholds and thresholds beyond int32
+    (general kernel; a shared tile need not fit int32), depths at the thresholds and far outside
+    int32, run lengths that are not multiples of the tile, and replica counts large enough to leave
+    the 32-bit window sum of the summary. Every (policy, trace) summary equals the oracle's, with the
+    three-way split, with shared tiles not recognised (KSA_SWEEP_NOSHARED) and through the general
+    kernels alone."""
+    torch = torch_mod()
+    rng = np.random.default_rng(777 + A)
+    mask = (1 << A) - 1
+    for case in range(4):
+        thresholds = [(100, 10), (250, 25), (2**31 + 5, -(2**31) - 5), (7, 6), (2**31 - 1, -(2**31)), (50, 60),
+                      (2**40, 2**40 - 1)]
+        pols = []
+        for up, down in (thresholds[i] for i in rng.permutation(len(thresholds))[:5]):
+            for _ in range(int(rng.choice([3, 4, 5, 8, 9]))):  # run of policies sharing the thresholds
+                big = rng.integers(0, 4) == 0
+                pols.append(ksa.Policy(attr_mask=mask, scale_up_messages=up, scale_down_messages=down,
+                                       poll_period=5 * S, scale_up_cool_down=int(rng.integers(0, 7)) * 5 * S,
+                                       scale_down_cool_down=int(rng.integers(0, 9)) * 3 * S,
+                                       max_pods=int(rng.integers(2, 12)) if not big else 2**31 - 1,
+                                       min_pods=int(rng.integers(0, 3)),
+                                       scale_up_pods=int(rng.integers(1, 4)) if not big else 2**27 + 11,
+                                       scale_down_pods=int(rng.integers(1, 4)) if not big else 2**26 + 3))
+        P = len(pols)
+        T = int(rng.choice([1, 2, 3, 40, 75, 131]))
+        N = int(rng.choice([1, 33, 130]))
+        depth_np = adversarial_depth(rng, T, A, N, pols[0])
+        edge = np.array([100, 99, 10, 11, 250, 25, 7, 6, 2**31 + 5, 2**31 + 4, -(2**31) - 5, -(2**31) - 4, 2**31 - 1,
+                         -(2**31), 2**40, 2**40 - 1, 50, 60], dtype=np.int64)
+        pick = rng.integers(0, 2, size=depth_np.shape) == 0
+        depth_np[pick] = edge[rng.integers(0, edge.size, size=int(pick.sum()))] // (A if A > 1 else 1)
+        r0 = rng.integers(-2, 9, size=N).astype(np.int32)
+        st = (r0, np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+        want = [oracle_lib.replay(p.to_c(), depth_np, T, A, N, N, 0, *st, want_full=False, want_summary=True).summary
+                for p in pols]
+        d = torch.from_numpy(depth_np).to(engine.dev)
+        r0d = torch.from_numpy(r0).to(engine.dev)
+        for env in ({}, {"KSA_SWEEP_NOSHARED": "1"}, {"KSA_SWEEP_GENERAL": "1"}):
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            got = engine.replay_sweep(pols, d, T, A, N, N, r0d).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(P, N)
+            for k in env:
+                monkeypatch.delenv(k)
+            for i in range(P):
+                assert got[i].tobytes() == want[i].tobytes(), f"A={A} case {case} env {env} policy {i}/{P}: {pols[i]}"
+
+
+@pytest.mark.parametrize("A", [1, 2])
+def test_summary_sum_is_exact_beyond_the_32_bit_window(engine, A):
+    """The summary kernels add the replica counts of up to 31 ticks in 32 bits and fold; a trace whose
+    replica count leaves +-2^26 gets its sum recomputed exactly. Traces far beyond that (steps of
+    2^27, limits at the int32 extremes, negative and wrapping counts, Q6) next to ordinary ones, in
+    chunks (the running minimum / maximum come from the record) and with a failure mask: the
+    64-bit sum_replicas and everything else equal the oracle's, for every summary variant."""
+    torch = torch_mod()
+    rng = np.random.default_rng(31337 + A)
+    mask = (1 << A) - 1
+    N, T = 97, 300
+    pols = [ksa.Policy(attr_mask=mask, scale_up_messages=100, scale_down_messages=10, scale_up_cool_down=0,
+                       scale_down_cool_down=5 * S, max_pods=2**31 - 1, min_pods=-(2**31), scale_up_pods=2**27 + 1,
+                       scale_down_pods=2**25 + 7),
+            ksa.Policy(attr_mask=mask, scale_up_messages=10, scale_down_messages=100, scale_up_cool_down=10 * S,
+                       scale_down_cool_down=0, max_pods=2**31 - 1, min_pods=-(2**31), scale_up_pods=2**30,
+                       scale_down_pods=2**29 + 5),
+            ksa.Policy(attr_mask=mask, scale_up_messages=100, scale_down_messages=10, max_pods=2**26 + 40,
+                       min_pods=2**26 - 40, scale_up_pods=7, scale_down_pods=9, scale_up_cool_down=0,
+                       scale_down_cool_down=0)]
+    depth_np = rng.integers(0, 140 // A, size=(T, A, N), dtype=np.int64)
+    fail_np = rng.choice(np.array([0, 0, 0, 0, 1, 2, 4], dtype=np.uint8), size=(T, N))
+    r0 = rng.integers(-5, 9, size=N).astype(np.int32)
+    r0[::7] = 2**26 - 3          # starts next to the limit of the fast path
+    r0[3::11] = -(2**31) + 5
+    r0[5::13] = 2**31 - 9
+    st = (r0, np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+    d = torch.from_numpy(depth_np).to(engine.dev)
+    f = torch.from_numpy(fail_np).to(engine.dev)
+    try:
+        for pol in pols:
+            for fail_arr, fail_dev in ((None, None), (fail_np, f)):
+                ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, N, 0, *st, want_full=False, want_summary=True,
+                                        fail=fail_arr)
+                ids = summary_variants(engine) if fail_dev is None else [0] + variants_present(engine, 3)
+                for sv in ids:
+                    if fail_dev is None:
+                        engine.set_variant(0, sv)
+                    else:
+                        os.environ["KSA_FAULTS_VARIANT"] = str(sv)
+                        engine.set_variant(0, -2 if sv == 0 else 0)
+                    for chunks in ((T,), (64, 31, 1, T - 96)):
+                        state = engine.state_from_host(*st)
+                        summ = engine.new_summary(N)
+                        t0 = 0
+                        for tc in chunks:
+                            engine.replay_summary(pol, d[t0:t0 + tc].contiguous(), tc, A, N, N, t0, state, summary=summ,
+                                                  fail=None if fail_dev is None else fail_dev[t0:t0 + tc].contiguous())
+                            t0 += tc
+                        got = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+                        assert got.tobytes() == ref.summary.tobytes(), f"A={A} variant {sv} chunks {chunks} faults {fail_dev is not None}: {pol}"
+        # the sweep keeps the same accumulators
+        r0d = torch.from_numpy(r0).to(engine.dev)
+        sweep_pols = [p for p in pols for _ in range(3)]
+        got = engine.replay_sweep(sweep_pols, d, T, A, N, N, r0d).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(sweep_pols), N)
+        for i, pol in enumerate(sweep_pols):
+            ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, N, 0, *st, want_full=False, want_summary=True)
+            assert got[i].tobytes() == ref.summary.tobytes(), f"sweep policy {i}: {pol}"
+    finally:
+        os.environ.pop("KSA_FAULTS_VARIANT", None)
+        engine.set_variant(0, 0)
