@@ -127,12 +127,23 @@ def run_config4(args):
                 out.append(a.elapsed_time(b))
         return out
 
-    if args.sweep_tune:  # every tuning point of ksa_sweep.cu (KSA_SWEEP_VARIANT), then the default
-        for vi in range(38):
-            os.environ["KSA_SWEEP_VARIANT"] = str(vi)
+    if args.sweep_tune:  # every launch shape the loaded build has (KSA_SWEEP_VARIANT), then the default
+        ids = [vi for vi in range(64) if eng.variant_name(4, vi)]
+        for knob in ("KSA_SWEEP_SHARED_VARIANT", "KSA_SWEEP_VARIANT"):  # shared-tile kernel alone, then all kinds
+            for vi in ids:
+                os.environ[knob] = str(vi)
+                try:
+                    t = min(time_sweep(1))
+                except ksa.KsaError as e:
+                    print(f"# {knob}={vi}: {e}", flush=True)
+                    continue
+                print(f"# {knob}={vi} ({eng.variant_name(4, vi)}): {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
+            os.environ.pop(knob, None)
+        for knob in ("KSA_SWEEP_NOSHARED", "KSA_SWEEP_GENERAL"):
+            os.environ[knob] = "1"
             t = min(time_sweep(1))
-            print(f"# sweep variant {vi}: {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
-        os.environ.pop("KSA_SWEEP_VARIANT", None)
+            print(f"# {knob}=1: {t:.3f} ms  {P * N * T / (t * 1e-3):.3e} decisions/s", flush=True)
+            os.environ.pop(knob, None)
     ms = time_sweep(args.reps)
     # parity sample: 3 policies x all traces against the single-policy summary kernel
     ok = True
@@ -259,7 +270,7 @@ def run_config6(args):
     state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
     out = {}
     if args.sweep_tune:
-        for fid in range(1, 10):
+        for fid in [i for i in range(1, 32) if eng.variant_name(2, i) or eng.variant_name(3, i)]:
             os.environ["KSA_FAULTS_VARIANT"] = str(fid)
             for mode in ("full", "summary"):
                 ts = []
