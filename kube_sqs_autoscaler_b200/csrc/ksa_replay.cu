@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       unsigned long long acc = (unsigned long long)buf[j][0][v];  // sqs.go:56-64, wrapping
 #pragma unroll
       for (int p = 1; p < A; ++p) acc += (unsigned long long)buf[j][p][v];
-      if constexpr (MODE == MODE_SUMMARY && FMA) {
+      if constexpr (MODE == MODE_SUMMARY && FMA && !FAULTS3) {
         unsigned lo = (unsigned)acc;
         asm("lop3.b32 %0, %0, %1, 16, 0x78;" : "+r"(lo) : "r"(taint[v]));  // lo ^ (taint & 16)
         acc = (acc & 0xffffffff00000000ull) | lo;
