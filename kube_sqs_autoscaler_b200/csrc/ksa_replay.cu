@@ -674,11 +674,16 @@ const Variant kFullVariants[] = {
 };
 const Variant kSummaryVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 0, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
-    KSA_VARIANT(20, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    // ring of 12 ticks: 1.000 (16) and 1.005 (24) of the measured copy peak at A = 1 against 0.979 / 0.987
+    // for the ring of 8 (20, 21) once the loop is at 32 instructions per decision
+    // (profiles/r02_variants.txt); A = 2, 3 keep the shapes of 20 / 21
+    KSA_VARIANT(16, MODE_SUMMARY, 1, 12, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
     // STEP 6: for policies with scale_up_messages > scale_down_messages only (ksa_step_fma ORDERED);
     // replay_common substitutes the general default when the policy is not ordered.
-    KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
 #ifdef KSA_TUNING_VARIANTS
+    KSA_VARIANT(20, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
+    KSA_VARIANT(21, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 8, 1, 3, 128, 10, 1, 2, 128, 10),
     KSA_VARIANT(5, MODE_SUMMARY, 2, 8, HINT_NA, 1, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
     KSA_VARIANT(7, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
     KSA_VARIANT(8, MODE_SUMMARY, 2, 8, HINT_NA, 2, 128, 4, 2, 4, 128, 4, 2, 3, 128, 4),
@@ -688,13 +693,13 @@ const Variant kSummaryVariants[] = {
     KSA_VARIANT(13, MODE_SUMMARY, 1, 4, HINT_NA, 2, 128, 12, 1, 2, 128, 12, 1, 2, 128, 10),
     KSA_VARIANT(14, MODE_SUMMARY, 1, 6, HINT_NA, 2, 128, 10, 1, 3, 128, 10, 1, 2, 128, 10),
     KSA_VARIANT(15, MODE_SUMMARY, 1, 8, HINT_NA, 2, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
-    KSA_VARIANT(16, MODE_SUMMARY, 1, 12, HINT_NA, 2, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
+    KSA_VARIANT(31, MODE_SUMMARY, 1, 12, HINT_NA, 2, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
     KSA_VARIANT(17, MODE_SUMMARY, 1, 16, HINT_NA, 2, 128, 6, 1, 8, 128, 6, 1, 5, 128, 6),
     KSA_VARIANT(18, MODE_SUMMARY, 1, 8, HINT_NA, 2, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
     KSA_VARIANT(19, MODE_SUMMARY, 1, 8, HINT_NA, 2, 64, 16, 1, 4, 64, 16, 1, 3, 64, 16),
     KSA_VARIANT(22, MODE_SUMMARY, 2, 4, HINT_NA, 6, 128, 8, 2, 3, 128, 8, 2, 2, 128, 8),
     KSA_VARIANT(23, MODE_SUMMARY, 1, 8, HINT_NA, 6, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
-    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 6, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
+    KSA_VARIANT(32, MODE_SUMMARY, 1, 12, HINT_NA, 6, 128, 8, 1, 6, 128, 8, 1, 4, 128, 8),
     KSA_VARIANT(25, MODE_SUMMARY, 1, 8, HINT_NA, 6, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
     // 30..: rows staged in shared memory by cp.async.bulk (ksa_summary_bulk_kernel). Measured
     // 0.87 (33) / 0.86 (38) of the copy bandwidth against 0.92 for the register ring (21), so they
@@ -749,8 +754,8 @@ constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per 
 constexpr int kDefaultFullV2 = 43;   // fewer than 327680 traces: two traces per thread
 constexpr int kDefaultFullOpt = 16;  // used when one of the two outputs is NULL
 constexpr int kDefaultFullOptV1 = 46;  // the same below 196608 traces
-constexpr int kDefaultSummary = 20;  // one trace per thread: no interleaved state machines, no predicate spills
-constexpr int kDefaultSummaryOrdered = 21;  // the same with the ordered-thresholds step
+constexpr int kDefaultSummary = 16;  // one trace per thread: no interleaved state machines, no predicate spills
+constexpr int kDefaultSummaryOrdered = 24;  // the same with the ordered-thresholds step
 constexpr int kDefaultFullFaults = 8, kDefaultFullFaultsV1 = 9, kDefaultFullFaultsOpt = 1;
 constexpr int kDefaultSummaryFaults = 10, kDefaultSummaryFaultsOrdered = 11;
 

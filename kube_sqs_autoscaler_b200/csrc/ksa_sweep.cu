@@ -371,12 +371,11 @@ struct SweepVariant {
 // were measured (profiles/r01_config4_sweep_tune.txt). KSA_SWEEP_VARIANT=<id> (environment)
 // overrides the default for measurements and tests.
 const SweepVariant kSweepVariants[] = {
-    KSA_SWEEP(2, 4, 2, 128, 4),   // A=1: narrow and shared tiles
-    KSA_SWEEP(37, 4, 1, 128, 5),  // A=1: general tiles
+    KSA_SWEEP(26, 4, 3, 128, 4),  // A=1: every kind
     KSA_SWEEP(33, 4, 1, 256, 2),  // A=2,3: every kind (three 2-KB rows per tick want the wider block)
     KSA_SWEEP_LANE(9, 2, 4, 128, 8),  // the second layout (lane = policy), kept as a cross-check
 #ifdef KSA_TUNING_VARIANTS
-    KSA_SWEEP(0, 4, 4, 128, 3), KSA_SWEEP(1, 2, 4, 128, 6), KSA_SWEEP(3, 2, 4, 256, 3),
+    KSA_SWEEP(0, 4, 4, 128, 3), KSA_SWEEP(1, 2, 4, 128, 6), KSA_SWEEP(2, 4, 2, 128, 4), KSA_SWEEP(3, 2, 4, 256, 3),
     KSA_SWEEP(4, 1, 8, 128, 8), KSA_SWEEP(5, 8, 2, 128, 2), KSA_SWEEP(6, 4, 4, 64, 6), KSA_SWEEP(7, 3, 4, 128, 4),
     KSA_SWEEP_LANE(8, 1, 4, 128, 10), KSA_SWEEP_LANE(10, 1, 8, 128, 8),
     KSA_SWEEP_LANE(11, 2, 2, 128, 8), KSA_SWEEP_LANE(12, 1, 4, 256, 4), KSA_SWEEP_LANE(13, 2, 4, 256, 4),
@@ -386,11 +385,11 @@ const SweepVariant kSweepVariants[] = {
     KSA_SWEEP_CH(19, 4, 4, 128, 3, 1), KSA_SWEEP_CH(20, 8, 2, 128, 2, 2), KSA_SWEEP_CH(21, 8, 2, 128, 2, 4),
     KSA_SWEEP_CH(22, 6, 2, 128, 3, 2), KSA_SWEEP_CH(23, 4, 4, 64, 6, 2),
     // 24..: more unchained R=4 points (the narrow step needs fewer predicates)
-    KSA_SWEEP(24, 4, 1, 128, 4), KSA_SWEEP(25, 4, 2, 64, 8), KSA_SWEEP(26, 4, 3, 128, 4), KSA_SWEEP(27, 4, 2, 256, 2),
+    KSA_SWEEP(24, 4, 1, 128, 4), KSA_SWEEP(25, 4, 2, 64, 8), KSA_SWEEP(27, 4, 2, 256, 2),
     KSA_SWEEP(28, 4, 2, 128, 5), KSA_SWEEP(29, 4, 2, 128, 3),
     // 30..: 256-thread blocks (2 KB depth rows per block and tick; better with three attributes)
     KSA_SWEEP_CH(30, 4, 2, 256, 2, 2), KSA_SWEEP_CH(31, 4, 4, 256, 2, 2), KSA_SWEEP(32, 4, 3, 256, 2),
-    KSA_SWEEP(34, 4, 1, 512, 1), KSA_SWEEP(35, 4, 2, 512, 1), KSA_SWEEP_CH(36, 4, 1, 256, 2, 2),
+    KSA_SWEEP(34, 4, 1, 512, 1), KSA_SWEEP(35, 4, 2, 512, 1), KSA_SWEEP_CH(36, 4, 1, 256, 2, 2), KSA_SWEEP(37, 4, 1, 128, 5),
     // 38..: shapes for the shared-threshold tiles (fewer live predicates: deeper rings / more blocks fit)
     KSA_SWEEP(38, 4, 2, 128, 6), KSA_SWEEP(39, 4, 4, 128, 4), KSA_SWEEP(40, 8, 2, 128, 2), KSA_SWEEP(41, 8, 1, 128, 3),
     KSA_SWEEP(42, 6, 2, 128, 3), KSA_SWEEP(43, 4, 2, 64, 10), KSA_SWEEP(44, 8, 2, 64, 5),
@@ -401,12 +400,12 @@ const SweepVariant* find_sweep_variant(int id) {
     if (v.id == id) return &v;
   return nullptr;
 }
-// Defaults per tile kind and number of attributes (index A-1), from profiles/r01_config4_sweep_tune.txt.
-// All have R = 4, which the split launch of a mixed grid needs (tiles of the kernels must coincide).
-//   narrow tiles:  A=1: R4 D2 128x4 unchained (71.5 ms on configs[3]); A=2,3: R4 D1 256x2 (83 ms at A=3,
-//                  112 ms with the A=1 choice)
-//   other tiles:   A=1: R4 D1 128x5 unchained (75.3 ms); A=2,3: R4 D1 256x2 (87 ms at A=3)
-constexpr int kDefaultSweepId[3][3] = {{37, 33, 33}, {2, 33, 33}, {2, 33, 33}};
+// Defaults per tile kind and number of attributes (index A-1). All have R = 4, which the split launch
+// of a mixed grid needs (tiles of the kernels must coincide).
+//   A=1: R4 D3 128x4 for every kind: 58.4 ms on configs[3] (profiles/r02_sweep_tune.txt; R4 D2 128x4,
+//        the round-1 choice for narrow tiles: 61.6 ms; R4 D1 128x5 for general tiles: 60.3 ms)
+//   A=2,3: R4 D1 256x2 (three 2-KB rows per tick want the wider block; profiles/r01_config4_sweep_tune.txt)
+constexpr int kDefaultSweepId[3][3] = {{26, 33, 33}, {26, 33, 33}, {26, 33, 33}};
 
 // Grid of a sweep launch, or false if it does not fit one launch. Register-tile kernels:
 // (gw trace blocks, policy tiles, groups of gw trace blocks), see the block mapping in the kernel;

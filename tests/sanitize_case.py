@@ -71,7 +71,7 @@ def main():
             r0 = torch.from_numpy(st[0]).to(eng.dev)
             want = [oracle_lib.replay(p.to_c(), depth, T, A, N, ld, 0, *st, want_full=False, want_summary=True).summary
                     for p in pols]
-            for sv in [str(i) for i in (0, 2, 5, 8, 9, 16, 20, 33, 37) if eng.variant_name(4, i)]:
+            for sv in [str(i) for i in (0, 2, 5, 8, 9, 16, 20, 26, 33, 37) if eng.variant_name(4, i)]:
                 os.environ["KSA_SWEEP_VARIANT"] = sv
                 got = eng.replay_sweep(pols, d, T, A, N, ld, r0).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
                 for i in range(len(pols)):

@@ -443,7 +443,7 @@ def test_sweep_fast_path_edges_match_oracle(engine, monkeypatch):
     r0_dev = torch.from_numpy(r0[0]).to(engine.dev)
     for general in ("0", "1"):
         monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
-        for sv in variants_present(engine, 4, (0, 1, 2, 5, 6, 7, 9, 16, 17, 18, 19, 20, 21, 22, 23, 33, 37, 40)):
+        for sv in variants_present(engine, 4, (0, 1, 2, 5, 6, 7, 9, 16, 17, 18, 19, 20, 21, 22, 23, 26, 33, 37, 40)):
             monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
             got = engine.replay_sweep(pols, depth, T, A, N, N, r0_dev).cpu().numpy().view(ksa.SUMMARY_DTYPE)
             got = got.reshape(len(pols), N)
@@ -751,7 +751,7 @@ def test_summary_counters_survive_long_saturated_runs(engine, monkeypatch):
     r0 = torch.from_numpy(st[0]).to(engine.dev)
     for general in ("0", "1"):
         monkeypatch.setenv("KSA_SWEEP_GENERAL", general)
-        for sv in variants_present(engine, 4, (0, 2, 5, 9, 16, 22, 27, 33, 37)):
+        for sv in variants_present(engine, 4, (0, 2, 5, 9, 16, 22, 26, 27, 33, 37)):
             monkeypatch.setenv("KSA_SWEEP_VARIANT", str(sv))
             got = engine.replay_sweep(pols, depth, T, A, N, N, r0).cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(len(pols), N)
             for i in range(len(pols)):
