@@ -18,21 +18,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BRA = re.compile(r"BRA(?:\.U)?\s+(?:!?U?P\d,\s*)?(0x[0-9a-f]+)")
 
 
-def main():
-    args = sys.argv[1:]
-    so = os.path.join(ROOT, "kube_sqs_autoscaler_b200", "libksareplay.so")
-    which = 0
-    for flag in ("--lib", "--loop"):
-        if flag in args:
-            k = args.index(flag)
-            if flag == "--lib":
-                so = args[k + 1]
-            else:
-                which = int(args[k + 1])
-            del args[k:k + 2]
-    pat, per = args[0], float(args[1])
-    out = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
-    for f in out.split("Function : ")[1:]:
+_SASS = {}
+
+
+def hot_path(so, pat, per, which=0):
+    """[(kernel name, loop start, loop end, cold block or None, instructions, {opcode: count})] for
+    every function of `so` whose mangled name contains `pat`."""
+    if so not in _SASS:
+        _SASS[so] = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
+    res = []
+    for f in _SASS[so].split("Function : ")[1:]:
         name = f.split("\n", 1)[0].strip()
         if pat not in name:
             continue
@@ -43,7 +38,6 @@ def main():
                 ins.append((int(m.group(1), 16), m.group(2).strip()))
         loops = sorted({(int(m.group(1), 16), a) for a, t in ins for m in [BRA.search(t)] if m and int(m.group(1), 16) < a})
         if len(loops) <= which:
-            print(name, "no such loop")
             continue
         lo, hi = loops[which]
         skip = None
@@ -57,10 +51,35 @@ def main():
         for t in hot:
             tt = t.split()
             hist[(tt[1] if tt[0].startswith("@") else tt[0]).split(".")[0]] += 1
-        print(name)
-        print(f"  loop 0x{lo:x}..0x{hi:x}" + (f", cold block 0x{skip[0]:x}..0x{skip[1]:x} left out" if skip else "") +
-              f": {len(hot)} instructions = {len(hot) / per:.2f} per decision")
-        print("  " + ", ".join(f"{k} {v / per:.2f}" for k, v in hist.most_common()))
+        res.append((name, lo, hi, skip, len(hot), hist))
+    return res
+
+
+def describe(entry, per):
+    name, lo, hi, skip, n, hist = entry
+    return (f"{name}\n  loop 0x{lo:x}..0x{hi:x}" + (f", cold block 0x{skip[0]:x}..0x{skip[1]:x} left out" if skip else "") +
+            f": {n} instructions = {n / per:.2f} per decision\n  " +
+            ", ".join(f"{k} {v / per:.2f}" for k, v in hist.most_common()))
+
+
+def main():
+    args = sys.argv[1:]
+    so = os.path.join(ROOT, "kube_sqs_autoscaler_b200", "libksareplay.so")
+    which = 0
+    for flag in ("--lib", "--loop"):
+        if flag in args:
+            k = args.index(flag)
+            if flag == "--lib":
+                so = args[k + 1]
+            else:
+                which = int(args[k + 1])
+            del args[k:k + 2]
+    pat, per = args[0], float(args[1])
+    found = hot_path(so, pat, per, which)
+    if not found:
+        print("no kernel / no such loop for", pat)
+    for e in found:
+        print(describe(e, per))
 
 
 if __name__ == "__main__":

@@ -1,0 +1,69 @@
+#!/usr/bin/env python
+"""Instruction counts of the default kernels' steady-state loops, from the SASS of the built library.
+
+    python tools/sass_report.py            # rewrites profiles/sass_counts.json and profiles/r02_sass_main_loops.txt
+
+bench.py reads profiles/sass_counts.json for the issue-rate roofline of the policy sweep
+(instructions per decision x decisions/s against 148 SMs x 4 schedulers x 32 lanes x clock).
+Run it again whenever a kernel or a default launch shape changes (tests/test_host_logic.py checks
+that the file still matches the library when cuobjdump is available)."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import sass_hot  # noqa: E402
+
+LIB = os.path.join(ROOT, "kube_sqs_autoscaler_b200", "libksareplay.so")
+
+# (key, what, mangled-name pattern, decisions per trip of the steady-state loop)
+KERNELS = [
+    ("full", "ksa_replay_full, A=1, default (8 traces per thread, ring of 2)",
+     "ksa_replay_kernelILi1ELi8ELi2ELi1ELi0ELi2ELi256ELi2E", 16),
+    ("full_small_n", "ksa_replay_full, A=1, below 196608 traces (1 trace per thread, ring of 8)",
+     "ksa_replay_kernelILi1ELi1ELi8ELi1ELi0ELi2ELi128ELi8E", 8),
+    ("summary_ordered", "ksa_replay_summary, A=1, scale_up_messages > scale_down_messages (1 trace per thread, ring of 12)",
+     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi6ELi128ELi8E", 12),
+    ("summary", "ksa_replay_summary, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi2ELi128ELi8E", 12),
+    ("full_faults", "ksa_replay_full_faults, A=1 (4 traces per thread, ring of 4)",
+     "ksa_replay_kernelILi1ELi4ELi4ELi1ELi0ELi8ELi128ELi5E", 16),
+    ("summary_faults_ordered", "ksa_replay_summary_faults, A=1, ordered thresholds (1 trace per thread, ring of 8)",
+     "ksa_replay_kernelILi1ELi1ELi8ELi1ELi1ELi9ELi128ELi8E", 8),
+    ("summary_faults", "ksa_replay_summary_faults, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi8ELi1ELi1ELi10ELi128ELi8E", 8),
+    ("sweep_shared", "ksa_replay_sweep, A=1, tiles sharing their thresholds (4 policies per thread, ring of 3)",
+     "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi2E", 12),
+    ("sweep_narrow", "ksa_replay_sweep, A=1, ordered int32 thresholds", "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi1E", 12),
+    ("sweep_general", "ksa_replay_sweep, A=1, any thresholds", "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi0E", 12),
+]
+
+
+def collect(lib=LIB):
+    counts, text = {}, []
+    for key, what, pat, per in KERNELS:
+        found = sass_hot.hot_path(lib, pat, per)
+        if len(found) != 1:
+            raise SystemExit(f"{key}: {len(found)} kernels match {pat}: update tools/sass_report.py (a default changed?)")
+        counts[key] = round(found[0][4] / per, 2)
+        text.append(f"## {key}: {what}\n{sass_hot.describe(found[0], per)}\n")
+    return counts, text
+
+
+def main():
+    counts, text = collect()
+    out = {"source": "tools/sass_report.py: cuobjdump -sass of libksareplay.so, steady-state loop without its cold fold / flush block",
+           "instructions_per_decision": counts,
+           "sweep_instructions_per_decision": {k[len("sweep_"):]: v for k, v in counts.items() if k.startswith("sweep_")}}
+    with open(os.path.join(ROOT, "profiles", "sass_counts.json"), "w") as f:
+        json.dump(out, f, indent=1)
+        f.write("\n")
+    with open(os.path.join(ROOT, "profiles", "r02_sass_main_loops.txt"), "w") as f:
+        f.write("# Steady-state loops of the default kernels (sm_100a SASS of kube_sqs_autoscaler_b200/libksareplay.so).\n"
+                "# tools/sass_report.py; opcode counts are per decision (1 decision = 1 trace x 1 tick [x 1 policy]).\n"
+                "# ALU pipe (half rate): ISETP, SEL, LOP3, VIADDMNMX, VIMNMX(3), IADD3, LEA; FMA pipe: IMAD.\n\n")
+        f.write("\n".join(text))
+    print(json.dumps(out["instructions_per_decision"], indent=1))
+
+
+if __name__ == "__main__":
+    main()
