@@ -199,7 +199,8 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  *   state        in/out carry state (see ksa_state)
  *   replicas_dev [T][ld] int32  replica count after each tick     (may be NULL: not written)
  *   events_dev   [T][ld] uint8  KSA_EV_* bits of each tick        (may be NULL: not written)
- * Limits: 1 <= T <= 2^30, 1 <= N <= 2^31-1, N <= ld.
+ * Limits: 1 <= T <= 2^30 - 64 per call (chunk longer traces: the carry state makes that exact),
+ * 1 <= N <= 2^31-1, N <= ld.
  */
 int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
                     int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,

@@ -220,7 +220,7 @@ extern "C" int ksa_pipeline_create(ksa_pipeline** out, int device, int64_t N, in
   if (N < 1 || N > 0x7fffffffll) return ksa_fail(KSA_EINVAL, "N=%lld outside [1, 2^31-1]", (long long)N);
   if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
   if (chunk_ticks < 1 || chunk_ticks > KSA_MAX_CHUNK_TICKS)
-    return ksa_fail(KSA_EINVAL, "chunk_ticks=%lld outside [1, 2^30]", (long long)chunk_ticks);
+    return ksa_fail(KSA_EINVAL, "chunk_ticks=%lld outside [1, 2^30 - 64]", (long long)chunk_ticks);
   ksa_pipeline* p = new (std::nothrow) ksa_pipeline();
   if (!p) return ksa_fail(KSA_ENOMEM, "out of host memory");
   std::memset(p, 0, sizeof(*p));
@@ -276,7 +276,7 @@ static cudaError_t copy_rows_d2h(void* dst, const void* src, size_t elem, int64_
 
 // fail_host == NULL: the plain replay; otherwise the *_faults kernels with the mask staged
 // alongside the depths (one more byte per decision on the H2D stream).
-static int pipeline_run(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
+static int pipeline_run_inner(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
                         const uint8_t* fail_host, int64_t T, int64_t N, int64_t tick0,
                         int32_t* state_replicas_host, int64_t* state_last_up_host,
                         int64_t* state_last_down_host, int32_t* replicas_host, uint8_t* events_host,
@@ -365,6 +365,29 @@ static int pipeline_run(ksa_pipeline* p, const ksa_policy* policy, const int64_t
   KSA_CUDA(cudaStreamSynchronize(p->s_k));
   KSA_CUDA(cudaStreamSynchronize(p->s_out));
   return KSA_OK;
+}
+
+// The calls are synchronous: when they return, nothing may still be reading the caller's host buffers
+// or writing into them, also after an error. pipeline_run_inner returns at the first failing call;
+// this wrapper then waits for whatever had been queued on the three streams (ignoring further
+// errors) before the status goes back, so the caller can free or reuse its buffers and the next
+// call finds the staging buffers and events idle.
+static int pipeline_run(ksa_pipeline* p, const ksa_policy* policy, const int64_t* depth_host,
+                        const uint8_t* fail_host, int64_t T, int64_t N, int64_t tick0,
+                        int32_t* state_replicas_host, int64_t* state_last_up_host,
+                        int64_t* state_last_down_host, int32_t* replicas_host, uint8_t* events_host,
+                        ksa_summary* summary_host) {
+  const int rc = pipeline_run_inner(p, policy, depth_host, fail_host, T, N, tick0, state_replicas_host,
+                                    state_last_up_host, state_last_down_host, replicas_host, events_host,
+                                    summary_host);
+  if (rc != KSA_OK && p) {
+    DeviceGuard guard(p->device);
+    cudaStreamSynchronize(p->s_in);
+    cudaStreamSynchronize(p->s_k);
+    cudaStreamSynchronize(p->s_out);
+    cudaGetLastError();  // the message of the first failure is already in ksa_last_error()
+  }
+  return rc;
 }
 
 extern "C" int ksa_pipeline_replay(ksa_pipeline* p, const ksa_policy* policy,

@@ -148,7 +148,7 @@ int check_gen(const ksa_gen_params* g, int64_t T, int32_t A, int64_t N, int64_t 
     return ksa_fail(KSA_EINVAL, "unknown generator family %d", g->family);
   if (g->reserved != 0 || g->reserved2 != 0) return ksa_fail(KSA_EINVAL, "reserved fields must be 0");
   if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
-  if (T < 0 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [0, 2^30]", (long long)T);
+  if (T < 0 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [0, 2^30 - 64]", (long long)T);
   if (N < 0 || N > 0x7fffffffll || ld < N) return ksa_fail(KSA_EINVAL, "bad N=%lld / ld=%lld", (long long)N, (long long)ld);
   if (g->low_max < 0 || g->high_min <= g->low_max || g->high_max < g->high_min ||
       g->high_max > 0xFFFFFFFFll)

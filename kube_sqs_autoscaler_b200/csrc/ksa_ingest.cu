@@ -61,34 +61,43 @@ __global__ void __launch_bounds__(THREADS) transpose_kernel(const SRC* __restric
 template <typename SRC, int TT, int TN, int THREADS>
 int launch_transpose(const void* src, long long src_ld, long long T, long long N, int A, int a, long long ld,
                      long long* dst, cudaStream_t st) {
-  const long long gx = (T + TT - 1) / TT, gy = (N + TN - 1) / TN;
-  if (gx > 0x7fffffffll || gy > 65535)
-    return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max %d traces)", N, 65535 * TN);
+  const long long gx = (T + TT - 1) / TT;
+  if (gx > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "T=%lld too large for one launch", T);
   constexpr size_t smem = sizeof(SRC) * (size_t)TN * (TT + 1);
   if (smem > 227 * 1024) return ksa_fail(KSA_EINVAL, "transpose shape %dx%d needs %zu bytes of shared memory", TT, TN, smem);
   auto kernel = transpose_kernel<SRC, TT, TN, THREADS>;
   if (smem > 48 * 1024) KSA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kernel<<<dim3((unsigned)gx, (unsigned)gy), THREADS, smem, st>>>((const SRC*)src, src_ld, T, N, A, a, ld, dst);
-  KSA_LAUNCH_CHECK("transpose_kernel");
+  // The trace axis is on gridDim.y (at most 65535 tiles): more traces go in slabs, one launch each,
+  // so that every trace count the replay entry points accept can be ingested.
+  constexpr long long kSlab = 65535ll * TN;
+  for (long long nb = 0; nb < N; nb += kSlab) {
+    const long long ns = N - nb < kSlab ? N - nb : kSlab;
+    kernel<<<dim3((unsigned)gx, (unsigned)((ns + TN - 1) / TN)), THREADS, smem, st>>>(
+        (const SRC*)src + nb * src_ld, src_ld, T, ns, A, a, ld, dst + nb);
+    KSA_LAUNCH_CHECK("transpose_kernel");
+  }
   return KSA_OK;
 }
 
 template <typename SRC>
 int dispatch_transpose(int shape, const void* src, long long src_ld, long long T, long long N, int A, int a,
                        long long ld, long long* dst, cudaStream_t st) {
-  switch (shape) {
+  switch (shape) {  // the two defaults in every build, the other tile shapes that were measured in the tuning build
+    case 4: return launch_transpose<SRC, 64, 128, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+    case 7: return launch_transpose<SRC, 256, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
+#ifdef KSA_TUNING_VARIANTS
+    case 0: return launch_transpose<SRC, 64, 64, 256>(src, src_ld, T, N, A, a, ld, dst, st);
     case 1: return launch_transpose<SRC, 128, 64, 512>(src, src_ld, T, N, A, a, ld, dst, st);
     case 2: return launch_transpose<SRC, 256, 32, 256>(src, src_ld, T, N, A, a, ld, dst, st);
     case 3: return launch_transpose<SRC, 128, 128, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
-    case 4: return launch_transpose<SRC, 64, 128, 512>(src, src_ld, T, N, A, a, ld, dst, st);
     case 5: return launch_transpose<SRC, 128, 32, 256>(src, src_ld, T, N, A, a, ld, dst, st);
     case 6: return launch_transpose<SRC, 512, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
-    case 7: return launch_transpose<SRC, 256, 32, 512>(src, src_ld, T, N, A, a, ld, dst, st);
     case 8: return launch_transpose<SRC, 512, 32, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
     case 9: return launch_transpose<SRC, 256, 64, 512>(src, src_ld, T, N, A, a, ld, dst, st);
     case 10: return launch_transpose<SRC, 32, 256, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
     case 11: return launch_transpose<SRC, 64, 256, 1024>(src, src_ld, T, N, A, a, ld, dst, st);
-    default: return launch_transpose<SRC, 64, 64, 256>(src, src_ld, T, N, A, a, ld, dst, st);
+#endif
+    default: return ksa_fail(KSA_EINVAL, "transpose shape %d is not in this build (KSA_TRANSPOSE_SHAPE)", shape);
   }
 }
 // profiles/r01_ingest_tune.txt: int64 source 256 ticks x 32 traces, 512 threads (1.00 of the copy
@@ -269,21 +278,30 @@ extern "C" int ksa_ingest_decimal(const char* text_dev, int32_t width, int64_t c
   if (count < 0) return ksa_fail(KSA_EINVAL, "count < 0");
   if (count == 0) return KSA_OK;
   int U = 8;
+#ifdef KSA_TUNING_VARIANTS
   if (const char* e = std::getenv("KSA_DECIMAL_UNROLL")) U = std::atoi(e);  // tuning knob (tools/): 1, 2, 4 or 8
   if (U != 1 && U != 2 && U != 4) U = 8;
+#endif
   const long long blocks = (count + 256 * U - 1) / (256 * U);
   if (blocks > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "count too large for one launch");
   cudaStream_t st = (cudaStream_t)stream;
   const bool vec = (width % 16 == 0) && ksa_aligned(text_dev, 16);
   long long* out = (long long*)values_dev;
 #define KSA_DEC(WV, UU) decimal_kernel<WV, UU><<<(unsigned)blocks, 256, 0, st>>>(text_dev, width, count, out, fail_dev)
+#ifdef KSA_TUNING_VARIANTS
+#define KSA_DEC_U(WV) \
+  if (U == 1) KSA_DEC(WV, 1); else if (U == 2) KSA_DEC(WV, 2); else if (U == 4) KSA_DEC(WV, 4); else KSA_DEC(WV, 8)
+#else
+#define KSA_DEC_U(WV) KSA_DEC(WV, 8)  // profiles/r01_ingest_tune.txt: 8 records per thread
+#endif
   if (vec && width == 16) {
-    if (U == 1) KSA_DEC(1, 1); else if (U == 2) KSA_DEC(1, 2); else if (U == 4) KSA_DEC(1, 4); else KSA_DEC(1, 8);
+    KSA_DEC_U(1);
   } else if (vec && width == 32) {
-    if (U == 1) KSA_DEC(2, 1); else if (U == 2) KSA_DEC(2, 2); else if (U == 4) KSA_DEC(2, 4); else KSA_DEC(2, 8);
+    KSA_DEC_U(2);
   } else {
-    if (U == 1) KSA_DEC(0, 1); else if (U == 2) KSA_DEC(0, 2); else if (U == 4) KSA_DEC(0, 4); else KSA_DEC(0, 8);
+    KSA_DEC_U(0);
   }
+#undef KSA_DEC_U
 #undef KSA_DEC
   KSA_LAUNCH_CHECK("decimal_kernel");
   return KSA_OK;
@@ -294,10 +312,14 @@ extern "C" int ksa_ingest_transpose_mask(const uint8_t* src_dev, int64_t src_ld,
   if (!src_dev || !fail_dev) return ksa_fail(KSA_EINVAL, "NULL pointer");
   if (T < 0 || N < 0 || src_ld < T || ld < N) return ksa_fail(KSA_EINVAL, "bad T/N/src_ld/ld");
   if (T == 0 || N == 0) return KSA_OK;
-  const long long gx = (T + 63) / 64, gy = (N + 63) / 64;
-  if (gx > 0x7fffffffll || gy > 65535) return ksa_fail(KSA_ELIMIT, "N=%lld too large for one launch (max %d traces)", (long long)N, 65535 * 64);
-  transpose_mask_kernel<<<dim3((unsigned)gx, (unsigned)gy), 256, 0, (cudaStream_t)stream>>>(
-      src_dev, src_ld, T, N, ld, fail_dev, accumulate);
-  KSA_LAUNCH_CHECK("transpose_mask_kernel");
+  const long long gx = (T + 63) / 64;
+  if (gx > 0x7fffffffll) return ksa_fail(KSA_ELIMIT, "T=%lld too large for one launch", (long long)T);
+  constexpr long long kSlab = 65535ll * 64;  // gridDim.y holds 65535 tiles of 64 traces: slabs beyond that
+  for (long long nb = 0; nb < N; nb += kSlab) {
+    const long long ns = N - nb < kSlab ? N - nb : kSlab;
+    transpose_mask_kernel<<<dim3((unsigned)gx, (unsigned)((ns + 63) / 64)), 256, 0, (cudaStream_t)stream>>>(
+        src_dev + nb * src_ld, src_ld, T, ns, ld, fail_dev + nb, accumulate);
+    KSA_LAUNCH_CHECK("transpose_mask_kernel");
+  }
   return KSA_OK;
 }

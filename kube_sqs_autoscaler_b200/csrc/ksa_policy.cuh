@@ -31,9 +31,9 @@ static_assert(sizeof(ksa_policy_k) == 48, "ksa_policy_k is part of the sweep ABI
 
 // A call replays at most KSA_MAX_CHUNK_TICKS ticks; longer traces are chunked by the caller
 // (the carry state makes that exact). Inside a call, ticks are numbered i = 1..T.
-#define KSA_MAX_CHUNK_TICKS (1ll << 30)
+#define KSA_MAX_CHUNK_TICKS ((1ll << 30) - 64)
 // Cool-downs longer than a chunk behave, inside the chunk, like "blocked until the chunk ends".
-#define KSA_COOL_CAP ((1 << 30) + 1)
+#define KSA_COOL_CAP (1 << 30)
 
 // Chunk-local cool-down state of one direction: `s` = the first local tick at which the gate is
 // open again, so the gate is a single compare:   blocked at local tick i   <=>   i < s.
@@ -43,7 +43,9 @@ static_assert(sizeof(ksa_policy_k) == 48, "ksa_policy_k is part of the sweep ABI
 // Equivalence with the reference's `last.Add(cool).After(now)`: SURVEY.md §3.4 gives the tick form
 // `k - last < cool` with k = tick0 + i; for an inherited stamp that is i < cool - (tick0 - last),
 // and clamping the right-hand side into [0, c] does not change the comparison for
-// 1 <= i <= T <= 2^30 < KSA_COOL_CAP. All values stay below 2^31: i + c <= 2^30 + 2^30 + 1.
+// 1 <= i <= T <= KSA_MAX_CHUNK_TICKS < KSA_COOL_CAP. All values fit int32: a stamp is at most
+// i + c <= (2^30 - 64) + 2^30 = 2^31 - 64 (the kernels that number ticks per group of D add at most
+// 2D <= 32 to c instead of i, and go down to -(T + 2D) > -2^31).
 __device__ __forceinline__ int ksa_local_stamp(long long cool, int c, long long tick0, long long last) {
   long long s = cool - (tick0 - last);
   s = s < 0 ? 0 : s;

@@ -786,7 +786,7 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
     return ksa_fail(KSA_EINVAL, "NULL pointer inside ksa_state");
   if (mode == MODE_SUMMARY && !summary_dev) return ksa_fail(KSA_EINVAL, "NULL summary_dev");
   if (T < 1 || T > KSA_MAX_CHUNK_TICKS)
-    return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]; chunk longer traces", (long long)T);
+    return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30 - 64]; chunk longer traces", (long long)T);
   if (N < 1 || N > 0x7fffffffll) return ksa_fail(KSA_EINVAL, "N=%lld outside [1, 2^31-1]", (long long)N);
   if (ld < N) return ksa_fail(KSA_EINVAL, "ld=%lld < N=%lld", (long long)ld, (long long)N);
   if (tick0 < 0) return ksa_fail(KSA_EINVAL, "tick0=%lld < 0", (long long)tick0);

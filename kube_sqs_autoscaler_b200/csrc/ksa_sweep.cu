@@ -541,7 +541,7 @@ extern "C" int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* pol
   if (!policies || !policies_dev || !depth_dev || !replicas0_dev || !summary_dev)
     return ksa_fail(KSA_EINVAL, "NULL pointer");
   if (P < 1 || P > (1 << 20)) return ksa_fail(KSA_EINVAL, "P=%d outside [1, 2^20]", P);
-  if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]", (long long)T);
+  if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30 - 64]", (long long)T);
   if (N < 1 || N > 0x7fffffffll || ld < N) return ksa_fail(KSA_EINVAL, "bad N=%lld / ld=%lld", (long long)N, (long long)ld);
   if (A < 1 || A > KSA_MAX_ATTRS) return ksa_fail(KSA_EINVAL, "A=%d outside [1,3]", A);
   cudaStream_t st = (cudaStream_t)stream;
@@ -596,7 +596,7 @@ extern "C" int ksa_replay_sweep_static(const ksa_policy* policies, int32_t P,
                     "P=%d exceeds the built-in policy table of ksa_replay_sweep_static (%d policies); "
                     "split the grid or use ksa_replay_sweep with a caller-provided table",
                     P, KSA_SWEEP_STATIC_MAX_POLICIES);
-  if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30]", (long long)T);
+  if (T < 1 || T > KSA_MAX_CHUNK_TICKS) return ksa_fail(KSA_EINVAL, "T=%lld outside [1, 2^30 - 64]", (long long)T);
   if (N < 1 || N > 0x7fffffffll || ld < N) return ksa_fail(KSA_EINVAL, "bad N=%lld / ld=%lld", (long long)N, (long long)ld);
 
   int device = -1;
@@ -732,6 +732,7 @@ extern "C" int ksa_sweep_reduce(const ksa_summary* summary_dev, int32_t P, int64
   sweep_reduce_kernel<W, U><<<(unsigned)blocks, W * 32, 0, (cudaStream_t)stream>>>(                       \
       summary_dev, P, N, *cost, (long long*)policy_cost_dev, best_policy_dev, (long long*)best_cost_dev)
   switch (shape) {
+#ifdef KSA_TUNING_VARIANTS
     case 1: KSA_RED(16, 8); break;
     case 2: KSA_RED(32, 4); break;
     case 3: KSA_RED(32, 8); break;
@@ -739,6 +740,7 @@ extern "C" int ksa_sweep_reduce(const ksa_summary* summary_dev, int32_t P, int64
     case 5: KSA_RED(16, 4); break;
     case 6: KSA_RED(32, 1); break;
     case 7: KSA_RED(32, 3); break;
+#endif
     default: KSA_RED(32, 2); break;  // 0.184 ms on 4096 x 4096 records; (16, 4): 0.244 ms (profiles/r01_config4_reduce.txt)
   }
 #undef KSA_RED

@@ -112,6 +112,26 @@ def test_transpose_kernel_matches_numpy(engine, dtype, T, N, A, a):
 
 
 @pytest.mark.gpu
+def test_ingest_takes_every_trace_count_the_replay_takes(engine):
+    """The transposes put the trace axis on gridDim.y (65535 tiles); more traces than one launch
+    holds go in slabs. One more than a slab of the int32 tile (64 ticks x 128 traces), of the int64
+    tile (256 x 32) and of the mask tile (64 x 64), a few ticks each: equal to numpy."""
+    import torch
+
+    T = 3
+    for dtype, N in ((np.int32, 65535 * 128 + 77), (np.int64, 65535 * 32 + 5)):
+        src = (np.arange(N * T, dtype=np.int64) * 2654435761 % 100003 - 50000).astype(dtype).reshape(N, T)
+        got = engine.ingest_transpose(torch.from_numpy(src).to(engine.dev), T, N, 1, 0, N)
+        want = torch.from_numpy(src).to(engine.dev).t().to(torch.int64)
+        assert bool(torch.equal(got[:, 0, :], want)), dtype
+        del got, want
+    N = 65535 * 64 + 9
+    m = (np.arange(N * T, dtype=np.int64) * 40503 % 251 % 8).astype(np.uint8).reshape(N, T)
+    got = engine.ingest_transpose_mask(torch.from_numpy(m).to(engine.dev), T, N, N)
+    assert bool(torch.equal(got, torch.from_numpy(m).to(engine.dev).t()))
+
+
+@pytest.mark.gpu
 def test_recorded_strings_to_trajectory(engine):
     """The whole ingest chain on a small recording: per-queue histories of attribute STRINGS (what
     SQS returns, sqs/sqs.go:58) -> Atoi decode -> transpose to tick-major -> replay with the parse
