@@ -807,6 +807,16 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   args.summary = summary_dev;
 
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
+  // Trace counts far below what fills the GPU: chunks of the time axis in parallel (ksa_timepar.cu;
+  // same results). Only the library default takes this path; an explicit variant gets its kernel.
+  if (mode == MODE_FULL && !faults && replicas_dev && events_dev && want < 0) {
+    const int K = ksa_timepar_chunks(T, N);
+    if (K >= 2) {
+      rc = ksa_timepar_replay_full(args.pk, depth_dev, T, A, N, ld, tick0, state, replicas_dev, events_dev, K,
+                                   (cudaStream_t)stream);
+      if (rc <= 0) return rc;  // done, or an error; 1 = the scratch is busy: plain kernels below
+    }
+  }
   const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
   const int default_summary = ordered ? kDefaultSummaryOrdered : kDefaultSummary;
   // Full mode: 8 traces per thread need ~600k traces to fill 148 SMs; below that the kernel is bound

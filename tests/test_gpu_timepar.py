@@ -1,0 +1,119 @@
+"""Full-trajectory replay with the time axis cut into chunks (csrc/ksa_timepar.cu): the path
+ksa_replay_full takes by itself when the traces are too few to fill the GPU. It must give exactly
+what the sequential replay gives whatever the number of chunks and whether or not the speculative
+chunks ever converge to the true trajectory, so the chunk count is forced here
+(KSA_TIMEPAR_CHUNKS) on small cases: random adversarial policies, and traces built never to
+converge. Everything against the CPU oracle, through the C ABI, bit for bit."""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import pytest
+
+import kube_sqs_autoscaler_b200 as ksa
+from tests import oracle_lib
+from tests.helpers import S
+from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
+
+pytestmark = pytest.mark.gpu
+
+
+def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label):
+    """Replay with `chunks` forced (None = the library's own choice); returns the launches it took."""
+    import torch
+
+    ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st)
+    d = torch.from_numpy(np.ascontiguousarray(depth)).to(engine.dev)
+    if chunks is None:
+        os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+    else:
+        os.environ["KSA_TIMEPAR_CHUNKS"] = str(chunks)
+    try:
+        state = engine.state_from_host(*st)
+        engine.launch_count()
+        r, e = engine.replay_full(pol, d, T, A, N, ld, tick0, state)
+        launches = engine.launch_count()
+        r, e = r.cpu().numpy(), e.cpu().numpy()
+    finally:
+        os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+    where = np.argwhere(r[:, :N] != ref.replicas[:, :N])
+    assert where.size == 0, f"{label}: replicas differ first at (tick, trace) {where[0]} of {where.shape[0]}"
+    assert np.array_equal(e[:, :N], ref.events[:, :N]), f"{label}: events differ"
+    assert np.array_equal(state.replicas.cpu().numpy(), ref.state_replicas), f"{label}: carry replicas differ"
+    assert np.array_equal(state.last_up.cpu().numpy(), ref.state_last_up), f"{label}: last_up differs"
+    assert np.array_equal(state.last_down.cpu().numpy(), ref.state_last_down), f"{label}: last_down differs"
+    return launches
+
+
+@pytest.mark.parametrize("A", [1, 2, 3])
+def test_random_policies_any_chunk_count(engine, A):
+    rng = np.random.default_rng(5150 + A)
+    for case in range(10):
+        pol = random_policy(rng, A)
+        T = int(rng.choice([40, 97, 260, 700]))
+        N = int(rng.choice([1, 33, 130, 1000]))
+        ld = (N + 15) // 16 * 16 if case % 2 else N
+        tick0 = int(rng.choice([0, 0, 23, 10**6, 2**40]))
+        depth = adversarial_depth(rng, T, A, ld, pol)
+        st = random_state(rng, N, tick0)
+        for chunks in (2, 3, 5, 16):
+            if (T + chunks - 1) // chunks < 16:
+                continue
+            took = run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks,
+                                 f"A={A} case {case} T={T} N={N} chunks={chunks} {pol}")
+            assert took == 3, "the forced chunk count was not used"
+
+
+def test_traces_that_never_converge(engine):
+    """The speculative chunks start from the trace's initial replica count with both gates open.
+    Cases where that never meets the true trajectory: replicas outside [min, max] with the one-sided
+    clamps (Q4: an r0 above max only comes down by down-events), min > max, cool-downs longer than
+    the whole call (the true gates stay shut, the guessed ones are open), a constant depth over the
+    threshold (scale calls every cool-down period, the phase set by history), and wrapping steps."""
+    rng = np.random.default_rng(99)
+    T, N = 400, 77
+    cases = [
+        ("r0 outside the clamp", ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=0, max_pods=5, min_pods=1),
+         rng.integers(0, 400, size=(T, 1, N)), rng.integers(-40, 60, size=N)),
+        ("min above max", ksa.Policy(attr_mask=1, max_pods=2, min_pods=9, scale_up_cool_down=5 * S, scale_down_cool_down=0),
+         rng.integers(0, 400, size=(T, 1, N)), rng.integers(-3, 14, size=N)),
+        ("cool-downs longer than the call", ksa.Policy(attr_mask=1, scale_up_cool_down=10**6 * S, scale_down_cool_down=10**5 * S),
+         rng.integers(0, 400, size=(T, 1, N)), rng.integers(1, 6, size=N)),
+        ("constant load, phase from history", ksa.Policy(attr_mask=1, scale_up_cool_down=35 * S, scale_down_cool_down=55 * S,
+                                                          max_pods=1000, min_pods=-1000),
+         np.concatenate([np.full((T // 2, 1, N), 500), np.full((T - T // 2, 1, N), 0)]), rng.integers(1, 6, size=N)),
+        ("wrapping steps", ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=5 * S, max_pods=2**31 - 1,
+                                      min_pods=-(2**31), scale_up_pods=2**30 + 12345, scale_down_pods=2**29 + 7),
+         rng.integers(0, 400, size=(T, 1, N)), rng.integers(-5, 9, size=N)),
+    ]
+    for name, pol, depth, r0 in cases:
+        depth = np.ascontiguousarray(depth, dtype=np.int64)
+        for tick0, ju, jd in ((0, 0, 0), (1000, 998, 1000)):
+            st = (r0.astype(np.int32), np.full(N, ju, dtype=np.int64), np.full(N, jd, dtype=np.int64))
+            for chunks in (2, 7, 25):
+                run_and_check(engine, pol, depth, T, 1, N, N, tick0, st, chunks, f"{name} tick0={tick0} chunks={chunks}")
+
+
+def test_every_checkpoint_and_the_automatic_choice(engine):
+    """Chunks long enough to hold all four checkpoints (32, 128, 512, 2048 ticks), with cool-downs that
+    keep the speculative and the true gates apart for hundreds of ticks, so that convergence happens
+    at the late checkpoints or not at all; then the library's own choice of chunks for a small block
+    (N = 4096 x T = 8192 takes the time-parallel path: three launches) and a block it must leave to
+    the plain kernels (too few ticks)."""
+    rng = np.random.default_rng(4)
+    N, T = 64, 6200
+    for cu, cd in ((10, 30), (700, 90), (3000, 2500)):
+        pol = ksa.Policy(attr_mask=1, scale_up_cool_down=cu * 5 * S, scale_down_cool_down=cd * 5 * S, max_pods=40, min_pods=0)
+        depth = rng.integers(0, 400, size=(T, 1, N), dtype=np.int64)
+        depth[rng.integers(0, 3, size=depth.shape) == 0] = 0
+        st = (rng.integers(0, 41, size=N).astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+        for chunks in (2, 3):
+            assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"cool {cu}/{cd} chunks={chunks}") == 3
+    N, T = 4096, 8192
+    pol = ksa.Policy(attr_mask=1)
+    gen = ksa.GenParams(seed=11)
+    depth = oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, N)
+    st = oracle_lib.fresh_state(gen.seed, 0, N, 1, 5)
+    assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, None, "automatic, 4096 x 8192") == 3
+    assert run_and_check(engine, pol, depth[:512], 512, 1, N, N, 0, st, None, "automatic, 4096 x 512") <= 2
