@@ -32,8 +32,8 @@
 // scale call of the true trajectory (a pass-1 stamp only counts if it was taken after the tick
 // from which pass 1's trajectory is the true one).
 //
-// Scratch: one 80-byte record per (trace, chunk) in a fixed device array of the library image
-// (kMaxChunks records, 20 MB per GPU), so the entry point still allocates nothing. One time-parallel
+// Scratch: one 128-byte record per (trace, chunk) in a fixed device array of the library image
+// (kMaxChunks records, 32 MB per GPU), so the entry point still allocates nothing. One time-parallel
 // replay per device at a time: a call that finds the scratch busy takes the plain kernels instead.
 #include "ksa_internal.h"
 
@@ -43,8 +43,8 @@
 namespace {
 
 constexpr int kMaxChunks = 1 << 18;   // records: traces x chunks of one call
-constexpr int kChecks = 4;
-__host__ __device__ constexpr int check_tick(int j) { return j == 0 ? 32 : j == 1 ? 128 : j == 2 ? 512 : 2048; }
+constexpr int kChecks = 8;
+__host__ __device__ constexpr int check_tick(int j) { return 32 << j; }  // 32, 64, ..., 4096 ticks into the chunk
 constexpr int D = 8;                  // ring depth of pass 1 (the checkpoint ticks are multiples of it)
 constexpr int BLOCK = 128;
 
@@ -58,7 +58,7 @@ struct TpChunk {
   TpState ck[kChecks];  // pass 1: state after chunk tick check_tick(j), if the chunk has it
   int pad;
 };
-static_assert(sizeof(TpChunk) == 80, "scratch record");
+static_assert(sizeof(TpChunk) == 128, "scratch record");
 
 static __device__ __align__(256) TpChunk g_tp_scratch[kMaxChunks];
 
@@ -142,9 +142,8 @@ __global__ void __launch_bounds__(BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4)) tp_spec_
 #pragma unroll
     for (int j = 0; j < D; ++j) tick(t + j, j, true);
     const int done = t + D;  // ticks of the chunk replayed so far
-#pragma unroll
-    for (int q = 0; q < kChecks; ++q)
-      if (done == check_tick(q)) rec->ck[q] = TpState{s.r, s.su, s.sd};
+    if ((done & (done - 1)) == 0 && done >= check_tick(0) && done <= check_tick(kChecks - 1))  // 32, 64, ..., 4096
+      rec->ck[31 - __clz(done) - 5] = TpState{s.r, s.su, s.sd};
   }
 #pragma unroll 1
   for (; t < len; t += D) {
@@ -156,8 +155,10 @@ __global__ void __launch_bounds__(BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4)) tp_spec_
   rec->status = 0;
 }
 
-// Replay ticks [from, len) of chunk (t0, len) from state s, plainly, rewriting the outputs. Stops after
-// a checkpoint tick j >= first_check whose pass-1 state has the same future; returns that j, or -1.
+// Replay chunk (t0, len) from state s, rewriting the outputs, in groups of D ticks with the depths
+// of the next group already in flight (a plain loop waits a memory latency per tick). Stops after a
+// checkpoint tick j >= first_check whose pass-1 state has the same future; returns that j, or -1
+// when the chunk ends first.
 template <int A>
 __device__ int tp_replay_until_match(const TpArgs& a, const ksa_step_consts& c, long long n, int t0, int len,
                                      const TpChunk* rec, int first_check, ksa_trace_regs& s) {
@@ -165,16 +166,25 @@ __device__ int tp_replay_until_match(const TpArgs& a, const ksa_step_consts& c, 
   const long long* dp = a.depth + (long long)t0 * row + n;
   int* rp = a.replicas + (long long)t0 * a.ld + n;
   unsigned char* ep = a.events + (long long)t0 * a.ld + n;
-  int next = first_check;
-  while (next < kChecks && !has_check(len, next)) next = kChecks;  // checkpoints are increasing: none further
-  for (int tt = 0; tt < len; ++tt) {
-    const long long msgs = load_sum(dp + (long long)tt * row, a.ld, A);
-    const unsigned ev = ksa_step(c, msgs, t0 + tt + 1, s);
-    rp[(long long)tt * a.ld] = s.r;
-    ep[(long long)tt * a.ld] = (unsigned char)ev;
-    if (next < kChecks && tt + 1 == check_tick(next)) {
+  int next = (first_check < kChecks && has_check(len, first_check)) ? first_check : kChecks;
+  long long buf[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) buf[j] = j < len ? load_sum(dp + (long long)j * row, a.ld, A) : 0;
+  for (int t = 0; t < len; t += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const int tt = t + j;
+      if (tt < len) {
+        const long long msgs = buf[j];
+        if (tt + D < len) buf[j] = load_sum(dp + (long long)(tt + D) * row, a.ld, A);
+        const unsigned ev = ksa_step(c, msgs, t0 + tt + 1, s);
+        rp[(long long)tt * a.ld] = s.r;
+        ep[(long long)tt * a.ld] = (unsigned char)ev;
+      }
+    }
+    if (next < kChecks && t + D == check_tick(next)) {  // checkpoint ticks are multiples of D
       const TpState mine{s.r, s.su, s.sd};
-      if (same_future(mine, rec->ck[next], t0 + tt + 1)) return next;
+      if (same_future(mine, rec->ck[next], t0 + t + D)) return next;
       ++next;
       if (next < kChecks && !has_check(len, next)) next = kChecks;
     }

@@ -37,41 +37,91 @@ void check(int rc, const char* what) {
   if (rc != KSA_OK) die(std::string(what) + ": " + ksa_last_error());
 }
 
-// time.ParseDuration (what flag.DurationVar uses, main.go:83-85): [+-] then (number unit)+,
-// units ns us µs ms s m h; "0" alone is allowed.
+// time.ParseDuration (what flag.DurationVar uses, main.go:83-85), restated from Go's algorithm:
+//   [-+]?([0-9]*(\.[0-9]*)?[a-z]+)+   units ns us µs μs ms s m h; "0" alone is allowed.
+// Integer arithmetic in uint64 with Go's overflow checks (leadingInt: a number above 2^63 is an
+// error; value * unit and the running total must stay <= 2^63, and only a negative duration may
+// be exactly 2^63 ns); the fractional part goes through float64 exactly as in Go:
+// uint64(float64(f) * (float64(unit) / scale)), f and scale from leadingFraction, which stops
+// taking digits once f would pass 2^63 - 1.
 bool parse_duration(const std::string& text, int64_t* out) {
+  const uint64_t kLimit = 1ull << 63;
   size_t p = 0;
+  const size_t n = text.size();
   bool neg = false;
-  if (p < text.size() && (text[p] == '+' || text[p] == '-')) neg = text[p++] == '-';
-  if (text.substr(p) == "0") {
+  if (p < n && (text[p] == '+' || text[p] == '-')) neg = text[p++] == '-';
+  if (text.compare(p, std::string::npos, "0") == 0) {
     *out = 0;
     return true;
   }
-  if (p >= text.size()) return false;
-  long double total = 0;
-  while (p < text.size()) {
-    size_t q = p;
-    while (q < text.size() && (std::isdigit((unsigned char)text[q]) || text[q] == '.')) ++q;
-    if (q == p) return false;
-    const std::string num = text.substr(p, q - p);
-    if (num == "." || std::count(num.begin(), num.end(), '.') > 1) return false;
-    size_t u = q;
-    while (u < text.size() && !std::isdigit((unsigned char)text[u]) && text[u] != '.') ++u;
-    const std::string unit = text.substr(q, u - q);
-    long double scale;
-    if (unit == "ns") scale = 1;
-    else if (unit == "us" || unit == "\xC2\xB5s" || unit == "\xCE\xBCs") scale = 1e3L;
-    else if (unit == "ms") scale = 1e6L;
-    else if (unit == "s") scale = 1e9L;
-    else if (unit == "m") scale = 60e9L;
-    else if (unit == "h") scale = 3600e9L;
+  if (p >= n) return false;
+  uint64_t d = 0;
+  while (p < n) {
+    if (!(text[p] == '.' || (text[p] >= '0' && text[p] <= '9'))) return false;
+    // leadingInt
+    uint64_t v = 0;
+    const size_t int_begin = p;
+    while (p < n && text[p] >= '0' && text[p] <= '9') {
+      if (v > kLimit / 10) return false;
+      v = v * 10 + (uint64_t)(text[p] - '0');
+      if (v > kLimit) return false;
+      ++p;
+    }
+    const bool pre = p != int_begin;
+    // leadingFraction
+    uint64_t f = 0;
+    double scale = 1;
+    bool post = false;
+    if (p < n && text[p] == '.') {
+      ++p;
+      const size_t frac_begin = p;
+      bool overflow = false;
+      while (p < n && text[p] >= '0' && text[p] <= '9') {
+        if (!overflow) {
+          if (f > (kLimit - 1) / 10) {
+            overflow = true;
+          } else {
+            const uint64_t y = f * 10 + (uint64_t)(text[p] - '0');
+            if (y > kLimit) {
+              overflow = true;
+            } else {
+              f = y;
+              scale *= 10;
+            }
+          }
+        }
+        ++p;
+      }
+      post = p != frac_begin;
+    }
+    if (!pre && !post) return false;  // no digits (e.g. ".s")
+    const size_t unit_begin = p;
+    while (p < n && text[p] != '.' && !(text[p] >= '0' && text[p] <= '9')) ++p;
+    if (p == unit_begin) return false;  // missing unit
+    const std::string unit = text.substr(unit_begin, p - unit_begin);
+    uint64_t mult;
+    if (unit == "ns") mult = 1;
+    else if (unit == "us" || unit == "\xC2\xB5s" || unit == "\xCE\xBCs") mult = 1000ull;  // U+00B5, U+03BC
+    else if (unit == "ms") mult = 1000000ull;
+    else if (unit == "s") mult = 1000000000ull;
+    else if (unit == "m") mult = 60ull * 1000000000ull;
+    else if (unit == "h") mult = 3600ull * 1000000000ull;
     else return false;
-    total += std::strtold(num.c_str(), nullptr) * scale;
-    p = u;
+    if (v > kLimit / mult) return false;
+    v *= mult;
+    if (f > 0) {
+      v += (uint64_t)((double)f * ((double)mult / scale));
+      if (v > kLimit) return false;
+    }
+    d += v;
+    if (d > kLimit) return false;
   }
-  if (total > 9223372036854775807.0L) return false;
-  *out = (int64_t)total;
-  if (neg) *out = -*out;
+  if (neg) {
+    *out = (int64_t)(0ull - d);  // 2^63 becomes math.MinInt64, as in Go
+    return true;
+  }
+  if (d > kLimit - 1) return false;
+  *out = (int64_t)d;
   return true;
 }
 
@@ -173,7 +223,10 @@ Options parse(int argc, char** argv) {
       }
       return out->front();
     };
-    if (k == "poll-period") o.policy.poll_period_ns = as_dur("poll-period");
+    if (k == "parse-duration") {  // print what time.ParseDuration gives for the value and stop (no GPU needed)
+      std::printf("%lld\n", (long long)as_dur("parse-duration"));
+      std::exit(0);
+    } else if (k == "poll-period") o.policy.poll_period_ns = as_dur("poll-period");
     else if (k == "scale-down-cool-down") o.policy.scale_down_cool_down_ns = as_list("scale-down-cool-down", true, &o.down_cool);
     else if (k == "scale-up-cool-down") o.policy.scale_up_cool_down_ns = as_list("scale-up-cool-down", true, &o.up_cool);
     else if (k == "scale-up-messages") o.policy.scale_up_messages = as_list("scale-up-messages", false, &o.up_msgs);

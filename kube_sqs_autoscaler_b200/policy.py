@@ -23,42 +23,83 @@ DEFAULT_ATTRIBUTE_NAMES = (  # sqs/sqs.go:28-32, main.go:28
 
 _UNIT_NS = {"ns": 1, "us": 1_000, "µs": 1_000, "μs": 1_000, "ms": 1_000_000, "s": 1_000_000_000,
             "m": 60_000_000_000, "h": 3_600_000_000_000}
-_DUR_PART = re.compile(r"(\d+\.?\d*|\.\d+)(ns|us|µs|μs|ms|s|m|h)")
-_I64_MAX = (1 << 63) - 1
+_LIMIT = 1 << 63
 
 
 def parse_duration(text: str) -> int:
-    """Go `time.ParseDuration` → nanoseconds (what flag.DurationVar does, main.go:83-85).
-
-    Accepts an optional sign, then one or more decimal numbers each with a unit suffix
-    ("300ms", "-1.5h", "2h45m"); "0" is allowed without a unit. Raises ValueError otherwise.
+    """Go `time.ParseDuration` → nanoseconds (what flag.DurationVar does, main.go:83-85), restated
+    from Go's algorithm: `[-+]?([0-9]*(\\.[0-9]*)?[a-z]+)+`, "0" allowed without a unit, no
+    surrounding white space. Integer arithmetic with Go's overflow checks (a number above 2^63, a
+    product or a total above 2^63 is an error; only a negative duration may be exactly 2^63 ns);
+    the fraction goes through float64 as in Go: `uint64(float64(f) * (float64(unit) / scale))`.
+    The C++ host (host/ksa_replay_cli.cpp) has the same function; tests compare the two.
+    Raises ValueError otherwise.
     """
-    s = text.strip()
-    if not s:
-        raise ValueError(f"time: invalid duration {text!r}")
-    sign = 1
-    if s[0] in "+-":
-        sign = -1 if s[0] == "-" else 1
+    bad = ValueError(f"time: invalid duration {text!r}")
+    s = text
+    neg = False
+    if s[:1] in ("+", "-"):
+        neg = s[0] == "-"
         s = s[1:]
     if s == "0":
         return 0
     if not s:
-        raise ValueError(f"time: invalid duration {text!r}")
-    pos, total = 0, 0
-    while pos < len(s):
-        m = _DUR_PART.match(s, pos)
-        if not m:
-            raise ValueError(f"time: invalid duration {text!r}")
-        num, unit = m.group(1), m.group(2)
-        whole, _, frac = num.partition(".")
-        scale = _UNIT_NS[unit]
-        total += int(whole or "0") * scale
-        if frac:
-            total += int(frac) * scale // (10 ** len(frac))  # Go truncates the fraction too
-        pos = m.end()
-    if total > _I64_MAX:
-        raise ValueError(f"time: invalid duration {text!r}")
-    return sign * total
+        raise bad
+    d = 0
+    while s:
+        if not (s[0] == "." or s[0].isascii() and s[0].isdigit()):
+            raise bad
+        i, v = 0, 0
+        while i < len(s) and s[i].isascii() and s[i].isdigit():  # leadingInt
+            if v > _LIMIT // 10:
+                raise bad
+            v = v * 10 + int(s[i])
+            if v > _LIMIT:
+                raise bad
+            i += 1
+        pre = i > 0
+        s = s[i:]
+        f, scale, post = 0, 1.0, False
+        if s[:1] == ".":  # leadingFraction
+            s = s[1:]
+            i, overflow = 0, False
+            while i < len(s) and s[i].isascii() and s[i].isdigit():
+                if not overflow:
+                    if f > (_LIMIT - 1) // 10:
+                        overflow = True
+                    else:
+                        y = f * 10 + int(s[i])
+                        if y > _LIMIT:
+                            overflow = True
+                        else:
+                            f, scale = y, scale * 10
+                i += 1
+            post = i > 0
+            s = s[i:]
+        if not pre and not post:
+            raise bad
+        i = 0
+        while i < len(s) and s[i] != "." and not (s[i].isascii() and s[i].isdigit()):
+            i += 1
+        if i == 0:
+            raise bad
+        unit = _UNIT_NS.get(s[:i])
+        s = s[i:]
+        if unit is None or v > _LIMIT // unit:
+            raise bad
+        v *= unit
+        if f > 0:
+            v += int(float(f) * (float(unit) / scale))
+            if v > _LIMIT:
+                raise bad
+        d += v
+        if d > _LIMIT:
+            raise bad
+    if neg:
+        return -d
+    if d > _LIMIT - 1:
+        raise bad
+    return d
 
 
 def attr_mask_from_names(names: str) -> int:
