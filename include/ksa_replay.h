@@ -17,7 +17,11 @@
  *    void* (NULL = legacy default stream). All launches are asynchronous on that stream.
  *  - Every function returns 0 (KSA_OK) or a negative KSA_E* code; ksa_last_error() returns the
  *    thread-local message of the last failure. Nothing aborts, nothing falls back to the CPU.
- *  - The caller owns every buffer. The replay entry points allocate nothing.
+ *  - The caller owns every buffer. The replay entry points allocate nothing, on the device or on
+ *    the host heap (ksa_dev_alloc / ksa_host_alloc and ksa_pipeline_create are the allocating
+ *    helpers). Two fixed arrays live in the library's device image on every GPU that loads it:
+ *    the policy table of ksa_replay_sweep_static (192 KB) and the scratch records of the
+ *    time-parallel path of ksa_replay_full (32 MB, see there).
  *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
  *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
  *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.
@@ -201,6 +205,13 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  *   events_dev   [T][ld] uint8  KSA_EV_* bits of each tick        (may be NULL: not written)
  * Limits: 1 <= T <= 2^30 - 64 per call (chunk longer traces: the carry state makes that exact),
  * 1 <= N <= 2^31-1, N <= ld.
+ * Few traces, many ticks (N <= 98304, T >= 4096, both outputs wanted): one thread per trace cannot
+ * fill the GPU, so the library cuts the time axis into chunks that are replayed in parallel from
+ * guessed states and then stitched exactly (csrc/ksa_timepar.cu; results are identical, the
+ * trajectory and the carry state bit for bit). That path keeps its per-chunk records in a fixed
+ * scratch array inside the library, so only one such call runs per GPU at a time: a call that
+ * finds the scratch in use by a call on another stream, or a stream that is being captured, takes
+ * the one-thread-per-trace kernels instead (same results, slower).
  */
 int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
                     int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
@@ -228,8 +239,12 @@ int ksa_summary_clear(ksa_summary* summary_dev, int64_t N, void* stream);
  *                  skipped), event bit KSA_EV_UP_FAILED.
  *   KSA_FAIL_DOWN  ScaleDown failed (main.go:71-74): likewise; an up-scale earlier in the same tick
  *                  stands; event bit KSA_EV_DOWN_FAILED.
- * A failing Scale call fails whether or not the replica count is at its limit (the reference's
- * Get comes first, scale/scale.go:55,82). Algorithmic traffic: +1 byte per decision.
+ * KSA_FAIL_UP / KSA_FAIL_DOWN model a failure of the Get at the top of ScaleUp / ScaleDown
+ * (scale/scale.go:55-58, 82-85): the call fails whether or not the replica count is at its limit.
+ * A failing Update (scale/scale.go:72-75, 100-103) is the same thing away from the limit and cannot
+ * happen at the limit (scale/scale.go:62-65, 89-92 return before it), so a recording that
+ * distinguishes the two should not set the bit for an Update failure at the limit.
+ * Algorithmic traffic: +1 byte per decision.
  */
 int ksa_replay_full_faults(const ksa_policy* policy, const int64_t* depth_dev,
                            const uint8_t* fail_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
@@ -258,6 +273,10 @@ int ksa_gen_faults(uint64_t seed, uint32_t poll_log2, uint32_t up_log2, uint32_t
  *   policies_dev  [P] device scratch for the kernel-side policy table, sizeof(ksa_policy_k)=48 B
  *                 each (caller-allocated: P * 48 bytes)
  *   summary_dev   [P][N] ksa_summary, overwritten
+ * The table is written by small kernels on `stream` that carry the converted records in their
+ * parameters (no copy from a host buffer is left pending when the call returns). Policies are
+ * replayed in register tiles of 4 consecutive policies; a tile whose policies share both message
+ * thresholds (the usual layout of a parameter grid: thresholds vary slowest) runs fastest.
  */
 int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* policies_dev,
                      const int64_t* depth_dev, int64_t T, int32_t A, int64_t N, int64_t ld,
@@ -284,8 +303,8 @@ int ksa_replay_sweep(const ksa_policy* policies, int32_t P, void* policies_dev,
  *  - The first call on each device looks up the array's device address (once, with that device
  *    current). Make that first call before starting any stream capture on the device.
  *  - All calls on one device share the one array. It keeps the previous call's records; every call
- *    rewrites records [0, P) before its kernel reads them and nothing beyond P-1 is read, so stale
- *    contents are harmless. But two calls whose work overlaps on the same GPU (different streams,
+ *    rewrites records [0, P) (kernels on `stream`, ahead of the sweep kernel) and nothing beyond
+ *    P-1 is read, so stale contents are harmless. But two calls whose work overlaps on the same GPU (different streams,
  *    or different host threads) race on the table: run them on one stream, or wait for the first
  *    to finish. Calls on different GPUs do not interfere.
  */
@@ -431,8 +450,11 @@ int ksa_pipeline_replay_faults(ksa_pipeline* p, const ksa_policy* policy, const 
 int ksa_set_variant(int32_t full_variant, int32_t summary_variant);
 
 /* Name of a variant ("V4_D4_H1_B128x7": traces per thread, prefetch depth, load hint, block x
- * min-blocks-per-SM), or NULL if there is no such id. mode 0 = full, 1 = summary; id 0 = the scalar
- * kernel, id -1 = the library default. */
+ * min-blocks-per-SM), or NULL if this build of the library has no such id. mode 0 = full, 1 =
+ * summary, 2 / 3 = the same for the *_faults entry points (ids of KSA_FAULTS_VARIANT), 4 = launch
+ * shapes of the sweep (ids of KSA_SWEEP_VARIANT); id 0 = the scalar kernel, id -1 = the library
+ * default. The product build carries the kernels the library selects by itself; the tuning build
+ * (-DKSA_TUNING_VARIANTS, `python __graft_entry__.py --tuning`) adds every point that was measured. */
 const char* ksa_variant_name(int32_t mode, int32_t id);
 
 /* Number of kernel launches issued by this library on the calling thread since the last call

@@ -747,6 +747,12 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(15, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(16, MODE_SUMMARY, 1, 8, HINT_NA, 9, 256, 4, 1, 4, 256, 4, 1, 3, 256, 4),
     KSA_VARIANT(17, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
+    KSA_VARIANT(22, MODE_SUMMARY, 1, 16, HINT_NA, 9, 128, 5, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(23, MODE_SUMMARY, 1, 24, HINT_NA, 9, 128, 4, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 7, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(25, MODE_SUMMARY, 1, 12, HINT_NA, 9, 256, 3, 1, 4, 256, 3, 1, 3, 256, 3),
+    KSA_VARIANT(26, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 5, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(27, MODE_SUMMARY, 1, 16, HINT_NA, 9, 128, 4, 1, 4, 128, 6, 1, 3, 128, 6),
 #endif
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak

@@ -80,6 +80,17 @@ def test_static_sweep_matches_sweep_on_two_calls_in_a_row(engine):
         assert torch.equal(out_static, out_ref), f"call {call + 1}: static sweep differs from ksa_replay_sweep"
         got = out_static.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(P, N)
         assert got["up_applied"].sum() > 0 and got["down_applied"].sum() > 0 and got["up_cool"].sum() > 0
+        if name == "second":
+            # and directly against the CPU oracle, policy by policy (the sibling entry point is
+            # oracle-tested on other grids; this makes the check of the static one first-hand)
+            from tests import oracle_lib
+
+            d_host = depth.cpu().numpy()
+            st = (r0.cpu().numpy(), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+            pols = second
+            for i, pol in enumerate(pols):
+                ref = oracle_lib.replay(pol.to_c(), d_host, T, 1, N, N, 0, *st, want_full=False, want_summary=True)
+                assert got[i].tobytes() == ref.summary.tobytes(), f"static sweep, policy {i}: differs from the oracle"
 
 
 def test_static_sweep_rejects_a_grid_larger_than_its_table(engine):
