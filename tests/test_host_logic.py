@@ -26,10 +26,47 @@ def test_parse_duration_go_syntax(text, ns):
     assert parse_duration(text) == ns
 
 
-@pytest.mark.parametrize("text", ["", "5", "s", "1.s.", "5 s", "1d", "--1s", "9223372036854775808ns"])
+REJECTED_DURATIONS = ["", "5", "s", "1.s.", "5 s", " 5s", "5s ", "1d", "--1s", "+", "-", ".", ".s", "1..5s", "1e3s", "５s",
+                      "9223372036854775808ns", "9223372036854775807us", "2562048h", "3000000h", "1h9223372036854775807ns",
+                      "99999999999999999999s", "0.9223372036854775808e1s"]
+ACCEPTED_DURATIONS = [
+    ("5s", 5 * S), ("2h45m", (2 * 3600 + 45 * 60) * S), ("-1.5h", -5400 * S), ("0", 0), ("+0", 0), ("-0", 0), ("1µs", 1000),
+    ("1μs", 1000), (".5s", S // 2), ("1.s", S), ("0.000000001s", 1), ("0.0000000001s", 0), ("1.0000000001s", S),
+    ("9223372036854775807ns", 2**63 - 1), ("-9223372036854775808ns", -(2**63)), ("2562047h47m16.854775807s", 2**63 - 1),
+    ("0.3333333333333333333333333333s", 333333333), ("1.999999999999999999999h", 7200 * S),  # Go's float64 fraction rounds up to 2h
+     ("100ms50us7ns", 100_050_007),
+    ("00000000000000000000005s", 5 * S),
+]
+
+
+@pytest.mark.parametrize("text", REJECTED_DURATIONS)
 def test_parse_duration_rejects(text):
     with pytest.raises(ValueError):
         parse_duration(text)
+
+
+@pytest.mark.parametrize("text,ns", ACCEPTED_DURATIONS)
+def test_parse_duration_edges(text, ns):
+    assert parse_duration(text) == ns
+
+
+def test_cli_parses_durations_like_the_python_host(built):
+    """The C++ host and the Python host restate time.ParseDuration separately (integer arithmetic with
+    Go's overflow checks, the fraction through float64 as Go does): same value or same rejection on
+    every case above. `ksa-replay --parse-duration=X` prints the nanoseconds and exits before any
+    CUDA call."""
+    import subprocess
+
+    def cli(text):
+        r = subprocess.run([built.CLI, f"--parse-duration={text}"], capture_output=True, text=True)
+        return r.returncode, r.stdout.strip(), r.stderr
+
+    for text, ns in ACCEPTED_DURATIONS + [("5m", 300 * S), ("300ms", 300_000_000), ("+3s", 3 * S)]:
+        rc, out, err = cli(text)
+        assert rc == 0 and int(out) == ns, (text, rc, out, err)
+    for text in REJECTED_DURATIONS:
+        rc, out, err = cli(text)
+        assert rc == 2 and "invalid duration" in err, (text, rc, out, err)
 
 
 def test_reference_command_line_parses_unchanged():
