@@ -728,9 +728,14 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(0, MODE_SUMMARY, 1, 8, HINT_NA, 4, 128, 4, 1, 4, 128, 4, 1, 4, 128, 4),
     // STEP 9 / 10: ksa_step_faults_fma3 (counts the failures itself); 9 = ordered thresholds only,
     // replay_common substitutes 10 otherwise
+    // ring of 12 ticks, 7 blocks of 128 per SM (73 registers): 6.45 ms on 2^20 x 4000 with failures =
+    // 0.906 of the measured copy peak; the ring of 8 at 8 blocks per SM (ids 10 / 11): 6.66 ms, 0.878
+    // (profiles/r02_faults_tune.txt). A = 2, 3 keep the shapes of 10 / 11.
+    KSA_VARIANT(28, MODE_SUMMARY, 1, 12, HINT_NA, 10, 128, 7, 1, 3, 128, 8, 1, 2, 128, 8),
+    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 7, 1, 3, 128, 8, 1, 2, 128, 8),
+#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(10, MODE_SUMMARY, 1, 8, HINT_NA, 10, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
     KSA_VARIANT(11, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 8, 1, 3, 128, 8, 1, 2, 128, 8),
-#ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(1, MODE_SUMMARY, 2, 4, HINT_NA, 4, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(2, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 7, 2, 3, 128, 6, 2, 2, 128, 6),
     KSA_VARIANT(3, MODE_SUMMARY, 2, 4, HINT_NA, 5, 128, 6, 2, 3, 128, 6, 2, 2, 128, 6),
@@ -749,7 +754,9 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(17, MODE_SUMMARY, 1, 8, HINT_NA, 9, 128, 10, 1, 4, 128, 10, 1, 3, 128, 10),
     KSA_VARIANT(22, MODE_SUMMARY, 1, 16, HINT_NA, 9, 128, 5, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(23, MODE_SUMMARY, 1, 24, HINT_NA, 9, 128, 4, 1, 4, 128, 6, 1, 3, 128, 6),
-    KSA_VARIANT(24, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 7, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(29, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 7, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(30, MODE_SUMMARY, 1, 10, HINT_NA, 9, 128, 7, 1, 4, 128, 6, 1, 3, 128, 6),
+    KSA_VARIANT(31, MODE_SUMMARY, 1, 14, HINT_NA, 9, 128, 6, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(25, MODE_SUMMARY, 1, 12, HINT_NA, 9, 256, 3, 1, 4, 256, 3, 1, 3, 256, 3),
     KSA_VARIANT(26, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 5, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(27, MODE_SUMMARY, 1, 16, HINT_NA, 9, 128, 4, 1, 4, 128, 6, 1, 3, 128, 6),
@@ -763,7 +770,7 @@ constexpr int kDefaultFullOptV1 = 46;  // the same below 196608 traces
 constexpr int kDefaultSummary = 16;  // one trace per thread: no interleaved state machines, no predicate spills
 constexpr int kDefaultSummaryOrdered = 24;  // the same with the ordered-thresholds step
 constexpr int kDefaultFullFaults = 8, kDefaultFullFaultsV1 = 9, kDefaultFullFaultsOpt = 1;
-constexpr int kDefaultSummaryFaults = 10, kDefaultSummaryFaultsOrdered = 11;
+constexpr int kDefaultSummaryFaults = 28, kDefaultSummaryFaultsOrdered = 24;
 
 template <size_t K>
 const Variant* find_variant(const Variant (&table)[K], int id) {

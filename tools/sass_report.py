@@ -28,9 +28,9 @@ KERNELS = [
     ("summary", "ksa_replay_summary, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi2ELi128ELi8E", 12),
     ("full_faults", "ksa_replay_full_faults, A=1 (4 traces per thread, ring of 4)",
      "ksa_replay_kernelILi1ELi4ELi4ELi1ELi0ELi8ELi128ELi5E", 16),
-    ("summary_faults_ordered", "ksa_replay_summary_faults, A=1, ordered thresholds (1 trace per thread, ring of 8)",
-     "ksa_replay_kernelILi1ELi1ELi8ELi1ELi1ELi9ELi128ELi8E", 8),
-    ("summary_faults", "ksa_replay_summary_faults, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi8ELi1ELi1ELi10ELi128ELi8E", 8),
+    ("summary_faults_ordered", "ksa_replay_summary_faults, A=1, ordered thresholds (1 trace per thread, ring of 12)",
+     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi9ELi128ELi7E", 12),
+    ("summary_faults", "ksa_replay_summary_faults, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi10ELi128ELi7E", 12),
     ("sweep_shared", "ksa_replay_sweep, A=1, tiles sharing their thresholds (4 policies per thread, ring of 3)",
      "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi2E", 12),
     ("sweep_narrow", "ksa_replay_sweep, A=1, ordered int32 thresholds", "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi1E", 12),
