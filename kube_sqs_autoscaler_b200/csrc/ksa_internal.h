@@ -40,9 +40,9 @@ int ksa_full_variant();
 int ksa_summary_variant();
 
 // Time-parallel full replay for small trace counts (ksa_timepar.cu).
-int ksa_timepar_chunks(int64_t T, int64_t N);
+int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm_out, int* wide_out);
 int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, int64_t T, int32_t A, int64_t N,
                             int64_t ld, int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
-                            uint8_t* events_dev, int K, cudaStream_t st);
+                            uint8_t* events_dev, int K, int L, int warm, int wide, cudaStream_t st);
 
 static inline bool ksa_aligned(const void* p, size_t a) { return ((uintptr_t)p & (a - 1)) == 0; }

@@ -823,10 +823,13 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   // Trace counts far below what fills the GPU: chunks of the time axis in parallel (ksa_timepar.cu;
   // same results). Only the library default takes this path; an explicit variant gets its kernel.
   if (mode == MODE_FULL && !faults && replicas_dev && events_dev && want < 0) {
-    const int K = ksa_timepar_chunks(T, N);
+    const bool vector_ok = (N % 8 == 0) && (ld % 16 == 0) && ksa_aligned(depth_dev, 32) &&
+                           ksa_aligned(replicas_dev, 32) && ksa_aligned(events_dev, 16);
+    int L = 0, warm = 0, wide = 0;
+    const int K = ksa_timepar_plan(T, N, vector_ok, &L, &warm, &wide);
     if (K >= 2) {
-      rc = ksa_timepar_replay_full(args.pk, depth_dev, T, A, N, ld, tick0, state, replicas_dev, events_dev, K,
-                                   (cudaStream_t)stream);
+      rc = ksa_timepar_replay_full(args.pk, depth_dev, T, A, N, ld, tick0, state, replicas_dev, events_dev, K, L,
+                                   warm, wide, (cudaStream_t)stream);
       if (rc <= 0) return rc;  // done, or an error; 1 = the scratch is busy: plain kernels below
     }
   }
