@@ -438,7 +438,7 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm
   if (forced == 0) return 0;
   bool wide = vector_ok;
   if (const char* e = std::getenv("KSA_TIMEPAR_WIDE")) wide = wide && std::atoi(e) != 0;
-  int warm = 64;
+  int warm = 128;  // profiles/r02_small_n.txt: 0.80 of the copy peak at 4096 x 10^5 against 0.78 with 64, 0.68 with none
   if (const char* e = std::getenv("KSA_TIMEPAR_WARM")) warm = std::max(0, std::atoi(e)) / 8 * 8;
   long long K;
   if (forced > 0) {
@@ -448,7 +448,7 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm
     // One trace per thread fills the GPU at about 2^18 threads, eight per thread (1-KB requests, the
     // shape that reaches the copy peak) at about 400k trace-chunks (profiles/r01_small_n_variants.txt).
     // Chunks of at least 8 x warm ticks keep the warm-up and the re-replayed prefixes small.
-    if (N > 98304 || T < 4096) return 0;
+    if (N > 196608 || T < 4096) return 0;
     const long long want = wide ? 393216 : 262144;
     K = (want + N - 1) / N;
     const long long kmax = T / (8 * std::max(warm, 64));

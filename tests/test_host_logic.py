@@ -213,3 +213,19 @@ def test_cli_keeps_the_reference_flag_surface(built):
                             "--aws-region=us-west-2", "--traces", "64", "--ticks", "8"],
                            capture_output=True, text=True)
         assert r.returncode == 2 and "ksa_device_count" in r.stderr  # flags parsed, then no GPU
+
+
+def test_sass_counts_file_matches_the_built_library(built):
+    """profiles/sass_counts.json feeds bench.py's issue-rate roofline of the policy sweep; it must be
+    the count of the library that is actually built (tools/sass_report.py regenerates it)."""
+    import json
+    import shutil
+
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    from tools import sass_report
+
+    counts, _ = sass_report.collect()
+    with open(os.path.join(ROOT, "profiles", "sass_counts.json")) as f:
+        committed = json.load(f)["instructions_per_decision"]
+    assert counts == committed, "kernels changed: run python tools/sass_report.py and commit profiles/"
