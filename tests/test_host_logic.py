@@ -226,6 +226,6 @@ def test_sass_counts_file_matches_the_built_library(built):
     from tools import sass_report
 
     counts, _ = sass_report.collect()
-    with open(os.path.join(ROOT, "profiles", "sass_counts.json")) as f:
+    with open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "sass_counts.json")) as f:
         committed = json.load(f)["instructions_per_decision"]
     assert counts == committed, "kernels changed: run python tools/sass_report.py and commit profiles/"
