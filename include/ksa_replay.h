@@ -21,7 +21,7 @@
  *    the host heap (ksa_dev_alloc / ksa_host_alloc and ksa_pipeline_create are the allocating
  *    helpers). Two fixed arrays live in the library's device image on every GPU that loads it:
  *    the policy table of ksa_replay_sweep_static (192 KB) and the scratch records of the
- *    time-parallel path of ksa_replay_full (32 MB, see there).
+ *    time-parallel path of ksa_replay_full (34 MB, see there).
  *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
  *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
  *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.
@@ -205,7 +205,7 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  *   events_dev   [T][ld] uint8  KSA_EV_* bits of each tick        (may be NULL: not written)
  * Limits: 1 <= T <= 2^30 - 64 per call (chunk longer traces: the carry state makes that exact),
  * 1 <= N <= 2^31-1, N <= ld.
- * Few traces, many ticks (N <= 98304, T >= 4096, both outputs wanted): one thread per trace cannot
+ * Few traces, many ticks (N <= 196608, T >= 4096, both outputs wanted): one thread per trace cannot
  * fill the GPU, so the library cuts the time axis into chunks that are replayed in parallel from
  * guessed states and then stitched exactly (csrc/ksa_timepar.cu; results are identical, the
  * trajectory and the carry state bit for bit). That path keeps its per-chunk records in a fixed
