@@ -39,22 +39,22 @@ import (
 
 // Attribute bits, in the order of sqs.DefaultAttributeNames (sqs/sqs.go:28-32).
 const (
-	AttrMessages           uint32 = C.KSA_ATTR_MESSAGES
-	AttrMessagesDelayed    uint32 = C.KSA_ATTR_MESSAGES_DELAYED
-	AttrMessagesNotVisible uint32 = C.KSA_ATTR_MESSAGES_NOT_VISIBLE
+	AttrMessages = uint32(C.KSA_ATTR_MESSAGES)
+	AttrMessagesDelayed = uint32(C.KSA_ATTR_MESSAGES_DELAYED)
+	AttrMessagesNotVisible = uint32(C.KSA_ATTR_MESSAGES_NOT_VISIBLE)
 )
 
 // Event bits: one per log line of the reference (include/ksa_replay.h).
 const (
-	EvUpApplied   uint8 = C.KSA_EV_UP_APPLIED
-	EvDownApplied uint8 = C.KSA_EV_DOWN_APPLIED
-	EvUpNoop      uint8 = C.KSA_EV_UP_NOOP
-	EvDownNoop    uint8 = C.KSA_EV_DOWN_NOOP
-	EvUpCool      uint8 = C.KSA_EV_UP_COOL
-	EvDownCool    uint8 = C.KSA_EV_DOWN_COOL
-	EvUpFailed    uint8 = C.KSA_EV_UP_FAILED
-	EvDownFailed  uint8 = C.KSA_EV_DOWN_FAILED
-	EvPollFailed  uint8 = C.KSA_EV_POLL_FAILED
+	EvUpApplied = uint8(C.KSA_EV_UP_APPLIED)
+	EvDownApplied = uint8(C.KSA_EV_DOWN_APPLIED)
+	EvUpNoop = uint8(C.KSA_EV_UP_NOOP)
+	EvDownNoop = uint8(C.KSA_EV_DOWN_NOOP)
+	EvUpCool = uint8(C.KSA_EV_UP_COOL)
+	EvDownCool = uint8(C.KSA_EV_DOWN_COOL)
+	EvUpFailed = uint8(C.KSA_EV_UP_FAILED)
+	EvDownFailed = uint8(C.KSA_EV_DOWN_FAILED)
+	EvPollFailed = uint8(C.KSA_EV_POLL_FAILED)
 )
 
 var attributeNames = []string{
