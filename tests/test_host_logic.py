@@ -229,3 +229,22 @@ def test_sass_counts_file_matches_the_built_library(built):
     with open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "sass_counts.json")) as f:
         committed = json.load(f)["instructions_per_decision"]
     assert counts == committed, "kernels changed: run python tools/sass_report.py and commit profiles/"
+
+
+def test_chunk_limits_keep_stamps_inside_int32():
+    """csrc/ksa_policy.cuh keeps the cool-down stamps of a call in int32: a stamp is `tick + c` with
+    tick <= KSA_MAX_CHUNK_TICKS and c <= KSA_COOL_CAP (with T = 2^30 and the cap at
+    2^30 + 1 the sum passed INT_MAX). The cap must still exceed every tick of a call, or a clamped
+    cool-down would open its gate inside the call."""
+    import re
+
+    here = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(here, "kube_sqs_autoscaler_b200", "csrc", "ksa_policy.cuh")).read()
+    max_ticks = re.search(r"#define KSA_MAX_CHUNK_TICKS \(\(1ll << 30\) - (\d+)\)", text)
+    cap = re.search(r"#define KSA_COOL_CAP \(1 << (\d+)\)", text)
+    assert max_ticks and cap, "the two limits are not spelled as this test expects"
+    T, c = (1 << 30) - int(max_ticks.group(1)), 1 << int(cap.group(1))
+    assert T + c <= 2**31 - 1          # the largest stamp a kernel can form
+    assert c > T                       # a capped cool-down stays shut for the whole call
+    assert -(T + 32) > -(2**31)        # group-relative stamps of the summary kernels (ring <= 16)
+    assert 32 + c <= 2**31 - 1

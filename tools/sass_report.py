@@ -38,6 +38,37 @@ KERNELS = [
 ]
 
 
+# Kernels without a steady-state loop: the whole kernel, per element it moves.
+WHOLE = [
+    ("transpose_int64", "ksa_ingest_transpose, int64 source, tile of 256 ticks x 32 traces, 512 threads",
+     "transpose_kernelIxLi256ELi32ELi512E", 256 * 32),
+    ("transpose_int32", "ksa_ingest_transpose, int32 source, tile of 64 ticks x 128 traces, 512 threads",
+     "transpose_kernelIiLi64ELi128ELi512E", 64 * 128),
+]
+
+
+def whole_kernel(lib, pat, per):
+    """(name, instructions of the whole kernel x threads per block / elements per block, histogram)."""
+    import collections
+    import re
+    import subprocess
+
+    if lib not in sass_hot._SASS:
+        sass_hot._SASS[lib] = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
+    for f in sass_hot._SASS[lib].split("Function : ")[1:]:
+        name = f.split("\n", 1)[0].strip()
+        if pat not in name:
+            continue
+        hist = collections.Counter()
+        for line in f.splitlines():
+            m = re.match(r"\s+/\*([0-9a-f]{4,5})\*/\s+(.*?);", line)
+            if m:
+                t = m.group(2).split()
+                hist[(t[1] if t[0].startswith("@") else t[0]).split(".")[0]] += 1
+        return name, hist
+    raise SystemExit(f"no kernel matches {pat}")
+
+
 def collect(lib=LIB):
     counts, text = {}, []
     for key, what, pat, per in KERNELS:
@@ -46,6 +77,14 @@ def collect(lib=LIB):
             raise SystemExit(f"{key}: {len(found)} kernels match {pat}: update tools/sass_report.py (a default changed?)")
         counts[key] = round(found[0][4] / per, 2)
         text.append(f"## {key}: {what}\n{sass_hot.describe(found[0], per)}\n")
+    for key, what, pat, elements in WHOLE:
+        name, hist = whole_kernel(lib, pat, elements)
+        threads = int(pat.rsplit("ELi", 1)[1].rstrip("E"))
+        n = sum(hist.values())
+        counts[key] = round(n * threads / elements, 2)
+        text.append(f"## {key}: {what}\n{name}\n  whole kernel, fully unrolled: {n} instructions per thread x {threads} threads / "
+                    f"{elements} elements = {n * threads / elements:.2f} per element\n  " +
+                    ", ".join(f"{k} {v * threads / elements:.2f}" for k, v in hist.most_common()) + "\n")
     return counts, text
 
 
