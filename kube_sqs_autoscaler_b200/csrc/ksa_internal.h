@@ -39,10 +39,19 @@ int ksa_policy_to_k(const ksa_policy* p, int32_t A, ksa_policy_k* out);
 int ksa_full_variant();
 int ksa_summary_variant();
 
-// Time-parallel full replay for small trace counts (ksa_timepar.cu).
-int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm_out, int* wide_out);
-int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, int64_t T, int32_t A, int64_t N,
-                            int64_t ld, int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
-                            uint8_t* events_dev, int K, int L, int warm, int wide, cudaStream_t st);
+// Time-parallel replays for small trace counts (ksa_timepar.cu); fail_dev == NULL: no failure mask.
+int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vector_ok, int* L_out, int* warm_out,
+                     int* wide_out);
+int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, const uint8_t* fail_dev, int64_t T,
+                            int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                            int32_t* replicas_dev, uint8_t* events_dev, int K, int L, int warm, int wide,
+                            cudaStream_t st);
+int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
+                               int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                               ksa_summary* summary_dev, int K, int L, int warm, cudaStream_t st);
+// Its pass 1: the default summary kernel over (trace blocks, chunks of L ticks) (ksa_replay.cu).
+int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
+                              int L, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, int K, int32_t* st_r,
+                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, cudaStream_t stream);
 
 static inline bool ksa_aligned(const void* p, size_t a) { return ((uintptr_t)p & (a - 1)) == 0; }

@@ -35,6 +35,11 @@ struct ReplayArgs {
   int* replicas;           // full mode, may be NULL
   unsigned char* events;   // full mode, may be NULL
   ksa_summary* summary;    // summary mode
+  // Time-parallel summary launches only (TP kernels, ksa_timepar.cu): the call's T ticks are cut
+  // into chunks of `T` ticks (above), blockIdx.y = chunk, and chunk k of trace n keeps its carry
+  // state and its summary at index k * tp_stride + n of the arrays above (scratch, not the caller's).
+  int tp_total;            // ticks of the whole call
+  long long tp_stride;     // traces of the call
 };
 
 // MODE_FULL writes both outputs; MODE_FULL_OPT tests the two output pointers at run time (either may
@@ -174,13 +179,18 @@ __device__ __forceinline__ void load_fail(const unsigned char* p, unsigned (&w)[
 
 typedef ksa_summary_acc SummaryRegs;
 
-template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB>
+template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB, bool TP = false>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
   ksa_step_consts c(a.pk);
-  const int T = a.T;
+  // TP: this block replays chunk blockIdx.y of the time axis as if it were a call of its own
+  // (ticks tick0 + 1 .. tick0 + T of the trace, state and summary in the chunk's own slots).
+  const int ky = TP ? (int)blockIdx.y : 0;
+  const long long si = TP ? ky * a.tp_stride + n0 : n0;  // index into the state and summary arrays
+  const int T = TP ? min(a.T, a.tp_total - ky * a.T) : a.T;
+  const long long tick0 = TP ? a.tick0 + (long long)ky * a.T : a.tick0;
   const int one = a.one;  // always 1; see ksa_step_fma
   constexpr bool FAULTS = (STEP == 4 || STEP == 5 || STEP == 7 || STEP == 8 || STEP == 9 || STEP == 10);
   constexpr bool FMA = (STEP == 2 || STEP == 5 || STEP == 6 || STEP == 7 || STEP == 8 || STEP == 9 || STEP == 10);
@@ -205,15 +215,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   ksa_trace_regs s[V];
 #pragma unroll
   for (int v = 0; v < V; ++v) {
-    s[v].r = a.st_r[n0 + v];
-    s[v].su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
-    s[v].sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
+    s[v].r = a.st_r[si + v];
+    s[v].su = ksa_local_stamp(a.pk.cu, c.cu, tick0, a.st_ju[si + v]);
+    s[v].sd = ksa_local_stamp(a.pk.cd, c.cd, tick0, a.st_jd[si + v]);
   }
   SummaryRegs sm[MODE == MODE_SUMMARY ? V : 1];
   if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      const ksa_summary* q = a.summary + n0 + v;
+      const ksa_summary* q = a.summary + si + v;
       ksa_summary_acc_init(sm[v], q->min_replicas, q->max_replicas, q->sum_replicas, q->hash);
     }
   }
@@ -227,15 +237,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        ksa_summary_flush(sm[v], a.summary + n0 + v);
-        if constexpr (FAULTS3) ksa_summary_flush_faults3(sm[v], a.summary + n0 + v);
-        else if constexpr (FAULTS) ksa_summary_flush_faults(sm[v], a.summary + n0 + v);
+        ksa_summary_flush(sm[v], a.summary + si + v);
+        if constexpr (FAULTS3) ksa_summary_flush_faults3(sm[v], a.summary + si + v);
+        else if constexpr (FAULTS) ksa_summary_flush_faults(sm[v], a.summary + si + v);
       }
     }
   };
 
   const long long row = (long long)A * a.ld;  // elements between consecutive ticks
-  const long long* dp = a.depth + n0;
+  const long long* dp = a.depth + n0 + (TP ? (long long)ky * a.T * row : 0ll);
   int* rp = (MODE != MODE_SUMMARY) ? a.replicas + n0 : nullptr;
   unsigned char* ep = (MODE != MODE_SUMMARY) ? a.events + n0 : nullptr;
   const bool want_r = MODE == MODE_FULL || (MODE == MODE_FULL_OPT && a.replicas != nullptr);
@@ -250,7 +260,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
       for (int p = 0; p < A; ++p) load_depth<V, HINT>(dp + (long long)j * row + p * a.ld, buf[j][p]);
     }
   // The failure mask rides the same ring (one byte per trace and tick).
-  const unsigned char* fp = FAULTS ? a.fail + n0 : nullptr;
+  const unsigned char* fp = FAULTS ? a.fail + n0 + (TP ? (long long)ky * a.T * a.ld : 0ll) : nullptr;
   unsigned fbuf[FAULTS ? D : 1][(V + 3) / 4];
   if constexpr (FAULTS) {
 #pragma unroll
@@ -422,24 +432,24 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
     for (int v = 0; v < V; ++v) {
       if (sm[v].bad) {  // a replica count left +-KSA_SUM_SAFE: redo the sum exactly (ksa_summary_acc)
         ksa_trace_regs s0;  // the state this call started from is still in global memory
-        s0.r = a.st_r[n0 + v];
-        s0.su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
-        s0.sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
-        sm[v].sum = a.summary[n0 + v].sum_replicas +
+        s0.r = a.st_r[si + v];
+        s0.su = ksa_local_stamp(a.pk.cu, c.cu, tick0, a.st_ju[si + v]);
+        s0.sd = ksa_local_stamp(a.pk.cd, c.cd, tick0, a.st_jd[si + v]);
+        sm[v].sum = a.summary[si + v].sum_replicas +
                     ksa_exact_sum(a.pk, dp + v, row, a.ld, A, FAULTS ? fp + v : nullptr, a.ld, T, s0);
       }
     }
   }
 #pragma unroll
   for (int v = 0; v < V; ++v) {
-    a.st_r[n0 + v] = s[v].r;
-    a.st_ju[n0 + v] = ksa_global_stamp(s[v].su, c.cu, a.tick0, a.st_ju[n0 + v]);
-    a.st_jd[n0 + v] = ksa_global_stamp(s[v].sd, c.cd, a.tick0, a.st_jd[n0 + v]);
+    a.st_r[si + v] = s[v].r;
+    a.st_ju[si + v] = ksa_global_stamp(s[v].su, c.cu, tick0, a.st_ju[si + v]);
+    a.st_jd[si + v] = ksa_global_stamp(s[v].sd, c.cd, tick0, a.st_jd[si + v]);
   }
   if constexpr (MODE == MODE_SUMMARY) {
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      ksa_summary* q = a.summary + n0 + v;
+      ksa_summary* q = a.summary + si + v;
       q->final_replicas = s[v].r;
       q->min_replicas = sm[v].rmin;
       q->max_replicas = sm[v].rmax;
@@ -715,7 +725,9 @@ const Variant kFullFaultsVariants[] = {
     KSA_VARIANT(1, MODE_FULL_OPT, 8, 2, HINT_NA, 4, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
     // STEP 8: the second spelling of the failure-aware step (ksa_step_faults_fma2), event byte out
     KSA_VARIANT(8, MODE_FULL, 4, 4, HINT_NA, 8, 128, 5, 4, 2, 128, 5, 2, 3, 128, 6),
-    KSA_VARIANT(9, MODE_FULL, 1, 8, HINT_NA, 8, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),  // small trace counts
+    // one trace per thread below 262144 traces: 0.83 / 0.82 / 0.77 of the copy peak at 98304 / 131072 / 196608
+    // against 0.49 / 0.62 / 0.74 for four per thread (profiles/r02_small_n_modes.txt)
+    KSA_VARIANT(9, MODE_FULL, 1, 8, HINT_NA, 8, 128, 8, 1, 4, 128, 8, 1, 3, 128, 8),
 #ifdef KSA_TUNING_VARIANTS
     KSA_VARIANT(2, MODE_FULL, 8, 2, HINT_NA, 5, 128, 4, 4, 3, 128, 4, 4, 2, 128, 4),
     KSA_VARIANT(3, MODE_FULL, 8, 2, HINT_NA, 5, 256, 2, 4, 3, 256, 2, 4, 2, 256, 2),
@@ -761,6 +773,16 @@ const Variant kSummaryFaultsVariants[] = {
     KSA_VARIANT(26, MODE_SUMMARY, 1, 12, HINT_NA, 9, 128, 5, 1, 4, 128, 6, 1, 3, 128, 6),
     KSA_VARIANT(27, MODE_SUMMARY, 1, 16, HINT_NA, 9, 128, 4, 1, 4, 128, 6, 1, 3, 128, 6),
 #endif
+};
+// The summary defaults (16 / 24, with failures 28 / 24) as chunk-of-the-time-axis kernels for
+// ksa_timepar.cu: [failure mask * 2 + ordered thresholds][A - 1]. One trace per thread, scalar
+// loads: any layout.
+#define KSA_KTP(A, D, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE_SUMMARY, STEP, 128, MINB, true>
+const replay_kernel_fn kSummaryChunkKernels[4][3] = {
+    {KSA_KTP(1, 12, 2, 8), KSA_KTP(2, 3, 2, 10), KSA_KTP(3, 2, 2, 10)},
+    {KSA_KTP(1, 12, 6, 8), KSA_KTP(2, 3, 6, 10), KSA_KTP(3, 2, 6, 10)},
+    {KSA_KTP(1, 12, 10, 7), KSA_KTP(2, 3, 10, 8), KSA_KTP(3, 2, 10, 8)},
+    {KSA_KTP(1, 12, 9, 7), KSA_KTP(2, 3, 9, 8), KSA_KTP(3, 2, 9, 8)},
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per thread
@@ -818,22 +840,30 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   args.replicas = replicas_dev;
   args.events = events_dev;
   args.summary = summary_dev;
+  args.tp_total = 0;
+  args.tp_stride = 0;
 
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
+  const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
   // Trace counts far below what fills the GPU: chunks of the time axis in parallel (ksa_timepar.cu;
   // same results). Only the library default takes this path; an explicit variant gets its kernel.
-  if (mode == MODE_FULL && !faults && replicas_dev && events_dev && want < 0) {
-    const bool vector_ok = (N % 8 == 0) && (ld % 16 == 0) && ksa_aligned(depth_dev, 32) &&
-                           ksa_aligned(replicas_dev, 32) && ksa_aligned(events_dev, 16);
+  if (want < 0 && (mode == MODE_SUMMARY || (replicas_dev && events_dev)) &&
+      !(faults && std::getenv("KSA_FAULTS_VARIANT"))) {
+    const bool vector_ok = mode == MODE_FULL && (N % 8 == 0) && (ld % 16 == 0) && ksa_aligned(depth_dev, 32) &&
+                           ksa_aligned(replicas_dev, 32) && ksa_aligned(events_dev, 16) &&
+                           (!faults || ksa_aligned(fail_dev, 16));
     int L = 0, warm = 0, wide = 0;
-    const int K = ksa_timepar_plan(T, N, vector_ok, &L, &warm, &wide);
+    const int K = ksa_timepar_plan(T, N, mode == MODE_SUMMARY, faults, vector_ok, &L, &warm, &wide);
     if (K >= 2) {
-      rc = ksa_timepar_replay_full(args.pk, depth_dev, T, A, N, ld, tick0, state, replicas_dev, events_dev, K, L,
-                                   warm, wide, (cudaStream_t)stream);
+      cudaStream_t s = (cudaStream_t)stream;
+      rc = mode == MODE_FULL
+               ? ksa_timepar_replay_full(args.pk, depth_dev, args.fail, T, A, N, ld, tick0, state, replicas_dev,
+                                         events_dev, K, L, warm, wide, s)
+               : ksa_timepar_replay_summary(args.pk, ordered, depth_dev, args.fail, T, A, N, ld, tick0, state,
+                                            summary_dev, K, L, warm, s);
       if (rc <= 0) return rc;  // done, or an error; 1 = the scratch is busy: plain kernels below
     }
   }
-  const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
   const int default_summary = ordered ? kDefaultSummaryOrdered : kDefaultSummary;
   // Full mode: 8 traces per thread need ~600k traces to fill 148 SMs; below that the kernel is bound
   // by the per-thread state chain, not by HBM, and fewer traces per thread win
@@ -850,7 +880,7 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   if (faults) {
     // The tuning knob KSA_FAULTS_VARIANT=<id> (environment) selects another table entry for measurements.
     const bool both = replicas_dev && events_dev;
-    int fid = mode == MODE_FULL ? (both ? (N < 131072 ? kDefaultFullFaultsV1 : kDefaultFullFaults) : kDefaultFullFaultsOpt)
+    int fid = mode == MODE_FULL ? (both ? (N < 262144 ? kDefaultFullFaultsV1 : kDefaultFullFaults) : kDefaultFullFaultsOpt)
                                 : (ordered ? kDefaultSummaryFaultsOrdered : kDefaultSummaryFaults);
     const int fid_default = fid;
     if (const char* e = std::getenv("KSA_FAULTS_VARIANT")) fid = std::atoi(e);
@@ -887,6 +917,37 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
 }
 
 }  // namespace
+
+// Pass 1 of the time-parallel summary replay (ksa_timepar.cu): K chunks of L ticks of every trace,
+// each replayed like a call of its own by the default summary kernel, with the chunk's carry state
+// at st_*[k * N + n] (in: the state the chunk starts from; out: the state it ends with) and its
+// summary accumulated into partial[k * N + n].
+int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
+                              int L, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, int K, int32_t* st_r,
+                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, cudaStream_t stream) {
+  ReplayArgs args;
+  args.pk = pk;
+  args.depth = (const long long*)depth_dev;
+  args.fail = fail_dev;
+  args.ld = ld;
+  args.tick0 = tick0;
+  args.n_begin = 0;
+  args.n_count = N;
+  args.T = L;
+  args.one = 1;
+  args.st_r = st_r;
+  args.st_ju = (long long*)st_ju;
+  args.st_jd = (long long*)st_jd;
+  args.replicas = nullptr;
+  args.events = nullptr;
+  args.summary = partial;
+  args.tp_total = (int)T;
+  args.tp_stride = N;
+  const long long blocks = (N + 127) / 128;
+  kSummaryChunkKernels[(fail_dev ? 2 : 0) + (ordered ? 1 : 0)][A - 1]<<<dim3((unsigned)blocks, (unsigned)K), 128, 0, stream>>>(args);
+  KSA_LAUNCH_CHECK("ksa_replay_kernel (chunks of the time axis)");
+  return KSA_OK;
+}
 
 extern "C" int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T,
                                int32_t A, int64_t N, int64_t ld, int64_t tick0,

@@ -52,6 +52,14 @@ constexpr int kChecks = 3;
 __host__ __device__ constexpr int check_tick(int j) { return 64 << (2 * j); }  // 64, 256, 1024 ticks into the chunk
 constexpr int kMargin = 8;            // a chunk has checkpoint j if check_tick(j) + kMargin <= its length
 constexpr int BLOCK = 128;
+// Trace counts up to which the chunked path is taken by default: where it stops paying against one
+// trace per thread over the whole call (profiles/r02_small_n_modes.txt).
+constexpr long long kTpMaxSummary = 65536;        // 0.774 against 0.764 of the copy peak there, 0.82 / 0.87 at 98304
+constexpr long long kTpMaxSummaryFaults = 49152;  // 0.674 / 0.621; 0.646 / 0.693 at 65536
+constexpr long long kTpMaxFullFaults = 81920;     // 0.773 / 0.750; 0.81 / 0.83 at 98304
+// ... and again where one trace per thread starts a second, nearly empty wave of 148 x 1024 threads
+// (163840 traces: 0.81 against 0.73), as long as two chunks still fit one wave of pass 1
+constexpr long long kTpFullFaultsSecondWave = 151552;
 
 struct TpState {
   int r, su, sd;  // replicas; first local tick at which the up / down gate is open (ksa_policy.cuh)
@@ -71,6 +79,7 @@ static __device__ int g_tp_count;
 struct TpArgs {
   ksa_policy_k pk;
   const long long* depth;
+  const unsigned char* fail;  // [T][ld] KSA_FAIL_* bits (the *_faults entry points), else NULL
   long long ld, tick0, N;
   int T, A, K, L;  // ticks of the call, attribute planes, chunks, ticks per chunk (a multiple of 8)
   int warm;        // ticks replayed before a chunk without output (a multiple of 8, <= L)
@@ -112,12 +121,26 @@ template <int V>
 __device__ __forceinline__ void tp_load(const long long* p, long long (&v)[V]) {
   if constexpr (V == 1) {
     asm volatile("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(v[0]) : "l"(p));
+  } else if constexpr (V == 4) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
   } else {
-    static_assert(V == 8, "V is 1 or 8");
+    static_assert(V == 8, "V is 1, 4 or 8");
     asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
     asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(v[4]), "=l"(v[5]), "=l"(v[6]), "=l"(v[7]) : "l"(p + 4));
+  }
+}
+// V failure-mask bytes of one tick (V = 4: one packed word, V = 8: two)
+template <int V>
+__device__ __forceinline__ void tp_load_fail(const unsigned char* p, unsigned (&w)[V == 8 ? 2 : 1]) {
+  if constexpr (V == 1) {
+    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(w[0]) : "l"(p));
+  } else if constexpr (V == 4) {
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w[0]) : "l"(p));
+  } else {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p));
   }
 }
 __device__ __forceinline__ unsigned tp_pack4(unsigned e0, unsigned e1, unsigned e2, unsigned e3) {
@@ -133,6 +156,11 @@ __device__ __forceinline__ void tp_store(int* rp, unsigned char* ep, const int (
   if constexpr (V == 1) {
     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(rp), "r"(r[0]) : "memory");
     asm volatile("st.global.cs.b8 [%0], %1;" ::"l"(ep), "r"(e[0]) : "memory");
+  } else if constexpr (V == 4) {
+    asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(rp), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3])
+                 : "memory");
+    const unsigned w0 = tp_pack4(e[0], e[1], e[2], e[3]);
+    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(ep), "r"(w0) : "memory");
   } else {
     asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(rp), "r"(r[0]), "r"(r[1]), "r"(r[2]),
                  "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
@@ -141,10 +169,10 @@ __device__ __forceinline__ void tp_store(int* rp, unsigned char* ep, const int (
   }
 }
 
-template <int A, int V, int D, int TPB, int MINB>
+template <int A, int V, int D, int TPB, int MINB, bool FAULTS>
 __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constant__ TpArgs a) {
   const long long n0 = ((long long)blockIdx.x * TPB + threadIdx.x) * V;
-  if (n0 >= a.N) return;  // (V = 8: N is a multiple of 8)
+  if (n0 >= a.N) return;  // (V > 1: N is a multiple of 8)
   const int k = blockIdx.y;
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
@@ -177,8 +205,21 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
 #pragma unroll
       for (int p = 0; p < A; ++p) tp_load<V>(dp + (long long)(tb + j) * row + p * a.ld, buf[j][p]);
     }
+  // the failure mask rides the same ring
+  const unsigned char* fp = FAULTS ? a.fail + n0 : nullptr;
+  unsigned fbuf[FAULTS ? D : 1][V == 8 ? 2 : 1];
+  if constexpr (FAULTS) {
+#pragma unroll
+    for (int j = 0; j < D; ++j)
+      if (tb + j < te) tp_load_fail<V>(fp + (long long)(tb + j) * a.ld, fbuf[j]);
+  }
   auto tick = [&](const int tt, const int j, const bool prefetch, const bool store) {
     long long msgs[V];
+    unsigned fw[V == 8 ? 2 : 1];
+    if constexpr (FAULTS) {
+#pragma unroll
+      for (int w = 0; w < (V == 8 ? 2 : 1); ++w) fw[w] = fbuf[j][w];
+    }
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       unsigned long long acc = (unsigned long long)buf[j][0][v];  // sqs.go:56-64, wrapping
@@ -189,12 +230,18 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
     if (prefetch) {
 #pragma unroll
       for (int p = 0; p < A; ++p) tp_load<V>(dp + (long long)(tt + D) * row + p * a.ld, buf[j][p]);
+      if constexpr (FAULTS) tp_load_fail<V>(fp + (long long)(tt + D) * a.ld, fbuf[j]);
     }
     int rr[V];
     unsigned ev[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
-      ev[v] = ksa_step_fma_byte(c, msgs[v], tt + 1, one, s[v]);
+      if constexpr (FAULTS) {
+        const unsigned f = V == 1 ? fw[0] : (fw[v / 4] >> (8 * (v % 4))) & 0xffu;  // a u8 load is zero-extended
+        ev[v] = ksa_step_faults_fma2<false, false>(c, msgs[v], f, tt + 1, one, s[v]);
+      } else {
+        ev[v] = ksa_step_fma_byte(c, msgs[v], tt + 1, one, s[v]);
+      }
       rr[v] = s[v].r;
     }
     if (store) tp_store<V>(rp + (long long)tt * a.ld, ep + (long long)tt * a.ld, rr, ev);
@@ -241,7 +288,7 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
 // of the next group already in flight (a plain loop waits a memory latency per tick). Stops after a
 // checkpoint tick j >= first_check whose pass-1 state has the same future; returns that j, or -1
 // when the chunk ends first.
-template <int A>
+template <int A, bool FAULTS>
 __device__ int tp_replay_until_match(const TpArgs& a, const ksa_step_consts& c, long long n, int t0, int len,
                                      const TpChunk* rec, int first_check, ksa_trace_regs& s) {
   constexpr int G = 8;
@@ -249,17 +296,26 @@ __device__ int tp_replay_until_match(const TpArgs& a, const ksa_step_consts& c, 
   const long long* dp = a.depth + (long long)t0 * row + n;
   int* rp = a.replicas + (long long)t0 * a.ld + n;
   unsigned char* ep = a.events + (long long)t0 * a.ld + n;
+  const unsigned char* fp = FAULTS ? a.fail + (long long)t0 * a.ld + n : nullptr;
   long long buf[G];
+  unsigned fbuf[FAULTS ? G : 1];
 #pragma unroll
-  for (int j = 0; j < G; ++j) buf[j] = j < len ? load_sum(dp + (long long)j * row, a.ld, A) : 0;
+  for (int j = 0; j < G; ++j) {
+    buf[j] = j < len ? load_sum(dp + (long long)j * row, a.ld, A) : 0;
+    if constexpr (FAULTS) fbuf[j] = j < len ? (unsigned)__ldg(fp + (long long)j * a.ld) : 0u;
+  }
   for (int t = 0; t < len; t += G) {
 #pragma unroll
     for (int j = 0; j < G; ++j) {
       const int tt = t + j;
       if (tt < len) {
         const long long msgs = buf[j];
-        if (tt + G < len) buf[j] = load_sum(dp + (long long)(tt + G) * row, a.ld, A);
-        const unsigned ev = ksa_step(c, msgs, t0 + tt + 1, s);
+        const unsigned f = FAULTS ? fbuf[j] : 0u;
+        if (tt + G < len) {
+          buf[j] = load_sum(dp + (long long)(tt + G) * row, a.ld, A);
+          if constexpr (FAULTS) fbuf[j] = (unsigned)__ldg(fp + (long long)(tt + G) * a.ld);
+        }
+        const unsigned ev = FAULTS ? ksa_step_faults(c, msgs, f, t0 + tt + 1, s) : ksa_step(c, msgs, t0 + tt + 1, s);
         rp[(long long)tt * a.ld] = s.r;
         ep[(long long)tt * a.ld] = (unsigned char)ev;
       }
@@ -293,7 +349,7 @@ __global__ void __launch_bounds__(BLOCK) tp_check_kernel(const __grid_constant__
 }
 
 // ---- pass 2b -------------------------------------------------------------------------------------
-template <int A>
+template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_fix_kernel(const __grid_constant__ TpArgs a) {
   const int idx = blockIdx.x * BLOCK + threadIdx.x;
   if (idx >= g_tp_count) return;
@@ -306,7 +362,7 @@ __global__ void __launch_bounds__(BLOCK) tp_fix_kernel(const __grid_constant__ T
   TpChunk* const rec = record(a, k, n);
   const TpState entry = record(a, k - 1, n)->exit1;
   ksa_trace_regs s{entry.r, entry.su, entry.sd};
-  const int j = tp_replay_until_match<A>(a, c, n, t0, len, rec, 0, s);
+  const int j = tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, 0, s);
   rec->entry1 = TpState{s.r, s.su, s.sd};  // (the slot is free: pass 2a has read it)
   rec->status = j >= 0 ? j + 1 : -1;
 }
@@ -317,7 +373,7 @@ __device__ __forceinline__ int later_stamp(int keep, int cand, int c, int after)
   return (cand - c > after) ? cand : keep;
 }
 
-template <int A>
+template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__ TpArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
@@ -376,7 +432,7 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
         // if pass 2b rewrote the whole chunk, nothing of pass 1 is left in it.
         ksa_trace_regs s{cur.r, cur.su, cur.sd};
         const int first = status < 0 ? kChecks : (status == 0 ? 0 : status - 1);
-        const int j = tp_replay_until_match<A>(a, c, n, t0, len, rec, first, s);
+        const int j = tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, first, s);
         cur.su = s.su;
         cur.sd = s.sd;
         if (j >= 0) {
@@ -395,48 +451,622 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
   a.st_jd[n] = ksa_global_stamp(cur.sd, c.cd, a.tick0, a.st_jd[n]);
 }
 
+// ==== summary mode ================================================================================
+//
+// ksa_replay_summary / ksa_replay_summary_faults for few traces. A chunk of the time axis is
+// replayed exactly like a call of its own: chunk k of trace n has a carry state (replicas and the
+// two stamps as absolute ticks, the caller's own format) and a ksa_summary record in the scratch,
+// and pass 1 IS the default summary kernel (ksa_replay.cu, one trace per thread) over a grid of
+// (trace blocks, chunks). A record's counters, sum and min / max combine by addition and min / max;
+// the fingerprint of a chunk started from 0 is an affine map of the fingerprint before it
+// (lo' = lo * M^len + h), so the chunks' fingerprints chain by multiply-adds.
+//
+//  pass 0  thread (trace, chunk): chunk 0 takes the caller's state; chunk k > 0 replays the `warm`
+//          ticks before its first one from a guess (the caller's state) and keeps what it ends
+//          with as its entry state. Clears the chunk's summary record.
+//  pass 1  the summary kernel: entry state -> exit state, summary record.
+//  pass 2a thread (trace, chunk >= 1): does the previous chunk's exit state have the same future as
+//          this chunk's entry state? If not, the chunk goes on the list.
+//  pass 2b thread (list item): replay the whole chunk again from the previous chunk's exit state
+//          (plain loop), overwriting its summary record; remember the state it ends with and whether
+//          that has the same future as pass 1's exit state (which the next chunk was judged by).
+//  pass 3  warp (trace): if every chunk is fine, all records were computed from the true states by
+//          induction: the lanes combine them in order (each lane a run of chunks, then a tree over the
+//          lanes). Otherwise lane 0 walks the chunks with the true state and replays again whatever was
+//          replayed from a wrong one. The result is added to the caller's record and state.
+//
+// "Same future" at the first tick B + 1 of a chunk, with `rem` ticks of the call left: equal replica
+// counts, and for each direction the same first tick at which the gate is open, both clamped into
+// [1, rem + 1] (open from the chunk's first tick on is one case, shut for the rest of the call another).
+// The caller's stamps are the true ones: per direction the latest stamp that a valid chunk took
+// inside its own ticks (later than B), else what came before it.
+//
+// Scratch: the 64-byte slots of g_tp_scratch seen as arrays over (chunk, trace) — three carry
+// states (pass 1's in/out, the entry copy, pass 2b's exit) and a status word — plus one ksa_summary per
+// slot (g_tp_partial, 32 MB).
+
+static __device__ __align__(256) ksa_summary g_tp_partial[kMaxChunks];
+
+struct TpCarry {
+  int* r;
+  long long* ju;
+  long long* jd;
+};
+struct TpSumArgs {
+  ksa_policy_k pk;
+  const long long* depth;
+  const unsigned char* fail;
+  long long ld, tick0, N;
+  int T, A, K, L, warm, one;
+  int piece;  // pass 2b cuts a chunk into pieces of this many ticks (a multiple of 8, at most 32 pieces)
+  unsigned mL_lo, mL_hi, mE_lo, mE_hi;  // the fingerprint multipliers to the power L / the last chunk's length
+  int* st_r;           // the caller's state and summaries
+  long long* st_ju;
+  long long* st_jd;
+  ksa_summary* summary;
+  TpCarry io, en, fx;  // scratch: pass 1's state (in: entry, out: exit), entry copy, pass 2b's exit
+  int* status;         // 0 pass 1's record stands; 1 pass 2b's record, exit as pass 1's; -1 pass 2b's, exit differs
+  ksa_summary* part;
+};
+
+struct TpG {  // a carry state in the caller's format
+  int r;
+  long long ju, jd;
+};
+__device__ __forceinline__ TpG tp_get(const TpCarry& c, long long i) { return TpG{c.r[i], c.ju[i], c.jd[i]}; }
+__device__ __forceinline__ void tp_put(const TpCarry& c, long long i, const TpG& g) {
+  c.r[i] = g.r;
+  c.ju[i] = g.ju;
+  c.jd[i] = g.jd;
+}
+// First tick after B (1-based) at which a gate with stamp `last` is open, clamped into [1, rem + 1].
+__device__ __forceinline__ int tp_gate(long long cool, int c, long long B, long long last, int rem) {
+  return min(max(ksa_local_stamp(cool, c, B, last), 1), rem + 1);
+}
+__device__ __forceinline__ bool tp_same_future(const ksa_policy_k& pk, const ksa_step_consts& c, const TpG& a,
+                                               const TpG& b, long long B, int rem) {
+  return a.r == b.r && tp_gate(pk.cu, c.cu, B, a.ju, rem) == tp_gate(pk.cu, c.cu, B, b.ju, rem) &&
+         tp_gate(pk.cd, c.cd, B, a.jd, rem) == tp_gate(pk.cd, c.cd, B, b.jd, rem);
+}
+
+__device__ __forceinline__ void tp_summary_clear(ksa_summary& q) {
+  q.final_replicas = 0;
+  q.min_replicas = INT_MAX;
+  q.max_replicas = INT_MIN;
+  q.up_applied = q.down_applied = q.up_noop = q.down_noop = q.up_cool = q.down_cool = 0u;
+  q.poll_failed = q.up_failed = q.down_failed = 0u;
+  q.sum_replicas = 0;
+  q.hash = 0ull;
+}
+// One tick into a record, the plain way (the definition of the fields, include/ksa_replay.h).
+__device__ __forceinline__ void tp_summary_add(ksa_summary& q, int r, unsigned ev) {
+  q.final_replicas = r;
+  q.min_replicas = min(q.min_replicas, r);
+  q.max_replicas = max(q.max_replicas, r);
+  q.up_applied += (ev & KSA_EV_UP_APPLIED) ? 1u : 0u;
+  q.down_applied += (ev & KSA_EV_DOWN_APPLIED) ? 1u : 0u;
+  q.up_noop += (ev & KSA_EV_UP_NOOP) ? 1u : 0u;
+  q.down_noop += (ev & KSA_EV_DOWN_NOOP) ? 1u : 0u;
+  q.up_cool += (ev & KSA_EV_UP_COOL) ? 1u : 0u;
+  q.down_cool += (ev & KSA_EV_DOWN_COOL) ? 1u : 0u;
+  const unsigned fb = ev & (unsigned)KSA_EV_POLL_FAILED;  // both failure bits = the poll failed
+  q.poll_failed += fb == (unsigned)KSA_EV_POLL_FAILED ? 1u : 0u;
+  q.up_failed += fb == (unsigned)KSA_EV_UP_FAILED ? 1u : 0u;
+  q.down_failed += fb == (unsigned)KSA_EV_DOWN_FAILED ? 1u : 0u;
+  q.sum_replicas = (long long)((unsigned long long)q.sum_replicas + (unsigned long long)(long long)r);
+  q.hash = ksa_hash_step(q.hash, r, ev);
+}
+
+// Ticks [first, first + count) of the call for trace n, from carry state g (plain loop, the depths
+// of the next 8 ticks in flight). With `q` the ticks are added to that record.
+template <int A, bool FAULTS>
+__device__ void tp_sum_replay(const TpSumArgs& a, const ksa_step_consts& c, long long n, int first, int count, TpG& g,
+                              ksa_summary* q) {
+  constexpr int G = 8;
+  const long long B = a.tick0 + first;
+  ksa_trace_regs s{g.r, ksa_local_stamp(a.pk.cu, c.cu, B, g.ju), ksa_local_stamp(a.pk.cd, c.cd, B, g.jd)};
+  const long long row = (long long)A * a.ld;
+  const long long* dp = a.depth + (long long)first * row + n;
+  const unsigned char* fp = FAULTS ? a.fail + (long long)first * a.ld + n : nullptr;
+  long long buf[G];
+  unsigned fbuf[FAULTS ? G : 1];
+#pragma unroll
+  for (int j = 0; j < G; ++j) {
+    buf[j] = j < count ? load_sum(dp + (long long)j * row, a.ld, A) : 0;
+    if constexpr (FAULTS) fbuf[j] = j < count ? (unsigned)__ldg(fp + (long long)j * a.ld) : 0u;
+  }
+  for (int t = 0; t < count; t += G) {
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+      const int tt = t + j;
+      if (tt < count) {
+        const long long msgs = buf[j];
+        const unsigned f = FAULTS ? fbuf[j] : 0u;
+        if (tt + G < count) {
+          buf[j] = load_sum(dp + (long long)(tt + G) * row, a.ld, A);
+          if constexpr (FAULTS) fbuf[j] = (unsigned)__ldg(fp + (long long)(tt + G) * a.ld);
+        }
+        const unsigned ev = FAULTS ? ksa_step_faults(c, msgs, f, tt + 1, s) : ksa_step(c, msgs, tt + 1, s);
+        if (q) tp_summary_add(*q, s.r, ev);
+      }
+    }
+  }
+  g.r = s.r;
+  g.ju = ksa_global_stamp(s.su, c.cu, B, g.ju);
+  g.jd = ksa_global_stamp(s.sd, c.cd, B, g.jd);
+}
+
+// `count` ticks (a multiple of 8) from tick `first` of the call for trace n, nothing recorded: the
+// warm-up of a speculative start. The FMA-steered steps of the main kernels, the depths of the next
+// 8 ticks in flight.
+template <int A, bool FAULTS>
+__device__ __forceinline__ void tp_sum_warm(const TpSumArgs& a, const ksa_step_consts& c, long long n, int first,
+                                            int count, TpG& g) {
+  constexpr int G = 8;
+  const long long B = a.tick0 + first;
+  ksa_trace_regs s{g.r, ksa_local_stamp(a.pk.cu, c.cu, B, g.ju), ksa_local_stamp(a.pk.cd, c.cd, B, g.jd)};
+  const long long row = (long long)A * a.ld;
+  const long long* dp = a.depth + (long long)first * row + n;
+  const unsigned char* fp = FAULTS ? a.fail + (long long)first * a.ld + n : nullptr;
+  const int one = a.one;
+  long long buf[G][A];
+  unsigned fbuf[FAULTS ? G : 1][1];
+#pragma unroll
+  for (int j = 0; j < G; ++j) {
+#pragma unroll
+    for (int p = 0; p < A; ++p) tp_load<1>(dp + (long long)j * row + p * a.ld, *(long long(*)[1]) & buf[j][p]);
+    if constexpr (FAULTS) tp_load_fail<1>(fp + (long long)j * a.ld, fbuf[j]);
+  }
+#pragma unroll 1
+  for (int t = 0; t < count; t += G) {
+    const bool more = t + G < count;
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+      unsigned long long acc = (unsigned long long)buf[j][0];  // sqs/sqs.go:56-64, wrapping
+#pragma unroll
+      for (int p = 1; p < A; ++p) acc += (unsigned long long)buf[j][p];
+      const unsigned f = FAULTS ? fbuf[j][0] : 0u;
+      if (more) {
+#pragma unroll
+        for (int p = 0; p < A; ++p)
+          tp_load<1>(dp + (long long)(t + j + G) * row + p * a.ld, *(long long(*)[1]) & buf[j][p]);
+        if constexpr (FAULTS) tp_load_fail<1>(fp + (long long)(t + j + G) * a.ld, fbuf[j]);
+      }
+      if constexpr (FAULTS) ksa_step_faults_fma2<false, false>(c, (long long)acc, f, t + j + 1, one, s);
+      else ksa_step_fma_byte(c, (long long)acc, t + j + 1, one, s);
+    }
+  }
+  g.r = s.r;
+  g.ju = ksa_global_stamp(s.su, c.cu, B, g.ju);
+  g.jd = ksa_global_stamp(s.sd, c.cd, B, g.jd);
+}
+
+// ---- pass 0 --------------------------------------------------------------------------------------
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_sum_warm_kernel(const __grid_constant__ TpSumArgs a) {
+  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_tp_count = 0;  // pass 2a's list starts empty
+  if (n >= a.N) return;
+  const int k = blockIdx.y;
+  const ksa_step_consts c(a.pk);
+  TpG g{a.st_r[n], a.st_ju[n], a.st_jd[n]};
+  if (k > 0 && a.warm > 0) tp_sum_warm<A, FAULTS>(a, c, n, k * a.L - a.warm, a.warm, g);
+  const long long idx = (long long)k * a.N + n;
+  tp_put(a.io, idx, g);
+  tp_put(a.en, idx, g);
+  a.status[idx] = 0;
+  ksa_summary q;
+  tp_summary_clear(q);
+  a.part[idx] = q;
+}
+
+// ---- pass 2a -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) tp_sum_check_kernel(const __grid_constant__ TpSumArgs a) {
+  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  const int k = blockIdx.y + 1;
+  bool need = false;
+  if (n < a.N) {
+    const ksa_step_consts c(a.pk);
+    const long long idx = (long long)k * a.N + n;
+    need = !tp_same_future(a.pk, c, tp_get(a.io, idx - a.N), tp_get(a.en, idx), a.tick0 + (long long)k * a.L,
+                           a.T - k * a.L);
+  }
+  const unsigned vote = __ballot_sync(0xffffffffu, need);  // one atomic per warp
+  if (vote == 0u) return;
+  const int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == __ffs(vote) - 1) base = atomicAdd(&g_tp_count, __popc(vote));
+  base = __shfl_sync(0xffffffffu, base, __ffs(vote) - 1);
+  if (need) g_tp_list[base + __popc(vote & ((1u << lane) - 1u))] = (int)((long long)k * a.N + n);
+}
+
+// The stamp was taken inside ticks (B, B + len] (a stamp is the absolute tick it was taken at).
+__device__ __forceinline__ bool tp_taken(long long stamp, long long B, int len) { return stamp > B && stamp <= B + len; }
+
+// What a run of consecutive chunks adds up to. `m`, `h`: the run maps a fingerprint lane x to x * m + h.
+struct TpRun {
+  int any;  // the run has at least one chunk
+  int r;    // replicas after its last tick
+  int has_u, has_d;  // a stamp was taken inside the run
+  long long ju, jd;
+  int rmin, rmax;
+  unsigned cnt[9];
+  long long sum;
+  unsigned m_lo, h_lo, m_hi, h_hi;
+};
+__device__ __forceinline__ void tp_run_init(TpRun& x) {
+  x.any = x.r = x.has_u = x.has_d = 0;
+  x.ju = x.jd = 0;
+  x.rmin = INT_MAX;
+  x.rmax = INT_MIN;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) x.cnt[i] = 0u;
+  x.sum = 0;
+  x.m_lo = x.m_hi = 1u;
+  x.h_lo = x.h_hi = 0u;
+}
+// x followed by y
+__device__ __forceinline__ void tp_run_append(TpRun& x, const TpRun& y) {
+  if (y.any) {
+    x.any = 1;
+    x.r = y.r;
+  }
+  if (y.has_u) {
+    x.has_u = 1;
+    x.ju = y.ju;
+  }
+  if (y.has_d) {
+    x.has_d = 1;
+    x.jd = y.jd;
+  }
+  x.rmin = min(x.rmin, y.rmin);
+  x.rmax = max(x.rmax, y.rmax);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) x.cnt[i] += y.cnt[i];
+  x.sum = (long long)((unsigned long long)x.sum + (unsigned long long)y.sum);
+  x.h_lo = x.h_lo * y.m_lo + y.h_lo;
+  x.m_lo *= y.m_lo;
+  x.h_hi = x.h_hi * y.m_hi + y.h_hi;
+  x.m_hi *= y.m_hi;
+}
+// One chunk as a run: its record, the state it ended with, the tick before its first (B), its
+// length, and whether its stamps count wherever they were taken (chunk 0 carries the caller's own).
+__device__ __forceinline__ void tp_run_of_chunk(TpRun& x, const ksa_summary& q, const TpG& exit, long long B, int len,
+                                                bool whole, unsigned m_lo, unsigned m_hi) {
+  x.any = 1;
+  x.r = exit.r;
+  x.has_u = whole || tp_taken(exit.ju, B, len);
+  x.has_d = whole || tp_taken(exit.jd, B, len);
+  x.ju = exit.ju;
+  x.jd = exit.jd;
+  x.rmin = q.min_replicas;
+  x.rmax = q.max_replicas;
+  x.cnt[0] = q.up_applied;
+  x.cnt[1] = q.down_applied;
+  x.cnt[2] = q.up_noop;
+  x.cnt[3] = q.down_noop;
+  x.cnt[4] = q.up_cool;
+  x.cnt[5] = q.down_cool;
+  x.cnt[6] = q.poll_failed;
+  x.cnt[7] = q.up_failed;
+  x.cnt[8] = q.down_failed;
+  x.sum = q.sum_replicas;
+  x.m_lo = m_lo;
+  x.h_lo = (unsigned)q.hash;
+  x.m_hi = m_hi;
+  x.h_hi = (unsigned)(q.hash >> 32);
+}
+__device__ __forceinline__ long long tp_shfl_ll(long long v, int src) {
+  const int lo = __shfl_sync(0xffffffffu, (int)(unsigned)v, src);
+  const int hi = __shfl_sync(0xffffffffu, (int)((unsigned long long)v >> 32), src);
+  return (long long)(((unsigned long long)(unsigned)hi << 32) | (unsigned)lo);
+}
+__device__ __forceinline__ void tp_run_shfl(TpRun& y, const TpRun& x, int src) {
+  y.any = __shfl_sync(0xffffffffu, x.any, src);
+  y.r = __shfl_sync(0xffffffffu, x.r, src);
+  y.has_u = __shfl_sync(0xffffffffu, x.has_u, src);
+  y.has_d = __shfl_sync(0xffffffffu, x.has_d, src);
+  y.ju = tp_shfl_ll(x.ju, src);
+  y.jd = tp_shfl_ll(x.jd, src);
+  y.rmin = __shfl_sync(0xffffffffu, x.rmin, src);
+  y.rmax = __shfl_sync(0xffffffffu, x.rmax, src);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) y.cnt[i] = __shfl_sync(0xffffffffu, x.cnt[i], src);
+  y.sum = tp_shfl_ll(x.sum, src);
+  y.m_lo = __shfl_sync(0xffffffffu, x.m_lo, src);
+  y.h_lo = __shfl_sync(0xffffffffu, x.h_lo, src);
+  y.m_hi = __shfl_sync(0xffffffffu, x.m_hi, src);
+  y.h_hi = __shfl_sync(0xffffffffu, x.h_hi, src);
+}
+
+__device__ __forceinline__ TpG tp_shfl_g(const TpG& g, int src) {
+  return TpG{__shfl_sync(0xffffffffu, g.r, src), tp_shfl_ll(g.ju, src), tp_shfl_ll(g.jd, src)};
+}
+__device__ __forceinline__ unsigned tp_pow_u32(unsigned base, unsigned e) {
+  unsigned r = 1u;
+  for (; e; e >>= 1, base *= base)
+    if (e & 1u) r *= base;
+  return r;
+}
+// ---- pass 2b -------------------------------------------------------------------------------------
+// A listed chunk has to be replayed from its true entry state. One thread doing that alone needs the
+// whole chunk's ticks one after the other (a millisecond for 1350 ticks: twice pass 1). A warp does
+// it the way the call itself is done, one level down: the chunk is cut into up to 32 pieces of
+// a.piece ticks, lane 0 replays the first from the true entry state, every other lane warms up from
+// the guess before its piece and replays it; then the boundaries are checked in order, and a lane
+// whose entry state did not have the true future replays its piece again from its left neighbour's
+// exit state. Usually no boundary fails: warm-up + piece ticks of latency instead of the chunk's.
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_sum_fix_kernel(const __grid_constant__ TpSumArgs a) {
+  const int item = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
+  if (item >= g_tp_count) return;  // (whole warps)
+  const int lane = threadIdx.x & 31;
+  const long long idx = g_tp_list[item];
+  const int k = (int)(idx / a.N);
+  const long long n = idx % a.N;
+  const int t0 = k * a.L;
+  const int len = min(a.L, a.T - t0);
+  const ksa_step_consts c(a.pk);
+  const int pieces = (len + a.piece - 1) / a.piece;  // <= 32
+  const bool mine = lane < pieces;
+  const int first = t0 + lane * a.piece;             // my piece: ticks [first, first + count) of the call
+  const int count = mine ? min(a.piece, t0 + len - first) : 0;
+  const TpG entry0 = tp_get(a.io, idx - a.N);  // the previous chunk's exit state from pass 1: the chunk's entry
+  TpG g = entry0, used = entry0;
+  ksa_summary q;
+  tp_summary_clear(q);
+  if (mine) {
+    if (lane > 0) {
+      g = TpG{a.st_r[n], a.st_ju[n], a.st_jd[n]};
+      const int w = min(a.warm, first);
+      if (w > 0) tp_sum_warm<A, FAULTS>(a, c, n, first - w, w, g);
+      used = g;
+    }
+    tp_sum_replay<A, FAULTS>(a, c, n, first, count, g, &q);
+  }
+  for (int r = 0; r + 1 < pieces; ++r) {
+    const TpG left = tp_shfl_g(g, r);  // exit state of piece r: true by induction
+    bool redo = false;
+    if (lane == r + 1) redo = !tp_same_future(a.pk, c, left, used, a.tick0 + first, a.T - first);
+    if (__shfl_sync(0xffffffffu, (int)redo, r + 1) && lane == r + 1) {
+      g = used = left;
+      tp_summary_clear(q);
+      tp_sum_replay<A, FAULTS>(a, c, n, first, count, g, &q);
+    }
+  }
+  // the pieces in order -> the chunk
+  TpRun run;
+  tp_run_init(run);
+  if (mine) {
+    const long long B = a.tick0 + first;
+    tp_run_of_chunk(run, q, g, B, count, false, tp_pow_u32(KSA_HASH_MUL_LO, (unsigned)count),
+                    tp_pow_u32(KSA_HASH_MUL_HI, (unsigned)count));
+  }
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    TpRun other;
+    tp_run_shfl(other, run, min(lane + off, 31));
+    if ((lane & (2 * off - 1)) == 0 && lane + off < 32) tp_run_append(run, other);
+  }
+  if (lane != 0) return;
+  q.final_replicas = run.r;
+  q.min_replicas = run.rmin;
+  q.max_replicas = run.rmax;
+  q.up_applied = run.cnt[0];
+  q.down_applied = run.cnt[1];
+  q.up_noop = run.cnt[2];
+  q.down_noop = run.cnt[3];
+  q.up_cool = run.cnt[4];
+  q.down_cool = run.cnt[5];
+  q.poll_failed = run.cnt[6];
+  q.up_failed = run.cnt[7];
+  q.down_failed = run.cnt[8];
+  q.sum_replicas = run.sum;
+  q.hash = ((unsigned long long)run.h_hi << 32) | run.h_lo;
+  a.part[idx] = q;
+  const TpG exit{run.r, run.has_u ? run.ju : entry0.ju, run.has_d ? run.jd : entry0.jd};
+  tp_put(a.fx, idx, exit);
+  const bool last = k == a.K - 1;  // (nothing is judged by the last chunk's exit)
+  a.status[idx] =
+      last || tp_same_future(a.pk, c, exit, tp_get(a.io, idx), a.tick0 + t0 + len, a.T - t0 - len) ? 1 : -1;
+}
+
+// ---- pass 3 --------------------------------------------------------------------------------------
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_constant__ TpSumArgs a) {
+  const long long n = (long long)blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
+  if (n >= a.N) return;  // (whole warps)
+  const int lane = threadIdx.x & 31;
+  const ksa_step_consts c(a.pk);
+  const int per = (a.K + 31) / 32;
+  const int k0 = lane * per, k1 = min(a.K, k0 + per);
+  TpRun run;
+  tp_run_init(run);
+  bool fine = true;
+  for (int k = k0; k < k1; ++k) {
+    const long long idx = (long long)k * a.N + n;
+    const int status = a.status[idx];
+    fine = fine && status >= 0;
+    const bool last = k == a.K - 1;
+    TpRun one;
+    tp_run_of_chunk(one, a.part[idx], status != 0 ? tp_get(a.fx, idx) : tp_get(a.io, idx),
+                    a.tick0 + (long long)k * a.L, min(a.L, a.T - k * a.L), k == 0, last ? a.mE_lo : a.mL_lo,
+                    last ? a.mE_hi : a.mL_hi);
+    tp_run_append(run, one);
+  }
+  fine = __all_sync(0xffffffffu, fine);
+  if (fine) {
+    // every chunk was replayed from (the equivalent of) the true state: combine the lanes' runs in order
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      TpRun other;
+      tp_run_shfl(other, run, min(lane + off, 31));
+      if ((lane & (2 * off - 1)) == 0) tp_run_append(run, other);
+    }
+  } else if (lane == 0) {
+    // some chunk never met the true trajectory: walk the chunks in order with the true state
+    tp_run_init(run);
+    TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+    TpRun one;
+    tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
+    tp_run_append(run, one);
+    for (int k = 1; k < a.K; ++k) {
+      const long long idx = (long long)k * a.N + n;
+      const int t0 = k * a.L;
+      const int len = min(a.L, a.T - t0);
+      const long long B = a.tick0 + t0;
+      const bool last = k == a.K - 1;
+      const int status = a.status[idx];
+      const TpG used = status != 0 ? tp_get(a.io, idx - a.N) : tp_get(a.en, idx);  // what the record was replayed from
+      if (tp_same_future(a.pk, c, used, cur, B, a.T - t0)) {
+        const TpG exit = status != 0 ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+        tp_run_of_chunk(one, a.part[idx], exit, B, len, false, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
+        cur.r = exit.r;
+        cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
+        cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
+      } else {
+        ksa_summary q;
+        tp_summary_clear(q);
+        tp_sum_replay<A, FAULTS>(a, c, n, t0, len, cur, &q);
+        tp_run_of_chunk(one, q, cur, B, len, true, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
+      }
+      tp_run_append(run, one);
+    }
+  }
+  if (lane != 0) return;
+  // add the call to the caller's record (a read-modify-write: calls accumulate) and write the state back
+  ksa_summary q = a.summary[n];
+  q.final_replicas = run.r;
+  q.min_replicas = min(q.min_replicas, run.rmin);
+  q.max_replicas = max(q.max_replicas, run.rmax);
+  q.up_applied += run.cnt[0];
+  q.down_applied += run.cnt[1];
+  q.up_noop += run.cnt[2];
+  q.down_noop += run.cnt[3];
+  q.up_cool += run.cnt[4];
+  q.down_cool += run.cnt[5];
+  q.poll_failed += run.cnt[6];
+  q.up_failed += run.cnt[7];
+  q.down_failed += run.cnt[8];
+  q.sum_replicas = (long long)((unsigned long long)q.sum_replicas + (unsigned long long)run.sum);
+  const unsigned lo = (unsigned)q.hash * run.m_lo + run.h_lo;
+  const unsigned hi = (unsigned)(q.hash >> 32) * run.m_hi + run.h_hi;
+  q.hash = ((unsigned long long)hi << 32) | lo;
+  a.summary[n] = q;
+  a.st_r[n] = run.r;
+  a.st_ju[n] = run.ju;  // (chunk 0 always carries a stamp: has_u / has_d are set)
+  a.st_jd[n] = run.jd;
+}
+
 // One time-parallel replay per device at a time (the scratch is shared): `busy` is recorded after
 // the last launch of a call and queried by the next one.
 constexpr int kMaxDevices = 64;
 std::mutex g_tp_mutex;
 cudaEvent_t g_tp_busy[kMaxDevices] = {};
 cudaStream_t g_tp_stream[kMaxDevices] = {};  // stream of the call that recorded `busy`
+char* g_tp_scratch_addr[kMaxDevices] = {};   // device addresses of the two scratch arrays (host code only has
+ksa_summary* g_tp_partial_addr[kMaxDevices] = {};  // stand-ins for them: cudaGetSymbolAddress, once per device)
 
-template <int A>
+// Takes the scratch of the current device for a call on `st`. Returns KSA_OK with the device index, an
+// error, or 1: the scratch is in use by an earlier call on another stream, or `st` is being captured.
+// The caller holds g_tp_mutex and calls tp_release after its last launch.
+int tp_acquire(cudaStream_t st, int* device_out) {
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) {
+    cudaGetLastError();
+    return 1;
+  }
+  if (cap != cudaStreamCaptureStatusNone) return 1;
+  int device = -1;
+  KSA_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= kMaxDevices) return 1;
+  if (!g_tp_busy[device]) {
+    KSA_CUDA(cudaEventCreateWithFlags(&g_tp_busy[device], cudaEventDisableTiming));
+  } else if (cudaEventQuery(g_tp_busy[device]) != cudaSuccess) {
+    cudaGetLastError();
+    // On the same stream the new call is ordered behind the old one anyway; on another stream the
+    // two would overlap on the scratch: plain path.
+    if (st != g_tp_stream[device]) return 1;
+  }
+  *device_out = device;
+  return KSA_OK;
+}
+int tp_release(cudaStream_t st, int device) {
+  KSA_CUDA(cudaEventRecord(g_tp_busy[device], st));
+  g_tp_stream[device] = st;
+  return KSA_OK;
+}
+
+template <int A, bool FAULTS>
 int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
-  if (wide) {  // 8 traces per thread, the launch shape of the main kernel's default
-    constexpr int TPB = 256;
-    const unsigned gx = (unsigned)((a.N / 8 + TPB - 1) / TPB);
-    tp_spec_kernel<A, 8, A == 1 ? 2 : 1, TPB, A == 1 ? 2 : 1><<<dim3(gx, (unsigned)a.K), TPB, 0, st>>>(a);
+  if (wide) {
+    if constexpr (FAULTS) {
+      // 4 traces per thread, the shape of ksa_replay_full_faults' default: with eight interleaved the
+      // failure-aware step runs out of issue slots (1.68 ms against 0.94 without a mask at 4096 x 10^5)
+      const unsigned gx = (unsigned)((a.N / 4 + BLOCK - 1) / BLOCK);
+      tp_spec_kernel<A, 4, A == 1 ? 4 : (A == 2 ? 2 : 1), BLOCK, A == 3 ? 4 : 5, true><<<dim3(gx, (unsigned)a.K), BLOCK, 0, st>>>(a);
+    } else {  // 8 traces per thread, the launch shape of the main kernel's default
+      constexpr int TPB = 256;
+      const unsigned gx = (unsigned)((a.N / 8 + TPB - 1) / TPB);
+      tp_spec_kernel<A, 8, A == 1 ? 2 : 1, TPB, A == 1 ? 2 : 1, false><<<dim3(gx, (unsigned)a.K), TPB, 0, st>>>(a);
+    }
   } else {
     const unsigned gx = (unsigned)((a.N + BLOCK - 1) / BLOCK);
-    tp_spec_kernel<A, 1, 8, BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4)><<<dim3(gx, (unsigned)a.K), BLOCK, 0, st>>>(a);
+    tp_spec_kernel<A, 1, 8, BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4), FAULTS><<<dim3(gx, (unsigned)a.K), BLOCK, 0, st>>>(a);
   }
   KSA_LAUNCH_CHECK("tp_spec_kernel");
   const unsigned gn = (unsigned)((a.N + BLOCK - 1) / BLOCK);
   tp_check_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_check_kernel");
   const long long items = a.N * (a.K - 1);  // (the list's length is only known on the device: idle threads return at once)
-  tp_fix_kernel<A><<<(unsigned)((items + BLOCK - 1) / BLOCK), BLOCK, 0, st>>>(a);
+  tp_fix_kernel<A, FAULTS><<<(unsigned)((items + BLOCK - 1) / BLOCK), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_fix_kernel");
-  tp_chain_kernel<A><<<gn, BLOCK, 0, st>>>(a);
+  tp_chain_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_chain_kernel");
   return KSA_OK;
+}
+
+template <int A, bool FAULTS>
+int tp_sum_launch(const TpSumArgs& a, bool ordered, cudaStream_t st) {
+  const unsigned gn = (unsigned)((a.N + BLOCK - 1) / BLOCK);
+  tp_sum_warm_kernel<A, FAULTS><<<dim3(gn, (unsigned)a.K), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_sum_warm_kernel");
+  const int rc = ksa_replay_summary_chunks(a.pk, ordered, (const int64_t*)a.depth, a.fail, a.L, a.T, A, a.N, a.ld, a.tick0,
+                                           a.K, a.io.r, (int64_t*)a.io.ju, (int64_t*)a.io.jd, a.part, st);
+  if (rc != KSA_OK) return rc;
+  tp_sum_check_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_sum_check_kernel");
+  // (the list's length is only known on the device: a warp per possible item, idle warps return at once)
+  const long long items = a.N * (a.K - 1);
+  const long long warps_per_block = BLOCK / 32;
+  tp_sum_fix_kernel<A, FAULTS><<<(unsigned)((items + warps_per_block - 1) / warps_per_block), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_sum_fix_kernel");
+  tp_sum_chain_kernel<A, FAULTS><<<(unsigned)((a.N + warps_per_block - 1) / warps_per_block), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_sum_chain_kernel");
+  return KSA_OK;
+}
+
+unsigned pow_u32(unsigned base, unsigned e) {
+  unsigned r = 1u;
+  for (; e; e >>= 1, base *= base)
+    if (e & 1u) r *= base;
+  return r;
 }
 
 }  // namespace
 
 // How the time-parallel replay would cut this call: chunks K (0 = take the plain kernels: too many
 // traces to gain, too few ticks, or no room in the scratch), ticks per chunk L, warm-up ticks, and
-// whether pass 1 can run 8 traces per thread (`vector_ok`: the layout the vector kernels need and N
-// a multiple of 8). Environment, for tests and measurements: KSA_TIMEPAR_CHUNKS=<K> forces K chunks
-// whenever that is possible at all (0 turns the path off), KSA_TIMEPAR_WARM=<ticks> the warm-up,
-// KSA_TIMEPAR_WIDE=0 one trace per thread.
-int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm_out, int* wide_out) {
+// whether pass 1 can run several traces per thread (`vector_ok`: full mode with the layout the vector
+// kernels need and N a multiple of 8; summary mode runs one trace per thread). Environment, for
+// tests and measurements: KSA_TIMEPAR_CHUNKS=<K> forces K chunks whenever that is possible at all
+// (0 turns the path off), KSA_TIMEPAR_WARM=<ticks> the warm-up, KSA_TIMEPAR_WIDE=0 one trace per thread.
+int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vector_ok, int* L_out, int* warm_out,
+                     int* wide_out) {
   int forced = -1;
   if (const char* e = std::getenv("KSA_TIMEPAR_CHUNKS")) forced = std::atoi(e);
   if (forced == 0) return 0;
-  bool wide = vector_ok;
+  bool wide = vector_ok && !summary;
   if (const char* e = std::getenv("KSA_TIMEPAR_WIDE")) wide = wide && std::atoi(e) != 0;
   int warm = 128;  // profiles/r02_small_n.txt: 0.80 of the copy peak at 4096 x 10^5 against 0.78 with 64, 0.68 with none
   if (const char* e = std::getenv("KSA_TIMEPAR_WARM")) warm = std::max(0, std::atoi(e)) / 8 * 8;
@@ -445,12 +1075,28 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm
     K = forced;
     if (K < 2 || (T + K - 1) / K < 16) return 0;
   } else {
-    // One trace per thread fills the GPU at about 2^18 threads, eight per thread (1-KB requests, the
-    // shape that reaches the copy peak) at about 400k trace-chunks (profiles/r01_small_n_variants.txt).
+    if (T < 4096) return 0;
+    const long long kSMs = 148;
+    if (summary || (faults && wide)) {
+      // Pass 1 runs blocks of 128 threads (one trace each; with a mask in full mode four each), 8 per SM
+      // (7 / 5 with a failure mask): K is the largest count whose grid fills whole waves of those
+      // slots: a grid of 2.3 waves takes as long as one of 3 (profiles/r02_small_n_modes.txt).
+      const long long per_block = summary ? 128 : 512;
+      const long long slots = kSMs * (summary ? (faults ? 7 : 8) : 5);
+      const long long waves = summary ? 2 : 1;
+      const long long blocks_x = (N + per_block - 1) / per_block;
+      if (summary ? N > (faults ? kTpMaxSummaryFaults : kTpMaxSummary)
+                  : (N > kTpMaxFullFaults && N <= kTpFullFaultsSecondWave))
+        return 0;
+      K = waves * slots / blocks_x;
+    } else {
+      // One trace per thread fills the GPU at about 2^18 threads, eight per thread (1-KB requests, the
+      // shape that reaches the copy peak) at about 400k trace-chunks (profiles/r01_small_n_variants.txt).
+      if (N > 196608) return 0;
+      const long long want = wide ? 393216 : 262144;
+      K = (want + N - 1) / N;
+    }
     // Chunks of at least 8 x warm ticks keep the warm-up and the re-replayed prefixes small.
-    if (N > 196608 || T < 4096) return 0;
-    const long long want = wide ? 393216 : 262144;
-    K = (want + N - 1) / N;
     const long long kmax = T / (8 * std::max(warm, 64));
     if (K > kmax) K = kmax;
     if (K > 512) K = 512;
@@ -466,33 +1112,21 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool vector_ok, int* L_out, int* warm
   return (int)K;
 }
 
-// ksa_replay_full for (T, N) with both outputs and no failure mask, in K chunks per trace. Returns
-// KSA_OK, an error, or 1 if the scratch is in use by an earlier call on another stream of this
-// device (or the stream is being captured): the caller then takes the plain path.
-int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, int64_t T, int32_t A, int64_t N,
-                            int64_t ld, int64_t tick0, const ksa_state* state, int32_t* replicas_dev,
-                            uint8_t* events_dev, int K, int L, int warm, int wide, cudaStream_t st) {
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) {
-    cudaGetLastError();
-    return 1;
-  }
-  if (cap != cudaStreamCaptureStatusNone) return 1;
-  int device = -1;
-  KSA_CUDA(cudaGetDevice(&device));
-  if (device < 0 || device >= kMaxDevices) return 1;
+// ksa_replay_full / ksa_replay_full_faults (fail_dev != NULL) for (T, N) with both outputs, in K
+// chunks per trace. Returns KSA_OK, an error, or 1 if the scratch is in use by an earlier call on
+// another stream of this device (or the stream is being captured): the caller then takes the plain path.
+int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, const uint8_t* fail_dev, int64_t T,
+                            int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                            int32_t* replicas_dev, uint8_t* events_dev, int K, int L, int warm, int wide,
+                            cudaStream_t st) {
   std::lock_guard<std::mutex> lock(g_tp_mutex);
-  if (!g_tp_busy[device]) {
-    KSA_CUDA(cudaEventCreateWithFlags(&g_tp_busy[device], cudaEventDisableTiming));
-  } else if (cudaEventQuery(g_tp_busy[device]) != cudaSuccess) {
-    cudaGetLastError();
-    // On the same stream the new call is ordered behind the old one anyway; on another stream the
-    // two would overlap on the scratch: plain path.
-    if (st != g_tp_stream[device]) return 1;
-  }
+  int device = -1;
+  int rc = tp_acquire(st, &device);
+  if (rc != KSA_OK) return rc;
   TpArgs a;
   a.pk = pk;
   a.depth = (const long long*)depth_dev;
+  a.fail = fail_dev;
   a.ld = ld;
   a.tick0 = tick0;
   a.N = N;
@@ -507,9 +1141,76 @@ int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, in
   a.st_jd = (long long*)state->last_down_tick_dev;
   a.replicas = replicas_dev;
   a.events = events_dev;
-  int rc = A == 1 ? tp_launch<1>(a, wide != 0, st) : A == 2 ? tp_launch<2>(a, wide != 0, st) : tp_launch<3>(a, wide != 0, st);
+  const bool w = wide != 0;
+  if (fail_dev)
+    rc = A == 1 ? tp_launch<1, true>(a, w, st) : A == 2 ? tp_launch<2, true>(a, w, st) : tp_launch<3, true>(a, w, st);
+  else
+    rc = A == 1 ? tp_launch<1, false>(a, w, st) : A == 2 ? tp_launch<2, false>(a, w, st) : tp_launch<3, false>(a, w, st);
   if (rc != KSA_OK) return rc;
-  KSA_CUDA(cudaEventRecord(g_tp_busy[device], st));
-  g_tp_stream[device] = st;
-  return KSA_OK;
+  return tp_release(st, device);
+}
+
+// ksa_replay_summary / ksa_replay_summary_faults (fail_dev != NULL) in K chunks per trace; returns as above.
+int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
+                               int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
+                               ksa_summary* summary_dev, int K, int L, int warm, cudaStream_t st) {
+  std::lock_guard<std::mutex> lock(g_tp_mutex);
+  int device = -1;
+  int rc = tp_acquire(st, &device);
+  if (rc != KSA_OK) return rc;
+  if (!g_tp_scratch_addr[device]) {
+    // In host code the arrays' names are not device addresses: ask the runtime, with this device current.
+    void* p = nullptr;
+    void* q = nullptr;
+    KSA_CUDA(cudaGetSymbolAddress(&p, g_tp_scratch));
+    KSA_CUDA(cudaGetSymbolAddress(&q, g_tp_partial));
+    g_tp_scratch_addr[device] = (char*)p;
+    g_tp_partial_addr[device] = (ksa_summary*)q;
+  }
+  TpSumArgs a;
+  a.pk = pk;
+  a.depth = (const long long*)depth_dev;
+  a.fail = fail_dev;
+  a.ld = ld;
+  a.tick0 = tick0;
+  a.N = N;
+  a.T = (int)T;
+  a.A = A;
+  a.K = K;
+  a.L = L;
+  a.warm = warm;
+  a.one = 1;
+  a.piece = std::max(16, ((L + 31) / 32 + 7) / 8 * 8);
+  const int lenE = (int)(T - (int64_t)(K - 1) * L);
+  a.mL_lo = pow_u32(KSA_HASH_MUL_LO, (unsigned)L);
+  a.mL_hi = pow_u32(KSA_HASH_MUL_HI, (unsigned)L);
+  a.mE_lo = pow_u32(KSA_HASH_MUL_LO, (unsigned)lenE);
+  a.mE_hi = pow_u32(KSA_HASH_MUL_HI, (unsigned)lenE);
+  a.st_r = state->replicas_dev;
+  a.st_ju = (long long*)state->last_up_tick_dev;
+  a.st_jd = (long long*)state->last_down_tick_dev;
+  a.summary = summary_dev;
+  // the 64 bytes per slot of g_tp_scratch, as arrays over the kMaxChunks slots
+  char* base = g_tp_scratch_addr[device];
+  const size_t M = (size_t)kMaxChunks;
+  auto carry = [&](size_t off) {
+    TpCarry c;
+    c.r = (int*)(base + off * M);
+    c.ju = (long long*)(base + (off + 4) * M);
+    c.jd = (long long*)(base + (off + 12) * M);
+    return c;
+  };
+  a.io = carry(0);
+  a.en = carry(20);
+  a.fx = carry(40);
+  a.status = (int*)(base + 60 * M);
+  a.part = g_tp_partial_addr[device];
+  if (fail_dev)
+    rc = A == 1 ? tp_sum_launch<1, true>(a, ordered, st)
+                : A == 2 ? tp_sum_launch<2, true>(a, ordered, st) : tp_sum_launch<3, true>(a, ordered, st);
+  else
+    rc = A == 1 ? tp_sum_launch<1, false>(a, ordered, st)
+                : A == 2 ? tp_sum_launch<2, false>(a, ordered, st) : tp_sum_launch<3, false>(a, ordered, st);
+  if (rc != KSA_OK) return rc;
+  return tp_release(st, device);
 }

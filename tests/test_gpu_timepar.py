@@ -1,9 +1,10 @@
-"""Full-trajectory replay with the time axis cut into chunks (csrc/ksa_timepar.cu): the path
-ksa_replay_full takes by itself when the traces are too few to fill the GPU. It must give exactly
-what the sequential replay gives whatever the number of chunks and whether or not the speculative
-chunks ever converge to the true trajectory, so the chunk count is forced here
-(KSA_TIMEPAR_CHUNKS) on small cases: random adversarial policies, and traces built never to
-converge. Everything against the CPU oracle, through the C ABI, bit for bit."""
+"""Replay with the time axis cut into chunks (csrc/ksa_timepar.cu): the path the four replay entry
+points (full / summary, with or without a failure mask) take by themselves when the traces are too
+few to fill the GPU. It must give exactly what the sequential replay gives whatever the number of
+chunks and whether or not the speculative chunks ever converge to the true trajectory, so the chunk
+count is forced here (KSA_TIMEPAR_CHUNKS) on small cases: random adversarial policies, and traces
+built never to converge. Every case goes through the full and the summary entry point. Everything
+against the CPU oracle, through the C ABI, bit for bit."""
 from __future__ import annotations
 
 import os
@@ -20,6 +21,7 @@ pytestmark = pytest.mark.gpu
 
 
 TP_LAUNCHES = 4  # pass 1, 2a, 2b, 3
+TP_SUMMARY_LAUNCHES = 5  # pass 0 (entry states), 1, 2a, 2b, 3
 
 
 def chunks_used(T, chunks):
@@ -30,12 +32,14 @@ def chunks_used(T, chunks):
     return (T + L - 1) // L
 
 
-def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, warm=None, wide=None):
-    """Replay with `chunks` forced (None = the library's own choice); returns the launches it took."""
+def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, warm=None, wide=None, fail=None):
+    """Full and summary replay with `chunks` forced (None = the library's own choice), `fail` = a
+    [T][ld] failure mask for the *_faults entry points; returns the launches the full replay took."""
     import torch
 
-    ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st)
+    ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st, want_summary=True, fail=fail)
     d = torch.from_numpy(np.ascontiguousarray(depth)).to(engine.dev)
+    f = None if fail is None else torch.from_numpy(np.ascontiguousarray(fail, dtype=np.uint8)).to(engine.dev)
     for key, val in (("KSA_TIMEPAR_CHUNKS", chunks), ("KSA_TIMEPAR_WARM", warm), ("KSA_TIMEPAR_WIDE", wide)):
         if val is None:
             os.environ.pop(key, None)
@@ -44,19 +48,38 @@ def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, war
     try:
         state = engine.state_from_host(*st)
         engine.launch_count()
-        r, e = engine.replay_full(pol, d, T, A, N, ld, tick0, state)
+        r, e = engine.replay_full(pol, d, T, A, N, ld, tick0, state, fail=f)
         launches = engine.launch_count()
         r, e = r.cpu().numpy(), e.cpu().numpy()
+        state2 = engine.state_from_host(*st)
+        summ = engine.new_summary(N)
+        engine.launch_count()
+        engine.replay_summary(pol, d, T, A, N, ld, tick0, state2, summary=summ, fail=f)
+        launches_summary = engine.launch_count()
+        summ = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
     finally:
         for key in ("KSA_TIMEPAR_CHUNKS", "KSA_TIMEPAR_WARM", "KSA_TIMEPAR_WIDE"):
             os.environ.pop(key, None)
     where = np.argwhere(r[:, :N] != ref.replicas[:, :N])
     assert where.size == 0, f"{label}: replicas differ first at (tick, trace) {where[0]} of {where.shape[0]}"
     assert np.array_equal(e[:, :N], ref.events[:, :N]), f"{label}: events differ"
-    assert np.array_equal(state.replicas.cpu().numpy(), ref.state_replicas), f"{label}: carry replicas differ"
-    assert np.array_equal(state.last_up.cpu().numpy(), ref.state_last_up), f"{label}: last_up differs"
-    assert np.array_equal(state.last_down.cpu().numpy(), ref.state_last_down), f"{label}: last_down differs"
+    for name, s in (("full", state), ("summary", state2)):
+        assert np.array_equal(s.replicas.cpu().numpy(), ref.state_replicas), f"{label}: {name}: carry replicas differ"
+        assert np.array_equal(s.last_up.cpu().numpy(), ref.state_last_up), f"{label}: {name}: last_up differs"
+        assert np.array_equal(s.last_down.cpu().numpy(), ref.state_last_down), f"{label}: {name}: last_down differs"
+    if summ.tobytes() != ref.summary.tobytes():
+        for field in ksa.SUMMARY_DTYPE.names:
+            bad = np.flatnonzero(summ[field] != ref.summary[field])
+            assert bad.size == 0, (f"{label}: summary field {field} differs for {bad.size} traces, first {bad[0]}: "
+                                   f"{summ[field][bad[0]]} != {ref.summary[field][bad[0]]}")
+    if chunks is not None and chunks_used(T, chunks) >= 2:
+        assert launches_summary == TP_SUMMARY_LAUNCHES, f"{label}: the summary replay did not use the forced chunk count"
     return launches
+
+
+def random_mask(rng, T, ld, p=0.08):
+    """KSA_FAIL_* bits, each set with probability p."""
+    return ((rng.random((T, ld)) < p) * 1 + (rng.random((T, ld)) < p) * 2 + (rng.random((T, ld)) < p) * 4).astype(np.uint8)
 
 
 @pytest.mark.parametrize("A", [1, 2, 3])
@@ -70,11 +93,12 @@ def test_random_policies_any_chunk_count(engine, A):
         tick0 = int(rng.choice([0, 0, 23, 10**6, 2**40]))
         depth = adversarial_depth(rng, T, A, ld, pol)
         st = random_state(rng, N, tick0)
+        fail = random_mask(rng, T, ld) if case % 3 == 0 else None  # the *_faults entry points
         for chunks in (2, 3, 5, 16):
             for warm, wide in ((None, None), (0, 1), (8, 0), (40, 1)):
                 took = run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks,
-                                     f"A={A} case {case} T={T} N={N} ld={ld} chunks={chunks} warm={warm} wide={wide} {pol}",
-                                     warm=warm, wide=wide)
+                                     f"A={A} case {case} T={T} N={N} ld={ld} chunks={chunks} warm={warm} wide={wide} "
+                                     f"mask={fail is not None} {pol}", warm=warm, wide=wide, fail=fail)
                 if chunks_used(T, chunks) >= 2:
                     assert took == TP_LAUNCHES, "the forced chunk count was not used"
 
@@ -114,6 +138,8 @@ def _never_converging_cases(engine, rng, T, N):
                 for warm in (None, 0, 16):
                     run_and_check(engine, pol, depth, T, 1, N, N, tick0, st, chunks,
                                   f"{name} tick0={tick0} chunks={chunks} warm={warm}", warm=warm)
+            run_and_check(engine, pol, depth, T, 1, N, N, tick0, st, 7, f"{name} tick0={tick0} with failures",
+                          warm=16, fail=random_mask(rng, T, N, 0.2))
 
 
 def test_every_checkpoint_and_the_automatic_choice(engine):
@@ -139,4 +165,58 @@ def test_every_checkpoint_and_the_automatic_choice(engine):
     depth = oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, N)
     st = oracle_lib.fresh_state(gen.seed, 0, N, 1, 5)
     assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, None, "automatic, 4096 x 8192") == TP_LAUNCHES
+    fail = oracle_lib.gen_faults(7, 5, 4, 4, 0, T, 0, N, N)
+    assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, None, "automatic, 4096 x 8192, failures",
+                         fail=fail) == TP_LAUNCHES
     assert run_and_check(engine, pol, depth[:512], 512, 1, N, N, 0, st, None, "automatic, 4096 x 512") <= 2
+
+
+def test_summary_calls_accumulate_across_chunked_calls(engine):
+    """ksa_replay_summary adds to the records it is given: two calls, each cut into chunks of its
+    own, must leave what one sequential replay of all ticks leaves (counters, sum, min / max, and the
+    fingerprint continued from the first call's)."""
+    import torch
+
+    rng = np.random.default_rng(77)
+    for A, fail_p in ((1, None), (3, 0.1)):
+        pol = random_policy(rng, A)
+        T1, T2, N, tick0 = 330, 270, 200, 17
+        T = T1 + T2
+        depth = adversarial_depth(rng, T, A, N, pol)
+        fail = None if fail_p is None else random_mask(rng, T, N, fail_p)
+        st = random_state(rng, N, tick0)
+        ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, N, tick0, *st, want_summary=True, fail=fail)
+        d = torch.from_numpy(np.ascontiguousarray(depth)).to(engine.dev)
+        f = None if fail is None else torch.from_numpy(fail).to(engine.dev)
+        os.environ["KSA_TIMEPAR_CHUNKS"] = "4"
+        os.environ["KSA_TIMEPAR_WARM"] = "16"
+        try:
+            state = engine.state_from_host(*st)
+            summ = engine.new_summary(N)
+            engine.launch_count()
+            engine.replay_summary(pol, d[:T1], T1, A, N, N, tick0, state, summary=summ, fail=None if f is None else f[:T1])
+            assert engine.launch_count() == TP_SUMMARY_LAUNCHES
+            engine.replay_summary(pol, d[T1:], T2, A, N, N, tick0 + T1, state, summary=summ,
+                                  fail=None if f is None else f[T1:])
+        finally:
+            os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+            os.environ.pop("KSA_TIMEPAR_WARM", None)
+        got = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
+        assert got.tobytes() == ref.summary.tobytes(), f"A={A}: accumulated summary differs"
+        assert np.array_equal(state.replicas.cpu().numpy(), ref.state_replicas)
+        assert np.array_equal(state.last_up.cpu().numpy(), ref.state_last_up)
+        assert np.array_equal(state.last_down.cpu().numpy(), ref.state_last_down)
+
+
+def test_replica_counts_beyond_the_32_bit_window_in_chunks(engine):
+    """The summary kernel's 32-bit window sum falls back to an exact recomputation when replica
+    counts leave +-2^26 (ksa_summary_acc); in a chunked call that recomputation starts from the
+    chunk's own entry state."""
+    rng = np.random.default_rng(3)
+    T, N = 320, 96
+    pol = ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=2 * 5 * S, max_pods=2**31 - 1,
+                     min_pods=-(2**31), scale_up_pods=2**27 + 5, scale_down_pods=2**25)
+    depth = np.ascontiguousarray(rng.integers(0, 400, size=(T, 1, N)), dtype=np.int64)
+    st = (rng.integers(-5, 9, size=N).astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+    for chunks in (2, 5):
+        run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"wide replica counts, chunks={chunks}", warm=8)

@@ -1,12 +1,13 @@
 #!/usr/bin/env python
-"""Full-trajectory replay at trace counts that do not fill the GPU: plain kernels against the
-time-parallel path (csrc/ksa_timepar.cu), one line per (traces, ticks, chunks).
+"""Replay at trace counts that do not fill the GPU: plain kernels against the time-parallel path
+(csrc/ksa_timepar.cu), one line per (traces, ticks, chunks).
 
-    python tools/small_n.py [--chunks 0,auto,2,4,...]
+    python tools/small_n.py [--mode full|summary|full_faults|summary_faults] [--chunks 0,auto,2,4,...]
 
-CUDA events around the call (three launches on the time-parallel path), best of 4 after 2 warm-ups;
-13 B per decision against the measured copy peak. The trajectory fingerprint of every variant is
-compared with the plain kernels'."""
+CUDA events around the call (four or five launches on the time-parallel path), best of 4 after 2
+warm-ups; 13 B per decision in full mode, 8 in summary mode, one more with a failure mask, against
+the measured copy peak. The outputs of every variant (trajectory fingerprint or the summary
+records, and the carry state) are compared with the plain kernels'."""
 from __future__ import annotations
 
 import argparse
@@ -26,6 +27,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shapes", default="4096x100000,16384x40000,65536x10000,98304x10000,131072x10000")
     ap.add_argument("--chunks", default="0,auto,2,4,8,16,32,64,128")
+    ap.add_argument("--mode", default="full", choices=["full", "summary", "full_faults", "summary_faults"])
+    ap.add_argument("--warm", default="", help="comma list of KSA_TIMEPAR_WARM values to try (default: the library's)")
     args = ap.parse_args()
     try:
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
@@ -40,12 +43,19 @@ def main():
         replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
         events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
         state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
+        summary_mode = args.mode.startswith("summary")
+        fail = eng.gen_faults(gen.seed, 5, 4, 4, 0, T, 0, N, N) if args.mode.endswith("faults") else None
+        bytes_per = (8 if summary_mode else 13) + (1 if fail is not None else 0)
         ref = None
-        for ch in args.chunks.split(","):
+        for ch, warm in [(c, w) for c in args.chunks.split(",") for w in (args.warm.split(",") if args.warm else [""])]:
             if ch == "auto":
                 os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
             else:
                 os.environ["KSA_TIMEPAR_CHUNKS"] = ch
+            if warm:
+                os.environ["KSA_TIMEPAR_WARM"] = warm
+            else:
+                os.environ.pop("KSA_TIMEPAR_WARM", None)
             ts = []
             launches = 0
             for rep in range(6):
@@ -54,22 +64,28 @@ def main():
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 eng.launch_count()
                 a.record()
-                eng.replay_full(pol, depth, T, 1, N, N, 0, st, replicas=replicas, events=events)
+                if summary_mode:
+                    summ = eng.new_summary(N)
+                    a.record()
+                    eng.replay_summary(pol, depth, T, 1, N, N, 0, st, summary=summ, fail=fail)
+                else:
+                    eng.replay_full(pol, depth, T, 1, N, N, 0, st, replicas=replicas, events=events, fail=fail)
                 b.record()
                 torch.cuda.synchronize()
                 launches = eng.launch_count()
                 if rep >= 2:
                     ts.append(a.elapsed_time(b))
-            h = eng.traj_hash(replicas, events, T, N, N)
+            h = summ if summary_mode else eng.traj_hash(replicas, events, T, N, N)
             hs = (h, st.replicas.clone(), st.last_up.clone(), st.last_down.clone())
             if ref is None:
                 ref = hs
             same = all(bool(torch.equal(x, y)) for x, y in zip(hs, ref))
             ms = min(ts)
-            gbs = 13 * N * T / (ms * 1e-3) / 1e9
-            print(f"N={N:7d} T={T:6d} chunks={ch:>4s} launches={launches} {ms:8.3f} ms {N * T / (ms * 1e-3):.3e} decisions/s "
+            gbs = bytes_per * N * T / (ms * 1e-3) / 1e9
+            print(f"{args.mode} N={N:7d} T={T:6d} chunks={ch:>4s} warm={warm or '-':>3s} launches={launches} {ms:8.3f} ms {N * T / (ms * 1e-3):.3e} decisions/s "
                   f"{gbs:7.1f} GB/s frac={gbs / peak:5.3f} same_as_plain={same}", flush=True)
         os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+        os.environ.pop("KSA_TIMEPAR_WARM", None)
         del depth, replicas, events
 
 
