@@ -21,7 +21,7 @@
  *    the host heap (ksa_dev_alloc / ksa_host_alloc and ksa_pipeline_create are the allocating
  *    helpers). Two fixed arrays live in the library's device image on every GPU that loads it:
  *    the policy table of ksa_replay_sweep_static (192 KB) and the scratch records of the
- *    time-parallel path of ksa_replay_full (34 MB, see there).
+ *    time-parallel paths of the four replay entry points (66 MB, see ksa_replay_full).
  *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
  *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
  *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.
@@ -208,10 +208,12 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  * Few traces, many ticks (N <= 196608, T >= 4096, both outputs wanted): one thread per trace cannot
  * fill the GPU, so the library cuts the time axis into chunks that are replayed in parallel from
  * guessed states and then stitched exactly (csrc/ksa_timepar.cu; results are identical, the
- * trajectory and the carry state bit for bit). That path keeps its per-chunk records in a fixed
- * scratch array inside the library, so only one such call runs per GPU at a time: a call that
- * finds the scratch in use by a call on another stream, or a stream that is being captured, takes
- * the one-thread-per-trace kernels instead (same results, slower).
+ * trajectory and the carry state bit for bit). ksa_replay_summary and the two *_faults entry points
+ * do the same below their own trace counts (65536, 49152 / 81920): there the chunks' summary
+ * records, including the fingerprint, are combined in tick order. That path keeps its per-chunk
+ * records in fixed scratch arrays inside the library, so only one such call runs per GPU at a
+ * time: a call that finds the scratch in use by a call on another stream, or a stream that is being
+ * captured, takes the one-thread-per-trace kernels instead (same results, slower).
  */
 int ksa_replay_full(const ksa_policy* policy, const int64_t* depth_dev, int64_t T, int32_t A,
                     int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,

@@ -1,5 +1,5 @@
-// ksa_timepar.cu — full-trajectory replay for trace counts that cannot fill the GPU: the time axis
-// is cut into K chunks per trace and the chunks are replayed in parallel.
+// ksa_timepar.cu — replay for trace counts that cannot fill the GPU: the time axis is cut into K
+// chunks per trace and the chunks are replayed in parallel. First the full-trajectory replay.
 //
 // One thread per trace is bound by its own dependent chain (about 41 instructions per tick, one
 // after the other) once there are fewer traces than the GPU has thread slots: 4096 traces are 128
@@ -37,9 +37,15 @@
 // 1's trajectory is the true one; stamps taken during the warm-up never do).
 //
 // Scratch: one 64-byte record per (trace, chunk) and a 4-byte list slot, in fixed device arrays of
-// the library image (kMaxChunks records: 34 MB per GPU), so the entry point still allocates nothing.
+// the library image (kMaxChunks records: 34 MB per GPU; summary mode, further down, adds as many
+// ksa_summary records: 66 MB), so the entry points still allocate nothing.
 // One time-parallel replay per device at a time: a call that finds the scratch busy on another
 // stream takes the plain kernels instead.
+//
+// The same four passes serve ksa_replay_full_faults (FAULTS: the failure mask is read next to the
+// depths; a failed call changes no state, so a run from a wrong state still meets the true one).
+// ksa_replay_summary / ksa_replay_summary_faults have no trajectory to patch and are built
+// differently: second half of this file.
 #include "ksa_internal.h"
 
 #include <cstdlib>

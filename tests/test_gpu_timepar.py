@@ -220,3 +220,62 @@ def test_replica_counts_beyond_the_32_bit_window_in_chunks(engine):
     st = (rng.integers(-5, 9, size=N).astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
     for chunks in (2, 5):
         run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"wide replica counts, chunks={chunks}", warm=8)
+
+
+def test_chunked_paths_never_write_outside_their_outputs(engine):
+    """Canaries (compute-sanitizer is closed on this GPU pool): the outputs sit inside larger buffers
+    filled with a marker, with padding columns in every row; after a chunked call of each of the four
+    entry points the marker must be intact before, after and beside them, and the caller's state and
+    summary arrays must be the only other things written."""
+    import torch
+
+    rng = np.random.default_rng(8)
+    guard = 32
+    for A, N, ld, T, chunks, with_mask in ((1, 64, 80, 203, 3, False), (1, 72, 96, 417, 7, True),
+                                           (3, 9, 16, 160, 4, True), (2, 130, 144, 95, 2, False)):
+        pol = random_policy(rng, A)
+        depth_np = adversarial_depth(rng, T, A, ld, pol)
+        fail_np = random_mask(rng, T, ld) if with_mask else None
+        st = random_state(rng, N, 5)
+        ref = oracle_lib.replay(pol.to_c(), depth_np, T, A, N, ld, 5, *st, want_summary=True, fail=fail_np)
+        depth = torch.from_numpy(np.ascontiguousarray(depth_np)).to(engine.dev)
+        fail = None if fail_np is None else torch.from_numpy(fail_np).to(engine.dev)
+        rbuf = torch.full((T + 2 * guard, ld), -7777, dtype=torch.int32, device=engine.dev)
+        ebuf = torch.full((T + 2 * guard, ld), 0xEE, dtype=torch.uint8, device=engine.dev)
+        sbuf = torch.full((N + 2 * guard, 64), 0xEE, dtype=torch.uint8, device=engine.dev)
+        stbuf = [torch.full((N + 2 * guard,), 0x5A5A5A5A, dtype=dt, device=engine.dev) for dt in (torch.int32, torch.int64, torch.int64)]
+        os.environ["KSA_TIMEPAR_CHUNKS"] = str(chunks)
+        os.environ["KSA_TIMEPAR_WARM"] = "16"
+        try:
+            for mode in ("full", "summary"):
+                for buf, host in zip(stbuf, st):
+                    buf[guard:guard + N] = torch.from_numpy(np.asarray(host)).to(engine.dev)
+                state = ksa.TraceState(*(b[guard:guard + N] for b in stbuf))
+                summ = sbuf[guard:guard + N]
+                engine.lib.ksa_summary_clear(summ.data_ptr(), N, torch.cuda.current_stream().cuda_stream)
+                engine.launch_count()
+                if mode == "full":
+                    engine.replay_full(pol, depth, T, A, N, ld, 5, state, replicas=rbuf[guard:guard + T],
+                                       events=ebuf[guard:guard + T], fail=fail)
+                    assert engine.launch_count() == TP_LAUNCHES
+                else:
+                    engine.replay_summary(pol, depth, T, A, N, ld, 5, state, summary=summ, fail=fail)
+                    assert engine.launch_count() == TP_SUMMARY_LAUNCHES
+                label = f"{mode} A={A} N={N} ld={ld} T={T} chunks={chunks} mask={with_mask}"
+                assert (rbuf[:guard] == -7777).all() and (rbuf[guard + T:] == -7777).all(), label
+                assert (ebuf[:guard] == 0xEE).all() and (ebuf[guard + T:] == 0xEE).all(), label
+                assert (rbuf[guard:guard + T, N:] == -7777).all() and (ebuf[guard:guard + T, N:] == 0xEE).all(), label
+                assert (sbuf[:guard] == 0xEE).all() and (sbuf[guard + N:] == 0xEE).all(), label
+                for buf in stbuf:
+                    assert (buf[:guard] == 0x5A5A5A5A).all() and (buf[guard + N:] == 0x5A5A5A5A).all(), label
+                assert np.array_equal(stbuf[0][guard:guard + N].cpu().numpy(), ref.state_replicas), label
+                assert np.array_equal(stbuf[1][guard:guard + N].cpu().numpy(), ref.state_last_up), label
+                assert np.array_equal(stbuf[2][guard:guard + N].cpu().numpy(), ref.state_last_down), label
+                if mode == "full":
+                    assert np.array_equal(rbuf[guard:guard + T, :N].cpu().numpy(), ref.replicas[:, :N]), label
+                    assert np.array_equal(ebuf[guard:guard + T, :N].cpu().numpy(), ref.events[:, :N]), label
+                else:
+                    assert summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.summary.tobytes(), label
+        finally:
+            os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+            os.environ.pop("KSA_TIMEPAR_WARM", None)
