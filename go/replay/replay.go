@@ -203,6 +203,24 @@ func FreePinned(b []byte) error {
 	return call(func() C.int { return C.ksa_host_free(unsafe.Pointer(&b[0])) })
 }
 
+// PinSlice page-locks memory the caller already has (ksa_host_register), for instance a slice of a
+// shared mapping that the processes of one box, one per GPU, write their shards' summaries into.
+// The slice should start and end on page boundaries. Undo with UnpinSlice before unmapping.
+func PinSlice(b []byte) error {
+	if len(b) == 0 {
+		return nil
+	}
+	return call(func() C.int { return C.ksa_host_register(unsafe.Pointer(&b[0]), C.size_t(len(b))) })
+}
+
+// UnpinSlice undoes PinSlice.
+func UnpinSlice(b []byte) error {
+	if len(b) == 0 {
+		return nil
+	}
+	return call(func() C.int { return C.ksa_host_unregister(unsafe.Pointer(&b[0])) })
+}
+
 // Pipeline owns the device staging for up to N traces x A attributes on one GPU
 // (ksa_pipeline_create): host slices in, host slices out, copies overlapped with the kernels.
 type Pipeline struct {

@@ -176,6 +176,13 @@ int ksa_dev_alloc(void** ptr_dev, size_t bytes);
 int ksa_dev_free(void* ptr_dev);
 int ksa_host_alloc(void** ptr_host, size_t bytes); /* pinned (page-locked) host memory */
 int ksa_host_free(void* ptr_host);
+/* Page-lock memory the caller already has (cudaHostRegister) so that copies to and from it run at
+ * the link's rate and asynchronously. The case it is here for: the processes of one box (one per
+ * GPU) map one shared segment, each registers its own slice and writes its shard's summaries
+ * straight into it: the host-side gather of a sharded replay without a collective. ptr_host and
+ * bytes should be multiples of the page size. Undo with ksa_host_unregister before unmapping. */
+int ksa_host_register(void* ptr_host, size_t bytes);
+int ksa_host_unregister(void* ptr_host);
 int ksa_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream);
 int ksa_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream);
 int ksa_stream_sync(void* stream);

@@ -128,6 +128,8 @@ SIGNATURES = {
     "ksa_dev_free": (C.c_int, [_vp]),
     "ksa_host_alloc": (C.c_int, [_P(_vp), C.c_size_t]),
     "ksa_host_free": (C.c_int, [_vp]),
+    "ksa_host_register": (C.c_int, [_vp, C.c_size_t]),
+    "ksa_host_unregister": (C.c_int, [_vp]),
     "ksa_memcpy_h2d": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "ksa_memcpy_d2h": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "ksa_stream_sync": (C.c_int, [_vp]),

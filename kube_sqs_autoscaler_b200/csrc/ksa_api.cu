@@ -95,6 +95,20 @@ extern "C" int ksa_host_free(void* ptr_host) {
   KSA_CUDA(cudaFreeHost(ptr_host));
   return KSA_OK;
 }
+extern "C" int ksa_host_register(void* ptr_host, size_t bytes) {
+  if (!ptr_host || bytes == 0) return ksa_fail(KSA_EINVAL, "ksa_host_register: NULL pointer or no bytes");
+  cudaError_t e = cudaHostRegister(ptr_host, bytes, cudaHostRegisterPortable);
+  if (e == cudaErrorMemoryAllocation) {
+    cudaGetLastError();
+    return ksa_fail(KSA_ENOMEM, "cudaHostRegister(%zu) failed", bytes);
+  }
+  KSA_CUDA(e);
+  return KSA_OK;
+}
+extern "C" int ksa_host_unregister(void* ptr_host) {
+  KSA_CUDA(cudaHostUnregister(ptr_host));
+  return KSA_OK;
+}
 extern "C" int ksa_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream) {
   KSA_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
   return KSA_OK;
