@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <functional>
 
 #include "../../include/ksa_replay.h"
 #include "ksa_policy.cuh"
@@ -40,15 +41,19 @@ int ksa_full_variant();
 int ksa_summary_variant();
 
 // Time-parallel replays for small trace counts (ksa_timepar.cu); fail_dev == NULL: no failure mask.
+// `plain(unresolved_dev)` launches the one-trace-per-thread kernel of the call for the traces whose
+// flag in unresolved_dev[N] is set (the ones the chunked passes gave up); it runs last, on the same stream.
+typedef std::function<int(const int* unresolved_dev)> ksa_plain_launch;
 int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vector_ok, int* L_out, int* warm_out,
                      int* wide_out);
 int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, const uint8_t* fail_dev, int64_t T,
                             int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
                             int32_t* replicas_dev, uint8_t* events_dev, int K, int L, int warm, int wide,
-                            cudaStream_t st);
+                            const ksa_plain_launch& plain, cudaStream_t st);
 int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
                                int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
-                               ksa_summary* summary_dev, int K, int L, int warm, cudaStream_t st);
+                               ksa_summary* summary_dev, int K, int L, int warm, const ksa_plain_launch& plain,
+                               cudaStream_t st);
 // Its pass 1: the default summary kernel over (trace blocks, chunks of L ticks) (ksa_replay.cu).
 int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
                               int L, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, int K, int32_t* st_r,

@@ -40,6 +40,9 @@ struct ReplayArgs {
   // state and its summary at index k * tp_stride + n of the arrays above (scratch, not the caller's).
   int tp_total;            // ticks of the whole call
   long long tp_stride;     // traces of the call
+  // KSA_GATED kernels only: replay trace n only if gate[n] != 0. The launch that follows the chunked
+  // passes of ksa_timepar.cu, for the traces those gave up.
+  const int* gate;
 };
 
 // MODE_FULL writes both outputs; MODE_FULL_OPT tests the two output pointers at run time (either may
@@ -179,11 +182,20 @@ __device__ __forceinline__ void load_fail(const unsigned char* p, unsigned (&w)[
 
 typedef ksa_summary_acc SummaryRegs;
 
-template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB, bool TP = false>
+// LAUNCH: 0 = an ordinary call; KSA_CHUNKS = chunks of the time axis (TP below); KSA_GATED = only the
+// traces flagged in a.gate (both for ksa_timepar.cu; separate instantiations, so that the kernels of
+// ordinary calls are compiled exactly as before).
+enum { KSA_CHUNKS = 1, KSA_GATED = 2 };
+template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB, int LAUNCH = 0>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
+  constexpr bool TP = LAUNCH == KSA_CHUNKS;
+  if constexpr (LAUNCH == KSA_GATED) {
+    static_assert(V == 1, "gated launches run one trace per thread");
+    if (a.gate[n0] == 0) return;
+  }
   ksa_step_consts c(a.pk);
   // TP: this block replays chunk blockIdx.y of the time axis as if it were a call of its own
   // (ticks tick0 + 1 .. tick0 + T of the trace, state and summary in the chunk's own slots).
@@ -777,12 +789,26 @@ const Variant kSummaryFaultsVariants[] = {
 // The summary defaults (16 / 24, with failures 28 / 24) as chunk-of-the-time-axis kernels for
 // ksa_timepar.cu: [failure mask * 2 + ordered thresholds][A - 1]. One trace per thread, scalar
 // loads: any layout.
-#define KSA_KTP(A, D, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE_SUMMARY, STEP, 128, MINB, true>
+#define KSA_KTP(A, D, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE_SUMMARY, STEP, 128, MINB, KSA_CHUNKS>
 const replay_kernel_fn kSummaryChunkKernels[4][3] = {
     {KSA_KTP(1, 12, 2, 8), KSA_KTP(2, 3, 2, 10), KSA_KTP(3, 2, 2, 10)},
     {KSA_KTP(1, 12, 6, 8), KSA_KTP(2, 3, 6, 10), KSA_KTP(3, 2, 6, 10)},
     {KSA_KTP(1, 12, 10, 7), KSA_KTP(2, 3, 10, 8), KSA_KTP(3, 2, 10, 8)},
     {KSA_KTP(1, 12, 9, 7), KSA_KTP(2, 3, 9, 8), KSA_KTP(3, 2, 9, 8)},
+};
+// The one-trace-per-thread defaults of the four entry points as gated kernels (only the traces flagged in
+// ReplayArgs::gate): what follows the chunked passes. Summary: the table above with KSA_GATED; full mode:
+// variants 42 and, with a failure mask, 9. [A - 1]
+#define KSA_KG(A, D, MODE, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE, STEP, 128, MINB, KSA_GATED>
+const replay_kernel_fn kSummaryGatedKernels[4][3] = {
+    {KSA_KG(1, 12, MODE_SUMMARY, 2, 8), KSA_KG(2, 3, MODE_SUMMARY, 2, 10), KSA_KG(3, 2, MODE_SUMMARY, 2, 10)},
+    {KSA_KG(1, 12, MODE_SUMMARY, 6, 8), KSA_KG(2, 3, MODE_SUMMARY, 6, 10), KSA_KG(3, 2, MODE_SUMMARY, 6, 10)},
+    {KSA_KG(1, 12, MODE_SUMMARY, 10, 7), KSA_KG(2, 3, MODE_SUMMARY, 10, 8), KSA_KG(3, 2, MODE_SUMMARY, 10, 8)},
+    {KSA_KG(1, 12, MODE_SUMMARY, 9, 7), KSA_KG(2, 3, MODE_SUMMARY, 9, 8), KSA_KG(3, 2, MODE_SUMMARY, 9, 8)},
+};
+const replay_kernel_fn kFullGatedKernels[2][3] = {
+    {KSA_KG(1, 8, MODE_FULL, 2, 8), KSA_KG(2, 4, MODE_FULL, 2, 8), KSA_KG(3, 3, MODE_FULL, 2, 8)},
+    {KSA_KG(1, 8, MODE_FULL, 8, 8), KSA_KG(2, 4, MODE_FULL, 8, 8), KSA_KG(3, 3, MODE_FULL, 8, 8)},
 };
 constexpr int kDefaultFull = 32;      // profiles/r01_sweep_variants_a1_T2000.txt: 1.007 of the measured copy peak
 constexpr int kDefaultFullV1 = 42;   // fewer than 196608 traces: one trace per thread
@@ -842,6 +868,7 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   args.summary = summary_dev;
   args.tp_total = 0;
   args.tp_stride = 0;
+  args.gate = nullptr;
 
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
   const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
@@ -856,11 +883,24 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
     const int K = ksa_timepar_plan(T, N, mode == MODE_SUMMARY, faults, vector_ok, &L, &warm, &wide);
     if (K >= 2) {
       cudaStream_t s = (cudaStream_t)stream;
+      // what follows the chunked passes: the one-trace-per-thread default of this call (scalar accesses:
+      // any layout) over the traces they flagged
+      const replay_kernel_fn gated = mode == MODE_FULL ? kFullGatedKernels[faults ? 1 : 0][A - 1]
+                                                       : kSummaryGatedKernels[(faults ? 2 : 0) + (ordered ? 1 : 0)][A - 1];
+      const ksa_plain_launch plain = [&](const int* unresolved_dev) {
+        ReplayArgs g = args;
+        g.gate = unresolved_dev;
+        g.n_begin = 0;
+        g.n_count = N;
+        gated<<<dim3((unsigned)((N + 127) / 128)), 128, 0, s>>>(g);
+        KSA_LAUNCH_CHECK("ksa_replay_kernel (traces the chunked passes gave up)");
+        return KSA_OK;
+      };
       rc = mode == MODE_FULL
                ? ksa_timepar_replay_full(args.pk, depth_dev, args.fail, T, A, N, ld, tick0, state, replicas_dev,
-                                         events_dev, K, L, warm, wide, s)
+                                         events_dev, K, L, warm, wide, plain, s)
                : ksa_timepar_replay_summary(args.pk, ordered, depth_dev, args.fail, T, A, N, ld, tick0, state,
-                                            summary_dev, K, L, warm, s);
+                                            summary_dev, K, L, warm, plain, s);
       if (rc <= 0) return rc;  // done, or an error; 1 = the scratch is busy: plain kernels below
     }
   }
@@ -943,6 +983,7 @@ int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_
   args.summary = partial;
   args.tp_total = (int)T;
   args.tp_stride = N;
+  args.gate = nullptr;
   const long long blocks = (N + 127) / 128;
   kSummaryChunkKernels[(fail_dev ? 2 : 0) + (ordered ? 1 : 0)][A - 1]<<<dim3((unsigned)blocks, (unsigned)K), 128, 0, stream>>>(args);
   KSA_LAUNCH_CHECK("ksa_replay_kernel (chunks of the time axis)");

@@ -23,12 +23,20 @@
 //          outputs are already right. If no checkpoint matches, the whole chunk is rewritten.
 //  pass 3  thread (trace): if every chunk converged (2a or 2b), all entry states were the true ones by
 //          induction, and the carry state is the last chunk's exit with the latest TRUE stamps.
-//          Otherwise walk the chunks in order with the true state and replay again what was
-//          replayed from a wrong entry.
+//          Otherwise walk the chunks in order with the true state. A chunk replayed from the right
+//          gates but a replica count that is off, and in which no scale call happened, is marked to
+//          be shifted by the offset (the trace that goes quiet after some activity: its state never
+//          forgets, so no warm-up makes a guess meet it); up to two chunks that were replayed from a
+//          wrong entry are replayed again here; a trace that needs more is flagged and left alone.
+//  then    thread (trace, chunk): add the offset to the replica counts of the chunks marked for it;
+//          and the one-trace-per-thread kernel of ksa_replay.cu over the flagged traces only, from
+//          the caller's state. (Before these two, a single trace that never met its true trajectory
+//          made the call several times SLOWER than the plain kernels: pass 3 replayed its 10^5 ticks
+//          in one thread. Now the worst case is the chunked passes plus the plain kernel.)
 // Results are bit-identical to the sequential replay whatever K and `warm` are and whether or not
-// any chunk converges (a trace that never does is simply replayed sequentially by pass 3); the
-// tests force small chunks on adversarial policies (one-sided clamps with r0 outside [min, max],
-// min > max, cool-downs longer than the call) to check exactly that.
+// any chunk converges; the tests force small chunks on adversarial policies (one-sided clamps with
+// r0 outside [min, max], min > max, cool-downs longer than the call, traces that go quiet) to
+// check exactly that.
 //
 // "Same future" at tick t means equal replica counts and equal gates for every later tick: a stamp
 // that opens its gate at or before tick t + 1 is as good as any other such stamp. The stamps
@@ -81,6 +89,19 @@ static_assert(sizeof(TpChunk) == 64, "scratch record");
 static __device__ __align__(256) TpChunk g_tp_scratch[kMaxChunks];
 static __device__ int g_tp_list[kMaxChunks];  // (trace, chunk) items pass 2b has to replay
 static __device__ int g_tp_count;
+// Pass 3's verdict per trace: 0 = the call's results are written; 1 = this trace never met its true
+// trajectory within the few chunks pass 3 may replay itself: nothing was written for it, and the
+// one-trace-per-thread kernel that follows the passes (launched for flagged traces only) replays it
+// from the caller's state. Without that, one such trace made the whole call several times slower
+// than the plain kernels (pass 3 replaying 10^5 ticks in one thread: profiles/r02_small_n_modes.txt).
+constexpr int kMaxTraces = 196608;
+static __device__ int g_tp_unresolved[kMaxTraces];
+constexpr int kChainReplays = 2;  // chunks pass 3 replays by itself per trace before it gives the trace up
+
+// The offset pass 3 decided to shift a chunk's replica counts by (0: none; pass 2a clears it), applied by
+// tp_shift_kernel.
+static __device__ int g_tp_delta[kMaxChunks];
+constexpr int kLeftToShift = 100;  // TpChunk::status: pass 2b left the chunk to pass 3, which shifts it
 
 struct TpArgs {
   ksa_policy_k pk;
@@ -107,8 +128,25 @@ __device__ __forceinline__ int check_index(int done, int len) {
 }
 
 // Same behaviour from local tick t + 1 on.
+__device__ __forceinline__ bool same_gates(const TpState& a, const TpState& b, int t) {
+  return max(a.su, t + 1) == max(b.su, t + 1) && max(a.sd, t + 1) == max(b.sd, t + 1);
+}
 __device__ __forceinline__ bool same_future(const TpState& a, const TpState& b, int t) {
-  return a.r == b.r && max(a.su, t + 1) == max(b.su, t + 1) && max(a.sd, t + 1) == max(b.sd, t + 1);
+  return a.r == b.r && same_gates(a, b, t);
+}
+
+// A chunk replayed from the right gates but a replica count that was off by an offset need not be
+// replayed again if no scale call happened in it: which calls happen does not depend on the replica
+// count (a call that finds the limit reached stamps like any other: main.go:62,76, scale.go:62-65), so
+// the true run has none either, and its count is the replayed one plus the offset at every tick, with
+// the same events. This is for the trace that goes quiet after some activity — no call for thousands
+// of ticks: its state never forgets, so no warm-up makes a guess meet it, and before this test one such
+// trace made a call several times slower than the plain kernels (profiles/r02_small_n_modes.txt).
+// (tp_shift_safe, summary mode, has the general condition.)
+// No scale call in a chunk of pass 1 <=> it left both stamps as they were at the chunk's first tick (a call
+// at tick i stamps i + cool-down, later than anything the chunk could have entered with).
+__device__ __forceinline__ bool shift_safe(const TpChunk& rec) {
+  return rec.exit1.su == rec.entry1.su && rec.exit1.sd == rec.entry1.sd;
 }
 
 __device__ __forceinline__ long long load_sum(const long long* p, long long ld, int A) {
@@ -342,7 +380,15 @@ __global__ void __launch_bounds__(BLOCK) tp_check_kernel(const __grid_constant__
   bool need = false;
   if (n < a.N) {
     const TpState entry = record(a, k - 1, n)->exit1;
-    need = !same_future(entry, record(a, k, n)->entry1, k * a.L);
+    TpChunk* const rec = record(a, k, n);
+    need = !same_future(entry, rec->entry1, k * a.L);
+    g_tp_delta[(long long)k * a.N + n] = 0;
+    // only the replica count is off, and the chunk can be shifted by an offset: not for pass 2b. Pass 3
+    // does that, with the true offset (which it alone knows: the previous chunk may itself get shifted)
+    if (need && same_gates(entry, rec->entry1, k * a.L) && shift_safe(*rec)) {
+      rec->status = kLeftToShift;
+      need = false;
+    }
   }
   // one atomic per warp
   const unsigned vote = __ballot_sync(0xffffffffu, need);
@@ -395,7 +441,7 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
     const TpChunk* rec = record(a, k, n);
     const int status = rec->status;
     const int t0 = k * a.L;
-    all = all && status >= 0;
+    all = all && status >= 0 && status != kLeftToShift;
     const int tc = status <= 0 ? t0 : t0 + check_tick(status - 1);
     if (status > 0) {  // pass 2b's own replay, from the chunk's first tick
       su = max(su, later_stamp(INT_MIN, rec->entry1.su, c.cu, t0));
@@ -410,13 +456,26 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
     cur.sd = sd;
   } else {
     // Some chunk never converged: walk the chunks in order with the true state.
+    int replays = 0;
     for (int k = 1; k < a.K; ++k) {
       const int t0 = k * a.L;
       const int len = min(a.L, a.T - t0);
       const TpChunk* rec = record(a, k, n);
       const TpState used = record(a, k - 1, n)->exit1;  // pass 2's entry state
       const int status = rec->status;
-      if (same_future(used, cur, t0)) {
+      if (status == 0 || status == kLeftToShift) {
+        // the outputs and exit1 are pass 1's, replayed from entry1: they stand if that has the true future,
+        // or if only its replica count is off by an offset the chunk can be shifted by (tp_shift_kernel)
+        const long long delta = (long long)cur.r - rec->entry1.r;
+        if (same_gates(rec->entry1, cur, t0) && (delta == 0 || shift_safe(*rec))) {
+          if (delta != 0) g_tp_delta[(long long)k * a.N + n] = (int)delta;
+          cur.r = (int)(rec->exit1.r + delta);
+          cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, t0);
+          cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, t0);
+          continue;
+        }
+      }
+      if (status != kLeftToShift && same_future(used, cur, t0)) {
         // pass 2 started from (the equivalent of) the true state: its work stands
         if (status < 0) {  // 2b rewrote the whole chunk; its end state is in the entry1 slot
           cur.r = rec->entry1.r;
@@ -436,8 +495,12 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
         // an earlier chunk never converged: replay this one from the true state. The outputs are pass 2b's
         // up to its checkpoint and pass 1's after it, so only checkpoints from there on can end the replay;
         // if pass 2b rewrote the whole chunk, nothing of pass 1 is left in it.
+        if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
+          g_tp_unresolved[n] = 1;
+          return;
+        }
         ksa_trace_regs s{cur.r, cur.su, cur.sd};
-        const int first = status < 0 ? kChecks : (status == 0 ? 0 : status - 1);
+        const int first = status < 0 ? kChecks : (status == 0 || status == kLeftToShift ? 0 : status - 1);
         const int j = tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, first, s);
         cur.su = s.su;
         cur.sd = s.sd;
@@ -452,9 +515,32 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
       }
     }
   }
+  g_tp_unresolved[n] = 0;
   a.st_r[n] = cur.r;
   a.st_ju[n] = ksa_global_stamp(cur.su, c.cu, a.tick0, a.st_ju[n]);
   a.st_jd[n] = ksa_global_stamp(cur.sd, c.cd, a.tick0, a.st_jd[n]);
+}
+
+// ---- after pass 3: the chunks it decided to shift --------------------------------------------------
+// Thread (trace, chunk >= 1): add the chunk's offset to its replica counts (the events are the same).
+__global__ void __launch_bounds__(BLOCK) tp_shift_kernel(const __grid_constant__ TpArgs a) {
+  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (n >= a.N) return;
+  const int k = blockIdx.y + 1;
+  const int delta = g_tp_delta[(long long)k * a.N + n];
+  if (delta == 0 || g_tp_unresolved[n] != 0) return;  // (a trace pass 3 gave up is rewritten by the plain kernel)
+  const int t0 = k * a.L;
+  const int len = min(a.L, a.T - t0);
+  int* rp = a.replicas + (long long)t0 * a.ld + n;
+  constexpr int G = 8;  // loads of a group first: one memory latency per 8 ticks
+  for (int t = 0; t < len; t += G) {
+    int v[G];
+#pragma unroll
+    for (int j = 0; j < G; ++j) v[j] = t + j < len ? rp[(long long)(t + j) * a.ld] : 0;
+#pragma unroll
+    for (int j = 0; j < G; ++j)
+      if (t + j < len) rp[(long long)(t + j) * a.ld] = (int)((unsigned)v[j] + (unsigned)delta);
+  }
 }
 
 // ==== summary mode ================================================================================
@@ -478,8 +564,12 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
 //          that has the same future as pass 1's exit state (which the next chunk was judged by).
 //  pass 3  warp (trace): if every chunk is fine, all records were computed from the true states by
 //          induction: the lanes combine them in order (each lane a run of chunks, then a tree over the
-//          lanes). Otherwise lane 0 walks the chunks with the true state and replays again whatever was
-//          replayed from a wrong one. The result is added to the caller's record and state.
+//          lanes). Otherwise lane 0 walks the chunks with the true state: a record replayed from the
+//          right gates but a replica count that is off by an offset is shifted by it when the chunk
+//          never came near a limit (tp_shift_safe: min, max, sum and the fingerprint's replica lane
+//          move with the offset, everything else stands); up to two chunks that were replayed from a
+//          wrong state are replayed again; a trace that needs more is flagged and left to the
+//          one-trace-per-thread kernel that follows. The result is added to the caller's record and state.
 //
 // "Same future" at the first tick B + 1 of a chunk, with `rem` ticks of the call left: equal replica
 // counts, and for each direction the same first tick at which the gate is open, both clamped into
@@ -506,12 +596,14 @@ struct TpSumArgs {
   int T, A, K, L, warm, one;
   int piece;  // pass 2b cuts a chunk into pieces of this many ticks (a multiple of 8, at most 32 pieces)
   unsigned mL_lo, mL_hi, mE_lo, mE_hi;  // the fingerprint multipliers to the power L / the last chunk's length
+  unsigned gL_lo, gE_lo;                // 1 + M + ... + M^(len-1) for the replica lane's multiplier, same two lengths
   int* st_r;           // the caller's state and summaries
   long long* st_ju;
   long long* st_jd;
   ksa_summary* summary;
   TpCarry io, en, fx;  // scratch: pass 1's state (in: entry, out: exit), entry copy, pass 2b's exit
-  int* status;         // 0 pass 1's record stands; 1 pass 2b's record, exit as pass 1's; -1 pass 2b's, exit differs
+  int* status;         // 0 pass 1's record stands; 1 pass 2b's record, exit as pass 1's; -1 pass 2b's, exit differs;
+                       // 2 pass 1's record, entry off by a replica offset the chunk can be shifted by (pass 3 does)
   ksa_summary* part;
 };
 
@@ -529,10 +621,49 @@ __device__ __forceinline__ void tp_put(const TpCarry& c, long long i, const TpG&
 __device__ __forceinline__ int tp_gate(long long cool, int c, long long B, long long last, int rem) {
   return min(max(ksa_local_stamp(cool, c, B, last), 1), rem + 1);
 }
+__device__ __forceinline__ bool tp_same_gates(const ksa_policy_k& pk, const ksa_step_consts& c, const TpG& a,
+                                              const TpG& b, long long B, int rem) {
+  return tp_gate(pk.cu, c.cu, B, a.ju, rem) == tp_gate(pk.cu, c.cu, B, b.ju, rem) &&
+         tp_gate(pk.cd, c.cd, B, a.jd, rem) == tp_gate(pk.cd, c.cd, B, b.jd, rem);
+}
 __device__ __forceinline__ bool tp_same_future(const ksa_policy_k& pk, const ksa_step_consts& c, const TpG& a,
                                                const TpG& b, long long B, int rem) {
-  return a.r == b.r && tp_gate(pk.cu, c.cu, B, a.ju, rem) == tp_gate(pk.cu, c.cu, B, b.ju, rem) &&
-         tp_gate(pk.cd, c.cd, B, a.jd, rem) == tp_gate(pk.cd, c.cd, B, b.jd, rem);
+  return a.r == b.r && tp_same_gates(pk, c, a, b, B, rem);
+}
+
+// A chunk replayed from the right gates but a replica count that was off by `delta` (true = replayed +
+// delta) need not be replayed again if it never came near a limit: which calls happen does not depend
+// on the replica count (a call that finds the limit reached stamps like any other, main.go:62,76;
+// scale.go:62-65), so both runs make the same calls, and as long as every one of them is applied in
+// full in both — no clamp (scale.go:67-69, 95-97), no call at the limit — the true trajectory is the
+// replayed one plus delta at every tick. Sufficient, from the chunk's record `q` (replayed from
+// `entry_r`): no scale-up call at all, or every count of the chunk below max in both runs (a clamped or
+// refused step leaves the count at or above max); likewise for scale-down. The chunk that goes quiet
+// after some activity — no call for thousands of ticks — is the case this is for: its state never
+// forgets, so no amount of warm-up makes a guess meet it.
+__device__ __forceinline__ bool tp_shift_safe(const ksa_step_consts& c, const ksa_summary& q, int entry_r,
+                                              long long delta) {
+  const long long hi = max((long long)q.max_replicas, (long long)entry_r);
+  const long long lo = min((long long)q.min_replicas, (long long)entry_r);
+  if (hi + delta > INT_MAX || lo + delta < INT_MIN) return false;
+  if ((q.up_applied | q.up_noop) != 0u &&
+      !(c.up32 >= 0 && c.up32 <= (1 << 30) && hi < c.max32 && hi + delta < c.max32))
+    return false;
+  if ((q.down_applied | q.down_noop) != 0u &&
+      !(c.down32 >= 0 && c.down32 <= (1 << 30) && lo > c.min32 && lo + delta > c.min32))
+    return false;
+  return true;
+}
+// The record and exit state of such a chunk (`len` ticks; g_lo = 1 + M + ... + M^(len-1) for the
+// fingerprint's replica lane: every tick's term moves by delta).
+__device__ __forceinline__ void tp_shift(ksa_summary& q, TpG& exit, long long delta, int len, unsigned g_lo) {
+  q.final_replicas = (int)(q.final_replicas + delta);
+  q.min_replicas = (int)(q.min_replicas + delta);
+  q.max_replicas = (int)(q.max_replicas + delta);
+  q.sum_replicas = (long long)((unsigned long long)q.sum_replicas + (unsigned long long)delta * (unsigned long long)len);
+  const unsigned lo = (unsigned)q.hash + (unsigned)delta * g_lo;
+  q.hash = (q.hash & 0xffffffff00000000ull) | lo;
+  exit.r = (int)(exit.r + delta);
 }
 
 __device__ __forceinline__ void tp_summary_clear(ksa_summary& q) {
@@ -674,8 +805,16 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_check_kernel(const __grid_consta
   if (n < a.N) {
     const ksa_step_consts c(a.pk);
     const long long idx = (long long)k * a.N + n;
-    need = !tp_same_future(a.pk, c, tp_get(a.io, idx - a.N), tp_get(a.en, idx), a.tick0 + (long long)k * a.L,
-                           a.T - k * a.L);
+    const TpG entry = tp_get(a.io, idx - a.N), guessed = tp_get(a.en, idx);
+    const long long B = a.tick0 + (long long)k * a.L;
+    need = !tp_same_future(a.pk, c, entry, guessed, B, a.T - k * a.L);
+    // only the replica count is off, and by an offset the chunk can be shifted by: not for pass 2b. Pass 3
+    // does that, with the true offset (which it alone knows: the previous chunk may itself be shifted)
+    if (need && tp_same_gates(a.pk, c, entry, guessed, B, a.T - k * a.L) &&
+        tp_shift_safe(c, a.part[idx], guessed.r, (long long)entry.r - guessed.r)) {
+      a.status[idx] = 2;
+      need = false;
+    }
   }
   const unsigned vote = __ballot_sync(0xffffffffu, need);  // one atomic per warp
   if (vote == 0u) return;
@@ -888,14 +1027,14 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
   const int k0 = lane * per, k1 = min(a.K, k0 + per);
   TpRun run;
   tp_run_init(run);
-  bool fine = true;
+  bool fine = true, unresolved = false;
   for (int k = k0; k < k1; ++k) {
     const long long idx = (long long)k * a.N + n;
     const int status = a.status[idx];
-    fine = fine && status >= 0;
+    fine = fine && (status == 0 || status == 1);
     const bool last = k == a.K - 1;
     TpRun one;
-    tp_run_of_chunk(one, a.part[idx], status != 0 ? tp_get(a.fx, idx) : tp_get(a.io, idx),
+    tp_run_of_chunk(one, a.part[idx], status == 1 ? tp_get(a.fx, idx) : tp_get(a.io, idx),
                     a.tick0 + (long long)k * a.L, min(a.L, a.T - k * a.L), k == 0, last ? a.mE_lo : a.mL_lo,
                     last ? a.mE_hi : a.mL_hi);
     tp_run_append(run, one);
@@ -911,6 +1050,7 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
     }
   } else if (lane == 0) {
     // some chunk never met the true trajectory: walk the chunks in order with the true state
+    int replays = 0;
     tp_run_init(run);
     TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
     TpRun one;
@@ -923,14 +1063,23 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
       const long long B = a.tick0 + t0;
       const bool last = k == a.K - 1;
       const int status = a.status[idx];
-      const TpG used = status != 0 ? tp_get(a.io, idx - a.N) : tp_get(a.en, idx);  // what the record was replayed from
-      if (tp_same_future(a.pk, c, used, cur, B, a.T - t0)) {
-        const TpG exit = status != 0 ? tp_get(a.fx, idx) : tp_get(a.io, idx);
-        tp_run_of_chunk(one, a.part[idx], exit, B, len, false, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
+      const bool fixed = status == 1 || status < 0;  // the record is pass 2b's, replayed from the previous chunk's pass-1 exit
+      const TpG used = fixed ? tp_get(a.io, idx - a.N) : tp_get(a.en, idx);  // what the record was replayed from
+      const bool gates = tp_same_gates(a.pk, c, used, cur, B, a.T - t0);
+      const long long delta = (long long)cur.r - used.r;
+      if (gates && (delta == 0 || tp_shift_safe(c, a.part[idx], used.r, delta))) {
+        ksa_summary q = a.part[idx];
+        TpG exit = fixed ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+        if (delta != 0) tp_shift(q, exit, delta, len, last ? a.gE_lo : a.gL_lo);
+        tp_run_of_chunk(one, q, exit, B, len, false, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
         cur.r = exit.r;
         cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
         cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
       } else {
+        if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
+          unresolved = true;
+          break;
+        }
         ksa_summary q;
         tp_summary_clear(q);
         tp_sum_replay<A, FAULTS>(a, c, n, t0, len, cur, &q);
@@ -940,6 +1089,8 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
     }
   }
   if (lane != 0) return;
+  g_tp_unresolved[n] = unresolved ? 1 : 0;
+  if (unresolved) return;
   // add the call to the caller's record (a read-modify-write: calls accumulate) and write the state back
   ksa_summary q = a.summary[n];
   q.final_replicas = run.r;
@@ -970,8 +1121,25 @@ constexpr int kMaxDevices = 64;
 std::mutex g_tp_mutex;
 cudaEvent_t g_tp_busy[kMaxDevices] = {};
 cudaStream_t g_tp_stream[kMaxDevices] = {};  // stream of the call that recorded `busy`
-char* g_tp_scratch_addr[kMaxDevices] = {};   // device addresses of the two scratch arrays (host code only has
-ksa_summary* g_tp_partial_addr[kMaxDevices] = {};  // stand-ins for them: cudaGetSymbolAddress, once per device)
+// Device addresses of the scratch arrays: in host code their names are only stand-ins for them
+// (cudaGetSymbolAddress, once per device, with that device current).
+char* g_tp_scratch_addr[kMaxDevices] = {};
+ksa_summary* g_tp_partial_addr[kMaxDevices] = {};
+int* g_tp_unresolved_addr[kMaxDevices] = {};
+
+int tp_addresses(int device) {
+  if (g_tp_scratch_addr[device]) return KSA_OK;
+  void* p = nullptr;
+  void* q = nullptr;
+  void* u = nullptr;
+  KSA_CUDA(cudaGetSymbolAddress(&p, g_tp_scratch));
+  KSA_CUDA(cudaGetSymbolAddress(&q, g_tp_partial));
+  KSA_CUDA(cudaGetSymbolAddress(&u, g_tp_unresolved));
+  g_tp_partial_addr[device] = (ksa_summary*)q;
+  g_tp_unresolved_addr[device] = (int*)u;
+  g_tp_scratch_addr[device] = (char*)p;
+  return KSA_OK;
+}
 
 // Takes the scratch of the current device for a call on `st`. Returns KSA_OK with the device index, an
 // error, or 1: the scratch is in use by an earlier call on another stream, or `st` is being captured.
@@ -1029,6 +1197,8 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
   KSA_LAUNCH_CHECK("tp_fix_kernel");
   tp_chain_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_chain_kernel");
+  tp_shift_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_shift_kernel");
   return KSA_OK;
 }
 
@@ -1057,6 +1227,12 @@ unsigned pow_u32(unsigned base, unsigned e) {
   for (; e; e >>= 1, base *= base)
     if (e & 1u) r *= base;
   return r;
+}
+// 1 + m + m^2 + ... + m^(n-1) mod 2^32, by halving: G(2k) = G(k) (1 + m^k), G(2k + 1) = G(2k) m + 1
+unsigned geo_u32(unsigned m, unsigned n) {
+  if (n == 0) return 0u;
+  if (n & 1u) return geo_u32(m, n - 1) * m + 1u;
+  return geo_u32(m, n / 2) * (1u + pow_u32(m, n / 2));
 }
 
 }  // namespace
@@ -1110,7 +1286,7 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vecto
   }
   long long L = ((T + K - 1) / K + 7) / 8 * 8;
   K = (T + L - 1) / L;  // (rounding L up may leave fewer chunks)
-  if (K < 2 || N * K > kMaxChunks) return 0;
+  if (K < 2 || N * K > kMaxChunks || N > kMaxTraces) return 0;
   if (warm > L) warm = (int)L;
   *L_out = (int)L;
   *warm_out = warm;
@@ -1124,10 +1300,12 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vecto
 int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, const uint8_t* fail_dev, int64_t T,
                             int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
                             int32_t* replicas_dev, uint8_t* events_dev, int K, int L, int warm, int wide,
-                            cudaStream_t st) {
+                            const ksa_plain_launch& plain, cudaStream_t st) {
   std::lock_guard<std::mutex> lock(g_tp_mutex);
   int device = -1;
   int rc = tp_acquire(st, &device);
+  if (rc != KSA_OK) return rc;
+  rc = tp_addresses(device);
   if (rc != KSA_OK) return rc;
   TpArgs a;
   a.pk = pk;
@@ -1153,26 +1331,22 @@ int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, co
   else
     rc = A == 1 ? tp_launch<1, false>(a, w, st) : A == 2 ? tp_launch<2, false>(a, w, st) : tp_launch<3, false>(a, w, st);
   if (rc != KSA_OK) return rc;
+  rc = plain(g_tp_unresolved_addr[device]);  // the traces pass 3 gave up, one thread each, from the caller's state
+  if (rc != KSA_OK) return rc;
   return tp_release(st, device);
 }
 
 // ksa_replay_summary / ksa_replay_summary_faults (fail_dev != NULL) in K chunks per trace; returns as above.
 int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
                                int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, const ksa_state* state,
-                               ksa_summary* summary_dev, int K, int L, int warm, cudaStream_t st) {
+                               ksa_summary* summary_dev, int K, int L, int warm, const ksa_plain_launch& plain,
+                               cudaStream_t st) {
   std::lock_guard<std::mutex> lock(g_tp_mutex);
   int device = -1;
   int rc = tp_acquire(st, &device);
   if (rc != KSA_OK) return rc;
-  if (!g_tp_scratch_addr[device]) {
-    // In host code the arrays' names are not device addresses: ask the runtime, with this device current.
-    void* p = nullptr;
-    void* q = nullptr;
-    KSA_CUDA(cudaGetSymbolAddress(&p, g_tp_scratch));
-    KSA_CUDA(cudaGetSymbolAddress(&q, g_tp_partial));
-    g_tp_scratch_addr[device] = (char*)p;
-    g_tp_partial_addr[device] = (ksa_summary*)q;
-  }
+  rc = tp_addresses(device);
+  if (rc != KSA_OK) return rc;
   TpSumArgs a;
   a.pk = pk;
   a.depth = (const long long*)depth_dev;
@@ -1192,6 +1366,8 @@ int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64
   a.mL_hi = pow_u32(KSA_HASH_MUL_HI, (unsigned)L);
   a.mE_lo = pow_u32(KSA_HASH_MUL_LO, (unsigned)lenE);
   a.mE_hi = pow_u32(KSA_HASH_MUL_HI, (unsigned)lenE);
+  a.gL_lo = geo_u32(KSA_HASH_MUL_LO, (unsigned)L);
+  a.gE_lo = geo_u32(KSA_HASH_MUL_LO, (unsigned)lenE);
   a.st_r = state->replicas_dev;
   a.st_ju = (long long*)state->last_up_tick_dev;
   a.st_jd = (long long*)state->last_down_tick_dev;
@@ -1217,6 +1393,8 @@ int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64
   else
     rc = A == 1 ? tp_sum_launch<1, false>(a, ordered, st)
                 : A == 2 ? tp_sum_launch<2, false>(a, ordered, st) : tp_sum_launch<3, false>(a, ordered, st);
+  if (rc != KSA_OK) return rc;
+  rc = plain(g_tp_unresolved_addr[device]);
   if (rc != KSA_OK) return rc;
   return tp_release(st, device);
 }

@@ -950,3 +950,39 @@ def test_summary_sum_is_exact_beyond_the_32_bit_window(engine, A):
     finally:
         os.environ.pop("KSA_FAULTS_VARIANT", None)
         engine.set_variant(0, 0)
+
+
+def test_registered_host_memory_takes_the_summaries(engine):
+    """ksa_host_register page-locks memory the caller already has (a slice of a shared mapping in the
+    multi-GPU gather of bench.py): summaries copied into a registered slice of an anonymous mapping
+    must arrive exactly, neighbours untouched; registering nothing is an error."""
+    import ctypes as C
+    import mmap
+
+    import torch
+
+    from kube_sqs_autoscaler_b200 import _abi
+
+    N, T, page = 512, 64, mmap.PAGESIZE
+    rng = np.random.default_rng(21)
+    pol = ksa.Policy(attr_mask=1)
+    depth = rng.integers(0, 300, size=(T, 1, N), dtype=np.int64)
+    st = oracle_lib.fresh_state(3, 0, N, 1, 5)
+    ref = oracle_lib.replay(pol.to_c(), depth, T, 1, N, N, 0, *st, want_summary=True)
+    summ = engine.replay_summary(pol, torch.from_numpy(depth).to(engine.dev), T, 1, N, N, 0, engine.state_from_host(*st))
+    m = mmap.mmap(-1, 3 * N * 64)  # three slices; the middle one (page-aligned: N * 64 = 8 pages) is ours
+    assert (N * 64) % page == 0
+    buf = np.frombuffer(m, dtype=np.uint8)
+    buf[:] = 0xEE
+    mid = buf.ctypes.data + N * 64
+    _abi.check(engine.lib.ksa_host_register(mid, N * 64))
+    try:
+        _abi.check(engine.lib.ksa_memcpy_d2h(mid, summ.data_ptr(), N * 64, torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+    finally:
+        _abi.check(engine.lib.ksa_host_unregister(mid))
+    assert buf[N * 64:2 * N * 64].tobytes() == ref.summary.tobytes()
+    assert (buf[:N * 64] == 0xEE).all() and (buf[2 * N * 64:] == 0xEE).all()
+    assert engine.lib.ksa_host_register(None, 0) == _abi.KSA_EINVAL
+    del buf
+    m.close()

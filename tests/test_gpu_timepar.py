@@ -20,8 +20,8 @@ from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 pytestmark = pytest.mark.gpu
 
 
-TP_LAUNCHES = 4  # pass 1, 2a, 2b, 3
-TP_SUMMARY_LAUNCHES = 5  # pass 0 (entry states), 1, 2a, 2b, 3
+TP_LAUNCHES = 6  # pass 1, 2a, 2b, 3, the shift of replica counts, and the one-trace-per-thread kernel for the traces pass 3 gave up
+TP_SUMMARY_LAUNCHES = 6  # pass 0 (entry states), 1, 2a, 2b, 3, and that kernel
 
 
 def chunks_used(T, chunks):
@@ -279,3 +279,43 @@ def test_chunked_paths_never_write_outside_their_outputs(engine):
         finally:
             os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
             os.environ.pop("KSA_TIMEPAR_WARM", None)
+
+
+def test_traces_that_go_quiet_or_stay_away_from_the_limits(engine):
+    """A chunk replayed from the right gates but a replica count that is off by an offset is not
+    replayed again when it never came near a limit: pass 3 shifts its record (summary mode). The two
+    situations that lead there: a trace that goes quiet after some activity (no scale call for the
+    rest of the call: the state never forgets, a guess never meets it), and limits so far apart that
+    every call is applied in full. Also the neighbours of that rule: counts that touch a limit in one
+    of the two runs only, steps that wrap, failures in between."""
+    rng = np.random.default_rng(41)
+    T = 640
+    for N in (70, 64):
+        cases = []
+        quiet = rng.integers(0, 400, size=(T, 1, N))
+        quiet[90:] = 50  # between the default thresholds from tick 90 on
+        cases.append(("goes quiet", ksa.Policy(attr_mask=1), quiet, rng.integers(1, 6, size=N)))
+        cases.append(("goes quiet outside the limits", ksa.Policy(attr_mask=1, max_pods=3, min_pods=2), quiet,
+                      rng.integers(-4, 9, size=N)))
+        busy = rng.integers(0, 400, size=(T, 1, N))
+        cases.append(("limits far apart", ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=0,
+                                                    max_pods=10**6, min_pods=-(10**6), scale_up_pods=3, scale_down_pods=2),
+                      busy, rng.integers(-50, 50, size=N)))
+        cases.append(("limits far apart, cool-downs", ksa.Policy(attr_mask=1, scale_up_cool_down=15 * S, scale_down_cool_down=40 * S,
+                                                                max_pods=10**6, min_pods=-(10**6), scale_up_pods=7, scale_down_pods=1),
+                      busy, rng.integers(-50, 50, size=N)))
+        near = rng.integers(0, 400, size=(T, 1, N))
+        near[rng.integers(0, 4, size=near.shape) != 0] = 50  # a call every few ticks
+        cases.append(("limits a few steps away", ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=0,
+                                                           max_pods=12, min_pods=-3), near, rng.integers(-6, 16, size=N)))
+        cases.append(("steps that wrap", ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=0, max_pods=2**31 - 1,
+                                                   min_pods=-(2**31), scale_up_pods=2**31 - 5, scale_down_pods=2**30 + 3),
+                      near, rng.integers(-6, 16, size=N)))
+        for name, pol, depth, r0 in cases:
+            depth = np.ascontiguousarray(depth, dtype=np.int64)
+            st = (r0.astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+            for chunks in (2, 5, 13):
+                for warm in (0, 16):
+                    run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"{name} N={N} chunks={chunks} warm={warm}", warm=warm)
+            run_and_check(engine, pol, depth, T, 1, N, N, 0, st, 5, f"{name} N={N} with failures", warm=8,
+                          fail=random_mask(rng, T, N, 0.15))

@@ -18,20 +18,20 @@ import sass_hot  # noqa: E402
 LIB = os.path.join(ROOT, "kube_sqs_autoscaler_b200", "libksareplay.so")
 
 # (key, what, mangled-name pattern, decisions per trip of the steady-state loop); the replay kernel's
-# last template argument (Lb0E) is "not a chunk-of-the-time-axis launch" (ksa_timepar.cu)
+# last template argument (Li0E) is "an ordinary call, neither chunks of the time axis nor gated" (ksa_timepar.cu)
 KERNELS = [
     ("full", "ksa_replay_full, A=1, default (8 traces per thread, ring of 2)",
-     "ksa_replay_kernelILi1ELi8ELi2ELi1ELi0ELi2ELi256ELi2ELb0EE", 16),
+     "ksa_replay_kernelILi1ELi8ELi2ELi1ELi0ELi2ELi256ELi2ELi0EE", 16),
     ("full_small_n", "ksa_replay_full, A=1, below 196608 traces (1 trace per thread, ring of 8)",
-     "ksa_replay_kernelILi1ELi1ELi8ELi1ELi0ELi2ELi128ELi8ELb0EE", 8),
+     "ksa_replay_kernelILi1ELi1ELi8ELi1ELi0ELi2ELi128ELi8ELi0EE", 8),
     ("summary_ordered", "ksa_replay_summary, A=1, scale_up_messages > scale_down_messages (1 trace per thread, ring of 12)",
-     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi6ELi128ELi8ELb0EE", 12),
-    ("summary", "ksa_replay_summary, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi2ELi128ELi8ELb0EE", 12),
+     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi6ELi128ELi8ELi0EE", 12),
+    ("summary", "ksa_replay_summary, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi2ELi128ELi8ELi0EE", 12),
     ("full_faults", "ksa_replay_full_faults, A=1 (4 traces per thread, ring of 4)",
-     "ksa_replay_kernelILi1ELi4ELi4ELi1ELi0ELi8ELi128ELi5ELb0EE", 16),
+     "ksa_replay_kernelILi1ELi4ELi4ELi1ELi0ELi8ELi128ELi5ELi0EE", 16),
     ("summary_faults_ordered", "ksa_replay_summary_faults, A=1, ordered thresholds (1 trace per thread, ring of 12)",
-     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi9ELi128ELi7ELb0EE", 12),
-    ("summary_faults", "ksa_replay_summary_faults, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi10ELi128ELi7ELb0EE", 12),
+     "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi9ELi128ELi7ELi0EE", 12),
+    ("summary_faults", "ksa_replay_summary_faults, A=1, any policy", "ksa_replay_kernelILi1ELi1ELi12ELi1ELi1ELi10ELi128ELi7ELi0EE", 12),
     ("sweep_shared", "ksa_replay_sweep, A=1, tiles sharing their thresholds (4 policies per thread, ring of 3)",
      "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi2E", 12),
     ("sweep_narrow", "ksa_replay_sweep, A=1, ordered int32 thresholds", "ksa_sweep_kernelILi1ELi4ELi3ELi128ELi4ELi0ELi1E", 12),

@@ -28,6 +28,9 @@ def main():
     ap.add_argument("--shapes", default="4096x100000,16384x40000,65536x10000,98304x10000,131072x10000")
     ap.add_argument("--chunks", default="0,auto,2,4,8,16,32,64,128")
     ap.add_argument("--mode", default="full", choices=["full", "summary", "full_faults", "summary_faults"])
+    ap.add_argument("--quiet-after", type=int, default=0,
+                    help="ticks after which every depth is 50 (between the thresholds: no scale event ever again, so a "
+                         "chunk started from a guessed replica count never meets the true trajectory); 0 = off")
     ap.add_argument("--warm", default="", help="comma list of KSA_TIMEPAR_WARM values to try (default: the library's)")
     args = ap.parse_args()
     try:
@@ -40,6 +43,8 @@ def main():
     for shape in args.shapes.split(","):
         N, T = (int(x) for x in shape.split("x"))
         depth = eng.gen_traces(gen, 0, T, 1, 0, N, N)
+        if args.quiet_after:
+            depth[args.quiet_after:] = 50
         replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
         events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
         state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
