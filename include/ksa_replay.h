@@ -21,7 +21,7 @@
  *    the host heap (ksa_dev_alloc / ksa_host_alloc and ksa_pipeline_create are the allocating
  *    helpers). Two fixed arrays live in the library's device image on every GPU that loads it:
  *    the policy table of ksa_replay_sweep_static (192 KB) and the scratch records of the
- *    time-parallel paths of the four replay entry points (66 MB, see ksa_replay_full).
+ *    time-parallel paths of the four replay entry points (69 MB, see ksa_replay_full).
  *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
  *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
  *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.

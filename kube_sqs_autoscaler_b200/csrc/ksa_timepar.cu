@@ -46,7 +46,7 @@
 //
 // Scratch: one 64-byte record per (trace, chunk) and a 4-byte list slot, in fixed device arrays of
 // the library image (kMaxChunks records: 34 MB per GPU; summary mode, further down, adds as many
-// ksa_summary records: 66 MB), so the entry points still allocate nothing.
+// ksa_summary records: 69 MB), so the entry points still allocate nothing.
 // One time-parallel replay per device at a time: a call that finds the scratch busy on another
 // stream takes the plain kernels instead.
 //
