@@ -626,7 +626,7 @@ def test_cli_shards_over_gpus_without_changing_results(engine):
     assert r.returncode == 2 and "CUDA devices" in r.stderr
 
 
-@pytest.mark.parametrize("P,N", [(1, 1), (7, 37), (9, 515), (33, 4099)])
+@pytest.mark.parametrize("P,N", [(1, 1), (7, 37), (9, 515), (33, 4099), (300, 700), (129, 9500), (70, 9472)])
 def test_sweep_reduce_matches_restatement(engine, P, N):
     """ksa_sweep_reduce (extension): totals per policy, argmin per trace and its cost, bit-exact
     against oracle/policy_py.sweep_reduce on real sweep summaries and on wrapping random records;
