@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--quiet-after", type=int, default=0,
                     help="ticks after which every depth is 50 (between the thresholds: no scale event ever again, so a "
                          "chunk started from a guessed replica count never meets the true trajectory); 0 = off")
+    ap.add_argument("--fail-log2", default="5,4,4", help="failure mask: poll, up, down bits each with probability 2^-k (0 = never)")
     ap.add_argument("--warm", default="", help="comma list of KSA_TIMEPAR_WARM values to try (default: the library's)")
     args = ap.parse_args()
     try:
@@ -49,7 +50,8 @@ def main():
         events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
         state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
         summary_mode = args.mode.startswith("summary")
-        fail = eng.gen_faults(gen.seed, 5, 4, 4, 0, T, 0, N, N) if args.mode.endswith("faults") else None
+        fl = [int(x) for x in args.fail_log2.split(",")]
+        fail = eng.gen_faults(gen.seed, fl[0], fl[1], fl[2], 0, T, 0, N, N) if args.mode.endswith("faults") else None
         bytes_per = (8 if summary_mode else 13) + (1 if fail is not None else 0)
         ref = None
         for ch, warm in [(c, w) for c in args.chunks.split(",") for w in (args.warm.split(",") if args.warm else [""])]:
