@@ -57,6 +57,7 @@ int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64
 // Its pass 1: the default summary kernel over (trace blocks, chunks of L ticks) (ksa_replay.cu).
 int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
                               int L, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, int K, int32_t* st_r,
-                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, cudaStream_t stream);
+                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, const int* marks_dev, int mark,
+                              cudaStream_t stream);
 
 static inline bool ksa_aligned(const void* p, size_t a) { return ((uintptr_t)p & (a - 1)) == 0; }

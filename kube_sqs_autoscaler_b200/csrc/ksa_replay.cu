@@ -41,8 +41,10 @@ struct ReplayArgs {
   int tp_total;            // ticks of the whole call
   long long tp_stride;     // traces of the call
   // KSA_GATED kernels only: replay trace n only if gate[n] != 0. The launch that follows the chunked
-  // passes of ksa_timepar.cu, for the traces those gave up.
+  // passes of ksa_timepar.cu, for the traces those gave up. KSA_CHUNKS_MARKED kernels: replay chunk k of
+  // trace n only if gate[k * tp_stride + n] == gate_value.
   const int* gate;
+  int gate_value;
 };
 
 // MODE_FULL writes both outputs; MODE_FULL_OPT tests the two output pointers at run time (either may
@@ -185,13 +187,14 @@ typedef ksa_summary_acc SummaryRegs;
 // LAUNCH: 0 = an ordinary call; KSA_CHUNKS = chunks of the time axis (TP below); KSA_GATED = only the
 // traces flagged in a.gate (both for ksa_timepar.cu; separate instantiations, so that the kernels of
 // ordinary calls are compiled exactly as before).
-enum { KSA_CHUNKS = 1, KSA_GATED = 2 };
+// KSA_CHUNKS_MARKED = KSA_CHUNKS for the (chunk, trace) pairs with a.gate[chunk * traces + trace] == a.gate_value only.
+enum { KSA_CHUNKS = 1, KSA_GATED = 2, KSA_CHUNKS_MARKED = 3 };
 template <int A, int V, int D, int HINT, int MODE, int STEP, int BLOCK, int MINB, int LAUNCH = 0>
 __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_constant__ ReplayArgs a) {
   const long long g = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (g * V >= a.n_count) return;
   const long long n0 = a.n_begin + g * V;
-  constexpr bool TP = LAUNCH == KSA_CHUNKS;
+  constexpr bool TP = LAUNCH == KSA_CHUNKS || LAUNCH == KSA_CHUNKS_MARKED;
   if constexpr (LAUNCH == KSA_GATED) {
     static_assert(V == 1, "gated launches run one trace per thread");
     if (a.gate[n0] == 0) return;
@@ -201,6 +204,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ksa_replay_kernel(const __grid_co
   // (ticks tick0 + 1 .. tick0 + T of the trace, state and summary in the chunk's own slots).
   const int ky = TP ? (int)blockIdx.y : 0;
   const long long si = TP ? ky * a.tp_stride + n0 : n0;  // index into the state and summary arrays
+  if constexpr (LAUNCH == KSA_CHUNKS_MARKED) {
+    static_assert(V == 1, "marked chunks run one trace per thread");
+    if (a.gate[si] != a.gate_value) return;
+  }
   const int T = TP ? min(a.T, a.tp_total - ky * a.T) : a.T;
   const long long tick0 = TP ? a.tick0 + (long long)ky * a.T : a.tick0;
   const int one = a.one;  // always 1; see ksa_step_fma
@@ -790,11 +797,19 @@ const Variant kSummaryFaultsVariants[] = {
 // ksa_timepar.cu: [failure mask * 2 + ordered thresholds][A - 1]. One trace per thread, scalar
 // loads: any layout.
 #define KSA_KTP(A, D, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE_SUMMARY, STEP, 128, MINB, KSA_CHUNKS>
+#define KSA_KTL(A, D, STEP, MINB) ksa_replay_kernel<A, 1, D, HINT_NA, MODE_SUMMARY, STEP, 128, MINB, KSA_CHUNKS_MARKED>
 const replay_kernel_fn kSummaryChunkKernels[4][3] = {
     {KSA_KTP(1, 12, 2, 8), KSA_KTP(2, 3, 2, 10), KSA_KTP(3, 2, 2, 10)},
     {KSA_KTP(1, 12, 6, 8), KSA_KTP(2, 3, 6, 10), KSA_KTP(3, 2, 6, 10)},
     {KSA_KTP(1, 12, 10, 7), KSA_KTP(2, 3, 10, 8), KSA_KTP(3, 2, 10, 8)},
     {KSA_KTP(1, 12, 9, 7), KSA_KTP(2, 3, 9, 8), KSA_KTP(3, 2, 9, 8)},
+};
+// ... and for marked chunks only (the chunks ksa_timepar.cu replays a second time)
+const replay_kernel_fn kSummaryMarkedChunkKernels[4][3] = {
+    {KSA_KTL(1, 12, 2, 8), KSA_KTL(2, 3, 2, 10), KSA_KTL(3, 2, 2, 10)},
+    {KSA_KTL(1, 12, 6, 8), KSA_KTL(2, 3, 6, 10), KSA_KTL(3, 2, 6, 10)},
+    {KSA_KTL(1, 12, 10, 7), KSA_KTL(2, 3, 10, 8), KSA_KTL(3, 2, 10, 8)},
+    {KSA_KTL(1, 12, 9, 7), KSA_KTL(2, 3, 9, 8), KSA_KTL(3, 2, 9, 8)},
 };
 // The one-trace-per-thread defaults of the four entry points as gated kernels (only the traces flagged in
 // ReplayArgs::gate): what follows the chunked passes. Summary: the table above with KSA_GATED; full mode:
@@ -869,6 +884,7 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
   args.tp_total = 0;
   args.tp_stride = 0;
   args.gate = nullptr;
+  args.gate_value = 0;
 
   const int want = mode == MODE_FULL ? ksa_full_variant() : ksa_summary_variant();
   const bool ordered = policy->scale_up_messages > policy->scale_down_messages;
@@ -962,9 +978,11 @@ int replay_common(int mode, bool faults, const ksa_policy* policy, const int64_t
 // each replayed like a call of its own by the default summary kernel, with the chunk's carry state
 // at st_*[k * N + n] (in: the state the chunk starts from; out: the state it ends with) and its
 // summary accumulated into partial[k * N + n].
+// marks_dev != NULL: only the chunks with marks_dev[k * N + n] == mark.
 int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_t* depth_dev, const uint8_t* fail_dev,
                               int L, int64_t T, int32_t A, int64_t N, int64_t ld, int64_t tick0, int K, int32_t* st_r,
-                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, cudaStream_t stream) {
+                              int64_t* st_ju, int64_t* st_jd, ksa_summary* partial, const int* marks_dev, int mark,
+                              cudaStream_t stream) {
   ReplayArgs args;
   args.pk = pk;
   args.depth = (const long long*)depth_dev;
@@ -983,9 +1001,11 @@ int ksa_replay_summary_chunks(const ksa_policy_k& pk, bool ordered, const int64_
   args.summary = partial;
   args.tp_total = (int)T;
   args.tp_stride = N;
-  args.gate = nullptr;
+  args.gate = marks_dev;
+  args.gate_value = mark;
+  const int kind = (fail_dev ? 2 : 0) + (ordered ? 1 : 0);
   const long long blocks = (N + 127) / 128;
-  kSummaryChunkKernels[(fail_dev ? 2 : 0) + (ordered ? 1 : 0)][A - 1]<<<dim3((unsigned)blocks, (unsigned)K), 128, 0, stream>>>(args);
+  (marks_dev ? kSummaryMarkedChunkKernels : kSummaryChunkKernels)[kind][A - 1]<<<dim3((unsigned)blocks, (unsigned)K), 128, 0, stream>>>(args);
   KSA_LAUNCH_CHECK("ksa_replay_kernel (chunks of the time axis)");
   return KSA_OK;
 }

@@ -68,8 +68,11 @@ constexpr int kMargin = 8;            // a chunk has checkpoint j if check_tick(
 constexpr int BLOCK = 128;
 // Trace counts up to which the chunked path is taken by default: where it stops paying against one
 // trace per thread over the whole call (profiles/r02_small_n_modes.txt).
-constexpr long long kTpMaxSummary = 65536;        // 0.774 against 0.764 of the copy peak there, 0.82 / 0.87 at 98304
-constexpr long long kTpMaxSummaryFaults = 49152;  // 0.674 / 0.621; 0.646 / 0.693 at 65536
+// (summary mode: on depths with long stretches on one side of a threshold many chunks are replayed twice;
+// the limit is where that still costs no more than the plain kernel: random-walk depths, 32768 traces:
+// 1.76 ms against 1.69; at 49152: 2.00 against 1.49, while independent depths gain 0.66 -> 0.80 there)
+constexpr long long kTpMaxSummary = 32768;
+constexpr long long kTpMaxSummaryFaults = 32768;  // independent depths 0.47 -> 0.65, random walk 1.94 -> 2.19 ms
 constexpr long long kTpMaxFullFaults = 81920;     // 0.773 / 0.750; 0.81 / 0.83 at 98304
 // ... and again where one trace per thread starts a second, nearly empty wave of 148 x 1024 threads
 // (163840 traces: 0.81 against 0.73), as long as two chunks still fit one wave of pass 1
@@ -595,6 +598,7 @@ struct TpSumArgs {
   long long ld, tick0, N;
   int T, A, K, L, warm, one;
   int piece;  // pass 2b cuts a chunk into pieces of this many ticks (a multiple of 8, at most 32 pieces)
+  int fix_limit;  // ... unless more chunks than this are listed
   unsigned mL_lo, mL_hi, mE_lo, mE_hi;  // the fingerprint multipliers to the power L / the last chunk's length
   unsigned gL_lo, gE_lo;                // 1 + M + ... + M^(len-1) for the replica lane's multiplier, same two lengths
   int* st_r;           // the caller's state and summaries
@@ -603,7 +607,10 @@ struct TpSumArgs {
   ksa_summary* summary;
   TpCarry io, en, fx;  // scratch: pass 1's state (in: entry, out: exit), entry copy, pass 2b's exit
   int* status;         // 0 pass 1's record stands; 1 pass 2b's record, exit as pass 1's; -1 pass 2b's, exit differs;
-                       // 2 pass 1's record, entry off by a replica offset the chunk can be shifted by (pass 3 does)
+                       // 2 pass 1's record, entry off by a replica offset the chunk can be shifted by (pass 3 does);
+                       // 3 replayed a second time from the entry state pass 3a worked out (in `en`); 4 pass 1's
+                       // record of a chunk in which every tick met the same threshold, left to pass 3a; 5 pass 1's
+                       // record of a chunk listed for pass 2b (which replaces the 5 unless it gives the chunk up)
   ksa_summary* part;
 };
 
@@ -692,6 +699,47 @@ __device__ __forceinline__ void tp_summary_add(ksa_summary& q, int r, unsigned e
   q.down_failed += fb == (unsigned)KSA_EV_DOWN_FAILED ? 1u : 0u;
   q.sum_replicas = (long long)((unsigned long long)q.sum_replicas + (unsigned long long)(long long)r);
   q.hash = ksa_hash_step(q.hash, r, ev);
+}
+
+// A chunk in which EVERY tick met the scale-up threshold (1) or the scale-down threshold (2), from its
+// record (a tick that meets a threshold logs exactly one of that direction's three lines); 0 otherwise,
+// and for policies whose thresholds overlap (both can be met in one tick) or with a failure mask (a
+// failed call takes no stamp). That is a property of the depths, not of the state the chunk was replayed
+// from. It is the saturated queue (replicas at max, ScaleUp called every cool-down period) and the idle
+// one (at min, ScaleDown every period): the two steady states of a real fleet. The calls of such a
+// stretch are exactly one cool-down apart, their phase set by its first call, so a chunk started from
+// a guess deep inside one keeps the wrong phase for ever: no warm-up helps.
+template <bool FAULTS>
+__device__ __forceinline__ int tp_pure_kind(const ksa_policy_k& pk, const ksa_summary& q, int len) {
+  if (FAULTS || !(pk.up_msgs > pk.down_msgs)) return 0;
+  if ((long long)q.up_applied + q.up_noop + q.up_cool == len) return 1;
+  if ((long long)q.down_applied + q.down_noop + q.down_cool == len) return 2;
+  return 0;
+}
+// ... but what such a chunk does to a state is simple: the first call at the first tick the gate is
+// open, then one every cool-down period, each a full step towards the limit. The state after the
+// chunk's `len` ticks (first tick B + 1) from state g. False: not worked out (steps that are negative
+// or could wrap).
+__device__ __forceinline__ bool tp_pure_exit(const ksa_policy_k& pk, const ksa_step_consts& c, int kind, long long B,
+                                             int len, TpG& g) {
+  const bool up = kind == 1;
+  const int step = up ? c.up32 : c.down32;
+  if (step < 0 || step > (1 << 30)) return false;
+  const int cool = up ? c.cu : c.cd;
+  const int s = ksa_local_stamp(up ? pk.cu : pk.cd, cool, B, up ? g.ju : g.jd);  // blocked at local tick i <=> i < s
+  const long long first = max(1, s);
+  if (first > len) return true;  // the gate stays shut for the whole chunk
+  const long long period = max(cool, 1);
+  const long long calls = (len - first) / period + 1;
+  const long long last = first + (calls - 1) * period;
+  if (up) {
+    g.ju = B + last;
+    if (g.r < c.max32) g.r = (int)min((long long)g.r + calls * step, (long long)c.max32);  // scale.go:62-69
+  } else {
+    g.jd = B + last;
+    if (g.r > c.min32) g.r = (int)max((long long)g.r - calls * step, (long long)c.min32);  // scale.go:89-97
+  }
+  return true;
 }
 
 // Ticks [first, first + count) of the call for trace n, from carry state g (plain loop, the depths
@@ -798,6 +846,7 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_warm_kernel(const __grid_constan
 }
 
 // ---- pass 2a -------------------------------------------------------------------------------------
+template <bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_check_kernel(const __grid_constant__ TpSumArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   const int k = blockIdx.y + 1;
@@ -815,6 +864,13 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_check_kernel(const __grid_consta
       a.status[idx] = 2;
       need = false;
     }
+    // every tick of the chunk met the same threshold: replaying it in pieces would meet the same wrong
+    // phases. Pass 3a works out its true entry state, and it is replayed a second time from that
+    if (need && tp_pure_kind<FAULTS>(a.pk, a.part[idx], min(a.L, a.T - k * a.L)) != 0) {
+      a.status[idx] = 4;
+      need = false;
+    }
+    if (need) a.status[idx] = 5;  // listed; pass 2b replaces it when it gets the chunk done
   }
   const unsigned vote = __ballot_sync(0xffffffffu, need);  // one atomic per warp
   if (vote == 0u) return;
@@ -944,7 +1000,10 @@ __device__ __forceinline__ unsigned tp_pow_u32(unsigned base, unsigned e) {
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_fix_kernel(const __grid_constant__ TpSumArgs a) {
   const int item = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
-  if (item >= g_tp_count) return;  // (whole warps)
+  // This pass is for the few chunks whose guess met the truth a little late. When many are listed the
+  // guesses fail for a reason pieces would fail for too (profiles/r02_small_n_modes.txt: random-walk
+  // depths, 10.6 ms in here): everything is left to pass 3a and the second replay.
+  if (item >= g_tp_count || g_tp_count > a.fix_limit) return;  // (whole warps)
   const int lane = threadIdx.x & 31;
   const long long idx = g_tp_list[item];
   const int k = (int)(idx / a.N);
@@ -969,14 +1028,18 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_fix_kernel(const __grid_constant
     }
     tp_sum_replay<A, FAULTS>(a, c, n, first, count, g, &q);
   }
+  int redone = 0;
   for (int r = 0; r + 1 < pieces; ++r) {
     const TpG left = tp_shfl_g(g, r);  // exit state of piece r: true by induction
     bool redo = false;
     if (lane == r + 1) redo = !tp_same_future(a.pk, c, left, used, a.tick0 + first, a.T - first);
-    if (__shfl_sync(0xffffffffu, (int)redo, r + 1) && lane == r + 1) {
-      g = used = left;
-      tp_summary_clear(q);
-      tp_sum_replay<A, FAULTS>(a, c, n, first, count, g, &q);
+    if (__shfl_sync(0xffffffffu, (int)redo, r + 1)) {
+      if (++redone > 2) return;  // the pieces' guesses keep failing: nothing written, the chunk is pass 3a's
+      if (lane == r + 1) {
+        g = used = left;
+        tp_summary_clear(q);
+        tp_sum_replay<A, FAULTS>(a, c, n, first, count, g, &q);
+      }
     }
   }
   // the pieces in order -> the chunk
@@ -1011,12 +1074,100 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_fix_kernel(const __grid_constant
   a.part[idx] = q;
   const TpG exit{run.r, run.has_u ? run.ju : entry0.ju, run.has_d ? run.jd : entry0.jd};
   tp_put(a.fx, idx, exit);
+  tp_put(a.en, idx, entry0);  // what the record was replayed from (pass 3 compares it with the true state)
   const bool last = k == a.K - 1;  // (nothing is judged by the last chunk's exit)
   a.status[idx] =
       last || tp_same_future(a.pk, c, exit, tp_get(a.io, idx), a.tick0 + t0 + len, a.T - t0 - len) ? 1 : -1;
 }
 
 // ---- pass 3 --------------------------------------------------------------------------------------
+// The walk of lane 0 over a trace's chunks with the true state, for traces in which not every chunk is
+// fine. Chunk k's record was replayed from en(k) (pass 1: the guess after its warm-up; pass 2b and the
+// second replay: the state they were given) and ended with `exit`; it stands if en(k) has the true
+// future, or after a shift by the replica offset (tp_shift_safe). Otherwise:
+//  RESOLVE (pass 3a, before the second replay): the chunk is marked (status 3) to be replayed a second
+//    time from the true state, which is put where that replay reads it. What the chunk will end with is
+//    not known yet, and the next chunk needs it: worked out for a chunk in which every tick met the same
+//    threshold (tp_pure_exit), assumed to be what the first replay ended with otherwise (most chunks
+//    forget the state they were entered with). Wrong assumptions cost time, not correctness:
+//  FINAL (pass 3b, after the second replay): the same walk over what is there now. A chunk that still
+//    does not fit is replayed here, up to kChainReplays per trace; a trace that needs more is flagged for
+//    the one-trace-per-thread kernel that follows and nothing is written for it.
+template <int A, bool FAULTS, bool RESOLVE>
+__device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long long n, TpRun& run, bool& unresolved) {
+  int replays = 0;
+  tp_run_init(run);
+  TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+  TpRun one;
+  tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
+  tp_run_append(run, one);
+  for (int k = 1; k < a.K; ++k) {
+    const long long idx = (long long)k * a.N + n;
+    const int t0 = k * a.L;
+    const int len = min(a.L, a.T - t0);
+    const long long B = a.tick0 + t0;
+    const bool last = k == a.K - 1;
+    const int status = a.status[idx];
+    const bool fixed = status == 1 || status < 0;  // the record and its exit state are pass 2b's
+    const TpG used = tp_get(a.en, idx);
+    TpG exit = fixed ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+    ksa_summary q = a.part[idx];
+    const bool gates = tp_same_gates(a.pk, c, used, cur, B, a.T - t0);
+    const long long delta = (long long)cur.r - used.r;
+    if (gates && (delta == 0 || tp_shift_safe(c, q, used.r, delta))) {
+      if (delta != 0) tp_shift(q, exit, delta, len, last ? a.gE_lo : a.gL_lo);
+      tp_run_of_chunk(one, q, exit, B, len, false, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
+      cur.r = exit.r;
+      cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
+      cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
+    } else if (RESOLVE) {
+      tp_put(a.en, idx, cur);
+      tp_put(a.io, idx, cur);
+      const int kind = tp_pure_kind<FAULTS>(a.pk, q, len);
+      tp_summary_clear(q);
+      a.part[idx] = q;
+      a.status[idx] = 3;
+      TpG worked = cur;
+      if (kind != 0 && tp_pure_exit(a.pk, c, kind, B, len, worked)) {
+        cur = worked;
+      } else {
+        cur.r = exit.r;
+        cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
+        cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
+      }
+      continue;  // (pass 3a builds no result)
+    } else {
+      if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
+        unresolved = true;
+        return;
+      }
+      tp_summary_clear(q);
+      tp_sum_replay<A, FAULTS>(a, c, n, t0, len, cur, &q);
+      tp_run_of_chunk(one, q, cur, B, len, true, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
+    }
+    tp_run_append(run, one);
+  }
+}
+
+// ---- pass 3a: warp (trace) ----------------------------------------------------------------------
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_constant__ TpSumArgs a) {
+  const long long n = (long long)blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
+  if (n >= a.N) return;  // (whole warps)
+  const int lane = threadIdx.x & 31;
+  bool fine = true;
+  for (int k = lane; k < a.K; k += 32) {
+    const int status = a.status[(long long)k * a.N + n];
+    fine = fine && (status == 0 || status == 1);
+  }
+  if (__all_sync(0xffffffffu, fine) || lane != 0) return;
+  const ksa_step_consts c(a.pk);
+  TpRun run;
+  bool unresolved = false;
+  tp_sum_walk<A, FAULTS, true>(a, c, n, run, unresolved);
+}
+
+// ---- pass 3b: warp (trace) ----------------------------------------------------------------------
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_constant__ TpSumArgs a) {
   const long long n = (long long)blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
@@ -1049,44 +1200,7 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
       if ((lane & (2 * off - 1)) == 0) tp_run_append(run, other);
     }
   } else if (lane == 0) {
-    // some chunk never met the true trajectory: walk the chunks in order with the true state
-    int replays = 0;
-    tp_run_init(run);
-    TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
-    TpRun one;
-    tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
-    tp_run_append(run, one);
-    for (int k = 1; k < a.K; ++k) {
-      const long long idx = (long long)k * a.N + n;
-      const int t0 = k * a.L;
-      const int len = min(a.L, a.T - t0);
-      const long long B = a.tick0 + t0;
-      const bool last = k == a.K - 1;
-      const int status = a.status[idx];
-      const bool fixed = status == 1 || status < 0;  // the record is pass 2b's, replayed from the previous chunk's pass-1 exit
-      const TpG used = fixed ? tp_get(a.io, idx - a.N) : tp_get(a.en, idx);  // what the record was replayed from
-      const bool gates = tp_same_gates(a.pk, c, used, cur, B, a.T - t0);
-      const long long delta = (long long)cur.r - used.r;
-      if (gates && (delta == 0 || tp_shift_safe(c, a.part[idx], used.r, delta))) {
-        ksa_summary q = a.part[idx];
-        TpG exit = fixed ? tp_get(a.fx, idx) : tp_get(a.io, idx);
-        if (delta != 0) tp_shift(q, exit, delta, len, last ? a.gE_lo : a.gL_lo);
-        tp_run_of_chunk(one, q, exit, B, len, false, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
-        cur.r = exit.r;
-        cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
-        cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
-      } else {
-        if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
-          unresolved = true;
-          break;
-        }
-        ksa_summary q;
-        tp_summary_clear(q);
-        tp_sum_replay<A, FAULTS>(a, c, n, t0, len, cur, &q);
-        tp_run_of_chunk(one, q, cur, B, len, true, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
-      }
-      tp_run_append(run, one);
-    }
+    tp_sum_walk<A, FAULTS, false>(a, c, n, run, unresolved);
   }
   if (lane != 0) return;
   g_tp_unresolved[n] = unresolved ? 1 : 0;
@@ -1135,6 +1249,7 @@ int tp_addresses(int device) {
   KSA_CUDA(cudaGetSymbolAddress(&p, g_tp_scratch));
   KSA_CUDA(cudaGetSymbolAddress(&q, g_tp_partial));
   KSA_CUDA(cudaGetSymbolAddress(&u, g_tp_unresolved));
+
   g_tp_partial_addr[device] = (ksa_summary*)q;
   g_tp_unresolved_addr[device] = (int*)u;
   g_tp_scratch_addr[device] = (char*)p;
@@ -1208,16 +1323,24 @@ int tp_sum_launch(const TpSumArgs& a, bool ordered, cudaStream_t st) {
   tp_sum_warm_kernel<A, FAULTS><<<dim3(gn, (unsigned)a.K), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_sum_warm_kernel");
   const int rc = ksa_replay_summary_chunks(a.pk, ordered, (const int64_t*)a.depth, a.fail, a.L, a.T, A, a.N, a.ld, a.tick0,
-                                           a.K, a.io.r, (int64_t*)a.io.ju, (int64_t*)a.io.jd, a.part, st);
+                                           a.K, a.io.r, (int64_t*)a.io.ju, (int64_t*)a.io.jd, a.part, nullptr, 0, st);
   if (rc != KSA_OK) return rc;
-  tp_sum_check_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
+  tp_sum_check_kernel<FAULTS><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_sum_check_kernel");
   // (the list's length is only known on the device: a warp per possible item, idle warps return at once)
   const long long items = a.N * (a.K - 1);
   const long long warps_per_block = BLOCK / 32;
   tp_sum_fix_kernel<A, FAULTS><<<(unsigned)((items + warps_per_block - 1) / warps_per_block), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_sum_fix_kernel");
-  tp_sum_chain_kernel<A, FAULTS><<<(unsigned)((a.N + warps_per_block - 1) / warps_per_block), BLOCK, 0, st>>>(a);
+  const unsigned per_trace = (unsigned)((a.N + warps_per_block - 1) / warps_per_block);
+  tp_sum_resolve_kernel<A, FAULTS><<<per_trace, BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_sum_resolve_kernel");
+  // the chunks pass 3a marked, a second time, from the entry states it put into `io` (the same grid as pass 1,
+  // so that neighbouring traces still share their loads; the other threads return at once)
+  const int rc2 = ksa_replay_summary_chunks(a.pk, ordered, (const int64_t*)a.depth, a.fail, a.L, a.T, A, a.N, a.ld, a.tick0,
+                                            a.K, a.io.r, (int64_t*)a.io.ju, (int64_t*)a.io.jd, a.part, a.status, 3, st);
+  if (rc2 != KSA_OK) return rc2;
+  tp_sum_chain_kernel<A, FAULTS><<<per_trace, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_sum_chain_kernel");
   return KSA_OK;
 }
@@ -1361,6 +1484,7 @@ int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64
   a.warm = warm;
   a.one = 1;
   a.piece = std::max(16, ((L + 31) / 32 + 7) / 8 * 8);
+  a.fix_limit = (int)std::max<int64_t>(64, N * (K - 1) / 32);
   const int lenE = (int)(T - (int64_t)(K - 1) * L);
   a.mL_lo = pow_u32(KSA_HASH_MUL_LO, (unsigned)L);
   a.mL_hi = pow_u32(KSA_HASH_MUL_HI, (unsigned)L);
@@ -1387,6 +1511,7 @@ int ksa_timepar_replay_summary(const ksa_policy_k& pk, bool ordered, const int64
   a.fx = carry(40);
   a.status = (int*)(base + 60 * M);
   a.part = g_tp_partial_addr[device];
+
   if (fail_dev)
     rc = A == 1 ? tp_sum_launch<1, true>(a, ordered, st)
                 : A == 2 ? tp_sum_launch<2, true>(a, ordered, st) : tp_sum_launch<3, true>(a, ordered, st);

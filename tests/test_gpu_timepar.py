@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 
 
 TP_LAUNCHES = 6  # pass 1, 2a, 2b, 3, the shift of replica counts, and the one-trace-per-thread kernel for the traces pass 3 gave up
-TP_SUMMARY_LAUNCHES = 6  # pass 0 (entry states), 1, 2a, 2b, 3, and that kernel
+TP_SUMMARY_LAUNCHES = 8  # pass 0 (entry states), 1, 2a, 2b, 3a, the second replay of listed chunks, 3b, and that kernel
 
 
 def chunks_used(T, chunks):
@@ -319,3 +319,41 @@ def test_traces_that_go_quiet_or_stay_away_from_the_limits(engine):
                     run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"{name} N={N} chunks={chunks} warm={warm}", warm=warm)
             run_and_check(engine, pol, depth, T, 1, N, N, 0, st, 5, f"{name} N={N} with failures", warm=8,
                           fail=random_mask(rng, T, N, 0.15))
+
+
+def test_saturated_and_idle_queues(engine):
+    """The two steady states of a real fleet: a queue that stays above the scale-up threshold (replicas
+    at max, ScaleUp called every cool-down period) and one that stays empty (at min, ScaleDown every
+    period). The calls of such a stretch are exactly one cool-down apart and their phase is set by its
+    first call, so a chunk started from a guess inside the stretch keeps a wrong phase for ever. Summary
+    mode works out the true entry states (the stretch's effect on a state has a closed form) and
+    replays those chunks a second time; here with cool-downs that do and do not divide the chunk
+    length, stretches that begin and end inside chunks, and a random-walk depth (long stretches on one
+    side of a threshold)."""
+    rng = np.random.default_rng(63)
+    T = 900
+    for N in (70, 64):
+        sat = np.full((T, 1, N), 500)
+        idle = np.zeros((T, 1, N), dtype=np.int64)
+        mixed = rng.integers(0, 400, size=(T, 1, N))
+        mixed[150:520] = 500      # saturated from inside chunk ... to inside chunk ...
+        mixed[600:] = 0           # then idle to the end
+        per_trace = rng.integers(0, 400, size=(T, 1, N))
+        starts = rng.integers(50, 400, size=N)
+        for n in range(N):
+            per_trace[starts[n]:starts[n] + 350, 0, n] = 300 if n % 2 else 3
+        walk = np.clip(np.cumsum(rng.integers(-15, 16, size=(T, 1, N)), axis=0) + 250, 0, 500)
+        policies = [ksa.Policy(attr_mask=1),                                                               # cool-downs of 2 and 6 ticks
+                    ksa.Policy(attr_mask=1, scale_up_cool_down=35 * S, scale_down_cool_down=55 * S),       # 7 and 11
+                    ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=5 * S, max_pods=9),  # 0 and 1
+                    ksa.Policy(attr_mask=1, scale_up_cool_down=4000 * S, scale_down_cool_down=13 * S, max_pods=40, min_pods=-7,
+                               scale_up_pods=3, scale_down_pods=2),                                        # longer than a chunk
+                    ksa.Policy(attr_mask=1, scale_up_messages=10, scale_down_messages=100)]                # thresholds overlap
+        for pi, pol in enumerate(policies):
+            for name, depth in (("saturated", sat), ("idle", idle), ("mixed", mixed), ("per trace", per_trace), ("walk", walk)):
+                depth = np.ascontiguousarray(depth, dtype=np.int64)
+                st = (rng.integers(-2, 12, size=N).astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+                for chunks in (3, 7):
+                    run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"{name} policy {pi} N={N} chunks={chunks}", warm=16)
+            run_and_check(engine, policies[pi], np.ascontiguousarray(mixed, dtype=np.int64), T, 1, N, N, 0, st, 5,
+                          f"mixed policy {pi} N={N} with failures", warm=8, fail=random_mask(rng, T, N, 0.05))

@@ -31,6 +31,9 @@ def main():
     ap.add_argument("--quiet-after", type=int, default=0,
                     help="ticks after which every depth is 50 (between the thresholds: no scale event ever again, so a "
                          "chunk started from a guessed replica count never meets the true trajectory); 0 = off")
+    ap.add_argument("--family", default="bands", choices=["bands", "walk"],
+                    help="depth generator: independent values in three bands, or a bounded random walk (step 15, wall 500: long "
+                         "stretches on one side of a threshold, and between the two)")
     ap.add_argument("--fail-log2", default="5,4,4", help="failure mask: poll, up, down bits each with probability 2^-k (0 = never)")
     ap.add_argument("--warm", default="", help="comma list of KSA_TIMEPAR_WARM values to try (default: the library's)")
     args = ap.parse_args()
@@ -43,7 +46,11 @@ def main():
     gen = ksa.GenParams(seed=0x5EED0001)
     for shape in args.shapes.split(","):
         N, T = (int(x) for x in shape.split("x"))
-        depth = eng.gen_traces(gen, 0, T, 1, 0, N, N)
+        if args.family == "walk":
+            wgen = ksa.GenParams(seed=0x5EED0004, family=ksa.GEN_WALK, high_max=500, walk_step=15)
+            depth = eng.gen_traces(wgen, 0, T, 1, 0, N, N, walk=eng.gen_walk_init(wgen, 0, N))
+        else:
+            depth = eng.gen_traces(gen, 0, T, 1, 0, N, N)
         if args.quiet_after:
             depth[args.quiet_after:] = 50
         replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
