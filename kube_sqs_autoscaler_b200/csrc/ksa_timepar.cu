@@ -104,7 +104,20 @@ constexpr int kChainReplays = 2;  // chunks pass 3 replays by itself per trace b
 // The offset pass 3 decided to shift a chunk's replica counts by (0: none; pass 2a clears it), applied by
 // tp_shift_kernel.
 static __device__ int g_tp_delta[kMaxChunks];
-constexpr int kLeftToShift = 100;  // TpChunk::status: pass 2b left the chunk to pass 3, which shifts it
+constexpr int kLeftToShift = 100;  // TpChunk::status: pass 2a left the chunk to pass 3, which shifts it
+constexpr int kListed = 101;       // listed for pass 2b, which replaces it unless it leaves the chunk alone
+constexpr int kRerun = 102;        // replayed a second time from the entry state pass 3a put into entry1
+
+// What pass 2b replayed a listed chunk from (the previous chunk's exit state at that time: the second
+// replay may change that one later), and what kind of chunk it is (tp_classify_kernel).
+static __device__ TpState g_tp_used[kMaxChunks];
+static __device__ unsigned char g_tp_kind[kMaxChunks];
+// The probe's verdict (tp_probe_kernel): pairs (sampled trace, chunk start) at which warm-ups of three
+// lengths did not meet. Above TpArgs::probe_limit every pass returns at once and the plain kernel does the call.
+static __device__ int g_tp_probe_bad;
+// The trace has a chunk that neither stands as pass 1 wrote it nor was patched up to a checkpoint by pass 2b:
+// passes 3a / 3b walk its chunks in order (set by passes 2a / 2b, cleared by pass 3b).
+static __device__ int g_tp_walk[kMaxTraces];
 
 struct TpArgs {
   ksa_policy_k pk;
@@ -113,6 +126,9 @@ struct TpArgs {
   long long ld, tick0, N;
   int T, A, K, L;  // ticks of the call, attribute planes, chunks, ticks per chunk (a multiple of 8)
   int warm;        // ticks replayed before a chunk without output (a multiple of 8, <= L)
+  int fix_limit;   // pass 2b leaves everything to pass 3a when more chunks than this are listed
+  int probe_limit; // INT_MAX: no probe was run
+  int probe_traces, probe_stride;  // the probe's sample: groups of 32 adjacent traces, `stride` traces from group to group
   int one;
   int* st_r;
   long long* st_ju;
@@ -216,23 +232,32 @@ __device__ __forceinline__ void tp_store(int* rp, unsigned char* ep, const int (
   }
 }
 
-template <int A, int V, int D, int TPB, int MINB, bool FAULTS>
+// RERUN: the second replay. Only the chunks pass 3a marked (kRerun), from the entry state it put into
+// entry1, no warm-up; one trace per thread.
+template <int A, int V, int D, int TPB, int MINB, bool FAULTS, bool RERUN = false>
 __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constant__ TpArgs a) {
   const long long n0 = ((long long)blockIdx.x * TPB + threadIdx.x) * V;
-  if (n0 >= a.N) return;  // (V > 1: N is a multiple of 8)
-  const int k = blockIdx.y;
+  if (n0 >= a.N || g_tp_probe_bad > a.probe_limit) return;  // (V > 1: N is a multiple of 8)
+  const int k = RERUN ? blockIdx.y + 1 : blockIdx.y;
+  if constexpr (RERUN) {
+    static_assert(V == 1, "the second replay runs one trace per thread");
+    if (record(a, k, n0)->status != kRerun) return;
+  }
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
-  const int tb = k == 0 ? 0 : t0 - a.warm;  // first tick replayed
+  const int tb = (k == 0 || RERUN) ? t0 : t0 - a.warm;  // first tick replayed
   const int te = t0 + len;
   const ksa_step_consts c(a.pk);
   const int one = a.one;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_tp_count = 0;  // pass 2a's list starts empty
+  if (!RERUN && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_tp_count = 0;  // pass 2a's list starts empty
   ksa_trace_regs s[V];
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     s[v].r = a.st_r[n0 + v];
-    if (k == 0) {
+    if constexpr (RERUN) {
+      const TpState e = record(a, k, n0 + v)->entry1;
+      s[v] = ksa_trace_regs{e.r, e.su, e.sd};
+    } else if (k == 0) {
       s[v].su = ksa_local_stamp(a.pk.cu, c.cu, a.tick0, a.st_ju[n0 + v]);
       s[v].sd = ksa_local_stamp(a.pk.cd, c.cd, a.tick0, a.st_jd[n0 + v]);
     } else {
@@ -300,8 +325,10 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
 #pragma unroll
     for (int j = 0; j < D; ++j) tick(t + j, j, t + j + D < te, false);
   }
+  if constexpr (!RERUN) {
 #pragma unroll
-  for (int v = 0; v < V; ++v) record(a, k, n0 + v)->entry1 = TpState{s[v].r, s[v].su, s[v].sd};
+    for (int v = 0; v < V; ++v) record(a, k, n0 + v)->entry1 = TpState{s[v].r, s[v].su, s[v].sd};
+  }
   // the chunk: steady state, then the drain with guards
 #pragma unroll 1
   for (; t + 2 * D <= te; t += D) {
@@ -327,7 +354,7 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     record(a, k, n0 + v)->exit1 = TpState{s[v].r, s[v].su, s[v].sd};
-    record(a, k, n0 + v)->status = 0;
+    if constexpr (!RERUN) record(a, k, n0 + v)->status = 0;
   }
 }
 
@@ -376,11 +403,74 @@ __device__ int tp_replay_until_match(const TpArgs& a, const ksa_step_consts& c, 
   return -1;
 }
 
+// ---- before pass 1, for trace counts at which a second replay costs more than the plain kernel -----------
+// Do guesses meet the truth on these depths at all? Where every tick meets the same threshold for long
+// (a saturated or an idle queue) the scale calls come exactly one cool-down apart, and a run started
+// from a guess keeps whatever phase its starting tick gave it: such chunks are replayed a second time
+// (pass 3a), and from about 16384 traces on two chunked replays cost more than one plain one (random-walk
+// depths, profiles/r02_small_n_modes.txt). The probe tells in 25 us: for a sample of traces and every
+// chunk start, warm-ups of three lengths (their differences 61 and 97 ticks: no cool-down of a few
+// ticks divides them) either end in states with the same future, as runs that have met the truth do,
+// or not. Block = 32 (trace, chunk start) pairs x 3 warm-ups.
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(96) tp_probe_kernel(const __grid_constant__ TpArgs a) {
+  __shared__ TpState ended[3][32];
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_tp_probe_bad = 0;
+  const int variant = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const long long pair = (long long)blockIdx.x * 32 + lane;
+  const long long pairs = (long long)a.probe_traces * (a.K - 1);
+  const int k = (int)(pair / a.probe_traces) + 1;
+  // the sample: groups of 32 adjacent traces (a warp's loads are one 256-byte run), the groups spread over the call's traces
+  const long long sample = pair % a.probe_traces;
+  const long long n = (sample / 32) * a.probe_stride + sample % 32;
+  const bool live = pair < pairs && n < a.N;
+  const int t0 = k * a.L;
+  if (live) {
+    const ksa_step_consts c(a.pk);
+    const int w = min(variant == 0 ? 128 : (variant == 1 ? 189 : 286), t0);
+    ksa_trace_regs s{a.st_r[n], 0, 0};  // pass 1's guess
+    const int first = t0 - w;
+    constexpr int G = 16;
+    const long long row = (long long)A * a.ld;
+    const long long* dp = a.depth + (long long)first * row + n;
+    const unsigned char* fp = FAULTS ? a.fail + (long long)first * a.ld + n : nullptr;
+    long long buf[G];
+    unsigned fbuf[FAULTS ? G : 1];
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+      buf[j] = j < w ? load_sum(dp + (long long)j * row, a.ld, A) : 0;
+      if constexpr (FAULTS) fbuf[j] = j < w ? (unsigned)__ldg(fp + (long long)j * a.ld) : 0u;
+    }
+    for (int t = 0; t < w; t += G) {
+#pragma unroll
+      for (int j = 0; j < G; ++j) {
+        const int tt = t + j;
+        if (tt < w) {
+          const long long msgs = buf[j];
+          const unsigned f = FAULTS ? fbuf[j] : 0u;
+          if (tt + G < w) {
+            buf[j] = load_sum(dp + (long long)(tt + G) * row, a.ld, A);
+            if constexpr (FAULTS) fbuf[j] = (unsigned)__ldg(fp + (long long)(tt + G) * a.ld);
+          }
+          if constexpr (FAULTS) ksa_step_faults(c, msgs, f, first + tt + 1, s);
+          else ksa_step(c, msgs, first + tt + 1, s);
+        }
+      }
+    }
+    ended[variant][lane] = TpState{s.r, s.su, s.sd};
+  }
+  __syncthreads();
+  if (live && variant == 0 &&
+      !(same_future(ended[0][lane], ended[1][lane], t0) && same_future(ended[0][lane], ended[2][lane], t0)))
+    atomicAdd(&g_tp_probe_bad, 1);
+}
+
 // ---- pass 2a -------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(BLOCK) tp_check_kernel(const __grid_constant__ TpArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   const int k = blockIdx.y + 1;
   bool need = false;
+  if (g_tp_probe_bad > a.probe_limit) return;
   if (n < a.N) {
     const TpState entry = record(a, k - 1, n)->exit1;
     TpChunk* const rec = record(a, k, n);
@@ -390,8 +480,10 @@ __global__ void __launch_bounds__(BLOCK) tp_check_kernel(const __grid_constant__
     // does that, with the true offset (which it alone knows: the previous chunk may itself get shifted)
     if (need && same_gates(entry, rec->entry1, k * a.L) && shift_safe(*rec)) {
       rec->status = kLeftToShift;
+      g_tp_walk[n] = 1;
       need = false;
     }
+    if (need) rec->status = kListed;  // pass 2b replaces it when it gets the chunk done
   }
   // one atomic per warp
   const unsigned vote = __ballot_sync(0xffffffffu, need);
@@ -407,19 +499,90 @@ __global__ void __launch_bounds__(BLOCK) tp_check_kernel(const __grid_constant__
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_fix_kernel(const __grid_constant__ TpArgs a) {
   const int idx = blockIdx.x * BLOCK + threadIdx.x;
-  if (idx >= g_tp_count) return;
+  // This pass is for the few chunks whose guess met the truth a little late. When many are listed the
+  // guesses fail for a reason (stretches in which every tick meets a threshold: the phase of the calls):
+  // everything is left to pass 3a and the second replay.
+  if (idx >= g_tp_count || g_tp_probe_bad > a.probe_limit) return;
   const int item = g_tp_list[idx];
   const int k = (int)(item / a.N);
   const long long n = item % a.N;
+  if (g_tp_count > a.fix_limit) {
+    g_tp_walk[n] = 1;
+    return;
+  }
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
   const ksa_step_consts c(a.pk);
   TpChunk* const rec = record(a, k, n);
   const TpState entry = record(a, k - 1, n)->exit1;
+  g_tp_used[item] = entry;
   ksa_trace_regs s{entry.r, entry.su, entry.sd};
   const int j = tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, 0, s);
   rec->entry1 = TpState{s.r, s.su, s.sd};  // (the slot is free: pass 2a has read it)
   rec->status = j >= 0 ? j + 1 : -1;
+  if (j < 0) g_tp_walk[n] = 1;  // the chunk after it was judged by an exit state that is not the true one
+}
+
+// ---- between pass 2b and pass 3a ---------------------------------------------------------------------
+// Thread (trace, chunk >= 1) of a trace that will be walked: does EVERY tick of the chunk meet the scale-up
+// threshold (1), or the scale-down threshold (2)? From the event bytes pass 1 wrote (a tick that meets a
+// threshold logs exactly one of that direction's three lines, whatever the state); 0 otherwise, and
+// for policies whose thresholds overlap or with a failure mask (a failed call takes no stamp). Such a
+// chunk is the saturated queue (replicas at max, ScaleUp called every cool-down period) or the idle one
+// (at min, ScaleDown every period): the steady states of a real fleet. Its calls are exactly one
+// cool-down apart, their phase set by the first one, so a chunk started from a guess deep inside such a
+// stretch keeps the wrong phase for ever and no warm-up helps; but what the chunk does to a state has
+// a closed form (pure_exit), which is how pass 3a gets through it.
+template <bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_classify_kernel(const __grid_constant__ TpArgs a) {
+  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (n >= a.N || g_tp_probe_bad > a.probe_limit || g_tp_walk[n] == 0) return;
+  const int k = blockIdx.y + 1;
+  unsigned char kind = 0;
+  if (!FAULTS && a.pk.up_msgs > a.pk.down_msgs) {
+    const int t0 = k * a.L;
+    const int len = min(a.L, a.T - t0);
+    const unsigned char* ep = a.events + (long long)t0 * a.ld + n;
+    constexpr unsigned kUp = KSA_EV_UP_APPLIED | KSA_EV_UP_NOOP | KSA_EV_UP_COOL;
+    constexpr unsigned kDown = KSA_EV_DOWN_APPLIED | KSA_EV_DOWN_NOOP | KSA_EV_DOWN_COOL;
+    bool all_up = true, all_down = true;
+    constexpr int G = 8;
+    for (int t = 0; t < len && (all_up || all_down); t += G) {
+      unsigned e[G];
+#pragma unroll
+      for (int j = 0; j < G; ++j) e[j] = t + j < len ? (unsigned)ep[(long long)(t + j) * a.ld] : (kUp | kDown);
+#pragma unroll
+      for (int j = 0; j < G; ++j) {
+        all_up = all_up && (e[j] & kUp) != 0u;
+        all_down = all_down && (e[j] & kDown) != 0u;
+      }
+    }
+    kind = all_up ? 1 : (all_down ? 2 : 0);
+  }
+  g_tp_kind[(long long)k * a.N + n] = kind;
+}
+
+// The state after a chunk of that kind: the first call at the first tick the gate is open, then one
+// every cool-down period, each a full step towards the limit (scale.go:62-69, 89-97). Chunk = local
+// ticks t0 + 1 .. t0 + len. False: not worked out (steps that are negative or could wrap).
+__device__ __forceinline__ bool pure_exit(const ksa_step_consts& c, int kind, int t0, int len, TpState& g) {
+  const bool up = kind == 1;
+  const int step = up ? c.up32 : c.down32;
+  if (step < 0 || step > (1 << 30)) return false;
+  const int cool = up ? c.cu : c.cd;
+  const long long first = max(t0 + 1, up ? g.su : g.sd);  // blocked at local tick i <=> i < s
+  if (first > t0 + len) return true;                      // the gate stays shut for the whole chunk
+  const long long period = max(cool, 1);
+  const long long calls = (t0 + len - first) / period + 1;
+  const long long last = first + (calls - 1) * period;
+  if (up) {
+    g.su = (int)(last + cool);
+    if (g.r < c.max32) g.r = (int)min((long long)g.r + calls * step, (long long)c.max32);
+  } else {
+    g.sd = (int)(last + cool);
+    if (g.r > c.min32) g.r = (int)max((long long)g.r - calls * step, (long long)c.min32);
+  }
+  return true;
 }
 
 // ---- pass 3 --------------------------------------------------------------------------------------
@@ -428,94 +591,130 @@ __device__ __forceinline__ int later_stamp(int keep, int cand, int c, int after)
   return (cand - c > after) ? cand : keep;
 }
 
+// The walk over a trace's chunks with the true state, for traces in which not every chunk simply stands.
+//  - A chunk whose outputs are pass 1's or the second replay's (status 0, kLeftToShift, kListed, kRerun)
+//    was replayed from entry1 and ended with exit1: it stands if entry1 has the true future, or, when only
+//    the replica count is off and no scale call happened in it, after a shift (tp_shift_kernel).
+//  - A chunk pass 2b patched (status j + 1, -1) was replayed from g_tp_used: it stands if that has the
+//    true future.
+//  Otherwise:
+//  RESOLVE (pass 3a, before the second replay): the chunk is marked (kRerun) to be replayed a second time
+//    from the true state, which goes into entry1. What it will end with is not known yet, and the next
+//    chunk needs it: worked out for a chunk in which every tick met the same threshold (pure_exit), assumed
+//    to be what it ended with the first time otherwise (most chunks forget the state they were entered
+//    with). Wrong assumptions cost time, not correctness:
+//  FINAL (pass 3b, after the second replay): the same walk over what is there now. A chunk that still does
+//    not fit is replayed here, up to kChainReplays per trace; a trace that needs more is flagged for the
+//    one-trace-per-thread kernel that follows and its state is left alone.
+// Returns false if the trace is given up.
+template <int A, bool FAULTS, bool RESOLVE>
+__device__ bool tp_walk(const TpArgs& a, const ksa_step_consts& c, long long n, TpState& cur) {
+  int replays = 0;
+  for (int k = 1; k < a.K; ++k) {
+    const int t0 = k * a.L;
+    const int len = min(a.L, a.T - t0);
+    const long long idx = (long long)k * a.N + n;
+    TpChunk* const rec = record(a, k, n);
+    const int status = rec->status;
+    const bool patched = status < 0 || (status >= 1 && status <= kChecks);
+    if (!patched) {
+      const long long delta = (long long)cur.r - rec->entry1.r;
+      if (same_gates(rec->entry1, cur, t0) && (delta == 0 || shift_safe(*rec))) {
+        if (!RESOLVE && delta != 0) g_tp_delta[idx] = (int)delta;
+        cur.r = (int)(rec->exit1.r + delta);
+        cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, t0);
+        continue;
+      }
+    } else if (same_future(g_tp_used[idx], cur, t0)) {
+      // pass 2b started from (the equivalent of) the true state: its work stands
+      if (status < 0) {  // 2b rewrote the whole chunk; its end state is in the entry1 slot
+        cur.r = rec->entry1.r;
+        cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
+      } else {
+        const int tc = t0 + check_tick(status - 1);  // pass 1's trajectory is the true one after tc
+        cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
+        cur.r = rec->exit1.r;
+        cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, tc);
+        cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, tc);
+      }
+      continue;
+    }
+    if (RESOLVE) {
+      // what the chunk ended with the first time (pass 2b's end state is in the entry1 slot)
+      const TpState ended = status < 0 ? rec->entry1 : rec->exit1;
+      rec->entry1 = cur;
+      rec->status = kRerun;
+      TpState worked = cur;
+      const int kind = g_tp_kind[idx];
+      if (kind != 0 && pure_exit(c, kind, t0, len, worked)) {
+        cur = worked;
+      } else {
+        cur.r = ended.r;
+        cur.su = later_stamp(cur.su, ended.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, ended.sd, c.cd, t0);
+      }
+    } else {
+      if (++replays > kChainReplays) return false;  // left to the plain kernel that follows (g_tp_unresolved)
+      ksa_trace_regs s{cur.r, cur.su, cur.sd};
+      tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, kChecks, s);  // (the whole chunk: no checkpoint applies)
+      cur = TpState{s.r, s.su, s.sd};
+      g_tp_delta[idx] = 0;
+    }
+  }
+  return true;
+}
+
+// ---- pass 3a: thread (trace) -----------------------------------------------------------------------
+template <int A, bool FAULTS>
+__global__ void __launch_bounds__(BLOCK) tp_resolve_kernel(const __grid_constant__ TpArgs a) {
+  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (n >= a.N || g_tp_probe_bad > a.probe_limit || g_tp_walk[n] == 0) return;
+  const ksa_step_consts c(a.pk);
+  TpState cur = record(a, 0, n)->exit1;  // chunk 0 ran from the true state
+  tp_walk<A, FAULTS, true>(a, c, n, cur);
+}
+
+// ---- pass 3b: thread (trace) -----------------------------------------------------------------------
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__ TpArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
+  if (g_tp_probe_bad > a.probe_limit) {  // the probe called the chunked passes off: every trace is the plain kernel's
+    g_tp_unresolved[n] = 1;
+    return;
+  }
   const ksa_step_consts c(a.pk);
   TpState cur = record(a, 0, n)->exit1;  // chunk 0 ran from the true state
-  // Every chunk converged (the common case): all entry states were the true ones, the replica count is
-  // the last chunk's, and each stamp is the latest one taken where the trajectory was the true one.
-  // Valid candidates are later than anything before them, so "latest" is a maximum and the loop has
-  // no dependence from one chunk's record to the next one's loads.
-  bool all = true;
-  int su = cur.su, sd = cur.sd;
-  for (int k = 1; k < a.K; ++k) {
-    const TpChunk* rec = record(a, k, n);
-    const int status = rec->status;
-    const int t0 = k * a.L;
-    all = all && status >= 0 && status != kLeftToShift;
-    const int tc = status <= 0 ? t0 : t0 + check_tick(status - 1);
-    if (status > 0) {  // pass 2b's own replay, from the chunk's first tick
-      su = max(su, later_stamp(INT_MIN, rec->entry1.su, c.cu, t0));
-      sd = max(sd, later_stamp(INT_MIN, rec->entry1.sd, c.cd, t0));
+  if (g_tp_walk[n] == 0) {
+    // Every chunk stands as pass 1 wrote it, or as pass 2b patched it up to a checkpoint from the previous
+    // chunk's exit (the common case): all entry states were the true ones, the replica count is the last
+    // chunk's, and each stamp is the latest one taken where the trajectory was the true one. Valid
+    // candidates are later than anything before them, so "latest" is a maximum and the loop has no
+    // dependence from one chunk's record to the next one's loads.
+    int su = cur.su, sd = cur.sd;
+    for (int k = 1; k < a.K; ++k) {
+      const TpChunk* rec = record(a, k, n);
+      const int status = rec->status;
+      const int t0 = k * a.L;
+      const int tc = status == 0 ? t0 : t0 + check_tick(status - 1);
+      if (status > 0) {  // pass 2b's own replay, from the chunk's first tick
+        su = max(su, later_stamp(INT_MIN, rec->entry1.su, c.cu, t0));
+        sd = max(sd, later_stamp(INT_MIN, rec->entry1.sd, c.cd, t0));
+      }
+      su = max(su, later_stamp(INT_MIN, rec->exit1.su, c.cu, tc));
+      sd = max(sd, later_stamp(INT_MIN, rec->exit1.sd, c.cd, tc));
     }
-    su = max(su, later_stamp(INT_MIN, rec->exit1.su, c.cu, tc));
-    sd = max(sd, later_stamp(INT_MIN, rec->exit1.sd, c.cd, tc));
-  }
-  if (all) {
     cur.r = record(a, a.K - 1, n)->exit1.r;
     cur.su = su;
     cur.sd = sd;
   } else {
-    // Some chunk never converged: walk the chunks in order with the true state.
-    int replays = 0;
-    for (int k = 1; k < a.K; ++k) {
-      const int t0 = k * a.L;
-      const int len = min(a.L, a.T - t0);
-      const TpChunk* rec = record(a, k, n);
-      const TpState used = record(a, k - 1, n)->exit1;  // pass 2's entry state
-      const int status = rec->status;
-      if (status == 0 || status == kLeftToShift) {
-        // the outputs and exit1 are pass 1's, replayed from entry1: they stand if that has the true future,
-        // or if only its replica count is off by an offset the chunk can be shifted by (tp_shift_kernel)
-        const long long delta = (long long)cur.r - rec->entry1.r;
-        if (same_gates(rec->entry1, cur, t0) && (delta == 0 || shift_safe(*rec))) {
-          if (delta != 0) g_tp_delta[(long long)k * a.N + n] = (int)delta;
-          cur.r = (int)(rec->exit1.r + delta);
-          cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, t0);
-          cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, t0);
-          continue;
-        }
-      }
-      if (status != kLeftToShift && same_future(used, cur, t0)) {
-        // pass 2 started from (the equivalent of) the true state: its work stands
-        if (status < 0) {  // 2b rewrote the whole chunk; its end state is in the entry1 slot
-          cur.r = rec->entry1.r;
-          cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
-          cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
-        } else {
-          const int tc = status == 0 ? t0 : t0 + check_tick(status - 1);  // pass 1's trajectory is true after tc
-          if (status > 0) {
-            cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
-            cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
-          }
-          cur.r = rec->exit1.r;
-          cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, tc);
-          cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, tc);
-        }
-      } else {
-        // an earlier chunk never converged: replay this one from the true state. The outputs are pass 2b's
-        // up to its checkpoint and pass 1's after it, so only checkpoints from there on can end the replay;
-        // if pass 2b rewrote the whole chunk, nothing of pass 1 is left in it.
-        if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
-          g_tp_unresolved[n] = 1;
-          return;
-        }
-        ksa_trace_regs s{cur.r, cur.su, cur.sd};
-        const int first = status < 0 ? kChecks : (status == 0 || status == kLeftToShift ? 0 : status - 1);
-        const int j = tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, first, s);
-        cur.su = s.su;
-        cur.sd = s.sd;
-        if (j >= 0) {
-          const int tc = t0 + check_tick(j);
-          cur.r = rec->exit1.r;
-          cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, tc);
-          cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, tc);
-        } else {
-          cur.r = s.r;
-        }
-      }
+    g_tp_walk[n] = 0;  // (for the next call)
+    if (!tp_walk<A, FAULTS, false>(a, c, n, cur)) {
+      g_tp_unresolved[n] = 1;
+      return;
     }
   }
   g_tp_unresolved[n] = 0;
@@ -530,6 +729,7 @@ __global__ void __launch_bounds__(BLOCK) tp_shift_kernel(const __grid_constant__
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
   const int k = blockIdx.y + 1;
+  if (g_tp_probe_bad > a.probe_limit) return;
   const int delta = g_tp_delta[(long long)k * a.N + n];
   if (delta == 0 || g_tp_unresolved[n] != 0) return;  // (a trace pass 3 gave up is rewritten by the plain kernel)
   const int t0 = k * a.L;
@@ -1288,6 +1488,11 @@ int tp_release(cudaStream_t st, int device) {
 
 template <int A, bool FAULTS>
 int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
+  if (a.probe_limit != INT_MAX) {
+    const long long pairs = (long long)a.probe_traces * (a.K - 1);
+    tp_probe_kernel<A, FAULTS><<<(unsigned)((pairs + 31) / 32), 96, 0, st>>>(a);
+    KSA_LAUNCH_CHECK("tp_probe_kernel");
+  }
   if (wide) {
     if constexpr (FAULTS) {
       // 4 traces per thread, the shape of ksa_replay_full_faults' default: with eight interleaved the
@@ -1310,6 +1515,14 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
   const long long items = a.N * (a.K - 1);  // (the list's length is only known on the device: idle threads return at once)
   tp_fix_kernel<A, FAULTS><<<(unsigned)((items + BLOCK - 1) / BLOCK), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_fix_kernel");
+  // traces with chunks that neither stand nor got patched: what kind of chunks they have, their true entry
+  // states, a second replay of the chunks that need one (threads of the other chunks return at once)
+  tp_classify_kernel<FAULTS><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_classify_kernel");
+  tp_resolve_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_resolve_kernel");
+  tp_spec_kernel<A, 1, 8, BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4), FAULTS, true><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_spec_kernel (second replay)");
   tp_chain_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_chain_kernel");
   tp_shift_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
@@ -1442,6 +1655,15 @@ int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, co
   a.K = K;
   a.L = L;
   a.warm = warm;
+  a.fix_limit = (int)std::max<int64_t>(64, N * (K - 1) / 32);
+  // Up to 16384 traces even two chunked replays beat the plain kernel; beyond, a probe decides first
+  // (KSA_TIMEPAR_PROBE=0 / 1 forces it off / on).
+  bool probe = N > 16384;
+  if (const char* e = std::getenv("KSA_TIMEPAR_PROBE")) probe = std::atoi(e) != 0;
+  a.probe_traces = (int)std::min<int64_t>(N / 32 * 32, 512);
+  a.probe_stride = a.probe_traces >= 32 ? (int)(N / (a.probe_traces / 32)) : 0;
+  if (a.probe_traces < 32) probe = false;
+  a.probe_limit = probe ? (int)((int64_t)a.probe_traces * (K - 1) / 8) : INT_MAX;
   a.one = 1;
   a.st_r = state->replicas_dev;
   a.st_ju = (long long*)state->last_up_tick_dev;

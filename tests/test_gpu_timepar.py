@@ -20,7 +20,7 @@ from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 pytestmark = pytest.mark.gpu
 
 
-TP_LAUNCHES = 6  # pass 1, 2a, 2b, 3, the shift of replica counts, and the one-trace-per-thread kernel for the traces pass 3 gave up
+TP_LAUNCHES = 9  # pass 1, 2a, 2b, the chunks' kinds, 3a, the second replay, 3b, the shift of replica counts, the kernel for traces given up
 TP_SUMMARY_LAUNCHES = 8  # pass 0 (entry states), 1, 2a, 2b, 3a, the second replay of listed chunks, 3b, and that kernel
 
 
@@ -32,7 +32,7 @@ def chunks_used(T, chunks):
     return (T + L - 1) // L
 
 
-def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, warm=None, wide=None, fail=None):
+def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, warm=None, wide=None, fail=None, probe=None):
     """Full and summary replay with `chunks` forced (None = the library's own choice), `fail` = a
     [T][ld] failure mask for the *_faults entry points; returns the launches the full replay took."""
     import torch
@@ -40,7 +40,8 @@ def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, war
     ref = oracle_lib.replay(pol.to_c(), depth, T, A, N, ld, tick0, *st, want_summary=True, fail=fail)
     d = torch.from_numpy(np.ascontiguousarray(depth)).to(engine.dev)
     f = None if fail is None else torch.from_numpy(np.ascontiguousarray(fail, dtype=np.uint8)).to(engine.dev)
-    for key, val in (("KSA_TIMEPAR_CHUNKS", chunks), ("KSA_TIMEPAR_WARM", warm), ("KSA_TIMEPAR_WIDE", wide)):
+    for key, val in (("KSA_TIMEPAR_CHUNKS", chunks), ("KSA_TIMEPAR_WARM", warm), ("KSA_TIMEPAR_WIDE", wide),
+                     ("KSA_TIMEPAR_PROBE", probe)):
         if val is None:
             os.environ.pop(key, None)
         else:
@@ -58,7 +59,7 @@ def run_and_check(engine, pol, depth, T, A, N, ld, tick0, st, chunks, label, war
         launches_summary = engine.launch_count()
         summ = summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1)
     finally:
-        for key in ("KSA_TIMEPAR_CHUNKS", "KSA_TIMEPAR_WARM", "KSA_TIMEPAR_WIDE"):
+        for key in ("KSA_TIMEPAR_CHUNKS", "KSA_TIMEPAR_WARM", "KSA_TIMEPAR_WIDE", "KSA_TIMEPAR_PROBE"):
             os.environ.pop(key, None)
     where = np.argwhere(r[:, :N] != ref.replicas[:, :N])
     assert where.size == 0, f"{label}: replicas differ first at (tick, trace) {where[0]} of {where.shape[0]}"
@@ -357,3 +358,9 @@ def test_saturated_and_idle_queues(engine):
                     run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"{name} policy {pi} N={N} chunks={chunks}", warm=16)
             run_and_check(engine, policies[pi], np.ascontiguousarray(mixed, dtype=np.int64), T, 1, N, N, 0, st, 5,
                           f"mixed policy {pi} N={N} with failures", warm=8, fail=random_mask(rng, T, N, 0.05))
+            # the probe that comes before pass 1 of the full replay above 16384 traces, forced on: on the saturated
+            # depths it calls the chunked passes off (every trace goes to the plain kernel), on random ones it does not
+            for name, depth in (("saturated", sat), ("independent", rng.integers(0, 400, size=(T, 1, N)))):
+                took = run_and_check(engine, pol, np.ascontiguousarray(depth, dtype=np.int64), T, 1, N, N, 0, st, 3,
+                                     f"{name} policy {pi} N={N} with the probe", probe=1)
+                assert took == TP_LAUNCHES + 1
