@@ -21,7 +21,7 @@
  *    the host heap (ksa_dev_alloc / ksa_host_alloc and ksa_pipeline_create are the allocating
  *    helpers). Two fixed arrays live in the library's device image on every GPU that loads it:
  *    the policy table of ksa_replay_sweep_static (192 KB) and the scratch records of the
- *    time-parallel paths of the four replay entry points (69 MB, see ksa_replay_full).
+ *    time-parallel paths of the four replay entry points (76 MB, see ksa_replay_full).
  *  - Ticks: tick k (1-based, absolute) happens at t0 + k*poll (main.go:41). A call replays the
  *    T ticks tick0+1 .. tick0+T; `tick0` is the number of ticks already replayed for these
  *    traces (0 for a fresh start), which is what lets long traces be streamed in T-chunks.
@@ -216,8 +216,11 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  * fill the GPU, so the library cuts the time axis into chunks that are replayed in parallel from
  * guessed states and then stitched exactly (csrc/ksa_timepar.cu; results are identical, the
  * trajectory and the carry state bit for bit). ksa_replay_summary and the two *_faults entry points
- * do the same below their own trace counts (65536, 49152 / 81920): there the chunks' summary
- * records, including the fingerprint, are combined in tick order. That path keeps its per-chunk
+ * do the same below their own trace counts (32768, 32768 / 81920): there the chunks' summary
+ * records, including the fingerprint, are combined in tick order. Chunks whose guess never meets
+ * the truth (a queue that stays saturated, idle or quiet) are worked out or replayed a second time,
+ * and above 16384 traces a 60 us probe decides first whether the depths suit the path at all; the
+ * worst case found costs 1.3 x the plain kernels. That path keeps its per-chunk
  * records in fixed scratch arrays inside the library, so only one such call runs per GPU at a
  * time: a call that finds the scratch in use by a call on another stream, or a stream that is being
  * captured, takes the one-thread-per-trace kernels instead (same results, slower).

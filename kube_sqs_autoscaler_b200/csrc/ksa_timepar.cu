@@ -20,23 +20,34 @@
 //          done; otherwise it goes on a list.
 //  pass 2b thread (list item): replay from the entry state, rewriting the outputs, until the state at a
 //          checkpoint has the same future as what pass 1 left there: from that tick on pass 1's
-//          outputs are already right. If no checkpoint matches, the whole chunk is rewritten.
-//  pass 3  thread (trace): if every chunk converged (2a or 2b), all entry states were the true ones by
+//          outputs are already right. If no checkpoint matches, the whole chunk is rewritten. Only
+//          when few chunks are listed: many mean that the guesses fail for a reason.
+//  pass 3a thread (trace), for traces with chunks that neither stand nor got patched: walk the chunks in
+//          order with the true state, O(1) per chunk. A chunk replayed from the right gates but a
+//          replica count that is off, and without a scale call, is shifted by the offset (the trace
+//          that goes quiet: its state never forgets). Any other chunk that does not fit is marked to
+//          be replayed a second time from the true state; the state after it is worked out for a chunk
+//          in which every tick met the same threshold (the saturated and the idle queue: calls exactly
+//          one cool-down apart, a guess keeps a wrong phase for ever; tp_classify_kernel, pure_exit),
+//          assumed to be what the chunk ended with the first time otherwise.
+//  then    the second replay: pass 1's kernel, one trace per thread, over the marked chunks.
+//  pass 3b thread (trace): if every chunk stands or was patched, all entry states were the true ones by
 //          induction, and the carry state is the last chunk's exit with the latest TRUE stamps.
-//          Otherwise walk the chunks in order with the true state. A chunk replayed from the right
-//          gates but a replica count that is off, and in which no scale call happened, is marked to
-//          be shifted by the offset (the trace that goes quiet after some activity: its state never
-//          forgets, so no warm-up makes a guess meet it); up to two chunks that were replayed from a
-//          wrong entry are replayed again here; a trace that needs more is flagged and left alone.
+//          Otherwise the same walk over what is there now: wrong assumptions of pass 3a show as chunks
+//          that still do not fit; up to two are replayed here, a trace that needs more is flagged
+//          and left alone.
 //  then    thread (trace, chunk): add the offset to the replica counts of the chunks marked for it;
 //          and the one-trace-per-thread kernel of ksa_replay.cu over the flagged traces only, from
-//          the caller's state. (Before these two, a single trace that never met its true trajectory
-//          made the call several times SLOWER than the plain kernels: pass 3 replayed its 10^5 ticks
-//          in one thread. Now the worst case is the chunked passes plus the plain kernel.)
+//          the caller's state. (Before passes 3a / second replay, a single trace that never met its
+//          true trajectory made the call several times SLOWER than the plain kernels: pass 3 replayed
+//          its 10^5 ticks in one thread.)
+//  first   above 16384 traces, where two chunked replays cost more than one plain one: a probe
+//          (tp_probe_kernel) of whether guesses meet the truth on these depths at all; if not, every
+//          pass returns at once and the plain kernel does the call.
 // Results are bit-identical to the sequential replay whatever K and `warm` are and whether or not
 // any chunk converges; the tests force small chunks on adversarial policies (one-sided clamps with
-// r0 outside [min, max], min > max, cool-downs longer than the call, traces that go quiet) to
-// check exactly that.
+// r0 outside [min, max], min > max, cool-downs longer than the call, traces that go quiet, saturated
+// and idle queues, random walks) to check exactly that.
 //
 // "Same future" at tick t means equal replica counts and equal gates for every later tick: a stamp
 // that opens its gate at or before tick t + 1 is as good as any other such stamp. The stamps
@@ -44,13 +55,13 @@
 // the true trajectory (a pass-1 stamp only counts if it was taken after the tick from which pass
 // 1's trajectory is the true one; stamps taken during the warm-up never do).
 //
-// Scratch: one 64-byte record per (trace, chunk) and a 4-byte list slot, in fixed device arrays of
-// the library image (kMaxChunks records: 34 MB per GPU; summary mode, further down, adds as many
-// ksa_summary records: 69 MB), so the entry points still allocate nothing.
+// Scratch: per (trace, chunk) a 64-byte record, a list slot and a few words, in fixed device arrays of
+// the library image (kMaxChunks slots: 44 MB per GPU; summary mode, further down, adds as many
+// ksa_summary records: 76 MB), so the entry points still allocate nothing.
 // One time-parallel replay per device at a time: a call that finds the scratch busy on another
 // stream takes the plain kernels instead.
 //
-// The same four passes serve ksa_replay_full_faults (FAULTS: the failure mask is read next to the
+// The same passes serve ksa_replay_full_faults (FAULTS: the failure mask is read next to the
 // depths; a failed call changes no state, so a run from a wrong state still meets the true one).
 // ksa_replay_summary / ksa_replay_summary_faults have no trajectory to patch and are built
 // differently: second half of this file.
