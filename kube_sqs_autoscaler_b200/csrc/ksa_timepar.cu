@@ -864,6 +864,10 @@ __device__ __forceinline__ bool tp_shift_safe(const ksa_step_consts& c, const ks
   const long long hi = max((long long)q.max_replicas, (long long)entry_r);
   const long long lo = min((long long)q.min_replicas, (long long)entry_r);
   if (hi + delta > INT_MAX || lo + delta < INT_MIN) return false;
+  // With overlapping thresholds a tick can step up AND down: the count after the tick does not show
+  // whether the step up was clamped in between (found by tools/fuzz_timepar.py). Only chunks without any
+  // call are shifted then.
+  if (!(c.up_msgs > c.down_msgs) && (q.up_applied | q.up_noop | q.down_applied | q.down_noop) != 0u) return false;
   if ((q.up_applied | q.up_noop) != 0u &&
       !(c.up32 >= 0 && c.up32 <= (1 << 30) && hi < c.max32 && hi + delta < c.max32))
     return false;

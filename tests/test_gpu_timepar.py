@@ -364,3 +364,29 @@ def test_saturated_and_idle_queues(engine):
                 took = run_and_check(engine, pol, np.ascontiguousarray(depth, dtype=np.int64), T, 1, N, N, 0, st, 3,
                                      f"{name} policy {pi} N={N} with the probe", probe=1)
                 assert took == TP_LAUNCHES + 1
+
+
+def test_overlapping_thresholds_step_up_and_down_in_one_tick(engine):
+    """With scale_up_messages <= scale_down_messages a tick can step up and down: the replica count
+    after the tick does not show whether the step up was clamped in between, so a chunk with calls
+    must not be shifted by a replica offset (found by tools/fuzz_timepar.py: seed 2, cases 36 and 161)."""
+    rng = np.random.default_rng(2)
+    T, N = 780, 96
+    for pol in (ksa.Policy(attr_mask=1, poll_period=7 * S, scale_up_cool_down=42 * S, scale_down_cool_down=11 * S, scale_up_messages=252,
+                           scale_down_messages=366, scale_up_pods=11, scale_down_pods=6, max_pods=5, min_pods=-3),
+                ksa.Policy(attr_mask=1, poll_period=7 * S, scale_up_cool_down=35 * S, scale_down_cool_down=0, scale_up_messages=10,
+                           scale_down_messages=386, scale_up_pods=3, scale_down_pods=1, max_pods=6, min_pods=-3)):
+        depth = np.ascontiguousarray(rng.integers(0, 800, size=(T, 1, N)), dtype=np.int64)
+        st = (rng.integers(-3, 12, size=N).astype(np.int32), np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+        for chunks in (2, 5, 30):
+            run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"overlapping thresholds chunks={chunks} {pol}", warm=0)
+
+
+def test_random_shapes_policies_and_depths(engine):
+    """A short run of tools/fuzz_timepar.py: random shapes, policies (adversarial and ordinary), depths
+    mixed per trace (independent, random walks, saturated / idle / quiet stretches), masks, chunk
+    counts, warm-ups and probe settings through the full and the summary entry point."""
+    from tools import fuzz_timepar
+
+    assert fuzz_timepar.run(120, 11, engine) == 0
+    assert fuzz_timepar.run(120, 12, engine) == 0
