@@ -64,8 +64,9 @@ def run(cases: int, seed: int, eng=None) -> int:
                              scale_up_cool_down=int(rng.integers(0, 9)) * 5 * S, scale_down_cool_down=int(rng.integers(0, 14)) * 5 * S,
                              max_pods=int(rng.integers(3, 12)), min_pods=int(rng.integers(0, 3)),
                              scale_up_pods=int(rng.integers(1, 4)), scale_down_pods=int(rng.integers(1, 3)))
-        T = int(rng.integers(40, 1500))
-        N = int(rng.choice([1, 8, 33, 64, 96, 130, 256, 515]))
+        auto = rng.integers(0, 8) == 0  # now and then a call long enough for the library's own choice of chunks
+        T = int(rng.integers(4096, 7000)) if auto else int(rng.integers(40, 1500))
+        N = int(rng.choice([64, 520, 2048])) if auto else int(rng.choice([1, 8, 33, 64, 96, 130, 256, 515]))
         ld = N if rng.integers(0, 2) else (N + 15) // 16 * 16
         tick0 = int(rng.choice([0, 0, 7, 10**6]))
         d = depths(rng, T, A, ld, int(pol.scale_up_messages), int(pol.scale_down_messages))
@@ -79,7 +80,13 @@ def run(cases: int, seed: int, eng=None) -> int:
         ref = oracle_lib.replay(pol.to_c(), d, T, A, N, ld, tick0, *st, want_summary=True, fail=fail)
         env = {"KSA_TIMEPAR_CHUNKS": str(int(rng.choice([2, 3, 4, 7, 12, 30]))), "KSA_TIMEPAR_WARM": str(int(rng.choice([0, 8, 24, 64, 128]))),
                "KSA_TIMEPAR_WIDE": str(int(rng.integers(0, 2))), "KSA_TIMEPAR_PROBE": str(int(rng.integers(0, 2)))}
-        os.environ.update(env)
+        if auto:
+            env["KSA_TIMEPAR_CHUNKS"] = ""
+        for k, v in env.items():
+            if v == "":
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
         dd = torch.from_numpy(d).to(eng.dev)
         ff = None if fail is None else torch.from_numpy(fail).to(eng.dev)
         s1, s2 = eng.state_from_host(*st), eng.state_from_host(*st)
