@@ -390,3 +390,38 @@ def test_random_shapes_policies_and_depths(engine):
 
     assert fuzz_timepar.run(120, 11, engine) == 0
     assert fuzz_timepar.run(120, 12, engine) == 0
+
+
+def test_two_streams_share_the_scratch_safely(engine):
+    """The chunked passes keep their records in scratch arrays inside the library: one such call per
+    GPU at a time. A call that finds the scratch in use by a call on another stream takes the plain
+    kernels instead; calls on one stream are ordered anyway. Both give the oracle's results."""
+    import torch
+
+    gen_a, gen_b = ksa.GenParams(seed=101), ksa.GenParams(seed=202)
+    N, T = 4096, 8192
+    pol = ksa.Policy(attr_mask=1)
+    cases = []
+    for gen in (gen_a, gen_b):
+        depth = oracle_lib.gen_traces(gen.to_c(), 0, T, 1, 0, N, N)
+        st = oracle_lib.fresh_state(gen.seed, 0, N, 1, 5)
+        ref = oracle_lib.replay(pol.to_c(), depth, T, 1, N, N, 0, *st, want_summary=True)
+        cases.append((torch.from_numpy(depth).to(engine.dev), st, ref))
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(device=engine.dev), torch.cuda.Stream(device=engine.dev)]
+    for order in ((0, 1), (1, 1), (0, 0)):  # two streams, then the same stream twice
+        outs = []
+        for (d, st, ref), si in zip(cases, order):
+            with torch.cuda.stream(streams[si]):
+                s1, s2 = engine.state_from_host(*st), engine.state_from_host(*st)
+                r, e = engine.replay_full(pol, d, T, 1, N, N, 0, s1)
+                summ = engine.replay_summary(pol, d, T, 1, N, N, 0, s2)
+                outs.append((r, e, summ, s1, s2, ref))
+        torch.cuda.synchronize()
+        for r, e, summ, s1, s2, ref in outs:
+            assert np.array_equal(r.cpu().numpy(), ref.replicas) and np.array_equal(e.cpu().numpy(), ref.events)
+            assert summ.cpu().numpy().view(ksa.SUMMARY_DTYPE).reshape(-1).tobytes() == ref.summary.tobytes()
+            for s in (s1, s2):
+                assert np.array_equal(s.replicas.cpu().numpy(), ref.state_replicas)
+                assert np.array_equal(s.last_up.cpu().numpy(), ref.state_last_up)
+                assert np.array_equal(s.last_down.cpu().numpy(), ref.state_last_down)
