@@ -118,6 +118,8 @@ static __device__ int g_tp_delta[kMaxChunks];
 constexpr int kLeftToShift = 100;  // TpChunk::status: pass 2a left the chunk to pass 3, which shifts it
 constexpr int kListed = 101;       // listed for pass 2b, which replaces it unless it leaves the chunk alone
 constexpr int kRerun = 102;        // replayed a second time from the entry state pass 3a put into entry1
+constexpr int kFill = 103;         // every tick met the same threshold: outputs written from the closed form (tp_fill_chunk),
+                                   // from the entry state in entry1; exit1 = the state after it, worked out by pass 3a
 
 // What pass 2b replayed a listed chunk from (the previous chunk's exit state at that time: the second
 // replay may change that one later), and what kind of chunk it is (tp_classify_kernel).
@@ -243,8 +245,36 @@ __device__ __forceinline__ void tp_store(int* rp, unsigned char* ep, const int (
   }
 }
 
+// The outputs of a chunk in which every tick met the scale-up (kind 1) or the scale-down threshold (2),
+// from its true entry state, without reading a depth: the cool-down line until the first call (the first
+// tick the gate is open) and between calls, one call every cool-down period; a call steps the count
+// towards the limit or finds it reached (scale.go:62-69, 89-97).
+__device__ void tp_fill_chunk(const TpArgs& a, const ksa_step_consts& c, long long n, int t0, int len, int kind,
+                              const TpState& entry) {
+  const bool up = kind == 1;
+  const int step = up ? c.up32 : c.down32, limit = up ? c.max32 : c.min32;
+  const int period = max(up ? c.cu : c.cd, 1);
+  const unsigned ev_cool = up ? KSA_EV_UP_COOL : KSA_EV_DOWN_COOL, ev_applied = up ? KSA_EV_UP_APPLIED : KSA_EV_DOWN_APPLIED,
+                 ev_noop = up ? KSA_EV_UP_NOOP : KSA_EV_DOWN_NOOP;
+  long long next = max(t0 + 1, up ? entry.su : entry.sd);  // local tick of the next call
+  int r = entry.r;
+  int* rp = a.replicas + (long long)t0 * a.ld + n;
+  unsigned char* ep = a.events + (long long)t0 * a.ld + n;
+  for (int t = 0; t < len; ++t) {
+    unsigned ev = ev_cool;
+    if (t0 + t + 1 == next) {
+      const bool applied = up ? r < limit : r > limit;
+      if (applied) r = up ? (int)min((long long)r + step, (long long)limit) : (int)max((long long)r - step, (long long)limit);
+      ev = applied ? ev_applied : ev_noop;
+      next += period;
+    }
+    rp[(long long)t * a.ld] = r;
+    ep[(long long)t * a.ld] = (unsigned char)ev;
+  }
+}
+
 // RERUN: the second replay. Only the chunks pass 3a marked (kRerun), from the entry state it put into
-// entry1, no warm-up; one trace per thread.
+// entry1, no warm-up; one trace per thread. Chunks marked kFill are written from the closed form instead.
 template <int A, int V, int D, int TPB, int MINB, bool FAULTS, bool RERUN = false>
 __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constant__ TpArgs a) {
   const long long n0 = ((long long)blockIdx.x * TPB + threadIdx.x) * V;
@@ -252,7 +282,18 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
   const int k = RERUN ? blockIdx.y + 1 : blockIdx.y;
   if constexpr (RERUN) {
     static_assert(V == 1, "the second replay runs one trace per thread");
-    if (record(a, k, n0)->status != kRerun) return;
+    const TpChunk* rec = record(a, k, n0);
+    const int status = rec->status;
+    // A warp whose marked chunks all have the closed form writes them; if one of them has to be replayed
+    // the others are replayed with it (from the same entry state: the same outputs) rather than making the
+    // warp do both one after the other (random-walk depths, 4096 x 10^5: 2.82 -> 3.59 ms when it did).
+    const bool replay = __any_sync(__activemask(), status == kRerun);
+    if (status != kRerun && status != kFill) return;
+    if (!replay) {
+      const ksa_step_consts cc(a.pk);
+      tp_fill_chunk(a, cc, n0, k * a.L, min(a.L, a.T - k * a.L), g_tp_kind[(long long)k * a.N + n0], rec->entry1);
+      return;
+    }
   }
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
@@ -661,6 +702,8 @@ __device__ bool tp_walk(const TpArgs& a, const ksa_step_consts& c, long long n, 
       TpState worked = cur;
       const int kind = g_tp_kind[idx];
       if (kind != 0 && pure_exit(c, kind, t0, len, worked)) {
+        rec->status = kFill;  // the outputs have a closed form too: written, not replayed
+        rec->exit1 = worked;
         cur = worked;
       } else {
         cur.r = ended.r;
@@ -821,7 +864,8 @@ struct TpSumArgs {
                        // 2 pass 1's record, entry off by a replica offset the chunk can be shifted by (pass 3 does);
                        // 3 replayed a second time from the entry state pass 3a worked out (in `en`); 4 pass 1's
                        // record of a chunk in which every tick met the same threshold, left to pass 3a; 5 pass 1's
-                       // record of a chunk listed for pass 2b (which replaces the 5 unless it gives the chunk up)
+                       // record of a chunk listed for pass 2b (which replaces the 5 unless it gives the chunk up);
+                       // 6 record and exit state worked out by pass 3a from the entry state in `en` (tp_pure_record)
   ksa_summary* part;
 };
 
@@ -954,6 +998,89 @@ __device__ __forceinline__ bool tp_pure_exit(const ksa_policy_k& pk, const ksa_s
     g.jd = B + last;
     if (g.r > c.min32) g.r = (int)max((long long)g.r - calls * step, (long long)c.min32);  // scale.go:89-97
   }
+  return true;
+}
+
+// m^n and 1 + m + ... + m^(n-1) mod 2^32 (bits of n from the top: n -> 2n: G (1 + P), P P; -> 2n + 1: G m + 1, P m)
+__device__ __forceinline__ void tp_pow_geo(unsigned m, unsigned n, unsigned& pw, unsigned& geo) {
+  pw = 1u;
+  geo = 0u;
+  for (int b = 31 - __clz((int)(n | 1u)); b >= 0; --b) {
+    geo *= 1u + pw;
+    pw *= pw;
+    if ((n >> b) & 1u) {
+      geo = geo * m + 1u;
+      pw *= m;
+    }
+  }
+}
+// ... and the whole RECORD of such a chunk has a closed form too, so that the saturated and the idle
+// queue cost no second replay: ticks before the first call and between calls log the cool-down line,
+// the first calls step the count towards the limit (at most 64 distinct counts are followed here, else
+// false: the chunk is replayed), the rest find the limit reached. Sum, min / max and the counters are
+// sums over those runs of equal counts; the fingerprint's replica lane is sum(count_t M^(len - t)), a
+// geometric sum per run, and its event lane the cool-down code's geometric sum plus corrections at the
+// call ticks, which form an arithmetic progression of exponents: a geometric sum with ratio M^period.
+// `in` = the true state before the chunk's first tick (B + 1); fills q and `out`.
+__device__ bool tp_pure_record(const ksa_policy_k& pk, const ksa_step_consts& c, int kind, long long B, int len,
+                               const TpG& in, ksa_summary& q, TpG& out) {
+  const bool up = kind == 1;
+  const int step = up ? c.up32 : c.down32;
+  if (step < 1 || step > (1 << 30)) return false;
+  const int cool = up ? c.cu : c.cd;
+  const int s = ksa_local_stamp(up ? pk.cu : pk.cd, cool, B, up ? in.ju : in.jd);  // blocked at local tick i <=> i < s
+  const long long first = max(1, s), period = max(cool, 1);
+  const long long calls = first > len ? 0 : (len - first) / period + 1;
+  const long long limit = up ? c.max32 : c.min32;
+  long long applied = 0;  // calls that still change the count
+  if (up ? in.r < limit : in.r > limit) applied = ((up ? limit - in.r : (long long)in.r - limit) + step - 1) / step;
+  applied = min(applied, calls);
+  if (applied > 64) return false;
+  const unsigned w_cool = up ? KSA_W_UP_COOL : KSA_W_DOWN_COOL, w_applied = up ? KSA_W_UP_APPLIED : KSA_W_DOWN_APPLIED,
+                 w_noop = up ? KSA_W_UP_NOOP : KSA_W_DOWN_NOOP;
+  tp_summary_clear(q);
+  unsigned lo = 0u, hi = 0u, pw, geo;
+  // a run of equal counts: local ticks [t0, t1]
+  auto run = [&](long long value, long long t0, long long t1) {
+    if (t1 < t0) return;
+    const int r = (int)value;
+    q.final_replicas = r;
+    q.min_replicas = min(q.min_replicas, r);
+    q.max_replicas = max(q.max_replicas, r);
+    q.sum_replicas = (long long)((unsigned long long)q.sum_replicas + (unsigned long long)(long long)r * (unsigned long long)(t1 - t0 + 1));
+    unsigned tail, unused;
+    tp_pow_geo(KSA_HASH_MUL_LO, (unsigned)(len - t1), tail, unused);
+    tp_pow_geo(KSA_HASH_MUL_LO, (unsigned)(t1 - t0 + 1), pw, geo);
+    lo += (unsigned)r * tail * geo;
+  };
+  long long r = in.r;
+  run(r, 1, calls == 0 ? len : first - 1);
+  for (long long j = 1; j <= applied; ++j) {
+    r = up ? min(r + step, limit) : max(r - step, limit);
+    const long long t = first + (j - 1) * period;
+    run(r, t, j == calls ? len : t + period - 1);
+    tp_pow_geo(KSA_HASH_MUL_HI, (unsigned)(len - t), pw, geo);
+    hi += (w_applied - w_cool) * pw;
+  }
+  if (applied < calls) {
+    run(r, first + applied * period, len);
+    // the calls that find the limit reached: ticks first + j period, j = applied .. calls - 1
+    const long long last = first + (calls - 1) * period;
+    unsigned ratio, tail;
+    tp_pow_geo(KSA_HASH_MUL_HI, (unsigned)period, ratio, geo);
+    tp_pow_geo(KSA_HASH_MUL_HI, (unsigned)(len - last), tail, geo);
+    tp_pow_geo(ratio, (unsigned)(calls - applied), pw, geo);
+    hi += (w_noop - w_cool) * tail * geo;
+  }
+  tp_pow_geo(KSA_HASH_MUL_HI, (unsigned)len, pw, geo);
+  hi += w_cool * geo;
+  q.hash = ((unsigned long long)hi << 32) | lo;
+  (up ? q.up_applied : q.down_applied) = (unsigned)applied;
+  (up ? q.up_noop : q.down_noop) = (unsigned)(calls - applied);
+  (up ? q.up_cool : q.down_cool) = (unsigned)(len - calls);
+  out = in;
+  out.r = (int)r;
+  if (calls > 0) (up ? out.ju : out.jd) = B + first + (calls - 1) * period;
   return true;
 }
 
@@ -1336,9 +1463,19 @@ __device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long l
       cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
       cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
     } else if (RESOLVE) {
+      const int kind = tp_pure_kind<FAULTS>(a.pk, q, len);
+      TpG after;
+      if (kind != 0 && tp_pure_record(a.pk, c, kind, B, len, cur, q, after)) {
+        // every tick met the same threshold: the chunk's record from the true state, worked out (status 6)
+        tp_put(a.en, idx, cur);
+        tp_put(a.io, idx, after);
+        a.part[idx] = q;
+        a.status[idx] = 6;
+        cur = after;
+        continue;
+      }
       tp_put(a.en, idx, cur);
       tp_put(a.io, idx, cur);
-      const int kind = tp_pure_kind<FAULTS>(a.pk, q, len);
       tp_summary_clear(q);
       a.part[idx] = q;
       a.status[idx] = 3;

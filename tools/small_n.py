@@ -31,6 +31,9 @@ def main():
     ap.add_argument("--quiet-after", type=int, default=0,
                     help="ticks after which every depth is 50 (between the thresholds: no scale event ever again, so a "
                          "chunk started from a guessed replica count never meets the true trajectory); 0 = off")
+    ap.add_argument("--steady-after", type=int, default=0,
+                    help="ticks after which odd traces stay at depth 500 (saturated: ScaleUp every cool-down period) and even "
+                         "ones at 0 (idle: ScaleDown every period); 0 = off")
     ap.add_argument("--family", default="bands", choices=["bands", "walk"],
                     help="depth generator: independent values in three bands, or a bounded random walk (step 15, wall 500: long "
                          "stretches on one side of a threshold, and between the two)")
@@ -53,6 +56,9 @@ def main():
             depth = eng.gen_traces(gen, 0, T, 1, 0, N, N)
         if args.quiet_after:
             depth[args.quiet_after:] = 50
+        if args.steady_after:
+            depth[args.steady_after:, :, 0::2] = 0
+            depth[args.steady_after:, :, 1::2] = 500
         replicas = torch.empty((T, N), dtype=torch.int32, device=eng.dev)
         events = torch.empty((T, N), dtype=torch.uint8, device=eng.dev)
         state0 = eng.new_state(N, seed=gen.seed, lo=1, hi=5)
