@@ -83,7 +83,10 @@ constexpr int BLOCK = 128;
 // the limit is where that still costs no more than the plain kernel: random-walk depths, 32768 traces:
 // 1.76 ms against 1.69; at 49152: 2.00 against 1.49, while independent depths gain 0.66 -> 0.80 there)
 constexpr long long kTpMaxSummary = 32768;
-constexpr long long kTpMaxSummaryFaults = 32768;  // independent depths 0.47 -> 0.65, random walk 1.94 -> 2.19 ms
+// With a failure mask there is no closed form for saturated / idle stretches (a failed call takes no stamp and
+// moves the phase), and runs from different phases meet only when failures happen to line them up: at 32768
+// traces of such queues the chunked passes cost 3.6 ms against 1.9 (profiles/r02_small_n_robust.txt)
+constexpr long long kTpMaxSummaryFaults = 16384;
 constexpr long long kTpMaxFullFaults = 81920;     // 0.773 / 0.750; 0.81 / 0.83 at 98304
 // ... and again where one trace per thread starts a second, nearly empty wave of 148 x 1024 threads
 // (163840 traces: 0.81 against 0.73), as long as two chunks still fit one wave of pass 1
@@ -1809,10 +1812,13 @@ int ksa_timepar_replay_full(const ksa_policy_k& pk, const int64_t* depth_dev, co
   a.warm = warm;
   a.fix_limit = (int)std::max<int64_t>(64, N * (K - 1) / 32);
   // Up to 16384 traces even two chunked replays beat the plain kernel; beyond, a probe decides first
-  // (KSA_TIMEPAR_PROBE=0 / 1 forces it off / on).
-  bool probe = N > 16384;
+  // (KSA_TIMEPAR_PROBE=0 / 1 forces it off / on). With a failure mask it always does: saturated / idle
+  // stretches have no closed form there, and a trace that stays unresolved costs the plain kernel's whole
+  // latency on top (4096 x 10^5 such queues: 18.1 ms against 10.3).
+  bool probe = N > 16384 || fail_dev != nullptr;
   if (const char* e = std::getenv("KSA_TIMEPAR_PROBE")) probe = std::atoi(e) != 0;
-  a.probe_traces = (int)std::min<int64_t>(N / 32 * 32, 512);
+  // about 8192 (trace, chunk start) pairs: the probe's time is its longest warm-up, not its size, as long as it is small
+  a.probe_traces = (int)std::min<int64_t>(N / 32 * 32, std::min<int64_t>(512, std::max<int64_t>(32, 8192 / (K - 1) / 32 * 32)));
   a.probe_stride = a.probe_traces >= 32 ? (int)(N / (a.probe_traces / 32)) : 0;
   if (a.probe_traces < 32) probe = false;
   a.probe_limit = probe ? (int)((int64_t)a.probe_traces * (K - 1) / 8) : INT_MAX;
