@@ -1,7 +1,10 @@
 """Multi-GPU layout: traces are independent (the only state is per trace: Spec.Replicas and the two
 stamps, main.go:37-38 + scale/scale.go:60), so the trace axis is cut into contiguous shards, one
 per rank / GPU, with no data-path collective. The only cross-rank step is a gather of the 64-byte
-per-trace summaries to rank 0 (torch.distributed over NCCL or gloo; plumbing, not the product).
+per-trace summaries to rank 0: through a host segment that every rank of the box maps and writes its
+own slice of (SharedHostSegment: every GPU's own host link carries its shard, and the copies can run
+while the next chunk is replayed), or with torch.distributed (gather_summaries; plumbing, not the
+product).
 """
 from __future__ import annotations
 
@@ -16,6 +19,82 @@ def shard_range(n_total: int, world: int, rank: int) -> tuple[int, int]:
     base, extra = divmod(n_total, world)
     begin = rank * base + min(rank, extra)
     return begin, begin + base + (1 if rank < extra else 0)
+
+
+class SharedHostSegment:
+    """`nbytes` of host memory that every rank of the box maps: a tmpfs file under /dev/shm created by
+    rank 0 (torch.distributed, any backend, carries its name). This rank owns bytes [lo, hi) of it and,
+    given the loaded library (`lib`: libksareplay through ctypes), page-locks them with
+    ksa_host_register so that device-to-host copies into them run at the link's rate and
+    asynchronously; `address(offset)` is where to copy to. After `barrier()` rank 0 reads the whole
+    segment through `array` (uint8). `ok` is False, on every rank, when /dev/shm cannot hold the
+    segment or the slice is not page-aligned: the caller then gathers another way."""
+
+    def __init__(self, nbytes: int, lo: int, hi: int, lib=None, group=None):
+        import mmap
+        import os
+
+        import torch.distributed as dist
+
+        self._dist, self._group, self._lib = dist, group, lib
+        self.rank = dist.get_rank(group)
+        self.path = self._map = self._registered = self.array = None
+        aligned = lo % mmap.PAGESIZE == 0 and hi % mmap.PAGESIZE == 0
+        flags = [None] * dist.get_world_size(group)
+        dist.all_gather_object(flags, bool(aligned), group=group)
+        box = [None]
+        if self.rank == 0 and all(flags):
+            try:
+                vfs = os.statvfs("/dev/shm")
+                if vfs.f_bavail * vfs.f_frsize > nbytes + (256 << 20):
+                    box[0] = f"/dev/shm/ksa_segment_{os.getpid()}_{os.environ.get('MASTER_PORT', '0')}"
+                    with open(box[0], "wb") as f:
+                        f.truncate(nbytes)
+            except OSError:
+                box[0] = None
+        dist.broadcast_object_list(box, src=0, group=group)
+        self.ok = box[0] is not None
+        if not self.ok:
+            return
+        self.path = box[0]
+        with open(self.path, "r+b") as f:
+            self._map = mmap.mmap(f.fileno(), nbytes)
+        self.array = np.frombuffer(self._map, dtype=np.uint8)
+        self.base = self.array.ctypes.data
+        self.lo, self.hi = lo, hi
+        self.array[lo:hi] = 0  # touch this rank's pages before they are locked
+        if lib is not None and hi > lo:
+            from . import _abi
+
+            _abi.check(lib.ksa_host_register(self.base + lo, hi - lo))
+            self._registered = self.base + lo
+        dist.barrier(group=group)
+
+    def address(self, offset: int = 0) -> int:
+        """Host address of byte `offset` of this rank's slice."""
+        return self.base + self.lo + offset
+
+    def barrier(self) -> None:
+        """Every rank's copies have been waited for by their owners: rank 0 may read `array`."""
+        self._dist.barrier(group=self._group)
+
+    def close(self) -> None:
+        if not self.ok:
+            return
+        if self._registered:
+            self._lib.ksa_host_unregister(self._registered)
+            self._registered = None
+        self.array = None
+        self._dist.barrier(group=self._group)
+        try:
+            self._map.close()
+        except BufferError:  # (a view of the mapping is still alive somewhere: the file goes anyway)
+            pass
+        if self.rank == 0:
+            import os
+
+            os.unlink(self.path)
+        self.ok = False
 
 
 def gather_summaries(local: np.ndarray, n_total: int, group=None):

@@ -15,7 +15,7 @@ if ROOT not in sys.path:
 
 from kube_sqs_autoscaler_b200 import Policy  # noqa: E402
 from kube_sqs_autoscaler_b200.engine import GenParams  # noqa: E402
-from kube_sqs_autoscaler_b200.shard import gather_summaries, shard_range  # noqa: E402
+from kube_sqs_autoscaler_b200.shard import SharedHostSegment, gather_summaries, shard_range  # noqa: E402
 
 N_TOTAL, T = 1001, 96
 POLICY = Policy(attr_mask=1)
@@ -38,6 +38,24 @@ def main() -> None:
     full = gather_summaries(res.summary, N_TOTAL)
     if rank == 0:
         np.save(sys.argv[1], full)
+    # the same gather through a host segment every rank maps (what bench.py's config5 does with page-locked
+    # slices and device-to-host copies; here plain host copies, and slices padded to whole pages)
+    import mmap
+
+    per = ((N_TOTAL + world - 1) // world * 64 + mmap.PAGESIZE - 1) // mmap.PAGESIZE * mmap.PAGESIZE
+    seg = SharedHostSegment(per * world, rank * per, (rank + 1) * per)
+    if seg.ok:
+        mine = np.ascontiguousarray(res.summary).view(np.uint8).reshape(-1)
+        seg.array[rank * per:rank * per + mine.size] = mine
+        seg.barrier()
+        if rank == 0:
+            for r in range(world):
+                rb, re_ = shard_range(N_TOTAL, world, r)
+                got = bytes(seg.array[r * per:r * per + (re_ - rb) * 64])
+                assert got == full[rb:re_].tobytes(), f"shared segment: slice of rank {r} differs"
+        seg.close()
+    unaligned = SharedHostSegment(per * world, rank * per + 8, (rank + 1) * per)  # not page-aligned: refused on every rank
+    assert not unaligned.ok
     dist.barrier()
     dist.destroy_process_group()
 
