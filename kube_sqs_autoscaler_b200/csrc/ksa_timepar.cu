@@ -617,13 +617,21 @@ __global__ void __launch_bounds__(BLOCK) tp_classify_kernel(const __grid_constan
   g_tp_kind[(long long)k * a.N + n] = kind;
 }
 
+// The closed forms below add steps in 64 bits; the reference adds in int32 and wraps (scale.go:66, 94) before it
+// clamps. They agree as long as a step from below the limit cannot pass INT_MAX (from above it: INT_MIN),
+// which only limits next to the ends of int32 can make happen (found by tools/fuzz_timepar.py: max_pods
+// = 2^31 - 1). Otherwise the chunk is replayed.
+__device__ __forceinline__ bool step_cannot_wrap(const ksa_step_consts& c, bool up) {
+  return up ? (long long)c.max32 + c.up32 <= INT_MAX : (long long)c.min32 - c.down32 >= INT_MIN;
+}
+
 // The state after a chunk of that kind: the first call at the first tick the gate is open, then one
 // every cool-down period, each a full step towards the limit (scale.go:62-69, 89-97). Chunk = local
 // ticks t0 + 1 .. t0 + len. False: not worked out (steps that are negative or could wrap).
 __device__ __forceinline__ bool pure_exit(const ksa_step_consts& c, int kind, int t0, int len, TpState& g) {
   const bool up = kind == 1;
   const int step = up ? c.up32 : c.down32;
-  if (step < 0 || step > (1 << 30)) return false;
+  if (step < 0 || step > (1 << 30) || !step_cannot_wrap(c, up)) return false;
   const int cool = up ? c.cu : c.cd;
   const long long first = max(t0 + 1, up ? g.su : g.sd);  // blocked at local tick i <=> i < s
   if (first > t0 + len) return true;                      // the gate stays shut for the whole chunk
@@ -868,7 +876,8 @@ struct TpSumArgs {
                        // 3 replayed a second time from the entry state pass 3a worked out (in `en`); 4 pass 1's
                        // record of a chunk in which every tick met the same threshold, left to pass 3a; 5 pass 1's
                        // record of a chunk listed for pass 2b (which replaces the 5 unless it gives the chunk up);
-                       // 6 record and exit state worked out by pass 3a from the entry state in `en` (tp_pure_record)
+                       // 6 record and exit state worked out by pass 3a from the entry state in `en` (tp_pure_record;
+                       // 7 / 8 on the way there)
   ksa_summary* part;
 };
 
@@ -916,10 +925,10 @@ __device__ __forceinline__ bool tp_shift_safe(const ksa_step_consts& c, const ks
   // call are shifted then.
   if (!(c.up_msgs > c.down_msgs) && (q.up_applied | q.up_noop | q.down_applied | q.down_noop) != 0u) return false;
   if ((q.up_applied | q.up_noop) != 0u &&
-      !(c.up32 >= 0 && c.up32 <= (1 << 30) && hi < c.max32 && hi + delta < c.max32))
+      !(c.up32 >= 0 && c.up32 <= (1 << 30) && hi < c.max32 && hi + delta < c.max32 && step_cannot_wrap(c, true)))
     return false;
   if ((q.down_applied | q.down_noop) != 0u &&
-      !(c.down32 >= 0 && c.down32 <= (1 << 30) && lo > c.min32 && lo + delta > c.min32))
+      !(c.down32 >= 0 && c.down32 <= (1 << 30) && lo > c.min32 && lo + delta > c.min32 && step_cannot_wrap(c, false)))
     return false;
   return true;
 }
@@ -986,7 +995,7 @@ __device__ __forceinline__ bool tp_pure_exit(const ksa_policy_k& pk, const ksa_s
                                              int len, TpG& g) {
   const bool up = kind == 1;
   const int step = up ? c.up32 : c.down32;
-  if (step < 0 || step > (1 << 30)) return false;
+  if (step < 0 || step > (1 << 30) || !step_cannot_wrap(c, up)) return false;
   const int cool = up ? c.cu : c.cd;
   const int s = ksa_local_stamp(up ? pk.cu : pk.cd, cool, B, up ? g.ju : g.jd);  // blocked at local tick i <=> i < s
   const long long first = max(1, s);
@@ -1029,7 +1038,7 @@ __device__ bool tp_pure_record(const ksa_policy_k& pk, const ksa_step_consts& c,
                                const TpG& in, ksa_summary& q, TpG& out) {
   const bool up = kind == 1;
   const int step = up ? c.up32 : c.down32;
-  if (step < 1 || step > (1 << 30)) return false;
+  if (step < 1 || step > (1 << 30) || !step_cannot_wrap(c, up)) return false;
   const int cool = up ? c.cu : c.cd;
   const int s = ksa_local_stamp(up ? pk.cu : pk.cd, cool, B, up ? in.ju : in.jd);  // blocked at local tick i <=> i < s
   const long long first = max(1, s), period = max(cool, 1);
@@ -1467,13 +1476,13 @@ __device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long l
       cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
     } else if (RESOLVE) {
       const int kind = tp_pure_kind<FAULTS>(a.pk, q, len);
-      TpG after;
-      if (kind != 0 && tp_pure_record(a.pk, c, kind, B, len, cur, q, after)) {
-        // every tick met the same threshold: the chunk's record from the true state, worked out (status 6)
+      TpG after = cur;
+      if (kind != 0 && tp_pure_exit(a.pk, c, kind, B, len, after)) {
+        // every tick met the same threshold: the state after the chunk is worked out here, its record from the
+        // true entry state by the warp's lanes after the walk (status 7 / 8 = kind, then 6: tp_sum_resolve_kernel)
         tp_put(a.en, idx, cur);
         tp_put(a.io, idx, after);
-        a.part[idx] = q;
-        a.status[idx] = 6;
+        a.status[idx] = 6 + kind;
         cur = after;
         continue;
       }
@@ -1482,14 +1491,9 @@ __device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long l
       tp_summary_clear(q);
       a.part[idx] = q;
       a.status[idx] = 3;
-      TpG worked = cur;
-      if (kind != 0 && tp_pure_exit(a.pk, c, kind, B, len, worked)) {
-        cur = worked;
-      } else {
-        cur.r = exit.r;
-        cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
-        cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
-      }
+      cur.r = exit.r;
+      cur.ju = tp_taken(exit.ju, B, len) ? exit.ju : cur.ju;
+      cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
       continue;  // (pass 3a builds no result)
     } else {
       if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
@@ -1515,11 +1519,34 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_cons
     const int status = a.status[(long long)k * a.N + n];
     fine = fine && (status == 0 || status == 1);
   }
-  if (__all_sync(0xffffffffu, fine) || lane != 0) return;
+  if (__all_sync(0xffffffffu, fine)) return;
   const ksa_step_consts c(a.pk);
-  TpRun run;
-  bool unresolved = false;
-  tp_sum_walk<A, FAULTS, true>(a, c, n, run, unresolved);
+  if (lane == 0) {
+    TpRun run;
+    bool unresolved = false;
+    tp_sum_walk<A, FAULTS, true>(a, c, n, run, unresolved);
+  }
+  __syncwarp();
+  // the records of the chunks the walk worked its way through in closed form: a few hundred instructions
+  // each (powers and geometric sums), shared out over the lanes
+  for (int k = 1 + lane; k < a.K; k += 32) {
+    const long long idx = (long long)k * a.N + n;
+    const int status = a.status[idx];
+    if (status != 7 && status != 8) continue;
+    const int len = min(a.L, a.T - k * a.L);
+    const TpG entry = tp_get(a.en, idx);
+    ksa_summary q;
+    TpG after;
+    if (tp_pure_record(a.pk, c, status - 6, a.tick0 + (long long)k * a.L, len, entry, q, after)) {
+      a.part[idx] = q;
+      a.status[idx] = 6;
+    } else {  // (too many distinct counts to follow: replayed a second time after all, from the same entry state)
+      tp_put(a.io, idx, entry);
+      tp_summary_clear(q);
+      a.part[idx] = q;
+      a.status[idx] = 3;
+    }
+  }
 }
 
 // ---- pass 3b: warp (trace) ----------------------------------------------------------------------

@@ -425,3 +425,24 @@ def test_two_streams_share_the_scratch_safely(engine):
                 assert np.array_equal(s.replicas.cpu().numpy(), ref.state_replicas)
                 assert np.array_equal(s.last_up.cpu().numpy(), ref.state_last_up)
                 assert np.array_equal(s.last_down.cpu().numpy(), ref.state_last_down)
+
+
+def test_limits_at_the_ends_of_int32(engine):
+    """The reference adds a step in int32 and wraps before it clamps (scale/scale.go:66, 94). With
+    max_pods = 2^31 - 1 a step from just below the limit passes INT_MAX and comes out negative; the
+    closed forms for saturated / idle stretches and the shift of a chunk add in 64 bits and must stay
+    away from such policies (found by tools/fuzz_timepar.py: seed 82, case 76)."""
+    rng = np.random.default_rng(82)
+    T, N = 975, 96
+    pol = ksa.Policy(attr_mask=1, scale_up_cool_down=20 * S, scale_down_cool_down=15 * S, scale_up_messages=183,
+                     scale_down_messages=20, scale_up_pods=8, scale_down_pods=5, max_pods=2**31 - 1, min_pods=-(2**31))
+    r0 = np.where(rng.integers(0, 2, size=N) == 0, 2**31 - 1 - rng.integers(0, 40, size=N),
+                  -(2**31) + rng.integers(0, 40, size=N)).astype(np.int32)
+    st = (r0, np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+    sat = np.full((T, 1, N), 500, dtype=np.int64)
+    idle = np.zeros((T, 1, N), dtype=np.int64)
+    mixed = np.ascontiguousarray(rng.integers(0, 400, size=(T, 1, N)), dtype=np.int64)
+    mixed[200:700] = 500
+    for name, depth in (("saturated", sat), ("idle", idle), ("mixed", mixed)):
+        for chunks in (3, 12):
+            run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"limits at the ends of int32, {name}, chunks={chunks}", warm=64)
