@@ -1549,6 +1549,40 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_cons
   }
 }
 
+// Does every chunk of the trace fit the true state now, as it stands or shifted by a replica offset? The walk
+// of tp_sum_walk without building the result: only the states are read (a record only where an offset has
+// to be judged), the next chunk's while this one is looked at. Leaves each chunk's offset in g_tp_delta
+// (summary mode has no other use for it). False: some chunk does not fit (the full walk decides what then).
+__device__ bool tp_sum_verify(const TpSumArgs& a, const ksa_step_consts& c, long long n) {
+  TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+  long long idx = a.N + n;
+  int status = a.status[idx];
+  TpG used = tp_get(a.en, idx);
+  TpG exit = (status == 1 || status < 0) ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+  for (int k = 1; k < a.K; ++k) {
+    const TpG used_k = used, exit_k = exit;
+    const long long idx_k = idx;
+    if (k + 1 < a.K) {  // the next chunk's states are on their way while this one is judged
+      idx += a.N;
+      status = a.status[idx];
+      used = tp_get(a.en, idx);
+      exit = (status == 1 || status < 0) ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+    }
+    const int t0 = k * a.L;
+    const int len = min(a.L, a.T - t0);
+    const long long B = a.tick0 + t0;
+    const long long delta = (long long)cur.r - used_k.r;
+    if (!tp_same_gates(a.pk, c, used_k, cur, B, a.T - t0)) return false;
+    if (delta != 0 && !tp_shift_safe(c, a.part[idx_k], used_k.r, delta)) return false;
+    if (delta != (long long)(int)delta) return false;  // (an offset of 2^31 or more: not one g_tp_delta holds)
+    g_tp_delta[idx_k] = (int)delta;
+    cur.r = (int)(exit_k.r + delta);
+    cur.ju = tp_taken(exit_k.ju, B, len) ? exit_k.ju : cur.ju;
+    cur.jd = tp_taken(exit_k.jd, B, len) ? exit_k.jd : cur.jd;
+  }
+  return true;
+}
+
 // ---- pass 3b: warp (trace) ----------------------------------------------------------------------
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_constant__ TpSumArgs a) {
@@ -1559,21 +1593,41 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
   const int per = (a.K + 31) / 32;
   const int k0 = lane * per, k1 = min(a.K, k0 + per);
   TpRun run;
-  tp_run_init(run);
   bool fine = true, unresolved = false;
-  for (int k = k0; k < k1; ++k) {
-    const long long idx = (long long)k * a.N + n;
-    const int status = a.status[idx];
-    fine = fine && (status == 0 || status == 1);
-    const bool last = k == a.K - 1;
-    TpRun one;
-    tp_run_of_chunk(one, a.part[idx], status == 1 ? tp_get(a.fx, idx) : tp_get(a.io, idx),
-                    a.tick0 + (long long)k * a.L, min(a.L, a.T - k * a.L), k == 0, last ? a.mE_lo : a.mL_lo,
-                    last ? a.mE_hi : a.mL_hi);
-    tp_run_append(run, one);
-  }
+  // this lane's run of chunks, in order; `shifted`: each chunk by the offset tp_sum_verify left for it
+  auto my_chunks = [&](const bool shifted) {
+    tp_run_init(run);
+    for (int k = k0; k < k1; ++k) {
+      const long long idx = (long long)k * a.N + n;
+      const int status = a.status[idx];
+      fine = fine && (status == 0 || status == 1);
+      const bool last = k == a.K - 1;
+      const int len = min(a.L, a.T - k * a.L);
+      ksa_summary q = a.part[idx];
+      TpG exit = (status == 1 || status < 0) ? tp_get(a.fx, idx) : tp_get(a.io, idx);
+      if (shifted && k > 0) {
+        const int delta = g_tp_delta[idx];
+        if (delta != 0) tp_shift(q, exit, delta, len, last ? a.gE_lo : a.gL_lo);
+      }
+      TpRun one;
+      tp_run_of_chunk(one, q, exit, a.tick0 + (long long)k * a.L, len, k == 0, last ? a.mE_lo : a.mL_lo,
+                      last ? a.mE_hi : a.mL_hi);
+      tp_run_append(run, one);
+    }
+  };
+  my_chunks(false);
   fine = __all_sync(0xffffffffu, fine);
-  if (fine) {
+  bool parallel = fine;
+  if (!fine) {
+    // not every chunk simply stands. If each fits the true state as it is or shifted (lane 0 looks: states
+    // only), the lanes combine them as above, with the offsets; else lane 0 walks and replays.
+    bool fits = false;
+    if (lane == 0) fits = tp_sum_verify(a, c, n);
+    parallel = __shfl_sync(0xffffffffu, (int)fits, 0) != 0;
+    __syncwarp();  // (lane 0's offsets are the other lanes' to read)
+    if (parallel) my_chunks(true);
+  }
+  if (parallel) {
     // every chunk was replayed from (the equivalent of) the true state: combine the lanes' runs in order
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {

@@ -446,3 +446,22 @@ def test_limits_at_the_ends_of_int32(engine):
     for name, depth in (("saturated", sat), ("idle", idle), ("mixed", mixed)):
         for chunks in (3, 12):
             run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"limits at the ends of int32, {name}, chunks={chunks}", warm=64)
+
+
+def test_replica_offsets_wider_than_int32(engine):
+    """A chunk replayed from a guess whose replica count is off by 2^31 or more (the trace starts near
+    INT_MIN, a negative scale_up_pods wraps it past the limit in the first ticks and the clamp brings it
+    to max_pods; the chunks after that see no call and were guessed from the caller's count). Such a
+    chunk is still right after a shift, and the shift has to be made in 64 bits all the way: the sum of
+    replicas is the one field that is not taken mod 2^32 (found by tools/fuzz_timepar.py: seed 92)."""
+    rng = np.random.default_rng(92)
+    T, N = 1282, 96
+    pol = ksa.Policy(attr_mask=1, scale_up_cool_down=0, scale_down_cool_down=13 * S, scale_up_messages=109,
+                     scale_down_messages=43, scale_up_pods=-3, scale_down_pods=11, max_pods=6, min_pods=0)
+    r0 = np.where(rng.integers(0, 2, size=N) == 0, -(2**31) + rng.integers(0, 3, size=N), rng.integers(0, 7, size=N)).astype(np.int32)
+    st = (r0, np.zeros(N, dtype=np.int64), np.zeros(N, dtype=np.int64))
+    depth = np.ascontiguousarray(rng.integers(44, 109, size=(T, 1, N)), dtype=np.int64)  # between the thresholds: no call
+    depth[:5] = 200
+    for chunks in (4, 30):
+        for warm in (0, 24):
+            run_and_check(engine, pol, depth, T, 1, N, N, 0, st, chunks, f"offsets wider than int32, chunks={chunks}, warm={warm}", warm=warm)
