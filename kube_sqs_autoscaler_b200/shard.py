@@ -21,6 +21,72 @@ def shard_range(n_total: int, world: int, rank: int) -> tuple[int, int]:
     return begin, begin + base + (1 if rank < extra else 0)
 
 
+def _cpu_list(text: str) -> set[int]:
+    """'0-3,8,10-11' (sysfs cpulist) -> {0, 1, 2, 3, 8, 10, 11}."""
+    cpus: set[int] = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def host_node_of_gpu(pci_bus_id: str, sysfs: str = "/sys") -> tuple[int, set[int]]:
+    """(NUMA node, its CPUs) of the PCI device `pci_bus_id` ('0000:1b:00.0'; any case), read from sysfs;
+    (-1, set()) when the platform does not say (one node, a VM without topology, no such device)."""
+    import os
+
+    try:
+        with open(os.path.join(sysfs, "bus/pci/devices", pci_bus_id.lower(), "numa_node")) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return -1, set()
+        with open(os.path.join(sysfs, "devices/system/node", f"node{node}", "cpulist")) as f:
+            return node, _cpu_list(f.read())
+    except (OSError, ValueError):
+        return -1, set()
+
+
+def bind_to_gpu_node(device: int, sysfs: str = "/sys") -> dict:
+    """One process per GPU: run this rank's host threads on the CPUs of the NUMA node the GPU hangs off,
+    so that the page-locked buffers it allocates afterwards (first touch: ksa_host_alloc, SharedHostSegment)
+    and the copies between them and the GPU stay on that node's memory and PCIe root. Call before
+    allocating host buffers. Never fails: returns what it found and did
+    ({"node": n, "cpus": k, "bound": bool, "why": ...}); a box that does not expose the topology, or a
+    CPU set (cgroup / taskset) that shares nothing with the node, is left as it is."""
+    import os
+
+    import torch
+
+    info = {"node": -1, "cpus": 0, "bound": False}
+    try:
+        prop = torch.cuda.get_device_properties(device)
+        bus = f"{getattr(prop, 'pci_domain_id', 0):04x}:{prop.pci_bus_id:02x}:{prop.pci_device_id:02x}.0"
+    except Exception as exc:  # (no CUDA, or a torch without the PCI fields)
+        info["why"] = f"no PCI address for device {device}: {exc}"
+        return info
+    node, cpus = host_node_of_gpu(bus, sysfs)
+    info["pci"] = bus
+    info["node"] = node
+    if node < 0:
+        info["why"] = "the platform reports no NUMA node for the GPU"
+        return info
+    try:
+        allowed = os.sched_getaffinity(0)
+        mine = cpus & allowed
+        info["cpus"] = len(mine)
+        if not mine:
+            info["why"] = "none of the node's CPUs is in this process's CPU set"
+            return info
+        if mine != allowed:
+            os.sched_setaffinity(0, mine)
+        info["bound"] = True
+    except OSError as exc:
+        info["why"] = f"sched_setaffinity: {exc}"
+    return info
+
+
 class SharedHostSegment:
     """`nbytes` of host memory that every rank of the box maps: a tmpfs file under /dev/shm created by
     rank 0 (torch.distributed, any backend, carries its name). This rank owns bytes [lo, hi) of it and,

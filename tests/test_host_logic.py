@@ -248,3 +248,28 @@ def test_chunk_limits_keep_stamps_inside_int32():
     assert c > T                       # a capped cool-down stays shut for the whole call
     assert -(T + 32) > -(2**31)        # group-relative stamps of the summary kernels (ring <= 16)
     assert 32 + c <= 2**31 - 1
+
+
+def test_gpu_numa_node_lookup_reads_sysfs_and_tolerates_its_absence(tmp_path):
+    """shard.host_node_of_gpu / bind_to_gpu_node: the node and CPU list come from sysfs; a platform that
+    reports -1, an unknown device or a missing tree leaves the process as it is (never an error)."""
+    import os
+
+    from kube_sqs_autoscaler_b200 import shard
+
+    assert shard._cpu_list("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert shard._cpu_list("\n") == set()
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("16-31,48-63\n")
+    assert shard.host_node_of_gpu("0000:1B:00.0", str(tmp_path)) == (1, set(range(16, 32)) | set(range(48, 64)))
+    (dev / "numa_node").write_text("-1\n")
+    assert shard.host_node_of_gpu("0000:1b:00.0", str(tmp_path)) == (-1, set())
+    assert shard.host_node_of_gpu("0000:ff:00.0", str(tmp_path)) == (-1, set())
+    before = os.sched_getaffinity(0)
+    info = shard.bind_to_gpu_node(0, str(tmp_path))  # no CUDA here (or no such device in the fake tree)
+    assert info["bound"] is False and "why" in info
+    assert os.sched_getaffinity(0) == before
