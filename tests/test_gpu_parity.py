@@ -986,3 +986,12 @@ def test_registered_host_memory_takes_the_summaries(engine):
     assert engine.lib.ksa_host_register(None, 0) == _abi.KSA_EINVAL
     del buf
     m.close()
+
+
+def test_random_cases_over_every_other_path(engine):
+    """A short run of tools/fuzz_paths.py: the plain kernels in every compiled variant (masks, T-chunks
+    handing the carry state on), policy grids through both sweep entry points in every tile mode and on
+    into the reduction, and the host pipeline with random stage lengths; start counts anywhere in int32."""
+    from tools import fuzz_paths
+
+    assert fuzz_paths.run(200, 21, engine) == 0

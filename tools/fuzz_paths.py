@@ -111,11 +111,13 @@ def case_sweep(rng, eng):
     N = int(rng.choice([1, 33, 130, 257, 600]))
     ld = N if rng.integers(0, 2) else (N + 15) // 16 * 16
     pols = []
-    while len(pols) < int(rng.integers(1, 40)):
+    mask = some_policy(rng, A).attr_mask  # one grid, one set of attributes (ksa_replay_sweep's contract)
+    want_p = int(rng.integers(1, 40))
+    while len(pols) < want_p:
         base = some_policy(rng, A)
         for _ in range(int(rng.choice([1, 1, 3, 4, 8, 9]))):  # a run with the same thresholds and attributes
             q = some_policy(rng, A)
-            pols.append(ksa.Policy(attr_mask=base.attr_mask, scale_up_messages=base.scale_up_messages,
+            pols.append(ksa.Policy(attr_mask=mask, scale_up_messages=base.scale_up_messages,
                                    scale_down_messages=base.scale_down_messages, poll_period=base.poll_period,
                                    scale_up_cool_down=q.scale_up_cool_down, scale_down_cool_down=q.scale_down_cool_down,
                                    scale_up_pods=q.scale_up_pods, scale_down_pods=q.scale_down_pods, max_pods=q.max_pods,
