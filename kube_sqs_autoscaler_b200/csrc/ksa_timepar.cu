@@ -28,7 +28,7 @@
 //          that goes quiet: its state never forgets). Any other chunk that does not fit is marked to
 //          be replayed a second time from the true state; the state after it is worked out for a chunk
 //          in which every tick met the same threshold (the saturated and the idle queue: calls exactly
-//          one cool-down apart, a guess keeps a wrong phase for ever; tp_classify_kernel, pure_exit),
+//          one cool-down apart, a guess keeps a wrong phase for ever; pass 1 notes such chunks, pure_exit),
 //          assumed to be what the chunk ended with the first time otherwise.
 //  then    the second replay: pass 1's kernel, one trace per thread, over the marked chunks.
 //  pass 3b thread (trace): if every chunk stands or was patched, all entry states were the true ones by
@@ -125,7 +125,7 @@ constexpr int kFill = 103;         // every tick met the same threshold: outputs
                                    // from the entry state in entry1; exit1 = the state after it, worked out by pass 3a
 
 // What pass 2b replayed a listed chunk from (the previous chunk's exit state at that time: the second
-// replay may change that one later), and what kind of chunk it is (tp_classify_kernel).
+// replay may change that one later), and what kind of chunk it is (noted by pass 1).
 static __device__ TpState g_tp_used[kMaxChunks];
 static __device__ unsigned char g_tp_kind[kMaxChunks];
 // The probe's verdict (tp_probe_kernel): pairs (sampled trace, chunk start) at which warm-ups of three
@@ -340,6 +340,9 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
     for (int j = 0; j < D; ++j)
       if (tb + j < te) tp_load_fail<V>(fp + (long long)(tb + j) * a.ld, fbuf[j]);
   }
+  unsigned kacc[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) kacc[v] = 0xffffffffu;
   auto tick = [&](const int tt, const int j, const bool prefetch, const bool store) {
     long long msgs[V];
     unsigned fw[V == 8 ? 2 : 1];
@@ -370,6 +373,10 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
         ev[v] = ksa_step_fma_byte(c, msgs[v], tt + 1, one, s[v]);
       }
       rr[v] = s[v].r;
+      // the chunk's kind, gathered on the way (see below): x 21 brings the three lines of a direction (bits 0 / 2 /
+      // 4 up, 1 / 3 / 5 down; at most one of each per tick, so nothing carries) onto bits 4 and 5
+      if constexpr (!FAULTS && !RERUN)
+        if (store) kacc[v] &= ev[v] * 21u;
     }
     if (store) tp_store<V>(rp + (long long)tt * a.ld, ep + (long long)tt * a.ld, rr, ev);
   };
@@ -410,6 +417,24 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
   for (int v = 0; v < V; ++v) {
     record(a, k, n0 + v)->exit1 = TpState{s[v].r, s[v].su, s[v].sd};
     if constexpr (!RERUN) record(a, k, n0 + v)->status = 0;
+  }
+  // Did EVERY tick of the chunk meet the scale-up threshold (kind 1), or the scale-down threshold (2)? A tick
+  // that meets a threshold logs exactly one of that direction's three lines, whatever the state, so the
+  // event bytes of this replay from a guess say it; 0 otherwise, and for policies whose thresholds overlap
+  // or with a failure mask (a failed call takes no stamp). Such a chunk is the saturated queue (replicas at
+  // max, ScaleUp called every cool-down period) or the idle one (at min, ScaleDown every period): the steady
+  // states of a real fleet. Its calls are exactly one cool-down apart, their phase set by the first one, so
+  // a chunk started from a guess deep inside such a stretch keeps the wrong phase for ever and no warm-up
+  // helps; but what the chunk does to a state has a closed form (pure_exit), which is how pass 3a gets
+  // through it. (A pass of its own over the event bytes took 0.29 ms at 4096 x 10^5.)
+  if constexpr (!RERUN) {
+    const bool ordered = a.pk.up_msgs > a.pk.down_msgs;
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      unsigned char kind = 0;
+      if (!FAULTS && ordered) kind = (kacc[v] & 16u) ? 1 : ((kacc[v] & 32u) ? 2 : 0);
+      g_tp_kind[(long long)k * a.N + n0 + v] = kind;
+    }
   }
 }
 
@@ -576,45 +601,6 @@ __global__ void __launch_bounds__(BLOCK) tp_fix_kernel(const __grid_constant__ T
   rec->entry1 = TpState{s.r, s.su, s.sd};  // (the slot is free: pass 2a has read it)
   rec->status = j >= 0 ? j + 1 : -1;
   if (j < 0) g_tp_walk[n] = 1;  // the chunk after it was judged by an exit state that is not the true one
-}
-
-// ---- between pass 2b and pass 3a ---------------------------------------------------------------------
-// Thread (trace, chunk >= 1) of a trace that will be walked: does EVERY tick of the chunk meet the scale-up
-// threshold (1), or the scale-down threshold (2)? From the event bytes pass 1 wrote (a tick that meets a
-// threshold logs exactly one of that direction's three lines, whatever the state); 0 otherwise, and
-// for policies whose thresholds overlap or with a failure mask (a failed call takes no stamp). Such a
-// chunk is the saturated queue (replicas at max, ScaleUp called every cool-down period) or the idle one
-// (at min, ScaleDown every period): the steady states of a real fleet. Its calls are exactly one
-// cool-down apart, their phase set by the first one, so a chunk started from a guess deep inside such a
-// stretch keeps the wrong phase for ever and no warm-up helps; but what the chunk does to a state has
-// a closed form (pure_exit), which is how pass 3a gets through it.
-template <bool FAULTS>
-__global__ void __launch_bounds__(BLOCK) tp_classify_kernel(const __grid_constant__ TpArgs a) {
-  const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
-  if (n >= a.N || g_tp_probe_bad > a.probe_limit || g_tp_walk[n] == 0) return;
-  const int k = blockIdx.y + 1;
-  unsigned char kind = 0;
-  if (!FAULTS && a.pk.up_msgs > a.pk.down_msgs) {
-    const int t0 = k * a.L;
-    const int len = min(a.L, a.T - t0);
-    const unsigned char* ep = a.events + (long long)t0 * a.ld + n;
-    constexpr unsigned kUp = KSA_EV_UP_APPLIED | KSA_EV_UP_NOOP | KSA_EV_UP_COOL;
-    constexpr unsigned kDown = KSA_EV_DOWN_APPLIED | KSA_EV_DOWN_NOOP | KSA_EV_DOWN_COOL;
-    bool all_up = true, all_down = true;
-    constexpr int G = 8;
-    for (int t = 0; t < len && (all_up || all_down); t += G) {
-      unsigned e[G];
-#pragma unroll
-      for (int j = 0; j < G; ++j) e[j] = t + j < len ? (unsigned)ep[(long long)(t + j) * a.ld] : (kUp | kDown);
-#pragma unroll
-      for (int j = 0; j < G; ++j) {
-        all_up = all_up && (e[j] & kUp) != 0u;
-        all_down = all_down && (e[j] & kDown) != 0u;
-      }
-    }
-    kind = all_up ? 1 : (all_down ? 2 : 0);
-  }
-  g_tp_kind[(long long)k * a.N + n] = kind;
 }
 
 // The closed forms below add steps in 64 bits; the reference adds in int32 and wraps (scale.go:66, 94) before it
@@ -1753,8 +1739,6 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
   KSA_LAUNCH_CHECK("tp_fix_kernel");
   // traces with chunks that neither stand nor got patched: what kind of chunks they have, their true entry
   // states, a second replay of the chunks that need one (threads of the other chunks return at once)
-  tp_classify_kernel<FAULTS><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
-  KSA_LAUNCH_CHECK("tp_classify_kernel");
   tp_resolve_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_resolve_kernel");
   tp_spec_kernel<A, 1, 8, BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4), FAULTS, true><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);

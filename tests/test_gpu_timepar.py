@@ -20,7 +20,7 @@ from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 pytestmark = pytest.mark.gpu
 
 
-TP_LAUNCHES = 9  # pass 1, 2a, 2b, the chunks' kinds, 3a, the second replay, 3b, the shift of replica counts, the kernel for traces given up
+TP_LAUNCHES = 8  # pass 1, 2a, 2b, 3a, the second replay, 3b, the shift of replica counts, the kernel for traces given up
 TP_SUMMARY_LAUNCHES = 8  # pass 0 (entry states), 1, 2a, 2b, 3a, the second replay of listed chunks, 3b, and that kernel
 
 
