@@ -248,6 +248,21 @@ __device__ __forceinline__ void tp_store(int* rp, unsigned char* ep, const int (
   }
 }
 
+// The closed forms below add steps in 64 bits; the reference adds in int32 and wraps (scale.go:66, 94) before it
+// clamps. They agree as long as a step from below the limit cannot pass INT_MAX (from above it: INT_MIN),
+// which only limits next to the ends of int32 can make happen (found by tools/fuzz_timepar.py: max_pods
+// = 2^31 - 1). Otherwise the chunk is replayed.
+__device__ __forceinline__ bool step_cannot_wrap(const ksa_step_consts& c, bool up) {
+  return up ? (long long)c.max32 + c.up32 <= INT_MAX : (long long)c.min32 - c.down32 >= INT_MIN;
+}
+
+// Whether chunks of that kind have the closed forms at all with this policy (pure_exit, tp_fill_chunk).
+__device__ __forceinline__ bool pure_steps_ok(const ksa_step_consts& c, int kind) {
+  const bool up = kind == 1;
+  const int step = up ? c.up32 : c.down32;
+  return step >= 0 && step <= (1 << 30) && step_cannot_wrap(c, up);
+}
+
 // The outputs of a chunk in which every tick met the scale-up (kind 1) or the scale-down threshold (2),
 // from its true entry state, without reading a depth: the cool-down line until the first call (the first
 // tick the gate is open) and between calls, one call every cool-down period; a call steps the count
@@ -276,8 +291,95 @@ __device__ void tp_fill_chunk(const TpArgs& a, const ksa_step_consts& c, long lo
   }
 }
 
+// Can the chunk's outputs be written from the closed form? Marked kFill by pass 3a, or taken by it as pass 1
+// replayed it (status 0; kListed / kLeftToShift: pass 2a had doubts that the true state did not confirm) and of a
+// kind that has the form: written again from its entry state it comes out as it is (before tp_shift_kernel:
+// a chunk that is off by a replica offset is written with that offset).
+__device__ __forceinline__ bool tp_fillable(const ksa_step_consts& c, int status, int kind) {
+  return status == kFill ||
+         ((status == 0 || status == kListed || status == kLeftToShift) && kind != 0 && pure_steps_ok(c, kind));
+}
+// The two kernels after pass 3a share the marked chunks out by the same rule. A group of 32 adjacent traces
+// (a warp of the second replay) with a chunk to be replayed is replayed by that warp, its kFill chunks with
+// it. Otherwise a group of 8 adjacent traces whose chunks are all fillable is written by tp_fill_kernel,
+// 256-bit stores (a warp: 256 traces, a kilobyte of replica counts per store; the steady state, every queue
+// saturated or idle, is all such groups), and what is left over by the second replay's threads one trace
+// each (the same bytes written that way everywhere took 0.88 ms at 4096 x 10^5: 2.3 TB/s).
+__device__ __forceinline__ bool tp_vector_layout(const TpArgs& a) {
+  return a.N % 8 == 0 && a.ld % 8 == 0 && ((unsigned long long)a.replicas & 31u) == 0u && ((unsigned long long)a.events & 7u) == 0u;
+}
+
+// Thread (8 adjacent traces, chunk, part of the chunk): the closed form gives the state at any tick, so a
+// chunk is cut into kFillParts runs of ticks for as many times the threads (8 traces per thread leave 1168
+// warps at 4096 x 10^5, and a warp needs some 100 instructions per tick of its 256 traces: 0.70 ms; in 4
+// parts 0.46, in 8 0.43 = 4.7 TB/s of stores).
+constexpr int kFillParts = 8;
+__device__ __forceinline__ bool pure_exit(const ksa_step_consts& c, int kind, int t0, int len, TpState& g);
+__global__ void __launch_bounds__(BLOCK) tp_fill_kernel(const __grid_constant__ TpArgs a) {
+  const long long n0 = ((long long)blockIdx.x * BLOCK + threadIdx.x) * 8;
+  if (g_tp_probe_bad > a.probe_limit || !tp_vector_layout(a)) return;
+  const int k = blockIdx.y + 1;
+  const ksa_step_consts c(a.pk);
+  int kind[8];
+  bool rerun = false, any = false, all = true;
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    const bool in = n0 + v < a.N;
+    const int status = in ? record(a, k, n0 + v)->status : -1;
+    kind[v] = in ? g_tp_kind[(long long)k * a.N + n0 + v] : 0;
+    rerun = rerun || status == kRerun;
+    any = any || status == kFill;
+    all = all && tp_fillable(c, status, kind[v]);
+  }
+  // lanes 4q .. 4q + 3 hold the 32 traces of one warp of the second replay
+  int group_rerun = rerun ? 1 : 0;  // (every lane takes part in both exchanges)
+  group_rerun |= __shfl_xor_sync(0xffffffffu, group_rerun, 1);
+  group_rerun |= __shfl_xor_sync(0xffffffffu, group_rerun, 2);
+  if (group_rerun != 0 || !any || !all) return;
+  const int t0 = k * a.L;
+  const int len = min(a.L, a.T - t0);
+  const int part = (len + kFillParts - 1) / kFillParts;
+  const int ta = min((int)blockIdx.z * part, len), tb = min(ta + part, len);  // my ticks of the chunk: t0 + ta + 1 .. t0 + tb
+  if (ta >= tb) return;
+  // per trace: ticks until its next call, its count, and the constants of its direction
+  int wait[8], r[8], step[8], limit[8], period[8];
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    const bool up = kind[v] == 1;
+    TpState g = record(a, k, n0 + v)->entry1;
+    if (ta > 0) pure_exit(c, kind[v], t0, ta, g);  // the state after the ticks before mine
+    const long long next = max(t0 + ta + 1, up ? g.su : g.sd);
+    wait[v] = (int)min(next - (t0 + ta + 1), (long long)INT_MAX);
+    r[v] = g.r;
+    step[v] = up ? c.up32 : -c.down32;  // (pure_steps_ok: 0 .. 2^30, and r + step cannot wrap on the side of the limit)
+    limit[v] = up ? c.max32 : c.min32;
+    period[v] = max(up ? c.cu : c.cd, 1) - 1;
+  }
+  int* rp = a.replicas + (long long)(t0 + ta) * a.ld + n0;
+  unsigned char* ep = a.events + (long long)(t0 + ta) * a.ld + n0;
+  for (int t = ta; t < tb; ++t) {
+    unsigned ev[8];
+#pragma unroll
+    for (int v = 0; v < 8; ++v) {
+      const bool up = kind[v] == 1;
+      const bool call = wait[v] == 0;
+      const bool applied = call && (up ? r[v] < limit[v] : r[v] > limit[v]);
+      const int stepped = (int)((unsigned)r[v] + (unsigned)step[v]);  // (used only where it cannot wrap)
+      const int moved = up ? min(stepped, limit[v]) : max(stepped, limit[v]);
+      r[v] = applied ? moved : r[v];
+      ev[v] = up ? (call ? (applied ? KSA_EV_UP_APPLIED : KSA_EV_UP_NOOP) : KSA_EV_UP_COOL)
+                 : (call ? (applied ? KSA_EV_DOWN_APPLIED : KSA_EV_DOWN_NOOP) : KSA_EV_DOWN_COOL);
+      wait[v] = call ? period[v] : wait[v] - 1;
+    }
+    tp_store<8>(rp, ep, r, ev);
+    rp += a.ld;
+    ep += a.ld;
+  }
+}
+
 // RERUN: the second replay. Only the chunks pass 3a marked (kRerun), from the entry state it put into
-// entry1, no warm-up; one trace per thread. Chunks marked kFill are written from the closed form instead.
+// entry1, no warm-up; one trace per thread. Chunks marked kFill are written from the closed form instead
+// (here or by tp_fill_kernel, see above), unless a chunk of the same warp is replayed: then they are replayed with it.
 template <int A, int V, int D, int TPB, int MINB, bool FAULTS, bool RERUN = false>
 __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constant__ TpArgs a) {
   const long long n0 = ((long long)blockIdx.x * TPB + threadIdx.x) * V;
@@ -290,13 +392,17 @@ __global__ void __launch_bounds__(TPB, MINB) tp_spec_kernel(const __grid_constan
     // A warp whose marked chunks all have the closed form writes them; if one of them has to be replayed
     // the others are replayed with it (from the same entry state: the same outputs) rather than making the
     // warp do both one after the other (random-walk depths, 4096 x 10^5: 2.82 -> 3.59 ms when it did).
-    const bool replay = __any_sync(__activemask(), status == kRerun);
-    if (status != kRerun && status != kFill) return;
-    if (!replay) {
+    const unsigned active = __activemask();
+    const bool replay = __any_sync(active, status == kRerun);
+    if (!replay) {  // nothing to replay in this warp: its kFill chunks are written, here or by tp_fill_kernel
       const ksa_step_consts cc(a.pk);
-      tp_fill_chunk(a, cc, n0, k * a.L, min(a.L, a.T - k * a.L), g_tp_kind[(long long)k * a.N + n0], rec->entry1);
+      const int kind = g_tp_kind[(long long)k * a.N + n0];
+      const unsigned fillable = __ballot_sync(active, tp_fillable(cc, status, kind));
+      const bool group = ((fillable >> (threadIdx.x & 24)) & 0xffu) == 0xffu;  // my 8 adjacent traces
+      if (status == kFill && !(group && tp_vector_layout(a))) tp_fill_chunk(a, cc, n0, k * a.L, min(a.L, a.T - k * a.L), kind, rec->entry1);
       return;
     }
+    if (status != kRerun && status != kFill) return;
   }
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
@@ -603,21 +709,13 @@ __global__ void __launch_bounds__(BLOCK) tp_fix_kernel(const __grid_constant__ T
   if (j < 0) g_tp_walk[n] = 1;  // the chunk after it was judged by an exit state that is not the true one
 }
 
-// The closed forms below add steps in 64 bits; the reference adds in int32 and wraps (scale.go:66, 94) before it
-// clamps. They agree as long as a step from below the limit cannot pass INT_MAX (from above it: INT_MIN),
-// which only limits next to the ends of int32 can make happen (found by tools/fuzz_timepar.py: max_pods
-// = 2^31 - 1). Otherwise the chunk is replayed.
-__device__ __forceinline__ bool step_cannot_wrap(const ksa_step_consts& c, bool up) {
-  return up ? (long long)c.max32 + c.up32 <= INT_MAX : (long long)c.min32 - c.down32 >= INT_MIN;
-}
-
 // The state after a chunk of that kind: the first call at the first tick the gate is open, then one
 // every cool-down period, each a full step towards the limit (scale.go:62-69, 89-97). Chunk = local
 // ticks t0 + 1 .. t0 + len. False: not worked out (steps that are negative or could wrap).
 __device__ __forceinline__ bool pure_exit(const ksa_step_consts& c, int kind, int t0, int len, TpState& g) {
   const bool up = kind == 1;
   const int step = up ? c.up32 : c.down32;
-  if (step < 0 || step > (1 << 30) || !step_cannot_wrap(c, up)) return false;
+  if (!pure_steps_ok(c, kind)) return false;
   const int cool = up ? c.cu : c.cd;
   const long long first = max(t0 + 1, up ? g.su : g.sd);  // blocked at local tick i <=> i < s
   if (first > t0 + len) return true;                      // the gate stays shut for the whole chunk
@@ -1743,6 +1841,10 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
   KSA_LAUNCH_CHECK("tp_resolve_kernel");
   tp_spec_kernel<A, 1, 8, BLOCK, A == 1 ? 8 : (A == 2 ? 5 : 4), FAULTS, true><<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_spec_kernel (second replay)");
+  if constexpr (!FAULTS) {  // (with a failure mask no chunk has a closed form)
+    tp_fill_kernel<<<dim3((unsigned)((a.N + 8 * BLOCK - 1) / (8 * BLOCK)), (unsigned)(a.K - 1), kFillParts), BLOCK, 0, st>>>(a);
+    KSA_LAUNCH_CHECK("tp_fill_kernel");
+  }
   tp_chain_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_chain_kernel");
   tp_shift_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);

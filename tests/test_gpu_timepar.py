@@ -20,7 +20,8 @@ from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 pytestmark = pytest.mark.gpu
 
 
-TP_LAUNCHES = 8  # pass 1, 2a, 2b, 3a, the second replay, 3b, the shift of replica counts, the kernel for traces given up
+TP_LAUNCHES = 9  # pass 1, 2a, 2b, 3a, the second replay, the chunks written from the closed form, 3b, the shift of replica counts, the kernel for traces given up
+TP_MASK_LAUNCHES = 8  # with a failure mask no chunk has a closed form (and a probe comes first when there are traces to sample)
 TP_SUMMARY_LAUNCHES = 8  # pass 0 (entry states), 1, 2a, 2b, 3a, the second replay of listed chunks, 3b, and that kernel
 
 
@@ -101,7 +102,7 @@ def test_random_policies_any_chunk_count(engine, A):
                                      f"A={A} case {case} T={T} N={N} ld={ld} chunks={chunks} warm={warm} wide={wide} "
                                      f"mask={fail is not None} {pol}", warm=warm, wide=wide, fail=fail)
                 if chunks_used(T, chunks) >= 2:  # (with a failure mask the probe comes first, if there are 32 traces to sample)
-                    assert took == TP_LAUNCHES + (1 if fail is not None and N >= 32 else 0), "the forced chunk count was not used"
+                    assert took == (TP_LAUNCHES if fail is None else TP_MASK_LAUNCHES + (1 if N >= 32 else 0)), "the forced chunk count was not used"
 
 
 def test_traces_that_never_converge(engine):
@@ -168,7 +169,7 @@ def test_every_checkpoint_and_the_automatic_choice(engine):
     assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, None, "automatic, 4096 x 8192") == TP_LAUNCHES
     fail = oracle_lib.gen_faults(7, 5, 4, 4, 0, T, 0, N, N)
     assert run_and_check(engine, pol, depth, T, 1, N, N, 0, st, None, "automatic, 4096 x 8192, failures",
-                         fail=fail) == TP_LAUNCHES + 1  # (with a failure mask the probe comes first)
+                         fail=fail) == TP_MASK_LAUNCHES + 1  # (with a failure mask the probe comes first)
     assert run_and_check(engine, pol, depth[:512], 512, 1, N, N, 0, st, None, "automatic, 4096 x 512") <= 2
 
 
@@ -258,7 +259,7 @@ def test_chunked_paths_never_write_outside_their_outputs(engine):
                 if mode == "full":
                     engine.replay_full(pol, depth, T, A, N, ld, 5, state, replicas=rbuf[guard:guard + T],
                                        events=ebuf[guard:guard + T], fail=fail)
-                    assert engine.launch_count() == TP_LAUNCHES + (1 if with_mask and N >= 32 else 0)  # (the probe)
+                    assert engine.launch_count() == (TP_MASK_LAUNCHES + (1 if N >= 32 else 0) if with_mask else TP_LAUNCHES)  # (the probe)
                 else:
                     engine.replay_summary(pol, depth, T, A, N, ld, 5, state, summary=summ, fail=fail)
                     assert engine.launch_count() == TP_SUMMARY_LAUNCHES
