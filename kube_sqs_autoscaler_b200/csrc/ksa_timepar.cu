@@ -757,45 +757,60 @@ __device__ __forceinline__ int later_stamp(int keep, int cand, int c, int after)
 template <int A, bool FAULTS, bool RESOLVE>
 __device__ bool tp_walk(const TpArgs& a, const ksa_step_consts& c, long long n, TpState& cur) {
   int replays = 0;
+  // One thread walks a trace's chunks in order, and a record costs a memory latency: the next chunk's
+  // (status, the two states, its kind) is on its way while this one is judged (4096 traces x 96 chunks:
+  // a tenth of a millisecond per walk without that). Nothing below writes a later chunk's record.
+  const TpChunk* ahead = record(a, 1, n);
+  int status_next = ahead->status;
+  TpState entry_next = ahead->entry1, exit_next = ahead->exit1;
+  int kind_next = g_tp_kind[a.N + n];
   for (int k = 1; k < a.K; ++k) {
     const int t0 = k * a.L;
     const int len = min(a.L, a.T - t0);
     const long long idx = (long long)k * a.N + n;
     TpChunk* const rec = record(a, k, n);
-    const int status = rec->status;
+    const int status = status_next;
+    const TpState entry1 = entry_next, exit1 = exit_next;
+    const int kind = kind_next;
+    if (k + 1 < a.K) {
+      ahead = record(a, k + 1, n);
+      status_next = ahead->status;
+      entry_next = ahead->entry1;
+      exit_next = ahead->exit1;
+      kind_next = g_tp_kind[idx + a.N];
+    }
     const bool patched = status < 0 || (status >= 1 && status <= kChecks);
     if (!patched) {
-      const long long delta = (long long)cur.r - rec->entry1.r;
-      if (same_gates(rec->entry1, cur, t0) && (delta == 0 || shift_safe(*rec))) {
+      const long long delta = (long long)cur.r - entry1.r;
+      if (same_gates(entry1, cur, t0) && (delta == 0 || (exit1.su == entry1.su && exit1.sd == entry1.sd))) {  // (shift_safe)
         if (!RESOLVE && delta != 0) g_tp_delta[idx] = (int)delta;
-        cur.r = (int)(rec->exit1.r + delta);
-        cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, t0);
-        cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, t0);
+        cur.r = (int)(exit1.r + delta);
+        cur.su = later_stamp(cur.su, exit1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, exit1.sd, c.cd, t0);
         continue;
       }
     } else if (same_future(g_tp_used[idx], cur, t0)) {
       // pass 2b started from (the equivalent of) the true state: its work stands
       if (status < 0) {  // 2b rewrote the whole chunk; its end state is in the entry1 slot
-        cur.r = rec->entry1.r;
-        cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
-        cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
+        cur.r = entry1.r;
+        cur.su = later_stamp(cur.su, entry1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, entry1.sd, c.cd, t0);
       } else {
         const int tc = t0 + check_tick(status - 1);  // pass 1's trajectory is the true one after tc
-        cur.su = later_stamp(cur.su, rec->entry1.su, c.cu, t0);
-        cur.sd = later_stamp(cur.sd, rec->entry1.sd, c.cd, t0);
-        cur.r = rec->exit1.r;
-        cur.su = later_stamp(cur.su, rec->exit1.su, c.cu, tc);
-        cur.sd = later_stamp(cur.sd, rec->exit1.sd, c.cd, tc);
+        cur.su = later_stamp(cur.su, entry1.su, c.cu, t0);
+        cur.sd = later_stamp(cur.sd, entry1.sd, c.cd, t0);
+        cur.r = exit1.r;
+        cur.su = later_stamp(cur.su, exit1.su, c.cu, tc);
+        cur.sd = later_stamp(cur.sd, exit1.sd, c.cd, tc);
       }
       continue;
     }
     if (RESOLVE) {
       // what the chunk ended with the first time (pass 2b's end state is in the entry1 slot)
-      const TpState ended = status < 0 ? rec->entry1 : rec->exit1;
+      const TpState ended = status < 0 ? entry1 : exit1;
       rec->entry1 = cur;
       rec->status = kRerun;
       TpState worked = cur;
-      const int kind = g_tp_kind[idx];
       if (kind != 0 && pure_exit(c, kind, t0, len, worked)) {
         rec->status = kFill;  // the outputs have a closed form too: written, not replayed
         rec->exit1 = worked;
