@@ -1554,17 +1554,28 @@ __device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long l
   TpRun one;
   tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
   tp_run_append(run, one);
+  // (the next chunk's status, states and record are on their way while this one is judged: nothing below
+  // writes a later chunk's)
+  int status_next = a.status[a.N + n];
+  TpG used_next = tp_get(a.en, a.N + n);
+  TpG exit_next = (status_next == 1 || status_next < 0) ? tp_get(a.fx, a.N + n) : tp_get(a.io, a.N + n);
+  ksa_summary q_next = a.part[a.N + n];
   for (int k = 1; k < a.K; ++k) {
     const long long idx = (long long)k * a.N + n;
     const int t0 = k * a.L;
     const int len = min(a.L, a.T - t0);
     const long long B = a.tick0 + t0;
     const bool last = k == a.K - 1;
-    const int status = a.status[idx];
-    const bool fixed = status == 1 || status < 0;  // the record and its exit state are pass 2b's
-    const TpG used = tp_get(a.en, idx);
-    TpG exit = fixed ? tp_get(a.fx, idx) : tp_get(a.io, idx);
-    ksa_summary q = a.part[idx];
+    const int status = status_next;
+    const TpG used = used_next;
+    TpG exit = exit_next;  // (pass 2b's where the record is: status 1, -1)
+    ksa_summary q = q_next;
+    if (!last) {
+      status_next = a.status[idx + a.N];
+      used_next = tp_get(a.en, idx + a.N);
+      exit_next = (status_next == 1 || status_next < 0) ? tp_get(a.fx, idx + a.N) : tp_get(a.io, idx + a.N);
+      q_next = a.part[idx + a.N];
+    }
     const bool gates = tp_same_gates(a.pk, c, used, cur, B, a.T - t0);
     const long long delta = (long long)cur.r - used.r;
     if (gates && (delta == 0 || tp_shift_safe(c, q, used.r, delta))) {
