@@ -1546,36 +1546,46 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_fix_kernel(const __grid_constant
 //  FINAL (pass 3b, after the second replay): the same walk over what is there now. A chunk that still
 //    does not fit is replayed here, up to kChainReplays per trace; a trace that needs more is flagged for
 //    the one-trace-per-thread kernel that follows and nothing is written for it.
+
+// One chunk of a trace as the walks need it. A walk is one thread going through a trace's chunks in
+// order, and reading a chunk's status, states and record where it needs them costs it two memory latencies
+// per chunk (which exit state counts depends on the status): 0.11 ms per walk at 4096 x 10^5, as much as a
+// fifth of pass 1. So the warp's lanes fetch 32 chunks at a time into shared memory, each lane one chunk
+// with all its loads in flight together, and lane 0 walks over those.
+struct TpStaged {
+  ksa_summary q;
+  TpG used, exit;  // what the record was replayed from, and what it ended with (pass 2b's where the record is)
+  int status;
+};
+__device__ __forceinline__ void tp_stage(const TpSumArgs& a, long long n, int k0, TpStaged* slots, int lane) {
+  __syncwarp();  // (lane 0 is done with what is there)
+  const int k = k0 + lane;
+  if (k < a.K) {
+    const long long idx = (long long)k * a.N + n;
+    const int status = a.status[idx];
+    const TpG io = tp_get(a.io, idx), fx = tp_get(a.fx, idx);  // both: neither load waits for the status
+    slots[lane].q = a.part[idx];
+    slots[lane].used = tp_get(a.en, idx);
+    slots[lane].exit = (status == 1 || status < 0) ? fx : io;
+    slots[lane].status = status;
+  }
+  __syncwarp();
+}
+
+// Chunks k0 .. k1 - 1 (staged in `slots`) of the walk; false: the trace is given up.
 template <int A, bool FAULTS, bool RESOLVE>
-__device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long long n, TpRun& run, bool& unresolved) {
-  int replays = 0;
-  tp_run_init(run);
-  TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+__device__ bool tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long long n, int k0, int k1, const TpStaged* slots,
+                            TpG& cur, TpRun& run, int& replays) {
   TpRun one;
-  tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
-  tp_run_append(run, one);
-  // (the next chunk's status, states and record are on their way while this one is judged: nothing below
-  // writes a later chunk's)
-  int status_next = a.status[a.N + n];
-  TpG used_next = tp_get(a.en, a.N + n);
-  TpG exit_next = (status_next == 1 || status_next < 0) ? tp_get(a.fx, a.N + n) : tp_get(a.io, a.N + n);
-  ksa_summary q_next = a.part[a.N + n];
-  for (int k = 1; k < a.K; ++k) {
+  for (int k = k0; k < k1; ++k) {
     const long long idx = (long long)k * a.N + n;
     const int t0 = k * a.L;
     const int len = min(a.L, a.T - t0);
     const long long B = a.tick0 + t0;
     const bool last = k == a.K - 1;
-    const int status = status_next;
-    const TpG used = used_next;
-    TpG exit = exit_next;  // (pass 2b's where the record is: status 1, -1)
-    ksa_summary q = q_next;
-    if (!last) {
-      status_next = a.status[idx + a.N];
-      used_next = tp_get(a.en, idx + a.N);
-      exit_next = (status_next == 1 || status_next < 0) ? tp_get(a.fx, idx + a.N) : tp_get(a.io, idx + a.N);
-      q_next = a.part[idx + a.N];
-    }
+    const TpG used = slots[k - k0].used;
+    TpG exit = slots[k - k0].exit;
+    ksa_summary q = slots[k - k0].q;
     const bool gates = tp_same_gates(a.pk, c, used, cur, B, a.T - t0);
     const long long delta = (long long)cur.r - used.r;
     if (gates && (delta == 0 || tp_shift_safe(c, q, used.r, delta))) {
@@ -1606,21 +1616,40 @@ __device__ void tp_sum_walk(const TpSumArgs& a, const ksa_step_consts& c, long l
       cur.jd = tp_taken(exit.jd, B, len) ? exit.jd : cur.jd;
       continue;  // (pass 3a builds no result)
     } else {
-      if (++replays > kChainReplays) {  // left to the plain kernel that follows (g_tp_unresolved)
-        unresolved = true;
-        return;
-      }
+      if (++replays > kChainReplays) return false;  // left to the plain kernel that follows (g_tp_unresolved)
       tp_summary_clear(q);
       tp_sum_replay<A, FAULTS>(a, c, n, t0, len, cur, &q);
       tp_run_of_chunk(one, q, cur, B, len, true, last ? a.mE_lo : a.mL_lo, last ? a.mE_hi : a.mL_hi);
     }
     tp_run_append(run, one);
   }
+  return true;
+}
+// The whole walk by a warp: lane 0 walks, all lanes stage. `run` and `unresolved` are lane 0's.
+template <int A, bool FAULTS, bool RESOLVE>
+__device__ void tp_sum_walk_warp(const TpSumArgs& a, const ksa_step_consts& c, long long n, TpStaged* slots, int lane,
+                                 TpRun& run, bool& unresolved) {
+  TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+  int replays = 0;
+  bool going = true;
+  if (lane == 0) {
+    tp_run_init(run);
+    TpRun one;
+    tp_run_of_chunk(one, a.part[n], cur, a.tick0, a.L, true, a.mL_lo, a.mL_hi);  // (K >= 2: chunk 0 has L ticks)
+    tp_run_append(run, one);
+  }
+  for (int k0 = 1; k0 < a.K; k0 += 32) {
+    tp_stage(a, n, k0, slots, lane);
+    if (lane == 0 && going) going = tp_sum_walk<A, FAULTS, RESOLVE>(a, c, n, k0, min(k0 + 32, a.K), slots, cur, run, replays);
+  }
+  if (lane == 0) unresolved = !going;
+  __syncwarp();
 }
 
 // ---- pass 3a: warp (trace) ----------------------------------------------------------------------
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_constant__ TpSumArgs a) {
+  __shared__ TpStaged stage[BLOCK / 32][32];
   const long long n = (long long)blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
   if (n >= a.N) return;  // (whole warps)
   const int lane = threadIdx.x & 31;
@@ -1631,12 +1660,9 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_cons
   }
   if (__all_sync(0xffffffffu, fine)) return;
   const ksa_step_consts c(a.pk);
-  if (lane == 0) {
-    TpRun run;
-    bool unresolved = false;
-    tp_sum_walk<A, FAULTS, true>(a, c, n, run, unresolved);
-  }
-  __syncwarp();
+  TpRun run;
+  bool unresolved = false;
+  tp_sum_walk_warp<A, FAULTS, true>(a, c, n, stage[threadIdx.x >> 5], lane, run, unresolved);
   // the records of the chunks the walk worked its way through in closed form: a few hundred instructions
   // each (powers and geometric sums), shared out over the lanes
   for (int k = 1 + lane; k < a.K; k += 32) {
@@ -1659,36 +1685,24 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_resolve_kernel(const __grid_cons
   }
 }
 
-// Does every chunk of the trace fit the true state now, as it stands or shifted by a replica offset? The walk
-// of tp_sum_walk without building the result: only the states are read (a record only where an offset has
-// to be judged), the next chunk's while this one is looked at. Leaves each chunk's offset in g_tp_delta
-// (summary mode has no other use for it). False: some chunk does not fit (the full walk decides what then).
-__device__ bool tp_sum_verify(const TpSumArgs& a, const ksa_step_consts& c, long long n) {
-  TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
-  long long idx = a.N + n;
-  int status = a.status[idx];
-  TpG used = tp_get(a.en, idx);
-  TpG exit = (status == 1 || status < 0) ? tp_get(a.fx, idx) : tp_get(a.io, idx);
-  for (int k = 1; k < a.K; ++k) {
-    const TpG used_k = used, exit_k = exit;
-    const long long idx_k = idx;
-    if (k + 1 < a.K) {  // the next chunk's states are on their way while this one is judged
-      idx += a.N;
-      status = a.status[idx];
-      used = tp_get(a.en, idx);
-      exit = (status == 1 || status < 0) ? tp_get(a.fx, idx) : tp_get(a.io, idx);
-    }
+// Does every chunk k0 .. k1 - 1 (staged) fit the true state now, as it stands or shifted by a replica offset?
+// The walk without building the result. Leaves each chunk's offset in g_tp_delta (summary mode has no other
+// use for it). False: some chunk does not fit (the full walk decides what then).
+__device__ bool tp_sum_verify(const TpSumArgs& a, const ksa_step_consts& c, long long n, int k0, int k1, const TpStaged* slots,
+                              TpG& cur) {
+  for (int k = k0; k < k1; ++k) {
+    const TpStaged& x = slots[k - k0];
     const int t0 = k * a.L;
     const int len = min(a.L, a.T - t0);
     const long long B = a.tick0 + t0;
-    const long long delta = (long long)cur.r - used_k.r;
-    if (!tp_same_gates(a.pk, c, used_k, cur, B, a.T - t0)) return false;
-    if (delta != 0 && !tp_shift_safe(c, a.part[idx_k], used_k.r, delta)) return false;
+    const long long delta = (long long)cur.r - x.used.r;
+    if (!tp_same_gates(a.pk, c, x.used, cur, B, a.T - t0)) return false;
+    if (delta != 0 && !tp_shift_safe(c, x.q, x.used.r, delta)) return false;
     if (delta != (long long)(int)delta) return false;  // (an offset of 2^31 or more: not one g_tp_delta holds)
-    g_tp_delta[idx_k] = (int)delta;
-    cur.r = (int)(exit_k.r + delta);
-    cur.ju = tp_taken(exit_k.ju, B, len) ? exit_k.ju : cur.ju;
-    cur.jd = tp_taken(exit_k.jd, B, len) ? exit_k.jd : cur.jd;
+    g_tp_delta[(long long)k * a.N + n] = (int)delta;
+    cur.r = (int)(x.exit.r + delta);
+    cur.ju = tp_taken(x.exit.ju, B, len) ? x.exit.ju : cur.ju;
+    cur.jd = tp_taken(x.exit.jd, B, len) ? x.exit.jd : cur.jd;
   }
   return true;
 }
@@ -1696,9 +1710,11 @@ __device__ bool tp_sum_verify(const TpSumArgs& a, const ksa_step_consts& c, long
 // ---- pass 3b: warp (trace) ----------------------------------------------------------------------
 template <int A, bool FAULTS>
 __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_constant__ TpSumArgs a) {
+  __shared__ TpStaged stage[BLOCK / 32][32];
   const long long n = (long long)blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
   if (n >= a.N) return;  // (whole warps)
   const int lane = threadIdx.x & 31;
+  TpStaged* const slots = stage[threadIdx.x >> 5];
   const ksa_step_consts c(a.pk);
   const int per = (a.K + 31) / 32;
   const int k0 = lane * per, k1 = min(a.K, k0 + per);
@@ -1729,10 +1745,14 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
   fine = __all_sync(0xffffffffu, fine);
   bool parallel = fine;
   if (!fine) {
-    // not every chunk simply stands. If each fits the true state as it is or shifted (lane 0 looks: states
-    // only), the lanes combine them as above, with the offsets; else lane 0 walks and replays.
-    bool fits = false;
-    if (lane == 0) fits = tp_sum_verify(a, c, n);
+    // not every chunk simply stands. If each fits the true state as it is or shifted (lane 0 looks), the
+    // lanes combine them as above, with the offsets; else lane 0 walks and replays.
+    bool fits = true;
+    TpG cur = tp_get(a.io, n);  // chunk 0 ran from the caller's state
+    for (int s0 = 1; s0 < a.K; s0 += 32) {
+      tp_stage(a, n, s0, slots, lane);
+      if (lane == 0 && fits) fits = tp_sum_verify(a, c, n, s0, min(s0 + 32, a.K), slots, cur);
+    }
     parallel = __shfl_sync(0xffffffffu, (int)fits, 0) != 0;
     __syncwarp();  // (lane 0's offsets are the other lanes' to read)
     if (parallel) my_chunks(true);
@@ -1745,8 +1765,8 @@ __global__ void __launch_bounds__(BLOCK) tp_sum_chain_kernel(const __grid_consta
       tp_run_shfl(other, run, min(lane + off, 31));
       if ((lane & (2 * off - 1)) == 0) tp_run_append(run, other);
     }
-  } else if (lane == 0) {
-    tp_sum_walk<A, FAULTS, false>(a, c, n, run, unresolved);
+  } else {
+    tp_sum_walk_warp<A, FAULTS, false>(a, c, n, slots, lane, run, unresolved);
   }
   if (lane != 0) return;
   g_tp_unresolved[n] = unresolved ? 1 : 0;
