@@ -121,6 +121,7 @@ static __device__ int g_tp_delta[kMaxChunks];
 constexpr int kLeftToShift = 100;  // TpChunk::status: pass 2a left the chunk to pass 3, which shifts it
 constexpr int kListed = 101;       // listed for pass 2b, which replaces it unless it leaves the chunk alone
 constexpr int kRerun = 102;        // replayed a second time from the entry state pass 3a put into entry1
+constexpr int kRedone = 104;       // replayed by pass 3b itself, from the true state: entry1 / exit1 are stale
 constexpr int kFill = 103;         // every tick met the same threshold: outputs written from the closed form (tp_fill_chunk),
                                    // from the entry state in entry1; exit1 = the state after it, worked out by pass 3a
 
@@ -320,6 +321,10 @@ __global__ void __launch_bounds__(BLOCK) tp_fill_kernel(const __grid_constant__ 
   if (g_tp_probe_bad > a.probe_limit || !tp_vector_layout(a)) return;
   const int k = blockIdx.y + 1;
   const ksa_step_consts c(a.pk);
+  int walked = 0;  // (only a trace pass 3a walked has marked chunks: the usual call stops here)
+#pragma unroll
+  for (int v = 0; v < 8; ++v) walked |= n0 + v < a.N ? g_tp_walk[n0 + v] : 0;
+  if (__ballot_sync(0xffffffffu, walked != 0) == 0u) return;
   int kind[8];
   bool rerun = false, any = false, all = true;
 #pragma unroll
@@ -826,6 +831,7 @@ __device__ bool tp_walk(const TpArgs& a, const ksa_step_consts& c, long long n, 
       tp_replay_until_match<A, FAULTS>(a, c, n, t0, len, rec, kChecks, s);  // (the whole chunk: no checkpoint applies)
       cur = TpState{s.r, s.su, s.sd};
       g_tp_delta[idx] = 0;
+      rec->status = kRedone;
     }
   }
   return true;
@@ -888,14 +894,59 @@ __global__ void __launch_bounds__(BLOCK) tp_chain_kernel(const __grid_constant__
 }
 
 // ---- after pass 3: the chunks it decided to shift --------------------------------------------------
-// Thread (trace, chunk >= 1): add the chunk's offset to its replica counts (the events are the same).
+// A chunk is shifted only if no scale call happened in it (shift_safe), so its replica count is ONE number
+// from its first tick to its last: what it ended with, plus the offset. Where 8 adjacent traces all have such
+// a chunk it is written, not read and added to: half the bytes, and 256-bit stores (the trace that goes
+// quiet is a fleet that goes quiet: 131072 x 10^4 quiet traces, 4.30 ms with every count read and
+// rewritten, the worst case against the plain kernels' 3.28). Other shifted chunks: tp_shift_kernel.
+__device__ __forceinline__ bool tp_constant_chunk(const TpChunk& rec, int unresolved) {
+  const int status = rec.status;
+  const bool patched = status < 0 || (status >= 1 && status <= kChecks) || status == kRedone;  // (entry1 is not its entry state)
+  return unresolved == 0 && !patched && shift_safe(rec);
+}
+// Thread (8 adjacent traces, chunk >= 1, part of the chunk).
+__global__ void __launch_bounds__(BLOCK) tp_shift_fill_kernel(const __grid_constant__ TpArgs a) {
+  const long long n0 = ((long long)blockIdx.x * BLOCK + threadIdx.x) * 8;
+  if (n0 >= a.N || g_tp_probe_bad > a.probe_limit || !tp_vector_layout(a)) return;  // (N is a multiple of 8)
+  const int k = blockIdx.y + 1;
+  int r[8], delta[8];
+  bool any = false, all = true;
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    delta[v] = g_tp_delta[(long long)k * a.N + n0 + v];
+    any = any || delta[v] != 0;
+  }
+  if (!any) return;  // (the usual call stops here)
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    const TpChunk* rec = record(a, k, n0 + v);
+    all = all && tp_constant_chunk(*rec, g_tp_unresolved[n0 + v]);
+    r[v] = (int)((unsigned)rec->exit1.r + (unsigned)delta[v]);
+  }
+  if (!all) return;
+  const int t0 = k * a.L;
+  const int len = min(a.L, a.T - t0);
+  const int part = (len + kFillParts - 1) / kFillParts;
+  const int ta = min((int)blockIdx.z * part, len), tb = min(ta + part, len);
+  int* rp = a.replicas + (long long)(t0 + ta) * a.ld + n0;
+  for (int t = ta; t < tb; ++t) {
+    asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(rp), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+    rp += a.ld;
+  }
+}
+// Thread (trace, chunk >= 1): add the chunk's offset to its replica counts (the events are the same), unless
+// tp_shift_fill_kernel had the chunk's group of 8 traces.
 __global__ void __launch_bounds__(BLOCK) tp_shift_kernel(const __grid_constant__ TpArgs a) {
   const long long n = (long long)blockIdx.x * BLOCK + threadIdx.x;
   if (n >= a.N) return;
   const int k = blockIdx.y + 1;
   if (g_tp_probe_bad > a.probe_limit) return;
   const int delta = g_tp_delta[(long long)k * a.N + n];
-  if (delta == 0 || g_tp_unresolved[n] != 0) return;  // (a trace pass 3 gave up is rewritten by the plain kernel)
+  const int unresolved = g_tp_unresolved[n];
+  const unsigned constant = __ballot_sync(__activemask(), tp_constant_chunk(*record(a, k, n), unresolved));
+  if (delta == 0 || unresolved != 0) return;  // (a trace pass 3 gave up is rewritten by the plain kernel)
+  if (tp_vector_layout(a) && ((constant >> (threadIdx.x & 24)) & 0xffu) == 0xffu) return;  // written already
   const int t0 = k * a.L;
   const int len = min(a.L, a.T - t0);
   int* rp = a.replicas + (long long)t0 * a.ld + n;
@@ -1893,6 +1944,8 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
   }
   tp_chain_kernel<A, FAULTS><<<gn, BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_chain_kernel");
+  tp_shift_fill_kernel<<<dim3((unsigned)((a.N + 8 * BLOCK - 1) / (8 * BLOCK)), (unsigned)(a.K - 1), kFillParts), BLOCK, 0, st>>>(a);
+  KSA_LAUNCH_CHECK("tp_shift_fill_kernel");
   tp_shift_kernel<<<dim3(gn, (unsigned)(a.K - 1)), BLOCK, 0, st>>>(a);
   KSA_LAUNCH_CHECK("tp_shift_kernel");
   return KSA_OK;

@@ -20,8 +20,8 @@ from tests.test_gpu_parity import adversarial_depth, random_policy, random_state
 pytestmark = pytest.mark.gpu
 
 
-TP_LAUNCHES = 9  # pass 1, 2a, 2b, 3a, the second replay, the chunks written from the closed form, 3b, the shift of replica counts, the kernel for traces given up
-TP_MASK_LAUNCHES = 8  # with a failure mask no chunk has a closed form (and a probe comes first when there are traces to sample)
+TP_LAUNCHES = 10  # pass 1, 2a, 2b, 3a, the second replay, the chunks written from the closed form, 3b, the shift of replica counts (two kernels), the kernel for traces given up
+TP_MASK_LAUNCHES = 9  # with a failure mask no chunk has a closed form (and a probe comes first when there are traces to sample)
 TP_SUMMARY_LAUNCHES = 8  # pass 0 (entry states), 1, 2a, 2b, 3a, the second replay of listed chunks, 3b, and that kernel
 
 
