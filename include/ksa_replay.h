@@ -212,15 +212,15 @@ int ksa_policy_cool_ticks(const ksa_policy* p, int64_t* up_ticks, int64_t* down_
  *   events_dev   [T][ld] uint8  KSA_EV_* bits of each tick        (may be NULL: not written)
  * Limits: 1 <= T <= 2^30 - 64 per call (chunk longer traces: the carry state makes that exact),
  * 1 <= N <= 2^31-1, N <= ld.
- * Few traces, many ticks (N <= 196608, T >= 4096, both outputs wanted): one thread per trace cannot
+ * Few traces, many ticks (N <= 49152, or 151552 < N <= 196608; T >= 4096, both outputs wanted): one thread per trace cannot
  * fill the GPU, so the library cuts the time axis into chunks that are replayed in parallel from
  * guessed states and then stitched exactly (csrc/ksa_timepar.cu; results are identical, the
  * trajectory and the carry state bit for bit). ksa_replay_summary and the two *_faults entry points
- * do the same below their own trace counts (32768, 16384 / 81920): there the chunks' summary
+ * do the same below their own trace counts (32768, 16384 / as above): there the chunks' summary
  * records, including the fingerprint, are combined in tick order. Chunks whose guess never meets
- * the truth (a queue that stays saturated, idle or quiet) are worked out or replayed a second time,
+ * the truth (a queue that stays saturated, idle or quiet) are worked out, shifted or replayed a second time,
  * and above 16384 traces, or with a failure mask, a 60 us probe decides first whether the depths suit the path at all; the
- * worst case found costs 1.3 x the plain kernels. That path keeps its per-chunk
+ * worst case found costs 1.06 x the plain kernels. That path keeps its per-chunk
  * records in fixed scratch arrays inside the library, so only one such call runs per GPU at a
  * time: a call that finds the scratch in use by a call on another stream, or a stream that is being
  * captured, takes the one-thread-per-trace kernels instead (same results, slower).

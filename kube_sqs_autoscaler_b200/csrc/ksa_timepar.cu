@@ -87,9 +87,17 @@ constexpr long long kTpMaxSummary = 32768;
 // moves the phase), and runs from different phases meet only when failures happen to line them up: at 32768
 // traces of such queues the chunked passes cost 3.6 ms against 1.9 (profiles/r02_small_n_robust.txt)
 constexpr long long kTpMaxSummaryFaults = 16384;
-constexpr long long kTpMaxFullFaults = 81920;     // 0.773 / 0.750; 0.81 / 0.83 at 98304
+// Full mode, with or without a mask: the limit is set by the depths on which chunks are replayed twice or
+// shifted, not by independent ones (profiles/r02_small_n_robust.txt, plain -> chunked ms; independent /
+// random walk / quiet / saturated-idle): 32768 traces 2.35 -> 1.68 / 2.45 / 2.10 / 2.45; 65536: 1.87 -> 1.67 /
+// 1.96 / 2.04 / 1.97; 98304: 2.24 -> 2.45 / 2.34 / 2.84 / 2.34 (the plain kernels are at 0.88 of the copy peak
+// there). With a mask, 49152: 2.73 -> 2.31 / 2.74 / 2.64 / 2.85; 65536: 2.04 -> 2.01 / 2.44 / 2.22 / 2.16.
+constexpr long long kTpMaxFull = 49152;
+constexpr long long kTpMaxFullFaults = 49152;
 // ... and again where one trace per thread starts a second, nearly empty wave of 148 x 1024 threads
-// (163840 traces: 0.81 against 0.73), as long as two chunks still fit one wave of pass 1
+// (163840 traces: 4.31 -> 2.91 / 4.35 / 3.51 / 4.36; with a mask 3.96 -> 3.69 / 4.10 / 3.99 / 4.05), as long as
+// two chunks still fit one wave of pass 1
+constexpr long long kTpFullSecondWave = 151552;
 constexpr long long kTpFullFaultsSecondWave = 151552;
 
 struct TpState {
@@ -2031,7 +2039,7 @@ int ksa_timepar_plan(int64_t T, int64_t N, bool summary, bool faults, bool vecto
     } else {
       // One trace per thread fills the GPU at about 2^18 threads, eight per thread (1-KB requests, the
       // shape that reaches the copy peak) at about 400k trace-chunks (profiles/r01_small_n_variants.txt).
-      if (N > 196608) return 0;
+      if (N > kMaxTraces || (N > kTpMaxFull && N <= kTpFullSecondWave)) return 0;
       const long long want = wide ? 393216 : 262144;
       K = (want + N - 1) / N;
     }
