@@ -30,13 +30,18 @@
 //          in which every tick met the same threshold (the saturated and the idle queue: calls exactly
 //          one cool-down apart, a guess keeps a wrong phase for ever; pass 1 notes such chunks, pure_exit),
 //          assumed to be what the chunk ended with the first time otherwise.
-//  then    the second replay: pass 1's kernel, one trace per thread, over the marked chunks.
+//  then    the second replay: pass 1's kernel, one trace per thread, over the marked chunks; and, for
+//          marked chunks in which every tick met the same threshold, no replay at all: their outputs
+//          have a closed form and are written without reading a depth (tp_fill_kernel: 8 adjacent
+//          traces per thread, 256-bit stores, where a whole group has the form).
 //  pass 3b thread (trace): if every chunk stands or was patched, all entry states were the true ones by
 //          induction, and the carry state is the last chunk's exit with the latest TRUE stamps.
 //          Otherwise the same walk over what is there now: wrong assumptions of pass 3a show as chunks
 //          that still do not fit; up to two are replayed here, a trace that needs more is flagged
 //          and left alone.
-//  then    thread (trace, chunk): add the offset to the replica counts of the chunks marked for it;
+//  then    the replica counts of the chunks marked for an offset: a chunk without a scale call has ONE
+//          count from its first tick to its last, which is written where 8 adjacent traces have such
+//          a chunk (tp_shift_fill_kernel) and read, added to and written back elsewhere (tp_shift_kernel);
 //          and the one-trace-per-thread kernel of ksa_replay.cu over the flagged traces only, from
 //          the caller's state. (Before passes 3a / second replay, a single trace that never met its
 //          true trajectory made the call several times SLOWER than the plain kernels: pass 3 replayed
