@@ -79,3 +79,80 @@ def test_closed_form_record_of_saturated_and_idle_chunks():
                int(s["up_cool" if up else "down_cool"]), int(s["hash"]), int(ref.state_replicas[0]),
                int((ref.state_last_up if up else ref.state_last_down)[0]))
         assert got == exp, (case, up, T, tick0, cu, cd, r0, ju, jd, pol)
+
+
+def pure_exit(up, step, c, limit, t0, length, r, gate):
+    """csrc/ksa_timepar.cu pure_exit: (replicas, gate) after `length` ticks t0+1 .. t0+length that all meet the
+    threshold; gate = the first local tick at which this direction's gate is open."""
+    first = max(t0 + 1, gate)
+    if first > t0 + length:
+        return r, gate
+    period = max(c, 1)
+    calls = (t0 + length - first) // period + 1
+    last = first + (calls - 1) * period
+    if up:
+        if r < limit:
+            r = min(r + calls * step, limit)
+    elif r > limit:
+        r = max(r - calls * step, limit)
+    return r, last + c
+
+
+def fill_part(up, step, c, limit, t0, ta, tb, r, gate):
+    """csrc/ksa_timepar.cu tp_fill_kernel for one trace: the outputs of ticks t0+ta+1 .. t0+tb of such a chunk
+    from the state at its first tick, jumping to tick ta by the closed form and counting the ticks to the
+    next call from there."""
+    if ta > 0:
+        r, gate = pure_exit(up, step, c, limit, t0, ta, r, gate)
+    wait = max(t0 + ta + 1, gate) - (t0 + ta + 1)
+    period = max(c, 1) - 1
+    cool, applied_ev, noop_ev = (ksa.EV_UP_COOL, ksa.EV_UP_APPLIED, ksa.EV_UP_NOOP) if up else \
+        (ksa.EV_DOWN_COOL, ksa.EV_DOWN_APPLIED, ksa.EV_DOWN_NOOP)
+    rs, es = [], []
+    for _ in range(ta, tb):
+        call = wait == 0
+        applied = call and (r < limit if up else r > limit)
+        if applied:
+            r = min(r + step, limit) if up else max(r - step, limit)
+        es.append((applied_ev if applied else noop_ev) if call else cool)
+        rs.append(r)
+        wait = period if call else wait - 1
+    return rs, es
+
+
+def test_closed_form_outputs_written_in_parts():
+    """The trajectory of a saturated / idle chunk written in runs of ticks, each from the closed-form state at its
+    first tick (tp_fill_kernel: 8 runs per chunk), equals the oracle's, for chunks that start anywhere in the
+    call with any gate state."""
+    rng = np.random.default_rng(6)
+    for case in range(300):
+        up = bool(rng.integers(0, 2))
+        T = int(rng.integers(2, 300))
+        cu, cd = int(rng.integers(0, 9)), int(rng.integers(0, 14))
+        pol = ksa.Policy(attr_mask=1, scale_up_messages=100, scale_down_messages=10, scale_up_cool_down=cu * 5 * S,
+                         scale_down_cool_down=cd * 5 * S, max_pods=int(rng.integers(2, 30)), min_pods=int(rng.integers(-3, 2)),
+                         scale_up_pods=int(rng.integers(0, 5)), scale_down_pods=int(rng.integers(0, 4)))
+        depth = np.full((T, 1, 1), 500 if up else 3, dtype=np.int64)
+        r0 = int(rng.integers(-5, 35))
+        # tick0 = 0 and stamps at 0: local gate-open ticks are cool-down + 0 (ksa_policy.cuh); a chunk starts at t0
+        ref = oracle_lib.replay(pol.to_c(), depth, T, 1, 1, 1, 0, np.array([r0], np.int32), np.zeros(1, np.int64),
+                                np.zeros(1, np.int64))
+        step, c, limit = (pol.scale_up_pods, cu, pol.max_pods) if up else (pol.scale_down_pods, cd, pol.min_pods)
+        t0 = int(rng.integers(0, T - 1))          # the chunk: ticks t0+1 .. T
+        r_in = r0 if t0 == 0 else int(ref.replicas[t0 - 1, 0])
+        # the gate at the chunk's first tick: the last call before it (an event other than the cool-down line) + c
+        gate = c  # (stamp 0 at tick0 = 0: open from tick c on)
+        for t in range(t0):
+            if int(ref.events[t, 0]) & (ksa.EV_UP_APPLIED | ksa.EV_UP_NOOP | ksa.EV_DOWN_APPLIED | ksa.EV_DOWN_NOOP):
+                gate = t + 1 + c
+        length = T - t0
+        parts = int(rng.choice([1, 2, 3, 8]))
+        per = (length + parts - 1) // parts
+        rs, es = [], []
+        for p in range(parts):
+            ta, tb = min(p * per, length), min(p * per + per, length)
+            a, b = fill_part(up, step, c, limit, t0, ta, tb, r_in, gate)
+            rs += a
+            es += b
+        assert rs == [int(x) for x in ref.replicas[t0:, 0]], (case, up, T, t0, cu, cd, r0, parts, pol)
+        assert es == [int(x) for x in ref.events[t0:, 0]], (case, up, T, t0, cu, cd, r0, parts, pol)
