@@ -1930,9 +1930,18 @@ int tp_launch(const TpArgs& a, bool wide, cudaStream_t st) {
       const unsigned gx = (unsigned)((a.N / 4 + BLOCK - 1) / BLOCK);
       tp_spec_kernel<A, 4, A == 1 ? 4 : (A == 2 ? 2 : 1), BLOCK, A == 3 ? 4 : 5, true><<<dim3(gx, (unsigned)a.K), BLOCK, 0, st>>>(a);
     } else {  // 8 traces per thread, the launch shape of the main kernel's default
-      constexpr int TPB = 256;
-      const unsigned gx = (unsigned)((a.N / 8 + TPB - 1) / TPB);
-      tp_spec_kernel<A, 8, A == 1 ? 2 : 1, TPB, A == 1 ? 2 : 1, false><<<dim3(gx, (unsigned)a.K), TPB, 0, st>>>(a);
+      // Blocks of 128 threads where the grid is a fraction of a wave (4096 x 10^5: 96 chunks x 2 blocks of 256 on
+      // 296 slots leave SMs with one block next to SMs with two; 4 blocks of 128: 1.121 -> 1.080 ms, 16384 x 40000:
+      // 1.623 -> 1.574; blocks of 64 the same). Above the limit (the second wave: two chunks, many blocks) 256.
+      if (a.N <= kTpMaxFull) {
+        constexpr int TPB = 128;
+        const unsigned gx = (unsigned)((a.N / 8 + TPB - 1) / TPB);
+        tp_spec_kernel<A, 8, A == 1 ? 2 : 1, TPB, A == 1 ? 4 : 2, false><<<dim3(gx, (unsigned)a.K), TPB, 0, st>>>(a);
+      } else {
+        constexpr int TPB = 256;
+        const unsigned gx = (unsigned)((a.N / 8 + TPB - 1) / TPB);
+        tp_spec_kernel<A, 8, A == 1 ? 2 : 1, TPB, A == 1 ? 2 : 1, false><<<dim3(gx, (unsigned)a.K), TPB, 0, st>>>(a);
+      }
     }
   } else {
     const unsigned gx = (unsigned)((a.N + BLOCK - 1) / BLOCK);
