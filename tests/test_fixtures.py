@@ -37,7 +37,7 @@ def test_fixture_file_is_what_the_exporter_writes():
 def test_fixture_file_is_well_formed():
     fx = load_golden("replay_fixtures.json")
     ids = [c["id"] for c in fx["cases"]]
-    assert len(ids) == len(set(ids)) and len(ids) >= 230
+    assert len(ids) == len(set(ids)) and len(ids) >= 254
     assert sum(c["source"].startswith("reference test") for c in fx["cases"]) == 10  # 6 loop + 4 clamp tests
     for c in fx["cases"]:
         T = len(c["depth"])
@@ -64,7 +64,7 @@ def test_kernels_reproduce_every_fixture(engine):
         pol = fixture_policy(c["policy"])
         rows = np.asarray(c["depth"], dtype=np.int64)
         T, A = rows.shape
-        N, ld = 35, 48
+        N, ld = (40, 48) if c["id"].startswith("steady-") else (35, 48)
         depth = np.zeros((T, A, ld), dtype=np.int64)
         depth[:, :, :N] = rows[:, :, None]
         fail = None
@@ -76,8 +76,14 @@ def test_kernels_reproduce_every_fixture(engine):
         want_r = np.asarray(c["replicas"], dtype=np.int32)
         want_e = np.asarray(c["events"], dtype=np.uint8)
         want_h = oracle_lib.traj_hash(want_r.reshape(T, 1), want_e.reshape(T, 1), T, 1, 1)[0]
+        # the long stretches also through the time-parallel paths, chunks forced (csrc/ksa_timepar.cu: closed
+        # forms for saturated / idle chunks, shifts for quiet ones), N = 40 so that the 256-bit kernels apply
+        chunked = c["id"].startswith("steady-")
         try:
-            for scalar in (False, True):
+            for scalar in (False, True, "chunks") if chunked else (False, True):
+                if scalar == "chunks":
+                    os.environ["KSA_TIMEPAR_CHUNKS"], os.environ["KSA_TIMEPAR_WARM"] = "5", "8"
+                    scalar = False
                 engine.set_variant(-2 if scalar else 0, -2 if scalar else 0)
                 st = engine.state_from_host(np.full(N, c["replicas0"], dtype=np.int32))
                 r, e = engine.replay_full(pol, d, T, A, N, ld, 0, st, fail=f)
@@ -92,3 +98,5 @@ def test_kernels_reproduce_every_fixture(engine):
                 assert (s["poll_failed"] == int((want_e == 0xC0).sum())).all(), (c["id"], scalar)
         finally:
             engine.set_variant(0, 0)
+            os.environ.pop("KSA_TIMEPAR_CHUNKS", None)
+            os.environ.pop("KSA_TIMEPAR_WARM", None)

@@ -8,8 +8,8 @@ clock and compares tick by tick; no CUDA and no cgo needed for that).
     python tools/export_fixtures.py --check    # exit 1 if the committed file differs
 
 Cases: the reference's 6 loop tests and 4 clamp tests (tests/golden/reference_kats.json), the
-hand-derived quirk vectors (tests/golden/derived_vectors.json), and 200 seeded random cases, half
-of them with injected call failures. Every case is computed by the C oracle's literal wall-clock
+hand-derived quirk vectors (tests/golden/derived_vectors.json), 200 seeded random cases, half
+of them with injected call failures, and 24 long saturated / idle / quiet stretches. Every case is computed by the C oracle's literal wall-clock
 restatement of Run (main.go:35-80) and, before it is written, required to agree with the oracle's
 tick model and with the independent Python restatement: three readings of the Go text. What the
 file cannot contain is the output of the Go code itself (no Go toolchain here): producing that
@@ -45,6 +45,7 @@ OUT = os.path.join(ROOT, "tests", "golden", "replay_fixtures.json")
 NAMES = policy_py.DEFAULT_ATTRIBUTE_NAMES
 SEED = 20261107
 N_RANDOM = 200
+N_STEADY = 24
 
 
 def policy_fields(pol: Policy) -> dict:
@@ -170,6 +171,42 @@ def build() -> dict:
         if i % 2 == 1:
             fail = rng.choice(np.array([0, 0, 0, 0, 0, 1, 2, 4, 3, 6, 7], dtype=np.uint8), size=T).tolist()
         cases.append(make_case(f"random-{i:03d}", f"seeded random case (seed {SEED})", pol, r0, rows, fail))
+    # Long stretches on one side of a threshold: the saturated queue (ScaleUp every cool-down period, replicas
+    # at max), the idle one (ScaleDown every period, at min), the quiet one (no call at all), and saturated
+    # with short dips. The scale calls of such a stretch come exactly one period apart, ceil(cool-down / poll
+    # period) ticks, with the phase of the first one: what the closed forms of csrc/ksa_timepar.cu rest on,
+    # so cool-downs that are not multiples of the poll period are in. (Own generator: the cases above keep
+    # their bytes.)
+    rng = np.random.default_rng(SEED + 1)
+    for i in range(N_STEADY):
+        poll = int(rng.choice([S, 5 * S, 7 * S]))
+        pol = Policy(attr_mask=1, poll_period=poll, scale_up_messages=100, scale_down_messages=10,
+                     max_pods=int(rng.integers(3, 9)), min_pods=int(rng.integers(0, 3)),
+                     scale_up_pods=int(rng.integers(1, 4)), scale_down_pods=int(rng.integers(1, 4)),
+                     scale_up_cool_down=int(rng.integers(0, 4 * poll)), scale_down_cool_down=int(rng.integers(0, 7 * poll)))
+        if i % 3 == 0:  # multiples of the poll period, the usual configuration (main.go:83-91: 5 s, 10 s, 30 s)
+            pol = Policy(attr_mask=1, poll_period=poll, scale_up_messages=100, scale_down_messages=10, max_pods=pol.max_pods,
+                         min_pods=pol.min_pods, scale_up_pods=pol.scale_up_pods, scale_down_pods=pol.scale_down_pods,
+                         scale_up_cool_down=int(rng.integers(0, 4)) * poll, scale_down_cool_down=int(rng.integers(0, 8)) * poll)
+        T = int(rng.integers(60, 161))
+        lead = int(rng.integers(0, 12))  # ordinary depths first: the stretch starts from some state and phase
+        kind = ("saturated", "idle", "quiet", "dips")[i % 4]
+        rows = [[int(rng.integers(0, 400))] for _ in range(lead)]
+        for t in range(T - lead):
+            if kind == "saturated":
+                rows.append([int(rng.integers(100, 900))])
+            elif kind == "idle":
+                rows.append([int(rng.integers(0, 11))])
+            elif kind == "quiet":
+                rows.append([int(rng.integers(11, 100))])
+            else:
+                rows.append([int(rng.integers(11, 100)) if rng.integers(0, 25) == 0 else int(rng.integers(100, 900))])
+        r0 = int(rng.integers(-2, 12))
+        fail = None
+        if i % 8 >= 6:  # a failed call takes no stamp: the next tick calls again, and the phase moves
+            fail = (rng.random(T) < 0.05).astype(np.uint8) * rng.choice(np.array([1, 2, 4], dtype=np.uint8), size=T)
+            fail = fail.tolist()
+        cases.append(make_case(f"steady-{i:02d}-{kind}", f"seeded {kind} stretch (seed {SEED + 1})", pol, r0, rows, fail))
     return {
         "_comment": "Generated by tools/export_fixtures.py; do not edit. Inputs and expected per-tick (replicas, event) of the "
                     "scaling policy, as computed by three restatements of main.go:35-80 / scale/scale.go:54-107 / "
